@@ -1,0 +1,353 @@
+// HBM-bound row kernels of the FastSpeech2 path: embedding + positional encoding + LayerNorm,
+// standalone LayerNorm, duration rounding, LengthRegulator (warp-scan prefix sum + vectorised
+// frame gather), bucketize + embedding add, mask -> length, fp32 -> bf16 cast.
+// All of them are sized so every warp moves 16-byte (or 8-byte for bf16x4) vectors, fully coalesced.
+#include "common.cuh"
+#include "../../include/ttsb200.h"
+
+namespace ttsb {
+
+// ------------------------------------------------------------------------------------------------
+// LayerNorm helpers: one warp per row, NV float4 per lane (D = 128*NV)
+// ------------------------------------------------------------------------------------------------
+template <int NV>
+__device__ __forceinline__ void warp_ln(float4 (&v)[NV], const float* __restrict__ g,
+                                        const float* __restrict__ b, float eps, int lane) {
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) s += v[i].x + v[i].y + v[i].z + v[i].w;
+  const float mean = warp_sum(s) * (1.f / (128.f * NV));
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const float a = v[i].x - mean, c = v[i].y - mean, d = v[i].z - mean, e = v[i].w - mean;
+    q += a * a + c * c + d * d + e * e;
+  }
+  const float rstd = rsqrtf(warp_sum(q) * (1.f / (128.f * NV)) + eps);
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const float4 gg = __ldg(reinterpret_cast<const float4*>(g) + i * 32 + lane);
+    const float4 bb = __ldg(reinterpret_cast<const float4*>(b) + i * 32 + lane);
+    v[i].x = fmaf((v[i].x - mean) * rstd, gg.x, bb.x);
+    v[i].y = fmaf((v[i].y - mean) * rstd, gg.y, bb.y);
+    v[i].z = fmaf((v[i].z - mean) * rstd, gg.z, bb.z);
+    v[i].w = fmaf((v[i].w - mean) * rstd, gg.w, bb.w);
+  }
+}
+
+__device__ __forceinline__ void store_bf16x4(__nv_bfloat16* dst, const float4& v) {
+  uint2 u;
+  u.x = pack_bf16(v.x, v.y);
+  u.y = pack_bf16(v.z, v.w);
+  *reinterpret_cast<uint2*>(dst) = u;
+}
+
+template <int NV>
+__global__ void __launch_bounds__(256)
+embed_pe_ln_kernel(const int64_t* __restrict__ ids, const float* __restrict__ table,
+                   const float* __restrict__ pe, const float* __restrict__ alpha,
+                   const float* __restrict__ g, const float* __restrict__ b, float eps,
+                   float* __restrict__ x0, __nv_bfloat16* __restrict__ xn, int64_t rows, int T, int V) {
+  constexpr int D = 128 * NV;
+  const int lane = threadIdx.x & 31;
+  const int64_t row = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int t = static_cast<int>(row % T);
+  int64_t id = ids[row];
+  if (id < 0 || id >= V) id = 0;  // the reference would raise; ids are validated on the host too
+  const float a = __ldg(alpha);
+  float4 v[NV];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const float4 e = __ldg(reinterpret_cast<const float4*>(table + id * D) + i * 32 + lane);
+    const float4 p = __ldg(reinterpret_cast<const float4*>(pe + static_cast<int64_t>(t) * D) + i * 32 + lane);
+    // separate multiply and add (no FMA contraction): bit-identical to `x + alpha * pe` (modules.py:110)
+    v[i] = make_float4(__fadd_rn(e.x, __fmul_rn(a, p.x)), __fadd_rn(e.y, __fmul_rn(a, p.y)),
+                       __fadd_rn(e.z, __fmul_rn(a, p.z)), __fadd_rn(e.w, __fmul_rn(a, p.w)));
+    reinterpret_cast<float4*>(x0 + row * D)[i * 32 + lane] = v[i];
+  }
+  warp_ln<NV>(v, g, b, eps, lane);
+#pragma unroll
+  for (int i = 0; i < NV; ++i) store_bf16x4(xn + row * D + (i * 32 + lane) * 4, v[i]);
+}
+
+template <int NV>
+__global__ void __launch_bounds__(256)
+layernorm_kernel(const float* __restrict__ x, const float* __restrict__ g, const float* __restrict__ b,
+                 float eps, __nv_bfloat16* __restrict__ y_bf16, float* __restrict__ y_f32, int64_t rows) {
+  constexpr int D = 128 * NV;
+  const int lane = threadIdx.x & 31;
+  const int64_t row = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  float4 v[NV];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) v[i] = __ldcs(reinterpret_cast<const float4*>(x + row * D) + i * 32 + lane);
+  warp_ln<NV>(v, g, b, eps, lane);
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    if (y_bf16) store_bf16x4(y_bf16 + row * D + (i * 32 + lane) * 4, v[i]);
+    if (y_f32) reinterpret_cast<float4*>(y_f32 + row * D)[i * 32 + lane] = v[i];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// duration rounding: clamp(round_half_even(exp(x) - 1), 0)
+// exp is evaluated in double and rounded once to fp32 (a correctly rounded fp32 exp), then the
+// reference's fp32 subtract and round-half-even (torch.round) follow.
+// ------------------------------------------------------------------------------------------------
+__global__ void round_durations_kernel(const float* __restrict__ log_d, int32_t* __restrict__ dur, int64_t n) {
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float e = static_cast<float>(exp(static_cast<double>(log_d[i])));
+  const float d = fmaxf(rintf(e - 1.0f), 0.f);
+  dur[i] = d > 2147483520.f ? 2147483647 : static_cast<int32_t>(d);
+}
+
+// ------------------------------------------------------------------------------------------------
+// LengthRegulator
+// ------------------------------------------------------------------------------------------------
+// One warp per utterance: inclusive prefix sum of max(dur,0) with a shuffle scan, 32 phonemes a step.
+__global__ void lr_scan_kernel(const int32_t* __restrict__ dur, int32_t* __restrict__ cum,
+                               int32_t* __restrict__ mel_len, int B, int L) {
+  const int lane = threadIdx.x & 31;
+  const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (b >= B) return;
+  int carry = 0;
+  for (int base = 0; base < L; base += 32) {
+    const int i = base + lane;
+    int v = (i < L) ? max(dur[static_cast<int64_t>(b) * L + i], 0) : 0;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += u;
+    }
+    v += carry;
+    if (i < L) cum[static_cast<int64_t>(b) * L + i] = v;
+    carry = __shfl_sync(0xffffffffu, v, 31);
+  }
+  if (lane == 0) mel_len[b] = carry;
+}
+
+constexpr int kLrFrames = 32;  // frames per CTA
+__global__ void __launch_bounds__(256)
+lr_expand_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict__ cum,
+                 const int32_t* __restrict__ mel_len, __nv_bfloat16* __restrict__ out,
+                 int32_t* __restrict__ frame_idx, int64_t* __restrict__ mel_pos,
+                 uint8_t* __restrict__ mel_mask, int L, int Tmax, int D) {
+  __shared__ int s_src[kLrFrames];
+  const int b = blockIdx.y;
+  const int t0 = blockIdx.x * kLrFrames;
+  const int len = min(mel_len[b], Tmax);
+  if (threadIdx.x < kLrFrames) {
+    const int t = t0 + threadIdx.x;
+    int src = -1;
+    if (t < len) {
+      // first phoneme whose inclusive cumulative duration exceeds t
+      const int32_t* c = cum + static_cast<int64_t>(b) * L;
+      int lo = 0, hi = L - 1;
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(c + mid) > t) hi = mid; else lo = mid + 1;
+      }
+      src = lo;
+    }
+    s_src[threadIdx.x] = src;
+    if (t < Tmax) {
+      const int64_t o = static_cast<int64_t>(b) * Tmax + t;
+      if (frame_idx) frame_idx[o] = src;
+      if (mel_pos) mel_pos[o] = (t < len) ? t + 1 : 0;
+      if (mel_mask) mel_mask[o] = (t < len || t == 0) ? 1 : 0;  // `arange <= mel_pos` (varianceadaptor.py:257)
+    }
+  }
+  __syncthreads();
+  const int chunks = D >> 3;  // 16-byte chunks per row
+  const int total = kLrFrames * chunks;
+  for (int c = threadIdx.x; c < total; c += blockDim.x) {
+    const int f = c / chunks;
+    const int k = c - f * chunks;
+    const int t = t0 + f;
+    if (t >= Tmax) break;
+    const int src = s_src[f];
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (src >= 0) v = __ldg(reinterpret_cast<const uint4*>(x + (static_cast<int64_t>(b) * L + src) * D) + k);
+    __stcs(reinterpret_cast<uint4*>(out + (static_cast<int64_t>(b) * Tmax + t) * D) + k, v);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// bucketize (right=False -> lower_bound) + two embedding gathers + add; warp per row
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int lower_bound_f32(const float* __restrict__ bins, int nb, float v) {
+  int lo = 0, hi = nb;  // answer in [0, nb]
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (__ldg(bins + mid) >= v) hi = mid; else lo = mid + 1;
+  }
+  return lo;
+}
+
+template <int NV>
+__global__ void __launch_bounds__(256)
+bucket_embed_add_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ p,
+                        const float* __restrict__ e, const float* __restrict__ pbins,
+                        const float* __restrict__ ebins, const float* __restrict__ ptab,
+                        const float* __restrict__ etab, __nv_bfloat16* __restrict__ out,
+                        int32_t* __restrict__ p_idx, int32_t* __restrict__ e_idx, int64_t rows, int nb) {
+  constexpr int D = 128 * NV;
+  const int lane = threadIdx.x & 31;
+  const int64_t row = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int pi = lower_bound_f32(pbins, nb, __ldg(p + row));
+  const int ei = lower_bound_f32(ebins, nb, __ldg(e + row));
+  if (lane == 0) {
+    if (p_idx) p_idx[row] = pi;
+    if (e_idx) e_idx[row] = ei;
+  }
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = i * 32 + lane;  // 4-element chunk
+    const uint2 xv = __ldcs(reinterpret_cast<const uint2*>(x + row * D) + c);
+    const float2 x01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&xv.x));
+    const float2 x23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&xv.y));
+    const float4 a = __ldg(reinterpret_cast<const float4*>(ptab + static_cast<int64_t>(pi) * D) + c);
+    const float4 bq = __ldg(reinterpret_cast<const float4*>(etab + static_cast<int64_t>(ei) * D) + c);
+    // the reference adds pitch first, then energy (varianceadaptor.py:123-126)
+    const float4 r = make_float4((x01.x + a.x) + bq.x, (x01.y + a.y) + bq.y, (x23.x + a.z) + bq.z,
+                                 (x23.y + a.w) + bq.w);
+    store_bf16x4(out + row * D + c * 4, r);
+  }
+}
+
+__global__ void mask_lengths_kernel(const uint8_t* __restrict__ mask, int32_t* __restrict__ kv_len, int B, int T) {
+  const int lane = threadIdx.x & 31;
+  const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (b >= B) return;
+  int last = 0;
+  for (int t = lane; t < T; t += 32)
+    if (mask[static_cast<int64_t>(b) * T + t]) last = t + 1;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) last = max(last, __shfl_xor_sync(0xffffffffu, last, o));
+  if (lane == 0) kv_len[b] = last;
+}
+
+__global__ void cast_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, int64_t n) {
+  const int64_t i = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) * 4;
+  if (i + 3 < n) {
+    const float4 v = *reinterpret_cast<const float4*>(x + i);
+    store_bf16x4(y + i, v);
+  } else {
+    for (int64_t j = i; j < n; ++j) y[j] = __float2bfloat16(x[j]);
+  }
+}
+
+}  // namespace ttsb
+
+using namespace ttsb;
+
+#define TTSB_LAUNCH_CHECK() TTSB_CHECK_CUDA(cudaGetLastError())
+
+extern "C" int ttsb200_mask_lengths(const uint8_t* mask, int32_t* kv_len, int32_t B, int32_t T,
+                                    ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(mask && kv_len && B > 0 && T > 0, "mask_lengths: bad args");
+  mask_lengths_kernel<<<(B + 7) / 8, 256, 0, static_cast<cudaStream_t>(s)>>>(mask, kv_len, B, T);
+  TTSB_LAUNCH_CHECK();
+  return TTSB_OK;
+}
+
+extern "C" int ttsb200_embed_pe_ln(const int64_t* ids, const float* table, const float* pe,
+                                   const float* alpha, const float* g, const float* b, float eps,
+                                   float* x0, void* xn, int32_t B, int32_t T, int32_t D, int32_t V,
+                                   ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(ids && table && pe && alpha && g && b && x0 && xn, "embed_pe_ln: null pointer");
+  TTSB_CHECK_ARG(B > 0 && T > 0 && V > 0, "embed_pe_ln: bad dims");
+  const int64_t rows = static_cast<int64_t>(B) * T;
+  const unsigned grid = static_cast<unsigned>((rows + 7) / 8);
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  if (D == 384)
+    embed_pe_ln_kernel<3><<<grid, 256, 0, st>>>(ids, table, pe, alpha, g, b, eps, x0,
+                                                static_cast<__nv_bfloat16*>(xn), rows, T, V);
+  else if (D == 256)
+    embed_pe_ln_kernel<2><<<grid, 256, 0, st>>>(ids, table, pe, alpha, g, b, eps, x0,
+                                                static_cast<__nv_bfloat16*>(xn), rows, T, V);
+  else
+    TTSB_CHECK_ARG(false, "embed_pe_ln: D=%d unsupported (256 or 384)", D);
+  TTSB_LAUNCH_CHECK();
+  return TTSB_OK;
+}
+
+extern "C" int ttsb200_layernorm(const float* x, const float* g, const float* b, float eps, void* y_bf16,
+                                 float* y_f32, int64_t rows, int32_t D, ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(x && g && b && (y_bf16 || y_f32) && rows > 0, "layernorm: bad args");
+  const unsigned grid = static_cast<unsigned>((rows + 7) / 8);
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  if (D == 384)
+    layernorm_kernel<3><<<grid, 256, 0, st>>>(x, g, b, eps, static_cast<__nv_bfloat16*>(y_bf16), y_f32, rows);
+  else if (D == 256)
+    layernorm_kernel<2><<<grid, 256, 0, st>>>(x, g, b, eps, static_cast<__nv_bfloat16*>(y_bf16), y_f32, rows);
+  else
+    TTSB_CHECK_ARG(false, "layernorm: D=%d unsupported (256 or 384)", D);
+  TTSB_LAUNCH_CHECK();
+  return TTSB_OK;
+}
+
+extern "C" int ttsb200_round_durations(const float* log_d, int32_t* dur, int64_t n, ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(log_d && dur && n > 0, "round_durations: bad args");
+  round_durations_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(s)>>>(
+      log_d, dur, n);
+  TTSB_LAUNCH_CHECK();
+  return TTSB_OK;
+}
+
+extern "C" int ttsb200_lr_scan(const int32_t* dur, int32_t* cum, int32_t* mel_len, int32_t B, int32_t L,
+                               ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(dur && cum && mel_len && B > 0 && L > 0, "lr_scan: bad args");
+  lr_scan_kernel<<<(B + 3) / 4, 128, 0, static_cast<cudaStream_t>(s)>>>(dur, cum, mel_len, B, L);
+  TTSB_LAUNCH_CHECK();
+  return TTSB_OK;
+}
+
+extern "C" int ttsb200_lr_expand(const void* x, const int32_t* cum, const int32_t* mel_len, void* out,
+                                 int32_t* frame_idx, int64_t* mel_pos, uint8_t* mel_mask, int32_t B,
+                                 int32_t L, int32_t Tmax, int32_t D, ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(x && cum && mel_len && out && B > 0 && L > 0 && Tmax > 0, "lr_expand: bad args");
+  TTSB_CHECK_ARG(D % 8 == 0, "lr_expand: D (%d) must be a multiple of 8", D);
+  dim3 grid((Tmax + kLrFrames - 1) / kLrFrames, B);
+  lr_expand_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(s)>>>(
+      static_cast<const __nv_bfloat16*>(x), cum, mel_len, static_cast<__nv_bfloat16*>(out), frame_idx,
+      mel_pos, mel_mask, L, Tmax, D);
+  TTSB_LAUNCH_CHECK();
+  return TTSB_OK;
+}
+
+extern "C" int ttsb200_bucket_embed_add(const void* x, const float* p, const float* e,
+                                        const float* pbins, const float* ebins, const float* ptab,
+                                        const float* etab, void* out, int32_t* p_idx, int32_t* e_idx,
+                                        int64_t rows, int32_t D, int32_t nb, ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(x && p && e && pbins && ebins && ptab && etab && out && rows > 0 && nb > 0,
+                 "bucket_embed_add: bad args");
+  const unsigned grid = static_cast<unsigned>((rows + 7) / 8);
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  if (D == 384)
+    bucket_embed_add_kernel<3><<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), p, e, pbins,
+                                                     ebins, ptab, etab, static_cast<__nv_bfloat16*>(out),
+                                                     p_idx, e_idx, rows, nb);
+  else if (D == 256)
+    bucket_embed_add_kernel<2><<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), p, e, pbins,
+                                                     ebins, ptab, etab, static_cast<__nv_bfloat16*>(out),
+                                                     p_idx, e_idx, rows, nb);
+  else
+    TTSB_CHECK_ARG(false, "bucket_embed_add: D=%d unsupported (256 or 384)", D);
+  TTSB_LAUNCH_CHECK();
+  return TTSB_OK;
+}
+
+extern "C" int ttsb200_cast_bf16(const float* x, void* y, int64_t n, ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(x && y && n > 0, "cast_bf16: bad args");
+  TTSB_CHECK_ARG((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(y) & 7) == 0,
+                 "cast_bf16: alignment");
+  const int64_t thr = (n + 3) / 4;
+  cast_bf16_kernel<<<static_cast<unsigned>((thr + 255) / 256), 256, 0, static_cast<cudaStream_t>(s)>>>(
+      x, static_cast<__nv_bfloat16*>(y), n);
+  TTSB_LAUNCH_CHECK();
+  return TTSB_OK;
+}

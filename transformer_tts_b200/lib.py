@@ -1,0 +1,267 @@
+"""ctypes binding of ``csrc/libttsb200.so`` (C ABI in ``include/ttsb200.h``).
+
+Thin, typed wrappers that take torch CUDA tensors, validate dtype / contiguity / device in Python
+and pass raw device pointers plus the current CUDA stream.  There is NO fallback: if the library is
+missing or a call fails, a RuntimeError is raised with ``ttsb200_last_error_string()``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+from typing import Optional
+
+import torch
+
+from . import _build
+
+EPI_AFFINE_ACT, EPI_RES_LN, EPI_FFN2, EPI_RELU_LN, EPI_RELU_LN_DOT = range(5)
+ACT_NONE, ACT_RELU, ACT_TANH = range(3)
+
+LAUNCH_COUNT = 0  # kernels launched through this binding (bench.py reports it as gpu_launches)
+
+
+class GemmArgs(C.Structure):
+    _fields_ = [
+        ("B", C.c_int32), ("T", C.c_int32), ("N", C.c_int32), ("C", C.c_int32),
+        ("taps", C.c_int32), ("pad_left", C.c_int32), ("block_n", C.c_int32),
+        ("epi", C.c_int32), ("act", C.c_int32),
+        ("x", C.c_void_p), ("ldx", C.c_int64), ("w", C.c_void_p),
+        ("bias", C.c_void_p), ("scale", C.c_void_p), ("res_f32", C.c_void_p),
+        ("res_bstride", C.c_int64), ("res_tstride", C.c_int64),
+        ("res_scale", C.c_void_p), ("res_bf16", C.c_void_p),
+        ("ln1_g", C.c_void_p), ("ln1_b", C.c_void_p), ("ln2_g", C.c_void_p), ("ln2_b", C.c_void_p),
+        ("eps", C.c_float),
+        ("dot_w", C.c_void_p), ("dot_b", C.c_void_p), ("row_mask", C.c_void_p),
+        ("out_f32", C.c_void_p), ("out_bf16", C.c_void_p), ("out2_f32", C.c_void_p),
+        ("out_row", C.c_void_p),
+    ]
+
+
+_LIB: Optional[C.CDLL] = None
+
+_SIGNATURES = {
+    "ttsb200_version": ([], C.c_int),
+    "ttsb200_last_error_string": ([], C.c_char_p),
+    "ttsb200_conv_gemm": ([C.POINTER(GemmArgs), C.c_void_p], C.c_int),
+    "ttsb200_attention_fwd": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
+                               C.c_int32, C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_attention_probs": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
+                                 C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_mask_lengths": ([C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_embed_pe_ln": ([C.c_void_p] * 6 + [C.c_float, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
+                                                 C.c_int32, C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_layernorm": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p,
+                           C.c_int64, C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_round_durations": ([C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p], C.c_int),
+    "ttsb200_lr_scan": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_lr_expand": ([C.c_void_p] * 7 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
+    "ttsb200_bucket_embed_add": ([C.c_void_p] * 10 + [C.c_int64, C.c_int32, C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_cast_bf16": ([C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p], C.c_int),
+}
+
+EXPORTED_SYMBOLS = tuple(_SIGNATURES)
+
+
+def lib_path() -> Path:
+    return _build.LIB_PATH
+
+
+def load() -> C.CDLL:
+    """Load the shared library (building it if the sources are newer).  Raises if impossible."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = _build.LIB_PATH
+    if _build.is_stale():
+        try:
+            _build.build()
+        except Exception as e:  # no nvcc on the GPU box is fine as long as a built .so travelled
+            if not path.exists():
+                raise RuntimeError(f"libttsb200.so is missing and cannot be built: {e}") from e
+    lib = C.CDLL(str(path))
+    for name, (argtypes, restype) in _SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is missing: fail loudly
+        fn.argtypes = argtypes
+        fn.restype = restype
+    _LIB = lib
+    return lib
+
+
+def _check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = load().ttsb200_last_error_string().decode()
+        raise RuntimeError(f"ttsb200 {what} failed (rc={rc}): {msg}")
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor], dtype=None, name: str = "tensor") -> Optional[int]:
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError(f"ttsb200: {name} must be a CUDA tensor (there is no CPU path)")
+    if dtype is not None and t.dtype != dtype:
+        raise TypeError(f"ttsb200: {name} must be {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise ValueError(f"ttsb200: {name} must be contiguous")
+    return t.data_ptr()
+
+
+def _count(n: int = 1) -> None:
+    global LAUNCH_COUNT
+    LAUNCH_COUNT += n
+
+
+# --------------------------------------------------------------------------------------------------
+# GEMM / conv
+# --------------------------------------------------------------------------------------------------
+def conv_gemm(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, *, taps: int = 1, pad_left: int = 0,
+              block_n: int, epi: int = EPI_AFFINE_ACT, act: int = ACT_NONE,
+              scale: Optional[torch.Tensor] = None,
+              res_f32: Optional[torch.Tensor] = None, res_bstride: int = 0, res_tstride: int = 0,
+              res_scale: Optional[torch.Tensor] = None, res_bf16: Optional[torch.Tensor] = None,
+              ln1: Optional[tuple] = None, ln2: Optional[tuple] = None, eps: float = 1e-5,
+              dot_w: Optional[torch.Tensor] = None, dot_b: Optional[torch.Tensor] = None,
+              row_mask: Optional[torch.Tensor] = None,
+              out_f32: Optional[torch.Tensor] = None, out_bf16: Optional[torch.Tensor] = None,
+              out2_f32: Optional[torch.Tensor] = None, out_row: Optional[torch.Tensor] = None) -> None:
+    """x: bf16 (B,T,C); w: bf16 (taps,N,C).  See include/ttsb200.h for the epilogue modes."""
+    B, T, Cin = x.shape
+    tw, N, Cw = w.shape
+    if tw != taps or Cw != Cin:
+        raise ValueError(f"conv_gemm: weight {tuple(w.shape)} does not match taps={taps}, C={Cin}")
+    a = GemmArgs()
+    a.B, a.T, a.N, a.C, a.taps, a.pad_left, a.block_n, a.epi, a.act = B, T, N, Cin, taps, pad_left, block_n, epi, act
+    a.x = _ptr(x, torch.bfloat16, "x"); a.ldx = Cin
+    a.w = _ptr(w, torch.bfloat16, "w")
+    a.bias = _ptr(bias, torch.float32, "bias")
+    a.scale = _ptr(scale, torch.float32, "scale")
+    a.res_f32 = _ptr(res_f32, torch.float32, "res_f32")
+    a.res_bstride, a.res_tstride = res_bstride, res_tstride
+    a.res_scale = _ptr(res_scale, torch.float32, "res_scale")
+    a.res_bf16 = _ptr(res_bf16, torch.bfloat16, "res_bf16")
+    if ln1 is not None:
+        a.ln1_g, a.ln1_b = _ptr(ln1[0], torch.float32, "ln1.weight"), _ptr(ln1[1], torch.float32, "ln1.bias")
+    if ln2 is not None:
+        a.ln2_g, a.ln2_b = _ptr(ln2[0], torch.float32, "ln2.weight"), _ptr(ln2[1], torch.float32, "ln2.bias")
+    a.eps = eps
+    a.dot_w = _ptr(dot_w, torch.float32, "dot_w")
+    a.dot_b = _ptr(dot_b, torch.float32, "dot_b")
+    a.row_mask = _ptr(row_mask, torch.uint8, "row_mask")
+    a.out_f32 = _ptr(out_f32, torch.float32, "out_f32")
+    a.out_bf16 = _ptr(out_bf16, torch.bfloat16, "out_bf16")
+    a.out2_f32 = _ptr(out2_f32, torch.float32, "out2_f32")
+    a.out_row = _ptr(out_row, torch.float32, "out_row")
+    _check(load().ttsb200_conv_gemm(C.byref(a), _stream()), "conv_gemm")
+    _count()
+
+
+# --------------------------------------------------------------------------------------------------
+# attention
+# --------------------------------------------------------------------------------------------------
+def attention_fwd(qkv: torch.Tensor, mask: torch.Tensor, kv_len: torch.Tensor, ctx: torch.Tensor, H: int) -> None:
+    B, T, W = qkv.shape
+    Dh = W // (3 * H)
+    _check(load().ttsb200_attention_fwd(_ptr(qkv, torch.bfloat16, "qkv"), _ptr(mask, torch.uint8, "mask"),
+                                        _ptr(kv_len, torch.int32, "kv_len"), _ptr(ctx, torch.bfloat16, "ctx"),
+                                        B, T, H, Dh, _stream()), "attention_fwd")
+    _count()
+
+
+def attention_probs(qkv: torch.Tensor, mask: torch.Tensor, H: int) -> torch.Tensor:
+    B, T, W = qkv.shape
+    Dh = W // (3 * H)
+    probs = torch.empty((B, H, T, T), device=qkv.device, dtype=torch.float32)
+    _check(load().ttsb200_attention_probs(_ptr(qkv, torch.bfloat16, "qkv"), _ptr(mask, torch.uint8, "mask"),
+                                          _ptr(probs), B, T, H, Dh, _stream()), "attention_probs")
+    _count()
+    return probs
+
+
+# --------------------------------------------------------------------------------------------------
+# row kernels
+# --------------------------------------------------------------------------------------------------
+def mask_lengths(mask: torch.Tensor) -> torch.Tensor:
+    B, T = mask.shape
+    out = torch.empty((B,), device=mask.device, dtype=torch.int32)
+    _check(load().ttsb200_mask_lengths(_ptr(mask, torch.uint8, "mask"), _ptr(out), B, T, _stream()), "mask_lengths")
+    _count()
+    return out
+
+
+def embed_pe_ln(ids, table, pe, alpha, g, b, eps, x0, xn) -> None:
+    B, T = ids.shape
+    V, D = table.shape
+    if pe.shape[0] < T or pe.shape[1] != D:
+        raise ValueError(f"embed_pe_ln: positional table {tuple(pe.shape)} too small for T={T}, D={D}")
+    _check(load().ttsb200_embed_pe_ln(_ptr(ids, torch.int64, "ids"), _ptr(table, torch.float32, "table"),
+                                      _ptr(pe, torch.float32, "pe"), _ptr(alpha, torch.float32, "alpha"),
+                                      _ptr(g, torch.float32, "g"), _ptr(b, torch.float32, "b"), eps,
+                                      _ptr(x0, torch.float32, "x0"), _ptr(xn, torch.bfloat16, "xn"),
+                                      B, T, D, V, _stream()), "embed_pe_ln")
+    _count()
+
+
+def layernorm(x, g, b, eps, y_bf16=None, y_f32=None) -> None:
+    D = x.shape[-1]
+    rows = x.numel() // D
+    _check(load().ttsb200_layernorm(_ptr(x, torch.float32, "x"), _ptr(g, torch.float32, "g"),
+                                    _ptr(b, torch.float32, "b"), eps, _ptr(y_bf16, torch.bfloat16, "y_bf16"),
+                                    _ptr(y_f32, torch.float32, "y_f32"), rows, D, _stream()), "layernorm")
+    _count()
+
+
+def round_durations(log_d: torch.Tensor) -> torch.Tensor:
+    out = torch.empty(log_d.shape, device=log_d.device, dtype=torch.int32)
+    _check(load().ttsb200_round_durations(_ptr(log_d, torch.float32, "log_d"), _ptr(out), log_d.numel(), _stream()),
+           "round_durations")
+    _count()
+    return out
+
+
+def lr_scan(dur: torch.Tensor):
+    B, L = dur.shape
+    cum = torch.empty((B, L), device=dur.device, dtype=torch.int32)
+    mel_len = torch.empty((B,), device=dur.device, dtype=torch.int32)
+    _check(load().ttsb200_lr_scan(_ptr(dur, torch.int32, "dur"), _ptr(cum), _ptr(mel_len), B, L, _stream()), "lr_scan")
+    _count()
+    return cum, mel_len
+
+
+def lr_expand(x: torch.Tensor, cum: torch.Tensor, mel_len: torch.Tensor, Tmax: int, want_aux: bool = True):
+    B, L, D = x.shape
+    dev = x.device
+    out = torch.empty((B, Tmax, D), device=dev, dtype=torch.bfloat16)
+    frame_idx = torch.empty((B, Tmax), device=dev, dtype=torch.int32) if want_aux else None
+    mel_pos = torch.empty((B, Tmax), device=dev, dtype=torch.int64) if want_aux else None
+    mel_mask = torch.empty((B, Tmax), device=dev, dtype=torch.uint8)
+    _check(load().ttsb200_lr_expand(_ptr(x, torch.bfloat16, "x"), _ptr(cum, torch.int32, "cum"),
+                                    _ptr(mel_len, torch.int32, "mel_len"), _ptr(out), _ptr(frame_idx),
+                                    _ptr(mel_pos), _ptr(mel_mask), B, L, Tmax, D, _stream()), "lr_expand")
+    _count()
+    return out, frame_idx, mel_pos, mel_mask
+
+
+def bucket_embed_add(x, p, e, pbins, ebins, ptab, etab, want_idx: bool = False):
+    D = x.shape[-1]
+    rows = x.numel() // D
+    out = torch.empty_like(x)
+    p_idx = torch.empty(p.shape, device=x.device, dtype=torch.int32) if want_idx else None
+    e_idx = torch.empty(e.shape, device=x.device, dtype=torch.int32) if want_idx else None
+    _check(load().ttsb200_bucket_embed_add(_ptr(x, torch.bfloat16, "x"), _ptr(p, torch.float32, "p"),
+                                           _ptr(e, torch.float32, "e"), _ptr(pbins, torch.float32, "pitch_bins"),
+                                           _ptr(ebins, torch.float32, "energy_bins"),
+                                           _ptr(ptab, torch.float32, "pitch_table"),
+                                           _ptr(etab, torch.float32, "energy_table"), _ptr(out), _ptr(p_idx),
+                                           _ptr(e_idx), rows, D, pbins.numel(), _stream()), "bucket_embed_add")
+    _count()
+    return out, p_idx, e_idx
+
+
+def cast_bf16(x: torch.Tensor) -> torch.Tensor:
+    y = torch.empty(x.shape, device=x.device, dtype=torch.bfloat16)
+    _check(load().ttsb200_cast_bf16(_ptr(x, torch.float32, "x"), _ptr(y), x.numel(), _stream()), "cast_bf16")
+    _count()
+    return y
