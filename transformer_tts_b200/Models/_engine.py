@@ -1,0 +1,237 @@
+"""Kernel-sequencing helpers shared by the drop-in modules.
+
+Holds the derived (bf16, re-laid-out, fused) weight caches and the functions that chain the
+sm_100a kernels of ``csrc/`` for one FFT block, one variance predictor and the PostNet.  The
+``state_dict`` stays in the reference layout (fp32, Conv1d weights (out,in,k), separate q/k/v);
+caches are rebuilt whenever a source parameter's storage or version counter changes
+(``load_state_dict`` and optimizer steps both bump ``Tensor._version``).
+
+Inference (eval, no autograd) only; the training path is not built yet and raises.
+"""
+from __future__ import annotations
+
+from functools import lru_cache
+from typing import Optional, Sequence
+
+import numpy as np
+import torch
+
+from .. import lib
+
+LN_EPS = 1e-5
+BN_EPS = 1e-5
+
+
+# --------------------------------------------------------------------------------------------------
+# positional table (Models/modules.py:97-105): exponents 2*i/d for sin (i already even) and
+# 2*(i+1)/d for cos, float64 math stored as fp32.  Vectorised here; tests check it bit-for-bit
+# against the oracle's scalar restatement of the reference loop.
+# --------------------------------------------------------------------------------------------------
+@lru_cache(maxsize=4)
+def positional_table_cpu(d_model: int, max_seq_len: int = 5000) -> torch.Tensor:
+    pos = np.arange(max_seq_len, dtype=np.float64)[:, None]
+    i = np.arange(0, d_model, 2, dtype=np.float64)[None, :]
+    pe = np.zeros((max_seq_len, d_model), dtype=np.float64)
+    pe[:, 0::2] = np.sin(pos / np.power(10000.0, (2 * i) / d_model))
+    pe[:, 1::2] = np.cos(pos / np.power(10000.0, (2 * (i + 1)) / d_model))
+    return torch.from_numpy(pe).to(torch.float32)
+
+
+_PE_DEVICE = {}
+
+
+def positional_table(d_model: int, device: torch.device, max_seq_len: int = 5000) -> torch.Tensor:
+    key = (d_model, max_seq_len, str(device))
+    t = _PE_DEVICE.get(key)
+    if t is None:
+        t = positional_table_cpu(d_model, max_seq_len).to(device).contiguous()
+        _PE_DEVICE[key] = t
+    return t
+
+
+# --------------------------------------------------------------------------------------------------
+# guards
+# --------------------------------------------------------------------------------------------------
+def require_inference(module: torch.nn.Module, what: str) -> None:
+    if module.training:
+        raise NotImplementedError(
+            f"{what}: only the inference path (model.eval()) is built on the sm_100a kernels so far; "
+            "the training step (backward kernels, SyncBatchNorm statistics) is not implemented")
+
+
+def require_cuda(t: torch.Tensor, what: str) -> None:
+    if not t.is_cuda:
+        raise RuntimeError(f"{what}: tensors must live on a CUDA device — this package has no CPU path")
+
+
+def mask_to_u8(mask: Optional[torch.Tensor], B: int, T: int, device) -> torch.Tensor:
+    """(B,1,T) / (B,T) bool-like -> contiguous uint8 (B,T); None -> all valid."""
+    if mask is None:
+        return torch.ones((B, T), dtype=torch.uint8, device=device)
+    if mask.dim() == 3:
+        if mask.shape[1] != 1:
+            raise NotImplementedError("only key-padding masks (B,1,T) are supported (fix_mask is out of scope)")
+        mask = mask[:, 0]
+    if tuple(mask.shape) != (B, T):
+        raise ValueError(f"mask shape {tuple(mask.shape)} does not match (B={B}, T={T})")
+    return (mask != 0).to(torch.uint8).contiguous()
+
+
+def _sig(params: Sequence[torch.Tensor]):
+    return tuple((p.data_ptr(), p._version) for p in params)
+
+
+def _bf16(w: torch.Tensor) -> torch.Tensor:
+    return w.detach().to(torch.bfloat16).contiguous()
+
+
+def _f32(w: torch.Tensor) -> torch.Tensor:
+    return w.detach().to(torch.float32).contiguous()
+
+
+def conv_w_to_taps(w: torch.Tensor) -> torch.Tensor:
+    """Conv1d weight (out, in, k) -> bf16 (k, out, in): one K-major GEMM operand per tap."""
+    return _bf16(w.detach().permute(2, 0, 1))
+
+
+class Cache:
+    """Per-module derived tensors with a staleness signature."""
+
+    def __init__(self):
+        self.sig = None
+        self.t = {}
+
+    def stale(self, params) -> bool:
+        return self.sig != _sig(params)
+
+    def commit(self, params) -> None:
+        self.sig = _sig(params)
+
+
+# --------------------------------------------------------------------------------------------------
+# FFT block (Models/layers.py:29-41) = 4 GEMM launches + 1 attention launch
+# --------------------------------------------------------------------------------------------------
+def layer_cache(layer) -> dict:
+    c: Cache = layer._ttsb_cache
+    a, ff = layer.attn, layer.ff
+    params = [a.q_linear.weight, a.q_linear.bias, a.k_linear.weight, a.k_linear.bias, a.v_linear.weight,
+              a.v_linear.bias, a.out.weight, a.out.bias, ff.f_1.weight, ff.f_1.bias, ff.f_2.weight, ff.f_2.bias,
+              ff.layer_norm.weight, ff.layer_norm.bias, layer.norm_1.weight, layer.norm_1.bias,
+              layer.norm_2.weight, layer.norm_2.bias]
+    if c.stale(params):
+        if a.concat_after:
+            raise NotImplementedError("concat_after=True is not supported (hparams default is False)")
+        t = c.t
+        t["wqkv"] = _bf16(torch.cat([a.q_linear.weight, a.k_linear.weight, a.v_linear.weight], 0)).unsqueeze(0).contiguous()
+        t["bqkv"] = _f32(torch.cat([a.q_linear.bias, a.k_linear.bias, a.v_linear.bias], 0))
+        t["wo"] = _bf16(a.out.weight).unsqueeze(0).contiguous()
+        t["bo"] = _f32(a.out.bias)
+        t["w1"] = conv_w_to_taps(ff.f_1.weight)
+        t["b1"] = _f32(ff.f_1.bias)
+        t["w2"] = conv_w_to_taps(ff.f_2.weight)
+        t["b2"] = _f32(ff.f_2.bias)
+        t["ln_ff"] = (_f32(ff.layer_norm.weight), _f32(ff.layer_norm.bias))
+        t["ln1"] = (_f32(layer.norm_1.weight), _f32(layer.norm_1.bias))
+        t["ln2"] = (_f32(layer.norm_2.weight), _f32(layer.norm_2.bias))
+        t["k"] = ff.f_1.weight.shape[-1]
+        c.commit(params)
+    return c.t
+
+
+def run_fft_block(t: dict, heads: int, x: torch.Tensor, xn: torch.Tensor, mask_u8: torch.Tensor,
+                  kv_len: torch.Tensor, next_ln, want_norm_f32: bool = False):
+    """x: fp32 residual stream (B,T,D); xn = norm_1(x) in bf16.  Returns (x', LN_next(x') bf16[, fp32])."""
+    B, T, D = x.shape
+    dev = x.device
+    k = t["k"]
+    qkv = torch.empty((B, T, 3 * D), device=dev, dtype=torch.bfloat16)
+    lib.conv_gemm(xn, t["wqkv"], t["bqkv"], block_n=128, out_bf16=qkv)  # modules.py:49-51
+    ctx = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
+    lib.attention_fwd(qkv, mask_u8, kv_len, ctx, heads)  # modules.py:7-21,58-65
+    y = torch.empty((B, T, D), device=dev, dtype=torch.float32)
+    yn = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
+    lib.conv_gemm(ctx, t["wo"], t["bo"], block_n=D, epi=lib.EPI_RES_LN, res_f32=x, res_bstride=T * D,
+                  res_tstride=D, ln1=t["ln2"], out_f32=y, out_bf16=yn)  # modules.py:68 + layers.py:33,35
+    h = torch.empty((B, T, 4 * D), device=dev, dtype=torch.bfloat16)
+    lib.conv_gemm(yn, t["w1"], t["b1"], taps=k, pad_left=k // 2, block_n=256, act=lib.ACT_RELU, out_bf16=h)  # modules.py:83
+    z = torch.empty((B, T, D), device=dev, dtype=torch.float32)
+    zn = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
+    zn32 = torch.empty((B, T, D), device=dev, dtype=torch.float32) if want_norm_f32 else None
+    lib.conv_gemm(h, t["w2"], t["b2"], taps=k, pad_left=k // 2, block_n=D, epi=lib.EPI_FFN2, res_bf16=yn,
+                  res_f32=y, res_bstride=T * D, res_tstride=D, ln1=t["ln_ff"], ln2=next_ln, out_f32=z,
+                  out_bf16=zn, out2_f32=zn32)  # modules.py:84-87 + layers.py:40 + next norm
+    return z, zn, zn32
+
+
+# --------------------------------------------------------------------------------------------------
+# VariancePredictor (Models/varianceadaptor.py:216-231) = 2 GEMM launches
+# --------------------------------------------------------------------------------------------------
+def predictor_cache(pred) -> dict:
+    c: Cache = pred._ttsb_cache
+    params = [pred.conv1.weight, pred.conv1.bias, pred.layer_norm1.weight, pred.layer_norm1.bias,
+              pred.conv2.weight, pred.conv2.bias, pred.layer_norm2.weight, pred.layer_norm2.bias,
+              pred.linear_layer.weight, pred.linear_layer.bias]
+    if c.stale(params):
+        t = c.t
+        t["w1"], t["b1"] = conv_w_to_taps(pred.conv1.weight), _f32(pred.conv1.bias)
+        t["w2"], t["b2"] = conv_w_to_taps(pred.conv2.weight), _f32(pred.conv2.bias)
+        t["ln1"] = (_f32(pred.layer_norm1.weight), _f32(pred.layer_norm1.bias))
+        t["ln2"] = (_f32(pred.layer_norm2.weight), _f32(pred.layer_norm2.bias))
+        t["dw"] = _f32(pred.linear_layer.weight.reshape(-1))
+        t["db"] = _f32(pred.linear_layer.bias.reshape(-1))
+        c.commit(params)
+    return c.t
+
+
+def run_predictor(t: dict, x_bf16: torch.Tensor, mask_u8: Optional[torch.Tensor]) -> torch.Tensor:
+    B, T, _ = x_bf16.shape
+    fs = t["b1"].numel()
+    dev = x_bf16.device
+    h = torch.empty((B, T, fs), device=dev, dtype=torch.bfloat16)
+    lib.conv_gemm(x_bf16, t["w1"], t["b1"], taps=3, pad_left=1, block_n=fs, epi=lib.EPI_RELU_LN, ln1=t["ln1"],
+                  out_bf16=h)  # varianceadaptor.py:217-219
+    out = torch.empty((B, T), device=dev, dtype=torch.float32)
+    lib.conv_gemm(h, t["w2"], t["b2"], taps=3, pad_left=1, block_n=fs, epi=lib.EPI_RELU_LN_DOT, ln1=t["ln2"],
+                  dot_w=t["dw"], dot_b=t["db"], row_mask=mask_u8, out_row=out)  # :220-229
+    return out
+
+
+# --------------------------------------------------------------------------------------------------
+# PostConvNet (Models/postnets.py:64-79), eval-mode BatchNorm folded into the conv epilogue
+# --------------------------------------------------------------------------------------------------
+def postnet_cache(pn) -> dict:
+    c: Cache = pn._ttsb_cache
+    bns = [pn.pre_batchnorm] + list(pn.batch_norm_list)
+    convs = [pn.conv1] + list(pn.conv_list)
+    params = [pn.out.weight, pn.out.bias, pn.conv2.weight, pn.conv2.bias]
+    for cv, bn in zip(convs, bns):
+        params += [cv.weight, cv.bias, bn.weight, bn.bias, bn.running_mean, bn.running_var]
+    if c.stale(params):
+        t = c.t
+        t["wout"], t["bout"] = _bf16(pn.out.weight).unsqueeze(0).contiguous(), _f32(pn.out.bias)
+        t["convs"] = []
+        for cv, bn in zip(convs, bns):
+            scale = bn.weight.detach().float() / torch.sqrt(bn.running_var.detach().float() + bn.eps)
+            shift = (cv.bias.detach().float() - bn.running_mean.detach().float()) * scale + bn.bias.detach().float()
+            t["convs"].append((conv_w_to_taps(cv.weight), scale.contiguous(), shift.contiguous()))
+        t["w2"], t["b2"] = conv_w_to_taps(pn.conv2.weight), _f32(pn.conv2.bias)
+        c.commit(params)
+    return c.t
+
+
+def run_postnet(t: dict, d_bf16: torch.Tensor):
+    B, T, D = d_bf16.shape
+    dev = d_bf16.device
+    md = t["bout"].numel()
+    mel_pre = torch.empty((B, T, md), device=dev, dtype=torch.float32)
+    mel_pre_bf = torch.empty((B, T, md), device=dev, dtype=torch.bfloat16)
+    lib.conv_gemm(d_bf16, t["wout"], t["bout"], block_n=md, out_f32=mel_pre, out_bf16=mel_pre_bf)  # postnets.py:67
+    h = mel_pre_bf
+    for w, scale, shift in t["convs"]:  # postnets.py:71-73 (pad 4 + drop last 4 == causal, pad_left 4)
+        o = torch.empty((B, T, w.shape[1]), device=dev, dtype=torch.bfloat16)
+        lib.conv_gemm(h, w, shift, taps=5, pad_left=4, block_n=128, act=lib.ACT_TANH, scale=scale, out_bf16=o)
+        h = o
+    mel_post = torch.empty((B, T, md), device=dev, dtype=torch.float32)
+    lib.conv_gemm(h, t["w2"], t["b2"], taps=5, pad_left=4, block_n=md, res_f32=mel_pre, res_bstride=T * md,
+                  res_tstride=md, out_f32=mel_post)  # postnets.py:74-75
+    return mel_pre, mel_post

@@ -1,0 +1,99 @@
+"""Drop-in for ``FastSpeech2`` of the reference's ``Models/fastspeech2.py:19-241``.
+
+Same 32-argument constructor, same ``forward`` signature, same 14-tuple, same ``state_dict`` keys
+(289 entries with the canonical hparams).  ``forward`` chains the sm_100a kernels:
+
+    embed+PE+LN -> 6 x [QKV GEMM, attention, out-proj GEMM(+res+LN), FFN1 GEMM(+ReLU), FFN2 GEMM(+LN+res+LN)]
+    -> duration predictor (2 GEMMs) -> round -> LengthRegulator (scan + expand)
+    -> pitch / energy predictors (4 GEMMs) -> bucketize+embedding add
+    -> decoder input GEMM(+PE+LN) -> 6 x FFT block -> PostNet (7 GEMMs)
+
+Research branches of the reference (SQ-VAE, hop embedding, debug post-model, conformer, speaker
+embeddings, fix_mask, perturbation) raise NotImplementedError instead of silently differing.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from .. import lib
+from . import _engine as E
+from .encoder import Encoder
+from .postnets import PostConvNet
+from .varianceadaptor import VarianceAdaptor
+
+
+class FastSpeech2(nn.Module):
+    def __init__(self, hp, src_vocab, trg_vocab, d_model_encoder, N_e, n_head_encoder, ff_conv_kernel_size_encoder,
+                 concat_after_encoder, d_model_decoder, N_d, n_head_decoder, ff_conv_kernel_size_decoder,
+                 concat_after_decoder, reduction_rate, dropout, dropout_postnet, dropout_variance_adaptor,
+                 n_bins, f0_min, f0_max, energy_min, energy_max, pitch_pred=True, energy_pred=True, accent_emb=False,
+                 output_type=None, num_group=None, log_offset=1., multi_speaker=False, spk_emb_dim=None,
+                 spk_emb_architecture=None, debug=False):
+        super().__init__()
+        self.hp = hp
+        self.spk_emb_architecture = spk_emb_architecture if spk_emb_architecture is not None else ''
+
+        def _off(name, default=False):
+            return getattr(hp, name, default)
+
+        unsupported = []
+        if str(_off('encoder_type', 'transformer')).lower() != 'transformer':
+            unsupported.append("encoder_type != 'transformer'")
+        if str(_off('decoder_type', 'transformer')).lower() != 'transformer':
+            unsupported.append("decoder_type != 'transformer'")
+        if _off('use_sq_vae'):
+            unsupported.append('use_sq_vae')
+        if _off('use_hop'):
+            unsupported.append('use_hop')
+        if debug:
+            unsupported.append('debug post-model')
+        if multi_speaker or self.spk_emb_architecture:
+            unsupported.append('speaker embeddings')
+        if accent_emb:
+            unsupported.append('accent_emb')
+        if not _off('postnet_pred', True):
+            unsupported.append('postnet_pred=False')
+        if unsupported:
+            raise NotImplementedError("FastSpeech2 (B200): out-of-scope options requested: " + ", ".join(unsupported))
+
+        self.encoder = Encoder(src_vocab, d_model_encoder, N_e, n_head_encoder, ff_conv_kernel_size_encoder,
+                               concat_after_encoder, dropout, multi_speaker=False, spk_emb_dim=None,
+                               accent_emb=accent_emb)
+        self.use_sq_vae = False
+        self.variance_adaptor = VarianceAdaptor(d_model_encoder, n_bins, f0_min, f0_max, energy_min, energy_max,
+                                                log_offset, pitch_pred, energy_pred, dropout=dropout_variance_adaptor,
+                                                use_rnn_length=_off('use_rnn_length'), use_pos=_off('use_pos'))
+        self.decoder = Encoder(d_model_encoder, d_model_decoder, N_d, n_head_decoder, ff_conv_kernel_size_decoder,
+                               concat_after_decoder, dropout, multi_speaker=False, spk_emb_dim=None, embedding=False,
+                               accent_emb=False)
+        self.postnet = PostConvNet(hp=hp, num_hidden=d_model_decoder, mel_dim=trg_vocab, reduction_rate=reduction_rate,
+                                   dropout=dropout_postnet)
+        self.debug = debug
+        self.return_attn = False   # materialise the (B,N,H,T,T) maps of slots 7/8 (parity tests only)
+        self.last_aux = None       # integer by-products of the last forward (durations, frame indices, ...)
+
+    def forward(self, src, src_mask, mel_mask=None, d_target=None, p_target=None, e_target=None, accent=None,
+                spkr_emb=None, fix_mask=None, spkr_emb_post=None, temperature=None, pitch_perturbation=False,
+                duration_perturbation=False, hop_size=None):
+        E.require_inference(self, "FastSpeech2")
+        E.require_cuda(src, "FastSpeech2")
+        if fix_mask is not None or accent is not None or spkr_emb is not None or spkr_emb_post is not None \
+                or temperature is not None or hop_size is not None or pitch_perturbation or duration_perturbation:
+            raise NotImplementedError("fix_mask / accent / speaker / temperature / hop / perturbation inputs are out of scope")
+        B, L = src.shape
+        dev = src.device
+        sm = E.mask_to_u8(src_mask, B, L, dev)
+        kv_src = lib.mask_lengths(sm)
+        e_bf, _, attn_enc = self.encoder.run(src, sm, kv_src, want_f32=False, return_attn=self.return_attn)  # :137
+        mm = None if mel_mask is None else E.mask_to_u8(mel_mask, B, mel_mask.shape[-1], dev)
+        va = self.variance_adaptor.run(e_bf, sm, mm, d_target, p_target, e_target, want_aux=True)  # :176-181
+        mel_u8 = va["mel_mask"]
+        kv_mel = lib.mask_lengths(mel_u8)
+        d_bf, _, attn_dec = self.decoder.run(va["x"], mel_u8, kv_mel, want_f32=False, return_attn=self.return_attn)  # :195
+        mel_pre, mel_post = self.postnet.run(d_bf)  # :197
+        self.last_aux = dict(dur=va["dur"], mel_len=va["mel_len"], frame_idx=va["frame_idx"], mel_pos=va["mel_pos"],
+                             mel_mask=mel_u8, p_idx=va["p_idx"], e_idx=va["e_idx"], encoder_output=e_bf,
+                             decoder_output=d_bf)
+        return (mel_pre, mel_post, va["log_d"], va["p"], va["e"], va["x"], va["text_dur"], attn_enc, attn_dec,
+                None, None, None, None, None)  # fastspeech2.py:241
