@@ -113,11 +113,11 @@ def _gen(key: str, seed: int) -> torch.Generator:
     return g
 
 
-def synth_state_dict(hp=None, seed: int = 0, frames_per_phoneme: float = 7.8) -> "OrderedDict[str, torch.Tensor]":
+def synth_state_dict(hp=None, seed: int = 0, frames_per_phoneme: float = 9.6) -> "OrderedDict[str, torch.Tensor]":
     """Deterministic fp32 state_dict in the reference layout.
 
     ``frames_per_phoneme`` sets the duration predictor's output bias (log(x+1)); with the default
-    the canonical model expands 128 phonemes to ~1000 frames (SURVEY §8d used log(11) for its init)."""
+    the canonical model expands 128 phonemes to ~1000 frames (measured: mean 7.8 frames per phoneme; SURVEY §8d used log(11) with its own init)."""
     hp = hp or make_hp()
     sd: "OrderedDict[str, torch.Tensor]" = OrderedDict()
     for key, (shape, kind) in state_dict_spec(hp).items():
