@@ -86,6 +86,37 @@ def test_gemm_affine_act(L, B, T, C, N, taps, pad, bn, act):
     assert rel_err(ob, v) < 1e-2
 
 
+@pytest.mark.parametrize("B,T,C,N,taps,pad,bn,act", [
+    (3, 333, 384, 1152, 1, 0, 192, 0),    # q/k/v: A-stationary sweep over 6 weight tiles, TMA stores
+    (2, 1103, 384, 1536, 1, 0, 256, 1),   # decoder FFN conv1: A-stationary, ragged last tile clipped by TMA
+    (70, 300, 384, 1536, 1, 0, 256, 1),   # more m-tiles than SMs: persistent loop, several units per CTA
+    (3, 130, 384, 1536, 5, 2, 256, 1),    # encoder FFN conv1 k=5: streaming A, double-buffered accumulators
+    (2, 140, 80, 384, 5, 4, 192, 2),      # postnet conv1, scale+shift+tanh
+    (40, 200, 384, 384, 5, 4, 192, 2),    # postnet conv_list, many tiles per CTA
+    (2, 200, 384, 384, 1, 0, 128, 0),
+    (2, 200, 256, 384, 1, 0, 384, 0),     # single (non double-buffered) accumulator, 2 UMMA boxes
+])
+def test_gemm_bf16_tma_store_paths(L, B, T, C, N, taps, pad, bn, act):
+    """bf16-only output: accumulator -> swizzled smem staging -> TMA store (the production path)."""
+    x = rnd(B, T, C, dtype=torch.bfloat16, seed=101)
+    w = rnd(taps, N, C, scale=1.0 / math.sqrt(C * taps), dtype=torch.bfloat16, seed=102)
+    bias = rnd(N, seed=103)
+    scale = (1.0 + 0.1 * rnd(N, seed=104)) if act == 2 else None
+    ob = torch.full((B * T + 128, N), 7.0, device=dev(), dtype=torch.bfloat16)
+    out = ob[: B * T].view(B, T, N)
+    L.conv_gemm(x, w, bias, taps=taps, pad_left=pad, block_n=bn, epi=L.EPI_AFFINE_ACT, act=act, scale=scale,
+                out_bf16=out)
+    torch.cuda.synchronize()
+    v = conv_ref(x, w, pad)
+    if scale is not None:
+        v = v * scale.double()
+    v = v + bias.double()
+    v = {0: v, 1: torch.relu(v), 2: torch.tanh(v)}[act]
+    assert rel_err(out, v) < 1e-2, rel_err(out, v)
+    assert (out.double() - v).abs().max().item() < 0.05 * max(1.0, v.abs().max().item())
+    assert (ob[B * T:] == 7.0).all(), "TMA store wrote past the tensor"
+
+
 def test_gemm_res_ln(L):
     B, T, C, N = 2, 300, 384, 384
     x = rnd(B, T, C, dtype=torch.bfloat16, seed=11)

@@ -145,7 +145,7 @@ def run_fft_block(t: dict, heads: int, x: torch.Tensor, xn: torch.Tensor, mask_u
     dev = x.device
     k = t["k"]
     qkv = torch.empty((B, T, 3 * D), device=dev, dtype=torch.bfloat16)
-    lib.conv_gemm(xn, t["wqkv"], t["bqkv"], block_n=128, out_bf16=qkv)  # modules.py:49-51
+    lib.conv_gemm(xn, t["wqkv"], t["bqkv"], block_n=192, out_bf16=qkv)  # modules.py:49-51
     ctx = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
     lib.attention_fwd(qkv, mask_u8, kv_len, ctx, heads)  # modules.py:7-21,58-65
     y = torch.empty((B, T, D), device=dev, dtype=torch.float32)
@@ -229,7 +229,7 @@ def run_postnet(t: dict, d_bf16: torch.Tensor):
     h = mel_pre_bf
     for w, scale, shift in t["convs"]:  # postnets.py:71-73 (pad 4 + drop last 4 == causal, pad_left 4)
         o = torch.empty((B, T, w.shape[1]), device=dev, dtype=torch.bfloat16)
-        lib.conv_gemm(h, w, shift, taps=5, pad_left=4, block_n=128, act=lib.ACT_TANH, scale=scale, out_bf16=o)
+        lib.conv_gemm(h, w, shift, taps=5, pad_left=4, block_n=192, act=lib.ACT_TANH, scale=scale, out_bf16=o)
         h = o
     mel_post = torch.empty((B, T, md), device=dev, dtype=torch.float32)
     lib.conv_gemm(h, t["w2"], t["b2"], taps=5, pad_left=4, block_n=md, res_f32=mel_pre, res_bstride=T * md,

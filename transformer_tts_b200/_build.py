@@ -14,7 +14,8 @@ from pathlib import Path
 CSRC = Path(__file__).resolve().parent / "csrc"
 LIB_PATH = CSRC / "libttsb200.so"
 SOURCES = ["api.cu", "gemm.cu", "attention.cu", "rowwise.cu"]
-HEADERS = [CSRC / "common.cuh", CSRC.parent.parent / "include" / "ttsb200.h"]
+HEADERS = [CSRC / "common.cuh", CSRC / "gemm_kernel.cuh", CSRC / "gemm_epilogue.inc", CSRC / "gemm_host.cuh",
+           CSRC.parent.parent / "include" / "ttsb200.h"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

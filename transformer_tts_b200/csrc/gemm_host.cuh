@@ -1,0 +1,143 @@
+// Host side of conv_gemm: tensor maps, persistent-grid launch, argument validation, C entry point.
+#pragma once
+
+namespace ttsb {
+
+static int g_num_sms = 0;
+
+static int num_sms() {
+  if (g_num_sms == 0) {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess &&
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
+      g_num_sms = n;
+    else
+      g_num_sms = 148;
+  }
+  return g_num_sms;
+}
+
+template <int BLOCK_N, int EPI, bool A_STAT>
+static int launch_gemm(const ttsb200_gemm_args& a, GemmDev& d, cudaStream_t stream) {
+  using Cfg = GemmCfg<BLOCK_N, A_STAT>;
+  static_assert(Cfg::kSmemBytes <= kMaxSmem, "shared memory budget exceeded");
+  CUtensorMap tmA, tmW, tmOut;
+  {
+    const uint64_t dims[3] = {static_cast<uint64_t>(a.C), static_cast<uint64_t>(a.T),
+                              static_cast<uint64_t>(a.B)};
+    const uint64_t strides[2] = {static_cast<uint64_t>(a.ldx) * 2,
+                                 static_cast<uint64_t>(a.ldx) * 2 * static_cast<uint64_t>(a.T)};
+    const uint32_t box[3] = {kBlockK, kBlockM, 1};
+    int rc = make_tmap_bf16(&tmA, a.x, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+  }
+  {
+    const uint64_t dims[2] = {static_cast<uint64_t>(a.C),
+                              static_cast<uint64_t>(a.taps) * static_cast<uint64_t>(a.N)};
+    const uint64_t strides[1] = {static_cast<uint64_t>(a.C) * 2};
+    const uint32_t box[2] = {kBlockK, static_cast<uint32_t>(Cfg::kWBoxN)};
+    int rc = make_tmap_bf16(&tmW, a.w, 2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+  }
+  if (a.out_bf16 && a.N % 64 == 0) {
+    const uint64_t dims[3] = {static_cast<uint64_t>(a.N), static_cast<uint64_t>(a.T),
+                              static_cast<uint64_t>(a.B)};
+    const uint64_t strides[2] = {static_cast<uint64_t>(a.N) * 2,
+                                 static_cast<uint64_t>(a.N) * 2 * static_cast<uint64_t>(a.T)};
+    const uint32_t box[3] = {64, kBlockM, 1};
+    int rc = make_tmap_bf16(&tmOut, a.out_bf16, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+  } else {
+    tmOut = tmA;  // never used for stores in this configuration; keeps the descriptor prefetch valid
+  }
+  auto kern = conv_gemm_kernel<BLOCK_N, EPI, A_STAT>;
+  static bool attr_done = false;  // per instantiation
+  if (!attr_done) {
+    TTSB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    attr_done = true;
+  }
+  d.m_tiles = (a.T + kBlockM - 1) / kBlockM;
+  d.n_tiles = a.N / BLOCK_N;
+  d.num_tiles = a.B * d.m_tiles * d.n_tiles;
+  const int units = A_STAT ? a.B * d.m_tiles : d.num_tiles;
+  const int grid = units < num_sms() ? units : num_sms();
+  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(tmA, tmW, tmOut, d);
+  TTSB_CHECK_CUDA(cudaGetLastError());
+  return TTSB_OK;
+}
+
+}  // namespace ttsb
+
+using namespace ttsb;
+
+extern "C" int ttsb200_conv_gemm(const ttsb200_gemm_args* a, ttsb200_stream_t stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  TTSB_CHECK_ARG(a != nullptr, "conv_gemm: null args");
+  TTSB_CHECK_ARG(a->B > 0 && a->T > 0 && a->N > 0 && a->C > 0 && a->taps > 0, "conv_gemm: bad dims");
+  TTSB_CHECK_ARG(a->x && a->w, "conv_gemm: null x/w");
+  TTSB_CHECK_ARG(a->C % 8 == 0 && a->ldx % 8 == 0 && a->ldx >= a->C,
+                 "conv_gemm: C (%d) and ldx (%lld) must be multiples of 8, ldx >= C", a->C, (long long)a->ldx);
+  TTSB_CHECK_ARG((reinterpret_cast<uintptr_t>(a->x) & 15) == 0 && (reinterpret_cast<uintptr_t>(a->w) & 15) == 0,
+                 "conv_gemm: x/w must be 16-byte aligned");
+  TTSB_CHECK_ARG(a->block_n > 0 && a->N % a->block_n == 0, "conv_gemm: N (%d) not a multiple of block_n (%d)",
+                 a->N, a->block_n);
+  TTSB_CHECK_ARG(a->bias != nullptr, "conv_gemm: bias required");
+  if (a->out_bf16)
+    TTSB_CHECK_ARG((reinterpret_cast<uintptr_t>(a->out_bf16) & 15) == 0, "conv_gemm: out_bf16 must be 16-byte aligned");
+  GemmDev d;
+  d.B = a->B; d.T = a->T; d.N = a->N; d.C = a->C; d.taps = a->taps; d.pad_left = a->pad_left;
+  d.epi = a->epi; d.act = a->act;
+  d.m_tiles = d.n_tiles = d.num_tiles = 0;
+  d.bias = a->bias; d.scale = a->scale; d.res_f32 = a->res_f32;
+  d.res_bstride = a->res_bstride; d.res_tstride = a->res_tstride; d.res_scale = a->res_scale;
+  d.res_bf16 = static_cast<const __nv_bfloat16*>(a->res_bf16);
+  d.ln1_g = a->ln1_g; d.ln1_b = a->ln1_b; d.ln2_g = a->ln2_g; d.ln2_b = a->ln2_b; d.eps = a->eps;
+  d.dot_w = a->dot_w; d.dot_b = a->dot_b; d.row_mask = a->row_mask;
+  d.out_f32 = a->out_f32; d.out_bf16 = static_cast<__nv_bfloat16*>(a->out_bf16);
+  d.out2_f32 = a->out2_f32; d.out_row = a->out_row;
+
+  const int e = a->epi, bn = a->block_n;
+  if (e == TTSB200_EPI_AFFINE_ACT) {
+    TTSB_CHECK_ARG(a->out_f32 || a->out_bf16, "conv_gemm: AFFINE_ACT needs an output");
+    if (a->res_f32)
+      TTSB_CHECK_ARG(a->res_tstride % 4 == 0 && a->res_bstride % 4 == 0, "conv_gemm: res strides % 4");
+    // A-stationary sweep: plain linears on <= 384 input channels with bf16-only output
+    const bool a_stat = a->taps == 1 && a->C <= 384 && a->C % 64 == 0 && a->out_bf16 && !a->out_f32 &&
+                        !a->res_f32 && a->N / bn >= 2;
+    if (bn == 80) return launch_gemm<80, TTSB200_EPI_AFFINE_ACT, false>(*a, d, stream);
+    if (bn == 128) {
+      if (a_stat) return launch_gemm<128, TTSB200_EPI_AFFINE_ACT, true>(*a, d, stream);
+      return launch_gemm<128, TTSB200_EPI_AFFINE_ACT, false>(*a, d, stream);
+    }
+    if (bn == 192) {
+      if (a_stat) return launch_gemm<192, TTSB200_EPI_AFFINE_ACT, true>(*a, d, stream);
+      return launch_gemm<192, TTSB200_EPI_AFFINE_ACT, false>(*a, d, stream);
+    }
+    if (bn == 256) {
+      if (a_stat) return launch_gemm<256, TTSB200_EPI_AFFINE_ACT, true>(*a, d, stream);
+      return launch_gemm<256, TTSB200_EPI_AFFINE_ACT, false>(*a, d, stream);
+    }
+    if (bn == 384) return launch_gemm<384, TTSB200_EPI_AFFINE_ACT, false>(*a, d, stream);
+  } else if (e == TTSB200_EPI_RES_LN) {
+    TTSB_CHECK_ARG(bn == a->N, "conv_gemm: LN epilogue needs block_n == N");
+    TTSB_CHECK_ARG(a->res_f32 && a->ln1_g && a->ln1_b && a->out_bf16, "conv_gemm: RES_LN operands");
+    TTSB_CHECK_ARG(a->res_tstride % 4 == 0 && a->res_bstride % 4 == 0, "conv_gemm: res strides % 4");
+    if (bn == 384) return launch_gemm<384, TTSB200_EPI_RES_LN, false>(*a, d, stream);
+  } else if (e == TTSB200_EPI_FFN2) {
+    TTSB_CHECK_ARG(bn == a->N, "conv_gemm: LN epilogue needs block_n == N");
+    TTSB_CHECK_ARG(a->res_f32 && a->res_bf16 && a->ln1_g && a->ln1_b && a->ln2_g && a->ln2_b && a->out_bf16,
+                   "conv_gemm: FFN2 operands");
+    TTSB_CHECK_ARG(a->res_tstride % 4 == 0 && a->res_bstride % 4 == 0, "conv_gemm: res strides % 4");
+    if (bn == 384) return launch_gemm<384, TTSB200_EPI_FFN2, false>(*a, d, stream);
+  } else if (e == TTSB200_EPI_RELU_LN) {
+    TTSB_CHECK_ARG(bn == a->N, "conv_gemm: LN epilogue needs block_n == N");
+    TTSB_CHECK_ARG(a->ln1_g && a->ln1_b && a->out_bf16, "conv_gemm: RELU_LN operands");
+    if (bn == 256) return launch_gemm<256, TTSB200_EPI_RELU_LN, false>(*a, d, stream);
+  } else if (e == TTSB200_EPI_RELU_LN_DOT) {
+    TTSB_CHECK_ARG(bn == a->N, "conv_gemm: LN epilogue needs block_n == N");
+    TTSB_CHECK_ARG(a->ln1_g && a->ln1_b && a->dot_w && a->dot_b && a->out_row, "conv_gemm: RELU_LN_DOT operands");
+    if (bn == 256) return launch_gemm<256, TTSB200_EPI_RELU_LN_DOT, false>(*a, d, stream);
+  }
+  set_last_error("conv_gemm: unsupported (epi=%d, block_n=%d)", e, bn);
+  return TTSB_ERR_ARG;
+}

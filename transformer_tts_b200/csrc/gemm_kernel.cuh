@@ -1,0 +1,172 @@
+// conv_gemm_kernel — included by gemm.cu (see the header comment there for the design).
+#pragma once
+
+namespace ttsb {
+
+template <int N, class F>
+__device__ __forceinline__ void for_each_chunk32(uint32_t trow, F&& f) {
+#pragma unroll 1
+  for (int c = 0; c < N; c += 32) {
+    float v[32];
+    tmem_ld32(trow + c, v);
+    tmem_ld_wait();
+    f(c, v);
+  }
+}
+
+template <int BLOCK_N, int EPI, bool A_STAT>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                 const __grid_constant__ CUtensorMap tmOut, const GemmDev p) {
+  using Cfg = GemmCfg<BLOCK_N, A_STAT>;
+  constexpr int S = Cfg::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint8_t* sARes = smem;                                  // A_STAT only: 6 x 16 KB
+  uint8_t* sStages = smem + Cfg::kAResBytes;
+  uint8_t* sStore = sStages + S * Cfg::kStageBytes;       // 2 x 16 KB, 1024-aligned
+  float* sBias = reinterpret_cast<float*>(sStore + Cfg::kStoreBytes);
+  float* sScale = sBias + BLOCK_N;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sScale + BLOCK_N);
+  uint64_t* bar_full = bars;             // [S]
+  uint64_t* bar_empty = bars + S;        // [S]
+  uint64_t* bar_accf = bars + 2 * S;     // [2]
+  uint64_t* bar_acce = bars + 2 * S + 2; // [2]
+  uint64_t* bar_af = bars + 2 * S + 4;   // resident A full
+  uint64_t* bar_ae = bars + 2 * S + 5;   // resident A free
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 6);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int kblocks = (p.C + kBlockK - 1) / kBlockK;
+  const int num_iters = A_STAT ? kblocks : p.taps * kblocks;
+  const int num_units = A_STAT ? p.B * p.m_tiles : p.num_tiles;
+  const int n_inner = A_STAT ? p.n_tiles : 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmW);
+    tma_prefetch_desc(&tmOut);
+    for (int s = 0; s < S; ++s) {
+      mbar_init(smem_u32(&bar_full[s]), 1);
+      mbar_init(smem_u32(&bar_empty[s]), 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(smem_u32(&bar_accf[i]), 1);
+      mbar_init(smem_u32(&bar_acce[i]), kEpiThreads);
+    }
+    mbar_init(smem_u32(bar_af), 1);
+    mbar_init(smem_u32(bar_ae), 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(smem_u32(tmem_slot), Cfg::kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // unit -> (b, t0, first n-tile); generic: unit = tile id with n fastest; A_STAT: unit = m-tile id
+  auto decode = [&](int unit, int& b, int& t0, int& nt0) {
+    int mt;
+    if (A_STAT) {
+      mt = unit;
+      nt0 = 0;
+    } else {
+      mt = unit / p.n_tiles;
+      nt0 = unit - mt * p.n_tiles;
+    }
+    b = mt / p.m_tiles;
+    t0 = (mt - b * p.m_tiles) * kBlockM;
+  };
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      uint32_t git = 0, ui = 0;
+      for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x, ++ui) {
+        int b, t0, nt0;
+        decode(unit, b, t0, nt0);
+        if (A_STAT) {
+          mbar_wait(smem_u32(bar_ae), (ui & 1) ^ 1);
+          mbar_arrive_expect_tx(smem_u32(bar_af), kblocks * Cfg::kABytes);
+          for (int kb = 0; kb < kblocks; ++kb)
+            tma_load_3d(smem_u32(sARes + kb * Cfg::kABytes), &tmA, smem_u32(bar_af), kb * kBlockK, t0, b);
+        }
+        for (int nt = nt0; nt < nt0 + n_inner; ++nt) {
+          for (int it = 0; it < num_iters; ++it, ++git) {
+            const int s = git % S;
+            const uint32_t ph = (git / S) & 1;
+            mbar_wait(smem_u32(&bar_empty[s]), ph ^ 1);
+            const uint32_t full = smem_u32(&bar_full[s]);
+            mbar_arrive_expect_tx(full, Cfg::kStageBytes);
+            const int tap = A_STAT ? 0 : it / kblocks;
+            const int c0 = (it - tap * kblocks) * kBlockK;
+            uint8_t* st = sStages + s * Cfg::kStageBytes;
+            uint8_t* sw = st;
+            if (!A_STAT) {
+              tma_load_3d(smem_u32(st), &tmA, full, c0, t0 + tap - p.pad_left, b);
+              sw = st + Cfg::kABytes;
+            }
+#pragma unroll
+            for (int wb = 0; wb < Cfg::kNumWBoxes; ++wb)
+              tma_load_2d(smem_u32(sw + wb * Cfg::kWBoxBytes), &tmW, full, c0,
+                          tap * p.N + nt * BLOCK_N + wb * Cfg::kWBoxN);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(kBlockM, Cfg::kWBoxN, 0, 0);
+      uint32_t git = 0, ti = 0, ui = 0;
+      for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x, ++ui) {
+        if (A_STAT) {
+          mbar_wait(smem_u32(bar_af), ui & 1);
+          tc_fence_after();
+        }
+        for (int nt = 0; nt < n_inner; ++nt, ++ti) {
+          const uint32_t ab = ti % Cfg::kNumAcc;
+          const uint32_t aph = (ti / Cfg::kNumAcc) & 1;
+          mbar_wait(smem_u32(&bar_acce[ab]), aph ^ 1);  // epilogue drained this accumulator
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + ab * BLOCK_N;
+          for (int it = 0; it < num_iters; ++it, ++git) {
+            const int s = git % S;
+            const uint32_t ph = (git / S) & 1;
+            mbar_wait(smem_u32(&bar_full[s]), ph);
+            tc_fence_after();
+            const uint32_t st = smem_u32(sStages + s * Cfg::kStageBytes);
+            const uint32_t a_base = A_STAT ? smem_u32(sARes + it * Cfg::kABytes) : st;
+            const uint32_t w_base = A_STAT ? st : st + Cfg::kABytes;
+#pragma unroll
+            for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+              const uint64_t adesc = umma_smem_desc(a_base + k * kUmmaK * 2, 16, 1024, kLayoutSW128);
+#pragma unroll
+              for (int wb = 0; wb < Cfg::kNumWBoxes; ++wb) {
+                const uint64_t bdesc =
+                    umma_smem_desc(w_base + wb * Cfg::kWBoxBytes + k * kUmmaK * 2, 16, 1024, kLayoutSW128);
+                umma_bf16(d_tmem + wb * Cfg::kWBoxN, adesc, bdesc, idesc, (it | k) != 0 ? 1u : 0u);
+              }
+            }
+            umma_commit(smem_u32(&bar_empty[s]));  // frees the smem stage when these MMAs retire
+          }
+          umma_commit(smem_u32(&bar_accf[ab]));  // accumulator complete
+        }
+        if (A_STAT) umma_commit(smem_u32(bar_ae));  // resident A may be overwritten
+      }
+    }
+  } else {
+#include "gemm_epilogue.inc"
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, Cfg::kTmemCols);
+}
+
+}  // namespace ttsb
