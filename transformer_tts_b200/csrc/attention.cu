@@ -26,6 +26,12 @@ constexpr int kAttSmem = 3 * kTileBytes + kPBytes + 1024 /*align*/ + 256 /*barri
 constexpr int kAttTmemCols = 256;
 constexpr float kLog2e = 1.4426950408889634f;
 
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 enum { BAR_Q = 0, BAR_KF, BAR_KE, BAR_VF, BAR_VE, BAR_SF, BAR_PF, BAR_OF, BAR_COUNT };
 
 __global__ void __launch_bounds__(kAttThreads, 2)
@@ -42,6 +48,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const uint8_t* _
   uint64_t* bars = reinterpret_cast<uint64_t*>(sP + kPBytes);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + BAR_COUNT);
   uint8_t* sflag = reinterpret_cast<uint8_t*>(tmem_slot + 4);  // 128 key flags of the current tile
+  volatile uint8_t* sclean = sflag + 128;                      // per softmax warp: all 32 of its flags valid
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -143,27 +150,38 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const uint8_t* _
       const uint32_t ph = j & 1;
       {
         const int key = j * kBKV + st;
-        sflag[st] = key < T ? (mask[static_cast<int64_t>(b) * T + key] ? 1 : 0) : 2;
+        const uint8_t f = key < T ? (mask[static_cast<int64_t>(b) * T + key] ? 1 : 0) : 2;
+        sflag[st] = f;
+        const bool wall = __all_sync(0xffffffffu, f == 1);
+        if (lane == 0) sclean[q] = wall ? 1 : 0;
       }
       asm volatile("bar.sync 1, 128;" ::: "memory");
+      // a tile whose 128 keys are all valid (every tile but the last of a prefix mask) needs no flags
+      const bool clean = (sclean[0] & sclean[1] & sclean[2] & sclean[3]) != 0;
       mbar_wait(smem_u32(&bars[BAR_SF]), ph);
       tc_fence_after();
-      // pass A: row max
+      // pass A: row max (raw scores on a clean tile: the positive scale commutes with max)
       float mx = -INFINITY;
 #pragma unroll 1
       for (int c = 0; c < kBKV; c += 32) {
         float v[32];
         tmem_ld32(tmem_S + lane_off + c, v);
         tmem_ld_wait();
+        if (clean) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const uint8_t f = sflag[c + i];
-          const float s = f == 1 ? v[i] * scale_log2 : (f == 0 ? masked : -INFINITY);
-          mx = fmaxf(mx, s);
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, v[i]);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const uint8_t f = sflag[c + i];
+            const float s = f == 1 ? v[i] * scale_log2 : (f == 0 ? masked : -INFINITY);
+            mx = fmaxf(mx, s);
+          }
         }
       }
+      if (clean) mx *= scale_log2;
       const float m_new = fmaxf(m, mx);
-      const float alpha = exp2f(m - m_new);  // m = -inf on the first tile -> 0
+      const float alpha = fast_exp2(m - m_new);  // m = -inf on the first tile -> 0
       // pass B: p = exp2(s - m_new) -> bf16 -> swizzled smem; fp32 row sum
       float lsum = 0.f;
 #pragma unroll 1
@@ -171,12 +189,20 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const uint8_t* _
         float v[32];
         tmem_ld32(tmem_S + lane_off + c, v);
         tmem_ld_wait();
+        if (clean) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const uint8_t f = sflag[c + i];
-          const float s = f == 1 ? v[i] * scale_log2 : (f == 0 ? masked : -INFINITY);
-          v[i] = exp2f(s - m_new);
-          lsum += v[i];
+          for (int i = 0; i < 32; ++i) {
+            v[i] = fast_exp2(fmaf(v[i], scale_log2, -m_new));
+            lsum += v[i];
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const uint8_t f = sflag[c + i];
+            const float s = f == 1 ? v[i] * scale_log2 : (f == 0 ? masked : -INFINITY);
+            v[i] = fast_exp2(s - m_new);
+            lsum += v[i];
+          }
         }
         uint8_t* pblk = prow + (c >> 6) * (kBQ * 128);
 #pragma unroll

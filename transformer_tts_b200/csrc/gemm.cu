@@ -41,8 +41,11 @@ struct GemmCfg {
   static constexpr int kStageBytes = A_STAT ? kWBytes : kABytes + kWBytes;
   static constexpr int kAResBytes = A_STAT ? 6 * kABytes : 0;            // resident A: up to C = 384
   static constexpr int kStoreBytes = 2 * kBlockM * 128;                  // two 128x64 bf16 staging boxes
-  static constexpr int kParamBytes = 2 * BLOCK_N * 4;                    // bias + scale of the tile
-  static constexpr int kFixed = kAResBytes + kStoreBytes + kParamBytes + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr bool kScaleInSmem = BLOCK_N <= 256;                   // 384-wide tiles read scale from L1
+  static constexpr int kParamBytes = (kScaleInSmem ? 2 : 1) * BLOCK_N * 4;  // bias (+ scale) of the tile
+  // no alignment slack: the kernel has no static smem, so the dynamic window starts 1024-aligned
+  // (checked at run time; a misaligned base traps instead of corrupting swizzled tiles)
+  static constexpr int kFixed = kAResBytes + kStoreBytes + kParamBytes + 256 /*barriers*/;
   static constexpr int kStagesFit = (kMaxSmem - kFixed) / kStageBytes;
   static constexpr int kStages = kStagesFit > 6 ? 6 : kStagesFit;
   static constexpr int kNumAcc = BLOCK_N <= 256 ? 2 : 1;

@@ -20,15 +20,18 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                  const __grid_constant__ CUtensorMap tmOut, const GemmDev p) {
   using Cfg = GemmCfg<BLOCK_N, A_STAT>;
   constexpr int S = Cfg::kStages;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~static_cast<uintptr_t>(1023));
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem) & 1023u) != 0) {
+    if (threadIdx.x == 0) printf("ttsb200: dynamic shared memory base is not 1024-byte aligned\n");
+    __trap();
+  }
   uint8_t* sARes = smem;                                  // A_STAT only: 6 x 16 KB
   uint8_t* sStages = smem + Cfg::kAResBytes;
   uint8_t* sStore = sStages + S * Cfg::kStageBytes;       // 2 x 16 KB, 1024-aligned
   float* sBias = reinterpret_cast<float*>(sStore + Cfg::kStoreBytes);
-  float* sScale = sBias + BLOCK_N;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sScale + BLOCK_N);
+  float* sScale = sBias + BLOCK_N;  // only backed by smem when Cfg::kScaleInSmem
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + (Cfg::kScaleInSmem ? 2 : 1) * BLOCK_N);
   uint64_t* bar_full = bars;             // [S]
   uint64_t* bar_empty = bars + S;        // [S]
   uint64_t* bar_accf = bars + 2 * S;     // [2]
