@@ -45,6 +45,8 @@ void set_last_error(const char* fmt, ...);
 // dims 1.. (dim 0 is contiguous).  Returns TTSB_OK or a negative code (last error set).
 int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
                    const uint64_t* strides_bytes, const uint32_t* box, CUtensorMapSwizzle swz);
+int make_tmap(CUtensorMap* out, CUtensorMapDataType dtype, const void* base, int rank, const uint64_t* dims,
+              const uint64_t* strides_bytes, const uint32_t* box, CUtensorMapSwizzle swz);
 
 // ----------------------------------------------------------------------------------------------
 // device helpers

@@ -27,11 +27,11 @@ namespace ttsb {
 constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;  // bf16 elements = one 128-byte swizzle row
 constexpr int kUmmaK = 16;
-constexpr int kGemmThreads = 192;
+constexpr int kGemmThreads = 224;  // 7 warps: TMA, MMA, 4 x epilogue, residual-ring producer
 constexpr int kEpiThreads = 128;
 constexpr int kMaxSmem = 232448;  // 227 KB opt-in limit per CTA
 
-template <int BLOCK_N, bool A_STAT>
+template <int BLOCK_N, bool A_STAT, bool RING = false>
 struct GemmCfg {
   static constexpr int kWBoxN = BLOCK_N <= 256 ? BLOCK_N : BLOCK_N / 2;  // TMA box rows / UMMA N
   static constexpr int kNumWBoxes = BLOCK_N / kWBoxN;
@@ -45,7 +45,12 @@ struct GemmCfg {
   static constexpr int kParamBytes = (kScaleInSmem ? 2 : 1) * BLOCK_N * 4;  // bias (+ scale) of the tile
   // no alignment slack: the kernel has no static smem, so the dynamic window starts 1024-aligned
   // (checked at run time; a misaligned base traps instead of corrupting swizzled tiles)
-  static constexpr int kFixed = kAResBytes + kStoreBytes + kParamBytes + 256 /*barriers*/;
+  // RING: residual operands of the LayerNorm epilogues (fp32 128x32 / bf16 128x64 boxes, 16 KB each) are
+  // prefetched by TMA into a 4-slot ring instead of being read row-by-row from global memory
+  static constexpr int kRingSlots = RING ? 4 : 0;
+  static constexpr int kRingSlotBytes = 16384;
+  static constexpr int kRingBytes = kRingSlots * kRingSlotBytes;
+  static constexpr int kFixed = kAResBytes + kStoreBytes + kRingBytes + kParamBytes + 256 /*barriers*/;
   static constexpr int kStagesFit = (kMaxSmem - kFixed) / kStageBytes;
   static constexpr int kStages = kStagesFit > 6 ? 6 : kStagesFit;
   static constexpr int kNumAcc = BLOCK_N <= 256 ? 2 : 1;
@@ -91,6 +96,22 @@ __device__ __forceinline__ void load_bf16x8(const __nv_bfloat16* src, float* v) 
     v[2 * i] = f.x;
     v[2 * i + 1] = f.y;
   }
+}
+
+// This thread's row of a TMA-loaded, 128B-swizzled ring box: 32 fp32 or 64 bf16 values.
+__device__ __forceinline__ void ring_row_f32(const uint8_t* box, int row, float* v) {
+  const uint8_t* rp = box + row * 128;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float4 f = *reinterpret_cast<const float4*>(rp + ((j ^ (row & 7)) << 4));
+    v[4 * j] = f.x; v[4 * j + 1] = f.y; v[4 * j + 2] = f.z; v[4 * j + 3] = f.w;
+  }
+}
+__device__ __forceinline__ void ring_row_bf16(const uint8_t* box, int row, float* v) {
+  const uint8_t* rp = box + row * 128;
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    load_bf16x8(reinterpret_cast<const __nv_bfloat16*>(rp + ((j ^ (row & 7)) << 4)), v + 8 * j);
 }
 
 __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }

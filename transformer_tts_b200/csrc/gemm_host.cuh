@@ -17,11 +17,11 @@ static int num_sms() {
   return g_num_sms;
 }
 
-template <int BLOCK_N, int EPI, bool A_STAT>
+template <int BLOCK_N, int EPI, bool A_STAT, bool RING = false>
 static int launch_gemm(const ttsb200_gemm_args& a, GemmDev& d, cudaStream_t stream) {
-  using Cfg = GemmCfg<BLOCK_N, A_STAT>;
+  using Cfg = GemmCfg<BLOCK_N, A_STAT, RING>;
   static_assert(Cfg::kSmemBytes <= kMaxSmem, "shared memory budget exceeded");
-  CUtensorMap tmA, tmW, tmOut;
+  CUtensorMap tmA, tmW, tmOut, tmRes32, tmResBf;
   {
     const uint64_t dims[3] = {static_cast<uint64_t>(a.C), static_cast<uint64_t>(a.T),
                               static_cast<uint64_t>(a.B)};
@@ -50,7 +50,26 @@ static int launch_gemm(const ttsb200_gemm_args& a, GemmDev& d, cudaStream_t stre
   } else {
     tmOut = tmA;  // never used for stores in this configuration; keeps the descriptor prefetch valid
   }
-  auto kern = conv_gemm_kernel<BLOCK_N, EPI, A_STAT>;
+  tmRes32 = tmA;
+  tmResBf = tmA;
+  if (RING) {
+    const uint64_t dims[3] = {static_cast<uint64_t>(a.N), static_cast<uint64_t>(a.T), static_cast<uint64_t>(a.B)};
+    {
+      const uint64_t strides[2] = {static_cast<uint64_t>(a.res_tstride) * 4, static_cast<uint64_t>(a.res_bstride) * 4};
+      const uint32_t box[3] = {32, kBlockM, 1};
+      int rc = make_tmap(&tmRes32, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, a.res_f32, 3, dims, strides, box,
+                         CU_TENSOR_MAP_SWIZZLE_128B);
+      if (rc) return rc;
+    }
+    if (EPI == TTSB200_EPI_FFN2) {
+      const uint64_t strides[2] = {static_cast<uint64_t>(a.N) * 2,
+                                   static_cast<uint64_t>(a.N) * 2 * static_cast<uint64_t>(a.T)};
+      const uint32_t box[3] = {64, kBlockM, 1};
+      int rc = make_tmap_bf16(&tmResBf, a.res_bf16, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+      if (rc) return rc;
+    }
+  }
+  auto kern = conv_gemm_kernel<BLOCK_N, EPI, A_STAT, RING>;
   static bool attr_done = false;  // per instantiation
   if (!attr_done) {
     TTSB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
@@ -61,7 +80,7 @@ static int launch_gemm(const ttsb200_gemm_args& a, GemmDev& d, cudaStream_t stre
   d.num_tiles = a.B * d.m_tiles * d.n_tiles;
   const int units = A_STAT ? a.B * d.m_tiles : d.num_tiles;
   const int grid = units < num_sms() ? units : num_sms();
-  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(tmA, tmW, tmOut, d);
+  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(tmA, tmW, tmOut, tmRes32, tmResBf, d);
   TTSB_CHECK_CUDA(cudaGetLastError());
   return TTSB_OK;
 }
@@ -122,12 +141,21 @@ extern "C" int ttsb200_conv_gemm(const ttsb200_gemm_args* a, ttsb200_stream_t st
     TTSB_CHECK_ARG(bn == a->N, "conv_gemm: LN epilogue needs block_n == N");
     TTSB_CHECK_ARG(a->res_f32 && a->ln1_g && a->ln1_b && a->out_bf16, "conv_gemm: RES_LN operands");
     TTSB_CHECK_ARG(a->res_tstride % 4 == 0 && a->res_bstride % 4 == 0, "conv_gemm: res strides % 4");
+    // residual prefetch ring: dense fp32 residual (not the broadcast positional table), short K
+    const bool ring = a->res_bstride == static_cast<int64_t>(a->T) * a->N && a->res_tstride == a->N &&
+                      !a->res_scale && a->taps * a->C <= 2048 &&
+                      (reinterpret_cast<uintptr_t>(a->res_f32) & 15) == 0;
+    if (bn == 384 && ring) return launch_gemm<384, TTSB200_EPI_RES_LN, false, true>(*a, d, stream);
     if (bn == 384) return launch_gemm<384, TTSB200_EPI_RES_LN, false>(*a, d, stream);
   } else if (e == TTSB200_EPI_FFN2) {
     TTSB_CHECK_ARG(bn == a->N, "conv_gemm: LN epilogue needs block_n == N");
     TTSB_CHECK_ARG(a->res_f32 && a->res_bf16 && a->ln1_g && a->ln1_b && a->ln2_g && a->ln2_b && a->out_bf16,
                    "conv_gemm: FFN2 operands");
     TTSB_CHECK_ARG(a->res_tstride % 4 == 0 && a->res_bstride % 4 == 0, "conv_gemm: res strides % 4");
+    const bool ring = a->res_bstride == static_cast<int64_t>(a->T) * a->N && a->res_tstride == a->N &&
+                      a->taps * a->C <= 2048 && (reinterpret_cast<uintptr_t>(a->res_f32) & 15) == 0 &&
+                      (reinterpret_cast<uintptr_t>(a->res_bf16) & 15) == 0;
+    if (bn == 384 && ring) return launch_gemm<384, TTSB200_EPI_FFN2, false, true>(*a, d, stream);
     if (bn == 384) return launch_gemm<384, TTSB200_EPI_FFN2, false>(*a, d, stream);
   } else if (e == TTSB200_EPI_RELU_LN) {
     TTSB_CHECK_ARG(bn == a->N, "conv_gemm: LN epilogue needs block_n == N");

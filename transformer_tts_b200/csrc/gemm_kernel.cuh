@@ -14,11 +14,12 @@ __device__ __forceinline__ void for_each_chunk32(uint32_t trow, F&& f) {
   }
 }
 
-template <int BLOCK_N, int EPI, bool A_STAT>
+template <int BLOCK_N, int EPI, bool A_STAT, bool RING>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
-                 const __grid_constant__ CUtensorMap tmOut, const GemmDev p) {
-  using Cfg = GemmCfg<BLOCK_N, A_STAT>;
+                 const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes32,
+                 const __grid_constant__ CUtensorMap tmResBf, const GemmDev p) {
+  using Cfg = GemmCfg<BLOCK_N, A_STAT, RING>;
   constexpr int S = Cfg::kStages;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;
@@ -29,7 +30,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint8_t* sARes = smem;                                  // A_STAT only: 6 x 16 KB
   uint8_t* sStages = smem + Cfg::kAResBytes;
   uint8_t* sStore = sStages + S * Cfg::kStageBytes;       // 2 x 16 KB, 1024-aligned
-  float* sBias = reinterpret_cast<float*>(sStore + Cfg::kStoreBytes);
+  uint8_t* sRing = sStore + Cfg::kStoreBytes;             // RING only: 4 x 16 KB
+  float* sBias = reinterpret_cast<float*>(sRing + Cfg::kRingBytes);
   float* sScale = sBias + BLOCK_N;  // only backed by smem when Cfg::kScaleInSmem
   uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + (Cfg::kScaleInSmem ? 2 : 1) * BLOCK_N);
   uint64_t* bar_full = bars;             // [S]
@@ -38,7 +40,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint64_t* bar_acce = bars + 2 * S + 2; // [2]
   uint64_t* bar_af = bars + 2 * S + 4;   // resident A full
   uint64_t* bar_ae = bars + 2 * S + 5;   // resident A free
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 6);
+  uint64_t* bar_rf = bars + 2 * S + 6;   // [4] ring slot filled
+  uint64_t* bar_re = bars + 2 * S + 10;  // [4] ring slot drained
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 14);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -61,6 +65,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     mbar_init(smem_u32(bar_af), 1);
     mbar_init(smem_u32(bar_ae), 1);
+    for (int i = 0; i < 4; ++i) {
+      mbar_init(smem_u32(&bar_rf[i]), 1);
+      mbar_init(smem_u32(&bar_re[i]), kEpiThreads);
+    }
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -163,8 +171,30 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (A_STAT) umma_commit(smem_u32(bar_ae));  // resident A may be overwritten
       }
     }
-  } else {
+  } else if (warp < 6) {
 #include "gemm_epilogue.inc"
+  } else if (RING) {
+    // ===================== residual-ring producer =====================
+    if (lane == 0) {
+      tma_prefetch_desc(&tmRes32);
+      tma_prefetch_desc(&tmResBf);
+      uint32_t rit = 0;
+      auto push = [&](const CUtensorMap* tm, int c0, int t0, int b) {
+        const int slot = rit & 3;
+        mbar_wait(smem_u32(&bar_re[slot]), ((rit >> 2) & 1) ^ 1);
+        const uint32_t full = smem_u32(&bar_rf[slot]);
+        mbar_arrive_expect_tx(full, Cfg::kRingSlotBytes);
+        tma_load_3d(smem_u32(sRing + slot * Cfg::kRingSlotBytes), tm, full, c0, t0, b);
+        ++rit;
+      };
+      for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+        int b, t0, nt0;
+        decode(unit, b, t0, nt0);
+        if (EPI == TTSB200_EPI_FFN2)
+          for (int g = 0; g < BLOCK_N / 64; ++g) push(&tmResBf, g * 64, t0, b);  // bf16 inner residual
+        for (int c = 0; c < BLOCK_N / 32; ++c) push(&tmRes32, c * 32, t0, b);    // fp32 residual stream
+      }
+    }
   }
 
   tc_fence_before();
