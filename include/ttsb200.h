@@ -55,7 +55,7 @@ enum { TTSB200_ACT_NONE = 0, TTSB200_ACT_RELU = 1, TTSB200_ACT_TANH = 2 };
 typedef struct ttsb200_gemm_args {
   /* problem */
   int32_t B, T, N, C, taps, pad_left;
-  int32_t block_n; /* 80, 128, 256 or 384; LN modes need block_n == N */
+  int32_t block_n; /* AFFINE_ACT: 80, 128, 192 or 256; LN modes need block_n == N (384; 256 for RELU_LN*) */
   int32_t epi, act;
   const void* x; /* bf16 (B,T,ldx) */
   int64_t ldx;   /* elements, >= C, multiple of 8 */

@@ -1,22 +1,28 @@
-// Implicit-GEMM conv1d / linear for sm_100a, v2: persistent CTAs, TMA -> tcgen05.mma -> TMEM with
-// double-buffered accumulators, fused epilogues, bf16 outputs staged through swizzled smem and
-// written with TMA stores.
+// Implicit-GEMM conv1d / linear for sm_100a, v3: persistent CTAs, TMA -> tcgen05.mma -> TMEM,
+// two epilogue warpgroups, every large output staged through swizzled smem and written by TMA.
 //
 //   acc[b,t,n] = sum_{j<taps} sum_{c<C} x[b, t+j-pad_left, c] * w[j, n, c]
 //
 // One tile = 128 time steps of ONE utterance x BLOCK_N output channels, so conv taps are plain
 // time-shifted TMA boxes and TMA's out-of-bounds zero fill is the conv zero padding (and clips the
-// ragged last tile on the store side).  Grid = min(#tiles, #SMs * CTAs/SM); each CTA walks tiles
-// tile = blockIdx.x + i*gridDim.x with n fastest, so concurrently running CTAs share activations
+// ragged last tile on the store side).  Grid = min(#units, #SMs); each CTA walks units
+// unit = blockIdx.x + i*gridDim.x with n fastest, so concurrently running CTAs share activations
 // and weights in L2.
 //
-// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer (one elected
-// thread), warps 2..5 = epilogue (thread == output row == TMEM lane).  With BLOCK_N <= 256 the
-// accumulator is double buffered in TMEM so the epilogue of tile i overlaps the main loop of i+1.
+// Warp roles (384 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer (one elected
+// thread), warp 2 = residual-ring producer (LayerNorm epilogues with a residual), warp 3 idle,
+// warps 4..11 = two epilogue warpgroups (thread == output row == TMEM lane).
+//   * AFFINE epilogue (BLOCK_N <= 256, double-buffered accumulators): warpgroup g owns accumulator g,
+//     i.e. alternate tiles, so each epilogue has two main loops of time to drain.
+//   * LayerNorm epilogues (the CTA owns whole rows, BLOCK_N == N): the two warpgroups split the
+//     columns in halves and exchange the per-row (sum, sum of squares) through smem.
+//     Residual operands arrive through a TMA-fed ring of 16 KB boxes; the fp32 residual-stream output
+//     is formed IN PLACE in its ring box and leaves by TMA store, so no thread ever issues a strided
+//     global load or store.
 //
 // A-stationary mode (taps == 1, C <= 384, AFFINE epilogue): the 128 x C activation tile is loaded
 // once and stays in smem while the CTA sweeps all N/BLOCK_N weight tiles; only weights stream through
-// the stage ring.  That cuts L2->SM traffic, which bounds K=384 GEMMs at this tile size.
+// the stage ring.
 //
 // Reference ops replaced: nn.Linear / nn.Conv1d call sites listed in include/ttsb200.h.
 #include "common.cuh"
@@ -27,12 +33,17 @@ namespace ttsb {
 constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;  // bf16 elements = one 128-byte swizzle row
 constexpr int kUmmaK = 16;
-constexpr int kGemmThreads = 224;  // 7 warps: TMA, MMA, 4 x epilogue, residual-ring producer
-constexpr int kEpiThreads = 128;
+constexpr int kGemmThreads = 384;  // 12 warps
+constexpr int kEpiWarp0 = 4;
+constexpr int kEpiThreads = 256;
+constexpr int kWgThreads = 128;
 constexpr int kMaxSmem = 232448;  // 227 KB opt-in limit per CTA
+constexpr int kBoxBytes16K = 16384;
 
-template <int BLOCK_N, bool A_STAT, bool RING = false>
+template <int BLOCK_N, int EPI, bool A_STAT>
 struct GemmCfg {
+  static constexpr bool kIsLN = EPI != TTSB200_EPI_AFFINE_ACT;
+  static constexpr bool kRing = EPI == TTSB200_EPI_RES_LN || EPI == TTSB200_EPI_FFN2;
   static constexpr int kWBoxN = BLOCK_N <= 256 ? BLOCK_N : BLOCK_N / 2;  // TMA box rows / UMMA N
   static constexpr int kNumWBoxes = BLOCK_N / kWBoxN;
   static constexpr int kABytes = kBlockM * kBlockK * 2;                  // 16 KB
@@ -40,17 +51,14 @@ struct GemmCfg {
   static constexpr int kWBoxBytes = kWBoxN * kBlockK * 2;
   static constexpr int kStageBytes = A_STAT ? kWBytes : kABytes + kWBytes;
   static constexpr int kAResBytes = A_STAT ? 6 * kABytes : 0;            // resident A: up to C = 384
-  static constexpr int kStoreBytes = 2 * kBlockM * 128;                  // two 128x64 bf16 staging boxes
-  static constexpr bool kScaleInSmem = BLOCK_N <= 256;                   // 384-wide tiles read scale from L1
-  static constexpr int kParamBytes = (kScaleInSmem ? 2 : 1) * BLOCK_N * 4;  // bias (+ scale) of the tile
-  // no alignment slack: the kernel has no static smem, so the dynamic window starts 1024-aligned
-  // (checked at run time; a misaligned base traps instead of corrupting swizzled tiles)
-  // RING: residual operands of the LayerNorm epilogues (fp32 128x32 / bf16 128x64 boxes, 16 KB each) are
-  // prefetched by TMA into a 4-slot ring instead of being read row-by-row from global memory
-  static constexpr int kRingSlots = RING ? 4 : 0;
-  static constexpr int kRingSlotBytes = 16384;
-  static constexpr int kRingBytes = kRingSlots * kRingSlotBytes;
-  static constexpr int kFixed = kAResBytes + kStoreBytes + kRingBytes + kParamBytes + 256 /*barriers*/;
+  // one bf16 staging box per warpgroup: 128 rows x 64 columns (AFFINE) or x 32 columns (LN epilogues)
+  static constexpr int kStoreBytes = kIsLN ? 2 * 8192 : 2 * kBoxBytes16K;
+  static constexpr int kRingSlots = kRing ? 4 : 0;  // even: each half owns its own slots
+  static constexpr int kRingBytes = kRingSlots * kBoxBytes16K;
+  // parameter vectors in smem: AFFINE: (bias, scale) per warpgroup; LN: bias, g1, b1, g2, b2, dot_w
+  static constexpr int kParamFloats = kIsLN ? 6 * BLOCK_N : 4 * BLOCK_N;
+  static constexpr int kStatBytes = kIsLN ? 2 * 2 * kBlockM * 8 : 0;     // [buf][half][row] float2
+  static constexpr int kFixed = kAResBytes + kStoreBytes + kRingBytes + kParamFloats * 4 + kStatBytes + 256;
   static constexpr int kStagesFit = (kMaxSmem - kFixed) / kStageBytes;
   static constexpr int kStages = kStagesFit > 6 ? 6 : kStagesFit;
   static constexpr int kNumAcc = BLOCK_N <= 256 ? 2 : 1;
@@ -59,17 +67,19 @@ struct GemmCfg {
   static_assert(kStages >= 2, "not enough shared memory for a pipeline");
   static_assert(kWBoxBytes % 1024 == 0, "W box must keep 1024B swizzle-atom alignment");
   static_assert(kWBoxN % 16 == 0 && kWBoxN <= 256, "UMMA N");
+  static_assert(!kIsLN || (BLOCK_N % 128 == 0), "LN epilogues split the row in two halves of 64-column groups");
+  static_assert(kIsLN || kNumAcc == 2, "AFFINE epilogue: one accumulator per epilogue warpgroup");
 };
 
 struct GemmDev {
   int B, T, N, C, taps, pad_left, epi, act;
   int m_tiles, n_tiles, num_tiles;
+  int res_bcast;  // residual has no batch dimension (positional table)
   const float* bias;
   const float* scale;
   const float* res_f32;
   long long res_bstride, res_tstride;
   const float* res_scale;
-  const __nv_bfloat16* res_bf16;
   const float *ln1_g, *ln1_b, *ln2_g, *ln2_b;
   float eps;
   const float* dot_w;
@@ -81,25 +91,14 @@ struct GemmDev {
   float* out_row;
 };
 
-__device__ __forceinline__ float apply_act(float v, int act) {
-  if (act == TTSB200_ACT_RELU) return fmaxf(v, 0.f);
-  if (act == TTSB200_ACT_TANH) return tanhf(v);
-  return v;
+__device__ __forceinline__ float tanh_fast(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
 }
 
-__device__ __forceinline__ void load_bf16x8(const __nv_bfloat16* src, float* v) {
-  uint4 u = *reinterpret_cast<const uint4*>(src);
-  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    float2 f = __bfloat1622float2(h[i]);
-    v[2 * i] = f.x;
-    v[2 * i + 1] = f.y;
-  }
-}
-
-// This thread's row of a TMA-loaded, 128B-swizzled ring box: 32 fp32 or 64 bf16 values.
-__device__ __forceinline__ void ring_row_f32(const uint8_t* box, int row, float* v) {
+// This thread's row of a TMA-loaded, 128B-swizzled box (128 rows x 128 bytes).
+__device__ __forceinline__ void box_row_ld_f32(const uint8_t* box, int row, float* v) {
   const uint8_t* rp = box + row * 128;
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
@@ -107,68 +106,68 @@ __device__ __forceinline__ void ring_row_f32(const uint8_t* box, int row, float*
     v[4 * j] = f.x; v[4 * j + 1] = f.y; v[4 * j + 2] = f.z; v[4 * j + 3] = f.w;
   }
 }
-__device__ __forceinline__ void ring_row_bf16(const uint8_t* box, int row, float* v) {
-  const uint8_t* rp = box + row * 128;
+__device__ __forceinline__ void box_row_st_f32(uint8_t* box, int row, const float* v) {
+  uint8_t* rp = box + row * 128;
 #pragma unroll
   for (int j = 0; j < 8; ++j)
-    load_bf16x8(reinterpret_cast<const __nv_bfloat16*>(rp + ((j ^ (row & 7)) << 4)), v + 8 * j);
+    *reinterpret_cast<float4*>(rp + ((j ^ (row & 7)) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+}
+// 32 bf16 values = 16-byte chunks [j0, j0+4) of the row
+__device__ __forceinline__ void box_row_ld_bf16x32(const uint8_t* box, int row, int j0, float* v) {
+  const uint8_t* rp = box + row * 128;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const uint4 u = *reinterpret_cast<const uint4*>(rp + (((j0 + j) ^ (row & 7)) << 4));
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 f = __bfloat1622float2(h[i]);
+      v[8 * j + 2 * i] = f.x;
+      v[8 * j + 2 * i + 1] = f.y;
+    }
+  }
+}
+// 32 bf16 values -> 16-byte chunks [j0, j0+4) of this thread's row of a 128x64 bf16 staging box
+__device__ __forceinline__ void box_row_st_bf16x32(uint8_t* box, int row, int j0, const float* v) {
+  uint8_t* rp = box + row * 128;
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    uint4 u;
+    u.x = pack_bf16(v[g * 8 + 0], v[g * 8 + 1]);
+    u.y = pack_bf16(v[g * 8 + 2], v[g * 8 + 3]);
+    u.z = pack_bf16(v[g * 8 + 4], v[g * 8 + 5]);
+    u.w = pack_bf16(v[g * 8 + 6], v[g * 8 + 7]);
+    *reinterpret_cast<uint4*>(rp + (((j0 + g) ^ (row & 7)) << 4)) = u;
+  }
 }
 
-__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+// 32 bf16 values = this thread's whole 64-byte row of a 128x32 bf16 staging box (SWIZZLE_64B:
+// 16-byte chunk j of row r lives at r*64 + ((j ^ ((r >> 1) & 3)) << 4))
+__device__ __forceinline__ void box_row_st_bf16x32_sw64(uint8_t* box, int row, const float* v) {
+  uint8_t* rp = box + row * 64;
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    uint4 u;
+    u.x = pack_bf16(v[g * 8 + 0], v[g * 8 + 1]);
+    u.y = pack_bf16(v[g * 8 + 2], v[g * 8 + 3]);
+    u.z = pack_bf16(v[g * 8 + 4], v[g * 8 + 5]);
+    u.w = pack_bf16(v[g * 8 + 6], v[g * 8 + 7]);
+    *reinterpret_cast<uint4*>(rp + ((g ^ ((row >> 1) & 3)) << 4)) = u;
+  }
+}
 
-// TMA store of one 64-column x 128-row bf16 box from swizzled smem; rows beyond T are clipped.
+__device__ __forceinline__ void epi_bar_all() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+__device__ __forceinline__ void wg_bar(int wg) { asm volatile("bar.sync %0, 128;" ::"r"(2 + wg) : "memory"); }
+
+// TMA store of one 128-row box from swizzled smem; rows beyond T are clipped by the tensor map.
 __device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, uint32_t src, int c0, int c1, int c2) {
   asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
                ::"l"(reinterpret_cast<uint64_t>(m)), "r"(src), "r"(c0), "r"(c1), "r"(c2)
                : "memory");
 }
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void tma_store_wait_read() {
-  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
-}
+__device__ __forceinline__ void tma_store_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
-
-// Writes 32 consecutive bf16 columns [c, c+32) of this thread's row into the 128x64 staging box
-// (SWIZZLE_128B: 16-byte chunk j of row r lives at r*128 + ((j ^ (r&7)) << 4)).
-__device__ __forceinline__ void stage_row32(uint8_t* box, int row, int c_in_box, const float* v) {
-  uint8_t* rp = box + row * 128;
-#pragma unroll
-  for (int g = 0; g < 4; ++g) {
-    const int ch = (c_in_box >> 3) + g;
-    uint4 u;
-    u.x = pack_bf16(v[g * 8 + 0], v[g * 8 + 1]);
-    u.y = pack_bf16(v[g * 8 + 2], v[g * 8 + 3]);
-    u.z = pack_bf16(v[g * 8 + 4], v[g * 8 + 5]);
-    u.w = pack_bf16(v[g * 8 + 6], v[g * 8 + 7]);
-    *reinterpret_cast<uint4*>(rp + ((ch ^ (row & 7)) << 4)) = u;
-  }
-}
-
-// Streams a [128 x 64*k] bf16 result through the two staging boxes.  `fill(c, v)` must produce
-// 32 output values for columns [c, c+32) of this thread's row.  All 128 epilogue threads call it.
-template <int NCOLS, class Fill>
-__device__ __forceinline__ void store_tile_bf16(const CUtensorMap* tmOut, uint8_t* sStore, uint32_t& gc, int row,
-                                                int et, int n0, int t0, int b, Fill&& fill) {
-#pragma unroll 1
-  for (int g = 0; g < NCOLS / 64; ++g, ++gc) {
-    uint8_t* box = sStore + (gc & 1) * (kBlockM * 128);  // gc counts store groups across tiles
-    if (et == 0) tma_store_wait_read<1>();  // the store issued from this box two groups ago has read it
-    epi_bar();
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      float v[32];
-      fill(g * 64 + h * 32, v);
-      stage_row32(box, row, h * 32, v);
-    }
-    fence_async_smem();
-    epi_bar();
-    if (et == 0) {
-      tma_store_3d(tmOut, smem_u32(box), n0 + g * 64, t0, b);
-      tma_store_commit();
-    }
-  }
-}
 
 }  // namespace ttsb
 

@@ -17,59 +17,64 @@ static int num_sms() {
   return g_num_sms;
 }
 
-template <int BLOCK_N, int EPI, bool A_STAT, bool RING = false>
+template <int BLOCK_N, int EPI, bool A_STAT>
 static int launch_gemm(const ttsb200_gemm_args& a, GemmDev& d, cudaStream_t stream) {
-  using Cfg = GemmCfg<BLOCK_N, A_STAT, RING>;
+  using Cfg = GemmCfg<BLOCK_N, EPI, A_STAT>;
   static_assert(Cfg::kSmemBytes <= kMaxSmem, "shared memory budget exceeded");
-  CUtensorMap tmA, tmW, tmOut, tmRes32, tmResBf;
+  CUtensorMap tmA, tmW, tmOut, tmOut32, tmRes32, tmResBf;
+  const uint64_t uN = static_cast<uint64_t>(a.N), uT = static_cast<uint64_t>(a.T), uB = static_cast<uint64_t>(a.B);
   {
-    const uint64_t dims[3] = {static_cast<uint64_t>(a.C), static_cast<uint64_t>(a.T),
-                              static_cast<uint64_t>(a.B)};
-    const uint64_t strides[2] = {static_cast<uint64_t>(a.ldx) * 2,
-                                 static_cast<uint64_t>(a.ldx) * 2 * static_cast<uint64_t>(a.T)};
+    const uint64_t dims[3] = {static_cast<uint64_t>(a.C), uT, uB};
+    const uint64_t strides[2] = {static_cast<uint64_t>(a.ldx) * 2, static_cast<uint64_t>(a.ldx) * 2 * uT};
     const uint32_t box[3] = {kBlockK, kBlockM, 1};
     int rc = make_tmap_bf16(&tmA, a.x, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
   }
   {
-    const uint64_t dims[2] = {static_cast<uint64_t>(a.C),
-                              static_cast<uint64_t>(a.taps) * static_cast<uint64_t>(a.N)};
+    const uint64_t dims[2] = {static_cast<uint64_t>(a.C), static_cast<uint64_t>(a.taps) * uN};
     const uint64_t strides[1] = {static_cast<uint64_t>(a.C) * 2};
     const uint32_t box[2] = {kBlockK, static_cast<uint32_t>(Cfg::kWBoxN)};
     int rc = make_tmap_bf16(&tmW, a.w, 2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
   }
+  tmOut = tmA;  // placeholders keep the descriptor prefetches valid when a map is unused
   if (a.out_bf16 && a.N % 64 == 0) {
-    const uint64_t dims[3] = {static_cast<uint64_t>(a.N), static_cast<uint64_t>(a.T),
-                              static_cast<uint64_t>(a.B)};
-    const uint64_t strides[2] = {static_cast<uint64_t>(a.N) * 2,
-                                 static_cast<uint64_t>(a.N) * 2 * static_cast<uint64_t>(a.T)};
-    const uint32_t box[3] = {64, kBlockM, 1};
-    int rc = make_tmap_bf16(&tmOut, a.out_bf16, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+    const uint64_t dims[3] = {uN, uT, uB};
+    const uint64_t strides[2] = {uN * 2, uN * 2 * uT};
+    // staging boxes: 64 columns / SWIZZLE_128B (AFFINE) or 32 columns / SWIZZLE_64B (LN epilogues)
+    const uint32_t box[3] = {Cfg::kIsLN ? 32u : 64u, kBlockM, 1};
+    int rc = make_tmap_bf16(&tmOut, a.out_bf16, 3, dims, strides, box,
+                            Cfg::kIsLN ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
-  } else {
-    tmOut = tmA;  // never used for stores in this configuration; keeps the descriptor prefetch valid
   }
+  tmOut32 = tmA;
   tmRes32 = tmA;
   tmResBf = tmA;
-  if (RING) {
-    const uint64_t dims[3] = {static_cast<uint64_t>(a.N), static_cast<uint64_t>(a.T), static_cast<uint64_t>(a.B)};
+  if (Cfg::kRing) {
+    const uint32_t box32[3] = {32, kBlockM, 1};
+    if (a.out_f32) {
+      const uint64_t dims[3] = {uN, uT, uB};
+      const uint64_t strides[2] = {uN * 4, uN * 4 * uT};
+      int rc = make_tmap(&tmOut32, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, a.out_f32, 3, dims, strides, box32,
+                         CU_TENSOR_MAP_SWIZZLE_128B);
+      if (rc) return rc;
+    }
     {
-      const uint64_t strides[2] = {static_cast<uint64_t>(a.res_tstride) * 4, static_cast<uint64_t>(a.res_bstride) * 4};
-      const uint32_t box[3] = {32, kBlockM, 1};
-      int rc = make_tmap(&tmRes32, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, a.res_f32, 3, dims, strides, box,
+      const uint64_t dims[3] = {uN, uT, d.res_bcast ? 1 : uB};
+      const uint64_t strides[2] = {uN * 4, uN * 4 * uT};
+      int rc = make_tmap(&tmRes32, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, a.res_f32, 3, dims, strides, box32,
                          CU_TENSOR_MAP_SWIZZLE_128B);
       if (rc) return rc;
     }
     if (EPI == TTSB200_EPI_FFN2) {
-      const uint64_t strides[2] = {static_cast<uint64_t>(a.N) * 2,
-                                   static_cast<uint64_t>(a.N) * 2 * static_cast<uint64_t>(a.T)};
+      const uint64_t dims[3] = {uN, uT, uB};
+      const uint64_t strides[2] = {uN * 2, uN * 2 * uT};
       const uint32_t box[3] = {64, kBlockM, 1};
       int rc = make_tmap_bf16(&tmResBf, a.res_bf16, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
       if (rc) return rc;
     }
   }
-  auto kern = conv_gemm_kernel<BLOCK_N, EPI, A_STAT, RING>;
+  auto kern = conv_gemm_kernel<BLOCK_N, EPI, A_STAT>;
   static bool attr_done = false;  // per instantiation
   if (!attr_done) {
     TTSB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
@@ -80,10 +85,12 @@ static int launch_gemm(const ttsb200_gemm_args& a, GemmDev& d, cudaStream_t stre
   d.num_tiles = a.B * d.m_tiles * d.n_tiles;
   const int units = A_STAT ? a.B * d.m_tiles : d.num_tiles;
   const int grid = units < num_sms() ? units : num_sms();
-  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(tmA, tmW, tmOut, tmRes32, tmResBf, d);
+  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(tmA, tmW, tmOut, tmOut32, tmRes32, tmResBf, d);
   TTSB_CHECK_CUDA(cudaGetLastError());
   return TTSB_OK;
 }
+
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 }  // namespace ttsb
 
@@ -96,20 +103,19 @@ extern "C" int ttsb200_conv_gemm(const ttsb200_gemm_args* a, ttsb200_stream_t st
   TTSB_CHECK_ARG(a->x && a->w, "conv_gemm: null x/w");
   TTSB_CHECK_ARG(a->C % 8 == 0 && a->ldx % 8 == 0 && a->ldx >= a->C,
                  "conv_gemm: C (%d) and ldx (%lld) must be multiples of 8, ldx >= C", a->C, (long long)a->ldx);
-  TTSB_CHECK_ARG((reinterpret_cast<uintptr_t>(a->x) & 15) == 0 && (reinterpret_cast<uintptr_t>(a->w) & 15) == 0,
-                 "conv_gemm: x/w must be 16-byte aligned");
+  TTSB_CHECK_ARG(aligned16(a->x) && aligned16(a->w), "conv_gemm: x/w must be 16-byte aligned");
   TTSB_CHECK_ARG(a->block_n > 0 && a->N % a->block_n == 0, "conv_gemm: N (%d) not a multiple of block_n (%d)",
                  a->N, a->block_n);
   TTSB_CHECK_ARG(a->bias != nullptr, "conv_gemm: bias required");
-  if (a->out_bf16)
-    TTSB_CHECK_ARG((reinterpret_cast<uintptr_t>(a->out_bf16) & 15) == 0, "conv_gemm: out_bf16 must be 16-byte aligned");
+  if (a->out_bf16) TTSB_CHECK_ARG(aligned16(a->out_bf16), "conv_gemm: out_bf16 must be 16-byte aligned");
+  if (a->out_f32) TTSB_CHECK_ARG(aligned16(a->out_f32), "conv_gemm: out_f32 must be 16-byte aligned");
   GemmDev d;
   d.B = a->B; d.T = a->T; d.N = a->N; d.C = a->C; d.taps = a->taps; d.pad_left = a->pad_left;
   d.epi = a->epi; d.act = a->act;
   d.m_tiles = d.n_tiles = d.num_tiles = 0;
+  d.res_bcast = 0;
   d.bias = a->bias; d.scale = a->scale; d.res_f32 = a->res_f32;
   d.res_bstride = a->res_bstride; d.res_tstride = a->res_tstride; d.res_scale = a->res_scale;
-  d.res_bf16 = static_cast<const __nv_bfloat16*>(a->res_bf16);
   d.ln1_g = a->ln1_g; d.ln1_b = a->ln1_b; d.ln2_g = a->ln2_g; d.ln2_b = a->ln2_b; d.eps = a->eps;
   d.dot_w = a->dot_w; d.dot_b = a->dot_b; d.row_mask = a->row_mask;
   d.out_f32 = a->out_f32; d.out_bf16 = static_cast<__nv_bfloat16*>(a->out_bf16);
@@ -119,7 +125,8 @@ extern "C" int ttsb200_conv_gemm(const ttsb200_gemm_args* a, ttsb200_stream_t st
   if (e == TTSB200_EPI_AFFINE_ACT) {
     TTSB_CHECK_ARG(a->out_f32 || a->out_bf16, "conv_gemm: AFFINE_ACT needs an output");
     if (a->res_f32)
-      TTSB_CHECK_ARG(a->res_tstride % 4 == 0 && a->res_bstride % 4 == 0, "conv_gemm: res strides % 4");
+      TTSB_CHECK_ARG(a->res_tstride % 4 == 0 && a->res_bstride % 4 == 0 && aligned16(a->res_f32),
+                     "conv_gemm: res strides % 4, 16-byte aligned");
     // A-stationary sweep: plain linears on <= 384 input channels with bf16-only output
     const bool a_stat = a->taps == 1 && a->C <= 384 && a->C % 64 == 0 && a->out_bf16 && !a->out_f32 &&
                         !a->res_f32 && a->N / bn >= 2;
@@ -136,27 +143,22 @@ extern "C" int ttsb200_conv_gemm(const ttsb200_gemm_args* a, ttsb200_stream_t st
       if (a_stat) return launch_gemm<256, TTSB200_EPI_AFFINE_ACT, true>(*a, d, stream);
       return launch_gemm<256, TTSB200_EPI_AFFINE_ACT, false>(*a, d, stream);
     }
-    if (bn == 384) return launch_gemm<384, TTSB200_EPI_AFFINE_ACT, false>(*a, d, stream);
-  } else if (e == TTSB200_EPI_RES_LN) {
+  } else if (e == TTSB200_EPI_RES_LN || e == TTSB200_EPI_FFN2) {
     TTSB_CHECK_ARG(bn == a->N, "conv_gemm: LN epilogue needs block_n == N");
-    TTSB_CHECK_ARG(a->res_f32 && a->ln1_g && a->ln1_b && a->out_bf16, "conv_gemm: RES_LN operands");
-    TTSB_CHECK_ARG(a->res_tstride % 4 == 0 && a->res_bstride % 4 == 0, "conv_gemm: res strides % 4");
-    // residual prefetch ring: dense fp32 residual (not the broadcast positional table), short K
-    const bool ring = a->res_bstride == static_cast<int64_t>(a->T) * a->N && a->res_tstride == a->N &&
-                      !a->res_scale && a->taps * a->C <= 2048 &&
-                      (reinterpret_cast<uintptr_t>(a->res_f32) & 15) == 0;
-    if (bn == 384 && ring) return launch_gemm<384, TTSB200_EPI_RES_LN, false, true>(*a, d, stream);
-    if (bn == 384) return launch_gemm<384, TTSB200_EPI_RES_LN, false>(*a, d, stream);
-  } else if (e == TTSB200_EPI_FFN2) {
-    TTSB_CHECK_ARG(bn == a->N, "conv_gemm: LN epilogue needs block_n == N");
-    TTSB_CHECK_ARG(a->res_f32 && a->res_bf16 && a->ln1_g && a->ln1_b && a->ln2_g && a->ln2_b && a->out_bf16,
-                   "conv_gemm: FFN2 operands");
-    TTSB_CHECK_ARG(a->res_tstride % 4 == 0 && a->res_bstride % 4 == 0, "conv_gemm: res strides % 4");
-    const bool ring = a->res_bstride == static_cast<int64_t>(a->T) * a->N && a->res_tstride == a->N &&
-                      a->taps * a->C <= 2048 && (reinterpret_cast<uintptr_t>(a->res_f32) & 15) == 0 &&
-                      (reinterpret_cast<uintptr_t>(a->res_bf16) & 15) == 0;
-    if (bn == 384 && ring) return launch_gemm<384, TTSB200_EPI_FFN2, false, true>(*a, d, stream);
-    if (bn == 384) return launch_gemm<384, TTSB200_EPI_FFN2, false>(*a, d, stream);
+    TTSB_CHECK_ARG(a->res_f32 && a->ln1_g && a->ln1_b && a->out_bf16, "conv_gemm: RES_LN/FFN2 operands");
+    // the fp32 residual is fetched by TMA: dense rows, per-utterance (T*N) or broadcast (0) batch stride
+    TTSB_CHECK_ARG(a->res_tstride == a->N &&
+                       (a->res_bstride == static_cast<int64_t>(a->T) * a->N || a->res_bstride == 0) &&
+                       aligned16(a->res_f32),
+                   "conv_gemm: res_f32 must be dense (tstride == N, bstride == T*N or 0) and 16-byte aligned");
+    d.res_bcast = a->res_bstride == 0 ? 1 : 0;
+    if (e == TTSB200_EPI_FFN2) {
+      TTSB_CHECK_ARG(a->res_bf16 && a->ln2_g && a->ln2_b && aligned16(a->res_bf16), "conv_gemm: FFN2 operands");
+      TTSB_CHECK_ARG(!a->res_scale, "conv_gemm: res_scale is a RES_LN operand");
+      if (bn == 384) return launch_gemm<384, TTSB200_EPI_FFN2, false>(*a, d, stream);
+    } else {
+      if (bn == 384) return launch_gemm<384, TTSB200_EPI_RES_LN, false>(*a, d, stream);
+    }
   } else if (e == TTSB200_EPI_RELU_LN) {
     TTSB_CHECK_ARG(bn == a->N, "conv_gemm: LN epilogue needs block_n == N");
     TTSB_CHECK_ARG(a->ln1_g && a->ln1_b && a->out_bf16, "conv_gemm: RELU_LN operands");

@@ -3,24 +3,16 @@
 
 namespace ttsb {
 
-template <int N, class F>
-__device__ __forceinline__ void for_each_chunk32(uint32_t trow, F&& f) {
-#pragma unroll 1
-  for (int c = 0; c < N; c += 32) {
-    float v[32];
-    tmem_ld32(trow + c, v);
-    tmem_ld_wait();
-    f(c, v);
-  }
-}
-
-template <int BLOCK_N, int EPI, bool A_STAT, bool RING>
+template <int BLOCK_N, int EPI, bool A_STAT>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
-                 const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes32,
-                 const __grid_constant__ CUtensorMap tmResBf, const GemmDev p) {
-  using Cfg = GemmCfg<BLOCK_N, A_STAT, RING>;
+                 const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmOut32,
+                 const __grid_constant__ CUtensorMap tmRes32, const __grid_constant__ CUtensorMap tmResBf,
+                 const GemmDev p) {
+  using Cfg = GemmCfg<BLOCK_N, EPI, A_STAT>;
   constexpr int S = Cfg::kStages;
+  constexpr int RS = Cfg::kRingSlots > 0 ? Cfg::kRingSlots : 1;
+  constexpr int HALF = BLOCK_N / 2;  // LN epilogues: columns per warpgroup
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;
   if ((smem_u32(smem) & 1023u) != 0) {
@@ -29,11 +21,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
   uint8_t* sARes = smem;                                  // A_STAT only: 6 x 16 KB
   uint8_t* sStages = smem + Cfg::kAResBytes;
-  uint8_t* sStore = sStages + S * Cfg::kStageBytes;       // 2 x 16 KB, 1024-aligned
-  uint8_t* sRing = sStore + Cfg::kStoreBytes;             // RING only: 4 x 16 KB
-  float* sBias = reinterpret_cast<float*>(sRing + Cfg::kRingBytes);
-  float* sScale = sBias + BLOCK_N;  // only backed by smem when Cfg::kScaleInSmem
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + (Cfg::kScaleInSmem ? 2 : 1) * BLOCK_N);
+  uint8_t* sStore = sStages + S * Cfg::kStageBytes;       // one bf16 staging box per warpgroup, 1024-aligned
+  uint8_t* sRing = sStore + Cfg::kStoreBytes;             // kRing only: 4 x 16 KB
+  float* sParam = reinterpret_cast<float*>(sRing + Cfg::kRingBytes);
+  float2* sStat = reinterpret_cast<float2*>(sParam + Cfg::kParamFloats);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sStat) + Cfg::kStatBytes);
   uint64_t* bar_full = bars;             // [S]
   uint64_t* bar_empty = bars + S;        // [S]
   uint64_t* bar_accf = bars + 2 * S;     // [2]
@@ -61,13 +53,13 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(smem_u32(&bar_accf[i]), 1);
-      mbar_init(smem_u32(&bar_acce[i]), kEpiThreads);
+      mbar_init(smem_u32(&bar_acce[i]), Cfg::kIsLN ? kEpiThreads : kWgThreads);
     }
     mbar_init(smem_u32(bar_af), 1);
     mbar_init(smem_u32(bar_ae), 1);
     for (int i = 0; i < 4; ++i) {
       mbar_init(smem_u32(&bar_rf[i]), 1);
-      mbar_init(smem_u32(&bar_re[i]), kEpiThreads);
+      mbar_init(smem_u32(&bar_re[i]), kWgThreads);
     }
     fence_mbar_init();
   }
@@ -171,30 +163,33 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (A_STAT) umma_commit(smem_u32(bar_ae));  // resident A may be overwritten
       }
     }
-  } else if (warp < 6) {
-#include "gemm_epilogue.inc"
-  } else if (RING) {
+  } else if (warp == 2) {
     // ===================== residual-ring producer =====================
-    if (lane == 0) {
+    // Items are pushed in the order the two warpgroups consume them: item i belongs to half (i & 1).
+    if (Cfg::kRing && lane == 0) {
       tma_prefetch_desc(&tmRes32);
       tma_prefetch_desc(&tmResBf);
-      uint32_t rit = 0;
+      uint32_t i = 0;
       auto push = [&](const CUtensorMap* tm, int c0, int t0, int b) {
-        const int slot = rit & 3;
-        mbar_wait(smem_u32(&bar_re[slot]), ((rit >> 2) & 1) ^ 1);
+        const int slot = i % RS;
+        mbar_wait(smem_u32(&bar_re[slot]), ((i / RS) & 1) ^ 1);
         const uint32_t full = smem_u32(&bar_rf[slot]);
-        mbar_arrive_expect_tx(full, Cfg::kRingSlotBytes);
-        tma_load_3d(smem_u32(sRing + slot * Cfg::kRingSlotBytes), tm, full, c0, t0, b);
-        ++rit;
+        mbar_arrive_expect_tx(full, kBoxBytes16K);
+        tma_load_3d(smem_u32(sRing + slot * kBoxBytes16K), tm, full, c0, t0, b);
+        ++i;
       };
       for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
         int b, t0, nt0;
         decode(unit, b, t0, nt0);
         if (EPI == TTSB200_EPI_FFN2)
-          for (int g = 0; g < BLOCK_N / 64; ++g) push(&tmResBf, g * 64, t0, b);  // bf16 inner residual
-        for (int c = 0; c < BLOCK_N / 32; ++c) push(&tmRes32, c * 32, t0, b);    // fp32 residual stream
+          for (int g = 0; g < HALF / 64; ++g)
+            for (int hh = 0; hh < 2; ++hh) push(&tmResBf, hh * HALF + g * 64, t0, b);  // bf16 inner residual
+        for (int c = 0; c < HALF / 32; ++c)
+          for (int hh = 0; hh < 2; ++hh) push(&tmRes32, hh * HALF + c * 32, t0, p.res_bcast ? 0 : b);  // fp32 stream
       }
     }
+  } else if (warp >= kEpiWarp0) {
+#include "gemm_epilogue.inc"
   }
 
   tc_fence_before();
