@@ -85,11 +85,13 @@ int ttsb200_conv_gemm(const ttsb200_gemm_args* args, ttsb200_stream_t stream);
  * Fused masked multi-head self-attention (Models/modules.py:7-21 inside :43-70).
  *   qkv: bf16 (B,T,3*H*Dh) as [q | k | v] along the last axis (the fused q/k/v linears' output)
  *   ctx: bf16 (B,T,H*Dh)  = concat_h softmax(mask(q k^T / sqrt(Dh), -1e4)) v
- * mask (B,T) uint8 marks valid keys; kv_len[b] = 1 + index of the last valid key (0 = none) lets
- * the kernel skip fully padded key tiles (their probabilities are exactly 0 in fp32).
+ * mask (B,T) uint8 marks valid keys; kv_info (B,2) int32 from ttsb200_mask_lengths:
+ * kv_info[b][0] = 1 + index of the last valid key (0 = none) lets the kernel skip fully padded key
+ * tiles (their probabilities are exactly 0 in fp32); kv_info[b][1] = length of the all-valid prefix,
+ * inside which key tiles never read the mask.
  * Dh must be 96 (H*Dh = 384) in this build.
  * ---------------------------------------------------------------------------------------------- */
-int ttsb200_attention_fwd(const void* qkv, const uint8_t* mask, const int32_t* kv_len, void* ctx,
+int ttsb200_attention_fwd(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
                           int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t stream);
 /* Debug/parity only: also materialise the (B,H,T,T) fp32 probabilities the reference returns
  * (Models/modules.py:21, Models/encoder.py:97,105).  Plain CUDA-core kernel, not on the timed path. */
@@ -99,8 +101,9 @@ int ttsb200_attention_probs(const void* qkv, const uint8_t* mask, float* probs, 
 /* ------------------------------------------------------------------------------------------------
  * HBM-bound row kernels
  * ---------------------------------------------------------------------------------------------- */
-/* kv_len[b] = 1 + last index with mask != 0 (0 if none).  (mask contract: train_fastspeech2.py:55-82) */
-int ttsb200_mask_lengths(const uint8_t* mask, int32_t* kv_len, int32_t B, int32_t T,
+/* kv_info (B,2) int32: [b][0] = 1 + last index with mask != 0 (0 if none), [b][1] = index of the first
+ * zero (T if none).  (mask contract: train_fastspeech2.py:55-82) */
+int ttsb200_mask_lengths(const uint8_t* mask, int32_t* kv_info, int32_t B, int32_t T,
                          ttsb200_stream_t stream);
 
 /* x0 = table[ids] + alpha*pe[t]  (Models/encoder.py:84,94; Models/modules.py:107-111) and

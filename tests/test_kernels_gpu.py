@@ -216,7 +216,7 @@ def test_attention(L, B, T, lens):
     for i, n in enumerate(lens):
         mask[i, :n] = 1
     kv = L.mask_lengths(mask)
-    assert kv.tolist() == lens
+    assert kv[:, 0].tolist() == lens and kv[:, 1].tolist() == lens  # prefix masks: last valid + 1 == clean prefix
     ctx = torch.empty(B, T, H * Dh, device=dev(), dtype=torch.bfloat16)
     L.attention_fwd(qkv, mask, kv, ctx, H)
     torch.cuda.synchronize()

@@ -51,8 +51,8 @@ struct GemmCfg {
   static constexpr int kWBoxBytes = kWBoxN * kBlockK * 2;
   static constexpr int kStageBytes = A_STAT ? kWBytes : kABytes + kWBytes;
   static constexpr int kAResBytes = A_STAT ? 6 * kABytes : 0;            // resident A: up to C = 384
-  // one bf16 staging box per warpgroup: 128 rows x 64 columns (AFFINE) or x 32 columns (LN epilogues)
-  static constexpr int kStoreBytes = kIsLN ? 2 * 8192 : 2 * kBoxBytes16K;
+  // one bf16 staging box per warpgroup: 128 rows x 32 columns (SWIZZLE_64B)
+  static constexpr int kStoreBytes = 2 * 8192;
   static constexpr int kRingSlots = kRing ? 4 : 0;  // even: each half owns its own slots
   static constexpr int kRingBytes = kRingSlots * kBoxBytes16K;
   // parameter vectors in smem: AFFINE: (bias, scale) per warpgroup; LN: bias, g1, b1, g2, b2, dot_w

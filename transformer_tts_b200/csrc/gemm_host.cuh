@@ -41,10 +41,8 @@ static int launch_gemm(const ttsb200_gemm_args& a, GemmDev& d, cudaStream_t stre
   if (a.out_bf16 && a.N % 64 == 0) {
     const uint64_t dims[3] = {uN, uT, uB};
     const uint64_t strides[2] = {uN * 2, uN * 2 * uT};
-    // staging boxes: 64 columns / SWIZZLE_128B (AFFINE) or 32 columns / SWIZZLE_64B (LN epilogues)
-    const uint32_t box[3] = {Cfg::kIsLN ? 32u : 64u, kBlockM, 1};
-    int rc = make_tmap_bf16(&tmOut, a.out_bf16, 3, dims, strides, box,
-                            Cfg::kIsLN ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B);
+    const uint32_t box[3] = {32, kBlockM, 1};  // staging boxes: 128 rows x 32 columns, SWIZZLE_64B
+    int rc = make_tmap_bf16(&tmOut, a.out_bf16, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_64B);
     if (rc) return rc;
   }
   tmOut32 = tmA;

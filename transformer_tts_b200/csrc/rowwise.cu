@@ -218,16 +218,25 @@ bucket_embed_add_kernel(const __nv_bfloat16* __restrict__ x, const float* __rest
   }
 }
 
-__global__ void mask_lengths_kernel(const uint8_t* __restrict__ mask, int32_t* __restrict__ kv_len, int B, int T) {
+// kv_info[b] = (1 + index of the last valid key, length of the all-valid prefix)
+__global__ void mask_lengths_kernel(const uint8_t* __restrict__ mask, int32_t* __restrict__ kv_info, int B, int T) {
   const int lane = threadIdx.x & 31;
   const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (b >= B) return;
-  int last = 0;
-  for (int t = lane; t < T; t += 32)
+  int last = 0, first_zero = T;
+  for (int t = lane; t < T; t += 32) {
     if (mask[static_cast<int64_t>(b) * T + t]) last = t + 1;
+    else first_zero = min(first_zero, t);
+  }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) last = max(last, __shfl_xor_sync(0xffffffffu, last, o));
-  if (lane == 0) kv_len[b] = last;
+  for (int o = 16; o > 0; o >>= 1) {
+    last = max(last, __shfl_xor_sync(0xffffffffu, last, o));
+    first_zero = min(first_zero, __shfl_xor_sync(0xffffffffu, first_zero, o));
+  }
+  if (lane == 0) {
+    kv_info[2 * b] = last;
+    kv_info[2 * b + 1] = first_zero;
+  }
 }
 
 __global__ void cast_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, int64_t n) {
@@ -246,10 +255,10 @@ using namespace ttsb;
 
 #define TTSB_LAUNCH_CHECK() TTSB_CHECK_CUDA(cudaGetLastError())
 
-extern "C" int ttsb200_mask_lengths(const uint8_t* mask, int32_t* kv_len, int32_t B, int32_t T,
+extern "C" int ttsb200_mask_lengths(const uint8_t* mask, int32_t* kv_info, int32_t B, int32_t T,
                                     ttsb200_stream_t s) {
-  TTSB_CHECK_ARG(mask && kv_len && B > 0 && T > 0, "mask_lengths: bad args");
-  mask_lengths_kernel<<<(B + 7) / 8, 256, 0, static_cast<cudaStream_t>(s)>>>(mask, kv_len, B, T);
+  TTSB_CHECK_ARG(mask && kv_info && B > 0 && T > 0, "mask_lengths: bad args");
+  mask_lengths_kernel<<<(B + 7) / 8, 256, 0, static_cast<cudaStream_t>(s)>>>(mask, kv_info, B, T);
   TTSB_LAUNCH_CHECK();
   return TTSB_OK;
 }

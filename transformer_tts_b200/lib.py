@@ -185,7 +185,7 @@ def attention_probs(qkv: torch.Tensor, mask: torch.Tensor, H: int) -> torch.Tens
 # --------------------------------------------------------------------------------------------------
 def mask_lengths(mask: torch.Tensor) -> torch.Tensor:
     B, T = mask.shape
-    out = torch.empty((B,), device=mask.device, dtype=torch.int32)
+    out = torch.empty((B, 2), device=mask.device, dtype=torch.int32)  # (1 + last valid, clean-prefix length)
     _check(load().ttsb200_mask_lengths(_ptr(mask, torch.uint8, "mask"), _ptr(out), B, T, _stream()), "mask_lengths")
     _count()
     return out
