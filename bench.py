@@ -140,8 +140,8 @@ def reference_arm(args):
 
 def kernel_rooflines(model, peaks, tmax):
     """Per-kernel rooflines at the decoder shape of the workload (B x Tmax rows): every hot kernel is timed
-    alone with CUDA events on the launching stream, rotating over three buffer sets so that consecutive
-    launches never find their operands in the 126 MB L2.  Algorithmic work per launch as in DESIGN.md."""
+    alone with CUDA events around a captured graph of 12 launches, rotating over three buffer sets so that
+    consecutive launches never find their operands in the 126 MB L2.  Algorithmic work per launch as in DESIGN.md."""
     import torch
 
     from transformer_tts_b200 import lib
@@ -218,18 +218,28 @@ def kernel_rooflines(model, peaks, tmax):
         ("layernorm standalone fp32 -> bf16", t_ln, "hbm", M * D * (4 + s2)),
     ]
     out = []
-    n = 12
+    reps = 4
     for name, fn, bound, work in specs:
         for i in range(NS):
-            fn(i)
-        ev = [torch.cuda.Event(enable_timing=True) for _ in range(n + 1)]
+            fn(i)  # warm-up: first-call attribute setup, allocator pools
         torch.cuda.synchronize()
-        ev[0].record()
-        for i in range(n):
-            fn(i % NS)
-            ev[i + 1].record()
+        # reps x NS launches captured in one CUDA graph: back-to-back on the device, no host launch gaps
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            for _ in range(reps):
+                for i in range(NS):
+                    fn(i)
+        graph.replay()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize()
-        ms = statistics.median(ev[i].elapsed_time(ev[i + 1]) for i in range(n))
+        times = []
+        for _ in range(3):
+            e0.record()
+            graph.replay()
+            e1.record()
+            torch.cuda.synchronize()
+            times.append(e0.elapsed_time(e1) / (reps * NS))
+        ms = statistics.median(times)
         if bound == "tensor":
             ach, peak, unit = work / (ms * 1e-3) / 1e12, peaks["tc_burst"], "TFLOP/s"
         else:

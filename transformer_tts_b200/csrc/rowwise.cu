@@ -128,7 +128,7 @@ __global__ void lr_scan_kernel(const int32_t* __restrict__ dur, int32_t* __restr
   if (lane == 0) mel_len[b] = carry;
 }
 
-constexpr int kLrFrames = 32;  // frames per CTA
+constexpr int kLrFrames = 64;  // frames per CTA
 __global__ void __launch_bounds__(256)
 lr_expand_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict__ cum,
                  const int32_t* __restrict__ mel_len, __nv_bfloat16* __restrict__ out,
@@ -162,30 +162,36 @@ lr_expand_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict_
   __syncthreads();
   const int chunks = D >> 3;  // 16-byte chunks per row
   const int total = kLrFrames * chunks;
-  for (int c = threadIdx.x; c < total; c += blockDim.x) {
-    const int f = c / chunks;
-    const int k = c - f * chunks;
-    const int t = t0 + f;
-    if (t >= Tmax) break;
-    const int src = s_src[f];
-    uint4 v = make_uint4(0, 0, 0, 0);
-    if (src >= 0) v = __ldg(reinterpret_cast<const uint4*>(x + (static_cast<int64_t>(b) * L + src) * D) + k);
-    __stcs(reinterpret_cast<uint4*>(out + (static_cast<int64_t>(b) * Tmax + t) * D) + k, v);
+  const uint4* xb = reinterpret_cast<const uint4*>(x + static_cast<int64_t>(b) * L * D);
+  uint4* ob = reinterpret_cast<uint4*>(out + (static_cast<int64_t>(b) * Tmax + t0) * D);
+  // four independent 16-byte gathers in flight per thread before the first store
+  constexpr int U = 4;
+  for (int c0 = threadIdx.x; c0 < total; c0 += U * 256) {
+    uint4 v[U];
+    bool ok[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int c = c0 + u * 256;
+      const int f = c / chunks;
+      ok[u] = c < total && t0 + f < Tmax;
+      v[u] = make_uint4(0, 0, 0, 0);
+      if (ok[u]) {
+        const int src = s_src[f];
+        if (src >= 0) v[u] = __ldg(xb + static_cast<int64_t>(src) * chunks + (c - f * chunks));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (ok[u]) __stcs(ob + c0 + u * 256, v[u]);
   }
 }
 
 // ------------------------------------------------------------------------------------------------
 // bucketize (right=False -> lower_bound) + two embedding gathers + add; warp per row
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ int lower_bound_f32(const float* __restrict__ bins, int nb, float v) {
-  int lo = 0, hi = nb;  // answer in [0, nb]
-  while (lo < hi) {
-    const int mid = (lo + hi) >> 1;
-    if (__ldg(bins + mid) >= v) hi = mid; else lo = mid + 1;
-  }
-  return lo;
-}
-
+// Each lane keeps 8 consecutive bin edges of both tables in registers; lower_bound(v) = number of edges
+// that are not >= v, summed over the warp (edges ascend, so this is the first index with bins[i] >= v,
+// and a NaN lands in the last bucket exactly like the binary search / torch.bucketize).
 template <int NV>
 __global__ void __launch_bounds__(256)
 bucket_embed_add_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ p,
@@ -195,26 +201,47 @@ bucket_embed_add_kernel(const __nv_bfloat16* __restrict__ x, const float* __rest
                         int32_t* __restrict__ p_idx, int32_t* __restrict__ e_idx, int64_t rows, int nb) {
   constexpr int D = 128 * NV;
   const int lane = threadIdx.x & 31;
-  const int64_t row = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (row >= rows) return;
-  const int pi = lower_bound_f32(pbins, nb, __ldg(p + row));
-  const int ei = lower_bound_f32(ebins, nb, __ldg(e + row));
-  if (lane == 0) {
-    if (p_idx) p_idx[row] = pi;
-    if (e_idx) e_idx[row] = ei;
-  }
+  const int64_t warp0 = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t nwarps = static_cast<int64_t>(gridDim.x) * (blockDim.x >> 5);
+  float pb[8], eb[8];
 #pragma unroll
-  for (int i = 0; i < NV; ++i) {
-    const int c = i * 32 + lane;  // 4-element chunk
-    const uint2 xv = __ldcs(reinterpret_cast<const uint2*>(x + row * D) + c);
-    const float2 x01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&xv.x));
-    const float2 x23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&xv.y));
-    const float4 a = __ldg(reinterpret_cast<const float4*>(ptab + static_cast<int64_t>(pi) * D) + c);
-    const float4 bq = __ldg(reinterpret_cast<const float4*>(etab + static_cast<int64_t>(ei) * D) + c);
-    // the reference adds pitch first, then energy (varianceadaptor.py:123-126)
-    const float4 r = make_float4((x01.x + a.x) + bq.x, (x01.y + a.y) + bq.y, (x23.x + a.z) + bq.z,
-                                 (x23.y + a.w) + bq.w);
-    store_bf16x4(out + row * D + c * 4, r);
+  for (int i = 0; i < 8; ++i) {
+    const int k = lane * 8 + i;
+    pb[i] = k < nb ? __ldg(pbins + k) : INFINITY;
+    eb[i] = k < nb ? __ldg(ebins + k) : INFINITY;
+  }
+  for (int64_t row = warp0; row < rows; row += nwarps) {
+    const float pv = __ldg(p + row), ev = __ldg(e + row);
+    // issue the activation loads before the bucket reduction
+    uint2 xv[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) xv[i] = __ldcs(reinterpret_cast<const uint2*>(x + row * D) + i * 32 + lane);
+    int pc = 0, ec = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      pc += !(pb[i] >= pv);
+      ec += !(eb[i] >= ev);
+    }
+    int both = pc | (ec << 16);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) both += __shfl_xor_sync(0xffffffffu, both, o);
+    const int pi = min(both & 0xffff, nb), ei = min(both >> 16, nb);
+    if (lane == 0) {
+      if (p_idx) p_idx[row] = pi;
+      if (e_idx) e_idx[row] = ei;
+    }
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = i * 32 + lane;  // 4-element chunk
+      const float2 x01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&xv[i].x));
+      const float2 x23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&xv[i].y));
+      const float4 a = __ldg(reinterpret_cast<const float4*>(ptab + static_cast<int64_t>(pi) * D) + c);
+      const float4 bq = __ldg(reinterpret_cast<const float4*>(etab + static_cast<int64_t>(ei) * D) + c);
+      // the reference adds pitch first, then energy (varianceadaptor.py:123-126)
+      const float4 r = make_float4((x01.x + a.x) + bq.x, (x01.y + a.y) + bq.y, (x23.x + a.z) + bq.z,
+                                   (x23.y + a.w) + bq.w);
+      store_bf16x4(out + row * D + c * 4, r);
+    }
   }
 }
 
@@ -334,7 +361,9 @@ extern "C" int ttsb200_bucket_embed_add(const void* x, const float* p, const flo
                                         int64_t rows, int32_t D, int32_t nb, ttsb200_stream_t s) {
   TTSB_CHECK_ARG(x && p && e && pbins && ebins && ptab && etab && out && rows > 0 && nb > 0,
                  "bucket_embed_add: bad args");
-  const unsigned grid = static_cast<unsigned>((rows + 7) / 8);
+  TTSB_CHECK_ARG(nb <= 256, "bucket_embed_add: at most 256 bin edges (got %d)", nb);
+  const int64_t want = (rows + 7) / 8;
+  const unsigned grid = static_cast<unsigned>(want < 148 * 16 ? want : 148 * 16);  // persistent warps, 4+ rows each
   cudaStream_t st = static_cast<cudaStream_t>(s);
   if (D == 384)
     bucket_embed_add_kernel<3><<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), p, e, pbins,
