@@ -50,7 +50,12 @@ enum {
   TTSB200_EPI_RELU_LN_DOT = 4  /* out_row = mask ? dot(LN1(relu(acc+bias)), dot_w) + dot_b : 0
                                   — Models/varianceadaptor.py:220-229                               */
 };
-enum { TTSB200_ACT_NONE = 0, TTSB200_ACT_RELU = 1, TTSB200_ACT_TANH = 2 };
+enum {
+  TTSB200_ACT_NONE = 0,
+  TTSB200_ACT_RELU = 1,
+  TTSB200_ACT_TANH = 2,
+  TTSB200_ACT_RELU_GRAD = 3 /* backward of ReLU: v = gate_bf16[b,t,n] > 0 ? v : 0 (dgrad GEMMs) */
+};
 
 typedef struct ttsb200_gemm_args {
   /* problem */
@@ -77,6 +82,9 @@ typedef struct ttsb200_gemm_args {
   void* out_bf16;
   float* out2_f32;
   float* out_row; /* (B,T) */
+  /* training extras (NULL in inference) */
+  float* pre_f32;        /* LN epilogues: pre-LayerNorm value (B,T,N) saved for the backward pass */
+  const void* gate_bf16; /* ACT_RELU_GRAD: saved forward activation, bf16 (B,T,N) */
 } ttsb200_gemm_args;
 
 int ttsb200_conv_gemm(const ttsb200_gemm_args* args, ttsb200_stream_t stream);
@@ -93,6 +101,11 @@ int ttsb200_conv_gemm(const ttsb200_gemm_args* args, ttsb200_stream_t stream);
  * ---------------------------------------------------------------------------------------------- */
 int ttsb200_attention_fwd(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
                           int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t stream);
+/* Training forward: same kernel, also writes lse2 (B,H,T) fp32 = log2-domain log-sum-exp of every
+ * query row, so that p = exp2(s * log2(e)/sqrt(Dh) - lse2) in the backward kernels. */
+int ttsb200_attention_fwd_lse(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
+                              float* lse2, int32_t B, int32_t T, int32_t H, int32_t Dh,
+                              ttsb200_stream_t stream);
 /* Debug/parity only: also materialise the (B,H,T,T) fp32 probabilities the reference returns
  * (Models/modules.py:21, Models/encoder.py:97,105).  Plain CUDA-core kernel, not on the timed path. */
 int ttsb200_attention_probs(const void* qkv, const uint8_t* mask, float* probs, int32_t B, int32_t T,
@@ -144,6 +157,83 @@ int ttsb200_bucket_embed_add(const void* x_bf16, const float* p, const float* e,
 
 /* fp32 -> bf16 cast of a dense buffer (weight/activation staging). */
 int ttsb200_cast_bf16(const float* x, void* y_bf16, int64_t n, ttsb200_stream_t stream);
+
+/* ================================================================================================
+ * TRAINING STEP (forward extras above: pre_f32, gate_bf16, ttsb200_attention_fwd_lse).
+ * The reference has no explicit backward code: it calls loss.backward() / optimizer.step()
+ * (train_fastspeech2.py:304-315) and PyTorch autograd differentiates the modules cited below.
+ * Input-gradient ("dgrad") GEMMs reuse ttsb200_conv_gemm with transposed, tap-flipped weights.
+ * ============================================================================================== */
+
+/* Weight gradient of nn.Linear / nn.Conv1d (Models/modules.py:49-51,68,83-84; varianceadaptor.py:217,220;
+ * postnets.py:67,71-74):  dW[j,n,c] += sum_{b,t} dy[b,t,n] * x[b,t+j-pad_left,c].
+ * dy bf16 (B,T,ld_dy) (N columns used), x bf16 (B,T,ld_x) (C columns used); dW fp32, element (j,n,c) at
+ * dw[j*stride_tap + n*stride_n + c*stride_c], ACCUMULATED with atomics (zero it first). tcgen05, both
+ * operands MN-major, split-K over time. */
+int ttsb200_conv_wgrad(const void* dy, int64_t ld_dy, const void* x, int64_t ld_x, float* dw,
+                       int64_t stride_tap, int64_t stride_n, int64_t stride_c, int32_t B, int32_t T,
+                       int32_t N, int32_t C, int32_t taps, int32_t pad_left, ttsb200_stream_t stream);
+
+/* Backward of ttsb200_attention_fwd (autograd of Models/modules.py:7-21): dqkv bf16 (B,T,3*H*Dh) =
+ * [dq | dk | dv] from qkv, dctx bf16 (B,T,H*Dh), the saved lse2 (B,H,T) and delta (B,H,T) =
+ * rowsum(dctx * ctx) per head (ttsb200_attn_delta). */
+int ttsb200_attention_bwd(const void* qkv, const void* dctx, const uint8_t* mask, const int32_t* kv_info,
+                          const float* lse2, const float* delta, void* dqkv, int32_t B, int32_t T,
+                          int32_t H, int32_t Dh, ttsb200_stream_t stream);
+int ttsb200_attn_delta(const void* dctx, const void* ctx, float* delta, int32_t B, int32_t T, int32_t H,
+                       int32_t Dh, ttsb200_stream_t stream);
+
+/* LayerNorm backward (Models/layers.py:31,35; modules.py:87; varianceadaptor.py:219,222; encoder.py:112).
+ * x = saved pre-LN input (rows,D) fp32, statistics are recomputed.  Exactly one gradient source:
+ * g_f32 (rows,D) | g_bf16 (rows,D) | g_row[rows] * g_vec[D] (the predictor's 256->1 linear head,
+ * varianceadaptor.py:223-229; rows with row_mask == 0 contribute 0).  dx (+ add_f32) goes to dx_f32 and/or
+ * dx_bf16; relu_gate zeroes dx where x <= 0 (x is then a ReLU output).  dgamma/dbeta/dvec (D) and dscal (1)
+ * are ACCUMULATED (dvec = sum g_row * LN(x), dscal = sum g_row: the linear head's weight/bias grads). */
+int ttsb200_layernorm_bwd(const float* x, const float* gamma, const float* beta, const float* g_f32,
+                          const void* g_bf16, const float* g_row, const float* g_vec,
+                          const uint8_t* row_mask, const float* add_f32, int32_t relu_gate, float* dx_f32,
+                          void* dx_bf16, float* dgamma, float* dbeta, float* dvec, float* dscal,
+                          int64_t rows, int32_t D, float eps, ttsb200_stream_t stream);
+
+/* out[c] += sum_rows x[row*ld + c]  (bias gradients); x bf16 or fp32. */
+int ttsb200_colsum(const void* x, int32_t is_bf16, int64_t ld, float* out, int64_t rows, int32_t cols,
+                   ttsb200_stream_t stream);
+
+/* BatchNorm1d (training mode) + tanh of the PostNet (Models/postnets.py:71-73).  x fp32 (rows,384) is the
+ * conv output; stats (2,384) accumulates [sum x | sum x^2]; mean_rstd (2,384) = [mean | rstd] is derived by
+ * the caller (after the cross-rank all-reduce of SyncBatchNorm). */
+int ttsb200_bn_stats(const float* x, float* stats, int64_t rows, int32_t C, ttsb200_stream_t stream);
+int ttsb200_bn_tanh_fwd(const float* x, const float* mean_rstd, const float* gamma, const float* beta,
+                        void* h_bf16, int64_t rows, int32_t C, ttsb200_stream_t stream);
+/* apply == 0: red (2,384) += [sum dt | sum dt*xhat] with dt = dh*(1-h^2)  (= dbeta | dgamma);
+ * apply == 1: dx bf16 = gamma*rstd*(dt - red[0]*inv_count - xhat*red[1]*inv_count). */
+int ttsb200_bn_tanh_bwd(const void* dh_bf16, const void* h_bf16, const float* x, const float* mean_rstd,
+                        const float* gamma, float* red, void* dx_bf16, int64_t rows, int32_t C,
+                        float inv_count, int32_t apply, ttsb200_stream_t stream);
+
+/* LengthRegulator backward (Models/varianceadaptor.py:167-177): dx[b,l,:] = add[b,l,:] + sum of g[b,t,:]
+ * over the frames of phoneme l (cum from ttsb200_lr_scan, frames beyond Tmax were cropped). fp32. */
+int ttsb200_lr_bwd(const float* g, const int32_t* cum, float* dx, const float* add_f32, int32_t B, int32_t L,
+                   int32_t Tmax, int32_t D, ttsb200_stream_t stream);
+
+/* Embedding weight gradient, table[idx[row],:] += g[row,:] (skip_idx = padding_idx or -1; encoder.py:55,
+ * varianceadaptor.py:123-126), and/or dalpha += sum_rows g[row,:].pe[row % T,:] (modules.py:110). */
+int ttsb200_embed_bwd(const float* g, const int64_t* idx64, const int32_t* idx32, float* table,
+                      int32_t skip_idx, const float* pe, float* dalpha, int64_t rows, int32_t T, int32_t D,
+                      int32_t V, ttsb200_stream_t stream);
+
+/* nn.L1Loss (mean) and its gradient (train_fastspeech2.py:212-217,245-259): loss += scale*sum|pred-target|,
+ * grad = scale*sign(pred-target); log_target: target := log(target+1) (duration loss). */
+int ttsb200_l1_loss(const float* pred, const float* target, float* grad, void* grad_bf16, float* loss,
+                    int64_t n, float scale, int32_t log_target, ttsb200_stream_t stream);
+
+/* Optimizer over one flat fp32 buffer (train_fastspeech2.py:117-120,304-315): out += sum g^2; then
+ * g' = g*gscale*min(1, clip/(sqrt(sumsq)*gscale + 1e-6)) (clip_grad_norm_; clip <= 0 disables) and one
+ * torch.optim.Adam step (step >= 1 for the bias corrections). */
+int ttsb200_sumsq(const float* g, float* out, int64_t n, ttsb200_stream_t stream);
+int ttsb200_adam_step(float* p, const float* g, float* m, float* v, const float* sumsq, int64_t n,
+                      float gscale, float clip, float lr, float beta1, float beta2, float eps, int32_t step,
+                      ttsb200_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -39,8 +39,8 @@ enum { BAR_Q = 0, BAR_KF, BAR_KE, BAR_VF, BAR_VE, BAR_SF, BAR_SE, BAR_PF, BAR_OF
 
 __global__ void __launch_bounds__(kAttThreads, 2)
 attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const uint8_t* __restrict__ mask,
-                     const int32_t* __restrict__ kv_info, __nv_bfloat16* __restrict__ ctx, int T, int H,
-                     float scale_log2) {
+                     const int32_t* __restrict__ kv_info, __nv_bfloat16* __restrict__ ctx,
+                     float* __restrict__ lse2, int T, int H, float scale_log2) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
@@ -249,6 +249,8 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const uint8_t* _
     tc_fence_after();
     const int t = q0 + row;
     const float inv = 1.f / l;
+    // training: log2-domain log-sum-exp of the row, p = exp2(s*scale_log2 - lse2) in the backward kernels
+    if (lse2 != nullptr && t < T) lse2[(static_cast<int64_t>(b) * H + h) * T + t] = m + log2f(l);
     __nv_bfloat16* op = ctx + (static_cast<int64_t>(b) * T + (t < T ? t : 0)) * D + h * kDh;
 #pragma unroll
     for (int c = 0; c < kDh; c += 32) {
@@ -324,8 +326,9 @@ __global__ void attention_probs_kernel(const __nv_bfloat16* __restrict__ qkv, co
 
 using namespace ttsb;
 
-extern "C" int ttsb200_attention_fwd(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
-                                     int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t s) {
+extern "C" int ttsb200_attention_fwd_lse(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
+                                         float* lse2, int32_t B, int32_t T, int32_t H, int32_t Dh,
+                                         ttsb200_stream_t s) {
   TTSB_CHECK_ARG(qkv && mask && kv_info && ctx, "attention_fwd: null pointer");
   TTSB_CHECK_ARG(B > 0 && T > 0 && H > 0, "attention_fwd: bad dims");
   TTSB_CHECK_ARG(Dh == kDh, "attention_fwd: head dim %d unsupported (this build: %d)", Dh, kDh);
@@ -347,9 +350,14 @@ extern "C" int ttsb200_attention_fwd(const void* qkv, const uint8_t* mask, const
   dim3 grid((T + kBQ - 1) / kBQ, H, B);
   const float scale_log2 = kLog2e / sqrtf(static_cast<float>(Dh));
   attention_fwd_kernel<<<grid, kAttThreads, kAttSmem, static_cast<cudaStream_t>(s)>>>(
-      tm, mask, kv_info, static_cast<__nv_bfloat16*>(ctx), T, H, scale_log2);
+      tm, mask, kv_info, static_cast<__nv_bfloat16*>(ctx), lse2, T, H, scale_log2);
   TTSB_CHECK_CUDA(cudaGetLastError());
   return TTSB_OK;
+}
+
+extern "C" int ttsb200_attention_fwd(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
+                                     int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t s) {
+  return ttsb200_attention_fwd_lse(qkv, mask, kv_info, ctx, nullptr, B, T, H, Dh, s);
 }
 
 extern "C" int ttsb200_attention_probs(const void* qkv, const uint8_t* mask, float* probs, int32_t B,

@@ -89,6 +89,8 @@ struct GemmDev {
   __nv_bfloat16* out_bf16;
   float* out2_f32;
   float* out_row;
+  float* pre_f32;                 // LN epilogues: the pre-LayerNorm value (saved for the backward pass)
+  const __nv_bfloat16* gate_bf16; // AFFINE + ACT_RELU_GRAD: v = gate > 0 ? v : 0
 };
 
 __device__ __forceinline__ float tanh_fast(float x) {

@@ -118,6 +118,12 @@ extern "C" int ttsb200_conv_gemm(const ttsb200_gemm_args* a, ttsb200_stream_t st
   d.dot_w = a->dot_w; d.dot_b = a->dot_b; d.row_mask = a->row_mask;
   d.out_f32 = a->out_f32; d.out_bf16 = static_cast<__nv_bfloat16*>(a->out_bf16);
   d.out2_f32 = a->out2_f32; d.out_row = a->out_row;
+  d.pre_f32 = a->pre_f32; d.gate_bf16 = static_cast<const __nv_bfloat16*>(a->gate_bf16);
+  if (a->pre_f32) TTSB_CHECK_ARG(aligned16(a->pre_f32) && a->epi != TTSB200_EPI_AFFINE_ACT,
+                                 "conv_gemm: pre_f32 is an output of the LayerNorm epilogues, 16-byte aligned");
+  if (a->act == TTSB200_ACT_RELU_GRAD)
+    TTSB_CHECK_ARG(a->gate_bf16 && aligned16(a->gate_bf16) && a->epi == TTSB200_EPI_AFFINE_ACT && a->N % 8 == 0,
+                   "conv_gemm: ACT_RELU_GRAD needs gate_bf16 (B,T,N), AFFINE epilogue");
 
   const int e = a->epi, bn = a->block_n;
   if (e == TTSB200_EPI_AFFINE_ACT) {

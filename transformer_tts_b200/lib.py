@@ -15,7 +15,7 @@ import torch
 from . import _build
 
 EPI_AFFINE_ACT, EPI_RES_LN, EPI_FFN2, EPI_RELU_LN, EPI_RELU_LN_DOT = range(5)
-ACT_NONE, ACT_RELU, ACT_TANH = range(3)
+ACT_NONE, ACT_RELU, ACT_TANH, ACT_RELU_GRAD = range(4)
 
 LAUNCH_COUNT = 0  # kernels launched through this binding (bench.py reports it as gpu_launches)
 
@@ -34,6 +34,7 @@ class GemmArgs(C.Structure):
         ("dot_w", C.c_void_p), ("dot_b", C.c_void_p), ("row_mask", C.c_void_p),
         ("out_f32", C.c_void_p), ("out_bf16", C.c_void_p), ("out2_f32", C.c_void_p),
         ("out_row", C.c_void_p),
+        ("pre_f32", C.c_void_p), ("gate_bf16", C.c_void_p),
     ]
 
 
@@ -57,6 +58,24 @@ _SIGNATURES = {
     "ttsb200_lr_expand": ([C.c_void_p] * 7 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
     "ttsb200_bucket_embed_add": ([C.c_void_p] * 10 + [C.c_int64, C.c_int32, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_cast_bf16": ([C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p], C.c_int),
+    # ---- training step ----
+    "ttsb200_attention_fwd_lse": ([C.c_void_p] * 5 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
+    "ttsb200_conv_wgrad": ([C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64,
+                            C.c_int64] + [C.c_int32] * 6 + [C.c_void_p], C.c_int),
+    "ttsb200_attention_bwd": ([C.c_void_p] * 7 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
+    "ttsb200_attn_delta": ([C.c_void_p] * 3 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
+    "ttsb200_layernorm_bwd": ([C.c_void_p] * 9 + [C.c_int32] + [C.c_void_p] * 6 + [C.c_int64, C.c_int32, C.c_float,
+                                                                                 C.c_void_p], C.c_int),
+    "ttsb200_colsum": ([C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_bn_stats": ([C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_bn_tanh_fwd": ([C.c_void_p] * 5 + [C.c_int64, C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_bn_tanh_bwd": ([C.c_void_p] * 7 + [C.c_int64, C.c_int32, C.c_float, C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_lr_bwd": ([C.c_void_p] * 4 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
+    "ttsb200_embed_bwd": ([C.c_void_p] * 4 + [C.c_int32, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
+                                              C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_l1_loss": ([C.c_void_p] * 5 + [C.c_int64, C.c_float, C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_sumsq": ([C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p], C.c_int),
+    "ttsb200_adam_step": ([C.c_void_p] * 5 + [C.c_int64] + [C.c_float] * 6 + [C.c_int32, C.c_void_p], C.c_int),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)
@@ -126,7 +145,8 @@ def conv_gemm(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, *, taps: int
               dot_w: Optional[torch.Tensor] = None, dot_b: Optional[torch.Tensor] = None,
               row_mask: Optional[torch.Tensor] = None,
               out_f32: Optional[torch.Tensor] = None, out_bf16: Optional[torch.Tensor] = None,
-              out2_f32: Optional[torch.Tensor] = None, out_row: Optional[torch.Tensor] = None) -> None:
+              out2_f32: Optional[torch.Tensor] = None, out_row: Optional[torch.Tensor] = None,
+              pre_f32: Optional[torch.Tensor] = None, gate_bf16: Optional[torch.Tensor] = None) -> None:
     """x: bf16 (B,T,C); w: bf16 (taps,N,C).  See include/ttsb200.h for the epilogue modes."""
     B, T, Cin = x.shape
     tw, N, Cw = w.shape
@@ -154,6 +174,8 @@ def conv_gemm(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, *, taps: int
     a.out_bf16 = _ptr(out_bf16, torch.bfloat16, "out_bf16")
     a.out2_f32 = _ptr(out2_f32, torch.float32, "out2_f32")
     a.out_row = _ptr(out_row, torch.float32, "out_row")
+    a.pre_f32 = _ptr(pre_f32, torch.float32, "pre_f32")
+    a.gate_bf16 = _ptr(gate_bf16, torch.bfloat16, "gate_bf16")
     _check(load().ttsb200_conv_gemm(C.byref(a), _stream()), "conv_gemm")
     _count()
 
@@ -161,12 +183,15 @@ def conv_gemm(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, *, taps: int
 # --------------------------------------------------------------------------------------------------
 # attention
 # --------------------------------------------------------------------------------------------------
-def attention_fwd(qkv: torch.Tensor, mask: torch.Tensor, kv_len: torch.Tensor, ctx: torch.Tensor, H: int) -> None:
+def attention_fwd(qkv: torch.Tensor, mask: torch.Tensor, kv_len: torch.Tensor, ctx: torch.Tensor, H: int,
+                  lse2: Optional[torch.Tensor] = None) -> None:
+    """lse2 (B,H,T) fp32, when given, receives the log2-domain log-sum-exp of every row (training)."""
     B, T, W = qkv.shape
     Dh = W // (3 * H)
-    _check(load().ttsb200_attention_fwd(_ptr(qkv, torch.bfloat16, "qkv"), _ptr(mask, torch.uint8, "mask"),
-                                        _ptr(kv_len, torch.int32, "kv_len"), _ptr(ctx, torch.bfloat16, "ctx"),
-                                        B, T, H, Dh, _stream()), "attention_fwd")
+    _check(load().ttsb200_attention_fwd_lse(_ptr(qkv, torch.bfloat16, "qkv"), _ptr(mask, torch.uint8, "mask"),
+                                            _ptr(kv_len, torch.int32, "kv_len"), _ptr(ctx, torch.bfloat16, "ctx"),
+                                            _ptr(lse2, torch.float32, "lse2"), B, T, H, Dh, _stream()),
+           "attention_fwd")
     _count()
 
 
@@ -265,3 +290,151 @@ def cast_bf16(x: torch.Tensor) -> torch.Tensor:
     _check(load().ttsb200_cast_bf16(_ptr(x, torch.float32, "x"), _ptr(y), x.numel(), _stream()), "cast_bf16")
     _count()
     return y
+
+
+# --------------------------------------------------------------------------------------------------
+# training step (include/ttsb200.h, "TRAINING STEP")
+# --------------------------------------------------------------------------------------------------
+def conv_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, *, taps: int = 1, pad_left: int = 0,
+               n_off: int = 0, N: Optional[int] = None, conv_layout: bool = False) -> None:
+    """dW += dy^T (*) x.  dy bf16 (B,T,ld) of which columns [n_off, n_off+N) are used; x bf16 (B,T,C).
+    dw fp32: (N,C) for a linear, (taps,N,C) or — conv_layout — the reference's Conv1d (N,C,taps)."""
+    B, T, ldy = dy.shape
+    Cin = x.shape[2]
+    N = ldy - n_off if N is None else N
+    _ptr(dy, torch.bfloat16, "dy"); _ptr(x, torch.bfloat16, "x"); _ptr(dw, torch.float32, "dw")
+    if dw.numel() != taps * N * Cin:
+        raise ValueError(f"conv_wgrad: dw has {dw.numel()} elements, expected {taps}*{N}*{Cin}")
+    if conv_layout:
+        sj, sn, sc = 1, Cin * taps, taps
+    else:
+        sj, sn, sc = N * Cin, Cin, 1
+    _check(load().ttsb200_conv_wgrad(dy.data_ptr() + 2 * n_off, ldy, x.data_ptr(), x.shape[2], dw.data_ptr(), sj, sn,
+                                     sc, B, T, N, Cin, taps, pad_left, _stream()), "conv_wgrad")
+    _count()
+
+
+def attn_delta(dctx: torch.Tensor, ctx: torch.Tensor, H: int) -> torch.Tensor:
+    B, T, D = ctx.shape
+    delta = torch.empty((B, H, T), device=ctx.device, dtype=torch.float32)
+    _check(load().ttsb200_attn_delta(_ptr(dctx, torch.bfloat16, "dctx"), _ptr(ctx, torch.bfloat16, "ctx"),
+                                     _ptr(delta), B, T, H, D // H, _stream()), "attn_delta")
+    _count()
+    return delta
+
+
+def attention_bwd(qkv, dctx, mask, kv_len, lse2, delta, H: int) -> torch.Tensor:
+    B, T, W = qkv.shape
+    dqkv = torch.empty_like(qkv)
+    _check(load().ttsb200_attention_bwd(_ptr(qkv, torch.bfloat16, "qkv"), _ptr(dctx, torch.bfloat16, "dctx"),
+                                        _ptr(mask, torch.uint8, "mask"), _ptr(kv_len, torch.int32, "kv_len"),
+                                        _ptr(lse2, torch.float32, "lse2"), _ptr(delta, torch.float32, "delta"),
+                                        _ptr(dqkv), B, T, H, W // (3 * H), _stream()), "attention_bwd")
+    _count(2)
+    return dqkv
+
+
+def layernorm_bwd(x, gamma, *, beta=None, g_f32=None, g_bf16=None, g_row=None, g_vec=None, row_mask=None,
+                  add_f32=None, relu_gate=False, dx_f32=None, dx_bf16=None, dgamma=None, dbeta=None, dvec=None,
+                  dscal=None, eps: float = 1e-5) -> None:
+    D = x.shape[-1]
+    rows = x.numel() // D
+    _check(load().ttsb200_layernorm_bwd(
+        _ptr(x, torch.float32, "x"), _ptr(gamma, torch.float32, "gamma"), _ptr(beta, torch.float32, "beta"),
+        _ptr(g_f32, torch.float32, "g_f32"), _ptr(g_bf16, torch.bfloat16, "g_bf16"),
+        _ptr(g_row, torch.float32, "g_row"), _ptr(g_vec, torch.float32, "g_vec"),
+        _ptr(row_mask, torch.uint8, "row_mask"), _ptr(add_f32, torch.float32, "add_f32"), int(relu_gate),
+        _ptr(dx_f32, torch.float32, "dx_f32"), _ptr(dx_bf16, torch.bfloat16, "dx_bf16"),
+        _ptr(dgamma, torch.float32, "dgamma"), _ptr(dbeta, torch.float32, "dbeta"),
+        _ptr(dvec, torch.float32, "dvec"), _ptr(dscal, torch.float32, "dscal"), rows, D, eps, _stream()),
+        "layernorm_bwd")
+    _count()
+
+
+def colsum(x: torch.Tensor, out: torch.Tensor, cols: Optional[int] = None, col_off: int = 0) -> None:
+    """out[c] += sum over rows of x[..., col_off + c]; x bf16 or fp32 (.., ld)."""
+    ld = x.shape[-1]
+    rows = x.numel() // ld
+    cols = ld - col_off if cols is None else cols
+    if x.dtype not in (torch.bfloat16, torch.float32):
+        raise TypeError("colsum: bf16 or fp32")
+    _ptr(x, None, "x"); _ptr(out, torch.float32, "out")
+    _check(load().ttsb200_colsum(x.data_ptr() + col_off * x.element_size(), int(x.dtype == torch.bfloat16), ld,
+                                 out.data_ptr(), rows, cols, _stream()), "colsum")
+    _count()
+
+
+def bn_stats(x: torch.Tensor, stats: torch.Tensor) -> None:
+    Cc = x.shape[-1]
+    _check(load().ttsb200_bn_stats(_ptr(x, torch.float32, "x"), _ptr(stats, torch.float32, "stats"),
+                                   x.numel() // Cc, Cc, _stream()), "bn_stats")
+    _count()
+
+
+def bn_tanh_fwd(x, mean_rstd, gamma, beta, h) -> None:
+    Cc = x.shape[-1]
+    _check(load().ttsb200_bn_tanh_fwd(_ptr(x, torch.float32, "x"), _ptr(mean_rstd, torch.float32, "mean_rstd"),
+                                      _ptr(gamma, torch.float32, "gamma"), _ptr(beta, torch.float32, "beta"),
+                                      _ptr(h, torch.bfloat16, "h"), x.numel() // Cc, Cc, _stream()), "bn_tanh_fwd")
+    _count()
+
+
+def bn_tanh_bwd(dh, h, x, mean_rstd, gamma, red, dx, inv_count: float, apply: bool) -> None:
+    Cc = x.shape[-1]
+    _check(load().ttsb200_bn_tanh_bwd(_ptr(dh, torch.bfloat16, "dh"), _ptr(h, torch.bfloat16, "h"),
+                                      _ptr(x, torch.float32, "x"), _ptr(mean_rstd, torch.float32, "mean_rstd"),
+                                      _ptr(gamma, torch.float32, "gamma"), _ptr(red, torch.float32, "red"),
+                                      _ptr(dx, torch.bfloat16, "dx"), x.numel() // Cc, Cc, inv_count, int(apply),
+                                      _stream()), "bn_tanh_bwd")
+    _count()
+
+
+def lr_bwd(g: torch.Tensor, cum: torch.Tensor, add_f32: Optional[torch.Tensor] = None) -> torch.Tensor:
+    B, Tmax, D = g.shape
+    L = cum.shape[1]
+    dx = torch.empty((B, L, D), device=g.device, dtype=torch.float32)
+    _check(load().ttsb200_lr_bwd(_ptr(g, torch.float32, "g"), _ptr(cum, torch.int32, "cum"), _ptr(dx),
+                                 _ptr(add_f32, torch.float32, "add_f32"), B, L, Tmax, D, _stream()), "lr_bwd")
+    _count()
+    return dx
+
+
+def embed_bwd(g: torch.Tensor, T: int, *, idx: Optional[torch.Tensor] = None, table: Optional[torch.Tensor] = None,
+              skip_idx: int = -1, pe: Optional[torch.Tensor] = None, dalpha: Optional[torch.Tensor] = None) -> None:
+    D = g.shape[-1]
+    rows = g.numel() // D
+    i64 = idx if idx is not None and idx.dtype == torch.int64 else None
+    i32 = idx if idx is not None and idx.dtype == torch.int32 else None
+    if idx is not None and i64 is None and i32 is None:
+        raise TypeError("embed_bwd: idx must be int64 or int32")
+    V = table.shape[0] if table is not None else 0
+    _check(load().ttsb200_embed_bwd(_ptr(g, torch.float32, "g"), _ptr(i64), _ptr(i32),
+                                    _ptr(table, torch.float32, "table"), skip_idx, _ptr(pe, torch.float32, "pe"),
+                                    _ptr(dalpha, torch.float32, "dalpha"), rows, T, D, V, _stream()), "embed_bwd")
+    _count()
+
+
+def l1_loss(pred, target, loss, *, grad=None, grad_bf16=None, log_target: bool = False) -> None:
+    n = pred.numel()
+    if target.numel() != n:
+        raise ValueError("l1_loss: shape mismatch")
+    _check(load().ttsb200_l1_loss(_ptr(pred, torch.float32, "pred"), _ptr(target, torch.float32, "target"),
+                                  _ptr(grad, torch.float32, "grad"), _ptr(grad_bf16, torch.bfloat16, "grad_bf16"),
+                                  _ptr(loss, torch.float32, "loss"), n, 1.0 / n, int(log_target), _stream()),
+           "l1_loss")
+    _count()
+
+
+def sumsq(g: torch.Tensor, out: torch.Tensor) -> None:
+    _check(load().ttsb200_sumsq(_ptr(g, torch.float32, "g"), _ptr(out, torch.float32, "out"), g.numel(), _stream()),
+           "sumsq")
+    _count()
+
+
+def adam_step(p, g, m, v, sumsq_t, *, gscale: float, clip: float, lr: float, beta1: float, beta2: float, eps: float,
+              step: int) -> None:
+    _check(load().ttsb200_adam_step(_ptr(p, torch.float32, "p"), _ptr(g, torch.float32, "g"),
+                                    _ptr(m, torch.float32, "m"), _ptr(v, torch.float32, "v"),
+                                    _ptr(sumsq_t, torch.float32, "sumsq"), p.numel(), gscale, clip, lr, beta1, beta2,
+                                    eps, step, _stream()), "adam_step")
+    _count()
