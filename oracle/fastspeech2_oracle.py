@@ -217,18 +217,20 @@ def variance_adaptor(sd, pfx: str, x: Tensor, src_mask, mel_mask, d_target, p_ta
 # --------------------------------------------------------------------------------------------------
 # Models/postnets.py:64-79  PostConvNet.forward (prev_version=True, eval-mode BatchNorm, dropout 0)
 # --------------------------------------------------------------------------------------------------
-def _bn_eval(sd, pfx: str, x: Tensor) -> Tensor:
+def _bn_eval(sd, pfx: str, x: Tensor, training: bool = False) -> Tensor:
+    if training:  # nn.BatchNorm1d in train(): batch statistics over all B*T positions (running stats not updated here)
+        return F.batch_norm(x, None, None, sd[pfx + "weight"], sd[pfx + "bias"], training=True, eps=1e-5)
     return F.batch_norm(x, sd[pfx + "running_mean"], sd[pfx + "running_var"], sd[pfx + "weight"],
                         sd[pfx + "bias"], training=False, eps=1e-5)
 
 
-def postnet(sd, pfx: str, x: Tensor):
+def postnet(sd, pfx: str, x: Tensor, training: bool = False):
     mel_pred = F.linear(x, sd[pfx + "out.weight"], sd[pfx + "out.bias"]).transpose(1, 2)  # :67
     h = F.conv1d(mel_pred, sd[pfx + "conv1.weight"], sd[pfx + "conv1.bias"], padding=4)[:, :, :-4]  # :71
-    h = torch.tanh(_bn_eval(sd, pfx + "pre_batchnorm.", h))
+    h = torch.tanh(_bn_eval(sd, pfx + "pre_batchnorm.", h, training))
     for i in range(3):  # :72-73
         h = F.conv1d(h, sd[f"{pfx}conv_list.{i}.weight"], sd[f"{pfx}conv_list.{i}.bias"], padding=4)[:, :, :-4]
-        h = torch.tanh(_bn_eval(sd, f"{pfx}batch_norm_list.{i}.", h))
+        h = torch.tanh(_bn_eval(sd, f"{pfx}batch_norm_list.{i}.", h, training))
     h = F.conv1d(h, sd[pfx + "conv2.weight"], sd[pfx + "conv2.bias"], padding=4)[:, :, :-4]  # :74
     post = mel_pred + h  # :75
     return mel_pred.transpose(1, 2), post.transpose(1, 2)  # :77
@@ -240,7 +242,7 @@ def postnet(sd, pfx: str, x: Tensor):
 def fastspeech2_forward(sd: Dict[str, Tensor], hp: dict, src: Tensor, src_mask: Tensor,
                         mel_mask: Optional[Tensor] = None, d_target: Optional[Tensor] = None,
                         p_target: Optional[Tensor] = None, e_target: Optional[Tensor] = None,
-                        return_attn: bool = False) -> dict:
+                        return_attn: bool = False, training: bool = False) -> dict:
     """hp keys: n_layer_encoder, n_head_encoder, n_layer_decoder, n_head_decoder, nbins, f0_min,
     f0_max, energy_min, energy_max.  Returns a dict with the reference's tuple slots by name."""
     bins = variance_bins(hp["nbins"], hp["f0_min"], hp["f0_max"], hp["energy_min"], hp["energy_max"])
@@ -254,9 +256,36 @@ def fastspeech2_forward(sd: Dict[str, Tensor], hp: dict, src: Tensor, src_mask: 
     dec_mask = mel_mask if d_target is not None else va["mel_mask"].unsqueeze(1)
     d_out, attn_dec = encoder(sd, "decoder.", va["x"], dec_mask, hp["n_layer_decoder"], hp["n_head_decoder"],
                               return_attn)  # :195
-    mel_pre, mel_post = postnet(sd, "postnet.", d_out)  # :197
+    mel_pre, mel_post = postnet(sd, "postnet.", d_out, training)  # :197
     return dict(outputs_prenet=mel_pre, outputs_postnet=mel_post, log_d_prediction=va["log_d"],
                 p_prediction=va["p"], e_prediction=va["e"], variance_adaptor_output=va["x"],
                 text_dur_predicted=va["text_dur"], attn_enc=attn_enc, attn_dec=attn_dec,
                 mel_pos=va["mel_pos"], mel_mask=va["mel_mask"], frame_idx=va["frame_idx"],
                 p_idx=va["p_idx"], e_idx=va["e_idx"], encoder_output=e_out, decoder_output=d_out)
+
+
+# --------------------------------------------------------------------------------------------------
+# train_fastspeech2.py:212-217,245-259  the five unmasked L1 terms of the training loss
+# --------------------------------------------------------------------------------------------------
+def training_losses(out: dict, mel: Tensor, alignment: Tensor, f0: Tensor, energy: Tensor) -> dict:
+    mel_loss = F.l1_loss(out["outputs_prenet"], mel)  # :212
+    post_mel_loss = F.l1_loss(out["outputs_postnet"], mel)  # :214
+    duration_loss = F.l1_loss(out["log_d_prediction"], torch.log(alignment.float() + 1))  # :245
+    f0_loss = F.l1_loss(out["p_prediction"], f0)  # :249
+    energy_loss = F.l1_loss(out["e_prediction"], energy)  # :254
+    loss = mel_loss + post_mel_loss + f0_loss + energy_loss + duration_loss  # :215,250,255,259
+    return dict(loss=loss, mel_loss=mel_loss, post_mel_loss=post_mel_loss, duration_loss=duration_loss,
+                f0_loss=f0_loss, energy_loss=energy_loss)
+
+
+def training_step_grads(sd: Dict[str, Tensor], hp: dict, text, src_mask, mel_mask, alignment, f0, energy, mel):
+    """Forward in train() semantics (BatchNorm batch statistics, dropout 0) + losses + autograd backward,
+    as train_fastspeech2.py:167,212-259,304 does.  Returns (losses, {name: grad}) for the float parameters."""
+    names = [k for k, v in sd.items() if v.is_floating_point() and "running_" not in k]
+    p = {k: (sd[k].detach().clone().requires_grad_(True) if k in names else sd[k]) for k in sd}
+    out = fastspeech2_forward(p, hp, text, src_mask, mel_mask=mel_mask, d_target=alignment, p_target=f0,
+                              e_target=energy, training=True)
+    losses = training_losses(out, mel, alignment, f0, energy)
+    grads = torch.autograd.grad(losses["loss"], [p[k] for k in names], allow_unused=True)
+    return ({k: v.detach() for k, v in losses.items()},
+            {k: (g if g is not None else torch.zeros_like(sd[k])) for k, g in zip(names, grads)}, out)

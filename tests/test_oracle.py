@@ -195,3 +195,28 @@ def test_oracle_matches_live_reference(world):
         o = O.fastspeech2_forward(sd, vars(hp), text, m)
     close(o["outputs_postnet"], out[1])
     close(o["log_d_prediction"], out[2])
+
+
+def test_golden_train_step(world):
+    """Oracle (autograd through the restatement, train() semantics) vs the unmodified reference's
+    loss.backward() on the same seeded batch (oracle/make_golden_train.py)."""
+    from oracle.make_golden_train import FULL, SUB, train_batch
+
+    hp, sd, digest = world
+    g = np.load(GOLDEN / "fs2_train_step.npz")
+    assert str(g["digest"]) == digest
+    text, pos, dur, pos_mel, f0, en, mel = train_batch()
+    losses, grads, out = O.training_step_grads(sd, vars(hp), text, (pos != 0).unsqueeze(-2),
+                                               (pos_mel != 0).unsqueeze(-2), dur, f0, en, mel)
+    ref = g["losses"]
+    for i, k in enumerate(["mel_loss", "post_mel_loss", "duration_loss", "f0_loss", "energy_loss", "loss"]):
+        assert abs(float(losses[k]) - ref[i]) <= 1e-5 * max(1.0, abs(ref[i])), k
+    close(out["outputs_postnet"].detach(), g["mel_post"], 1e-4)
+    norms = dict(zip([str(n) for n in g["names"]], g["grad_norms"]))
+    assert set(norms) == set(grads)
+    for n, gr in grads.items():
+        assert abs(float(gr.double().norm()) - norms[n]) <= 2e-3 * max(norms[n], 1e-6) + 1e-7, n
+    for n in FULL:
+        close(grads[n], g["full:" + n], 1e-3)
+    for n in SUB:
+        close(grads[n].reshape(grads[n].shape[0], -1)[::7, ::13], g["sub:" + n], 1e-3)

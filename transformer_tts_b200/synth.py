@@ -201,3 +201,13 @@ def synth_targets(pos_text: torch.Tensor, seed: int = 1234, max_dur: int = 15):
     f0 = torch.where(valid, f0, torch.zeros_like(f0))
     energy = torch.where(valid, energy, torch.zeros_like(energy))
     return dur, pos_mel, f0, energy
+
+
+def synth_mel(pos_mel: torch.Tensor, mel_dim: int = 80, seed: int = 1234) -> torch.Tensor:
+    """Training target mel (B,T,mel_dim): N(0,1) on valid frames, -0.5 on padding (the collate pad value,
+    datasets/datasets_fastspeech2.py:728-739)."""
+    g = torch.Generator(device="cpu")
+    g.manual_seed(seed + 29)
+    B, T = pos_mel.shape
+    mel = torch.randn((B, T, mel_dim), generator=g)
+    return torch.where((pos_mel != 0).unsqueeze(-1), mel, torch.full_like(mel, -0.5))

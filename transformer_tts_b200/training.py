@@ -1,0 +1,451 @@
+"""FastSpeech2 training step on the sm_100a kernels.
+
+What the reference does in ``train_fastspeech2.py:117-315`` with autocast + autograd + DDP/SyncBatchNorm +
+``torch.optim.Adam`` + Noam LR + ``clip_grad_norm_`` is restated here as an explicit kernel sequence:
+
+    forward  (training mode: saves pre-LayerNorm values, attention log-sum-exp, BatchNorm batch statistics)
+    losses   (five unmasked nn.L1Loss terms, train_fastspeech2.py:212-259) and their gradients in one kernel each
+    backward (dgrad GEMMs = conv_gemm with transposed tap-flipped weights; wgrad = tcgen05 MN-major split-K GEMM;
+              attention backward = two tcgen05 kernels; LayerNorm / BatchNorm / LengthRegulator / embedding
+              backward row kernels), every parameter gradient lands in ONE flat fp32 buffer
+    all-reduce of that buffer over NCCL (data parallel, one process per GPU), SyncBatchNorm statistics
+    optimizer (global-norm clip + Adam over the flat buffer, Noam learning rate)
+
+PyTorch is plumbing only (buffers, streams, torch.distributed).  There is no autograd graph and no fallback.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, Optional
+
+import torch
+import torch.distributed as dist
+
+from . import lib
+from .Models import _engine as E
+
+
+def noam_lr(step: int, d_model: int, warmup_factor: float, warmup_step: int) -> float:
+    """utils/utils.py:204-215 (get_learning_rate)."""
+    return warmup_factor * min(step ** -0.5, step * warmup_step ** -1.5) * (d_model ** -0.5)
+
+
+def _t(w_taps: torch.Tensor) -> torch.Tensor:
+    """Forward operand (taps, N, C) -> dgrad operand (taps, C, N), taps flipped: w'[j'][c][n] = w[taps-1-j'][n][c]."""
+    return w_taps.permute(0, 2, 1).flip(0).contiguous()
+
+
+class Trainer:
+    """Owns the flat parameter / gradient / Adam-state buffers of a ``FastSpeech2`` and runs training steps."""
+
+    def __init__(self, model, *, lr_max: float = 1e-3, betas=(0.9, 0.98), eps: float = 1e-9, clip: float = 1.0,
+                 warmup_step: int = 4000, warmup_factor: float = 1.0, fixed_lr: Optional[float] = None,
+                 process_group=None, sync_bn: bool = True, bn_momentum: float = 0.1):
+        lib.load()
+        self.model = model
+        self.pg = process_group
+        self.world = dist.get_world_size(process_group) if (dist.is_available() and dist.is_initialized()) else 1
+        self.sync_bn = sync_bn and self.world > 1
+        self.betas, self.eps, self.clip, self.lr_max = betas, eps, clip, lr_max
+        self.warmup_step, self.warmup_factor, self.fixed_lr = warmup_step, warmup_factor, fixed_lr
+        self.bn_momentum = bn_momentum
+        self.step_count = 0
+        params = [(n, p) for n, p in model.named_parameters()]
+        if not params or not params[0][1].is_cuda:
+            raise RuntimeError("Trainer: move the model to a CUDA device first (there is no CPU path)")
+        dev = params[0][1].device
+        self.dev = dev
+        # every tensor starts on a 16-byte boundary inside the flat buffers (vector loads, TMA bases)
+        offs, total = {}, 0
+        for n, p in params:
+            offs[n] = total
+            total += (p.numel() + 3) // 4 * 4
+        self.flat_p = torch.zeros(total, device=dev, dtype=torch.float32)
+        self.flat_g = torch.zeros(total, device=dev, dtype=torch.float32)
+        self.flat_m = torch.zeros(total, device=dev, dtype=torch.float32)
+        self.flat_v = torch.zeros(total, device=dev, dtype=torch.float32)
+        self.grads: Dict[int, torch.Tensor] = {}
+        self.names: Dict[int, str] = {}
+        with torch.no_grad():
+            for n, p in params:
+                o, k = offs[n], p.numel()
+                self.flat_p[o:o + k].copy_(p.detach().reshape(-1).float())
+                p.data = self.flat_p[o:o + k].view(p.shape)  # parameters become views of the flat buffer
+                g = self.flat_g[o:o + k].view(p.shape)
+                p.grad = g
+                self.grads[id(p)] = g
+                self.names[id(p)] = n
+        self.sumsq = torch.zeros(1, device=dev, dtype=torch.float32)
+        self.loss_buf = torch.zeros(8, device=dev, dtype=torch.float32)
+        self._zeros = {}
+        self.invalidate_caches()
+
+    # ------------------------------------------------------------------------------------------
+    def G(self, p: torch.Tensor) -> torch.Tensor:
+        return self.grads[id(p)]
+
+    def zeros(self, n: int) -> torch.Tensor:
+        z = self._zeros.get(n)
+        if z is None:
+            z = torch.zeros(n, device=self.dev, dtype=torch.float32)
+            self._zeros[n] = z
+        return z
+
+    def invalidate_caches(self) -> None:
+        """The optimizer kernel updates parameters through raw pointers: derived bf16 operands are stale."""
+        for m in self.model.modules():
+            c = getattr(m, "_ttsb_cache", None)
+            if c is not None:
+                c.sig = None
+
+    def lr(self) -> float:
+        if self.fixed_lr is not None:
+            return self.fixed_lr
+        d_model = self.model.decoder.norm.weight.numel()
+        return noam_lr(max(self.step_count, 1), d_model, self.warmup_factor, self.warmup_step)
+
+    # ------------------------------------------------------------------------------------------
+    # FFT stack (Models/encoder.py:83-112, layers.py:29-41)
+    # ------------------------------------------------------------------------------------------
+    def _stack_fwd(self, enc, src, mask_u8, kv):
+        t = enc._cache()
+        B, T = src.shape[0], src.shape[1]
+        D = enc.norm.weight.numel()
+        dev = src.device
+        pe = enc.pe.table(dev)
+        if T > pe.shape[0]:
+            raise ValueError(f"sequence length {T} exceeds the positional table ({pe.shape[0]})")
+        caches = [E.layer_cache(l) for l in enc.layers]
+        x = torch.empty((B, T, D), device=dev, dtype=torch.float32)
+        xn = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
+        ln_first = caches[0]["ln1"]
+        if enc.embedding:
+            lib.embed_pe_ln(src.contiguous(), t["table"], pe, t["alpha"], ln_first[0], ln_first[1], E.LN_EPS, x, xn)
+        else:
+            lib.conv_gemm(src, t["wemb"], t["bemb"], block_n=D, epi=lib.EPI_RES_LN, res_f32=pe, res_bstride=0,
+                          res_tstride=D, res_scale=t["alpha"], ln1=ln_first, out_f32=x, out_bf16=xn)
+        tape = dict(src=src, mask=mask_u8, kv=kv, pe=pe, T=T, blocks=[], caches=caches, top=t)
+        H = enc.heads
+        for i, lc in enumerate(caches):
+            k = lc["k"]
+            next_ln = t["norm"] if i == enc.N - 1 else caches[i + 1]["ln1"]
+            qkv = torch.empty((B, T, 3 * D), device=dev, dtype=torch.bfloat16)
+            lib.conv_gemm(xn, lc["wqkv"], lc["bqkv"], block_n=192, out_bf16=qkv)
+            ctx = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
+            lse = torch.empty((B, H, T), device=dev, dtype=torch.float32)
+            lib.attention_fwd(qkv, mask_u8, kv, ctx, H, lse2=lse)
+            y = torch.empty((B, T, D), device=dev, dtype=torch.float32)
+            yn = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
+            lib.conv_gemm(ctx, lc["wo"], lc["bo"], block_n=D, epi=lib.EPI_RES_LN, res_f32=x, res_bstride=T * D,
+                          res_tstride=D, ln1=lc["ln2"], out_f32=y, out_bf16=yn)
+            h = torch.empty((B, T, 4 * D), device=dev, dtype=torch.bfloat16)
+            lib.conv_gemm(yn, lc["w1"], lc["b1"], taps=k, pad_left=k // 2, block_n=256, act=lib.ACT_RELU, out_bf16=h)
+            z = torch.empty((B, T, D), device=dev, dtype=torch.float32)
+            zn = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
+            upre = torch.empty((B, T, D), device=dev, dtype=torch.float32)
+            lib.conv_gemm(h, lc["w2"], lc["b2"], taps=k, pad_left=k // 2, block_n=D, epi=lib.EPI_FFN2, res_bf16=yn,
+                          res_f32=y, res_bstride=T * D, res_tstride=D, ln1=lc["ln_ff"], ln2=next_ln, out_f32=z,
+                          out_bf16=zn, pre_f32=upre)
+            tape["blocks"].append(dict(x=x, xn=xn, qkv=qkv, ctx=ctx, lse=lse, y=y, yn=yn, h=h, upre=upre))
+            x, xn = z, zn
+        tape["z_last"] = x
+        return xn, tape
+
+    def _stack_bwd(self, enc, tape, g_out: torch.Tensor) -> torch.Tensor:
+        """g_out: fp32 gradient w.r.t. the stack output LN_norm(z_last).  Returns the fp32 gradient w.r.t. the
+        stack input features (decoder) or None (text encoder: the embedding table gradient is accumulated)."""
+        G = self.G
+        B, T, D = g_out.shape
+        dev = g_out.device
+        H = enc.heads
+        mask, kv = tape["mask"], tape["kv"]
+        f32 = lambda *s: torch.empty(s, device=dev, dtype=torch.float32)  # noqa: E731
+        bf = lambda *s: torch.empty(s, device=dev, dtype=torch.bfloat16)  # noqa: E731
+        dz = f32(B, T, D)
+        lib.layernorm_bwd(tape["z_last"], tape["top"]["norm"][0], g_f32=g_out, dx_f32=dz, dgamma=G(enc.norm.weight),
+                          dbeta=G(enc.norm.bias))
+        dz_bf = None
+        for i in range(enc.N - 1, -1, -1):
+            layer, lc, s = enc.layers[i], tape["caches"][i], tape["blocks"][i]
+            a, ff = layer.attn, layer.ff
+            k = lc["k"]
+            # z = y + LN_ff(upre)
+            dupre, dupre_bf = f32(B, T, D), bf(B, T, D)
+            lib.layernorm_bwd(s["upre"], lc["ln_ff"][0], g_f32=dz, dx_f32=dupre, dx_bf16=dupre_bf,
+                              dgamma=G(ff.layer_norm.weight), dbeta=G(ff.layer_norm.bias))
+            # upre = conv2(h) + b2 + yn
+            lib.colsum(dupre_bf, G(ff.f_2.bias))
+            lib.conv_wgrad(dupre_bf, s["h"], G(ff.f_2.weight), taps=k, pad_left=k // 2, conv_layout=True)
+            dh = bf(B, T, 4 * D)
+            lib.conv_gemm(dupre_bf, _t(lc["w2"]), self.zeros(4 * D), taps=k, pad_left=k - 1 - k // 2, block_n=256,
+                          act=lib.ACT_RELU_GRAD, gate_bf16=s["h"], out_bf16=dh)
+            # h = relu(conv1(yn) + b1)
+            lib.colsum(dh, G(ff.f_1.bias))
+            lib.conv_wgrad(dh, s["yn"], G(ff.f_1.weight), taps=k, pad_left=k // 2, conv_layout=True)
+            dyn = f32(B, T, D)
+            lib.conv_gemm(dh, _t(lc["w1"]), self.zeros(D), taps=k, pad_left=k - 1 - k // 2, block_n=192,
+                          res_f32=dupre, res_bstride=T * D, res_tstride=D, out_f32=dyn)
+            # yn = norm_2(y); z = y + ff(yn)
+            dy, dy_bf = f32(B, T, D), bf(B, T, D)
+            lib.layernorm_bwd(s["y"], lc["ln2"][0], g_f32=dyn, add_f32=dz, dx_f32=dy, dx_bf16=dy_bf,
+                              dgamma=G(layer.norm_2.weight), dbeta=G(layer.norm_2.bias))
+            # y = x + ctx Wo^T + bo
+            lib.colsum(dy_bf, G(a.out.bias))
+            lib.conv_wgrad(dy_bf, s["ctx"], G(a.out.weight))
+            dctx = bf(B, T, D)
+            lib.conv_gemm(dy_bf, _t(lc["wo"]), self.zeros(D), block_n=192, out_bf16=dctx)
+            delta = lib.attn_delta(dctx, s["ctx"], H)
+            dqkv = lib.attention_bwd(s["qkv"], dctx, mask, kv, s["lse"], delta, H)
+            for j, lin in enumerate((a.q_linear, a.k_linear, a.v_linear)):
+                lib.colsum(dqkv, G(lin.bias), cols=D, col_off=j * D)
+                lib.conv_wgrad(dqkv, s["xn"], G(lin.weight), n_off=j * D, N=D)
+            dxn = f32(B, T, D)
+            lib.conv_gemm(dqkv, _t(lc["wqkv"]), self.zeros(D), block_n=192, out_f32=dxn)
+            # xn = norm_1(x); y = x + attn(xn)
+            dx = f32(B, T, D)
+            dz_bf = bf(B, T, D) if i == 0 else None
+            lib.layernorm_bwd(s["x"], lc["ln1"][0], g_f32=dxn, add_f32=dy, dx_f32=dx, dx_bf16=dz_bf,
+                              dgamma=G(layer.norm_1.weight), dbeta=G(layer.norm_1.bias))
+            dz = dx
+        # x0 = embed(src) + alpha * pe
+        t = tape["top"]
+        if enc.embedding:
+            lib.embed_bwd(dz, T, idx=tape["src"], table=G(enc.embed.weight), skip_idx=0, pe=tape["pe"],
+                          dalpha=G(enc.pe.alpha))
+            return None
+        lib.embed_bwd(dz, T, pe=tape["pe"], dalpha=G(enc.pe.alpha))
+        lib.colsum(dz, G(enc.embed.bias))
+        lib.conv_wgrad(dz_bf, tape["src"], G(enc.embed.weight))
+        dsrc = f32(B, T, tape["src"].shape[2])
+        lib.conv_gemm(dz_bf, _t(t["wemb"]), self.zeros(tape["src"].shape[2]), block_n=192, out_f32=dsrc)
+        return dsrc
+
+    # ------------------------------------------------------------------------------------------
+    # VariancePredictor (Models/varianceadaptor.py:216-231)
+    # ------------------------------------------------------------------------------------------
+    def _pred_fwd(self, pred, x_bf16, mask_u8):
+        t = E.predictor_cache(pred)
+        B, T, _ = x_bf16.shape
+        fs = t["b1"].numel()
+        dev = x_bf16.device
+        h = torch.empty((B, T, fs), device=dev, dtype=torch.bfloat16)
+        r1 = torch.empty((B, T, fs), device=dev, dtype=torch.float32)
+        lib.conv_gemm(x_bf16, t["w1"], t["b1"], taps=3, pad_left=1, block_n=fs, epi=lib.EPI_RELU_LN, ln1=t["ln1"],
+                      out_bf16=h, pre_f32=r1)
+        out = torch.empty((B, T), device=dev, dtype=torch.float32)
+        r2 = torch.empty((B, T, fs), device=dev, dtype=torch.float32)
+        lib.conv_gemm(h, t["w2"], t["b2"], taps=3, pad_left=1, block_n=fs, epi=lib.EPI_RELU_LN_DOT, ln1=t["ln2"],
+                      dot_w=t["dw"], dot_b=t["db"], row_mask=mask_u8, out_row=out, pre_f32=r2)
+        return out, dict(x=x_bf16, h=h, r1=r1, r2=r2, mask=mask_u8, t=t)
+
+    def _pred_bwd(self, pred, tape, g_out: torch.Tensor, add_f32: Optional[torch.Tensor]) -> torch.Tensor:
+        """g_out (B,T) fp32 -> fp32 gradient w.r.t. the predictor input (+ add_f32)."""
+        G = self.G
+        t = tape["t"]
+        B, T, Din = tape["x"].shape
+        fs = t["b1"].numel()
+        dev = g_out.device
+        dc2 = torch.empty((B, T, fs), device=dev, dtype=torch.bfloat16)
+        lib.layernorm_bwd(tape["r2"], t["ln2"][0], beta=t["ln2"][1], g_row=g_out.contiguous(), g_vec=t["dw"],
+                          row_mask=tape["mask"], relu_gate=True, dx_bf16=dc2, dgamma=G(pred.layer_norm2.weight),
+                          dbeta=G(pred.layer_norm2.bias), dvec=G(pred.linear_layer.weight),
+                          dscal=G(pred.linear_layer.bias))
+        lib.colsum(dc2, G(pred.conv2.bias))
+        lib.conv_wgrad(dc2, tape["h"], G(pred.conv2.weight), taps=3, pad_left=1, conv_layout=True)
+        dh = torch.empty((B, T, fs), device=dev, dtype=torch.float32)
+        lib.conv_gemm(dc2, _t(t["w2"]), self.zeros(fs), taps=3, pad_left=1, block_n=128, out_f32=dh)
+        dc1 = torch.empty((B, T, fs), device=dev, dtype=torch.bfloat16)
+        lib.layernorm_bwd(tape["r1"], t["ln1"][0], g_f32=dh, relu_gate=True, dx_bf16=dc1,
+                          dgamma=G(pred.layer_norm1.weight), dbeta=G(pred.layer_norm1.bias))
+        lib.colsum(dc1, G(pred.conv1.bias))
+        lib.conv_wgrad(dc1, tape["x"], G(pred.conv1.weight), taps=3, pad_left=1, conv_layout=True)
+        dx = torch.empty((B, T, Din), device=dev, dtype=torch.float32)
+        kw = {} if add_f32 is None else dict(res_f32=add_f32, res_bstride=T * Din, res_tstride=Din)
+        lib.conv_gemm(dc1, _t(t["w1"]), self.zeros(Din), taps=3, pad_left=1, block_n=192, out_f32=dx, **kw)
+        return dx
+
+    # ------------------------------------------------------------------------------------------
+    # PostConvNet with BatchNorm batch statistics (Models/postnets.py:64-79, nn.BatchNorm1d in train())
+    # ------------------------------------------------------------------------------------------
+    def _bn_finish_stats(self, stats: torch.Tensor, rows_local: int, bn) -> tuple:
+        """[sum | sum^2] -> [mean | rstd] (+ running-stat update as nn.BatchNorm1d / SyncBatchNorm do)."""
+        count = float(rows_local)
+        if self.sync_bn:
+            dist.all_reduce(stats, group=self.pg)
+            count *= self.world
+        mean = stats[0] / count
+        var = (stats[1] / count - mean * mean).clamp_(min=0.0)
+        ms = torch.stack([mean, torch.rsqrt(var + bn.eps)]).contiguous()
+        with torch.no_grad():
+            m = self.bn_momentum
+            bn.running_mean.mul_(1 - m).add_(mean, alpha=m)
+            bn.running_var.mul_(1 - m).add_(var * (count / max(count - 1.0, 1.0)), alpha=m)
+            bn.num_batches_tracked += 1
+        return ms, count
+
+    def _postnet_fwd(self, pn, d_bf16):
+        t = E.postnet_cache(pn)
+        B, T, D = d_bf16.shape
+        dev = d_bf16.device
+        md = t["bout"].numel()
+        mel_pre = torch.empty((B, T, md), device=dev, dtype=torch.float32)
+        mel_pre_bf = torch.empty((B, T, md), device=dev, dtype=torch.bfloat16)
+        lib.conv_gemm(d_bf16, t["wout"], t["bout"], block_n=md, out_f32=mel_pre, out_bf16=mel_pre_bf)
+        convs = [pn.conv1] + list(pn.conv_list)
+        bns = [pn.pre_batchnorm] + list(pn.batch_norm_list)
+        h = mel_pre_bf
+        layers = []
+        for (w, _, _), cv, bn in zip(t["convs"], convs, bns):
+            c = torch.empty((B, T, D), device=dev, dtype=torch.float32)
+            lib.conv_gemm(h, w, cv.bias, taps=5, pad_left=4, block_n=192, out_f32=c)
+            stats = torch.zeros((2, D), device=dev, dtype=torch.float32)
+            lib.bn_stats(c, stats)
+            ms, count = self._bn_finish_stats(stats, B * T, bn)
+            o = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
+            lib.bn_tanh_fwd(c, ms, bn.weight, bn.bias, o)
+            layers.append(dict(x=h, c=c, ms=ms, h=o, count=count, w=w))
+            h = o
+        mel_post = torch.empty((B, T, md), device=dev, dtype=torch.float32)
+        lib.conv_gemm(h, t["w2"], t["b2"], taps=5, pad_left=4, block_n=md, res_f32=mel_pre, res_bstride=T * md,
+                      res_tstride=md, out_f32=mel_post)
+        return mel_pre, mel_post, dict(d=d_bf16, layers=layers, t=t, h_last=h)
+
+    def _postnet_bwd(self, pn, tape, g_pre: torch.Tensor, g_post: torch.Tensor, g_post_bf: torch.Tensor):
+        """fp32 gradient w.r.t. the decoder output from dL/dmel_pre and dL/dmel_post."""
+        G = self.G
+        t = tape["t"]
+        B, T, D = tape["d"].shape
+        md = g_pre.shape[-1]
+        dev = g_pre.device
+        convs = [pn.conv1] + list(pn.conv_list)
+        bns = [pn.pre_batchnorm] + list(pn.batch_norm_list)
+        # mel_post = mel_pre + conv2(h4)
+        lib.colsum(g_post, G(pn.conv2.bias))
+        lib.conv_wgrad(g_post_bf, tape["h_last"], G(pn.conv2.weight), taps=5, pad_left=4, conv_layout=True)
+        dh = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
+        lib.conv_gemm(g_post_bf, _t(t["w2"]), self.zeros(D), taps=5, pad_left=0, block_n=192, out_bf16=dh)
+        g_mel = g_pre + g_post  # both paths reach mel_pre (postnets.py:75)
+        dmel = torch.empty((B, T, md), device=dev, dtype=torch.float32)
+        dmel_bf = torch.empty((B, T, md), device=dev, dtype=torch.bfloat16)
+        for i in range(len(convs) - 1, -1, -1):
+            s, cv, bn = tape["layers"][i], convs[i], bns[i]
+            red = torch.zeros((2, D), device=dev, dtype=torch.float32)
+            lib.bn_tanh_bwd(dh, s["h"], s["c"], s["ms"], bn.weight, red, None, 1.0 / s["count"], apply=False)
+            G(bn.bias).add_(red[0])
+            G(bn.weight).add_(red[1])
+            if self.sync_bn:  # SyncBatchNorm backward: the two reductions are summed over all ranks
+                dist.all_reduce(red, group=self.pg)
+            dc = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
+            lib.bn_tanh_bwd(dh, s["h"], s["c"], s["ms"], bn.weight, red, dc, 1.0 / s["count"], apply=True)
+            lib.colsum(dc, G(cv.bias))
+            lib.conv_wgrad(dc, s["x"], G(cv.weight), taps=5, pad_left=4, conv_layout=True)
+            if i > 0:
+                dh = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
+                lib.conv_gemm(dc, _t(s["w"]), self.zeros(D), taps=5, pad_left=0, block_n=192, out_bf16=dh)
+            else:
+                lib.conv_gemm(dc, _t(s["w"]), self.zeros(md), taps=5, pad_left=0, block_n=md, res_f32=g_mel,
+                              res_bstride=T * md, res_tstride=md, out_f32=dmel, out_bf16=dmel_bf)
+        # mel_pre = out(d)
+        lib.colsum(dmel, G(pn.out.bias))
+        lib.conv_wgrad(dmel_bf, tape["d"], G(pn.out.weight))
+        dd = torch.empty((B, T, D), device=dev, dtype=torch.float32)
+        lib.conv_gemm(dmel_bf, _t(t["wout"]), self.zeros(D), block_n=192, out_f32=dd)
+        return dd
+
+    # ------------------------------------------------------------------------------------------
+    # whole model (Models/fastspeech2.py:118-241, teacher-forced as train_fastspeech2.py:167 calls it)
+    # ------------------------------------------------------------------------------------------
+    def forward_backward(self, text, src_mask, mel_mask, alignment, f0, energy, mel) -> Dict[str, torch.Tensor]:
+        """One forward + losses + backward.  Gradients ACCUMULATE into the flat buffer (zero_grad() first).
+        Returns the five loss terms and their sum as device scalars plus the model outputs."""
+        model = self.model
+        enc, va, dec, pn = model.encoder, model.variance_adaptor, model.decoder, model.postnet
+        B, L = text.shape
+        dev = text.device
+        sm = E.mask_to_u8(src_mask, B, L, dev)
+        kv_src = lib.mask_lengths(sm)
+        e_bf, tape_enc = self._stack_fwd(enc, text, sm, kv_src)
+        mm = E.mask_to_u8(mel_mask, B, mel_mask.shape[-1], dev)
+        Tm = mm.shape[1]
+        # ---- variance adaptor (varianceadaptor.py:66-129, teacher-forced) ----
+        log_d, tape_d = self._pred_fwd(va.duration_predictor, e_bf, sm)
+        dur = torch.clamp(alignment, min=0).to(torch.int32).contiguous()
+        cum, mel_len = lib.lr_scan(dur)
+        xe, _, _, _ = lib.lr_expand(e_bf, cum, mel_len, Tm, want_aux=False)
+        p, tape_p = self._pred_fwd(va.pitch_predictor, xe, mm)
+        e, tape_e = self._pred_fwd(va.energy_predictor, xe, mm)
+        pb, eb = va._bins(dev)
+        tabs = va._tables()
+        f0 = f0.to(torch.float32).contiguous()
+        energy = energy.to(torch.float32).contiguous()
+        va_x, p_idx, e_idx = lib.bucket_embed_add(xe, f0, energy, pb, eb, tabs["ptab"], tabs["etab"], want_idx=True)
+        kv_mel = lib.mask_lengths(mm)
+        d_bf, tape_dec = self._stack_fwd(dec, va_x, mm, kv_mel)
+        mel_pre, mel_post, tape_pn = self._postnet_fwd(pn, d_bf)
+
+        # ---- losses (train_fastspeech2.py:212-217,245-259): unmasked L1 means, summed ----
+        mel = mel.to(torch.float32).contiguous()
+        lb = self.loss_buf
+        lb.zero_()
+        g_pre = torch.empty_like(mel_pre)
+        g_post = torch.empty_like(mel_post)
+        g_post_bf = torch.empty(mel_post.shape, device=dev, dtype=torch.bfloat16)
+        g_d, g_p, g_e = torch.empty_like(log_d), torch.empty_like(p), torch.empty_like(e)
+        lib.l1_loss(mel_pre, mel, lb[0:1], grad=g_pre)
+        lib.l1_loss(mel_post, mel, lb[1:2], grad=g_post, grad_bf16=g_post_bf)
+        lib.l1_loss(log_d, alignment.to(torch.float32).contiguous(), lb[2:3], grad=g_d, log_target=True)
+        lib.l1_loss(p, f0, lb[3:4], grad=g_p)
+        lib.l1_loss(e, energy, lb[4:5], grad=g_e)
+
+        # ---- backward ----
+        G = self.G
+        dd = self._postnet_bwd(pn, tape_pn, g_pre, g_post, g_post_bf)
+        dva = self._stack_bwd(dec, tape_dec, dd)                      # fp32 (B,Tm,D) w.r.t. va_x
+        lib.embed_bwd(dva, Tm, idx=p_idx, table=G(va.pitch_embedding.weight))
+        lib.embed_bwd(dva, Tm, idx=e_idx, table=G(va.energy_embedding.weight))
+        dxe = self._pred_bwd(va.pitch_predictor, tape_p, g_p, dva)
+        dxe = self._pred_bwd(va.energy_predictor, tape_e, g_e, dxe)
+        de = lib.lr_bwd(dxe, cum)                                      # fp32 (B,L,D)
+        de = self._pred_bwd(va.duration_predictor, tape_d, g_d, de)
+        self._stack_bwd(enc, tape_enc, de)
+        total = lb[0:5].sum()
+        return dict(loss=total, mel_loss=lb[0], post_mel_loss=lb[1], duration_loss=lb[2], f0_loss=lb[3],
+                    energy_loss=lb[4], outputs_prenet=mel_pre, outputs_postnet=mel_post, log_d_prediction=log_d,
+                    p_prediction=p, e_prediction=e)
+
+    def zero_grad(self) -> None:
+        self.flat_g.zero_()
+
+    def optimizer_step(self) -> float:
+        """Gradient all-reduce (mean over ranks) + clip_grad_norm_ + Adam with the Noam learning rate
+        (train_fastspeech2.py:117-120,304-315).  Returns the learning rate used."""
+        self.step_count += 1
+        if self.world > 1:
+            dist.all_reduce(self.flat_g, group=self.pg)  # NCCL over NVLink; SUM, the mean is folded into gscale
+        gscale = 1.0 / self.world
+        self.sumsq.zero_()
+        lib.sumsq(self.flat_g, self.sumsq)
+        lr = self.lr()
+        lib.adam_step(self.flat_p, self.flat_g, self.flat_m, self.flat_v, self.sumsq, gscale=gscale,
+                      clip=float(self.clip or 0.0), lr=lr, beta1=self.betas[0], beta2=self.betas[1], eps=self.eps,
+                      step=self.step_count)
+        self.invalidate_caches()
+        return lr
+
+    def grad_norm(self) -> torch.Tensor:
+        return torch.sqrt(self.sumsq) / self.world
+
+    def train_step(self, text, src_mask, mel_mask, alignment, f0, energy, mel) -> Dict[str, torch.Tensor]:
+        self.zero_grad()
+        out = self.forward_backward(text, src_mask, mel_mask, alignment, f0, energy, mel)
+        out["lr"] = self.optimizer_step()
+        return out
+
+    def broadcast_parameters(self, src: int = 0) -> None:
+        """DDP's initial parameter broadcast, one collective over the flat buffer."""
+        if self.world > 1:
+            dist.broadcast(self.flat_p, src=src, group=self.pg)
+            for bn in [self.model.postnet.pre_batchnorm] + list(self.model.postnet.batch_norm_list):
+                dist.broadcast(bn.running_mean, src=src, group=self.pg)
+                dist.broadcast(bn.running_var, src=src, group=self.pg)
+            self.invalidate_caches()
