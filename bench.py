@@ -351,6 +351,114 @@ def ours(args):
         dist.destroy_process_group()
 
 
+def make_train_batch(rank: int, B: int):
+    """cfg3: ragged text, alignment in [2,15) on valid phonemes (T ~ 1000), N(0,1) mel, -0.5 padding."""
+    import torch
+
+    from transformer_tts_b200 import synth
+
+    text, pos, _ = synth.synth_text_batch(B, L_PHON, ragged=True, seed=1234 + rank, min_len=L_PHON // 2)
+    g = torch.Generator().manual_seed(4321 + rank)
+    dur = torch.randint(2, 15, (B, L_PHON), generator=g)
+    dur = torch.where(pos != 0, dur, torch.zeros_like(dur))
+    mel_len = dur.sum(1)
+    T = int(mel_len.max())
+    ar = torch.arange(1, T + 1).unsqueeze(0).expand(B, T)
+    pos_mel = torch.where(ar <= mel_len.unsqueeze(1), ar, torch.zeros_like(ar))
+    valid = pos_mel != 0
+    f0 = torch.where(valid, torch.rand((B, T), generator=g) * 729.0 + 71.0, torch.zeros(B, T))
+    en = torch.where(valid, torch.rand((B, T), generator=g) * 400.0, torch.zeros(B, T))
+    mel = synth.synth_mel(pos_mel, 80, seed=1234 + rank)
+    return dict(text=text, src_mask=(pos != 0).unsqueeze(-2), mel_mask=valid.unsqueeze(-2), alignment=dur, f0=f0,
+                energy=en, mel=mel), int(mel_len.sum())
+
+
+def train(args):
+    """BASELINE.json configs[2]: FastSpeech2 training step (fwd + bwd + clip + Adam/Noam), batch 32 per GPU,
+    data parallel over N GPUs with the gradient all-reduce through NCCL.  Not the headline metric: run with
+    `--workload train`.  value = valid mel frames trained per second over all ranks."""
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl")
+    from transformer_tts_b200 import build_fastspeech2, lib, synth
+    from transformer_tts_b200.training import Trainer
+
+    lib.load()
+    hp = synth.make_hp()
+    model = build_fastspeech2(hp)
+    model.load_state_dict(synth.synth_state_dict(hp))
+    model = model.cuda().train()
+    tr = Trainer(model)
+    tr.broadcast_parameters()
+    Bt = args.train_batch
+    host, frames = make_train_batch(rank, Bt)
+    host = {k: v.pin_memory() for k, v in host.items()}
+    dev = {k: v.cuda() for k, v in host.items()}
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def allr(x, op):
+        if world == 1:
+            return x
+        t = torch.tensor([x], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    for _ in range(max(3, args.warmup)):
+        out = tr.train_step(**dev)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    barrier()
+    l0 = lib.LAUNCH_COUNT
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        out = tr.train_step(**dev)
+    e1.record()
+    barrier()
+    launches = lib.LAUNCH_COUNT - l0
+    dev_ms = allr(e0.elapsed_time(e1), dist.ReduceOp.MAX)
+    loss_h = torch.empty(1).pin_memory()
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        d = {k: v.cuda(non_blocking=True) for k, v in host.items()}
+        out = tr.train_step(**d)
+        loss_h.copy_(out["loss"].reshape(1), non_blocking=True)
+    e1.record()
+    barrier()
+    e2e_ms = allr(e0.elapsed_time(e1), dist.ReduceOp.MAX)
+    sampler.stop_flag.set()
+    sampler.join(timeout=2)
+    total_frames = allr(float(frames), dist.ReduceOp.SUM)
+    if rank == 0:
+        h2d = sum(v.numel() * v.element_size() for v in host.values())
+        line = {"metric": "fastspeech2_train_mel_frames_per_sec", "value": total_frames * args.steps / (dev_ms * 1e-3),
+                "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+                "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "bf16", "data": "synthetic",
+                "config": {"workload": f"fastspeech2_train_step_bf16_B{Bt}_per_gpu_L128_T~1000_adam_noam_clip",
+                           "batch_per_gpu": Bt, "frames_per_step_per_gpu": frames, "t_max": int(dev["mel"].shape[1]),
+                           "parallelism": f"dp{world}, NCCL all-reduce of one flat fp32 gradient buffer "
+                                          f"({tr.flat_g.numel() * 4 / 1e6:.0f} MB)" + (", SyncBatchNorm" if world > 1 else ""),
+                           "l2": "working set per step (several GB of saved activations) exceeds the 126 MB L2"},
+                "e2e": {"value": total_frames * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                        "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms / args.steps},
+                "gpu_launches": launches, "clocks": sampler.summary(), "loss": float(out["loss"])}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -358,9 +466,13 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="infer", choices=["infer", "train"])
+    ap.add_argument("--train-batch", type=int, default=32)
     args = ap.parse_args()
     if args.impl == "reference":
         reference_arm(args)
+    elif args.workload == "train":
+        train(args)
     else:
         ours(args)
 

@@ -93,3 +93,52 @@ def test_two_rank_gloo_sharded_inference_matches_single_process():
             assert torch.allclose(torch.from_numpy(merged[k]), single[k], atol=1e-5, rtol=1e-5), k
         owned += local_ids
     assert sorted(owned) == [0, 1, 2, 3, 4]  # the two shards partition the utterances, no overlap
+
+
+# --------------------------------------------------------------------------------------------------
+# data-parallel TRAINING host logic (transformer_tts_b200/training.py) under gloo, world size 2
+# --------------------------------------------------------------------------------------------------
+def _train_dp_worker(rank, world, port, q):
+    import os
+
+    import torch
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from transformer_tts_b200.training import allreduce_mean_scale, noam_lr, sync_bn_moments
+
+    g = torch.Generator().manual_seed(5)
+    x_all = torch.randn(2 * 37, 8, generator=g) * 3 + 1  # rows of both ranks
+    grads_all = torch.randn(2, 1000, generator=g)
+    # gradient exchange: SUM all-reduce, mean folded into the returned scale
+    flat = grads_all[rank].clone()
+    scale = allreduce_mean_scale(flat, world)
+    mean_grad = flat * scale
+    # SyncBatchNorm moments from local [sum | sum^2]
+    x = x_all[rank * 37:(rank + 1) * 37]
+    stats = torch.stack([x.sum(0), (x * x).sum(0)])
+    ms, var, count = sync_bn_moments(stats, x.shape[0], world, True, 1e-5)
+    ok = torch.allclose(mean_grad, grads_all.mean(0), atol=1e-6)
+    ok &= count == 74.0 and torch.allclose(ms[0], x_all.mean(0), atol=1e-5)
+    ok &= torch.allclose(var, x_all.var(0, unbiased=False), rtol=1e-4, atol=1e-5)
+    ok &= torch.allclose(ms[1], torch.rsqrt(x_all.var(0, unbiased=False) + 1e-5), rtol=1e-4)
+    ok &= abs(noam_lr(1, 384, 1.0, 4000) - 4000 ** -1.5 * 384 ** -0.5) < 1e-15
+    ok &= abs(noam_lr(10000, 384, 1.0, 4000) - 10000 ** -0.5 * 384 ** -0.5) < 1e-15
+    q.put((rank, bool(ok)))
+    dist.destroy_process_group()
+
+
+def test_training_data_parallel_host_logic_gloo_world2():
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29400 + (os.getpid() % 500)
+    procs = [ctx.Process(target=_train_dp_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in range(2)]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(res) == [(0, True), (1, True)]

@@ -35,6 +35,26 @@ def _t(w_taps: torch.Tensor) -> torch.Tensor:
     return w_taps.permute(0, 2, 1).flip(0).contiguous()
 
 
+def allreduce_mean_scale(flat_g: torch.Tensor, world: int, group=None) -> float:
+    """Data-parallel gradient exchange: ONE all-reduce (SUM) over the flat gradient buffer; the mean is
+    not applied here but returned as the scale the optimizer kernel folds into its gradient read."""
+    if world > 1:
+        dist.all_reduce(flat_g, group=group)
+    return 1.0 / world
+
+
+def sync_bn_moments(stats: torch.Tensor, rows_local: int, world: int, sync: bool, eps: float, group=None):
+    """[sum x | sum x^2] (2,C) of the local rows -> ([mean | rstd] (2,C), biased var, global row count).  With
+    `sync` the sums are all-reduced first, which is what SyncBatchNorm's forward does."""
+    count = float(rows_local)
+    if sync and world > 1:
+        dist.all_reduce(stats, group=group)
+        count *= world
+    mean = stats[0] / count
+    var = (stats[1] / count - mean * mean).clamp_(min=0.0)
+    return torch.stack([mean, torch.rsqrt(var + eps)]).contiguous(), var, count
+
+
 class Trainer:
     """Owns the flat parameter / gradient / Adam-state buffers of a ``FastSpeech2`` and runs training steps."""
 
@@ -269,13 +289,8 @@ class Trainer:
     # ------------------------------------------------------------------------------------------
     def _bn_finish_stats(self, stats: torch.Tensor, rows_local: int, bn) -> tuple:
         """[sum | sum^2] -> [mean | rstd] (+ running-stat update as nn.BatchNorm1d / SyncBatchNorm do)."""
-        count = float(rows_local)
-        if self.sync_bn:
-            dist.all_reduce(stats, group=self.pg)
-            count *= self.world
-        mean = stats[0] / count
-        var = (stats[1] / count - mean * mean).clamp_(min=0.0)
-        ms = torch.stack([mean, torch.rsqrt(var + bn.eps)]).contiguous()
+        ms, var, count = sync_bn_moments(stats, rows_local, self.world, self.sync_bn, bn.eps, self.pg)
+        mean = ms[0]
         with torch.no_grad():
             m = self.bn_momentum
             bn.running_mean.mul_(1 - m).add_(mean, alpha=m)
@@ -420,9 +435,7 @@ class Trainer:
         """Gradient all-reduce (mean over ranks) + clip_grad_norm_ + Adam with the Noam learning rate
         (train_fastspeech2.py:117-120,304-315).  Returns the learning rate used."""
         self.step_count += 1
-        if self.world > 1:
-            dist.all_reduce(self.flat_g, group=self.pg)  # NCCL over NVLink; SUM, the mean is folded into gscale
-        gscale = 1.0 / self.world
+        gscale = allreduce_mean_scale(self.flat_g, self.world, self.pg)  # NCCL over NVLink
         self.sumsq.zero_()
         lib.sumsq(self.flat_g, self.sumsq)
         lr = self.lr()
