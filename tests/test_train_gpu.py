@@ -164,3 +164,51 @@ def test_train_step_matches_torch_adam_on_own_gradients():
     opt.step()
     torch.cuda.synchronize()
     assert (tr.flat_p - p_ref.detach()).abs().max().item() < 1e-6
+
+
+def test_dropin_autograd_mode_matches_trainer():
+    """The reference's own loop shape (train_fastspeech2.py:167-315): model.train(); model(...) ; nn.L1Loss terms;
+    loss.backward(); clip_grad_norm_; torch.optim.Adam.step() — with this package's modules in place of Models/."""
+    import torch.nn as nn
+
+    from transformer_tts_b200 import synth
+    from transformer_tts_b200.training import Trainer
+
+    hp, sd, model = build()
+    text, pos, _ = synth.synth_text_batch(3, 24, ragged=True, seed=21)
+    dur, pos_mel, f0, en = synth.synth_targets(pos, seed=21, max_dur=8)
+    mel = synth.synth_mel(pos_mel, hp.mel_dim, seed=21)
+    c = lambda t: t.cuda()  # noqa: E731
+    text, src_mask, mel_mask, dur, f0, en, mel = (c(t) for t in (text, (pos != 0).unsqueeze(-2),
+                                                                 (pos_mel != 0).unsqueeze(-2), dur, f0, en, mel))
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3, betas=(0.9, 0.98), eps=1e-9)
+    out = model(text, src_mask, mel_mask, dur, f0, en)
+    assert len(out) == 14 and out[0].requires_grad and out[7] is None
+    loss = nn.L1Loss()(out[0], mel) + nn.L1Loss()(out[1], mel)
+    loss = loss + nn.L1Loss()(out[3], f0) + nn.L1Loss()(out[4], en)
+    loss = loss + nn.L1Loss()(out[2], torch.log(dur.float() + 1))
+    loss.backward()
+    grads = {n: p.grad.detach().clone() for n, p in model.named_parameters()}
+    assert all(g is not None for g in grads.values()) and len(grads) == 277
+    w0 = model.postnet.conv2.weight.detach().clone()
+    torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
+    opt.step()
+    assert not torch.equal(w0, model.postnet.conv2.weight.detach())
+    out2 = model(text, src_mask, mel_mask, dur, f0, en)  # derived bf16 operands were refreshed (version counters)
+    assert not torch.equal(out2[1], out[1])
+    # same kernels through the Trainer on a fresh copy of the weights
+    _, _, model2 = build()
+    tr = Trainer(model2)
+    tr.zero_grad()
+    o = tr.forward_backward(text, src_mask, mel_mask, dur, f0, en, mel)
+    torch.cuda.synchronize()
+    assert abs(float(o["loss"]) - float(loss.detach())) < 1e-3 * abs(float(loss.detach()))
+    num = den = 0.0
+    for n, p in model2.named_parameters():
+        num += float(((tr.G(p) - grads[n]).double() ** 2).sum())
+        den += float((grads[n].double() ** 2).sum())
+    assert (num / den) ** 0.5 < 2e-3  # identical kernels; only fp32 atomic order and BN running stats differ
+    model.eval()
+    with torch.no_grad():
+        ev = model(text[:1], src_mask[:1])
+    assert ev[1].shape[-1] == hp.mel_dim

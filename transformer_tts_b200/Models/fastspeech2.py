@@ -76,8 +76,17 @@ class FastSpeech2(nn.Module):
     def forward(self, src, src_mask, mel_mask=None, d_target=None, p_target=None, e_target=None, accent=None,
                 spkr_emb=None, fix_mask=None, spkr_emb_post=None, temperature=None, pitch_perturbation=False,
                 duration_perturbation=False, hop_size=None):
-        E.require_inference(self, "FastSpeech2")
         E.require_cuda(src, "FastSpeech2")
+        if self.training:
+            if fix_mask is not None or accent is not None or spkr_emb is not None or spkr_emb_post is not None \
+                    or temperature is not None or hop_size is not None or pitch_perturbation or duration_perturbation:
+                raise NotImplementedError("fix_mask / accent / speaker / temperature / hop / perturbation inputs are "
+                                          "out of scope")
+            from ..training import autograd_forward
+
+            mel_pre, mel_post, log_d, p, e, va_x, text_dur = autograd_forward(self, src, src_mask, mel_mask, d_target,
+                                                                              p_target, e_target)
+            return (mel_pre, mel_post, log_d, p, e, va_x, text_dur, None, None, None, None, None, None, None)
         if fix_mask is not None or accent is not None or spkr_emb is not None or spkr_emb_post is not None \
                 or temperature is not None or hop_size is not None or pitch_perturbation or duration_perturbation:
             raise NotImplementedError("fix_mask / accent / speaker / temperature / hop / perturbation inputs are out of scope")

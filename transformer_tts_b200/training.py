@@ -35,6 +35,17 @@ def _t(w_taps: torch.Tensor) -> torch.Tensor:
     return w_taps.permute(0, 2, 1).flip(0).contiguous()
 
 
+def require_zero_dropout(model) -> None:
+    """Parity with the reference is only defined at dropout 0 and no RNG-mask kernels exist yet."""
+    bad = [n for n, m in model.named_modules()
+           if (isinstance(m, torch.nn.Dropout) and m.p > 0) or (isinstance(getattr(m, "dropout", None), float)
+                                                                 and m.dropout > 0)]
+    if bad:
+        raise NotImplementedError("training with dropout > 0 is not built (no RNG-mask kernels yet); construct the "
+                                  "model with dropout = dropout_postnet = dropout_variance_adaptor = 0; offending: "
+                                  + ", ".join(bad[:4]))
+
+
 def allreduce_mean_scale(flat_g: torch.Tensor, world: int, group=None) -> float:
     """Data-parallel gradient exchange: ONE all-reduce (SUM) over the flat gradient buffer; the mean is
     not applied here but returned as the scale the optimizer kernel folds into its gradient read."""
@@ -60,8 +71,14 @@ class Trainer:
 
     def __init__(self, model, *, lr_max: float = 1e-3, betas=(0.9, 0.98), eps: float = 1e-9, clip: float = 1.0,
                  warmup_step: int = 4000, warmup_factor: float = 1.0, fixed_lr: Optional[float] = None,
-                 process_group=None, sync_bn: bool = True, bn_momentum: float = 0.1):
+                 process_group=None, sync_bn: bool = True, bn_momentum: float = 0.1, flatten: bool = True):
+        """flatten=True (training loop owner): parameters are re-pointed into one flat fp32 buffer, `p.grad` are
+        views of the flat gradient buffer and optimizer_step() runs the fused clip+Adam kernel.
+        flatten=False (drop-in autograd mode, see `autograd_forward`): parameters are left alone, only the flat
+        gradient buffer exists and the caller's torch optimizer owns the update."""
         lib.load()
+        require_zero_dropout(model)
+        self.flatten = flatten
         self.model = model
         self.pg = process_group
         self.world = dist.get_world_size(process_group) if (dist.is_available() and dist.is_initialized()) else 1
@@ -80,27 +97,38 @@ class Trainer:
         for n, p in params:
             offs[n] = total
             total += (p.numel() + 3) // 4 * 4
-        self.flat_p = torch.zeros(total, device=dev, dtype=torch.float32)
-        self.flat_g = torch.zeros(total, device=dev, dtype=torch.float32)
-        self.flat_m = torch.zeros(total, device=dev, dtype=torch.float32)
-        self.flat_v = torch.zeros(total, device=dev, dtype=torch.float32)
+        self.params = [p for _, p in params]
+        self.offsets = [(offs[n], p.numel()) for n, p in params]
+        self.total = total
         self.grads: Dict[int, torch.Tensor] = {}
-        self.names: Dict[int, str] = {}
-        with torch.no_grad():
-            for n, p in params:
-                o, k = offs[n], p.numel()
-                self.flat_p[o:o + k].copy_(p.detach().reshape(-1).float())
-                p.data = self.flat_p[o:o + k].view(p.shape)  # parameters become views of the flat buffer
-                g = self.flat_g[o:o + k].view(p.shape)
-                p.grad = g
-                self.grads[id(p)] = g
-                self.names[id(p)] = n
+        self.names: Dict[int, str] = {id(p): n for n, p in params}
+        self.flat_g = torch.zeros(total, device=dev, dtype=torch.float32)
+        self._bind_grads()
+        if flatten:
+            self.flat_p = torch.zeros(total, device=dev, dtype=torch.float32)
+            self.flat_m = torch.zeros(total, device=dev, dtype=torch.float32)
+            self.flat_v = torch.zeros(total, device=dev, dtype=torch.float32)
+            with torch.no_grad():
+                for n, p in params:
+                    o, k = offs[n], p.numel()
+                    self.flat_p[o:o + k].copy_(p.detach().reshape(-1).float())
+                    p.data = self.flat_p[o:o + k].view(p.shape)  # parameters become views of the flat buffer
+                    p.grad = self.grads[id(p)]
         self.sumsq = torch.zeros(1, device=dev, dtype=torch.float32)
         self.loss_buf = torch.zeros(8, device=dev, dtype=torch.float32)
         self._zeros = {}
         self.invalidate_caches()
 
     # ------------------------------------------------------------------------------------------
+    def _bind_grads(self) -> None:
+        for p, (o, k) in zip(self.params, self.offsets):
+            self.grads[id(p)] = self.flat_g[o:o + k].view(p.shape)
+
+    def fresh_grads(self) -> None:
+        """A new zeroed gradient buffer (autograd mode hands the previous one to the caller's optimizer)."""
+        self.flat_g = torch.zeros(self.total, device=self.dev, dtype=torch.float32)
+        self._bind_grads()
+
     def G(self, p: torch.Tensor) -> torch.Tensor:
         return self.grads[id(p)]
 
@@ -370,9 +398,8 @@ class Trainer:
     # ------------------------------------------------------------------------------------------
     # whole model (Models/fastspeech2.py:118-241, teacher-forced as train_fastspeech2.py:167 calls it)
     # ------------------------------------------------------------------------------------------
-    def forward_backward(self, text, src_mask, mel_mask, alignment, f0, energy, mel) -> Dict[str, torch.Tensor]:
-        """One forward + losses + backward.  Gradients ACCUMULATE into the flat buffer (zero_grad() first).
-        Returns the five loss terms and their sum as device scalars plus the model outputs."""
+    def forward_train(self, text, src_mask, mel_mask, alignment, f0, energy):
+        """Teacher-forced forward in train() semantics.  Returns (outputs dict, tape for backward_train)."""
         model = self.model
         enc, va, dec, pn = model.encoder, model.variance_adaptor, model.decoder, model.postnet
         B, L = text.shape
@@ -397,6 +424,36 @@ class Trainer:
         kv_mel = lib.mask_lengths(mm)
         d_bf, tape_dec = self._stack_fwd(dec, va_x, mm, kv_mel)
         mel_pre, mel_post, tape_pn = self._postnet_fwd(pn, d_bf)
+        tape = dict(enc=tape_enc, dec=tape_dec, pn=tape_pn, d=tape_d, p=tape_p, e=tape_e, cum=cum, p_idx=p_idx,
+                    e_idx=e_idx, Tm=Tm, shapes=[mel_pre.shape, mel_post.shape, log_d.shape, p.shape, e.shape])
+        return dict(mel_pre=mel_pre, mel_post=mel_post, log_d=log_d, p=p, e=e, va_x=va_x, text_dur=xe,
+                    f0=f0, energy=energy), tape
+
+    def backward_train(self, tape, g_pre, g_post, g_d, g_p, g_e, g_post_bf=None) -> None:
+        """Gradients of every parameter from the gradients of the five outputs (accumulated into the flat buffer)."""
+        model = self.model
+        enc, va, dec, pn = model.encoder, model.variance_adaptor, model.decoder, model.postnet
+        G = self.G
+        Tm = tape["Tm"]
+        if g_post_bf is None:
+            g_post_bf = lib.cast_bf16(g_post)
+        dd = self._postnet_bwd(pn, tape["pn"], g_pre, g_post, g_post_bf)
+        dva = self._stack_bwd(dec, tape["dec"], dd)                    # fp32 (B,Tm,D) w.r.t. va_x
+        lib.embed_bwd(dva, Tm, idx=tape["p_idx"], table=G(va.pitch_embedding.weight))
+        lib.embed_bwd(dva, Tm, idx=tape["e_idx"], table=G(va.energy_embedding.weight))
+        dxe = self._pred_bwd(va.pitch_predictor, tape["p"], g_p, dva)
+        dxe = self._pred_bwd(va.energy_predictor, tape["e"], g_e, dxe)
+        de = lib.lr_bwd(dxe, tape["cum"])                              # fp32 (B,L,D)
+        de = self._pred_bwd(va.duration_predictor, tape["d"], g_d, de)
+        self._stack_bwd(enc, tape["enc"], de)
+
+    def forward_backward(self, text, src_mask, mel_mask, alignment, f0, energy, mel) -> Dict[str, torch.Tensor]:
+        """One forward + losses + backward.  Gradients ACCUMULATE into the flat buffer (zero_grad() first).
+        Returns the five loss terms and their sum as device scalars plus the model outputs."""
+        o, tape = self.forward_train(text, src_mask, mel_mask, alignment, f0, energy)
+        mel_pre, mel_post, log_d, p, e, f0, energy = (o[k] for k in ("mel_pre", "mel_post", "log_d", "p", "e", "f0",
+                                                                     "energy"))
+        dev = text.device
 
         # ---- losses (train_fastspeech2.py:212-217,245-259): unmasked L1 means, summed ----
         mel = mel.to(torch.float32).contiguous()
@@ -412,17 +469,7 @@ class Trainer:
         lib.l1_loss(p, f0, lb[3:4], grad=g_p)
         lib.l1_loss(e, energy, lb[4:5], grad=g_e)
 
-        # ---- backward ----
-        G = self.G
-        dd = self._postnet_bwd(pn, tape_pn, g_pre, g_post, g_post_bf)
-        dva = self._stack_bwd(dec, tape_dec, dd)                      # fp32 (B,Tm,D) w.r.t. va_x
-        lib.embed_bwd(dva, Tm, idx=p_idx, table=G(va.pitch_embedding.weight))
-        lib.embed_bwd(dva, Tm, idx=e_idx, table=G(va.energy_embedding.weight))
-        dxe = self._pred_bwd(va.pitch_predictor, tape_p, g_p, dva)
-        dxe = self._pred_bwd(va.energy_predictor, tape_e, g_e, dxe)
-        de = lib.lr_bwd(dxe, cum)                                      # fp32 (B,L,D)
-        de = self._pred_bwd(va.duration_predictor, tape_d, g_d, de)
-        self._stack_bwd(enc, tape_enc, de)
+        self.backward_train(tape, g_pre, g_post, g_d, g_p, g_e, g_post_bf)
         total = lb[0:5].sum()
         return dict(loss=total, mel_loss=lb[0], post_mel_loss=lb[1], duration_loss=lb[2], f0_loss=lb[3],
                     energy_loss=lb[4], outputs_prenet=mel_pre, outputs_postnet=mel_post, log_d_prediction=log_d,
@@ -434,6 +481,8 @@ class Trainer:
     def optimizer_step(self) -> float:
         """Gradient all-reduce (mean over ranks) + clip_grad_norm_ + Adam with the Noam learning rate
         (train_fastspeech2.py:117-120,304-315).  Returns the learning rate used."""
+        if not self.flatten:
+            raise RuntimeError("optimizer_step() needs flatten=True; in autograd mode the caller's optimizer steps")
         self.step_count += 1
         gscale = allreduce_mean_scale(self.flat_g, self.world, self.pg)  # NCCL over NVLink
         self.sumsq.zero_()
@@ -462,3 +511,43 @@ class Trainer:
                 dist.broadcast(bn.running_mean, src=src, group=self.pg)
                 dist.broadcast(bn.running_var, src=src, group=self.pg)
             self.invalidate_caches()
+
+
+# --------------------------------------------------------------------------------------------------
+# Drop-in autograd mode: model.train(); out = model(text, src_mask, mel_mask, alignment, f0, energy);
+# loss.backward(); torch optimizer.step()  — the reference's own loop (train_fastspeech2.py:167-315).
+# --------------------------------------------------------------------------------------------------
+class _FastSpeech2TrainFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, engine, text, src_mask, mel_mask, alignment, f0, energy, *params):
+        o, tape = engine.forward_train(text, src_mask, mel_mask, alignment, f0, energy)
+        ctx.engine, ctx.tape = engine, tape
+        ctx.mark_non_differentiable(o["va_x"], o["text_dur"])
+        return o["mel_pre"], o["mel_post"], o["log_d"], o["p"], o["e"], o["va_x"], o["text_dur"]
+
+    @staticmethod
+    def backward(ctx, g_pre, g_post, g_d, g_p, g_e, _g_va, _g_td):
+        engine, tape = ctx.engine, ctx.tape
+        o_shapes = tape["shapes"]
+
+        def z(g, shape):
+            return torch.zeros(shape, device=engine.dev, dtype=torch.float32) if g is None else g.float().contiguous()
+
+        engine.fresh_grads()
+        engine.backward_train(tape, z(g_pre, o_shapes[0]), z(g_post, o_shapes[1]), z(g_d, o_shapes[2]),
+                              z(g_p, o_shapes[3]), z(g_e, o_shapes[4]))
+        return (None,) * 7 + tuple(engine.G(p) for p in engine.params)
+
+
+def autograd_forward(model, text, src_mask, mel_mask, d_target, p_target, e_target):
+    """FastSpeech2.forward in train() mode: the 14-tuple of Models/fastspeech2.py:241 with autograd connected
+    to every parameter through one Function whose backward is `Trainer.backward_train`."""
+    if mel_mask is None or d_target is None or p_target is None or e_target is None:
+        raise NotImplementedError("training forward is teacher-forced: mel_mask, d_target, p_target, e_target are "
+                                  "required (train_fastspeech2.py:167)")
+    eng = getattr(model, "_ttsb_train_engine", None)
+    if eng is None:
+        eng = Trainer(model, flatten=False)
+        object.__setattr__(model, "_ttsb_train_engine", eng)
+    fn_out = _FastSpeech2TrainFn.apply(eng, text, src_mask, mel_mask, d_target, p_target, e_target, *eng.params)
+    return fn_out
