@@ -74,11 +74,19 @@ def test_train_step_vs_reference_golden():
     print("worst gradient-norm deviations:", worst[:5])
     assert worst[0][0] < 5e-2, worst[:5]
     pd = dict(model.named_parameters())
+    bad = []
     for n in FULL:
-        assert rel(tr.G(pd[n]), torch.from_numpy(g["full:" + n])) < 8e-2, n
+        ref_t = torch.from_numpy(g["full:" + n])
+        # pe.alpha gradients are scalars formed by heavily cancelling sums: measured against the same floor
+        e = float((tr.G(pd[n]).double().cpu() - ref_t.double()).norm() / max(float(ref_t.double().norm()), floor))
+        if e >= 8e-2:
+            bad.append((n, e))
     for n in SUB:
         gr = tr.G(pd[n])
-        assert rel(gr.reshape(gr.shape[0], -1)[::7, ::13], torch.from_numpy(g["sub:" + n])) < 8e-2, n
+        e = rel(gr.reshape(gr.shape[0], -1)[::7, ::13], torch.from_numpy(g["sub:" + n]))
+        if e >= 8e-2:
+            bad.append((n, e))
+    assert not bad, bad
     gg = float(torch.sqrt((tr.flat_g.double() ** 2).sum()))
     assert abs(gg - float(g["global_grad_norm"])) / float(g["global_grad_norm"]) < 3e-2
 

@@ -165,24 +165,49 @@ ln_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, cons
 
 // ------------------------------------------------------------------------------------------------
 // Column sums (bias gradients): out[c] += sum_rows x[row, c]; x bf16 or fp32 with leading dimension ld.
-// Thread = 4 consecutive columns; a CTA covers 1024 columns at most per pass, rows strided over blockIdx.y.
+// A thread owns one 16-byte chunk of columns (8 bf16 / 4 fp32) and walks rows; 256/chunks rows are read per
+// pass so every warp issues full 16-byte coalesced loads; partials meet in smem, one atomicAdd per column per CTA.
 // ------------------------------------------------------------------------------------------------
 template <typename TIn>
 __global__ void __launch_bounds__(256)
 colsum_kernel(const TIn* __restrict__ x, int64_t ld, float* __restrict__ out, int64_t rows, int cols) {
-  const int c = (blockIdx.x * 256 + threadIdx.x) * 4;
-  if (c >= cols) return;
-  float4 acc = make_float4(0, 0, 0, 0);
-  for (int64_t r = blockIdx.y; r < rows; r += gridDim.y) {
-    float4 v;
-    if constexpr (sizeof(TIn) == 2) v = ld_bf16x4(reinterpret_cast<const __nv_bfloat16*>(x) + r * ld + c);
-    else v = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(x) + r * ld + c);
-    acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+  constexpr int VEC = 16 / sizeof(TIn);
+  __shared__ float sbuf[256 * VEC];
+  const int cpr = cols / VEC;                       // chunks per row
+  const int cb0 = blockIdx.x * 256;                 // first chunk of this column block
+  const int cpb = min(cpr - cb0, 256);              // chunks in this block
+  const int rpp = 256 / cpb;                        // rows per pass
+  const int c = threadIdx.x % cpb, r0 = threadIdx.x / cpb;
+  float acc[VEC];
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) acc[i] = 0.f;
+  if (r0 < rpp) {
+    const TIn* base = x + static_cast<int64_t>(cb0 + c) * VEC;
+    for (int64_t r = static_cast<int64_t>(blockIdx.y) * rpp + r0; r < rows; r += static_cast<int64_t>(gridDim.y) * rpp) {
+      const uint4 u = __ldcs(reinterpret_cast<const uint4*>(base + r * ld));
+      if constexpr (sizeof(TIn) == 2) {
+        const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float2 f = __bfloat1622float2(h2[i]);
+          acc[2 * i] += f.x;
+          acc[2 * i + 1] += f.y;
+        }
+      } else {
+        const float* f = reinterpret_cast<const float*>(&u);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) acc[i] += f[i];
+      }
+    }
   }
-  atomicAdd(out + c, acc.x);
-  atomicAdd(out + c + 1, acc.y);
-  atomicAdd(out + c + 2, acc.z);
-  atomicAdd(out + c + 3, acc.w);
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) sbuf[threadIdx.x * VEC + i] = acc[i];
+  __syncthreads();
+  for (int i = threadIdx.x; i < cpb * VEC; i += 256) {
+    float sum = 0.f;
+    for (int r = 0; r < rpp; ++r) sum += sbuf[(r * cpb) * VEC + i];
+    atomicAdd(out + cb0 * VEC + i, sum);
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -372,6 +397,31 @@ embed_bwd_kernel(const float* __restrict__ g, const int64_t* __restrict__ idx64,
   }
 }
 
+// Embedding weight gradient for small vocabularies (V <= 256): a CTA privatises a 32-column slab of the table
+// in shared memory (V x 32 fp32 <= 32 KB), walks its share of the rows with one warp per row (128-byte coalesced
+// reads), accumulates with shared-memory atomics and flushes the slab once with global atomics.
+// grid = (D/32 slabs, row splits).
+__global__ void __launch_bounds__(kRowThreads)
+embed_scatter_kernel(const float* __restrict__ g, const int64_t* __restrict__ idx64, const int32_t* __restrict__ idx32,
+                     float* __restrict__ table, int skip_idx, int64_t rows, int D, int V) {
+  extern __shared__ float stab[];  // [V][32]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int col = blockIdx.x * 32 + lane;
+  for (int i = threadIdx.x; i < V * 32; i += kRowThreads) stab[i] = 0.f;
+  __syncthreads();
+  for (int64_t row = static_cast<int64_t>(blockIdx.y) * kRowWarps + warp; row < rows;
+       row += static_cast<int64_t>(gridDim.y) * kRowWarps) {
+    const int64_t id = idx64 ? idx64[row] : static_cast<int64_t>(idx32[row]);
+    if (id < 0 || id >= V || id == skip_idx) continue;
+    atomicAdd(&stab[id * 32 + lane], __ldcs(g + row * D + col));
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < V * 32; i += kRowThreads) {
+    const float v = stab[i];
+    if (v != 0.f) atomicAdd(table + static_cast<int64_t>(i >> 5) * D + blockIdx.x * 32 + (i & 31), v);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // L1 loss, mean reduction, with its gradient (nn.L1Loss, train_fastspeech2.py:212-217,245-259):
 //   loss += scale * sum |pred - target| ; grad = scale * sign(pred - target)       (scale = 1/numel)
@@ -519,8 +569,17 @@ extern "C" int ttsb200_layernorm_bwd(const float* x, const float* gamma, const f
 
 extern "C" int ttsb200_colsum(const void* x, int32_t is_bf16, int64_t ld, float* out, int64_t rows, int32_t cols,
                               ttsb200_stream_t s) {
-  TTSB_CHECK_ARG(x && out && rows > 0 && cols > 0 && cols % 4 == 0 && ld % 4 == 0, "colsum: bad args");
-  dim3 grid((cols / 4 + 255) / 256, static_cast<unsigned>(rows < 592 ? rows : 592));
+  const int vec = is_bf16 ? 8 : 4;
+  TTSB_CHECK_ARG(x && out && rows > 0 && cols > 0 && cols % vec == 0 && ld % vec == 0 &&
+                     (reinterpret_cast<uintptr_t>(x) & 15) == 0,
+                 "colsum: cols and ld must be multiples of %d, x 16-byte aligned", vec);
+  const int cpr = cols / vec;
+  const int cpb = cpr < 256 ? cpr : 256;
+  const int rpp = 256 / cpb;
+  int64_t gy = (rows + rpp * 8 - 1) / (rpp * 8);
+  if (gy > 592) gy = 592;
+  if (gy < 1) gy = 1;
+  dim3 grid((cpr + 255) / 256, static_cast<unsigned>(gy));
   if (is_bf16)
     colsum_kernel<__nv_bfloat16><<<grid, 256, 0, static_cast<cudaStream_t>(s)>>>(
         static_cast<const __nv_bfloat16*>(x), ld, out, rows, cols);
@@ -581,9 +640,30 @@ extern "C" int ttsb200_embed_bwd(const float* g, const int64_t* idx64, const int
                                  int32_t D, int32_t V, ttsb200_stream_t s) {
   TTSB_CHECK_ARG(g && rows > 0 && D == 384 && T > 0, "embed_bwd: bad args (D must be 384)");
   TTSB_CHECK_ARG((pe == nullptr) == (dalpha == nullptr), "embed_bwd: pe and dalpha go together");
-  embed_bwd_kernel<3><<<persistent_grid(rows), kRowThreads, 0, static_cast<cudaStream_t>(s)>>>(
-      g, idx64, idx32, table, skip_idx, pe, dalpha, rows, T, V);
-  TTSB_LAUNCH_CHECK();
+  TTSB_CHECK_ARG(table == nullptr || idx64 || idx32, "embed_bwd: a table needs indices");
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  float* table_generic = table;
+  if (table && V <= 256) {
+    // small vocabulary: shared-memory privatised scatter (one pass over g per table)
+    static bool attr_done = false;
+    if (!attr_done) {
+      TTSB_CHECK_CUDA(cudaFuncSetAttribute(embed_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           256 * 32 * 4));
+      attr_done = true;
+    }
+    int64_t gy = (rows + kRowWarps * 16 - 1) / (kRowWarps * 16);
+    if (gy > 48) gy = 48;
+    if (gy < 1) gy = 1;
+    dim3 grid(D / 32, static_cast<unsigned>(gy));
+    embed_scatter_kernel<<<grid, kRowThreads, V * 32 * sizeof(float), st>>>(g, idx64, idx32, table, skip_idx, rows, D, V);
+    TTSB_LAUNCH_CHECK();
+    table_generic = nullptr;
+  }
+  if (table_generic || dalpha) {
+    embed_bwd_kernel<3><<<persistent_grid(rows), kRowThreads, 0, st>>>(g, idx64, idx32, table_generic, skip_idx, pe,
+                                                                       dalpha, rows, T, V);
+    TTSB_LAUNCH_CHECK();
+  }
   return TTSB_OK;
 }
 

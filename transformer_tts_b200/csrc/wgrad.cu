@@ -38,6 +38,7 @@ struct WgradDev {
   int n_tiles, c_tiles, chunks_per_utt, total_chunks, chunks_per_split;
   float* dw;
   long long sj, sn, sc;  // element strides of dW[j][n][c]
+  int vec_ok;            // dW base and row strides keep 16-byte alignment for v4 reductions
 };
 
 __global__ void __launch_bounds__(kWgThreads, 1)
@@ -138,10 +139,20 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant__ C
         tmem_ld32(tmem_base + lane_off + c, v);
         tmem_ld_wait();
         if (n < p.N) {
+          if (p.sc == 1 && c0 + c + 32 <= p.C && p.vec_ok) {
+            // contiguous x-channels: 16-byte vector reductions (red.global.add.v4.f32, sm_90+)
+            float* dst = base + c0 + c;
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const int cc = c0 + c + i;
-            if (cc < p.C) atomicAdd(base + static_cast<long long>(cc) * p.sc, v[i]);
+            for (int i = 0; i < 32; i += 4)
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + i), "f"(v[i]), "f"(v[i + 1]),
+                           "f"(v[i + 2]), "f"(v[i + 3])
+                           : "memory");
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              const int cc = c0 + c + i;
+              if (cc < p.C) atomicAdd(base + static_cast<long long>(cc) * p.sc, v[i]);
+            }
           }
         }
       }
@@ -192,12 +203,13 @@ extern "C" int ttsb200_conv_wgrad(const void* dy, int64_t ld_dy, const void* x, 
   d.chunks_per_utt = (T + kWgK - 1) / kWgK;
   d.total_chunks = B * d.chunks_per_utt;
   const int tiles = d.n_tiles * d.c_tiles * taps;
-  int splits = (2 * 148 + tiles - 1) / tiles;  // about two waves of CTAs
+  int splits = (148 + tiles / 2) / tiles;  // about one wave of CTAs: every split costs a full tile of reductions
   if (splits > d.total_chunks) splits = d.total_chunks;
   if (splits < 1) splits = 1;
   d.chunks_per_split = (d.total_chunks + splits - 1) / splits;
   splits = (d.total_chunks + d.chunks_per_split - 1) / d.chunks_per_split;
   d.dw = dw; d.sj = stride_tap; d.sn = stride_n; d.sc = stride_c;
+  d.vec_ok = ((reinterpret_cast<uintptr_t>(dw) & 15) == 0 && stride_n % 4 == 0 && stride_tap % 4 == 0) ? 1 : 0;
   dim3 grid(tiles, splits);
   wgrad_kernel<<<grid, kWgThreads, kWgSmem, static_cast<cudaStream_t>(s)>>>(tmDy, tmX, d);
   TTSB_CHECK_CUDA(cudaGetLastError());

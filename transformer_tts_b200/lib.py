@@ -305,13 +305,17 @@ def conv_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, *, taps: int
     _ptr(dy, torch.bfloat16, "dy"); _ptr(x, torch.bfloat16, "x"); _ptr(dw, torch.float32, "dw")
     if dw.numel() != taps * N * Cin:
         raise ValueError(f"conv_wgrad: dw has {dw.numel()} elements, expected {taps}*{N}*{Cin}")
-    if conv_layout:
-        sj, sn, sc = 1, Cin * taps, taps
-    else:
-        sj, sn, sc = N * Cin, Cin, 1
-    _check(load().ttsb200_conv_wgrad(dy.data_ptr() + 2 * n_off, ldy, x.data_ptr(), x.shape[2], dw.data_ptr(), sj, sn,
-                                     sc, B, T, N, Cin, taps, pad_left, _stream()), "conv_wgrad")
+    target = dw
+    if conv_layout and taps > 1:
+        # accumulate tap-major (contiguous x-channels -> 16-byte vector reductions), then one strided add into the
+        # reference's Conv1d (out, in, k) layout
+        target = torch.zeros((taps, N, Cin), device=dw.device, dtype=torch.float32)
+    sj, sn, sc = N * Cin, Cin, 1
+    _check(load().ttsb200_conv_wgrad(dy.data_ptr() + 2 * n_off, ldy, x.data_ptr(), x.shape[2], target.data_ptr(), sj,
+                                     sn, sc, B, T, N, Cin, taps, pad_left, _stream()), "conv_wgrad")
     _count()
+    if target is not dw:
+        dw.view(N, Cin, taps).add_(target.permute(1, 2, 0))
 
 
 def attn_delta(dctx: torch.Tensor, ctx: torch.Tensor, H: int) -> torch.Tensor:
