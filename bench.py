@@ -217,9 +217,14 @@ def kernel_rooflines(model, peaks, tmax):
         ("bucket_embed_add pitch/energy bucketize + embedding add", t_bucket, "hbm", M * D * s2 * 2 + M * 8),
         ("layernorm standalone fp32 -> bf16", t_ln, "hbm", M * D * (4 + s2)),
     ]
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch from ONE `ncu --set full` capture of the same shapes
+    # (profiles/r01_hot_kernels_v5_full_summary.csv, tools/run_hot_kernels.py).  Writes that are still resident in
+    # the 126 MB write-back L2 when the kernel ends are not counted by the DRAM counters.
+    traffic_mb = [55.2 + 109.0, 157.0 + 36.1, 163.4 + 112.9, 56.3 + 162.8, 389.4 + 128.1, 6.3 + 2.4, 55.5 + 7.1,
+                  108.4 + 8.0]
     out = []
     reps = 4
-    for name, fn, bound, work in specs:
+    for (name, fn, bound, work), tr_mb in zip(specs, traffic_mb):
         for i in range(NS):
             fn(i)  # warm-up: first-call attribute setup, allocator pools
         torch.cuda.synchronize()
@@ -245,7 +250,7 @@ def kernel_rooflines(model, peaks, tmax):
         else:
             ach, peak, unit = work / (ms * 1e-3) / 1e9, peaks["hbm"], "GB/s"
         out.append({"kernel": name, "bound": bound, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak,
-                    "traffic": None, "ms_per_launch": ms, "algorithmic_work_per_launch": work,
+                    "traffic": tr_mb * 1e6, "ms_per_launch": ms, "algorithmic_work_per_launch": work,
                     "peak_source": peaks["src"] + (" burst bf16 (kernel timed alone)" if bound == "tensor" else " copy bandwidth")})
     return out
 
