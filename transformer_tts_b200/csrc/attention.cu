@@ -1,18 +1,19 @@
 // Fused masked multi-head self-attention for sm_100a (Models/modules.py:7-21 inside :43-70).
 //
-// One CTA = one (utterance, head, 128-query tile).  Per 128-key tile j:
-//   TMA (SWIZZLE_64B boxes of 32 head-dims x 128 rows) -> smem K, V
-//   tcgen05.mma  S_j = Q K_j^T        (M128 N128 K96, both operands K-major)        -> TMEM cols [0,128)
-//   softmax warps: S_j TMEM -> 128 registers per thread (thread == query row), columns released at once so
-//                  S_{j+1} is computed under the exponentials of tile j; scale, key-padding mask
-//                  (-1e4 like the reference), p = exp2(s - m) with a lazily moved reference point m
-//                  (O and l are rescaled only when the row maximum grew by more than 2^8),
+// One CTA = one (utterance, head, 128-query tile).  Per 64-key tile j:
+//   TMA (SWIZZLE_64B boxes of 32 head-dims x 64 rows) -> smem K (3 stages), V (2 stages)
+//   tcgen05.mma  S_j = Q K_j^T        (M128 N64 K96, both operands K-major)         -> TMEM S buffer j & 1
+//   softmax warps: S_j TMEM -> 64 registers per thread (thread == query row), buffer released at once; scale,
+//                  key-padding mask (-1e4 like the reference), p = exp2(s - m) with a lazily moved reference
+//                  point m (O and l are rescaled only when the row maximum grew by more than 2^8),
 //                  P (bf16) -> smem in the SWIZZLE_128B K-major layout
-//   tcgen05.mma  O += P_j V_j         (M128 N96 K128, V is the MN-major B operand)  -> TMEM cols [128,224)
-// O never leaves TMEM until the final O / l.  Two CTAs fit per SM (107 KB smem, 256 TMEM columns each)
-// so one CTA's softmax overlaps the other's MMAs.  Fully padded key tiles are skipped: with the
-// reference's -1e4 fill their probabilities underflow to exactly 0 in fp32 whenever the utterance has
-// one valid key.  Key tiles inside the all-valid prefix of the mask (kv_info[b][1]) never touch the mask.
+//   tcgen05.mma  O += P_j V_j         (M128 N96 K64, V is the MN-major B operand)   -> TMEM cols [128,224)
+// S is issued up to two tiles ahead, K/V loads up to three/two tiles ahead: no TMA round trip and no
+// TMEM -> register copy sits on the per-tile critical path.  O never leaves TMEM until the final O / l.
+// Two CTAs fit per SM (101 KB smem, 256 TMEM columns each) so one CTA's softmax overlaps the other's MMAs and
+// prologue/epilogue.  Fully padded key tiles are skipped: with the reference's -1e4 fill their probabilities
+// underflow to exactly 0 in fp32 whenever the utterance has one valid key.  Key tiles inside the all-valid
+// prefix of the mask (kv_info[b][1]) never touch the mask.
 #include "common.cuh"
 #include "../../include/ttsb200.h"
 
@@ -20,13 +21,23 @@ namespace ttsb {
 
 constexpr int kDh = 96;
 constexpr int kBQ = 128;
-constexpr int kBKV = 128;
+constexpr int kBKV = 64;                       // keys per tile
 constexpr int kAttThreads = 192;
-constexpr int kBoxBytes = 32 * 2 * 128;       // 32 dims x 128 rows bf16 = 8192
-constexpr int kTileBytes = 3 * kBoxBytes;     // 96 dims
-constexpr int kPBytes = kBQ * kBKV * 2;       // 32768
-constexpr int kAttSmem = 3 * kTileBytes + kPBytes + 1024 /*align*/ + 128 /*barriers*/ + 512 /*flags*/;
-constexpr int kAttTmemCols = 256;
+// A head's 96 dims are fetched as one 64-dim box (128-byte rows, SWIZZLE_128B) and one 32-dim box (64-byte rows,
+// SWIZZLE_64B): the TMA engine is paced by 128-byte lines, and three 64-byte boxes per row made the kernel
+// TMA-bound (19 B/clk/SM, 176 us with the softmax arithmetic removed).
+constexpr int kQBox0 = 128 * kBQ;              // 16 KB
+constexpr int kQBox1 = 64 * kBQ;               // 8 KB
+constexpr int kQBytes = kQBox0 + kQBox1;       // 24 KB
+constexpr int kKVBox0 = 128 * kBKV;            // 8 KB
+constexpr int kKVBox1 = 64 * kBKV;             // 4 KB
+constexpr int kKVBytes = kKVBox0 + kKVBox1;    // 12 KB
+constexpr int kKStages = 2;
+constexpr int kVStages = 2;
+constexpr int kAttSmem = kQBytes + (kKStages + kVStages) * kKVBytes + 1024 /*align*/ + 256 /*barriers*/ +
+                         256 /*flags*/;
+constexpr int kAttTmemCols = 256;              // S0 [0,64) S1 [64,128) O [128,224) P (bf16 pairs) [224,256)
+constexpr int kTmemP = 224;
 constexpr float kLog2e = 1.4426950408889634f;
 
 __device__ __forceinline__ float fast_exp2(float x) {
@@ -35,22 +46,60 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
-enum { BAR_Q = 0, BAR_KF, BAR_KE, BAR_VF, BAR_VE, BAR_SF, BAR_SE, BAR_PF, BAR_OF, BAR_COUNT };
+#if defined(TTSB_ATT_TRACE)
+__device__ long long g_att_trace[8192];
+#define ATT_TR(slot) do { if (tr_on) g_att_trace[tr_n++] = ((long long)(slot) << 56) | (clock64() & 0xFFFFFFFFFFFFFFLL); } while (0)
+#else
+#define ATT_TR(slot) do { } while (0)
+#endif
 
+// 2^x for x <= ~9 on the FMA/ALU pipes: x = n + f, n = round(x), f in [-0.5, 0.5]; 2^f by a degree-4 polynomial,
+// 2^n by adding n to the exponent field.  x is clamped at -126 (the result then flushes towards 2^-126 ~ 0).
+#ifndef TTSB_POLY
+#define TTSB_POLY 0
+#endif
+constexpr int kPolyOf4 = TTSB_POLY;  // elements per group of 4 evaluated by the polynomial instead of MUFU
+__device__ __forceinline__ float poly_exp2(float x) {
+  x = fmaxf(x, -126.f);
+  const float t = x + 12582912.f;          // 1.5 * 2^23: the low mantissa bits of t hold round(x)
+  const float f = x - (t - 12582912.f);
+  float p = fmaf(f, 0.0096181291f, 0.0555041087f);
+  p = fmaf(p, f, 0.2402265070f);
+  p = fmaf(p, f, 0.6931471806f);
+  p = fmaf(p, f, 1.0f);
+  return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
+}
+
+enum {
+  BAR_Q = 0,
+  BAR_KF,                       // [3] K stage filled
+  BAR_KE = BAR_KF + kKStages,   // [3] K stage consumed
+  BAR_VF = BAR_KE + kKStages,   // [2]
+  BAR_VE = BAR_VF + kVStages,   // [2]
+  BAR_SF = BAR_VE + kVStages,   // [2] S buffer written by the tensor core
+  BAR_SE = BAR_SF + 2,          // [2] S buffer read by the softmax warps
+  BAR_PF = BAR_SE + 2,          // P_j written to TMEM
+  BAR_OF,                       // P_j V_j retired (P columns reusable, O current)
+  BAR_COUNT
+};
+
+// v3: 64-key tiles, K triple- and V double-buffered in smem, S double-buffered in TMEM, so that neither a TMA
+// round trip nor the S -> registers copy sits on the per-tile critical path (v2 had single K/V buffers: its
+// per-tile time was 181 us of 226 us with the softmax arithmetic removed).
 __global__ void __launch_bounds__(kAttThreads, 2)
-attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const uint8_t* __restrict__ mask,
-                     const int32_t* __restrict__ kv_info, __nv_bfloat16* __restrict__ ctx,
-                     float* __restrict__ lse2, int T, int H, float scale_log2) {
+attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmQ32,
+                     const __grid_constant__ CUtensorMap tmKV, const __grid_constant__ CUtensorMap tmKV32,
+                     const uint8_t* __restrict__ mask, const int32_t* __restrict__ kv_info,
+                     __nv_bfloat16* __restrict__ ctx, float* __restrict__ lse2, int T, int H, float scale_log2) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
   uint8_t* sQ = smem;
-  uint8_t* sK = sQ + kTileBytes;
-  uint8_t* sV = sK + kTileBytes;
-  uint8_t* sP = sV + kTileBytes;  // offset 73728 = 72 * 1024
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + kPBytes);
+  uint8_t* sK = sQ + kQBytes;                   // [3] x 12 KB (each 1024-aligned: 12 KB = 12 * 1024)
+  uint8_t* sV = sK + kKStages * kKVBytes;       // [2] x 12 KB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + kVStages * kKVBytes);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + BAR_COUNT);
-  uint8_t* sflag = reinterpret_cast<uint8_t*>(tmem_slot + 4);  // [2][128] key flags of a tile outside the clean prefix
+  uint8_t* sflag = reinterpret_cast<uint8_t*>(tmem_slot + 4);  // [2][64] key flags of a tile outside the clean prefix
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -63,10 +112,38 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const uint8_t* _
   const int kv_eff = klen > 0 ? klen : T;   // no valid key: the reference degenerates to uniform over T
   const int nkv = (kv_eff + kBKV - 1) / kBKV;
 
+  auto load_k = [&](int j) {
+    const int ks = j % kKStages;
+    const uint32_t kf = smem_u32(&bars[BAR_KF + ks]);
+    mbar_arrive_expect_tx(kf, kKVBytes);
+    tma_load_3d(smem_u32(sK + ks * kKVBytes), &tmKV, kf, D + h * kDh, j * kBKV, b);
+    tma_load_3d(smem_u32(sK + ks * kKVBytes + kKVBox0), &tmKV32, kf, D + h * kDh + 64, j * kBKV, b);
+  };
+  auto load_v = [&](int j) {
+    const int vs = j % kVStages;
+    const uint32_t vf = smem_u32(&bars[BAR_VF + vs]);
+    mbar_arrive_expect_tx(vf, kKVBytes);
+    tma_load_3d(smem_u32(sV + vs * kKVBytes), &tmKV, vf, 2 * D + h * kDh, j * kBKV, b);
+    tma_load_3d(smem_u32(sV + vs * kKVBytes + kKVBox0), &tmKV32, vf, 2 * D + h * kDh + 64, j * kBKV, b);
+  };
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmQKV);
-    for (int i = 0; i < BAR_COUNT; ++i) mbar_init(smem_u32(&bars[i]), (i == BAR_PF || i == BAR_SE) ? 128 : 1);
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmQ32);
+    tma_prefetch_desc(&tmKV);
+    tma_prefetch_desc(&tmKV32);
+    for (int i = 0; i < BAR_COUNT; ++i)
+      mbar_init(smem_u32(&bars[i]), (i == BAR_SE || i == BAR_SE + 1 || i == BAR_PF) ? 128 : 1);
     fence_mbar_init();
+    // the first loads go out before the TMEM allocation and the CTA-wide sync: only this thread touches these
+    // barriers until then
+    const uint32_t qb = smem_u32(&bars[BAR_Q]);
+    mbar_arrive_expect_tx(qb, kQBytes);
+    tma_load_3d(smem_u32(sQ), &tmQ, qb, h * kDh, q0, b);
+    tma_load_3d(smem_u32(sQ + kQBox0), &tmQ32, qb, h * kDh + 64, q0, b);
+    load_k(0);
+    if (nkv > 1) load_k(1);
+    load_v(0);
+    if (nkv > 1) load_v(1);
   }
   if (warp == 1) {
     tmem_alloc(smem_u32(tmem_slot), kAttTmemCols);
@@ -76,71 +153,82 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const uint8_t* _
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tmem_S = tmem_base;
   const uint32_t tmem_O = tmem_base + 128;
 
   if (warp == 0) {
     if (lane == 0) {
-      const uint32_t qb = smem_u32(&bars[BAR_Q]);
-      mbar_arrive_expect_tx(qb, kTileBytes);
-#pragma unroll
-      for (int i = 0; i < 3; ++i) tma_load_3d(smem_u32(sQ + i * kBoxBytes), &tmQKV, qb, h * kDh + i * 32, q0, b);
-      for (int j = 0; j < nkv; ++j) {
-        const uint32_t ph = j & 1;
-        mbar_wait(smem_u32(&bars[BAR_KE]), ph ^ 1);
-        const uint32_t kf = smem_u32(&bars[BAR_KF]);
-        mbar_arrive_expect_tx(kf, kTileBytes);
-#pragma unroll
-        for (int i = 0; i < 3; ++i)
-          tma_load_3d(smem_u32(sK + i * kBoxBytes), &tmQKV, kf, D + h * kDh + i * 32, j * kBKV, b);
-        mbar_wait(smem_u32(&bars[BAR_VE]), ph ^ 1);
-        const uint32_t vf = smem_u32(&bars[BAR_VF]);
-        mbar_arrive_expect_tx(vf, kTileBytes);
-#pragma unroll
-        for (int i = 0; i < 3; ++i)
-          tma_load_3d(smem_u32(sV + i * kBoxBytes), &tmQKV, vf, 2 * D + h * kDh + i * 32, j * kBKV, b);
+      // V_i reuses the stage of V_{i-2} once P V_{i-2} has retired; K_{i+2} the stage of K_i once S_i has (S_i is
+      // issued right behind P V_{i-2}), so both loads run two tiles ahead of their consumers
+      for (int i = 0; i < nkv; ++i) {
+        if (i >= 2) {
+          mbar_wait(smem_u32(&bars[BAR_VE + (i & 1)]), ((i >> 1) - 1) & 1);
+          load_v(i);
+        }
+        if (i + 2 < nkv) {
+          mbar_wait(smem_u32(&bars[BAR_KE + (i & 1)]), (i >> 1) & 1);
+          load_k(i + 2);
+        }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc_s = umma_idesc_bf16(kBQ, kBKV, 0, 0);
-      constexpr uint32_t idesc_o = umma_idesc_bf16(kBQ, kDh, 0, 1);  // B = V is MN-major
-      const uint32_t q_base = smem_u32(sQ), k_base = smem_u32(sK), v_base = smem_u32(sV),
-                     p_base = smem_u32(sP);
-      // S_j = Q K_j^T is issued one tile AHEAD of O += P_j V_j: the softmax warps copy S_j into
-      // registers and release the TMEM columns at once, so S_{j+1} runs under the exponentials of tile j.
-      auto issue_s = [&](int j) {
-        mbar_wait(smem_u32(&bars[BAR_KF]), j & 1);
-        if (j > 0) mbar_wait(smem_u32(&bars[BAR_SE]), (j - 1) & 1);
-        tc_fence_after();
+    // ===================== MMA issuer =====================
+    // The WHOLE warp runs this loop converged (waits included) and only the tcgen05 instructions are predicated on
+    // one elected lane: every operand is then warp-uniform and lives in uniform registers.  Under `if (lane == 0)`
+    // the compiler wraps each UTCHMMA in an ELECT / R2UR.BROADCAST / BRA.U.ANY waterfall loop (~100 clk per MMA),
+    // which made this single thread the bottleneck of the kernel (2500 clk per 64-key tile).
+    constexpr uint32_t idesc_s = umma_idesc_bf16(kBQ, kBKV, 0, 0);
+    constexpr uint32_t idesc_o64 = umma_idesc_bf16(kBQ, 64, 0, 1);  // B = V is MN-major: dims [0,64) ...
+    constexpr uint32_t idesc_o32 = umma_idesc_bf16(kBQ, 32, 0, 1);  // ... and dims [64,96)
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t q_base = smem_u32(sQ);
+    const uint32_t leader = elect_one();
+    // S_j = Q K_j^T goes to S buffer j & 1 and is issued up to two tiles ahead of O += P_j V_j
+    auto issue_s = [&](int j) {
+      const int ks = j % kKStages;
+      mbar_wait(smem_u32(&bars[BAR_KF + ks]), (j / kKStages) & 1);
+      if (j >= 2) mbar_wait(smem_u32(&bars[BAR_SE + (j & 1)]), ((j >> 1) - 1) & 1);
+      tc_fence_after();
+      const uint32_t k_base = smem_u32(sK + ks * kKVBytes);
+      const uint32_t d_tmem = tb + (j & 1) * kBKV;
+      if (leader) {
 #pragma unroll
-        for (int ks = 0; ks < kDh / 16; ++ks) {
-          const uint32_t off = (ks >> 1) * kBoxBytes + (ks & 1) * 32;
-          umma_bf16(tmem_S, umma_smem_desc(q_base + off, 16, 512, kLayoutSW64),
-                    umma_smem_desc(k_base + off, 16, 512, kLayoutSW64), idesc_s, ks != 0);
-        }
-        umma_commit(smem_u32(&bars[BAR_KE]));
-        umma_commit(smem_u32(&bars[BAR_SF]));
-      };
-      mbar_wait(smem_u32(&bars[BAR_Q]), 0);
-      issue_s(0);
-      for (int j = 0; j < nkv; ++j) {
-        const uint32_t ph = j & 1;
-        if (j + 1 < nkv) issue_s(j + 1);
-        // ---- O += P_j V_j ----
-        mbar_wait(smem_u32(&bars[BAR_PF]), ph);
-        mbar_wait(smem_u32(&bars[BAR_VF]), ph);
-        tc_fence_after();
+        for (int kk = 0; kk < 4; ++kk)  // dims [0,64): 128-byte rows
+          umma_bf16(d_tmem, umma_smem_desc(q_base + kk * 32, 16, 1024, kLayoutSW128),
+                    umma_smem_desc(k_base + kk * 32, 16, 1024, kLayoutSW128), idesc_s, kk != 0);
 #pragma unroll
-        for (int ks = 0; ks < kBKV / 16; ++ks) {
-          const uint64_t adesc =
-              umma_smem_desc(p_base + (ks >> 2) * (kBQ * 128) + (ks & 3) * 32, 16, 1024, kLayoutSW128);
-          const uint64_t bdesc = umma_smem_desc(v_base + ks * 1024, kBoxBytes, 512, kLayoutSW64);
-          umma_bf16(tmem_O, adesc, bdesc, idesc_o, (j | ks) != 0);
+        for (int kk = 0; kk < 2; ++kk)  // dims [64,96): 64-byte rows
+          umma_bf16(d_tmem, umma_smem_desc(q_base + kQBox0 + kk * 32, 16, 512, kLayoutSW64),
+                    umma_smem_desc(k_base + kKVBox0 + kk * 32, 16, 512, kLayoutSW64), idesc_s, 1u);
+        umma_commit(smem_u32(&bars[BAR_KE + ks]));
+        umma_commit(smem_u32(&bars[BAR_SF + (j & 1)]));
+      }
+      __syncwarp();
+    };
+    mbar_wait(smem_u32(&bars[BAR_Q]), 0);
+    issue_s(0);
+    if (nkv > 1) issue_s(1);
+    for (int j = 0; j < nkv; ++j) {
+      const int vs = j % kVStages;
+      mbar_wait(smem_u32(&bars[BAR_PF]), j & 1);
+      mbar_wait(smem_u32(&bars[BAR_VF + vs]), (j / kVStages) & 1);
+      tc_fence_after();
+      const uint32_t v_base = smem_u32(sV + vs * kKVBytes);
+      if (leader) {
+#pragma unroll
+        for (int kk = 0; kk < kBKV / 16; ++kk) {
+          // A = P read from TMEM (16 keys = 8 packed columns per MMA), never through shared memory;
+          // B = V: 16 rows of 128 B (box 0) / of 64 B (box 1); SBO = 8 rows
+          const uint32_t a_tmem = tb + kTmemP + kk * 8;
+          umma_bf16_ts(tb + 128, a_tmem, umma_smem_desc(v_base + kk * 2048, kKVBox0, 1024, kLayoutSW128), idesc_o64,
+                       (j | kk) != 0);
+          umma_bf16_ts(tb + 128 + 64, a_tmem, umma_smem_desc(v_base + kKVBox0 + kk * 1024, kKVBox1, 512, kLayoutSW64),
+                       idesc_o32, (j | kk) != 0);
         }
-        umma_commit(smem_u32(&bars[BAR_VE]));
+        umma_commit(smem_u32(&bars[BAR_VE + vs]));
         umma_commit(smem_u32(&bars[BAR_OF]));
       }
+      __syncwarp();
+      if (j + 2 < nkv) issue_s(j + 2);
     }
   } else {
     // ===================== softmax / output warps: thread == query row =====================
@@ -153,26 +241,35 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const uint8_t* _
     // moved (and O, l rescaled) when the maximum has grown by more than 2^8, so p <= 256 stays well
     // inside bf16/fp32 range and the final O / l is unchanged.
     float m = -INFINITY, l = 0.f;
-    uint8_t* prow = sP + row * 128;
+#if defined(TTSB_ATT_TRACE)
+    const bool tr_on = TTSB_ATT_TRACE == 1 && blockIdx.x == 4 && blockIdx.y == 1 && blockIdx.z == 10 && threadIdx.x == 64;
+    int tr_n = 0;
+#endif
+    ATT_TR(0);
 
     for (int j = 0; j < nkv; ++j) {
-      const uint32_t ph = j & 1;
+      const uint32_t sb = j & 1;
       // a tile inside the all-valid prefix of the mask needs no flags (CTA-uniform decision)
       const bool clean = (j + 1) * kBKV <= kprefix;
-      uint8_t* flg = sflag + ph * 128;
+      uint8_t* flg = sflag + sb * kBKV;
       if (!clean) {
-        const int key = j * kBKV + st;
-        flg[st] = key < T ? (mask[static_cast<int64_t>(b) * T + key] ? 1 : 0) : 2;
+        if (st < kBKV) {
+          const int key = j * kBKV + st;
+          flg[st] = key < T ? (mask[static_cast<int64_t>(b) * T + key] ? 1 : 0) : 2;
+        }
         asm volatile("bar.sync 1, 128;" ::: "memory");
       }
-      mbar_wait(smem_u32(&bars[BAR_SF]), ph);
+      ATT_TR(1);
+      mbar_wait(smem_u32(&bars[BAR_SF + sb]), (j >> 1) & 1);
       tc_fence_after();
+      ATT_TR(2);
       float s[kBKV];
 #pragma unroll
-      for (int c = 0; c < kBKV; c += 32) tmem_ld32(tmem_S + lane_off + c, s + c);
+      for (int c = 0; c < kBKV; c += 32) tmem_ld32(tmem_base + sb * kBKV + lane_off + c, s + c);
       tmem_ld_wait();
       tc_fence_before();
-      mbar_arrive(smem_u32(&bars[BAR_SE]));  // S columns may be overwritten by the next QK^T
+      mbar_arrive(smem_u32(&bars[BAR_SE + sb]));  // this S buffer may be overwritten by Q K_{j+2}^T
+      ATT_TR(3);
       // scores in log2 units, masked like the reference (-1e4 fill; keys beyond T do not exist)
       float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
       if (clean) {
@@ -191,14 +288,16 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const uint8_t* _
       }
       float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       if (clean) mx *= scale_log2;  // the positive scale commutes with max
-      // P_{j-1} V_{j-1} must have retired before sP is overwritten (and before O is rescaled)
+      ATT_TR(4);
+      // P_{j-1} V_{j-1} must have retired before the P columns are overwritten (and before O is rescaled)
       if (j > 0) {
         mbar_wait(smem_u32(&bars[BAR_OF]), (j - 1) & 1);
         tc_fence_after();
       }
+      ATT_TR(5);
       const bool grow = mx > m + 8.f;  // also true on the first tile (m = -inf)
       if (__any_sync(0xffffffffu, grow)) {
-        const float m_new = fmaxf(m, mx);
+        const float m_new = grow ? mx : m;  // rows that did not grow keep their reference point (alpha = 1)
         const float alpha = fast_exp2(m - m_new);  // m = -inf -> 0
         l *= alpha;
         m = m_new;
@@ -219,30 +318,40 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const uint8_t* _
       float ls4[4] = {0.f, 0.f, 0.f, 0.f};
       const float neg_m = -m;
       const float sc = clean ? scale_log2 : 1.f;  // masked tiles were scaled while masking
+#if defined(TTSB_ATT_EXP) && TTSB_ATT_EXP >= 2
+      ls4[0] = s[0] + s[37] + s[59] + neg_m * sc;  // timing experiment only: no exponentials, no P stores
+      for (int c = 0; c < 0; c += 32) {
+#else
 #pragma unroll
       for (int c = 0; c < kBKV; c += 32) {
+#endif
         float* v = s + c;
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          v[i] = fast_exp2(fmaf(v[i], sc, neg_m));
+#if defined(TTSB_ATT_EXP) && TTSB_ATT_EXP >= 1
+          v[i] = fmaf(v[i], sc, neg_m);  // timing experiment only: no exponential
+#else
+          // MUFU.EX2 runs at 16/clk/SM and bounds this loop: every other pair of elements is evaluated on the FMA
+          // pipe instead (round-to-nearest split + degree-4 polynomial, relative error 4e-5 << bf16's 2^-9)
+          if ((i & 3) < kPolyOf4) v[i] = poly_exp2(fmaf(v[i], sc, neg_m));
+          else v[i] = fast_exp2(fmaf(v[i], sc, neg_m));
+#endif
           ls4[i & 3] += v[i];
         }
-        uint8_t* pblk = prow + (c >> 6) * (kBQ * 128);
+      }
+      // P (bf16 pairs, key 2c in the low half of column c) -> this thread's TMEM lane: the A operand of P V
+      {
+        uint32_t pk[kBKV / 2];
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          const int ch = ((c & 63) >> 3) + g;  // 16-byte chunk index inside the 128-byte row
-          uint4 u;
-          u.x = pack_bf16(v[g * 8 + 0], v[g * 8 + 1]);
-          u.y = pack_bf16(v[g * 8 + 2], v[g * 8 + 3]);
-          u.z = pack_bf16(v[g * 8 + 4], v[g * 8 + 5]);
-          u.w = pack_bf16(v[g * 8 + 6], v[g * 8 + 7]);
-          *reinterpret_cast<uint4*>(pblk + ((ch ^ (row & 7)) << 4)) = u;
-        }
+        for (int i = 0; i < kBKV / 2; ++i) pk[i] = pack_bf16(s[2 * i], s[2 * i + 1]);
+        tmem_st32(tmem_base + kTmemP + lane_off, reinterpret_cast<const float*>(pk));
+        tmem_st_wait();
       }
       l += (ls4[0] + ls4[1]) + (ls4[2] + ls4[3]);
-      fence_async_smem();  // generic-proxy smem writes -> visible to the tensor core (async proxy)
-      tc_fence_before();   // orders the O rescale (tcgen05.st) before the MMA that accumulates into O
+      ATT_TR(6);
+      tc_fence_before();   // orders the P store and the O rescale (tcgen05.st) before the MMA
       mbar_arrive(smem_u32(&bars[BAR_PF]));
+      ATT_TR(7);
     }
     // ---- O / l ----
     mbar_wait(smem_u32(&bars[BAR_OF]), (nkv - 1) & 1);
@@ -270,6 +379,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const uint8_t* _
       }
     }
     tc_fence_before();
+    ATT_TR(8);
   }
 
   tc_fence_before();
@@ -334,12 +444,19 @@ extern "C" int ttsb200_attention_fwd_lse(const void* qkv, const uint8_t* mask, c
   TTSB_CHECK_ARG(Dh == kDh, "attention_fwd: head dim %d unsupported (this build: %d)", Dh, kDh);
   TTSB_CHECK_ARG((reinterpret_cast<uintptr_t>(qkv) & 15) == 0 && (reinterpret_cast<uintptr_t>(ctx) & 15) == 0,
                  "attention_fwd: qkv/ctx must be 16-byte aligned");
-  CUtensorMap tm;
+  CUtensorMap tmQ, tmQ32, tmKV, tmKV32;
   const uint64_t ld = 3ull * H * Dh;
   const uint64_t dims[3] = {ld, static_cast<uint64_t>(T), static_cast<uint64_t>(B)};
   const uint64_t strides[2] = {ld * 2, ld * 2 * static_cast<uint64_t>(T)};
-  const uint32_t box[3] = {32, 128, 1};
-  int rc = make_tmap_bf16(&tm, qkv, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_64B);
+  const uint32_t box_q[3] = {64, kBQ, 1}, box_q32[3] = {32, kBQ, 1};
+  const uint32_t box_kv[3] = {64, kBKV, 1}, box_kv32[3] = {32, kBKV, 1};
+  int rc = make_tmap_bf16(&tmQ, qkv, 3, dims, strides, box_q, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc) return rc;
+  rc = make_tmap_bf16(&tmQ32, qkv, 3, dims, strides, box_q32, CU_TENSOR_MAP_SWIZZLE_64B);
+  if (rc) return rc;
+  rc = make_tmap_bf16(&tmKV, qkv, 3, dims, strides, box_kv, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc) return rc;
+  rc = make_tmap_bf16(&tmKV32, qkv, 3, dims, strides, box_kv32, CU_TENSOR_MAP_SWIZZLE_64B);
   if (rc) return rc;
   static bool attr_done = false;
   if (!attr_done) {
@@ -350,10 +467,16 @@ extern "C" int ttsb200_attention_fwd_lse(const void* qkv, const uint8_t* mask, c
   dim3 grid((T + kBQ - 1) / kBQ, H, B);
   const float scale_log2 = kLog2e / sqrtf(static_cast<float>(Dh));
   attention_fwd_kernel<<<grid, kAttThreads, kAttSmem, static_cast<cudaStream_t>(s)>>>(
-      tm, mask, kv_info, static_cast<__nv_bfloat16*>(ctx), lse2, T, H, scale_log2);
+      tmQ, tmQ32, tmKV, tmKV32, mask, kv_info, static_cast<__nv_bfloat16*>(ctx), lse2, T, H, scale_log2);
   TTSB_CHECK_CUDA(cudaGetLastError());
   return TTSB_OK;
 }
+
+#if defined(TTSB_ATT_TRACE)
+extern "C" int ttsb200_debug_att_trace(long long* dst, int n) {
+  return cudaMemcpyFromSymbol(dst, g_att_trace, n * sizeof(long long)) == cudaSuccess ? 0 : -1;
+}
+#endif
 
 extern "C" int ttsb200_attention_fwd(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
                                      int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t s) {
