@@ -8,7 +8,7 @@ mask = (torch.arange(T)[None, :] < lens[:, None]).to(torch.uint8).cuda()
 from transformer_tts_b200 import lib as L
 kv = L.mask_lengths(mask)
 ctx = torch.empty(B, T, H * Dh, dtype=torch.bfloat16, device='cuda')
-lib = C.CDLL("tools/exp/libatt_tr.so")
+lib = C.CDLL("tools/exp/libatt_tr" + (sys.argv[2] if len(sys.argv) > 2 else "1") + ".so")
 fn = lib.ttsb200_attention_fwd
 fn.argtypes = [C.c_void_p] * 4 + [C.c_int32] * 4 + [C.c_void_p]
 st = torch.cuda.current_stream().cuda_stream

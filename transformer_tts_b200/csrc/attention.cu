@@ -36,8 +36,8 @@ constexpr int kKStages = 2;
 constexpr int kVStages = 2;
 constexpr int kAttSmem = kQBytes + (kKStages + kVStages) * kKVBytes + 1024 /*align*/ + 256 /*barriers*/ +
                          256 /*flags*/;
-constexpr int kAttTmemCols = 256;              // S0 [0,64) S1 [64,128) O [128,224) P (bf16 pairs) [224,256)
-constexpr int kTmemP = 224;
+constexpr int kAttTmemCols = 256;              // S0 [0,64) S1 [64,128) O [128,224); P_j (bf16 pairs) overwrites the
+                                               // first 32 columns of its own S buffer once S_j sits in registers
 constexpr float kLog2e = 1.4426950408889634f;
 
 __device__ __forceinline__ float fast_exp2(float x) {
@@ -77,10 +77,9 @@ enum {
   BAR_VF = BAR_KE + kKStages,   // [2]
   BAR_VE = BAR_VF + kVStages,   // [2]
   BAR_SF = BAR_VE + kVStages,   // [2] S buffer written by the tensor core
-  BAR_SE = BAR_SF + 2,          // [2] S buffer read by the softmax warps
-  BAR_PF = BAR_SE + 2,          // P_j written to TMEM
-  BAR_OF,                       // P_j V_j retired (P columns reusable, O current)
-  BAR_COUNT
+  BAR_PF = BAR_SF + 2,          // [2] P_j written over S buffer j & 1
+  BAR_OF = BAR_PF + 2,          // [2] P_j V_j retired (S/P buffer j & 1 reusable, O current)
+  BAR_COUNT = BAR_OF + 2
 };
 
 // v3: 64-key tiles, K triple- and V double-buffered in smem, S double-buffered in TMEM, so that neither a TMA
@@ -132,7 +131,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     tma_prefetch_desc(&tmKV);
     tma_prefetch_desc(&tmKV32);
     for (int i = 0; i < BAR_COUNT; ++i)
-      mbar_init(smem_u32(&bars[i]), (i == BAR_SE || i == BAR_SE + 1 || i == BAR_PF) ? 128 : 1);
+      mbar_init(smem_u32(&bars[i]), (i == BAR_PF || i == BAR_PF + 1) ? 128 : 1);
     fence_mbar_init();
     // the first loads go out before the TMEM allocation and the CTA-wide sync: only this thread touches these
     // barriers until then
@@ -186,7 +185,8 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     auto issue_s = [&](int j) {
       const int ks = j % kKStages;
       mbar_wait(smem_u32(&bars[BAR_KF + ks]), (j / kKStages) & 1);
-      if (j >= 2) mbar_wait(smem_u32(&bars[BAR_SE + (j & 1)]), ((j >> 1) - 1) & 1);
+      // S buffer j & 1 last held P_{j-2}: P_{j-2} V_{j-2} was issued by this warp before this MMA and the tensor
+      // pipe executes one thread's MMAs in issue order, so the overwrite needs no barrier
       tc_fence_after();
       const uint32_t k_base = smem_u32(sK + ks * kKVBytes);
       const uint32_t d_tmem = tb + (j & 1) * kBKV;
@@ -209,7 +209,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     if (nkv > 1) issue_s(1);
     for (int j = 0; j < nkv; ++j) {
       const int vs = j % kVStages;
-      mbar_wait(smem_u32(&bars[BAR_PF]), j & 1);
+      mbar_wait(smem_u32(&bars[BAR_PF + (j & 1)]), (j >> 1) & 1);
       mbar_wait(smem_u32(&bars[BAR_VF + vs]), (j / kVStages) & 1);
       tc_fence_after();
       const uint32_t v_base = smem_u32(sV + vs * kKVBytes);
@@ -218,14 +218,14 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         for (int kk = 0; kk < kBKV / 16; ++kk) {
           // A = P read from TMEM (16 keys = 8 packed columns per MMA), never through shared memory;
           // B = V: 16 rows of 128 B (box 0) / of 64 B (box 1); SBO = 8 rows
-          const uint32_t a_tmem = tb + kTmemP + kk * 8;
+          const uint32_t a_tmem = tb + (j & 1) * kBKV + kk * 8;
           umma_bf16_ts(tb + 128, a_tmem, umma_smem_desc(v_base + kk * 2048, kKVBox0, 1024, kLayoutSW128), idesc_o64,
                        (j | kk) != 0);
           umma_bf16_ts(tb + 128 + 64, a_tmem, umma_smem_desc(v_base + kKVBox0 + kk * 1024, kKVBox1, 512, kLayoutSW64),
                        idesc_o32, (j | kk) != 0);
         }
         umma_commit(smem_u32(&bars[BAR_VE + vs]));
-        umma_commit(smem_u32(&bars[BAR_OF]));
+        umma_commit(smem_u32(&bars[BAR_OF + (j & 1)]));
       }
       __syncwarp();
       if (j + 2 < nkv) issue_s(j + 2);
@@ -267,8 +267,6 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
 #pragma unroll
       for (int c = 0; c < kBKV; c += 32) tmem_ld32(tmem_base + sb * kBKV + lane_off + c, s + c);
       tmem_ld_wait();
-      tc_fence_before();
-      mbar_arrive(smem_u32(&bars[BAR_SE + sb]));  // this S buffer may be overwritten by Q K_{j+2}^T
       ATT_TR(3);
       // scores in log2 units, masked like the reference (-1e4 fill; keys beyond T do not exist)
       float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
@@ -289,14 +287,14 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       if (clean) mx *= scale_log2;  // the positive scale commutes with max
       ATT_TR(4);
-      // P_{j-1} V_{j-1} must have retired before the P columns are overwritten (and before O is rescaled)
-      if (j > 0) {
-        mbar_wait(smem_u32(&bars[BAR_OF]), (j - 1) & 1);
-        tc_fence_after();
-      }
       ATT_TR(5);
       const bool grow = mx > m + 8.f;  // also true on the first tile (m = -inf)
       if (__any_sync(0xffffffffu, grow)) {
+        // the (rare) rescale of O needs P_{j-1} V_{j-1} retired
+        if (j > 0) {
+          mbar_wait(smem_u32(&bars[BAR_OF + (sb ^ 1)]), ((j - 1) >> 1) & 1);
+          tc_fence_after();
+        }
         const float m_new = grow ? mx : m;  // rows that did not grow keep their reference point (alpha = 1)
         const float alpha = fast_exp2(m - m_new);  // m = -inf -> 0
         l *= alpha;
@@ -344,17 +342,17 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         uint32_t pk[kBKV / 2];
 #pragma unroll
         for (int i = 0; i < kBKV / 2; ++i) pk[i] = pack_bf16(s[2 * i], s[2 * i + 1]);
-        tmem_st32(tmem_base + kTmemP + lane_off, reinterpret_cast<const float*>(pk));
+        tmem_st32(tmem_base + sb * kBKV + lane_off, reinterpret_cast<const float*>(pk));
         tmem_st_wait();
       }
       l += (ls4[0] + ls4[1]) + (ls4[2] + ls4[3]);
       ATT_TR(6);
       tc_fence_before();   // orders the P store and the O rescale (tcgen05.st) before the MMA
-      mbar_arrive(smem_u32(&bars[BAR_PF]));
+      mbar_arrive(smem_u32(&bars[BAR_PF + sb]));
       ATT_TR(7);
     }
     // ---- O / l ----
-    mbar_wait(smem_u32(&bars[BAR_OF]), (nkv - 1) & 1);
+    mbar_wait(smem_u32(&bars[BAR_OF + ((nkv - 1) & 1)]), ((nkv - 1) >> 1) & 1);
     tc_fence_after();
     const int t = q0 + row;
     const float inv = 1.f / l;
