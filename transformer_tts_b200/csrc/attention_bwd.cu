@@ -157,49 +157,58 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc_s = umma_idesc_bf16(kBQ, kBKV, 0, 0);
-      constexpr uint32_t idesc_t = umma_idesc_bf16(kBKV, kDh, 1, 1);  // A = P^T / dS^T (MN-major), B = dO / Q (MN-major)
-      const uint32_t k_base = smem_u32(sK), v_base = smem_u32(sV), p_base = smem_u32(sP), ds_base = smem_u32(sDS);
-      mbar_wait(smem_u32(&bars[D_KV]), 0);
-      for (int i = 0; i < nq; ++i) {
-        const int buf = i & 1;
-        const uint32_t q_base = smem_u32(sQ + buf * kTileBytes), do_base = smem_u32(sDO + buf * kTileBytes);
-        mbar_wait(smem_u32(&bars[D_QF0 + buf]), (i >> 1) & 1);
-        tc_fence_after();
-        // S = Q K^T, dP = dO V^T  (the softmax warps released these columns with PF of the previous tile)
+    // whole warp converged, tcgen05 instructions predicated on one elected lane: operands stay in uniform registers
+    // (under `if (lane == 0)` every UTCHMMA is wrapped in an ELECT / BRA.U.ANY waterfall loop)
+    constexpr uint32_t idesc_s = umma_idesc_bf16(kBQ, kBKV, 0, 0);
+    constexpr uint32_t idesc_t = umma_idesc_bf16(kBKV, kDh, 1, 1);  // A = P^T / dS^T (MN-major), B = dO / Q (MN-major)
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t k_base = smem_u32(sK), v_base = smem_u32(sV), p_base = smem_u32(sP), ds_base = smem_u32(sDS);
+    const uint32_t leader = elect_one();
+    mbar_wait(smem_u32(&bars[D_KV]), 0);
+    for (int i = 0; i < nq; ++i) {
+      const int buf = i & 1;
+      const uint32_t q_base = smem_u32(sQ + buf * kTileBytes), do_base = smem_u32(sDO + buf * kTileBytes);
+      mbar_wait(smem_u32(&bars[D_QF0 + buf]), (i >> 1) & 1);
+      tc_fence_after();
+      // S = Q K^T, dP = dO V^T  (the softmax warps released these columns with PF of the previous tile)
+      if (leader) {
 #pragma unroll
         for (int ks = 0; ks < kDh / 16; ++ks) {
           const uint32_t off = (ks >> 1) * kBoxBytes + (ks & 1) * 32;
-          umma_bf16(tmem_S, umma_smem_desc(q_base + off, 16, 512, kLayoutSW64),
+          umma_bf16(tb, umma_smem_desc(q_base + off, 16, 512, kLayoutSW64),
                     umma_smem_desc(k_base + off, 16, 512, kLayoutSW64), idesc_s, ks != 0);
         }
 #pragma unroll
         for (int ks = 0; ks < kDh / 16; ++ks) {
           const uint32_t off = (ks >> 1) * kBoxBytes + (ks & 1) * 32;
-          umma_bf16(tmem_dP, umma_smem_desc(do_base + off, 16, 512, kLayoutSW64),
+          umma_bf16(tb + 128, umma_smem_desc(do_base + off, 16, 512, kLayoutSW64),
                     umma_smem_desc(v_base + off, 16, 512, kLayoutSW64), idesc_s, ks != 0);
         }
         umma_commit(smem_u32(&bars[D_SF]));
-        mbar_wait(smem_u32(&bars[D_PF]), i & 1);
-        tc_fence_after();
-        // dV += P^T dO ; dK += dS^T Q   (reduction over the 128 queries, 16 per MMA)
+      }
+      __syncwarp();
+      mbar_wait(smem_u32(&bars[D_PF]), i & 1);
+      tc_fence_after();
+      // dV += P^T dO ; dK += dS^T Q   (reduction over the 128 queries, 16 per MMA)
+      if (leader) {
 #pragma unroll
         for (int ks = 0; ks < kBQ / 16; ++ks) {
           const uint64_t a_p = umma_smem_desc(p_base + ks * 2048, kBQ * 128, 1024, kLayoutSW128);
           const uint64_t b_do = umma_smem_desc(do_base + ks * 1024, kBoxBytes, 512, kLayoutSW64);
-          umma_bf16(tmem_dV, a_p, b_do, idesc_t, (i | ks) != 0);
+          umma_bf16(tb + 256, a_p, b_do, idesc_t, (i | ks) != 0);
         }
 #pragma unroll
         for (int ks = 0; ks < kBQ / 16; ++ks) {
           const uint64_t a_ds = umma_smem_desc(ds_base + ks * 2048, kBQ * 128, 1024, kLayoutSW128);
           const uint64_t b_q = umma_smem_desc(q_base + ks * 1024, kBoxBytes, 512, kLayoutSW64);
-          umma_bf16(tmem_dK, a_ds, b_q, idesc_t, (i | ks) != 0);
+          umma_bf16(tb + 384, a_ds, b_q, idesc_t, (i | ks) != 0);
         }
         umma_commit(smem_u32(&bars[D_QE0 + buf]));
       }
-      umma_commit(smem_u32(&bars[D_DONE]));
+      __syncwarp();
     }
+    if (leader) umma_commit(smem_u32(&bars[D_DONE]));
+    __syncwarp();
   } else {
     const int q = warp & 3;
     const int row = q * 32 + lane;
@@ -326,42 +335,49 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc_s = umma_idesc_bf16(kBQ, kBKV, 0, 0);
-      constexpr uint32_t idesc_q = umma_idesc_bf16(kBQ, kDh, 0, 1);  // A = dS (K-major), B = K_j (MN-major)
-      const uint32_t q_base = smem_u32(sQ), do_base = smem_u32(sDO), ds_base = smem_u32(sDS);
-      mbar_wait(smem_u32(&bars[Q_Q]), 0);
-      for (int j = 0; j < nkv; ++j) {
-        const int buf = j & 1;
-        const uint32_t k_base = smem_u32(sK + buf * kTileBytes), v_base = smem_u32(sV + buf * kTileBytes);
-        mbar_wait(smem_u32(&bars[Q_KF0 + buf]), (j >> 1) & 1);
-        tc_fence_after();
+    constexpr uint32_t idesc_s = umma_idesc_bf16(kBQ, kBKV, 0, 0);
+    constexpr uint32_t idesc_q = umma_idesc_bf16(kBQ, kDh, 0, 1);  // A = dS (K-major), B = K_j (MN-major)
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t q_base = smem_u32(sQ), do_base = smem_u32(sDO), ds_base = smem_u32(sDS);
+    const uint32_t leader = elect_one();
+    mbar_wait(smem_u32(&bars[Q_Q]), 0);
+    for (int j = 0; j < nkv; ++j) {
+      const int buf = j & 1;
+      const uint32_t k_base = smem_u32(sK + buf * kTileBytes), v_base = smem_u32(sV + buf * kTileBytes);
+      mbar_wait(smem_u32(&bars[Q_KF0 + buf]), (j >> 1) & 1);
+      tc_fence_after();
+      if (leader) {
 #pragma unroll
         for (int ks = 0; ks < kDh / 16; ++ks) {
           const uint32_t off = (ks >> 1) * kBoxBytes + (ks & 1) * 32;
-          umma_bf16(tmem_S, umma_smem_desc(q_base + off, 16, 512, kLayoutSW64),
+          umma_bf16(tb, umma_smem_desc(q_base + off, 16, 512, kLayoutSW64),
                     umma_smem_desc(k_base + off, 16, 512, kLayoutSW64), idesc_s, ks != 0);
         }
 #pragma unroll
         for (int ks = 0; ks < kDh / 16; ++ks) {
           const uint32_t off = (ks >> 1) * kBoxBytes + (ks & 1) * 32;
-          umma_bf16(tmem_dP, umma_smem_desc(do_base + off, 16, 512, kLayoutSW64),
+          umma_bf16(tb + 128, umma_smem_desc(do_base + off, 16, 512, kLayoutSW64),
                     umma_smem_desc(v_base + off, 16, 512, kLayoutSW64), idesc_s, ks != 0);
         }
         umma_commit(smem_u32(&bars[Q_SF]));
-        mbar_wait(smem_u32(&bars[Q_PF]), j & 1);
-        tc_fence_after();
+      }
+      __syncwarp();
+      mbar_wait(smem_u32(&bars[Q_PF]), j & 1);
+      tc_fence_after();
+      if (leader) {
 #pragma unroll
         for (int ks = 0; ks < kBKV / 16; ++ks) {
           const uint64_t adesc =
               umma_smem_desc(ds_base + (ks >> 2) * (kBQ * 128) + (ks & 3) * 32, 16, 1024, kLayoutSW128);
           const uint64_t bdesc = umma_smem_desc(k_base + ks * 1024, kBoxBytes, 512, kLayoutSW64);
-          umma_bf16(tmem_dQ, adesc, bdesc, idesc_q, (j | ks) != 0);
+          umma_bf16(tb + 256, adesc, bdesc, idesc_q, (j | ks) != 0);
         }
         umma_commit(smem_u32(&bars[Q_KE0 + buf]));
       }
-      umma_commit(smem_u32(&bars[Q_DONE]));
+      __syncwarp();
     }
+    if (leader) umma_commit(smem_u32(&bars[Q_DONE]));
+    __syncwarp();
   } else {
     const int q = warp & 3;
     const int row = q * 32 + lane;

@@ -124,8 +124,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // The whole warp runs the loop converged (waits included); only the tcgen05 instructions are predicated on one
+    // elected lane, so their operands are warp-uniform and live in uniform registers.  Under `if (lane == 0)` the
+    // compiler wraps every UTCHMMA in an ELECT / R2UR / BRA.U.ANY waterfall loop, which made MMA issue the limiter
+    // for the narrower tiles.
+    {
       constexpr uint32_t idesc = umma_idesc_bf16(kBlockM, Cfg::kWBoxN, 0, 0);
+      const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+      const uint32_t leader = elect_one();
       uint32_t git = 0, ti = 0, ui = 0;
       for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x, ++ui) {
         if (A_STAT) {
@@ -137,7 +143,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const uint32_t aph = (ti / Cfg::kNumAcc) & 1;
           mbar_wait(smem_u32(&bar_acce[ab]), aph ^ 1);  // epilogue drained this accumulator
           tc_fence_after();
-          const uint32_t d_tmem = tmem_base + ab * BLOCK_N;
+          const uint32_t d_tmem = tb + ab * BLOCK_N;
           for (int it = 0; it < num_iters; ++it, ++git) {
             const int s = git % S;
             const uint32_t ph = (git / S) & 1;
@@ -146,21 +152,28 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const uint32_t st = smem_u32(sStages + s * Cfg::kStageBytes);
             const uint32_t a_base = A_STAT ? smem_u32(sARes + it * Cfg::kABytes) : st;
             const uint32_t w_base = A_STAT ? st : st + Cfg::kABytes;
+            if (leader) {
 #pragma unroll
-            for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-              const uint64_t adesc = umma_smem_desc(a_base + k * kUmmaK * 2, 16, 1024, kLayoutSW128);
+              for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+                const uint64_t adesc = umma_smem_desc(a_base + k * kUmmaK * 2, 16, 1024, kLayoutSW128);
 #pragma unroll
-              for (int wb = 0; wb < Cfg::kNumWBoxes; ++wb) {
-                const uint64_t bdesc =
-                    umma_smem_desc(w_base + wb * Cfg::kWBoxBytes + k * kUmmaK * 2, 16, 1024, kLayoutSW128);
-                umma_bf16(d_tmem + wb * Cfg::kWBoxN, adesc, bdesc, idesc, (it | k) != 0 ? 1u : 0u);
+                for (int wb = 0; wb < Cfg::kNumWBoxes; ++wb) {
+                  const uint64_t bdesc =
+                      umma_smem_desc(w_base + wb * Cfg::kWBoxBytes + k * kUmmaK * 2, 16, 1024, kLayoutSW128);
+                  umma_bf16(d_tmem + wb * Cfg::kWBoxN, adesc, bdesc, idesc, (it | k) != 0 ? 1u : 0u);
+                }
               }
+              umma_commit(smem_u32(&bar_empty[s]));  // frees the smem stage when these MMAs retire
             }
-            umma_commit(smem_u32(&bar_empty[s]));  // frees the smem stage when these MMAs retire
+            __syncwarp();
           }
-          umma_commit(smem_u32(&bar_accf[ab]));  // accumulator complete
+          if (leader) umma_commit(smem_u32(&bar_accf[ab]));  // accumulator complete
+          __syncwarp();
         }
-        if (A_STAT) umma_commit(smem_u32(bar_ae));  // resident A may be overwritten
+        if (A_STAT) {
+          if (leader) umma_commit(smem_u32(bar_ae));  // resident A may be overwritten
+          __syncwarp();
+        }
       }
     }
   } else if (warp == 2) {

@@ -105,26 +105,31 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant__ C
         }
       }
     } else if (warp == 1) {
-      if (lane == 0) {
-        constexpr uint32_t idesc = umma_idesc_bf16(kWgM, kWgN, 1, 1);  // both operands MN-major
-        for (int i = 0; i < nch; ++i) {
-          const int s = i % kWgStages;
-          const uint32_t ph = (i / kWgStages) & 1;
-          mbar_wait(smem_u32(&bar_full[s]), ph);
-          tc_fence_after();
-          const uint32_t a_base = smem_u32(smem + s * kWgStageBytes);
-          const uint32_t b_base = a_base + 2 * kWgBox;
+      // whole warp converged, MMAs predicated on one elected lane (uniform-register operands, no waterfall loops)
+      constexpr uint32_t idesc = umma_idesc_bf16(kWgM, kWgN, 1, 1);  // both operands MN-major
+      const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+      const uint32_t leader = elect_one();
+      for (int i = 0; i < nch; ++i) {
+        const int s = i % kWgStages;
+        const uint32_t ph = (i / kWgStages) & 1;
+        mbar_wait(smem_u32(&bar_full[s]), ph);
+        tc_fence_after();
+        const uint32_t a_base = smem_u32(smem + s * kWgStageBytes);
+        const uint32_t b_base = a_base + 2 * kWgBox;
+        if (leader) {
 #pragma unroll
           for (int k = 0; k < kWgK / 16; ++k) {
             // 16 time rows per MMA: start at row 16k (128 B per row); LBO = next 64-channel box, SBO = 8 rows
             const uint64_t adesc = umma_smem_desc(a_base + k * 2048, kWgBox, 1024, kLayoutSW128);
             const uint64_t bdesc = umma_smem_desc(b_base + k * 2048, kWgBox, 1024, kLayoutSW128);
-            umma_bf16(tmem_base, adesc, bdesc, idesc, (i | k) != 0 ? 1u : 0u);
+            umma_bf16(tb, adesc, bdesc, idesc, (i | k) != 0 ? 1u : 0u);
           }
           umma_commit(smem_u32(&bar_empty[s]));
         }
-        umma_commit(smem_u32(bar_acc));
+        __syncwarp();
       }
+      if (leader) umma_commit(smem_u32(bar_acc));
+      __syncwarp();
     } else {
       // ---- epilogue: TMEM lane = n (dy channel), column = c (x channel) ----
       const int q = warp & 3;
