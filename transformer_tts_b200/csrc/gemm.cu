@@ -40,27 +40,32 @@ constexpr int kWgThreads = 128;
 constexpr int kMaxSmem = 232448;  // 227 KB opt-in limit per CTA
 constexpr int kBoxBytes16K = 16384;
 
-template <int BLOCK_N, int EPI, bool A_STAT>
+template <int BLOCK_N, int EPI, bool A_STAT, bool PAIR = false>
 struct GemmCfg {
   static constexpr bool kIsLN = EPI != TTSB200_EPI_AFFINE_ACT;
   static constexpr bool kRing = EPI == TTSB200_EPI_RES_LN || EPI == TTSB200_EPI_FFN2;
   static constexpr int kWBoxN = BLOCK_N <= 256 ? BLOCK_N : BLOCK_N / 2;  // TMA box rows / UMMA N
   static constexpr int kNumWBoxes = BLOCK_N / kWBoxN;
   static constexpr int kABytes = kBlockM * kBlockK * 2;                  // 16 KB
-  static constexpr int kWBytes = BLOCK_N * kBlockK * 2;
-  static constexpr int kWBoxBytes = kWBoxN * kBlockK * 2;
+  // CTA pair: each CTA of the pair stages half of the W tile's rows (the M=256 MMA reads both halves)
+  static constexpr int kWLoadN = PAIR ? kWBoxN / 2 : kWBoxN;             // rows per TMA box in this CTA
+  static constexpr int kWBoxBytes = kWLoadN * kBlockK * 2;
+  static constexpr int kWBytes = kNumWBoxes * kWBoxBytes;
   static constexpr int kStageBytes = A_STAT ? kWBytes : kABytes + kWBytes;
   static constexpr int kAResBytes = A_STAT ? 6 * kABytes : 0;            // resident A: up to C = 384
   // one bf16 staging box per warpgroup: 128 rows x 32 columns (SWIZZLE_64B)
-  static constexpr int kStoreBytes = 2 * 8192;
+  // (CTA pairs have the room for two per warpgroup: the TMA store of one chunk overlaps the next chunk's math)
+  static constexpr int kStoreBoxes = PAIR ? 2 : 1;
+  static constexpr int kStoreBytes = 2 * kStoreBoxes * 8192;
   static constexpr int kRingSlots = kRing ? 4 : 0;  // even: each half owns its own slots
   static constexpr int kRingBytes = kRingSlots * kBoxBytes16K;
   // parameter vectors in smem: AFFINE: (bias, scale) per warpgroup; LN: bias, g1, b1, g2, b2, dot_w
   static constexpr int kParamFloats = kIsLN ? 6 * BLOCK_N : 4 * BLOCK_N;
   static constexpr int kStatBytes = kIsLN ? 2 * 2 * kBlockM * 8 : 0;     // [buf][half][row] float2
-  static constexpr int kFixed = kAResBytes + kStoreBytes + kRingBytes + kParamFloats * 4 + kStatBytes + 256;
+  static constexpr int kFixed = kAResBytes + kStoreBytes + kRingBytes + kParamFloats * 4 + kStatBytes + 512;
   static constexpr int kStagesFit = (kMaxSmem - kFixed) / kStageBytes;
-  static constexpr int kStages = kStagesFit > 6 ? 6 : kStagesFit;
+  static constexpr int kMaxStages = PAIR ? 7 : 6;
+  static constexpr int kStages = kStagesFit > kMaxStages ? kMaxStages : kStagesFit;
   static constexpr int kNumAcc = BLOCK_N <= 256 ? 2 : 1;
   static constexpr int kTmemCols = (kNumAcc * BLOCK_N) <= 128 ? 128 : ((kNumAcc * BLOCK_N) <= 256 ? 256 : 512);
   static constexpr int kSmemBytes = kFixed + kStages * kStageBytes;
@@ -69,6 +74,7 @@ struct GemmCfg {
   static_assert(kWBoxN % 16 == 0 && kWBoxN <= 256, "UMMA N");
   static_assert(!kIsLN || (BLOCK_N % 128 == 0), "LN epilogues split the row in two halves of 64-column groups");
   static_assert(kIsLN || kNumAcc == 2, "AFFINE epilogue: one accumulator per epilogue warpgroup");
+  static_assert(!PAIR || (!kIsLN && kNumWBoxes == 1 && kWBoxN % 32 == 0), "CTA pairs: AFFINE epilogue, one W box");
 };
 
 struct GemmDev {
@@ -158,7 +164,67 @@ __device__ __forceinline__ void box_row_st_bf16x32_sw64(uint8_t* box, int row, c
   }
 }
 
+// ---- packed fp32 pairs (Blackwell FFMA2 / FADD2): half the issue slots of the scalar form, same IEEE results ----
+__device__ __forceinline__ void fma2(float& x, float& y, float sx, float sy, float bx, float by) {
+  asm("{\n\t"
+      ".reg .b64 a, s, b, d;\n\t"
+      "mov.b64 a, {%0, %1};\n\t"
+      "mov.b64 s, {%2, %3};\n\t"
+      "mov.b64 b, {%4, %5};\n\t"
+      "fma.rn.f32x2 d, a, s, b;\n\t"
+      "mov.b64 {%0, %1}, d;\n\t"
+      "}"
+      : "+f"(x), "+f"(y)
+      : "f"(sx), "f"(sy), "f"(bx), "f"(by));
+}
+__device__ __forceinline__ void add2(float& x, float& y, float bx, float by) {
+  asm("{\n\t"
+      ".reg .b64 a, b, d;\n\t"
+      "mov.b64 a, {%0, %1};\n\t"
+      "mov.b64 b, {%2, %3};\n\t"
+      "add.rn.f32x2 d, a, b;\n\t"
+      "mov.b64 {%0, %1}, d;\n\t"
+      "}"
+      : "+f"(x), "+f"(y)
+      : "f"(bx), "f"(by));
+}
+// max(x, 0) and round-to-nearest bf16 of a pair in one instruction (NaN stays NaN, as torch.relu keeps it)
+__device__ __forceinline__ uint32_t pack_bf16_relu(float lo, float hi) {
+  uint32_t d;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
+template <bool RELU>
+__device__ __forceinline__ void box_row_st_bf16x32_sw64_t(uint8_t* box, int row, const float* v) {
+  uint8_t* rp = box + row * 64;
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    uint4 u;
+    if (RELU) {
+      u.x = pack_bf16_relu(v[g * 8 + 0], v[g * 8 + 1]);
+      u.y = pack_bf16_relu(v[g * 8 + 2], v[g * 8 + 3]);
+      u.z = pack_bf16_relu(v[g * 8 + 4], v[g * 8 + 5]);
+      u.w = pack_bf16_relu(v[g * 8 + 6], v[g * 8 + 7]);
+    } else {
+      u.x = pack_bf16(v[g * 8 + 0], v[g * 8 + 1]);
+      u.y = pack_bf16(v[g * 8 + 2], v[g * 8 + 3]);
+      u.z = pack_bf16(v[g * 8 + 4], v[g * 8 + 5]);
+      u.w = pack_bf16(v[g * 8 + 6], v[g * 8 + 7]);
+    }
+    *reinterpret_cast<uint4*>(rp + ((g ^ ((row >> 1) & 3)) << 4)) = u;
+  }
+}
+
 __device__ __forceinline__ void epi_bar_all() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+// named barriers 4..7 / 8..11: staging box (warpgroup, box) full / free, between an epilogue warpgroup and its store warp
+constexpr int kBarFull0 = 4;
+constexpr int kBarFree0 = 8;
+__device__ __forceinline__ void nbar_sync(int id, int count) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+__device__ __forceinline__ void nbar_arrive(int id, int count) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
 __device__ __forceinline__ void wg_bar(int wg) { asm volatile("bar.sync %0, 128;" ::"r"(2 + wg) : "memory"); }
 
 // TMA store of one 128-row box from swizzled smem; rows beyond T are clipped by the tensor map.
@@ -169,6 +235,7 @@ __device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, uint32_t src,
 }
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
 }  // namespace ttsb

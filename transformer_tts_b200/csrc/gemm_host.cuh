@@ -17,9 +17,11 @@ static int num_sms() {
   return g_num_sms;
 }
 
-template <int BLOCK_N, int EPI, bool A_STAT>
+static int g_gemm_pair = 1;  // CTA-pair (cta_group::2) AFFINE kernels; ttsb200_debug_gemm_pair(0) turns them off
+
+template <int BLOCK_N, int EPI, bool A_STAT, bool PAIR = false>
 static int launch_gemm(const ttsb200_gemm_args& a, GemmDev& d, cudaStream_t stream) {
-  using Cfg = GemmCfg<BLOCK_N, EPI, A_STAT>;
+  using Cfg = GemmCfg<BLOCK_N, EPI, A_STAT, PAIR>;
   static_assert(Cfg::kSmemBytes <= kMaxSmem, "shared memory budget exceeded");
   CUtensorMap tmA, tmW, tmOut, tmOut32, tmRes32, tmResBf;
   const uint64_t uN = static_cast<uint64_t>(a.N), uT = static_cast<uint64_t>(a.T), uB = static_cast<uint64_t>(a.B);
@@ -33,7 +35,7 @@ static int launch_gemm(const ttsb200_gemm_args& a, GemmDev& d, cudaStream_t stre
   {
     const uint64_t dims[2] = {static_cast<uint64_t>(a.C), static_cast<uint64_t>(a.taps) * uN};
     const uint64_t strides[1] = {static_cast<uint64_t>(a.C) * 2};
-    const uint32_t box[2] = {kBlockK, static_cast<uint32_t>(Cfg::kWBoxN)};
+    const uint32_t box[2] = {kBlockK, static_cast<uint32_t>(Cfg::kWLoadN)};
     int rc = make_tmap_bf16(&tmW, a.w, 2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
   }
@@ -72,7 +74,7 @@ static int launch_gemm(const ttsb200_gemm_args& a, GemmDev& d, cudaStream_t stre
       if (rc) return rc;
     }
   }
-  auto kern = conv_gemm_kernel<BLOCK_N, EPI, A_STAT>;
+  auto kern = conv_gemm_kernel<BLOCK_N, EPI, A_STAT, PAIR>;
   static bool attr_done = false;  // per instantiation
   if (!attr_done) {
     TTSB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
@@ -81,6 +83,25 @@ static int launch_gemm(const ttsb200_gemm_args& a, GemmDev& d, cudaStream_t stre
   d.m_tiles = (a.T + kBlockM - 1) / kBlockM;
   d.n_tiles = a.N / BLOCK_N;
   d.num_tiles = a.B * d.m_tiles * d.n_tiles;
+  if (PAIR) {
+    const int mt_units = (a.B * d.m_tiles + 1) / 2;
+    const int units = A_STAT ? mt_units : mt_units * d.n_tiles;
+    const int pairs = units < num_sms() / 2 ? units : num_sms() / 2;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * pairs);
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    TTSB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmW, tmOut, tmOut32, tmRes32, tmResBf, d));
+    return TTSB_OK;
+  }
   const int units = A_STAT ? a.B * d.m_tiles : d.num_tiles;
   const int grid = units < num_sms() ? units : num_sms();
   kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(tmA, tmW, tmOut, tmOut32, tmRes32, tmResBf, d);
@@ -93,6 +114,14 @@ static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t
 }  // namespace ttsb
 
 using namespace ttsb;
+
+extern "C" void ttsb200_debug_gemm_pair(int on) { g_gemm_pair = on; }
+
+#if defined(TTSB_GEMM_TRACE)
+extern "C" int ttsb200_debug_gemm_trace(long long* dst, int n) {
+  return cudaMemcpyFromSymbol(dst, g_gemm_trace, n * sizeof(long long)) == cudaSuccess ? 0 : -1;
+}
+#endif
 
 extern "C" int ttsb200_conv_gemm(const ttsb200_gemm_args* a, ttsb200_stream_t stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
@@ -139,12 +168,18 @@ extern "C" int ttsb200_conv_gemm(const ttsb200_gemm_args* a, ttsb200_stream_t st
       if (a_stat) return launch_gemm<128, TTSB200_EPI_AFFINE_ACT, true>(*a, d, stream);
       return launch_gemm<128, TTSB200_EPI_AFFINE_ACT, false>(*a, d, stream);
     }
+    // CTA pairs halve the weight stream into each SM; worth it once there are at least two m-tiles per pair
+    const bool pair = g_gemm_pair && static_cast<long long>(a->B) * ((a->T + kBlockM - 1) / kBlockM) >= 2;
     if (bn == 192) {
+      if (a_stat && pair) return launch_gemm<192, TTSB200_EPI_AFFINE_ACT, true, true>(*a, d, stream);
       if (a_stat) return launch_gemm<192, TTSB200_EPI_AFFINE_ACT, true>(*a, d, stream);
+      if (pair) return launch_gemm<192, TTSB200_EPI_AFFINE_ACT, false, true>(*a, d, stream);
       return launch_gemm<192, TTSB200_EPI_AFFINE_ACT, false>(*a, d, stream);
     }
     if (bn == 256) {
+      if (a_stat && pair) return launch_gemm<256, TTSB200_EPI_AFFINE_ACT, true, true>(*a, d, stream);
       if (a_stat) return launch_gemm<256, TTSB200_EPI_AFFINE_ACT, true>(*a, d, stream);
+      if (pair) return launch_gemm<256, TTSB200_EPI_AFFINE_ACT, false, true>(*a, d, stream);
       return launch_gemm<256, TTSB200_EPI_AFFINE_ACT, false>(*a, d, stream);
     }
   } else if (e == TTSB200_EPI_RES_LN || e == TTSB200_EPI_FFN2) {
