@@ -12,7 +12,7 @@ def run(name, B, T, C_, N, taps, bn, act, pad=0):
     w = (torch.randn(taps, N, C_, device=dev) * 0.05).to(torch.bfloat16)
     b = torch.randn(N, device=dev) * 0.1
     outs, times = [], []
-    for pair in (0, 1):
+    for pair in (0, 2):
         lib.ttsb200_debug_gemm_pair(pair)
         o = torch.full((B, T, N), 7.0, device=dev, dtype=torch.bfloat16)
         fn = lambda: L.conv_gemm(x, w, b, taps=taps, pad_left=pad, block_n=bn, act=act, out_bf16=o)

@@ -39,6 +39,10 @@ def report(name, fn):
     nc = max(rows[0][23], 1)
     print(f"{'':28s} per 32-col chunk (wg0 thread 0): tmem_ld {rows[0][16]/nc:5.0f} math {rows[0][17]/nc:5.0f} free-wait {rows[0][18]/nc:5.0f} "
           f"sts {rows[0][19]/nc:5.0f} fence {rows[0][20]/nc:5.0f} arrive {rows[0][21]/nc:5.0f}  chunks {nc}")
+    if "LN" in name or "FFN2" in name:
+        nt_ = max(rows[0][23], 1)
+        print(f"{'':28s} LN epilogue per tile (wg0 t0): wait-acc {rows[0][16]/nt_:6.0f} pass1 {rows[0][17]/nt_:6.0f} xchg {rows[0][18]/nt_:6.0f} "
+              f"pass2 {rows[0][19]/nt_:6.0f} last {rows[0][20]/nt_:6.0f} (ring waits {rows[0][21]/nt_:6.0f}) tiles {nt_}")
     print(f"{'':28s} epilogue wg0 per tile: pre {rows[0][8]/tl:6.0f} wait-acc {rows[0][9]/tl:6.0f} work {rows[0][10]/tl:6.0f} clk | "
           f"wg1: pre {rows[0][11]/tl:6.0f} wait-acc {rows[0][12]/tl:6.0f} work {rows[0][13]/tl:6.0f}; MMA total/tile {rows[0][0]/max(rows[0][5],1):6.0f}")
     print(f"{name:28s} {e0.elapsed_time(e1)*1e3:7.1f} us | MMA warp clk/CTA: total {tot:9.0f}  wait A-tile {sum(r[1] for r in rows)/n/tot:5.1%}  "

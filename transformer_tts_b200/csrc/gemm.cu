@@ -55,7 +55,7 @@ struct GemmCfg {
   static constexpr int kAResBytes = A_STAT ? 6 * kABytes : 0;            // resident A: up to C = 384
   // one bf16 staging box per warpgroup: 128 rows x 32 columns (SWIZZLE_64B)
   // (CTA pairs have the room for two per warpgroup: the TMA store of one chunk overlaps the next chunk's math)
-  static constexpr int kStoreBoxes = PAIR ? 2 : 1;
+  static constexpr int kStoreBoxes = (PAIR && !kIsLN) ? 2 : 1;
   static constexpr int kStoreBytes = 2 * kStoreBoxes * 8192;
   static constexpr int kRingSlots = kRing ? 4 : 0;  // even: each half owns its own slots
   static constexpr int kRingBytes = kRingSlots * kBoxBytes16K;
@@ -74,7 +74,7 @@ struct GemmCfg {
   static_assert(kWBoxN % 16 == 0 && kWBoxN <= 256, "UMMA N");
   static_assert(!kIsLN || (BLOCK_N % 128 == 0), "LN epilogues split the row in two halves of 64-column groups");
   static_assert(kIsLN || kNumAcc == 2, "AFFINE epilogue: one accumulator per epilogue warpgroup");
-  static_assert(!PAIR || (!kIsLN && kNumWBoxes == 1 && kWBoxN % 32 == 0), "CTA pairs: AFFINE epilogue, one W box");
+  static_assert(!PAIR || kWBoxN % 32 == 0, "CTA pairs: each CTA stages half of every W box");
 };
 
 struct GemmDev {

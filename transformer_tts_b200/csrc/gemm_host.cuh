@@ -169,11 +169,12 @@ extern "C" int ttsb200_conv_gemm(const ttsb200_gemm_args* a, ttsb200_stream_t st
       return launch_gemm<128, TTSB200_EPI_AFFINE_ACT, false>(*a, d, stream);
     }
     // CTA pairs halve the weight stream into each SM; worth it once there are at least two m-tiles per pair
-    const bool pair = g_gemm_pair && static_cast<long long>(a->B) * ((a->T + kBlockM - 1) / kBlockM) >= 2;
-    if (bn == 192) {
-      if (a_stat && pair) return launch_gemm<192, TTSB200_EPI_AFFINE_ACT, true, true>(*a, d, stream);
+    // (ttsb200_debug_gemm_pair: 0 = never, 1 = where it measured faster, 2 = wherever it is implemented)
+    const int pair = static_cast<long long>(a->B) * ((a->T + kBlockM - 1) / kBlockM) >= 2 ? g_gemm_pair : 0;
+    if (bn == 192) {  // measured: the 192-wide tiles gain nothing from pairing (q|k|v 70 us single, 75 us paired)
+      if (a_stat && pair > 1) return launch_gemm<192, TTSB200_EPI_AFFINE_ACT, true, true>(*a, d, stream);
       if (a_stat) return launch_gemm<192, TTSB200_EPI_AFFINE_ACT, true>(*a, d, stream);
-      if (pair) return launch_gemm<192, TTSB200_EPI_AFFINE_ACT, false, true>(*a, d, stream);
+      if (pair > 1) return launch_gemm<192, TTSB200_EPI_AFFINE_ACT, false, true>(*a, d, stream);
       return launch_gemm<192, TTSB200_EPI_AFFINE_ACT, false>(*a, d, stream);
     }
     if (bn == 256) {
@@ -191,11 +192,14 @@ extern "C" int ttsb200_conv_gemm(const ttsb200_gemm_args* a, ttsb200_stream_t st
                        aligned16(a->res_f32),
                    "conv_gemm: res_f32 must be dense (tstride == N, bstride == T*N or 0) and 16-byte aligned");
     d.res_bcast = a->res_bstride == 0 ? 1 : 0;
+    const bool pair_ln = g_gemm_pair && static_cast<long long>(a->B) * ((a->T + kBlockM - 1) / kBlockM) >= 2;
     if (e == TTSB200_EPI_FFN2) {
       TTSB_CHECK_ARG(a->res_bf16 && a->ln2_g && a->ln2_b && aligned16(a->res_bf16), "conv_gemm: FFN2 operands");
       TTSB_CHECK_ARG(!a->res_scale, "conv_gemm: res_scale is a RES_LN operand");
+      if (bn == 384 && pair_ln) return launch_gemm<384, TTSB200_EPI_FFN2, false, true>(*a, d, stream);
       if (bn == 384) return launch_gemm<384, TTSB200_EPI_FFN2, false>(*a, d, stream);
     } else {
+      if (bn == 384 && pair_ln) return launch_gemm<384, TTSB200_EPI_RES_LN, false, true>(*a, d, stream);
       if (bn == 384) return launch_gemm<384, TTSB200_EPI_RES_LN, false>(*a, d, stream);
     }
   } else if (e == TTSB200_EPI_RELU_LN) {

@@ -67,8 +67,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(smem_u32(&bar_accf[i]), 1);
-      // pair: one arrival per epilogue warp of either CTA, all on the leader's barrier
-      mbar_init(smem_u32(&bar_acce[i]), PAIR ? 8 : (Cfg::kIsLN ? kEpiThreads : kWgThreads));
+      // every epilogue thread; pair: one arrival per epilogue warp of either CTA, all on the leader's barrier
+      mbar_init(smem_u32(&bar_acce[i]), PAIR ? 16 : kEpiThreads);
     }
     for (int i = 0; i < 6; ++i) {
       mbar_init(smem_u32(&bar_af[i]), 1);
@@ -148,8 +148,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               sw = st + Cfg::kABytes;
             }
             if (PAIR) {
-              tma_load_2d_2sm(smem_u32(sw), &tmW, full, c0,
-                              tap * p.N + nt * BLOCK_N + static_cast<int>(cta_rank) * Cfg::kWLoadN);
+#pragma unroll
+              for (int wb = 0; wb < Cfg::kNumWBoxes; ++wb)
+                tma_load_2d_2sm(smem_u32(sw + wb * Cfg::kWBoxBytes), &tmW, full, c0,
+                                tap * p.N + nt * BLOCK_N + wb * Cfg::kWBoxN + static_cast<int>(cta_rank) * Cfg::kWLoadN);
             } else {
 #pragma unroll
               for (int wb = 0; wb < Cfg::kNumWBoxes; ++wb)
@@ -262,14 +264,16 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const bool tma_out = (BLOCK_N % 64 == 0) && p.out_bf16 && !p.out_f32 && !p.res_f32;
     if (tma_out) {
       constexpr uint32_t NB = Cfg::kStoreBoxes;
+      constexpr int kSplit = ((BLOCK_N / 2 + 31) / 32) * 32;  // as in the epilogue: warpgroup g's column range
+      const int c_lo = wg == 0 ? 0 : kSplit;
+      const int c_hi = wg == 0 ? kSplit : BLOCK_N;
       uint8_t* my_box = sStore + wg * (Cfg::kStoreBytes / 2);
-      uint32_t ti = 0, sg = 0;
+      uint32_t sg = 0;
       for (int unit = unit0; unit < num_units; unit += ustride) {
         int b, t0, nt0;
         decode(unit, b, t0, nt0);
-        for (int nt = nt0; nt < nt0 + n_inner; ++nt, ++ti) {
-          if (static_cast<int>(ti & 1) != wg) continue;
-          for (int c = 0; c < BLOCK_N; c += 32, ++sg) {
+        for (int nt = nt0; nt < nt0 + n_inner; ++nt) {
+          for (int c = c_lo; c < c_hi; c += 32, ++sg) {
             const uint32_t bx = sg % NB;
             nbar_sync(kBarFull0 + wg * 2 + bx, kWgThreads + 32);
             if (lane == 0) {
