@@ -7,7 +7,8 @@ from transformer_tts_b200.Models import _engine as E
 _build.LIB_PATH = type(_build.LIB_PATH)("tools/exp/libgemm_tr.so")
 _build.is_stale = lambda: False
 L.load()
-B, T, D = 64, 1103, 384
+import os
+B, T, D = 64, int(os.environ.get('TT', '1103')), 384
 dev = "cuda"
 xs = (torch.randn(B, T, D, device=dev) * 0.5).to(torch.bfloat16)
 hs = torch.relu(torch.randn(B, T, 4 * D, device=dev)).to(torch.bfloat16)
