@@ -272,9 +272,9 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
       if (clean) {
 #pragma unroll
-        for (int i = 0; i < kBKV; i += 4) {
-          mx4[0] = fmaxf(mx4[0], s[i]); mx4[1] = fmaxf(mx4[1], s[i + 1]);
-          mx4[2] = fmaxf(mx4[2], s[i + 2]); mx4[3] = fmaxf(mx4[3], s[i + 3]);
+        for (int i = 0; i < kBKV; i += 8) {  // three-input max: half the issue slots
+          mx4[0] = max3(mx4[0], s[i], s[i + 4]); mx4[1] = max3(mx4[1], s[i + 1], s[i + 5]);
+          mx4[2] = max3(mx4[2], s[i + 2], s[i + 6]); mx4[3] = max3(mx4[3], s[i + 3], s[i + 7]);
         }
       } else {
 #pragma unroll
@@ -324,18 +324,32 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       for (int c = 0; c < kBKV; c += 32) {
 #endif
         float* v = s + c;
+#if defined(TTSB_ATT_EXP) || TTSB_POLY
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
 #if defined(TTSB_ATT_EXP) && TTSB_ATT_EXP >= 1
           v[i] = fmaf(v[i], sc, neg_m);  // timing experiment only: no exponential
 #else
-          // MUFU.EX2 runs at 16/clk/SM and bounds this loop: every other pair of elements is evaluated on the FMA
-          // pipe instead (round-to-nearest split + degree-4 polynomial, relative error 4e-5 << bf16's 2^-9)
+          // experiment (TTSB_POLY): part of the elements on the FMA pipe (round-to-nearest split + degree-4
+          // polynomial) instead of MUFU.EX2 — measured slower, the softmax warps are issue-bound
           if ((i & 3) < kPolyOf4) v[i] = poly_exp2(fmaf(v[i], sc, neg_m));
           else v[i] = fast_exp2(fmaf(v[i], sc, neg_m));
 #endif
           ls4[i & 3] += v[i];
         }
+#else
+        // packed f32x2 scale-subtract and row-sum (FFMA2 / FADD2): the softmax warps are issue-bound, MUFU.EX2
+        // (16/clk/SM) is the only per-element instruction that cannot be paired
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+          fma2(v[i], v[i + 1], sc, sc, neg_m, neg_m);
+          fma2(v[i + 2], v[i + 3], sc, sc, neg_m, neg_m);
+          v[i] = fast_exp2(v[i]); v[i + 1] = fast_exp2(v[i + 1]);
+          v[i + 2] = fast_exp2(v[i + 2]); v[i + 3] = fast_exp2(v[i + 3]);
+          add2(ls4[0], ls4[1], v[i], v[i + 1]);
+          add2(ls4[2], ls4[3], v[i + 2], v[i + 3]);
+        }
+#endif
       }
       // P (bf16 pairs, key 2c in the low half of column c) -> this thread's TMEM lane: the A operand of P V
       {

@@ -80,6 +80,9 @@ __device__ __forceinline__ void fence_mbar_init() {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+__device__ __forceinline__ void mbar_arrive_n(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
                : "memory");
@@ -314,6 +317,35 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(uint32_t M, uint32_t N, u
 }
 
 // ---- small math ------------------------------------------------------------------------------
+// ---- packed fp32 pairs (Blackwell FFMA2 / FADD2): half the issue slots of the scalar form, same IEEE results ----
+__device__ __forceinline__ void fma2(float& x, float& y, float sx, float sy, float bx, float by) {
+  asm("{\n\t"
+      ".reg .b64 a, s, b, d;\n\t"
+      "mov.b64 a, {%0, %1};\n\t"
+      "mov.b64 s, {%2, %3};\n\t"
+      "mov.b64 b, {%4, %5};\n\t"
+      "fma.rn.f32x2 d, a, s, b;\n\t"
+      "mov.b64 {%0, %1}, d;\n\t"
+      "}"
+      : "+f"(x), "+f"(y)
+      : "f"(sx), "f"(sy), "f"(bx), "f"(by));
+}
+__device__ __forceinline__ void add2(float& x, float& y, float bx, float by) {
+  asm("{\n\t"
+      ".reg .b64 a, b, d;\n\t"
+      "mov.b64 a, {%0, %1};\n\t"
+      "mov.b64 b, {%2, %3};\n\t"
+      "add.rn.f32x2 d, a, b;\n\t"
+      "mov.b64 {%0, %1}, d;\n\t"
+      "}"
+      : "+f"(x), "+f"(y)
+      : "f"(bx), "f"(by));
+}
+__device__ __forceinline__ float max3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);

@@ -164,30 +164,6 @@ __device__ __forceinline__ void box_row_st_bf16x32_sw64(uint8_t* box, int row, c
   }
 }
 
-// ---- packed fp32 pairs (Blackwell FFMA2 / FADD2): half the issue slots of the scalar form, same IEEE results ----
-__device__ __forceinline__ void fma2(float& x, float& y, float sx, float sy, float bx, float by) {
-  asm("{\n\t"
-      ".reg .b64 a, s, b, d;\n\t"
-      "mov.b64 a, {%0, %1};\n\t"
-      "mov.b64 s, {%2, %3};\n\t"
-      "mov.b64 b, {%4, %5};\n\t"
-      "fma.rn.f32x2 d, a, s, b;\n\t"
-      "mov.b64 {%0, %1}, d;\n\t"
-      "}"
-      : "+f"(x), "+f"(y)
-      : "f"(sx), "f"(sy), "f"(bx), "f"(by));
-}
-__device__ __forceinline__ void add2(float& x, float& y, float bx, float by) {
-  asm("{\n\t"
-      ".reg .b64 a, b, d;\n\t"
-      "mov.b64 a, {%0, %1};\n\t"
-      "mov.b64 b, {%2, %3};\n\t"
-      "add.rn.f32x2 d, a, b;\n\t"
-      "mov.b64 {%0, %1}, d;\n\t"
-      "}"
-      : "+f"(x), "+f"(y)
-      : "f"(bx), "f"(by));
-}
 // max(x, 0) and round-to-nearest bf16 of a pair in one instruction (NaN stays NaN, as torch.relu keeps it)
 __device__ __forceinline__ uint32_t pack_bf16_relu(float lo, float hi) {
   uint32_t d;

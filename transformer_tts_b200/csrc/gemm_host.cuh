@@ -17,7 +17,13 @@ static int num_sms() {
   return g_num_sms;
 }
 
-static int g_gemm_pair = 1;  // CTA-pair (cta_group::2) AFFINE kernels; ttsb200_debug_gemm_pair(0) turns them off
+// CTA-pair (cta_group::2) kernels: 0 = never, 1 = where they measured faster, 2 = wherever implemented.
+// ttsb200_debug_gemm_pair() or the environment variable TTSB200_GEMM_PAIR (read once) override the default.
+static int gemm_pair_default() {
+  const char* e = getenv("TTSB200_GEMM_PAIR");
+  return (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1;
+}
+static int g_gemm_pair = gemm_pair_default();
 
 template <int BLOCK_N, int EPI, bool A_STAT, bool PAIR = false>
 static int launch_gemm(const ttsb200_gemm_args& a, GemmDev& d, cudaStream_t stream) {
