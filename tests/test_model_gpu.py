@@ -224,3 +224,52 @@ def test_training_mode_is_loud(setup):
             model(torch.ones(1, 4, dtype=torch.long, device="cuda"), torch.ones(1, 1, 4, dtype=torch.bool, device="cuda"))
     finally:
         model.eval()
+
+
+def test_teacher_forced_forward_is_graph_capturable(setup):
+    """SURVEY §8b threading contract: with durations / pitch / energy teacher-forced there is no host read-back, so
+    the whole forward records into a CUDA graph; replays reproduce the eager result bit for bit, also after the
+    input buffers are overwritten in place."""
+    from transformer_tts_b200 import synth
+
+    hp, sd, sd_gpu, model = setup
+    B, L = 4, 48
+    text, pos, lens = synth.synth_text_batch(B, L, ragged=True, seed=77)
+    align, pos_mel, f0, energy = synth.synth_targets(pos, seed=77)
+    text, pos, align, pos_mel, f0, energy = (t.cuda() for t in (text, pos, align, pos_mel, f0, energy))
+    src_mask, mel_mask = (pos != 0).unsqueeze(-2), (pos_mel != 0).unsqueeze(-2)
+
+    def fwd():
+        with torch.no_grad():
+            o = model(text, src_mask, mel_mask=mel_mask, d_target=align, p_target=f0, e_target=energy)
+        return o[0], o[1], o[2]
+
+    eager = [t.clone() for t in fwd()]
+    torch.cuda.synchronize()
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        fwd()  # warm-up on the capture stream (extension load, caches)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            outs = fwd()
+    torch.cuda.synchronize()
+    g.replay()
+    torch.cuda.synchronize()
+    for a, b in zip(outs, eager):
+        assert torch.equal(a, b)
+    # same graph, new token ids written into the captured input buffer
+    text2, _, _ = synth.synth_text_batch(B, L, ragged=True, seed=78)
+    text2 = torch.where(pos != 0, text2.cuda(), torch.zeros_like(text))
+    keep = text.clone()
+    text.copy_(text2)
+    g.replay()
+    torch.cuda.synchronize()
+    replay2 = [t.clone() for t in outs]
+    eager2 = fwd()
+    torch.cuda.synchronize()
+    for a, b in zip(replay2, eager2):
+        assert torch.equal(a, b)
+    assert not torch.equal(replay2[0], eager[0])
+    text.copy_(keep)
