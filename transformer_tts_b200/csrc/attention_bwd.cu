@@ -24,7 +24,8 @@ namespace ab {
 constexpr int kDh = 96;
 constexpr int kBQ = 128;
 constexpr int kBKV = 128;
-constexpr int kThreads = 192;
+constexpr int kThreads = 320;  // TMA warp, MMA warp, 8 softmax warps (two per TMEM lane quarter: 64 keys each)
+constexpr int kSoftmaxThreads = 256;
 constexpr int kBoxBytes = 32 * 2 * 128;    // 32 dims x 128 rows bf16
 constexpr int kTileBytes = 3 * kBoxBytes;  // 96 dims = 24 KB
 constexpr int kPBytes = kBQ * kBKV * 2;    // 32 KB
@@ -71,6 +72,20 @@ __device__ __forceinline__ void softmax_bwd32(float* s /* in: s, out: p */, floa
   }
 }
 
+// The same for a tile whose keys are all valid (the common case): packed f32x2 arithmetic, no flags.
+//   neg_l2 = -lse2 (+inf -> p = 0 for query rows beyond T), neg_dsc = -delta * scale
+__device__ __forceinline__ void softmax_bwd32_clean(float* s, float* dp, float neg_l2, float neg_dsc, float scale_log2,
+                                                    float scale) {
+#pragma unroll
+  for (int i = 0; i < 32; i += 2) {
+    fma2(s[i], s[i + 1], scale_log2, scale_log2, neg_l2, neg_l2);
+    s[i] = ex2(s[i]);
+    s[i + 1] = ex2(s[i + 1]);
+    fma2(dp[i], dp[i + 1], scale, scale, neg_dsc, neg_dsc);
+    mul2(dp[i], dp[i + 1], s[i], s[i + 1]);
+  }
+}
+
 enum { D_KV = 0, D_QF0, D_QF1, D_QE0, D_QE1, D_SF, D_PF, D_DONE, D_COUNT };
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -97,6 +112,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
   const int D = H * kDh;
   const int klen = kv_info[2 * b];
   const int kv_eff = klen > 0 ? klen : T;
+  const bool clean = k0 + kBKV <= kv_info[2 * b + 1];  // every key of this tile is valid: no flags needed
   const int nq = (T + kBQ - 1) / kBQ;
   const int64_t ld = 3LL * D;
 
@@ -116,14 +132,14 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmQKV);
     tma_prefetch_desc(&tmDO);
-    for (int i = 0; i < D_COUNT; ++i) mbar_init(smem_u32(&bars[i]), i == D_PF ? 128 : 1);
+    for (int i = 0; i < D_COUNT; ++i) mbar_init(smem_u32(&bars[i]), i == D_PF ? kSoftmaxThreads : 1);
     fence_mbar_init();
   }
   if (warp == 1) {
     tmem_alloc(smem_u32(tmem_slot), 512);
     tmem_relinquish();
   }
-  if (threadIdx.x >= 64) {
+  if (threadIdx.x >= 64 && threadIdx.x < 64 + kBKV) {
     const int st = threadIdx.x - 64;
     const int key = k0 + st;
     sflag[st] = key < T ? (mask[static_cast<int64_t>(b) * T + key] ? 1 : 0) : 2;
@@ -210,7 +226,10 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
     if (leader) umma_commit(smem_u32(&bars[D_DONE]));
     __syncwarp();
   } else {
+    // eight softmax warps: warp % 4 is the TMEM lane quarter (query rows), `half` the 64-key half of the tile.  With
+    // one warp per scheduler the recompute was latency-bound; two per scheduler hide each other's stalls.
     const int q = warp & 3;
+    const int half = (warp - 2) >> 2;
     const int row = q * 32 + lane;
     const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
     const int64_t stat_base = (static_cast<int64_t>(b) * H + h) * T;
@@ -219,16 +238,18 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
       const bool row_ok = t < T;
       const float l2 = row_ok ? __ldg(lse2 + stat_base + t) : 0.f;
       const float dl = row_ok ? __ldg(delta + stat_base + t) : 0.f;
+      const float neg_l2 = row_ok ? -l2 : -INFINITY, neg_dsc = -dl * scale;
       // SF(i) also tells that the dV/dK MMAs of tile i-1 have retired (same in-order pipe): sP/sDS are free
       mbar_wait(smem_u32(&bars[D_SF]), i & 1);
       tc_fence_after();
 #pragma unroll 1
-      for (int c = 0; c < kBKV; c += 32) {
+      for (int c = half * 64; c < half * 64 + 64; c += 32) {
         float s[32], dp[32];
         tmem_ld32(tmem_S + lane_off + c, s);
         tmem_ld32(tmem_dP + lane_off + c, dp);
         tmem_ld_wait();
-        softmax_bwd32(s, dp, sflag + c, row_ok, l2, dl, scale_log2, scale);
+        if (clean) softmax_bwd32_clean(s, dp, neg_l2, neg_dsc, scale_log2, scale);
+        else softmax_bwd32(s, dp, sflag + c, row_ok, l2, dl, scale_log2, scale);
         store_row32(sP, row, c, s);
         store_row32(sDS, row, c, dp);
       }
@@ -241,8 +262,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
     tc_fence_after();
     const int key = k0 + row;
     __nv_bfloat16* base = dqkv + (static_cast<int64_t>(b) * T + (key < T ? key : 0)) * ld + h * kDh;
-#pragma unroll
-    for (int which = 0; which < 2; ++which) {
+    {
+      const int which = half;  // the two warps of a lane quarter write dK and dV side by side
       const uint32_t tm = which == 0 ? tmem_dK : tmem_dV;
       __nv_bfloat16* op = base + (which == 0 ? D : 2 * D);
 #pragma unroll
@@ -299,7 +320,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmQKV);
     tma_prefetch_desc(&tmDO);
-    for (int i = 0; i < Q_COUNT; ++i) mbar_init(smem_u32(&bars[i]), i == Q_PF ? 128 : 1);
+    for (int i = 0; i < Q_COUNT; ++i) mbar_init(smem_u32(&bars[i]), i == Q_PF ? kSoftmaxThreads : 1);
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -380,6 +401,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     __syncwarp();
   } else {
     const int q = warp & 3;
+    const int half = (warp - 2) >> 2;  // as in the dKV kernel: two warps per lane quarter, 64 keys each
     const int row = q * 32 + lane;
     const int st = threadIdx.x - 64;
     const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
@@ -388,20 +410,28 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     const int64_t stat_base = (static_cast<int64_t>(b) * H + h) * T;
     const float l2 = row_ok ? __ldg(lse2 + stat_base + t) : 0.f;
     const float dl = row_ok ? __ldg(delta + stat_base + t) : 0.f;
+    const float neg_l2 = row_ok ? -l2 : -INFINITY, neg_dsc = -dl * scale;
+    const int kprefix = kv_info[2 * b + 1];
     for (int j = 0; j < nkv; ++j) {
+      const bool clean = (j + 1) * kBKV <= kprefix;  // CTA-uniform
       uint8_t* flg = sflag + (j & 1) * 128;
-      const int key = j * kBKV + st;
-      flg[st] = key < T ? (mask[static_cast<int64_t>(b) * T + key] ? 1 : 0) : 2;
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (!clean) {
+        if (st < kBKV) {
+          const int key = j * kBKV + st;
+          flg[st] = key < T ? (mask[static_cast<int64_t>(b) * T + key] ? 1 : 0) : 2;
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+      }
       mbar_wait(smem_u32(&bars[Q_SF]), j & 1);  // also: the dQ MMAs of tile j-1 have retired, sDS is free
       tc_fence_after();
 #pragma unroll 1
-      for (int c = 0; c < kBKV; c += 32) {
+      for (int c = half * 64; c < half * 64 + 64; c += 32) {
         float s[32], dp[32];
         tmem_ld32(tmem_S + lane_off + c, s);
         tmem_ld32(tmem_dP + lane_off + c, dp);
         tmem_ld_wait();
-        softmax_bwd32(s, dp, flg + c, row_ok, l2, dl, scale_log2, scale);
+        if (clean) softmax_bwd32_clean(s, dp, neg_l2, neg_dsc, scale_log2, scale);
+        else softmax_bwd32(s, dp, flg + c, row_ok, l2, dl, scale_log2, scale);
         store_row32(sDS, row, c, dp);
       }
       fence_async_smem();
@@ -413,6 +443,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     __nv_bfloat16* op = dqkv + (static_cast<int64_t>(b) * T + (row_ok ? t : 0)) * ld + h * kDh;
 #pragma unroll
     for (int c = 0; c < kDh; c += 32) {
+      if ((c == 32 ? 1 : 0) != half) continue;  // warp-uniform split: half 0 writes columns 0-31 and 64-95, half 1 32-63
       float o[32];
       tmem_ld32(tmem_dQ + lane_off + c, o);
       tmem_ld_wait();

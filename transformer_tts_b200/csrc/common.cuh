@@ -341,6 +341,17 @@ __device__ __forceinline__ void add2(float& x, float& y, float bx, float by) {
       : "+f"(x), "+f"(y)
       : "f"(bx), "f"(by));
 }
+__device__ __forceinline__ void mul2(float& x, float& y, float ax, float ay) {
+  asm("{\n\t"
+      ".reg .b64 a, b, d;\n\t"
+      "mov.b64 a, {%0, %1};\n\t"
+      "mov.b64 b, {%2, %3};\n\t"
+      "mul.rn.f32x2 d, a, b;\n\t"
+      "mov.b64 {%0, %1}, d;\n\t"
+      "}"
+      : "+f"(x), "+f"(y)
+      : "f"(ax), "f"(ay));
+}
 __device__ __forceinline__ float max3(float a, float b, float c) {
   float d;
   asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
