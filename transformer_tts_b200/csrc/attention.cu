@@ -36,6 +36,7 @@ constexpr int kKStages = 2;
 constexpr int kVStages = 2;
 constexpr int kAttSmem = kQBytes + (kKStages + kVStages) * kKVBytes + 1024 /*align*/ + 256 /*barriers*/ +
                          256 /*flags*/;
+constexpr int kTmemQ = 224;                    // Q dims [0,64) as packed bf16 pairs: columns [224,256)
 constexpr int kAttTmemCols = 256;              // S0 [0,64) S1 [64,128) O [128,224); P_j (bf16 pairs) overwrites the
                                                // first 32 columns of its own S buffer once S_j sits in registers
 constexpr float kLog2e = 1.4426950408889634f;
@@ -79,7 +80,8 @@ enum {
   BAR_SF = BAR_VE + kVStages,   // [2] S buffer written by the tensor core
   BAR_PF = BAR_SF + 2,          // [2] P_j written over S buffer j & 1
   BAR_OF = BAR_PF + 2,          // [2] P_j V_j retired (S/P buffer j & 1 reusable, O current)
-  BAR_COUNT = BAR_OF + 2
+  BAR_QT = BAR_OF + 2,          // Q dims [0,64) copied into TMEM by the softmax threads
+  BAR_COUNT
 };
 
 // v3: 64-key tiles, K triple- and V double-buffered in smem, S double-buffered in TMEM, so that neither a TMA
@@ -131,7 +133,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     tma_prefetch_desc(&tmKV);
     tma_prefetch_desc(&tmKV32);
     for (int i = 0; i < BAR_COUNT; ++i)
-      mbar_init(smem_u32(&bars[i]), (i == BAR_PF || i == BAR_PF + 1) ? 128 : 1);
+      mbar_init(smem_u32(&bars[i]), (i == BAR_PF || i == BAR_PF + 1 || i == BAR_QT) ? 128 : 1);
     fence_mbar_init();
     // the first loads go out before the TMEM allocation and the CTA-wide sync: only this thread touches these
     // barriers until then
@@ -192,9 +194,9 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       const uint32_t d_tmem = tb + (j & 1) * kBKV;
       if (leader) {
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk)  // dims [0,64): 128-byte rows
-          umma_bf16(d_tmem, umma_smem_desc(q_base + kk * 32, 16, 1024, kLayoutSW128),
-                    umma_smem_desc(k_base + kk * 32, 16, 1024, kLayoutSW128), idesc_s, kk != 0);
+        for (int kk = 0; kk < 4; ++kk)  // dims [0,64): Q from TMEM (columns [224,256), 8 packed columns per k-step)
+          umma_bf16_ts(d_tmem, tb + kTmemQ + kk * 8, umma_smem_desc(k_base + kk * 32, 16, 1024, kLayoutSW128), idesc_s,
+                       kk != 0);
 #pragma unroll
         for (int kk = 0; kk < 2; ++kk)  // dims [64,96): 64-byte rows
           umma_bf16(d_tmem, umma_smem_desc(q_base + kQBox0 + kk * 32, 16, 512, kLayoutSW64),
@@ -205,6 +207,8 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       __syncwarp();
     };
     mbar_wait(smem_u32(&bars[BAR_Q]), 0);
+    mbar_wait(smem_u32(&bars[BAR_QT]), 0);
+    tc_fence_after();
     issue_s(0);
     if (nkv > 1) issue_s(1);
     for (int j = 0; j < nkv; ++j) {
@@ -241,6 +245,23 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     // moved (and O, l rescaled) when the maximum has grown by more than 2^8, so p <= 256 stays well
     // inside bf16/fp32 range and the final O / l is unchanged.
     float m = -INFINITY, l = 0.f;
+    // Q dims [0,64) -> TMEM once per CTA: the S MMAs then read their A operand from TMEM and only K from shared
+    // memory.  The kernel is shared-memory-bandwidth bound (per 64-key tile and CTA: 36 KB of Q/K operand reads for
+    // S, 12 KB of V for P V, 24 KB of TMA writes; 128 B/clk/SM), and re-reading Q for every key tile was 16 KB of it.
+    {
+      mbar_wait(smem_u32(&bars[BAR_Q]), 0);
+      const uint8_t* qrow = sQ + row * 128;  // SWIZZLE_128B box: 16-byte chunk c of row r sits at (c ^ (r & 7)) * 16
+      uint32_t qv[32];
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const uint4 u = *reinterpret_cast<const uint4*>(qrow + ((c ^ (row & 7)) << 4));
+        qv[4 * c] = u.x; qv[4 * c + 1] = u.y; qv[4 * c + 2] = u.z; qv[4 * c + 3] = u.w;
+      }
+      tmem_st32(tmem_base + kTmemQ + lane_off, reinterpret_cast<const float*>(qv));
+      tmem_st_wait();
+      tc_fence_before();
+      mbar_arrive(smem_u32(&bars[BAR_QT]));
+    }
 #if defined(TTSB_ATT_TRACE)
     const bool tr_on = TTSB_ATT_TRACE == 1 && blockIdx.x == 4 && blockIdx.y == 1 && blockIdx.z == 10 && threadIdx.x == 64;
     int tr_n = 0;
