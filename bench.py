@@ -422,7 +422,7 @@ def train(args):
     model = build_fastspeech2(hp)
     model.load_state_dict(synth.synth_state_dict(hp))
     model = model.cuda().train()
-    tr = Trainer(model)
+    tr = Trainer(model, optimizer=args.optimizer)
     tr.broadcast_parameters()
     Bt = args.train_batch
     host, frames = make_train_batch(rank, Bt)
@@ -474,7 +474,8 @@ def train(args):
                 "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
                 "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "bf16", "data": "synthetic",
-                "config": {"workload": f"fastspeech2_train_step_bf16_B{Bt}_per_gpu_L128_T~1000_adam_noam_clip",
+                "config": {"workload": f"fastspeech2_train_step_bf16_B{Bt}_per_gpu_L128_T~1000_"
+                                       + ("radam_lr1e-3_clip" if args.optimizer == "radam" else "adam_noam_clip"),
                            "batch_per_gpu": Bt, "frames_per_step_per_gpu": frames, "t_max": int(dev["mel"].shape[1]),
                            "parallelism": f"dp{world}, NCCL all-reduce of one flat fp32 gradient buffer "
                                           f"({tr.flat_g.numel() * 4 / 1e6:.0f} MB)" + (", SyncBatchNorm" if world > 1 else ""),
@@ -496,6 +497,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--workload", default="infer", choices=["infer", "train"])
     ap.add_argument("--train-batch", type=int, default=32)
+    ap.add_argument("--optimizer", default="radam", choices=["radam", "adam"],
+                    help="train workload: radam (BASELINE.json configs[2], radam.py) or adam + Noam rate (the "
+                         "reference's working default, SURVEY F5)")
     args = ap.parse_args()
     if args.impl == "reference":
         reference_arm(args)

@@ -129,6 +129,15 @@ int ttsb200_embed_pe_ln(const int64_t* ids, const float* table, const float* pe,
 int ttsb200_layernorm(const float* x, const float* g, const float* b, float eps, void* y_bf16,
                       float* y_f32, int64_t rows, int32_t D, ttsb200_stream_t stream);
 
+/* Tail of an FFT block for short batches (Models/modules.py:84-87, Models/layers.py:40,31): given
+ * u = conv2(h) + b2 (fp32, from conv_gemm AFFINE), yn = norm_2(y) (bf16) and the residual stream y (fp32):
+ * upre = u + yn; z = y + LayerNorm(upre; ln1); zn = LayerNorm(z; ln2).  Same arithmetic as the
+ * TTSB200_EPI_FFN2 epilogue; zn_f32 / pre_f32 (the saved pre-LayerNorm value) are optional. */
+int ttsb200_ffn2_tail(const float* u, const void* yn_bf16, const float* y, const float* ln1_g,
+                      const float* ln1_b, const float* ln2_g, const float* ln2_b, float eps, float* z,
+                      void* zn_bf16, float* zn_f32, float* pre_f32, int64_t rows, int32_t D,
+                      ttsb200_stream_t stream);
+
 /* duration = clamp(round_half_even(exp(log_d) - 1), 0)  (Models/varianceadaptor.py:75). int32 out. */
 int ttsb200_round_durations(const float* log_d, int32_t* dur, int64_t n, ttsb200_stream_t stream);
 
@@ -234,6 +243,15 @@ int ttsb200_sumsq(const float* g, float* out, int64_t n, ttsb200_stream_t stream
 int ttsb200_adam_step(float* p, const float* g, float* m, float* v, const float* sumsq, int64_t n,
                       float gscale, float clip, float lr, float beta1, float beta2, float eps, int32_t step,
                       ttsb200_stream_t stream);
+
+/* radam.RAdam.step (radam.py:30-92, the optimizer train_fastspeech2.py:412-414 builds for hp.optimizer ==
+ * 'radam': lr fixed at max_lr, betas (0.9, 0.98), eps 1e-9, weight_decay 0, degenerated_to_sgd=True) over the
+ * same flat buffers, with the same gradient scaling / clipping prologue as ttsb200_adam_step.  The rectification
+ * term N_sma and the step size are computed on the host in double, as the reference does in Python:
+ * N_sma >= 5 -> p -= lr*step_size*m/(sqrt(v)+eps), else p -= lr*m/(1-beta1^t). */
+int ttsb200_radam_step(float* p, const float* g, float* m, float* v, const float* sumsq, int64_t n,
+                       float gscale, float clip, float lr, float beta1, float beta2, float eps, int32_t step,
+                       ttsb200_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -289,3 +289,23 @@ def training_step_grads(sd: Dict[str, Tensor], hp: dict, text, src_mask, mel_mas
     grads = torch.autograd.grad(losses["loss"], [p[k] for k in names], allow_unused=True)
     return ({k: v.detach() for k, v in losses.items()},
             {k: (g if g is not None else torch.zeros_like(sd[k])) for k, g in zip(names, grads)}, out)
+
+
+def radam_step(p: Tensor, g: Tensor, m: Tensor, v: Tensor, step: int, lr: float = 1e-3, beta1: float = 0.9,
+               beta2: float = 0.98, eps: float = 1e-9):
+    """One radam.RAdam.step() for one tensor (radam.py:56-92; weight_decay 0, degenerated_to_sgd=True — the
+    optimizer train_fastspeech2.py:412-414 builds).  `step` is the 1-based count AFTER the increment at :61.
+    Returns (p, m, v) as new tensors."""
+    v = v * beta2 + (1 - beta2) * g * g                      # :58
+    m = m * beta1 + (1 - beta1) * g                          # :59
+    beta2_t = beta2 ** step                                  # :67
+    n_sma_max = 2 / (1 - beta2) - 1                          # :68
+    n_sma = n_sma_max - 2 * step * beta2_t / (1 - beta2_t)   # :69
+    if n_sma >= 5:                                           # :73-74, :83-88
+        step_size = math.sqrt((1 - beta2_t) * (n_sma - 4) / (n_sma_max - 4) * (n_sma - 2) / n_sma * n_sma_max /
+                              (n_sma_max - 2)) / (1 - beta1 ** step)
+        p = p - step_size * lr * m / (v.sqrt() + eps)
+    else:                                                    # :75-76, :89-93
+        step_size = 1.0 / (1 - beta1 ** step)
+        p = p - step_size * lr * m
+    return p, m, v

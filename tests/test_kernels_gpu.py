@@ -165,6 +165,37 @@ def test_gemm_ffn2(L, taps, pad, B, T):
     assert rel_err(zn, ln_ref(zr, g2, b2)) < 1e-2
 
 
+@pytest.mark.parametrize("taps,pad,B,T,bn", [(5, 2, 2, 150, 128), (5, 2, 30, 128, 192), (1, 0, 3, 70, 128)])
+def test_ffn2_short_batch_path(L, taps, pad, B, T, bn):
+    """Short batches: conv2 as a column-split AFFINE GEMM + the ffn2_tail row kernel; same arithmetic as the
+    EPI_FFN2 epilogue (modules.py:84-87 + layers.py:40,31), compared with it and with the float64 restatement."""
+    C, N = 1536, 384
+    h = torch.relu(rnd(B, T, C, seed=21)).to(torch.bfloat16)
+    w = rnd(taps, N, C, scale=1 / math.sqrt(C * taps), dtype=torch.bfloat16, seed=22)
+    bias = rnd(N, seed=23)
+    g1, b1, g2, b2 = 1 + 0.1 * rnd(N, seed=24), 0.1 * rnd(N, seed=25), 1 + 0.1 * rnd(N, seed=26), 0.1 * rnd(N, seed=27)
+    yn = rnd(B, T, N, dtype=torch.bfloat16, seed=28)
+    y = rnd(B, T, N, seed=29)
+    u = torch.empty(B, T, N, device=dev())
+    z, zn32, pre = (torch.empty(B, T, N, device=dev()) for _ in range(3))
+    zn = torch.empty(B, T, N, device=dev(), dtype=torch.bfloat16)
+    L.conv_gemm(h, w, bias, taps=taps, pad_left=pad, block_n=bn, out_f32=u)
+    L.ffn2_tail(u, yn, y, (g1, b1), (g2, b2), 1e-5, z, zn, zn32=zn32, pre_f32=pre)
+    z2 = torch.empty(B, T, N, device=dev())
+    zn2 = torch.empty(B, T, N, device=dev(), dtype=torch.bfloat16)
+    pre2 = torch.empty(B, T, N, device=dev())
+    L.conv_gemm(h, w, bias, taps=taps, pad_left=pad, block_n=384, epi=L.EPI_FFN2, res_bf16=yn, res_f32=y,
+                res_bstride=T * N, res_tstride=N, ln1=(g1, b1), ln2=(g2, b2), out_f32=z2, out_bf16=zn2, pre_f32=pre2)
+    torch.cuda.synchronize()
+    v = conv_ref(h, w, pad) + bias.double() + yn.double()
+    zr = y.double() + ln_ref(v, g1, b1)
+    assert rel_err(pre, v) < 2e-4
+    assert rel_err(z, zr) < 2e-4
+    assert rel_err(zn32, ln_ref(zr, g2, b2)) < 2e-4
+    assert rel_err(zn, ln_ref(zr, g2, b2)) < 1e-2
+    assert rel_err(z, z2) < 1e-5 and rel_err(pre, pre2) < 1e-5 and rel_err(zn, zn2) < 5e-3
+
+
 @pytest.mark.parametrize("B,T", [(3, 170), (40, 500)])
 def test_gemm_predictor(L, B, T):
     C, N = 384, 256

@@ -220,3 +220,34 @@ def test_golden_train_step(world):
         close(grads[n], g["full:" + n], 1e-3)
     for n in SUB:
         close(grads[n].reshape(grads[n].shape[0], -1)[::7, ::13], g["sub:" + n], 1e-3)
+
+
+def test_radam_oracle_matches_reference_golden():
+    """oracle.radam_step (restatement of radam.py:56-92) against the parameters the UNMODIFIED reference optimizer
+    produced (oracle/make_golden_radam.py), and against the live reference when it is present."""
+    gold = np.load(GOLDEN / "radam_steps.npz")
+    p, grads, want = (torch.from_numpy(gold[k]) for k in ("p0", "grads", "p_steps"))
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    live = None
+    if ref_loader.reference_available():
+        import sys
+        import warnings
+
+        if ref_loader.REFERENCE_ROOT not in sys.path:
+            sys.path.insert(0, ref_loader.REFERENCE_ROOT)
+        import radam
+
+        lp = torch.nn.Parameter(p.clone())
+        live = (lp, radam.RAdam([lp], lr=1e-3, betas=(0.9, 0.98), eps=1e-9), warnings)
+    for t in range(grads.shape[0]):
+        p, m, v = O.radam_step(p, grads[t], m, v, t + 1)
+        assert (p - want[t]).abs().max().item() < 1e-6, t
+        if live is not None:
+            lp, opt, warnings = live
+            lp.grad = grads[t].clone()
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")
+                opt.step()
+            assert (p - lp.detach()).abs().max().item() < 1e-6, t
+    close(m, gold["exp_avg"], 1e-6)
+    close(v, gold["exp_avg_sq"], 1e-6)

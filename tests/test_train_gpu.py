@@ -174,6 +174,31 @@ def test_train_step_matches_torch_adam_on_own_gradients():
     assert (tr.flat_p - p_ref.detach()).abs().max().item() < 1e-6
 
 
+def test_train_step_radam_matches_oracle_on_own_gradients():
+    """hp.optimizer == 'radam' (train_fastspeech2.py:412-414, radam.py:56-92): fixed rate 1e-3 (no Noam schedule,
+    :117-120), clip_grad_norm_(1.0) first.  The fused kernel equals the oracle's restatement on the same gradients."""
+    from oracle import fastspeech2_oracle as O
+    from transformer_tts_b200 import synth
+    from transformer_tts_b200.training import Trainer
+
+    hp, sd, model = build()
+    text, pos, _ = synth.synth_text_batch(2, 16, ragged=True, seed=9)
+    dur, pos_mel, f0, en = synth.synth_targets(pos, seed=9, max_dur=6)
+    mel = synth.synth_mel(pos_mel, hp.mel_dim, seed=9)
+    tr = Trainer(model, optimizer="radam")
+    p, m, v = tr.flat_p.cpu().clone(), torch.zeros(tr.total), torch.zeros(tr.total)
+    for step in (1, 2):
+        tr.zero_grad()
+        run_step(tr, (text, pos, dur, pos_mel, f0, en, mel))
+        g = tr.flat_g.cpu().clone()
+        g = g * min(1.0, 1.0 / (g.norm().item() + 1e-6))
+        lr = tr.optimizer_step()
+        assert lr == 1e-3
+        p, m, v = O.radam_step(p, g, m, v, step, lr=1e-3)
+        torch.cuda.synchronize()
+        assert (tr.flat_p.cpu() - p).abs().max().item() < 2e-6, step
+
+
 def test_dropin_autograd_mode_matches_trainer():
     """The reference's own loop shape (train_fastspeech2.py:167-315): model.train(); model(...) ; nn.L1Loss terms;
     loss.backward(); clip_grad_norm_; torch.optim.Adam.step() — with this package's modules in place of Models/."""

@@ -346,3 +346,40 @@ def test_adam_clip(L):
         assert abs(ss.item() - (gs.double() ** 2).sum().item()) / ss.item() < 1e-4
         L.adam_step(p, gs, m, v, ss, gscale=1.0, clip=1.0, lr=1e-3, beta1=0.9, beta2=0.98, eps=1e-9, step=step)
     assert (p - pr.detach()).abs().max().item() < 1e-5
+
+
+def test_radam_matches_reference_golden_and_oracle(L):
+    """ttsb200_radam_step against tests/golden/radam_steps.npz (the UNMODIFIED radam.RAdam of the reference,
+    oracle/make_golden_radam.py) and against the oracle's restatement of radam.py:56-92; steps 1-5 take the
+    degenerated-to-SGD branch, 6-8 the rectified one."""
+    import numpy as np
+    from pathlib import Path
+
+    from oracle import fastspeech2_oracle as O
+
+    gold = np.load(Path(__file__).resolve().parent / "golden" / "radam_steps.npz")
+    p0, grads, want = (torch.from_numpy(gold[k]) for k in ("p0", "grads", "p_steps"))
+    n = p0.numel()
+    buf = torch.zeros(4, (n + 3) // 4 * 4, device=dev())  # 16-byte aligned rows: p, g, m, v
+    p, g, m, v = (buf[i, :n] for i in range(4))
+    p.copy_(p0)
+    po, mo, vo = p0.clone(), torch.zeros(n), torch.zeros(n)
+    for t in range(grads.shape[0]):
+        g.copy_(grads[t])
+        L.radam_step(p, g, m, v, None, gscale=1.0, clip=0.0, lr=1e-3, beta1=0.9, beta2=0.98, eps=1e-9, step=t + 1)
+        po, mo, vo = O.radam_step(po, grads[t], mo, vo, t + 1)
+        assert (p.cpu() - want[t]).abs().max().item() < 2e-6, t
+        assert (p.cpu() - po).abs().max().item() < 2e-6, t
+    assert (m.cpu() - torch.from_numpy(gold["exp_avg"])).abs().max().item() < 1e-6
+    assert rel_err(v.cpu(), torch.from_numpy(gold["exp_avg_sq"])) < 1e-5
+    # clip + gradient-mean scale prologue shared with adam_step
+    ss = torch.zeros(1, device=dev())
+    g.copy_(grads[0] * 50)
+    L.sumsq(g, ss)
+    p1 = p.clone()
+    m1, v1 = m.clone(), v.clone()
+    L.radam_step(p, g, m, v, ss, gscale=0.5, clip=1.0, lr=1e-3, beta1=0.9, beta2=0.98, eps=1e-9, step=9)
+    gs = grads[0] * 25
+    gs = gs * min(1.0, 1.0 / (gs.norm().item() + 1e-6))
+    pw, _, _ = O.radam_step(p1.cpu(), gs, m1.cpu(), v1.cpu(), 9)
+    assert (p.cpu() - pw).abs().max().item() < 2e-6

@@ -154,13 +154,35 @@ def run_fft_block(t: dict, heads: int, x: torch.Tensor, xn: torch.Tensor, mask_u
                   res_tstride=D, ln1=t["ln2"], out_f32=y, out_bf16=yn)  # modules.py:68 + layers.py:33,35
     h = torch.empty((B, T, 4 * D), device=dev, dtype=torch.bfloat16)
     lib.conv_gemm(yn, t["w1"], t["b1"], taps=k, pad_left=k // 2, block_n=256, act=lib.ACT_RELU, out_bf16=h)  # modules.py:83
+    zn32 = torch.empty((B, T, D), device=dev, dtype=torch.float32) if want_norm_f32 else None
+    z, zn = run_ffn2(t, h, yn, y, next_ln, zn32=zn32)  # modules.py:84-87 + layers.py:40 + next norm
+    return z, zn, zn32
+
+
+# Whole-row LayerNorm epilogues run one CTA per 128-row tile.  With fewer tiles than this, the k-tap conv2 of
+# the text encoder (K = 1536*k) would occupy a fraction of the 148 SMs for its whole (tensor-bound) duration, so
+# the GEMM runs column-split over 2-3x the CTAs and a row kernel applies the two LayerNorms.
+SHORT_BATCH_TILES = 74
+
+
+def run_ffn2(t: dict, h: torch.Tensor, yn: torch.Tensor, y: torch.Tensor, next_ln, zn32=None, pre_f32=None):
+    """z = y + LN_ff(conv2(h) + b2 + yn); zn = LN_next(z).  Returns (z fp32, zn bf16)."""
+    B, T, D = y.shape
+    dev = y.device
+    k = t["k"]
     z = torch.empty((B, T, D), device=dev, dtype=torch.float32)
     zn = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
-    zn32 = torch.empty((B, T, D), device=dev, dtype=torch.float32) if want_norm_f32 else None
-    lib.conv_gemm(h, t["w2"], t["b2"], taps=k, pad_left=k // 2, block_n=D, epi=lib.EPI_FFN2, res_bf16=yn,
-                  res_f32=y, res_bstride=T * D, res_tstride=D, ln1=t["ln_ff"], ln2=next_ln, out_f32=z,
-                  out_bf16=zn, out2_f32=zn32)  # modules.py:84-87 + layers.py:40 + next norm
-    return z, zn, zn32
+    tiles = B * ((T + 127) // 128)
+    if tiles <= SHORT_BATCH_TILES and D == 384:
+        u = torch.empty((B, T, D), device=dev, dtype=torch.float32)
+        lib.conv_gemm(h, t["w2"], t["b2"], taps=k, pad_left=k // 2, block_n=128 if tiles * 3 <= 148 else 192,
+                      out_f32=u)
+        lib.ffn2_tail(u, yn, y, t["ln_ff"], next_ln, LN_EPS, z, zn, zn32=zn32, pre_f32=pre_f32)
+    else:
+        lib.conv_gemm(h, t["w2"], t["b2"], taps=k, pad_left=k // 2, block_n=D, epi=lib.EPI_FFN2, res_bf16=yn,
+                      res_f32=y, res_bstride=T * D, res_tstride=D, ln1=t["ln_ff"], ln2=next_ln, out_f32=z,
+                      out_bf16=zn, out2_f32=zn32, pre_f32=pre_f32)
+    return z, zn
 
 
 # --------------------------------------------------------------------------------------------------

@@ -91,6 +91,48 @@ layernorm_kernel(const float* __restrict__ x, const float* __restrict__ g, const
 }
 
 // ------------------------------------------------------------------------------------------------
+// FFN tail for SHORT batches (modules.py:84-87 + layers.py:40 + the next norm_1): when the batch holds
+// fewer 128-row tiles than half the SMs, the whole-row LayerNorm GEMM epilogue (one CTA per tile)
+// leaves most of the GPU idle.  conv2 then runs as a 192-wide AFFINE GEMM over twice the CTAs and
+// this row kernel finishes the block:
+//   upre = u + yn ; z = y + LN_ff(upre) ; zn = LN_next(z)
+// ------------------------------------------------------------------------------------------------
+template <int NV>
+__global__ void __launch_bounds__(256)
+ffn2_tail_kernel(const float* __restrict__ u, const __nv_bfloat16* __restrict__ yn, const float* __restrict__ y,
+                 const float* __restrict__ g1, const float* __restrict__ b1, const float* __restrict__ g2,
+                 const float* __restrict__ b2, float eps, float* __restrict__ z, __nv_bfloat16* __restrict__ zn,
+                 float* __restrict__ zn32, float* __restrict__ pre, int64_t rows) {
+  constexpr int D = 128 * NV;
+  const int lane = threadIdx.x & 31;
+  const int64_t row = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  float4 v[NV], r[NV];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    v[i] = __ldcs(reinterpret_cast<const float4*>(u + row * D) + i * 32 + lane);
+    const uint2 h = __ldg(reinterpret_cast<const uint2*>(yn + row * D) + i * 32 + lane);
+    const float2 lo = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&h.x));
+    const float2 hi = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&h.y));
+    v[i].x += lo.x; v[i].y += lo.y; v[i].z += hi.x; v[i].w += hi.y;
+    r[i] = __ldcs(reinterpret_cast<const float4*>(y + row * D) + i * 32 + lane);
+    if (pre) reinterpret_cast<float4*>(pre + row * D)[i * 32 + lane] = v[i];
+  }
+  warp_ln<NV>(v, g1, b1, eps, lane);
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    v[i].x += r[i].x; v[i].y += r[i].y; v[i].z += r[i].z; v[i].w += r[i].w;
+    reinterpret_cast<float4*>(z + row * D)[i * 32 + lane] = v[i];
+  }
+  warp_ln<NV>(v, g2, b2, eps, lane);
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    store_bf16x4(zn + row * D + (i * 32 + lane) * 4, v[i]);
+    if (zn32) reinterpret_cast<float4*>(zn32 + row * D)[i * 32 + lane] = v[i];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // duration rounding: clamp(round_half_even(exp(x) - 1), 0)
 // exp is evaluated in double and rounded once to fp32 (a correctly rounded fp32 exp), then the
 // reference's fp32 subtract and round-half-even (torch.round) follow.
@@ -322,6 +364,21 @@ extern "C" int ttsb200_layernorm(const float* x, const float* g, const float* b,
     layernorm_kernel<2><<<grid, 256, 0, st>>>(x, g, b, eps, static_cast<__nv_bfloat16*>(y_bf16), y_f32, rows);
   else
     TTSB_CHECK_ARG(false, "layernorm: D=%d unsupported (256 or 384)", D);
+  TTSB_LAUNCH_CHECK();
+  return TTSB_OK;
+}
+
+extern "C" int ttsb200_ffn2_tail(const float* u, const void* yn_bf16, const float* y, const float* ln1_g,
+                                 const float* ln1_b, const float* ln2_g, const float* ln2_b, float eps, float* z,
+                                 void* zn_bf16, float* zn_f32, float* pre_f32, int64_t rows, int32_t D,
+                                 ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(u && yn_bf16 && y && ln1_g && ln1_b && ln2_g && ln2_b && z && zn_bf16 && rows > 0,
+                 "ffn2_tail: bad args");
+  TTSB_CHECK_ARG(D == 384, "ffn2_tail: D=%d unsupported (384)", D);
+  const unsigned grid = static_cast<unsigned>((rows + 7) / 8);
+  ffn2_tail_kernel<3><<<grid, 256, 0, static_cast<cudaStream_t>(s)>>>(
+      u, static_cast<const __nv_bfloat16*>(yn_bf16), y, ln1_g, ln1_b, ln2_g, ln2_b, eps, z,
+      static_cast<__nv_bfloat16*>(zn_bf16), zn_f32, pre_f32, rows);
   TTSB_LAUNCH_CHECK();
   return TTSB_OK;
 }

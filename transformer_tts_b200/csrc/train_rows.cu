@@ -512,25 +512,47 @@ sumsq_kernel(const float* __restrict__ g, float* __restrict__ out, int64_t n) {
   }
 }
 
+// MODE 0: torch.optim.Adam (denominator sqrt(v)/sqrt(bc2) + eps, step lr/bc1)
+// MODE 1: radam.RAdam rectified branch (radam.py:83-88): p -= step * m / (sqrt(v) + eps), step = lr*step_size
+// MODE 2: radam.RAdam degenerated-to-SGD branch (radam.py:89-93, N_sma < 5): p -= step * m
+template <int MODE>
 __global__ void __launch_bounds__(256)
 adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
-            const float* __restrict__ sumsq, int64_t n, float gscale, float clip, float lr, float beta1,
-            float beta2, float eps, float bc1, float bc2_sqrt) {
+            const float* __restrict__ sumsq, int64_t n, float gscale, float clip, float step, float beta1,
+            float beta2, float eps, float bc2_sqrt) {
   float coef = gscale;
   if (clip > 0.f) {
     const float norm = sqrtf(__ldg(sumsq)) * gscale;
     const float c = clip / (norm + 1e-6f);  // torch.nn.utils.clip_grad_norm_
     coef *= c < 1.f ? c : 1.f;
   }
-  const float step = lr / bc1;
-  for (int64_t i = static_cast<int64_t>(blockIdx.x) * 256 + threadIdx.x; i < n;
+  const float inv_bc2 = 1.f / bc2_sqrt;
+  auto upd = [&](float& pi, float gi, float& mi, float& vi) {
+    gi *= coef;
+    mi = beta1 * mi + (1.f - beta1) * gi;
+    vi = beta2 * vi + (1.f - beta2) * gi * gi;
+    if (MODE == 0) pi -= step * mi / (sqrtf(vi) * inv_bc2 + eps);
+    else if (MODE == 1) pi -= step * mi / (sqrtf(vi) + eps);
+    else pi -= step * mi;
+  };
+  const int64_t n4 = n >> 2;  // the flat buffers are 16-byte aligned (every tensor starts on a multiple of 4)
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * 256 + threadIdx.x; i < n4;
        i += static_cast<int64_t>(gridDim.x) * 256) {
-    const float gi = g[i] * coef;
-    const float mi = beta1 * m[i] + (1.f - beta1) * gi;
-    const float vi = beta2 * v[i] + (1.f - beta2) * gi * gi;
-    m[i] = mi;
-    v[i] = vi;
-    p[i] -= step * mi / (sqrtf(vi) / bc2_sqrt + eps);
+    float4 pp = reinterpret_cast<float4*>(p)[i];
+    const float4 gg = __ldcs(reinterpret_cast<const float4*>(g) + i);
+    float4 mm = reinterpret_cast<float4*>(m)[i];
+    float4 vv = reinterpret_cast<float4*>(v)[i];
+    upd(pp.x, gg.x, mm.x, vv.x);
+    upd(pp.y, gg.y, mm.y, vv.y);
+    upd(pp.z, gg.z, mm.z, vv.z);
+    upd(pp.w, gg.w, mm.w, vv.w);
+    reinterpret_cast<float4*>(p)[i] = pp;
+    reinterpret_cast<float4*>(m)[i] = mm;
+    reinterpret_cast<float4*>(v)[i] = vv;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    const int64_t i = (n4 << 2) + threadIdx.x;
+    upd(p[i], g[i], m[i], v[i]);
   }
 }
 
@@ -697,16 +719,51 @@ extern "C" int ttsb200_sumsq(const float* g, float* out, int64_t n, ttsb200_stre
   return TTSB_OK;
 }
 
+static inline bool opt_aligned(const void* a, const void* b, const void* c, const void* d) {
+  return ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(c) |
+           reinterpret_cast<uintptr_t>(d)) & 15) == 0;
+}
+static inline unsigned opt_grid(int64_t n) {
+  const int64_t want = ((n >> 2) + 255) / 256;
+  return static_cast<unsigned>(want < 1 ? 1 : (want < 2368 ? want : 2368));
+}
+
 extern "C" int ttsb200_adam_step(float* p, const float* g, float* m, float* v, const float* sumsq, int64_t n,
                                  float gscale, float clip, float lr, float beta1, float beta2, float eps,
                                  int32_t step, ttsb200_stream_t s) {
   TTSB_CHECK_ARG(p && g && m && v && n > 0 && step > 0, "adam_step: bad args");
   TTSB_CHECK_ARG(clip <= 0.f || sumsq, "adam_step: clipping needs the squared gradient norm");
+  TTSB_CHECK_ARG(opt_aligned(p, g, m, v), "adam_step: buffers must be 16-byte aligned");
   const float bc1 = 1.f - powf(beta1, static_cast<float>(step));
   const float bc2_sqrt = sqrtf(1.f - powf(beta2, static_cast<float>(step)));
-  const int64_t want = (n + 255) / 256;
-  adam_kernel<<<static_cast<unsigned>(want < 2368 ? want : 2368), 256, 0, static_cast<cudaStream_t>(s)>>>(
-      p, g, m, v, sumsq, n, gscale, clip, lr, beta1, beta2, eps, bc1, bc2_sqrt);
+  adam_kernel<0><<<opt_grid(n), 256, 0, static_cast<cudaStream_t>(s)>>>(p, g, m, v, sumsq, n, gscale, clip,
+                                                                       lr / bc1, beta1, beta2, eps, bc2_sqrt);
+  TTSB_LAUNCH_CHECK();
+  return TTSB_OK;
+}
+
+extern "C" int ttsb200_radam_step(float* p, const float* g, float* m, float* v, const float* sumsq, int64_t n,
+                                  float gscale, float clip, float lr, float beta1, float beta2, float eps,
+                                  int32_t step, ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(p && g && m && v && n > 0 && step > 0, "radam_step: bad args");
+  TTSB_CHECK_ARG(clip <= 0.f || sumsq, "radam_step: clipping needs the squared gradient norm");
+  TTSB_CHECK_ARG(opt_aligned(p, g, m, v), "radam_step: buffers must be 16-byte aligned");
+  // radam.py:66-80, in double as the reference's Python floats
+  const double b1 = beta1, b2 = beta2, t = step;
+  const double beta2_t = pow(b2, t);
+  const double n_sma_max = 2.0 / (1.0 - b2) - 1.0;
+  const double n_sma = n_sma_max - 2.0 * t * beta2_t / (1.0 - beta2_t);
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  if (n_sma >= 5.0) {
+    const double step_size = sqrt((1.0 - beta2_t) * (n_sma - 4.0) / (n_sma_max - 4.0) * (n_sma - 2.0) / n_sma *
+                                  n_sma_max / (n_sma_max - 2.0)) / (1.0 - pow(b1, t));
+    adam_kernel<1><<<opt_grid(n), 256, 0, st>>>(p, g, m, v, sumsq, n, gscale, clip,
+                                                static_cast<float>(step_size * lr), beta1, beta2, eps, 1.f);
+  } else {
+    const double step_size = 1.0 / (1.0 - pow(b1, t));
+    adam_kernel<2><<<opt_grid(n), 256, 0, st>>>(p, g, m, v, sumsq, n, gscale, clip,
+                                                static_cast<float>(step_size * lr), beta1, beta2, eps, 1.f);
+  }
   TTSB_LAUNCH_CHECK();
   return TTSB_OK;
 }

@@ -76,6 +76,9 @@ _SIGNATURES = {
     "ttsb200_l1_loss": ([C.c_void_p] * 5 + [C.c_int64, C.c_float, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_sumsq": ([C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p], C.c_int),
     "ttsb200_adam_step": ([C.c_void_p] * 5 + [C.c_int64] + [C.c_float] * 6 + [C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_radam_step": ([C.c_void_p] * 5 + [C.c_int64] + [C.c_float] * 6 + [C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_ffn2_tail": ([C.c_void_p] * 7 + [C.c_float] + [C.c_void_p] * 4 + [C.c_int64, C.c_int32, C.c_void_p],
+                          C.c_int),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)
@@ -235,6 +238,22 @@ def layernorm(x, g, b, eps, y_bf16=None, y_f32=None) -> None:
     _check(load().ttsb200_layernorm(_ptr(x, torch.float32, "x"), _ptr(g, torch.float32, "g"),
                                     _ptr(b, torch.float32, "b"), eps, _ptr(y_bf16, torch.bfloat16, "y_bf16"),
                                     _ptr(y_f32, torch.float32, "y_f32"), rows, D, _stream()), "layernorm")
+    _count()
+
+
+def ffn2_tail(u, yn, y, ln1, ln2, eps, z, zn, zn32=None, pre_f32=None) -> None:
+    """z = y + LN(u + yn; ln1); zn = LN(z; ln2) — the FFN2 epilogue as a row kernel (short batches)."""
+    D = u.shape[-1]
+    rows = u.numel() // D
+    for name, t in (("yn", yn), ("y", y), ("z", z), ("zn", zn), ("zn32", zn32), ("pre_f32", pre_f32)):
+        if t is not None and t.numel() != u.numel():
+            raise ValueError(f"ffn2_tail: {name} has {t.numel()} elements, expected {u.numel()}")
+    _check(load().ttsb200_ffn2_tail(_ptr(u, torch.float32, "u"), _ptr(yn, torch.bfloat16, "yn"),
+                                    _ptr(y, torch.float32, "y"), _ptr(ln1[0], torch.float32, "ln1_g"),
+                                    _ptr(ln1[1], torch.float32, "ln1_b"), _ptr(ln2[0], torch.float32, "ln2_g"),
+                                    _ptr(ln2[1], torch.float32, "ln2_b"), eps, _ptr(z, torch.float32, "z"),
+                                    _ptr(zn, torch.bfloat16, "zn"), _ptr(zn32, torch.float32, "zn32"),
+                                    _ptr(pre_f32, torch.float32, "pre_f32"), rows, D, _stream()), "ffn2_tail")
     _count()
 
 
@@ -441,4 +460,14 @@ def adam_step(p, g, m, v, sumsq_t, *, gscale: float, clip: float, lr: float, bet
                                     _ptr(m, torch.float32, "m"), _ptr(v, torch.float32, "v"),
                                     _ptr(sumsq_t, torch.float32, "sumsq"), p.numel(), gscale, clip, lr, beta1, beta2,
                                     eps, step, _stream()), "adam_step")
+    _count()
+
+
+def radam_step(p, g, m, v, sumsq_t, *, gscale: float, clip: float, lr: float, beta1: float, beta2: float, eps: float,
+               step: int) -> None:
+    """radam.RAdam.step (radam.py:30-92) over the flat buffers, same clip/scale prologue as adam_step."""
+    _check(load().ttsb200_radam_step(_ptr(p, torch.float32, "p"), _ptr(g, torch.float32, "g"),
+                                     _ptr(m, torch.float32, "m"), _ptr(v, torch.float32, "v"),
+                                     _ptr(sumsq_t, torch.float32, "sumsq"), p.numel(), gscale, clip, lr, beta1, beta2,
+                                     eps, step, _stream()), "radam_step")
     _count()

@@ -71,13 +71,19 @@ class Trainer:
 
     def __init__(self, model, *, lr_max: float = 1e-3, betas=(0.9, 0.98), eps: float = 1e-9, clip: float = 1.0,
                  warmup_step: int = 4000, warmup_factor: float = 1.0, fixed_lr: Optional[float] = None,
-                 process_group=None, sync_bn: bool = True, bn_momentum: float = 0.1, flatten: bool = True):
+                 process_group=None, sync_bn: bool = True, bn_momentum: float = 0.1, flatten: bool = True,
+                 optimizer: str = "adam"):
         """flatten=True (training loop owner): parameters are re-pointed into one flat fp32 buffer, `p.grad` are
         views of the flat gradient buffer and optimizer_step() runs the fused clip+Adam kernel.
         flatten=False (drop-in autograd mode, see `autograd_forward`): parameters are left alone, only the flat
         gradient buffer exists and the caller's torch optimizer owns the update."""
         lib.load()
         require_zero_dropout(model)
+        # hp.optimizer (train_fastspeech2.py:412-416): 'radam' -> radam.RAdam at the fixed rate lr_max (the Noam
+        # schedule is skipped for it, :117-120); anything else -> torch.optim.Adam at the Noam rate
+        self.optimizer = optimizer.lower()
+        if self.optimizer not in ("adam", "noam", "radam"):
+            raise ValueError(f"Trainer: optimizer {optimizer!r} is not built (adam / noam / radam)")
         self.flatten = flatten
         self.model = model
         self.pg = process_group
@@ -149,6 +155,8 @@ class Trainer:
     def lr(self) -> float:
         if self.fixed_lr is not None:
             return self.fixed_lr
+        if self.optimizer == "radam":
+            return self.lr_max
         d_model = self.model.decoder.norm.weight.numel()
         return noam_lr(max(self.step_count, 1), d_model, self.warmup_factor, self.warmup_step)
 
@@ -188,12 +196,8 @@ class Trainer:
                           res_tstride=D, ln1=lc["ln2"], out_f32=y, out_bf16=yn)
             h = torch.empty((B, T, 4 * D), device=dev, dtype=torch.bfloat16)
             lib.conv_gemm(yn, lc["w1"], lc["b1"], taps=k, pad_left=k // 2, block_n=256, act=lib.ACT_RELU, out_bf16=h)
-            z = torch.empty((B, T, D), device=dev, dtype=torch.float32)
-            zn = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
             upre = torch.empty((B, T, D), device=dev, dtype=torch.float32)
-            lib.conv_gemm(h, lc["w2"], lc["b2"], taps=k, pad_left=k // 2, block_n=D, epi=lib.EPI_FFN2, res_bf16=yn,
-                          res_f32=y, res_bstride=T * D, res_tstride=D, ln1=lc["ln_ff"], ln2=next_ln, out_f32=z,
-                          out_bf16=zn, pre_f32=upre)
+            z, zn = E.run_ffn2(lc, h, yn, y, next_ln, pre_f32=upre)
             tape["blocks"].append(dict(x=x, xn=xn, qkv=qkv, ctx=ctx, lse=lse, y=y, yn=yn, h=h, upre=upre))
             x, xn = z, zn
         tape["z_last"] = x
@@ -488,9 +492,10 @@ class Trainer:
         self.sumsq.zero_()
         lib.sumsq(self.flat_g, self.sumsq)
         lr = self.lr()
-        lib.adam_step(self.flat_p, self.flat_g, self.flat_m, self.flat_v, self.sumsq, gscale=gscale,
-                      clip=float(self.clip or 0.0), lr=lr, beta1=self.betas[0], beta2=self.betas[1], eps=self.eps,
-                      step=self.step_count)
+        step_fn = lib.radam_step if self.optimizer == "radam" else lib.adam_step
+        step_fn(self.flat_p, self.flat_g, self.flat_m, self.flat_v, self.sumsq, gscale=gscale,
+                clip=float(self.clip or 0.0), lr=lr, beta1=self.betas[0], beta2=self.betas[1], eps=self.eps,
+                step=self.step_count)
         self.invalidate_caches()
         return lr
 
