@@ -23,4 +23,7 @@ for v in sys.argv[1:]:
         run(); ev[i + 1].record()
     torch.cuda.synchronize()
     ms = sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(n))[n // 2]
-    print(f"{v}: {ms*1e3:.1f} us  {fl/ms/1e9:.0f} TFLOP/s")
+    c = ctx.float().clone()
+    if 'ref' not in globals(): ref = c
+    err = float((c - ref).norm() / ref.norm())
+    print(f"{v}: {ms*1e3:.1f} us  {fl/ms/1e9:.0f} TFLOP/s  rel-L2 vs first variant {err:.2e}")

@@ -20,7 +20,7 @@ lib.ttsb200_debug_att_trace.argtypes = [C.c_void_p, C.c_int]
 assert lib.ttsb200_debug_att_trace(buf, 400) == 0
 ev = [(v >> 56, v & ((1 << 56) - 1)) for v in buf if v]
 t0 = ev[0][1]
-names = {10: "loop_top", 11: "PF_ok", 12: "VF_ok", 13: "PV_issued", 14: "KF_ok", 15: "SE_ok", 16: "S_issued", 0: "start", 1: "tile_begin", 2: "S_ready", 3: "S_loaded", 4: "max_done", 5: "OF_ok", 6: "exp_done", 7: "PF_arrived", 8: "end"}
+names = {9: "entry", 20: "synced", 21: "Q_landed", 10: "loop_top", 11: "PF_ok", 12: "VF_ok", 13: "PV_issued", 14: "KF_ok", 15: "SE_ok", 16: "S_issued", 0: "start", 1: "tile_begin", 2: "S_ready", 3: "S_loaded", 4: "max_done", 5: "OF_ok", 6: "exp_done", 7: "PF_arrived", 8: "end"}
 prev = t0
 for slot, t in ev[:int(sys.argv[1]) if len(sys.argv) > 1 else 10000]:
     print(f"{names[slot]:>11s} t={t - t0:7d} d={t - prev:6d}")

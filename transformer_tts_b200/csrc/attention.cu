@@ -71,6 +71,39 @@ __device__ __forceinline__ float poly_exp2(float x) {
   return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
 }
 
+// Packed variant (TTSB_POLY2 = pairs per group of 8 elements that take the FMA pipe instead of MUFU.EX2): the two
+// softmax warps that share an SM sub-partition contend for its 4-lane MUFU (a warp-wide EX2 holds it for 8 clk),
+// which is what the exponential phase of a tile is bound by; FFMA2/FADD2 evaluate two elements per issue slot.
+#ifndef TTSB_POLY2
+#define TTSB_POLY2 0
+#endif
+constexpr int kPoly2 = TTSB_POLY2;
+__device__ __forceinline__ void poly_exp2x2(float& x, float& y) {
+  x = fmaxf(x, -126.f);
+  y = fmaxf(y, -126.f);
+  float tx = x, ty = y;
+  add2(tx, ty, 12582912.f, 12582912.f);            // t = x + 1.5 * 2^23: low mantissa bits hold round(x)
+  float rx = tx, ry = ty;
+  add2(rx, ry, -12582912.f, -12582912.f);          // r = round(x)
+  fma2(rx, ry, -1.f, -1.f, x, y);                  // f = x - r in [-0.5, 0.5]
+  float px = rx, py = ry;
+  fma2(px, py, 0.0096181291f, 0.0096181291f, 0.0555041087f, 0.0555041087f);
+  fma2(px, py, rx, ry, 0.2402265070f, 0.2402265070f);
+  fma2(px, py, rx, ry, 0.6931471806f, 0.6931471806f);
+  fma2(px, py, rx, ry, 1.0f, 1.0f);
+  x = __int_as_float(__float_as_int(px) + (__float_as_int(tx) << 23));
+  y = __int_as_float(__float_as_int(py) + (__float_as_int(ty) << 23));
+}
+
+constexpr int kSk0 = 4, kSk1 = 2;   // k-steps of S: dims [0,64) with Q from TMEM, dims [64,96) with Q from smem
+constexpr int kPVk = kBKV / 16;     // k-steps of P V
+
+__device__ __forceinline__ void att_tma_store_3d(const CUtensorMap* m, uint32_t src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(src), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+
 enum {
   BAR_Q = 0,
   BAR_KF,                       // [3] K stage filled
@@ -90,9 +123,13 @@ enum {
 __global__ void __launch_bounds__(kAttThreads, 2)
 attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmQ32,
                      const __grid_constant__ CUtensorMap tmKV, const __grid_constant__ CUtensorMap tmKV32,
+                     const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmO32,
                      const uint8_t* __restrict__ mask, const int32_t* __restrict__ kv_info,
-                     __nv_bfloat16* __restrict__ ctx, float* __restrict__ lse2, int T, int H, float scale_log2) {
+                     float* __restrict__ lse2, int T, int H, float scale_log2) {
   extern __shared__ uint8_t smem_raw[];
+#if defined(TTSB_ATT_TRACE)
+  const long long t_entry = clock64();
+#endif
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
   uint8_t* sQ = smem;
@@ -127,32 +164,44 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     tma_load_3d(smem_u32(sV + vs * kKVBytes), &tmKV, vf, 2 * D + h * kDh, j * kBKV, b);
     tma_load_3d(smem_u32(sV + vs * kKVBytes + kKVBox0), &tmKV32, vf, 2 * D + h * kDh + 64, j * kBKV, b);
   };
-  if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmQ);
-    tma_prefetch_desc(&tmQ32);
-    tma_prefetch_desc(&tmKV);
-    tma_prefetch_desc(&tmKV32);
-    for (int i = 0; i < BAR_COUNT; ++i)
-      mbar_init(smem_u32(&bars[i]), (i == BAR_PF || i == BAR_PF + 1 || i == BAR_QT) ? 128 : 1);
-    fence_mbar_init();
-    // the first loads go out before the TMEM allocation and the CTA-wide sync: only this thread touches these
-    // barriers until then
-    const uint32_t qb = smem_u32(&bars[BAR_Q]);
-    mbar_arrive_expect_tx(qb, kQBytes);
-    tma_load_3d(smem_u32(sQ), &tmQ, qb, h * kDh, q0, b);
-    tma_load_3d(smem_u32(sQ + kQBox0), &tmQ32, qb, h * kDh + 64, q0, b);
-    load_k(0);
-    if (nkv > 1) load_k(1);
-    load_v(0);
-    if (nkv > 1) load_v(1);
+  // Prologue.  Thread 0 initialises the barriers and then issues ten TMA loads (~150 clk each for the issuing
+  // thread); the other warps only need the barriers and the TMEM base, so warp 0 ARRIVES on the start barrier and
+  // the rest SYNC on it: nobody waits for the load issue (this was ~1500 clk of every CTA's 3900-clk prologue).
+  if (warp == 0) {
+    if (lane == 0) {
+      tma_prefetch_desc(&tmQ);
+      tma_prefetch_desc(&tmQ32);
+      tma_prefetch_desc(&tmKV);
+      tma_prefetch_desc(&tmKV32);
+      for (int i = 0; i < BAR_COUNT; ++i)
+        mbar_init(smem_u32(&bars[i]), (i == BAR_PF || i == BAR_PF + 1 || i == BAR_QT) ? 128 : 1);
+      fence_mbar_init();
+    }
+    __syncwarp();
+    asm volatile("bar.arrive 2, %0;" ::"n"(kAttThreads) : "memory");
+    if (lane == 0) {
+      const uint32_t qb = smem_u32(&bars[BAR_Q]);
+      mbar_arrive_expect_tx(qb, kQBytes);
+      tma_load_3d(smem_u32(sQ), &tmQ, qb, h * kDh, q0, b);
+      tma_load_3d(smem_u32(sQ + kQBox0), &tmQ32, qb, h * kDh + 64, q0, b);
+      load_k(0);
+      load_v(0);
+      if (nkv > 1) {
+        load_k(1);
+        load_v(1);
+      }
+      tma_prefetch_desc(&tmO);
+      tma_prefetch_desc(&tmO32);
+    }
+  } else {
+    if (warp == 1) {
+      tmem_alloc(smem_u32(tmem_slot), kAttTmemCols);
+      tmem_relinquish();
+    }
+    tc_fence_before();
+    asm volatile("bar.sync 2, %0;" ::"n"(kAttThreads) : "memory");
+    tc_fence_after();
   }
-  if (warp == 1) {
-    tmem_alloc(smem_u32(tmem_slot), kAttTmemCols);
-    tmem_relinquish();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t tmem_O = tmem_base + 128;
 
@@ -183,27 +232,32 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
     const uint32_t q_base = smem_u32(sQ);
     const uint32_t leader = elect_one();
-    // S_j = Q K_j^T goes to S buffer j & 1 and is issued up to two tiles ahead of O += P_j V_j
-    auto issue_s = [&](int j) {
+#if defined(TTSB_ATT_TRACE)
+    const bool tr_on = TTSB_ATT_TRACE == 2 && blockIdx.x == 4 && blockIdx.y == 1 && blockIdx.z == 10 && lane == 0;
+    int tr_n = 0;
+#endif
+    // S_j = Q K_j^T goes to S buffer j & 1 and is issued up to two tiles ahead of O += P_j V_j.
+    // S buffer j & 1 last held P_{j-2}: P_{j-2} V_{j-2} was issued by this warp before S_j and the tensor pipe
+    // executes one thread's MMAs in issue order, so the overwrite needs no barrier.
+    auto s_mmas = [&](int j) {  // leader lane only
       const int ks = j % kKStages;
-      mbar_wait(smem_u32(&bars[BAR_KF + ks]), (j / kKStages) & 1);
-      // S buffer j & 1 last held P_{j-2}: P_{j-2} V_{j-2} was issued by this warp before this MMA and the tensor
-      // pipe executes one thread's MMAs in issue order, so the overwrite needs no barrier
-      tc_fence_after();
       const uint32_t k_base = smem_u32(sK + ks * kKVBytes);
       const uint32_t d_tmem = tb + (j & 1) * kBKV;
-      if (leader) {
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk)  // dims [0,64): Q from TMEM (columns [224,256), 8 packed columns per k-step)
-          umma_bf16_ts(d_tmem, tb + kTmemQ + kk * 8, umma_smem_desc(k_base + kk * 32, 16, 1024, kLayoutSW128), idesc_s,
-                       kk != 0);
+      for (int kk = 0; kk < kSk0; ++kk)  // dims [0,64): Q from TMEM (columns [224,256), 8 packed columns per k-step)
+        umma_bf16_ts(d_tmem, tb + kTmemQ + kk * 8, umma_smem_desc(k_base + kk * 32, 16, 1024, kLayoutSW128), idesc_s,
+                     kk != 0);
 #pragma unroll
-        for (int kk = 0; kk < 2; ++kk)  // dims [64,96): 64-byte rows
-          umma_bf16(d_tmem, umma_smem_desc(q_base + kQBox0 + kk * 32, 16, 512, kLayoutSW64),
-                    umma_smem_desc(k_base + kKVBox0 + kk * 32, 16, 512, kLayoutSW64), idesc_s, 1u);
-        umma_commit(smem_u32(&bars[BAR_KE + ks]));
-        umma_commit(smem_u32(&bars[BAR_SF + (j & 1)]));
-      }
+      for (int kk = 0; kk < kSk1; ++kk)  // dims [64,96): 64-byte rows
+        umma_bf16(d_tmem, umma_smem_desc(q_base + kQBox0 + kk * 32, 16, 512, kLayoutSW64),
+                  umma_smem_desc(k_base + kKVBox0 + kk * 32, 16, 512, kLayoutSW64), idesc_s, 1u);
+      umma_commit(smem_u32(&bars[BAR_KE + ks]));
+      umma_commit(smem_u32(&bars[BAR_SF + (j & 1)]));
+    };
+    auto issue_s = [&](int j) {
+      mbar_wait(smem_u32(&bars[BAR_KF + j % kKStages]), (j / kKStages) & 1);
+      tc_fence_after();
+      if (leader) s_mmas(j);
       __syncwarp();
     };
     mbar_wait(smem_u32(&bars[BAR_Q]), 0);
@@ -213,13 +267,20 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     if (nkv > 1) issue_s(1);
     for (int j = 0; j < nkv; ++j) {
       const int vs = j % kVStages;
-      mbar_wait(smem_u32(&bars[BAR_PF + (j & 1)]), (j >> 1) & 1);
-      mbar_wait(smem_u32(&bars[BAR_VF + vs]), (j / kVStages) & 1);
+      const bool more = j + 2 < nkv;
+      ATT_TR(10);
+      // ONE wait for everything this iteration consumes — P_j (softmax), V_j and K_{j+2} (TMA, both long landed):
+      // a poll of a completed barrier still costs the issuer ~150 clk, and this warp's round trip (P_j ready ->
+      // S_{j+2} ready) is half of the tile period, so three polls in a row were ~20 % of it.
+      const uint32_t vf = smem_u32(&bars[BAR_VF + vs]), vpar = (j / kVStages) & 1;
+      mbar_wait3(smem_u32(&bars[BAR_PF + (j & 1)]), (j >> 1) & 1, vf, vpar,
+                 more ? smem_u32(&bars[BAR_KF + (j + 2) % kKStages]) : vf, more ? ((j + 2) / kKStages) & 1 : vpar);
+      ATT_TR(12);
       tc_fence_after();
       const uint32_t v_base = smem_u32(sV + vs * kKVBytes);
       if (leader) {
 #pragma unroll
-        for (int kk = 0; kk < kBKV / 16; ++kk) {
+        for (int kk = 0; kk < kPVk; ++kk) {
           // A = P read from TMEM (16 keys = 8 packed columns per MMA), never through shared memory;
           // B = V: 16 rows of 128 B (box 0) / of 64 B (box 1); SBO = 8 rows
           const uint32_t a_tmem = tb + (j & 1) * kBKV + kk * 8;
@@ -230,9 +291,10 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         }
         umma_commit(smem_u32(&bars[BAR_VE + vs]));
         umma_commit(smem_u32(&bars[BAR_OF + (j & 1)]));
+        if (more) s_mmas(j + 2);
       }
       __syncwarp();
-      if (j + 2 < nkv) issue_s(j + 2);
+      ATT_TR(13);
     }
   } else {
     // ===================== softmax / output warps: thread == query row =====================
@@ -248,8 +310,17 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     // Q dims [0,64) -> TMEM once per CTA: the S MMAs then read their A operand from TMEM and only K from shared
     // memory.  The kernel is shared-memory-bandwidth bound (per 64-key tile and CTA: 36 KB of Q/K operand reads for
     // S, 12 KB of V for P V, 24 KB of TMA writes; 128 B/clk/SM), and re-reading Q for every key tile was 16 KB of it.
+#if defined(TTSB_ATT_TRACE)
+    long long t_sync, t_q;
+#endif
     {
+#if defined(TTSB_ATT_TRACE)
+      t_sync = clock64();
+#endif
       mbar_wait(smem_u32(&bars[BAR_Q]), 0);
+#if defined(TTSB_ATT_TRACE)
+      t_q = clock64();
+#endif
       const uint8_t* qrow = sQ + row * 128;  // SWIZZLE_128B box: 16-byte chunk c of row r sits at (c ^ (r & 7)) * 16
       uint32_t qv[32];
 #pragma unroll
@@ -265,6 +336,11 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
 #if defined(TTSB_ATT_TRACE)
     const bool tr_on = TTSB_ATT_TRACE == 1 && blockIdx.x == 4 && blockIdx.y == 1 && blockIdx.z == 10 && threadIdx.x == 64;
     int tr_n = 0;
+    if (tr_on) {
+      g_att_trace[tr_n++] = (9LL << 56) | (t_entry & 0xFFFFFFFFFFFFFFLL);
+      g_att_trace[tr_n++] = (20LL << 56) | (t_sync & 0xFFFFFFFFFFFFFFLL);
+      g_att_trace[tr_n++] = (21LL << 56) | (t_q & 0xFFFFFFFFFFFFFFLL);
+    }
 #endif
     ATT_TR(0);
 
@@ -362,13 +438,22 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         // packed f32x2 scale-subtract and row-sum (FFMA2 / FADD2): the softmax warps are issue-bound, MUFU.EX2
         // (16/clk/SM) is the only per-element instruction that cannot be paired
 #pragma unroll
-        for (int i = 0; i < 32; i += 4) {
-          fma2(v[i], v[i + 1], sc, sc, neg_m, neg_m);
-          fma2(v[i + 2], v[i + 3], sc, sc, neg_m, neg_m);
-          v[i] = fast_exp2(v[i]); v[i + 1] = fast_exp2(v[i + 1]);
-          v[i + 2] = fast_exp2(v[i + 2]); v[i + 3] = fast_exp2(v[i + 3]);
+        for (int i = 0; i < 32; i += 8) {
+#pragma unroll
+          for (int p = 0; p < 4; ++p) fma2(v[i + 2 * p], v[i + 2 * p + 1], sc, sc, neg_m, neg_m);
+#pragma unroll
+          for (int p = 0; p < 4; ++p) {
+            if (p < kPoly2) {
+              poly_exp2x2(v[i + 2 * p], v[i + 2 * p + 1]);
+            } else {
+              v[i + 2 * p] = fast_exp2(v[i + 2 * p]);
+              v[i + 2 * p + 1] = fast_exp2(v[i + 2 * p + 1]);
+            }
+          }
           add2(ls4[0], ls4[1], v[i], v[i + 1]);
           add2(ls4[2], ls4[3], v[i + 2], v[i + 3]);
+          add2(ls4[0], ls4[1], v[i + 4], v[i + 5]);
+          add2(ls4[2], ls4[3], v[i + 6], v[i + 7]);
         }
 #endif
       }
@@ -393,23 +478,37 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     const float inv = 1.f / l;
     // training: log2-domain log-sum-exp of the row, p = exp2(s*scale_log2 - lse2) in the backward kernels
     if (lse2 != nullptr && t < T) lse2[(static_cast<int64_t>(b) * H + h) * T + t] = m + log2f(l);
-    __nv_bfloat16* op = ctx + (static_cast<int64_t>(b) * T + (t < T ? t : 0)) * D + h * kDh;
+    // O / l -> bf16 -> the (dead) Q staging buffer in the layout of the two TMA boxes (128-byte rows SWIZZLE_128B for
+    // dims [0,64), 64-byte rows SWIZZLE_64B for [64,96)), then two TMA stores per CTA.  Row-per-thread 16-byte global
+    // stores cost one LSU wavefront per row and instruction (~2000 clk per CTA, ncu: long_sb on the next TMEM load);
+    // the TMA store also clips the rows beyond T.  Every S MMA (the last reader of the Q buffer) retired before
+    // BAR_OF of the last tile completed.
+    uint8_t* orow0 = sQ + row * 128;
+    uint8_t* orow1 = sQ + kQBox0 + row * 64;
 #pragma unroll
     for (int c = 0; c < kDh; c += 32) {
       float o[32];
       tmem_ld32(tmem_O + lane_off + c, o);
       tmem_ld_wait();
-      if (t < T) {
 #pragma unroll
-        for (int i = 0; i < 32; i += 8) {
-          uint4 u;
-          u.x = pack_bf16(o[i] * inv, o[i + 1] * inv);
-          u.y = pack_bf16(o[i + 2] * inv, o[i + 3] * inv);
-          u.z = pack_bf16(o[i + 4] * inv, o[i + 5] * inv);
-          u.w = pack_bf16(o[i + 6] * inv, o[i + 7] * inv);
-          *reinterpret_cast<uint4*>(op + c + i) = u;
-        }
+      for (int i = 0; i < 32; i += 8) {
+        uint4 u;
+        u.x = pack_bf16(o[i] * inv, o[i + 1] * inv);
+        u.y = pack_bf16(o[i + 2] * inv, o[i + 3] * inv);
+        u.z = pack_bf16(o[i + 4] * inv, o[i + 5] * inv);
+        u.w = pack_bf16(o[i + 6] * inv, o[i + 7] * inv);
+        const int g = (c + i) >> 3;  // 16-byte chunk of the row, compile-time after unrolling
+        if (g < 8) *reinterpret_cast<uint4*>(orow0 + ((g ^ (row & 7)) << 4)) = u;
+        else *reinterpret_cast<uint4*>(orow1 + (((g - 8) ^ ((row >> 1) & 3)) << 4)) = u;
       }
+    }
+    fence_async_smem();  // generic-proxy writes -> visible to the TMA engine
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    if (st == 0) {
+      att_tma_store_3d(&tmO, smem_u32(sQ), h * kDh, q0, b);
+      att_tma_store_3d(&tmO32, smem_u32(sQ + kQBox0), h * kDh + 64, q0, b);
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // smem must outlive the reads of the stores
     }
     tc_fence_before();
     ATT_TR(8);
@@ -491,6 +590,13 @@ extern "C" int ttsb200_attention_fwd_lse(const void* qkv, const uint8_t* mask, c
   if (rc) return rc;
   rc = make_tmap_bf16(&tmKV32, qkv, 3, dims, strides, box_kv32, CU_TENSOR_MAP_SWIZZLE_64B);
   if (rc) return rc;
+  CUtensorMap tmO, tmO32;  // ctx (B, T, H*Dh): the store boxes have the shape of the Q boxes
+  const uint64_t odims[3] = {static_cast<uint64_t>(H) * Dh, static_cast<uint64_t>(T), static_cast<uint64_t>(B)};
+  const uint64_t ostrides[2] = {odims[0] * 2, odims[0] * 2 * static_cast<uint64_t>(T)};
+  rc = make_tmap_bf16(&tmO, ctx, 3, odims, ostrides, box_q, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc) return rc;
+  rc = make_tmap_bf16(&tmO32, ctx, 3, odims, ostrides, box_q32, CU_TENSOR_MAP_SWIZZLE_64B);
+  if (rc) return rc;
   static bool attr_done = false;
   if (!attr_done) {
     TTSB_CHECK_CUDA(cudaFuncSetAttribute(attention_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -500,7 +606,7 @@ extern "C" int ttsb200_attention_fwd_lse(const void* qkv, const uint8_t* mask, c
   dim3 grid((T + kBQ - 1) / kBQ, H, B);
   const float scale_log2 = kLog2e / sqrtf(static_cast<float>(Dh));
   attention_fwd_kernel<<<grid, kAttThreads, kAttSmem, static_cast<cudaStream_t>(s)>>>(
-      tmQ, tmQ32, tmKV, tmKV32, mask, kv_info, static_cast<__nv_bfloat16*>(ctx), lse2, T, H, scale_log2);
+      tmQ, tmQ32, tmKV, tmKV32, tmO, tmO32, mask, kv_info, lse2, T, H, scale_log2);
   TTSB_CHECK_CUDA(cudaGetLastError());
   return TTSB_OK;
 }

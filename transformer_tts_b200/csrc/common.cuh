@@ -114,6 +114,35 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   }
 }
 
+// Waits for three barriers at once: the three try_waits are in flight together, so a wait whose barriers have all
+// completed costs one barrier round trip (~150 clk for a whole-warp poll) instead of three.
+__device__ __forceinline__ void mbar_wait3(uint32_t b0, uint32_t p0, uint32_t b1, uint32_t p1, uint32_t b2,
+                                           uint32_t p2) {
+  uint32_t spins = 0;
+  while (true) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred q0, q1, q2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 q0, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 q1, [%3], %4;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 q2, [%5], %6;\n\t"
+        "and.pred q0, q0, q1;\n\t"
+        "and.pred q0, q0, q2;\n\t"
+        "selp.b32 %0, 1, 0, q0;\n\t"
+        "}\n"
+        : "=r"(ok)
+        : "r"(b0), "r"(p0), "r"(b1), "r"(p1), "r"(b2), "r"(p2)
+        : "memory");
+    if (ok) break;
+    if (++spins > (1u << 26)) {
+      printf("ttsb200: mbarrier timeout block(%d,%d,%d) thread %d bars %u %u %u\n", blockIdx.x, blockIdx.y,
+             blockIdx.z, threadIdx.x, b0, b1, b2);
+      __trap();
+    }
+  }
+}
+
 // ---- TMA -------------------------------------------------------------------------------------
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
