@@ -22,7 +22,13 @@ namespace ttsb {
 constexpr int kDh = 96;
 constexpr int kBQ = 128;
 constexpr int kBKV = 64;                       // keys per tile
-constexpr int kAttThreads = 192;
+// Softmax column halves (threads per query row): 2 = eight softmax warps per CTA.  -DTTSB_ATT_HALVES=1 builds the
+// one-thread-per-row kernel.
+#ifndef TTSB_ATT_HALVES
+#define TTSB_ATT_HALVES 1
+#endif
+constexpr int kAttHalves = TTSB_ATT_HALVES;
+constexpr int kAttThreads = 64 + 128 * kAttHalves;
 // A head's 96 dims are fetched as one 64-dim box (128-byte rows, SWIZZLE_128B) and one 32-dim box (64-byte rows,
 // SWIZZLE_64B): the TMA engine is paced by 128-byte lines, and three 64-byte boxes per row made the kernel
 // TMA-bound (19 B/clk/SM, 176 us with the softmax arithmetic removed).
@@ -35,7 +41,7 @@ constexpr int kKVBytes = kKVBox0 + kKVBox1;    // 12 KB
 constexpr int kKStages = 2;
 constexpr int kVStages = 2;
 constexpr int kAttSmem = kQBytes + (kKStages + kVStages) * kKVBytes + 1024 /*align*/ + 256 /*barriers*/ +
-                         256 /*flags*/;
+                         256 /*flags*/ + 6 * kBQ * 4 /*row max / row sum exchange between the column halves*/;
 constexpr int kTmemQ = 224;                    // Q dims [0,64) as packed bf16 pairs: columns [224,256)
 constexpr int kAttTmemCols = 256;              // S0 [0,64) S1 [64,128) O [128,224); P_j (bf16 pairs) overwrites the
                                                // first 32 columns of its own S buffer once S_j sits in registers
@@ -120,7 +126,8 @@ enum {
 // v3: 64-key tiles, K triple- and V double-buffered in smem, S double-buffered in TMEM, so that neither a TMA
 // round trip nor the S -> registers copy sits on the per-tile critical path (v2 had single K/V buffers: its
 // per-tile time was 181 us of 226 us with the softmax arithmetic removed).
-__global__ void __launch_bounds__(kAttThreads, 2)
+template <int NH>
+__global__ void __launch_bounds__(64 + 128 * NH, 2)
 attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmQ32,
                      const __grid_constant__ CUtensorMap tmKV, const __grid_constant__ CUtensorMap tmKV32,
                      const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmO32,
@@ -138,6 +145,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
   uint64_t* bars = reinterpret_cast<uint64_t*>(sV + kVStages * kKVBytes);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + BAR_COUNT);
   uint8_t* sflag = reinterpret_cast<uint8_t*>(tmem_slot + 4);  // [2][64] key flags of a tile outside the clean prefix
+  float* sxch = reinterpret_cast<float*>(sflag + 240);         // [2 S buffers + final][2 halves][128 rows]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -174,11 +182,11 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       tma_prefetch_desc(&tmKV);
       tma_prefetch_desc(&tmKV32);
       for (int i = 0; i < BAR_COUNT; ++i)
-        mbar_init(smem_u32(&bars[i]), (i == BAR_PF || i == BAR_PF + 1 || i == BAR_QT) ? 128 : 1);
+        mbar_init(smem_u32(&bars[i]), (i == BAR_PF || i == BAR_PF + 1 || i == BAR_QT) ? 128 * NH : 1);
       fence_mbar_init();
     }
     __syncwarp();
-    asm volatile("bar.arrive 2, %0;" ::"n"(kAttThreads) : "memory");
+    asm volatile("bar.arrive 2, %0;" ::"n"(64 + 128 * NH) : "memory");
     if (lane == 0) {
       const uint32_t qb = smem_u32(&bars[BAR_Q]);
       mbar_arrive_expect_tx(qb, kQBytes);
@@ -199,7 +207,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       tmem_relinquish();
     }
     tc_fence_before();
-    asm volatile("bar.sync 2, %0;" ::"n"(kAttThreads) : "memory");
+    asm volatile("bar.sync 2, %0;" ::"n"(64 + 128 * NH) : "memory");
     tc_fence_after();
   }
   const uint32_t tmem_base = *tmem_slot;
@@ -297,19 +305,26 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       ATT_TR(13);
     }
   } else {
-    // ===================== softmax / output warps: thread == query row =====================
+    // ===================== softmax / output warps =====================
+    // NH = 1: thread == query row.  NH = 2: two threads per row — warps 2..5 take key columns [0,32) of every tile,
+    // warps 6..9 columns [32,64) (a warp reaches the TMEM lane quarter warp % 4, so warps w and w + 4 share rows).
+    // The tile period is a round trip (softmax chain + issuer chain) / 2, and with one softmax warp per CTA and
+    // sub-partition the chain is latency-bound; four shorter chains per sub-partition keep its MUFU busy.
+    constexpr int CW = kBKV / NH;     // S columns per thread
+    constexpr int OW = kDh / NH;      // O columns per thread in the rescale / output passes
     const int q = warp & 3;
+    const int half = NH == 1 ? 0 : (warp - 2) >> 2;
     const int row = q * 32 + lane;
-    const int st = threadIdx.x - 64;  // 0..127 among softmax threads
+    const int st = threadIdx.x - 64;  // 0 .. 128 * NH - 1 among softmax threads
     const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
     const float masked = -1e4f * kLog2e;  // reference fill value (modules.py:14), in log2 units
     // m is the reference point of the exponentials, not necessarily the running maximum: it is only
     // moved (and O, l rescaled) when the maximum has grown by more than 2^8, so p <= 256 stays well
-    // inside bf16/fp32 range and the final O / l is unchanged.
+    // inside bf16/fp32 range and the final O / l is unchanged.  With NH = 2 both threads of a row hold the same m
+    // and a partial l each.
     float m = -INFINITY, l = 0.f;
     // Q dims [0,64) -> TMEM once per CTA: the S MMAs then read their A operand from TMEM and only K from shared
-    // memory.  The kernel is shared-memory-bandwidth bound (per 64-key tile and CTA: 36 KB of Q/K operand reads for
-    // S, 12 KB of V for P V, 24 KB of TMA writes; 128 B/clk/SM), and re-reading Q for every key tile was 16 KB of it.
+    // memory (re-reading Q for every key tile was 16 KB of the 72 KB of shared-memory traffic per tile).
 #if defined(TTSB_ATT_TRACE)
     long long t_sync, t_q;
 #endif
@@ -322,13 +337,15 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       t_q = clock64();
 #endif
       const uint8_t* qrow = sQ + row * 128;  // SWIZZLE_128B box: 16-byte chunk c of row r sits at (c ^ (r & 7)) * 16
-      uint32_t qv[32];
+      uint32_t qv[32 / NH];
 #pragma unroll
-      for (int c = 0; c < 8; ++c) {
-        const uint4 u = *reinterpret_cast<const uint4*>(qrow + ((c ^ (row & 7)) << 4));
+      for (int c = 0; c < 8 / NH; ++c) {
+        const int cc = c + half * (8 / NH);
+        const uint4 u = *reinterpret_cast<const uint4*>(qrow + ((cc ^ (row & 7)) << 4));
         qv[4 * c] = u.x; qv[4 * c + 1] = u.y; qv[4 * c + 2] = u.z; qv[4 * c + 3] = u.w;
       }
-      tmem_st32(tmem_base + kTmemQ + lane_off, reinterpret_cast<const float*>(qv));
+      if constexpr (NH == 1) tmem_st32(tmem_base + kTmemQ + lane_off, reinterpret_cast<const float*>(qv));
+      else tmem_st16(tmem_base + kTmemQ + lane_off + half * 16, qv);
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(smem_u32(&bars[BAR_QT]));
@@ -354,38 +371,45 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
           const int key = j * kBKV + st;
           flg[st] = key < T ? (mask[static_cast<int64_t>(b) * T + key] ? 1 : 0) : 2;
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, %0;" ::"n"(128 * NH) : "memory");
       }
       ATT_TR(1);
       mbar_wait(smem_u32(&bars[BAR_SF + sb]), (j >> 1) & 1);
       tc_fence_after();
       ATT_TR(2);
-      float s[kBKV];
+      float s[CW];
 #pragma unroll
-      for (int c = 0; c < kBKV; c += 32) tmem_ld32(tmem_base + sb * kBKV + lane_off + c, s + c);
+      for (int c = 0; c < CW; c += 32) tmem_ld32(tmem_base + sb * kBKV + lane_off + half * CW + c, s + c);
       tmem_ld_wait();
       ATT_TR(3);
       // scores in log2 units, masked like the reference (-1e4 fill; keys beyond T do not exist)
       float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
       if (clean) {
 #pragma unroll
-        for (int i = 0; i < kBKV; i += 8) {  // three-input max: half the issue slots
+        for (int i = 0; i < CW; i += 8) {  // three-input max: half the issue slots
           mx4[0] = max3(mx4[0], s[i], s[i + 4]); mx4[1] = max3(mx4[1], s[i + 1], s[i + 5]);
           mx4[2] = max3(mx4[2], s[i + 2], s[i + 6]); mx4[3] = max3(mx4[3], s[i + 3], s[i + 7]);
         }
       } else {
 #pragma unroll
-        for (int i = 0; i < kBKV; ++i) {
-          const uint8_t f = flg[i];
+        for (int i = 0; i < CW; ++i) {
+          const uint8_t f = flg[half * CW + i];
           s[i] = f == 1 ? s[i] * scale_log2 : (f == 0 ? masked : -INFINITY);
           mx4[i & 3] = fmaxf(mx4[i & 3], s[i]);
         }
       }
       float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+      if constexpr (NH == 2) {
+        // the row maximum over both column halves: exchanged through shared memory, one 64-thread named barrier per
+        // lane quarter (the two warps that share these rows)
+        sxch[(sb * 2 + half) * kBQ + row] = mx;
+        asm volatile("bar.sync %0, 64;" ::"r"(3 + q) : "memory");
+        mx = fmaxf(mx, sxch[(sb * 2 + (half ^ 1)) * kBQ + row]);
+      }
       if (clean) mx *= scale_log2;  // the positive scale commutes with max
       ATT_TR(4);
       ATT_TR(5);
-      const bool grow = mx > m + 8.f;  // also true on the first tile (m = -inf)
+      const bool grow = mx > m + 8.f;  // also true on the first tile (m = -inf); identical in both halves
       if (__any_sync(0xffffffffu, grow)) {
         // the (rare) rescale of O needs P_{j-1} V_{j-1} retired
         if (j > 0) {
@@ -398,27 +422,27 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         m = m_new;
         if (j > 0) {
 #pragma unroll
-          for (int c = 0; c < kDh; c += 32) {
-            float o[32];
-            tmem_ld32(tmem_O + lane_off + c, o);
+          for (int c = 0; c < OW; c += 16) {
+            float o[16];
+            tmem_ld16(tmem_O + lane_off + half * OW + c, o);
             tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) o[i] *= alpha;
-            tmem_st32(tmem_O + lane_off + c, o);
+            for (int i = 0; i < 16; ++i) o[i] *= alpha;
+            tmem_st16(tmem_O + lane_off + half * OW + c, reinterpret_cast<const uint32_t*>(o));
           }
           tmem_st_wait();
         }
       }
-      // p = exp2(s - m) -> bf16 -> swizzled smem; fp32 row sum (four independent partial sums)
+      // p = exp2(s - m) -> bf16; fp32 row sum (four independent partial sums)
       float ls4[4] = {0.f, 0.f, 0.f, 0.f};
       const float neg_m = -m;
       const float sc = clean ? scale_log2 : 1.f;  // masked tiles were scaled while masking
 #if defined(TTSB_ATT_EXP) && TTSB_ATT_EXP >= 2
-      ls4[0] = s[0] + s[37] + s[59] + neg_m * sc;  // timing experiment only: no exponentials, no P stores
+      ls4[0] = s[0] + s[CW / 2] + s[CW - 1] + neg_m * sc;  // timing experiment only: no exponentials, no P stores
       for (int c = 0; c < 0; c += 32) {
 #else
 #pragma unroll
-      for (int c = 0; c < kBKV; c += 32) {
+      for (int c = 0; c < CW; c += 32) {
 #endif
         float* v = s + c;
 #if defined(TTSB_ATT_EXP) || TTSB_POLY
@@ -428,15 +452,15 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
           v[i] = fmaf(v[i], sc, neg_m);  // timing experiment only: no exponential
 #else
           // experiment (TTSB_POLY): part of the elements on the FMA pipe (round-to-nearest split + degree-4
-          // polynomial) instead of MUFU.EX2 — measured slower, the softmax warps are issue-bound
+          // polynomial) instead of MUFU.EX2 — measured slower
           if ((i & 3) < kPolyOf4) v[i] = poly_exp2(fmaf(v[i], sc, neg_m));
           else v[i] = fast_exp2(fmaf(v[i], sc, neg_m));
 #endif
           ls4[i & 3] += v[i];
         }
 #else
-        // packed f32x2 scale-subtract and row-sum (FFMA2 / FADD2): the softmax warps are issue-bound, MUFU.EX2
-        // (16/clk/SM) is the only per-element instruction that cannot be paired
+        // packed f32x2 scale-subtract and row-sum (FFMA2 / FADD2); MUFU.EX2 (16/clk/SM) is the only per-element
+        // instruction that cannot be paired
 #pragma unroll
         for (int i = 0; i < 32; i += 8) {
 #pragma unroll
@@ -459,10 +483,11 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       }
       // P (bf16 pairs, key 2c in the low half of column c) -> this thread's TMEM lane: the A operand of P V
       {
-        uint32_t pk[kBKV / 2];
+        uint32_t pk[CW / 2];
 #pragma unroll
-        for (int i = 0; i < kBKV / 2; ++i) pk[i] = pack_bf16(s[2 * i], s[2 * i + 1]);
-        tmem_st32(tmem_base + sb * kBKV + lane_off, reinterpret_cast<const float*>(pk));
+        for (int i = 0; i < CW / 2; ++i) pk[i] = pack_bf16(s[2 * i], s[2 * i + 1]);
+        if constexpr (NH == 1) tmem_st32(tmem_base + sb * kBKV + lane_off, reinterpret_cast<const float*>(pk));
+        else tmem_st16(tmem_base + sb * kBKV + lane_off + half * 16, pk);
         tmem_st_wait();
       }
       l += (ls4[0] + ls4[1]) + (ls4[2] + ls4[3]);
@@ -472,12 +497,17 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       ATT_TR(7);
     }
     // ---- O / l ----
+    if constexpr (NH == 2) {  // the row sum over both column halves (its own exchange slots: no reuse hazard)
+      sxch[(4 + half) * kBQ + row] = l;
+      asm volatile("bar.sync %0, 64;" ::"r"(3 + q) : "memory");
+      l += sxch[(4 + (half ^ 1)) * kBQ + row];
+    }
     mbar_wait(smem_u32(&bars[BAR_OF + ((nkv - 1) & 1)]), ((nkv - 1) >> 1) & 1);
     tc_fence_after();
     const int t = q0 + row;
     const float inv = 1.f / l;
     // training: log2-domain log-sum-exp of the row, p = exp2(s*scale_log2 - lse2) in the backward kernels
-    if (lse2 != nullptr && t < T) lse2[(static_cast<int64_t>(b) * H + h) * T + t] = m + log2f(l);
+    if (lse2 != nullptr && t < T && half == 0) lse2[(static_cast<int64_t>(b) * H + h) * T + t] = m + log2f(l);
     // O / l -> bf16 -> the (dead) Q staging buffer in the layout of the two TMA boxes (128-byte rows SWIZZLE_128B for
     // dims [0,64), 64-byte rows SWIZZLE_64B for [64,96)), then two TMA stores per CTA.  Row-per-thread 16-byte global
     // stores cost one LSU wavefront per row and instruction (~2000 clk per CTA, ncu: long_sb on the next TMEM load);
@@ -486,24 +516,24 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     uint8_t* orow0 = sQ + row * 128;
     uint8_t* orow1 = sQ + kQBox0 + row * 64;
 #pragma unroll
-    for (int c = 0; c < kDh; c += 32) {
-      float o[32];
-      tmem_ld32(tmem_O + lane_off + c, o);
+    for (int c = 0; c < OW; c += 16) {
+      float o[16];
+      tmem_ld16(tmem_O + lane_off + half * OW + c, o);
       tmem_ld_wait();
 #pragma unroll
-      for (int i = 0; i < 32; i += 8) {
+      for (int i = 0; i < 16; i += 8) {
         uint4 u;
         u.x = pack_bf16(o[i] * inv, o[i + 1] * inv);
         u.y = pack_bf16(o[i + 2] * inv, o[i + 3] * inv);
         u.z = pack_bf16(o[i + 4] * inv, o[i + 5] * inv);
         u.w = pack_bf16(o[i + 6] * inv, o[i + 7] * inv);
-        const int g = (c + i) >> 3;  // 16-byte chunk of the row, compile-time after unrolling
+        const int g = (half * OW + c + i) >> 3;  // 16-byte chunk of the row
         if (g < 8) *reinterpret_cast<uint4*>(orow0 + ((g ^ (row & 7)) << 4)) = u;
         else *reinterpret_cast<uint4*>(orow1 + (((g - 8) ^ ((row >> 1) & 3)) << 4)) = u;
       }
     }
     fence_async_smem();  // generic-proxy writes -> visible to the TMA engine
-    asm volatile("bar.sync 1, 128;" ::: "memory");
+    asm volatile("bar.sync 1, %0;" ::"n"(128 * NH) : "memory");
     if (st == 0) {
       att_tma_store_3d(&tmO, smem_u32(sQ), h * kDh, q0, b);
       att_tma_store_3d(&tmO32, smem_u32(sQ + kQBox0), h * kDh + 64, q0, b);
@@ -599,13 +629,13 @@ extern "C" int ttsb200_attention_fwd_lse(const void* qkv, const uint8_t* mask, c
   if (rc) return rc;
   static bool attr_done = false;
   if (!attr_done) {
-    TTSB_CHECK_CUDA(cudaFuncSetAttribute(attention_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kAttSmem));
+    TTSB_CHECK_CUDA(cudaFuncSetAttribute(attention_fwd_kernel<kAttHalves>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmem));
     attr_done = true;
   }
   dim3 grid((T + kBQ - 1) / kBQ, H, B);
   const float scale_log2 = kLog2e / sqrtf(static_cast<float>(Dh));
-  attention_fwd_kernel<<<grid, kAttThreads, kAttSmem, static_cast<cudaStream_t>(s)>>>(
+  attention_fwd_kernel<kAttHalves><<<grid, kAttThreads, kAttSmem, static_cast<cudaStream_t>(s)>>>(
       tmQ, tmQ32, tmKV, tmKV32, tmO, tmO32, mask, kv_info, lse2, T, H, scale_log2);
   TTSB_CHECK_CUDA(cudaGetLastError());
   return TTSB_OK;
