@@ -69,7 +69,7 @@ class ClockSampler(threading.Thread):
                     self.samples.append([s.strip() for s in out.split(",")])
             except Exception:
                 pass
-            self.stop_flag.wait(0.2)
+            self.stop_flag.wait(0.1)
 
     def summary(self):
         sm, mx, reasons = [], 0, set()
@@ -127,7 +127,7 @@ def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    r = cpu_oracle_run(max(1, min(args.steps, 5)), 1, sample_b=4)
+    r = cpu_oracle_run(max(1, min(args.steps, 20)), 1, sample_b=8)
     line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -322,7 +322,13 @@ def ours(args):
         e1.record()
         barrier()
         launches = lib.LAUNCH_COUNT - l0
-        dev_ms = max_over_ranks(e0.elapsed_time(e1))
+        my_ms = e0.elapsed_time(e1)
+        dev_ms = max_over_ranks(my_ms)
+        rank_ms = [my_ms / args.steps]
+        if world > 1:  # the step is the max over ranks: report every rank's own time next to it
+            g = [torch.zeros(1, device="cuda", dtype=torch.float64) for _ in range(world)]
+            dist.all_gather(g, torch.tensor([my_ms / args.steps], device="cuda", dtype=torch.float64))
+            rank_ms = [round(float(x.item()), 4) for x in g]
         # ---- end to end: pinned host inputs -> H2D -> forward -> mel_post D2H ----
         # Every step copies its inputs H2D and its mel D2H inside the timed region.  The D2H of step i runs on a
         # copy stream (two pinned buffers) while step i+1 computes, as a serving loop would; the timed region ends
@@ -360,7 +366,7 @@ def ours(args):
     e2e_value = total_frames * args.steps / (e2e_ms * 1e-3)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        r = cpu_oracle_run(2, 1, sample_b=4)
+        r = cpu_oracle_run(10, 1, sample_b=8)
         cpu = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]}
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -368,6 +374,7 @@ def ours(args):
                 "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "batch_per_gpu": B_PER_GPU, "phonemes": L_PHON,
                            "frames_per_step_per_gpu": frames, "t_max": tmax, "sharding": f"utterances x{world}, no collective",
+                           "ms_per_step_by_rank": rank_ms,
                            "l2": "working set per step (>1 GB of activations) exceeds the 126 MB L2; no explicit flush"},
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(text_h.numel() * 8 + mask_h.numel()),
                         "d2h_bytes_per_step": int(out_h[0].numel() * 4), "ms_per_step": e2e_ms / args.steps},
@@ -422,7 +429,7 @@ def train(args):
     model = build_fastspeech2(hp)
     model.load_state_dict(synth.synth_state_dict(hp))
     model = model.cuda().train()
-    tr = Trainer(model, optimizer=args.optimizer)
+    tr = Trainer(model, optimizer=args.optimizer, overlap_allreduce=args.overlap)
     tr.broadcast_parameters()
     Bt = args.train_batch
     host, frames = make_train_batch(rank, Bt)
@@ -491,12 +498,14 @@ def train(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--workload", default="infer", choices=["infer", "train"])
     ap.add_argument("--train-batch", type=int, default=32)
+    ap.add_argument("--overlap", action="store_true",
+                    help="train: overlapped tail/head gradient exchange instead of one all-reduce after the backward")
     ap.add_argument("--optimizer", default="radam", choices=["radam", "adam"],
                     help="train workload: radam (BASELINE.json configs[2], radam.py) or adam + Noam rate (the "
                          "reference's working default, SURVEY F5)")

@@ -42,7 +42,7 @@ def main():
     def make(sync):
         m = build_fastspeech2(hp)
         m.load_state_dict(sd)
-        return Trainer(m.cuda().train(), sync_bn=sync)
+        return Trainer(m.cuda().train(), sync_bn=sync, overlap_allreduce=sync)  # the overlapped exchange is the one checked
 
     tr = make(True)
     tr.broadcast_parameters()

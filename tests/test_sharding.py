@@ -106,7 +106,8 @@ def _train_dp_worker(rank, world, port, q):
 
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    from transformer_tts_b200.training import allreduce_mean_scale, noam_lr, sync_bn_moments
+    from transformer_tts_b200.training import (allreduce_mean_scale, allreduce_tail_begin, allreduce_tail_finish,
+                                               noam_lr, sync_bn_moments)
 
     g = torch.Generator().manual_seed(5)
     x_all = torch.randn(2 * 37, 8, generator=g) * 3 + 1  # rows of both ranks
@@ -115,11 +116,16 @@ def _train_dp_worker(rank, world, port, q):
     flat = grads_all[rank].clone()
     scale = allreduce_mean_scale(flat, world)
     mean_grad = flat * scale
+    # the overlapped exchange (tail first, asynchronously; head + join later) gives the same mean
+    flat2 = grads_all[rank].clone()
+    work = allreduce_tail_begin(flat2, 600)
+    scale2 = allreduce_tail_finish(flat2, 600, work, world)
+    ok_split = torch.allclose(flat2 * scale2, grads_all.mean(0), atol=1e-6)
     # SyncBatchNorm moments from local [sum | sum^2]
     x = x_all[rank * 37:(rank + 1) * 37]
     stats = torch.stack([x.sum(0), (x * x).sum(0)])
     ms, var, count = sync_bn_moments(stats, x.shape[0], world, True, 1e-5)
-    ok = torch.allclose(mean_grad, grads_all.mean(0), atol=1e-6)
+    ok = torch.allclose(mean_grad, grads_all.mean(0), atol=1e-6) and ok_split
     ok &= count == 74.0 and torch.allclose(ms[0], x_all.mean(0), atol=1e-5)
     ok &= torch.allclose(var, x_all.var(0, unbiased=False), rtol=1e-4, atol=1e-5)
     ok &= torch.allclose(ms[1], torch.rsqrt(x_all.var(0, unbiased=False) + 1e-5), rtol=1e-4)

@@ -54,6 +54,20 @@ def allreduce_mean_scale(flat_g: torch.Tensor, world: int, group=None) -> float:
     return 1.0 / world
 
 
+def allreduce_tail_begin(flat_g: torch.Tensor, tail_start: int, group=None):
+    """First half of the overlapped exchange: asynchronous all-reduce (SUM) of flat_g[tail_start:], the part of the
+    gradient buffer that is final once the decoder stack has run backward.  Returns the work handle."""
+    return dist.all_reduce(flat_g[tail_start:], group=group, async_op=True)
+
+
+def allreduce_tail_finish(flat_g: torch.Tensor, tail_start: int, work, world: int, group=None) -> float:
+    """Second half: all-reduce the head flat_g[:tail_start], join the tail; returns the mean scale like
+    `allreduce_mean_scale`."""
+    dist.all_reduce(flat_g[:tail_start], group=group)
+    work.wait()
+    return 1.0 / world
+
+
 def sync_bn_moments(stats: torch.Tensor, rows_local: int, world: int, sync: bool, eps: float, group=None):
     """[sum x | sum x^2] (2,C) of the local rows -> ([mean | rstd] (2,C), biased var, global row count).  With
     `sync` the sums are all-reduced first, which is what SyncBatchNorm's forward does."""
@@ -72,7 +86,7 @@ class Trainer:
     def __init__(self, model, *, lr_max: float = 1e-3, betas=(0.9, 0.98), eps: float = 1e-9, clip: float = 1.0,
                  warmup_step: int = 4000, warmup_factor: float = 1.0, fixed_lr: Optional[float] = None,
                  process_group=None, sync_bn: bool = True, bn_momentum: float = 0.1, flatten: bool = True,
-                 optimizer: str = "adam"):
+                 optimizer: str = "adam", overlap_allreduce: bool = False):
         """flatten=True (training loop owner): parameters are re-pointed into one flat fp32 buffer, `p.grad` are
         views of the flat gradient buffer and optimizer_step() runs the fused clip+Adam kernel.
         flatten=False (drop-in autograd mode, see `autograd_forward`): parameters are left alone, only the flat
@@ -85,6 +99,7 @@ class Trainer:
         if self.optimizer not in ("adam", "noam", "radam"):
             raise ValueError(f"Trainer: optimizer {optimizer!r} is not built (adam / noam / radam)")
         self.flatten = flatten
+        self.overlap_allreduce = overlap_allreduce
         self.model = model
         self.pg = process_group
         self.world = dist.get_world_size(process_group) if (dist.is_available() and dist.is_initialized()) else 1
@@ -109,6 +124,19 @@ class Trainer:
         self.grads: Dict[int, torch.Tensor] = {}
         self.names: Dict[int, str] = {id(p): n for n, p in params}
         self.flat_g = torch.zeros(total, device=dev, dtype=torch.float32)
+        # Gradient exchange overlapped with the backward: the backward runs PostNet -> decoder -> variance adaptor ->
+        # encoder and named_parameters() lists encoder, variance_adaptor, decoder, postnet, so once the decoder stack
+        # is done the TAIL of the flat buffer (decoder + postnet, ~45 % of the elements) is final and its all-reduce
+        # can run on NCCL's stream under the rest of the backward.  tail_start = None disables the overlap.
+        # Off by default: at 2 GPUs it measured 0.7 % SLOWER (16.54 vs 16.43 ms/step) — the NCCL kernel takes SMs
+        # from persistent backward kernels sized for all 148, and the whole exchange is only 0.6 ms of the step.
+        names = [n for n, _ in params]
+        first = next((i for i, n in enumerate(names) if n.startswith(("decoder.", "postnet."))), None)
+        self.tail_start = None
+        if first is not None and first > 0 and all(n.startswith(("decoder.", "postnet.")) for n in names[first:]):
+            self.tail_start = offs[names[first]]
+        self._overlap = False      # armed by train_step() only: an accumulating caller must not reduce early
+        self._pending = None
         self._bind_grads()
         if flatten:
             self.flat_p = torch.zeros(total, device=dev, dtype=torch.float32)
@@ -443,6 +471,9 @@ class Trainer:
             g_post_bf = lib.cast_bf16(g_post)
         dd = self._postnet_bwd(pn, tape["pn"], g_pre, g_post, g_post_bf)
         dva = self._stack_bwd(dec, tape["dec"], dd)                    # fp32 (B,Tm,D) w.r.t. va_x
+        if self._overlap and self.world > 1 and self.flatten and self.tail_start is not None:
+            # decoder + postnet gradients are final: reduce them while the adaptor and the encoder run backward
+            self._pending = allreduce_tail_begin(self.flat_g, self.tail_start, self.pg)
         lib.embed_bwd(dva, Tm, idx=tape["p_idx"], table=G(va.pitch_embedding.weight))
         lib.embed_bwd(dva, Tm, idx=tape["e_idx"], table=G(va.energy_embedding.weight))
         dxe = self._pred_bwd(va.pitch_predictor, tape["p"], g_p, dva)
@@ -488,7 +519,11 @@ class Trainer:
         if not self.flatten:
             raise RuntimeError("optimizer_step() needs flatten=True; in autograd mode the caller's optimizer steps")
         self.step_count += 1
-        gscale = allreduce_mean_scale(self.flat_g, self.world, self.pg)  # NCCL over NVLink
+        if self._pending is not None:  # the tail went out during the backward: reduce the head, join both
+            gscale = allreduce_tail_finish(self.flat_g, self.tail_start, self._pending, self.world, self.pg)
+            self._pending = None
+        else:
+            gscale = allreduce_mean_scale(self.flat_g, self.world, self.pg)  # NCCL over NVLink
         self.sumsq.zero_()
         lib.sumsq(self.flat_g, self.sumsq)
         lr = self.lr()
@@ -504,7 +539,11 @@ class Trainer:
 
     def train_step(self, text, src_mask, mel_mask, alignment, f0, energy, mel) -> Dict[str, torch.Tensor]:
         self.zero_grad()
-        out = self.forward_backward(text, src_mask, mel_mask, alignment, f0, energy, mel)
+        self._overlap = self.overlap_allreduce
+        try:
+            out = self.forward_backward(text, src_mask, mel_mask, alignment, f0, energy, mel)
+        finally:
+            self._overlap = False
         out["lr"] = self.optimizer_step()
         return out
 
