@@ -171,6 +171,72 @@ def test_free_running_batched(setup):
         assert rel_l2(valid_rows(out[1], ml), valid_rows(ref["outputs_postnet"], ml)) < 2e-2
 
 
+def test_full_size_properties_cfg2(setup):
+    """BASELINE.json configs[1] at full size (B=64, 128 phonemes -> ~1000 frames, free-running), where the oracle takes
+    minutes: size-independent properties instead.  Integer outputs are checked exactly (durations against the rounding
+    rule on OUR log_d, the frame->phoneme map as a sorted run-length expansion of the durations, lengths, positions,
+    mask); the mel through batch equivariance: reversing the batch reverses the outputs bit-for-bit (every tile's
+    arithmetic depends on its utterance only), and utterances run alone reproduce their rows of the batched run."""
+    from oracle import fastspeech2_oracle as O
+    from transformer_tts_b200 import synth
+
+    hp, sd, sd_gpu, model = setup
+    B, L = 64, 128
+    text, pos, _ = synth.synth_text_batch(B, L, ragged=True, seed=1234, min_len=L // 2)
+    text, pos = text.cuda(), pos.cuda()
+    src_mask = (pos != 0).unsqueeze(-2)
+    with torch.no_grad():
+        out = model(text, src_mask)
+        aux = dict(model.last_aux)
+        out_r = model(text.flip(0), src_mask.flip(0))
+        aux_r = dict(model.last_aux)
+        sub = [0, 17, 63]
+        outs_1 = [model(text[i:i + 1], src_mask[i:i + 1]) for i in sub]
+        out_h = model(text[16:48], src_mask[16:48])
+    torch.cuda.synchronize()
+    dur, mel_len, fidx = aux["dur"].long(), aux["mel_len"].long(), aux["frame_idx"].long()
+    Tm = out[0].shape[1]
+    assert 900 * B * 0.6 < int(mel_len.sum()) and Tm == int(mel_len.max())
+    # integer outputs: exact
+    assert torch.equal(dur, O.round_durations(out[2]).long())
+    assert (dur[pos == 0] == 0).all() and torch.equal(mel_len, dur.sum(1))
+    ar = torch.arange(Tm, device="cuda")
+    for b in (0, 1, 31, 63):
+        n = int(mel_len[b])
+        f = fidx[b, :n]
+        assert (f[1:] >= f[:-1]).all()                                   # sorted
+        assert torch.equal(torch.bincount(f, minlength=L), dur[b])      # run lengths == durations
+        assert torch.equal(aux["mel_pos"][b, :n].long(), ar[:n] + 1) and (aux["mel_pos"][b, n:] == 0).all()
+    assert torch.equal(aux["mel_mask"].bool(), O.get_mask_from_lengths(aux["mel_pos"]))
+    # batch equivariance: bit-exact
+    assert torch.equal(aux_r["dur"].flip(0), aux["dur"]) and torch.equal(out_r[2].flip(0), out[2])
+    for k in (0, 1):
+        assert torch.equal(out_r[k].flip(0), out[k]), f"output {k} is not equivariant under a batch reversal"
+    # half of the batch alone == its rows in the full batch, bit for bit: other utterances and the padding up to a
+    # different Tmax never leak into valid frames.  Exception, by the reference's own semantics: the variance
+    # predictors do not mask between their two k=3 convs (varianceadaptor.py:216-229), so an utterance that fills the
+    # whole time axis sees the conv's zero padding where a padded batch shows it LN(relu(bias)) rows — its last two
+    # pitch / energy values, hence its embeddings, hence (through attention) all its frames move a little.
+    Th = out_h[0].shape[1]
+    errs, edge = [], []
+    for j, i in enumerate(range(16, 48)):
+        n = int(mel_len[i])
+        (errs if n + 2 <= Th else edge).append(rel_l2(out_h[1][j, :n], out[1][i, :n]))
+        if n + 2 > Th:
+            dp = (out_h[3][j, :n] - out[3][i, :n]).abs()
+            assert float(dp[:n - 2].max()) < 0.05 * float(out[3][i, :n].abs().max()), "pitch moved away from the edge"
+    assert len(errs) >= 28 and max(errs) == 0.0, f"half batch vs full batch: {max(errs)}"
+    assert all(e < 3e-2 for e in edge)
+    # an utterance alone is always such an edge case and takes the short-batch kernel variants (other tile shapes and
+    # rounding points): same frame count, mel within 3x the bf16 bar
+    for i, o1 in zip(sub, outs_1):
+        n = int(mel_len[i])
+        assert o1[0].shape[1] == n
+        assert rel_l2(o1[1][0], out[1][i, :n]) < 3 * TOL_BF16
+    print(f"\n[cfg2 properties] frames={int(mel_len.sum())} Tmax={Tm} half-batch max rel-L2={max(errs):.2e} (edge utterances: {edge})")
+    assert torch.isfinite(out[1]).all()
+
+
 def test_attention_maps_on_request(setup):
     from transformer_tts_b200 import synth
 
