@@ -228,7 +228,7 @@ def kernel_rooflines(model, peaks, tmax):
     # dram__bytes_read.sum + dram__bytes_write.sum per launch from ONE `ncu --set full` capture of the same shapes
     # (profiles/r01_hot_kernels_v5_full_summary.csv, tools/run_hot_kernels.py).  Writes that are still resident in
     # the 126 MB write-back L2 when the kernel ends are not counted by the DRAM counters.
-    traffic_mb = [55.2 + 109.0, 157.0 + 36.1, 163.4 + 112.9, 56.3 + 162.8, 389.4 + 128.1, 6.3 + 2.4, 55.5 + 7.1,
+    traffic_mb = [55.2 + 109.0, 154.9 + 36.8, 163.4 + 112.9, 56.3 + 162.8, 389.4 + 128.1, 6.3 + 2.4, 55.5 + 7.1,
                   108.4 + 8.0]
     out = []
     reps = 4

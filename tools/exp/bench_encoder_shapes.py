@@ -32,8 +32,10 @@ def t(fn, n=50):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(); g_.replay(); e1.record(); torch.cuda.synchronize()
     return e0.elapsed_time(e1) / n * 1e3
-for pair in (0, 2):
-    lib.ttsb200_debug_gemm_pair(pair)
+lib.ttsb200_debug_gemm_astat_min.argtypes = [C.c_int]; lib.ttsb200_debug_gemm_astat_min.restype = None
+for pair, amin in ((1, 0), (1, 148), (2, 148)):
+    lib.ttsb200_debug_gemm_pair(pair); lib.ttsb200_debug_gemm_astat_min(amin)
+    print(f"astat_min={amin}", end=" ")
     print(f"T={T} pair={pair}: qkv {t(lambda: L.conv_gemm(xs, wq, bq, block_n=192, out_bf16=qkv)):6.1f}  "
           f"out-proj {t(lambda: L.conv_gemm(xs, wo, b2, block_n=D, epi=L.EPI_RES_LN, res_f32=x32, res_bstride=T * D, res_tstride=D, ln1=g, out_f32=o32, out_bf16=ob)):6.1f}  "
           f"ffn1 k9 {t(lambda: L.conv_gemm(xs, w1, b1, taps=9, pad_left=4, block_n=256, act=L.ACT_RELU, out_bf16=h)):6.1f}  "

@@ -122,6 +122,10 @@ static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t
 using namespace ttsb;
 
 extern "C" void ttsb200_debug_gemm_pair(int on) { g_gemm_pair = on; }
+// The A-stationary sweep gives one unit per 128-row tile; below this many row tiles (short batches: the encoder's
+// 64 x 128 phonemes are 64 tiles for 148 SMs) the tile-parallel schedule fills the machine better.
+static int g_astat_min_units = 148;  // measured: encoder q|k|v (64 tiles) 18.5 -> 12.1 us tile-parallel
+extern "C" void ttsb200_debug_gemm_astat_min(int units) { g_astat_min_units = units; }
 
 #if defined(TTSB_GEMM_TRACE)
 extern "C" int ttsb200_debug_gemm_trace(long long* dst, int n) {
@@ -168,7 +172,8 @@ extern "C" int ttsb200_conv_gemm(const ttsb200_gemm_args* a, ttsb200_stream_t st
                      "conv_gemm: res strides % 4, 16-byte aligned");
     // A-stationary sweep: plain linears on <= 384 input channels with bf16-only output
     const bool a_stat = a->taps == 1 && a->C <= 384 && a->C % 64 == 0 && a->out_bf16 && !a->out_f32 &&
-                        !a->res_f32 && a->N / bn >= 2;
+                        !a->res_f32 && a->N / bn >= 2 &&
+                        static_cast<long long>(a->B) * ((a->T + kBlockM - 1) / kBlockM) >= g_astat_min_units;
     if (bn == 80) return launch_gemm<80, TTSB200_EPI_AFFINE_ACT, false>(*a, d, stream);
     if (bn == 128) {
       if (a_stat) return launch_gemm<128, TTSB200_EPI_AFFINE_ACT, true>(*a, d, stream);
