@@ -40,3 +40,13 @@ for pair, amin in ((1, 0), (1, 148), (2, 148)):
           f"out-proj {t(lambda: L.conv_gemm(xs, wo, b2, block_n=D, epi=L.EPI_RES_LN, res_f32=x32, res_bstride=T * D, res_tstride=D, ln1=g, out_f32=o32, out_bf16=ob)):6.1f}  "
           f"ffn1 k9 {t(lambda: L.conv_gemm(xs, w1, b1, taps=9, pad_left=4, block_n=256, act=L.ACT_RELU, out_bf16=h)):6.1f}  "
           f"ffn2 {t(lambda: L.conv_gemm(hs, w2, b2, block_n=D, epi=L.EPI_FFN2, res_bf16=xs, res_f32=x32, res_bstride=T * D, res_tstride=D, ln1=g, ln2=g, out_f32=o32, out_bf16=ob)):6.1f} us", flush=True)
+# out-proj + residual + LayerNorm: whole-row epilogue on B*ceil(T/128) CTAs vs column-split AFFINE GEMM + row kernel
+lib.ttsb200_debug_gemm_pair(1)
+def split():
+    L.conv_gemm(xs, wo, b2, block_n=192, res_f32=x32, res_bstride=T * D, res_tstride=D, out_f32=o32)
+    L.layernorm(o32, g[0], g[1], 1e-5, y_bf16=ob)
+def split128():
+    L.conv_gemm(xs, wo, b2, block_n=128, res_f32=x32, res_bstride=T * D, res_tstride=D, out_f32=o32)
+    L.layernorm(o32, g[0], g[1], 1e-5, y_bf16=ob)
+fused = lambda: L.conv_gemm(xs, wo, b2, block_n=D, epi=L.EPI_RES_LN, res_f32=x32, res_bstride=T * D, res_tstride=D, ln1=g, out_f32=o32, out_bf16=ob)
+print(f"out-proj fused {t(fused):.1f} us, split(192)+LN {t(split):.1f} us, split(128)+LN {t(split128):.1f} us")
