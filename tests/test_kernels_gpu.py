@@ -389,3 +389,25 @@ def test_errors_are_loud(L):
     wd = torch.zeros(1, 384, 384, dtype=torch.bfloat16, device=dev())
     with pytest.raises(RuntimeError, match="unsupported|block_n"):
         L.conv_gemm(xd, wd, torch.zeros(384, device=dev()), block_n=96, out_bf16=torch.empty_like(xd))
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_second_device_in_one_process(L):
+    """The >48 KB shared-memory opt-in is per device: a process that already ran on cuda:0 must still be able to launch
+    every tensor-core kernel on cuda:1 (it is set once per device, not once per process)."""
+    outs = []
+    for dev in (0, 1):
+        with torch.cuda.device(dev):
+            g = torch.Generator().manual_seed(3)
+            B, T, H, Dh = 2, 200, 4, 96
+            qkv = (torch.randn(B, T, 3 * H * Dh, generator=g) * 0.5).to(torch.bfloat16).cuda()
+            mask = torch.ones(B, T, dtype=torch.uint8).cuda()
+            ctx = torch.empty(B, T, H * Dh, dtype=torch.bfloat16, device="cuda")
+            L.attention_fwd(qkv, mask, L.mask_lengths(mask), ctx, H)
+            x = (torch.randn(B, T, 384, generator=g) * 0.5).to(torch.bfloat16).cuda()
+            w = (torch.randn(1, 1152, 384, generator=g) * 0.05).to(torch.bfloat16).cuda()
+            o = torch.empty(B, T, 1152, dtype=torch.bfloat16, device="cuda")
+            L.conv_gemm(x, w, torch.zeros(1152, device="cuda"), block_n=192, out_bf16=o)
+            torch.cuda.synchronize()
+            outs.append((ctx.cpu(), o.cpu()))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])

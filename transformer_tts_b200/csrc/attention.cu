@@ -627,12 +627,7 @@ extern "C" int ttsb200_attention_fwd_lse(const void* qkv, const uint8_t* mask, c
   if (rc) return rc;
   rc = make_tmap_bf16(&tmO32, ctx, 3, odims, ostrides, box_q32, CU_TENSOR_MAP_SWIZZLE_64B);
   if (rc) return rc;
-  static bool attr_done = false;
-  if (!attr_done) {
-    TTSB_CHECK_CUDA(cudaFuncSetAttribute(attention_fwd_kernel<kAttHalves>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmem));
-    attr_done = true;
-  }
+  TTSB_SMEM_OPT_IN(attention_fwd_kernel<kAttHalves>, kAttSmem);
   dim3 grid((T + kBQ - 1) / kBQ, H, B);
   const float scale_log2 = kLog2e / sqrtf(static_cast<float>(Dh));
   attention_fwd_kernel<kAttHalves><<<grid, kAttThreads, kAttSmem, static_cast<cudaStream_t>(s)>>>(

@@ -492,14 +492,8 @@ extern "C" int ttsb200_attention_bwd(const void* qkv, const void* dctx, const ui
     int rc = make_tmap_bf16(&tmDO, dctx, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_64B);
     if (rc) return rc;
   }
-  static bool attr_done = false;
-  if (!attr_done) {
-    TTSB_CHECK_CUDA(cudaFuncSetAttribute(ab::attn_bwd_dkv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         ab::kSmemDkv));
-    TTSB_CHECK_CUDA(cudaFuncSetAttribute(ab::attn_bwd_dq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         ab::kSmemDq));
-    attr_done = true;
-  }
+  TTSB_SMEM_OPT_IN(ab::attn_bwd_dkv_kernel, ab::kSmemDkv);
+  TTSB_SMEM_OPT_IN(ab::attn_bwd_dq_kernel, ab::kSmemDq);
   const float scale = 1.f / sqrtf(static_cast<float>(Dh));
   const float scale_log2 = ab::kLog2e * scale;
   dim3 grid((T + 127) / 128, H, B);

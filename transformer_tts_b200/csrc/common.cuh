@@ -41,6 +41,20 @@ void set_last_error(const char* fmt, ...);
     }                                                                                      \
   } while (0)
 
+// Opt a kernel in to more than 48 KB of dynamic shared memory, once PER DEVICE (the attribute is per device: a
+// process-wide `static bool` would leave the second GPU of a multi-device process without it).
+#define TTSB_SMEM_OPT_IN(kern, bytes)                                                          \
+  do {                                                                                         \
+    static unsigned long long _done_mask = 0;                                                  \
+    int _dev = 0;                                                                              \
+    TTSB_CHECK_CUDA(cudaGetDevice(&_dev));                                                     \
+    if (!((_done_mask >> (_dev & 63)) & 1ull)) {                                               \
+      TTSB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (bytes))); \
+      _done_mask |= 1ull << (_dev & 63);                                                       \
+    }                                                                                          \
+  } while (0)
+
+
 // Encode a tiled bf16 tensor map (rank 2 or 3).  dims/strides innermost first; strides in BYTES for
 // dims 1.. (dim 0 is contiguous).  Returns TTSB_OK or a negative code (last error set).
 int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,

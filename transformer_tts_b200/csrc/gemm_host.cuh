@@ -81,11 +81,7 @@ static int launch_gemm(const ttsb200_gemm_args& a, GemmDev& d, cudaStream_t stre
     }
   }
   auto kern = conv_gemm_kernel<BLOCK_N, EPI, A_STAT, PAIR>;
-  static bool attr_done = false;  // per instantiation
-  if (!attr_done) {
-    TTSB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-    attr_done = true;
-  }
+  TTSB_SMEM_OPT_IN(kern, Cfg::kSmemBytes);  // per instantiation and device
   d.m_tiles = (a.T + kBlockM - 1) / kBlockM;
   d.n_tiles = a.N / BLOCK_N;
   d.num_tiles = a.B * d.m_tiles * d.n_tiles;

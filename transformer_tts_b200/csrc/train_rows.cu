@@ -667,12 +667,7 @@ extern "C" int ttsb200_embed_bwd(const float* g, const int64_t* idx64, const int
   float* table_generic = table;
   if (table && V <= 256) {
     // small vocabulary: shared-memory privatised scatter (one pass over g per table)
-    static bool attr_done = false;
-    if (!attr_done) {
-      TTSB_CHECK_CUDA(cudaFuncSetAttribute(embed_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           256 * 32 * 4));
-      attr_done = true;
-    }
+    TTSB_SMEM_OPT_IN(embed_scatter_kernel, 256 * 32 * 4);
     int64_t gy = (rows + kRowWarps * 16 - 1) / (kRowWarps * 16);
     if (gy > 48) gy = 48;
     if (gy < 1) gy = 1;

@@ -196,11 +196,7 @@ extern "C" int ttsb200_conv_wgrad(const void* dy, int64_t ld_dy, const void* x, 
     int rc = make_tmap_bf16(&tmX, x, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
   }
-  static bool attr_done = false;
-  if (!attr_done) {
-    TTSB_CHECK_CUDA(cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmem));
-    attr_done = true;
-  }
+  TTSB_SMEM_OPT_IN(wgrad_kernel, kWgSmem);
   WgradDev d;
   d.B = B; d.T = T; d.N = N; d.C = C; d.taps = taps; d.pad_left = pad_left;
   d.n_tiles = (N + kWgM - 1) / kWgM;
