@@ -50,7 +50,8 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     procs = []
     for s in SOURCES:
         obj = bdir / (s[:-3] + ".o")
-        cmd = [nvcc, *NVCC_FLAGS, "-c", str(CSRC / s), "-o", str(obj)]
+        # TTSB200_NVCC_FLAGS: extra -D switches for experiment builds (tools/exp), empty in a product build
+        cmd = [nvcc, *NVCC_FLAGS, *os.environ.get("TTSB200_NVCC_FLAGS", "").split(), "-c", str(CSRC / s), "-o", str(obj)]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         procs.append((s, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))

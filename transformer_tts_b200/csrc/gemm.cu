@@ -37,6 +37,9 @@ constexpr int kGemmThreads = 384;  // 12 warps
 constexpr int kEpiWarp0 = 4;
 constexpr int kEpiThreads = 256;
 constexpr int kWgThreads = 128;
+#ifndef TTSB_STORE_BOXES
+#define TTSB_STORE_BOXES 2   // bf16 staging boxes per epilogue warpgroup of the CTA-pair AFFINE kernels (1..3)
+#endif
 constexpr int kMaxSmem = 232448;  // 227 KB opt-in limit per CTA
 constexpr int kBoxBytes16K = 16384;
 
@@ -55,7 +58,7 @@ struct GemmCfg {
   static constexpr int kAResBytes = A_STAT ? 6 * kABytes : 0;            // resident A: up to C = 384
   // one bf16 staging box per warpgroup: 128 rows x 32 columns (SWIZZLE_64B)
   // (CTA pairs have the room for two per warpgroup: the TMA store of one chunk overlaps the next chunk's math)
-  static constexpr int kStoreBoxes = (PAIR && !kIsLN) ? 2 : 1;
+  static constexpr int kStoreBoxes = (PAIR && !kIsLN) ? TTSB_STORE_BOXES : 1;
   static constexpr int kStoreBytes = 2 * kStoreBoxes * 8192;
   static constexpr int kRingSlots = kRing ? 4 : 0;  // even: each half owns its own slots
   static constexpr int kRingBytes = kRingSlots * kBoxBytes16K;
@@ -193,8 +196,8 @@ __device__ __forceinline__ void box_row_st_bf16x32_sw64_t(uint8_t* box, int row,
 
 __device__ __forceinline__ void epi_bar_all() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 // named barriers 4..7 / 8..11: staging box (warpgroup, box) full / free, between an epilogue warpgroup and its store warp
-constexpr int kBarFull0 = 4;
-constexpr int kBarFree0 = 8;
+constexpr int kBarFull0 = 4;                          // [2 warpgroups][kStoreBoxes <= 3]
+constexpr int kBarFree0 = 4 + 2 * 3;                  // ids 10..15
 __device__ __forceinline__ void nbar_sync(int id, int count) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
 }
@@ -212,6 +215,7 @@ __device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, uint32_t src,
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read2() { asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
 }  // namespace ttsb

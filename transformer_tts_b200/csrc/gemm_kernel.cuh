@@ -275,15 +275,17 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int nt = nt0; nt < nt0 + n_inner; ++nt) {
           for (int c = c_lo; c < c_hi; c += 32, ++sg) {
             const uint32_t bx = sg % NB;
-            nbar_sync(kBarFull0 + wg * 2 + bx, kWgThreads + 32);
+            nbar_sync(kBarFull0 + wg * 3 + bx, kWgThreads + 32);
             if (lane == 0) {
               tma_store_3d(&tmOut, smem_u32(my_box + bx * 8192), nt * BLOCK_N + c, t0, b);
               tma_store_commit();
-              if (NB == 2) tma_store_wait_read1();  // the store before this one has read its box
+              // at most NB - 1 stores may still be reading: the oldest box is free again
+              if (NB == 3) tma_store_wait_read2();
+              else if (NB == 2) tma_store_wait_read1();
               else tma_store_wait_read0();
             }
             __syncwarp();
-            if (sg + 1 >= NB) nbar_arrive(kBarFree0 + wg * 2 + (sg + 1) % NB, kWgThreads + 32);
+            if (sg + 1 >= NB) nbar_arrive(kBarFree0 + wg * 3 + (sg + 1) % NB, kWgThreads + 32);
           }
         }
       }
@@ -291,7 +293,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       __syncwarp();
       // the stores not yet reported free: the last NB-1 of them
       for (uint32_t g = (sg + 1 >= NB ? sg + 1 - NB : 0); g < sg; ++g)
-        nbar_arrive(kBarFree0 + wg * 2 + g % NB, kWgThreads + 32);
+        nbar_arrive(kBarFree0 + wg * 3 + g % NB, kWgThreads + 32);
     }
   } else if (warp >= kEpiWarp0) {
 #include "gemm_epilogue.inc"
