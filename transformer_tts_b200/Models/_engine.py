@@ -152,11 +152,42 @@ def run_fft_block(t: dict, heads: int, x: torch.Tensor, xn: torch.Tensor, mask_u
     yn = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
     lib.conv_gemm(ctx, t["wo"], t["bo"], block_n=D, epi=lib.EPI_RES_LN, res_f32=x, res_bstride=T * D,
                   res_tstride=D, ln1=t["ln2"], out_f32=y, out_bf16=yn)  # modules.py:68 + layers.py:33,35
+    zn32 = torch.empty((B, T, D), device=dev, dtype=torch.float32) if want_norm_f32 else None
+    cb = ffn_chunk_utterances(B, T, D)
+    if cb < B:
+        # The 1536-wide hidden activation of the whole batch (217 MB at cfg2) is the largest HBM item of the step and
+        # conv1 is bound by writing it.  Run conv1 -> conv2 on groups of utterances whose hidden activation fits the
+        # 126 MB L2, through ONE reused buffer: conv2 reads it back from L2 and the next group overwrites the lines
+        # before they are ever written to DRAM.
+        z = torch.empty((B, T, D), device=dev, dtype=torch.float32)
+        zn = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
+        h = torch.empty((cb, T, 4 * D), device=dev, dtype=torch.bfloat16)
+        for b0 in range(0, B, cb):
+            b1 = min(B, b0 + cb)
+            hb = h[:b1 - b0]
+            lib.conv_gemm(yn[b0:b1], t["w1"], t["b1"], taps=k, pad_left=k // 2, block_n=256, act=lib.ACT_RELU,
+                          out_bf16=hb)  # modules.py:83
+            run_ffn2(t, hb, yn[b0:b1], y[b0:b1], next_ln, zn32=None if zn32 is None else zn32[b0:b1],
+                     out=(z[b0:b1], zn[b0:b1]))
+        return z, zn, zn32
     h = torch.empty((B, T, 4 * D), device=dev, dtype=torch.bfloat16)
     lib.conv_gemm(yn, t["w1"], t["b1"], taps=k, pad_left=k // 2, block_n=256, act=lib.ACT_RELU, out_bf16=h)  # modules.py:83
-    zn32 = torch.empty((B, T, D), device=dev, dtype=torch.float32) if want_norm_f32 else None
     z, zn = run_ffn2(t, h, yn, y, next_ln, zn32=zn32)  # modules.py:84-87 + layers.py:40 + next norm
     return z, zn, zn32
+
+
+# conv1 -> conv2 grouping (see run_fft_block): a group is FFN_GROUP_WAVES full waves of 128-row tiles over the 148 SMs
+# (a group of 17 utterances x 9 tiles = 153 tiles would run a second, almost empty wave); 0 disables the grouping.
+FFN_GROUP_WAVES = 0
+NUM_SMS = 148
+
+
+def ffn_chunk_utterances(B: int, T: int, D: int) -> int:
+    """Utterances per conv1 -> conv2 group: all of them when grouping is off or the hidden activation is small."""
+    m_tiles = (T + 127) // 128
+    if FFN_GROUP_WAVES <= 0 or B * T * 4 * D * 2 <= (96 << 20):
+        return B
+    return max(1, min(B, (NUM_SMS // m_tiles) * FFN_GROUP_WAVES))
 
 
 # Whole-row LayerNorm epilogues run one CTA per 128-row tile.  With fewer tiles than this, the k-tap conv2 of
@@ -165,13 +196,17 @@ def run_fft_block(t: dict, heads: int, x: torch.Tensor, xn: torch.Tensor, mask_u
 SHORT_BATCH_TILES = 74
 
 
-def run_ffn2(t: dict, h: torch.Tensor, yn: torch.Tensor, y: torch.Tensor, next_ln, zn32=None, pre_f32=None):
-    """z = y + LN_ff(conv2(h) + b2 + yn); zn = LN_next(z).  Returns (z fp32, zn bf16)."""
+def run_ffn2(t: dict, h: torch.Tensor, yn: torch.Tensor, y: torch.Tensor, next_ln, zn32=None, pre_f32=None,
+             out=None):
+    """z = y + LN_ff(conv2(h) + b2 + yn); zn = LN_next(z).  Returns (z fp32, zn bf16) (written into `out` if given)."""
     B, T, D = y.shape
     dev = y.device
     k = t["k"]
-    z = torch.empty((B, T, D), device=dev, dtype=torch.float32)
-    zn = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
+    if out is not None:
+        z, zn = out
+    else:
+        z = torch.empty((B, T, D), device=dev, dtype=torch.float32)
+        zn = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
     tiles = B * ((T + 127) // 128)
     if tiles <= SHORT_BATCH_TILES and D == 384:
         u = torch.empty((B, T, D), device=dev, dtype=torch.float32)
