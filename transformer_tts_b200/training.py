@@ -32,7 +32,10 @@ def noam_lr(step: int, d_model: int, warmup_factor: float, warmup_step: int) -> 
 
 def _t(w_taps: torch.Tensor) -> torch.Tensor:
     """Forward operand (taps, N, C) -> dgrad operand (taps, C, N), taps flipped: w'[j'][c][n] = w[taps-1-j'][n][c]."""
-    return w_taps.permute(0, 2, 1).flip(0).contiguous()
+    wt = w_taps.permute(0, 2, 1)
+    if w_taps.shape[0] > 1:  # a linear (one tap) needs no flip: one copy kernel instead of two
+        wt = wt.flip(0)
+    return wt.contiguous()
 
 
 def require_zero_dropout(model) -> None:
