@@ -62,8 +62,10 @@ __device__ __forceinline__ void block_col_atomic(float (&acc)[NV * 4], float* __
 //        w.r.t. the conv output)
 //   dgamma += sum_rows g*xhat, dbeta += sum_rows g, dvec += sum_rows g_row*y, dscal += sum_rows g_row
 // ------------------------------------------------------------------------------------------------
-template <int NV>
-__global__ void __launch_bounds__(kRowThreads)
+// HEAD = the predictor-head variant (g = g_row * g_vec, dvec / dscal outputs): its 36 extra registers per thread
+// cost the plain variant (19 launches per training step) its second resident CTA, so it is a template switch.
+template <int NV, bool HEAD>
+__global__ void __launch_bounds__(kRowThreads, HEAD ? 1 : 2)
 ln_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
               const float* __restrict__ g_f32, const __nv_bfloat16* __restrict__ g_bf16,
               const float* __restrict__ g_row, const float* __restrict__ g_vec,
@@ -80,8 +82,8 @@ ln_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, cons
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
     gm[i] = __ldg(reinterpret_cast<const float4*>(gamma) + i * 32 + lane);
-    bt[i] = beta ? __ldg(reinterpret_cast<const float4*>(beta) + i * 32 + lane) : make_float4(0, 0, 0, 0);
-    gv[i] = g_vec ? __ldg(reinterpret_cast<const float4*>(g_vec) + i * 32 + lane) : make_float4(0, 0, 0, 0);
+    bt[i] = (HEAD && beta) ? __ldg(reinterpret_cast<const float4*>(beta) + i * 32 + lane) : make_float4(0, 0, 0, 0);
+    gv[i] = (HEAD && g_vec) ? __ldg(reinterpret_cast<const float4*>(g_vec) + i * 32 + lane) : make_float4(0, 0, 0, 0);
   }
   float a_dg[NV * 4], a_db[NV * 4], a_dv[NV * 4];
 #pragma unroll
@@ -96,7 +98,7 @@ ln_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, cons
       s += v[i].x + v[i].y + v[i].z + v[i].w;
     }
     float gr = 0.f;
-    if (g_row) {
+    if (HEAD && g_row) {
       gr = __ldg(g_row + row);
       if (row_mask && row_mask[row] == 0) gr = 0.f;
     }
@@ -125,7 +127,7 @@ ln_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, cons
       a_dg[4 * i] += g[i].x * xh[i].x; a_dg[4 * i + 1] += g[i].y * xh[i].y;
       a_dg[4 * i + 2] += g[i].z * xh[i].z; a_dg[4 * i + 3] += g[i].w * xh[i].w;
       a_db[4 * i] += g[i].x; a_db[4 * i + 1] += g[i].y; a_db[4 * i + 2] += g[i].z; a_db[4 * i + 3] += g[i].w;
-      if (g_row) {
+      if (HEAD && g_row) {
         a_dv[4 * i] += gr * fmaf(gm[i].x, xh[i].x, bt[i].x); a_dv[4 * i + 1] += gr * fmaf(gm[i].y, xh[i].y, bt[i].y);
         a_dv[4 * i + 2] += gr * fmaf(gm[i].z, xh[i].z, bt[i].z); a_dv[4 * i + 3] += gr * fmaf(gm[i].w, xh[i].w, bt[i].w);
       }
@@ -156,8 +158,8 @@ ln_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, cons
   }
   if (dgamma) block_col_atomic<NV>(a_dg, dgamma, sbuf, lane, warp);
   if (dbeta) block_col_atomic<NV>(a_db, dbeta, sbuf, lane, warp);
-  if (dvec) block_col_atomic<NV>(a_dv, dvec, sbuf, lane, warp);
-  if (dscal) {
+  if (HEAD && dvec) block_col_atomic<NV>(a_dv, dvec, sbuf, lane, warp);
+  if (HEAD && dscal) {
     a_ds = warp_sum(a_ds);  // every lane of the warp carried the same gr: count it once
     if (lane == 0) atomicAdd(dscal, a_ds * (1.f / 32.f));
   }
@@ -575,12 +577,18 @@ extern "C" int ttsb200_layernorm_bwd(const float* x, const float* gamma, const f
   const unsigned grid = persistent_grid(rows);
   auto gb = static_cast<const __nv_bfloat16*>(g_bf16);
   auto db = static_cast<__nv_bfloat16*>(dx_bf16);
-  if (D == 384)
-    ln_bwd_kernel<3><<<grid, kRowThreads, 0, st>>>(x, gamma, beta, g_f32, gb, g_row, g_vec, row_mask, add_f32,
-                                                   relu_gate, dx_f32, db, dgamma, dbeta, dvec, dscal, rows, eps);
-  else if (D == 256)
-    ln_bwd_kernel<2><<<grid, kRowThreads, 0, st>>>(x, gamma, beta, g_f32, gb, g_row, g_vec, row_mask, add_f32,
-                                                   relu_gate, dx_f32, db, dgamma, dbeta, dvec, dscal, rows, eps);
+  const bool head = g_row != nullptr || g_vec != nullptr || dvec != nullptr || dscal != nullptr;
+#define TTSB_LN_BWD(NV, HEAD)                                                                                      \
+  ln_bwd_kernel<NV, HEAD><<<grid, kRowThreads, 0, st>>>(x, gamma, beta, g_f32, gb, g_row, g_vec, row_mask, add_f32, \
+                                                        relu_gate, dx_f32, db, dgamma, dbeta, dvec, dscal, rows, eps)
+  if (D == 384) {
+    if (head) TTSB_LN_BWD(3, true);
+    else TTSB_LN_BWD(3, false);
+  } else if (D == 256) {
+    if (head) TTSB_LN_BWD(2, true);
+    else TTSB_LN_BWD(2, false);
+  }
+#undef TTSB_LN_BWD
   else {
     set_last_error("layernorm_bwd: D=%d unsupported (384 or 256)", D);
     return TTSB_ERR_ARG;
