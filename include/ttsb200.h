@@ -85,9 +85,21 @@ typedef struct ttsb200_gemm_args {
   /* training extras (NULL in inference) */
   float* pre_f32;        /* LN epilogues: pre-LayerNorm value (B,T,N) saved for the backward pass */
   const void* gate_bf16; /* ACT_RELU_GRAD: saved forward activation, bf16 (B,T,N) */
+  /* ragged batches (NULL = every 128-row tile of every utterance): a device list of the row tiles to compute,
+   * entry = b * ceil(T/128) + tile, and its device length, from ttsb200_build_tile_map.  Rows of tiles that are
+   * not listed are neither read nor written (the reference computes its padding rows, Models/layers.py:29-41;
+   * nothing valid reads them in a k=1 block with masked keys). */
+  const int32_t* tile_map;
+  const int32_t* tile_count;
 } ttsb200_gemm_args;
 
 int ttsb200_conv_gemm(const ttsb200_gemm_args* args, ttsb200_stream_t stream);
+
+/* Row-tile list of a ragged batch for ttsb200_gemm_args.tile_map: utterance b contributes its first
+ * min(m_tiles, ceil((len[b*len_stride] + halo) / 128)) tiles; map has room for B*m_tiles entries, *count receives
+ * the number written.  len may be kv_info of ttsb200_mask_lengths (len_stride 2).  No host synchronisation. */
+int ttsb200_build_tile_map(const int32_t* len, int32_t len_stride, int32_t B, int32_t m_tiles, int32_t halo,
+                           int32_t* map, int32_t* count, ttsb200_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Fused masked multi-head self-attention (Models/modules.py:7-21 inside :43-70).
@@ -99,6 +111,10 @@ int ttsb200_conv_gemm(const ttsb200_gemm_args* args, ttsb200_stream_t stream);
  * inside which key tiles never read the mask.
  * Dh must be 96 (H*Dh = 384) in this build.
  * ---------------------------------------------------------------------------------------------- */
+/* As ttsb200_attention_fwd, but query tiles (128 rows) that start at or beyond kv_info[b][0] — pure padding of a
+ * ragged batch — are skipped: their ctx rows are left unwritten (pair with ttsb200_gemm_args.tile_map). */
+int ttsb200_attention_fwd_ragged(const void* qkv_bf16, const uint8_t* mask, const int32_t* kv_info, void* ctx_bf16,
+                                 int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t stream);
 int ttsb200_attention_fwd(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
                           int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t stream);
 /* Training forward: same kernel, also writes lse2 (B,H,T) fp32 = log2-domain log-sum-exp of every

@@ -339,3 +339,43 @@ def test_teacher_forced_forward_is_graph_capturable(setup):
         assert torch.equal(a, b)
     assert not torch.equal(replay2[0], eager[0])
     text.copy_(keep)
+
+
+def test_ragged_tile_list_is_bit_identical_on_valid_frames(setup):
+    """The frame-level stack drops 128-row tiles that are pure padding (lib.build_tile_map, _engine.RAGGED_TILES):
+    every valid frame must come out bit-identical to the dense schedule, the mel of dropped tiles is zero, and the
+    tile list itself is the exact run-length expansion of ceil(len / 128)."""
+    from transformer_tts_b200 import lib, synth
+    from transformer_tts_b200.Models import _engine as E
+
+    hp, sd, sd_gpu, model = setup
+    text, pos, _ = synth.synth_text_batch(6, 40, ragged=True, seed=9, min_len=6)
+    text, pos = text.cuda(), pos.cuda()
+    src_mask = (pos != 0).unsqueeze(-2)
+    outs = {}
+    old, old_sb = E.RAGGED_TILES, E.SHORT_BATCH_TILES
+    try:
+        E.SHORT_BATCH_TILES = 0  # same kernel variants in both runs (short batches otherwise take their own path)
+        for rag in (False, True):
+            E.RAGGED_TILES = rag
+            with torch.no_grad():
+                o = model(text, src_mask)
+            outs[rag] = (o[0].clone(), o[1].clone(), model.last_aux["mel_len"].long().clone())
+    finally:
+        E.RAGGED_TILES, E.SHORT_BATCH_TILES = old, old_sb
+    torch.cuda.synchronize()
+    ml = outs[True][2]
+    assert torch.equal(ml, outs[False][2])
+    T = outs[True][0].shape[1]
+    assert T > 128 and int(ml.min()) + 128 <= T, "the batch must have at least one droppable tile"
+    for i in range(ml.numel()):
+        n = int(ml[i])
+        for k in (0, 1):
+            assert torch.equal(outs[True][k][i, :n], outs[False][k][i, :n])
+        first_dropped = ((n + 127) // 128) * 128
+        assert (outs[True][1][i, first_dropped:] == 0).all()
+    kv = torch.stack([ml.int(), ml.int()], 1).contiguous()
+    tmap, count = lib.build_tile_map(kv, T)
+    m_tiles = (T + 127) // 128
+    want = [b * m_tiles + j for b in range(ml.numel()) for j in range(min(m_tiles, (int(ml[b]) + 127) // 128))]
+    assert int(count) == len(want) and tmap[:len(want)].tolist() == want

@@ -138,20 +138,29 @@ def layer_cache(layer) -> dict:
     return c.t
 
 
+# Ragged batches: the frame-level stack (k=1 convs, masked keys) and the causal PostNet never read a row beyond an
+# utterance's own length from a valid row, so 128-row tiles that are pure padding are dropped from the kernels' tile
+# lists (lib.build_tile_map).  At cfg2 the mean utterance is 995 frames against Tmax 1102: ~10 % of the tiles.
+RAGGED_TILES = True
+
+
 def run_fft_block(t: dict, heads: int, x: torch.Tensor, xn: torch.Tensor, mask_u8: torch.Tensor,
-                  kv_len: torch.Tensor, next_ln, want_norm_f32: bool = False):
-    """x: fp32 residual stream (B,T,D); xn = norm_1(x) in bf16.  Returns (x', LN_next(x') bf16[, fp32])."""
+                  kv_len: torch.Tensor, next_ln, want_norm_f32: bool = False, tile_map=None):
+    """x: fp32 residual stream (B,T,D); xn = norm_1(x) in bf16.  Returns (x', LN_next(x') bf16[, fp32]).
+    tile_map (k=1 blocks only): rows of unlisted 128-row tiles are neither read nor written."""
     B, T, D = x.shape
     dev = x.device
     k = t["k"]
     qkv = torch.empty((B, T, 3 * D), device=dev, dtype=torch.bfloat16)
-    lib.conv_gemm(xn, t["wqkv"], t["bqkv"], block_n=192, out_bf16=qkv)  # modules.py:49-51
+    if tile_map is not None and k != 1:
+        raise ValueError("run_fft_block: a ragged tile list needs k=1 convs (a k>1 conv reads its padding rows)")
+    lib.conv_gemm(xn, t["wqkv"], t["bqkv"], block_n=192, out_bf16=qkv, tile_map=tile_map)  # modules.py:49-51
     ctx = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
-    lib.attention_fwd(qkv, mask_u8, kv_len, ctx, heads)  # modules.py:7-21,58-65
+    lib.attention_fwd(qkv, mask_u8, kv_len, ctx, heads, skip_padded_queries=tile_map is not None)  # modules.py:7-21,58-65
     y = torch.empty((B, T, D), device=dev, dtype=torch.float32)
     yn = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
     lib.conv_gemm(ctx, t["wo"], t["bo"], block_n=D, epi=lib.EPI_RES_LN, res_f32=x, res_bstride=T * D,
-                  res_tstride=D, ln1=t["ln2"], out_f32=y, out_bf16=yn)  # modules.py:68 + layers.py:33,35
+                  res_tstride=D, ln1=t["ln2"], out_f32=y, out_bf16=yn, tile_map=tile_map)  # modules.py:68 + layers.py:33,35
     zn32 = torch.empty((B, T, D), device=dev, dtype=torch.float32) if want_norm_f32 else None
     cb = ffn_chunk_utterances(B, T, D)
     if cb < B:
@@ -171,8 +180,9 @@ def run_fft_block(t: dict, heads: int, x: torch.Tensor, xn: torch.Tensor, mask_u
                      out=(z[b0:b1], zn[b0:b1]))
         return z, zn, zn32
     h = torch.empty((B, T, 4 * D), device=dev, dtype=torch.bfloat16)
-    lib.conv_gemm(yn, t["w1"], t["b1"], taps=k, pad_left=k // 2, block_n=256, act=lib.ACT_RELU, out_bf16=h)  # modules.py:83
-    z, zn = run_ffn2(t, h, yn, y, next_ln, zn32=zn32)  # modules.py:84-87 + layers.py:40 + next norm
+    lib.conv_gemm(yn, t["w1"], t["b1"], taps=k, pad_left=k // 2, block_n=256, act=lib.ACT_RELU, out_bf16=h,
+                  tile_map=tile_map)  # modules.py:83
+    z, zn = run_ffn2(t, h, yn, y, next_ln, zn32=zn32, tile_map=tile_map)  # modules.py:84-87 + layers.py:40 + next norm
     return z, zn, zn32
 
 
@@ -197,7 +207,7 @@ SHORT_BATCH_TILES = 74
 
 
 def run_ffn2(t: dict, h: torch.Tensor, yn: torch.Tensor, y: torch.Tensor, next_ln, zn32=None, pre_f32=None,
-             out=None):
+             out=None, tile_map=None):
     """z = y + LN_ff(conv2(h) + b2 + yn); zn = LN_next(z).  Returns (z fp32, zn bf16) (written into `out` if given)."""
     B, T, D = y.shape
     dev = y.device
@@ -208,7 +218,7 @@ def run_ffn2(t: dict, h: torch.Tensor, yn: torch.Tensor, y: torch.Tensor, next_l
         z = torch.empty((B, T, D), device=dev, dtype=torch.float32)
         zn = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
     tiles = B * ((T + 127) // 128)
-    if tiles <= SHORT_BATCH_TILES and D == 384:
+    if tiles <= SHORT_BATCH_TILES and D == 384 and tile_map is None:
         u = torch.empty((B, T, D), device=dev, dtype=torch.float32)
         lib.conv_gemm(h, t["w2"], t["b2"], taps=k, pad_left=k // 2, block_n=128 if tiles * 3 <= 148 else 192,
                       out_f32=u)
@@ -216,7 +226,7 @@ def run_ffn2(t: dict, h: torch.Tensor, yn: torch.Tensor, y: torch.Tensor, next_l
     else:
         lib.conv_gemm(h, t["w2"], t["b2"], taps=k, pad_left=k // 2, block_n=D, epi=lib.EPI_FFN2, res_bf16=yn,
                       res_f32=y, res_bstride=T * D, res_tstride=D, ln1=t["ln_ff"], ln2=next_ln, out_f32=z,
-                      out_bf16=zn, out2_f32=zn32, pre_f32=pre_f32)
+                      out_bf16=zn, out2_f32=zn32, pre_f32=pre_f32, tile_map=tile_map)
     return z, zn
 
 
@@ -276,19 +286,24 @@ def postnet_cache(pn) -> dict:
     return c.t
 
 
-def run_postnet(t: dict, d_bf16: torch.Tensor):
+def run_postnet(t: dict, d_bf16: torch.Tensor, tile_map=None):
+    """tile_map: the convs are causal (pad 4 + drop the last 4), so a listed tile only reads listed rows; the mel
+    outputs of unlisted (padding) tiles are zero."""
     B, T, D = d_bf16.shape
     dev = d_bf16.device
     md = t["bout"].numel()
-    mel_pre = torch.empty((B, T, md), device=dev, dtype=torch.float32)
+    new = torch.empty if tile_map is None else torch.zeros
+    mel_pre = new((B, T, md), device=dev, dtype=torch.float32)
     mel_pre_bf = torch.empty((B, T, md), device=dev, dtype=torch.bfloat16)
-    lib.conv_gemm(d_bf16, t["wout"], t["bout"], block_n=md, out_f32=mel_pre, out_bf16=mel_pre_bf)  # postnets.py:67
+    lib.conv_gemm(d_bf16, t["wout"], t["bout"], block_n=md, out_f32=mel_pre, out_bf16=mel_pre_bf,
+                  tile_map=tile_map)  # postnets.py:67
     h = mel_pre_bf
     for w, scale, shift in t["convs"]:  # postnets.py:71-73 (pad 4 + drop last 4 == causal, pad_left 4)
         o = torch.empty((B, T, w.shape[1]), device=dev, dtype=torch.bfloat16)
-        lib.conv_gemm(h, w, shift, taps=5, pad_left=4, block_n=192, act=lib.ACT_TANH, scale=scale, out_bf16=o)
+        lib.conv_gemm(h, w, shift, taps=5, pad_left=4, block_n=192, act=lib.ACT_TANH, scale=scale, out_bf16=o,
+                      tile_map=tile_map)
         h = o
-    mel_post = torch.empty((B, T, md), device=dev, dtype=torch.float32)
+    mel_post = new((B, T, md), device=dev, dtype=torch.float32)
     lib.conv_gemm(h, t["w2"], t["b2"], taps=5, pad_left=4, block_n=md, res_f32=mel_pre, res_bstride=T * md,
-                  res_tstride=md, out_f32=mel_post)  # postnets.py:74-75
+                  res_tstride=md, out_f32=mel_post, tile_map=tile_map)  # postnets.py:74-75
     return mel_pre, mel_post

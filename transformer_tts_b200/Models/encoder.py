@@ -67,7 +67,7 @@ class Encoder(nn.Module):
             c.commit(params)
         return c.t
 
-    def run(self, src, mask_u8, kv_len, want_f32=False, return_attn=False):
+    def run(self, src, mask_u8, kv_len, want_f32=False, return_attn=False, tile_map=None):
         """Kernel sequence for the whole stack.  src: int64 ids (B,T) or bf16 features (B,T,C).
         Returns (LN_final(x) bf16, optional fp32 copy, attn maps or None)."""
         t = self._cache()
@@ -85,7 +85,8 @@ class Encoder(nn.Module):
             lib.embed_pe_ln(src.contiguous(), t["table"], pe, t["alpha"], ln_first[0], ln_first[1], E.LN_EPS, x, xn)
         else:
             lib.conv_gemm(src, t["wemb"], t["bemb"], block_n=D, epi=lib.EPI_RES_LN, res_f32=pe, res_bstride=0,
-                          res_tstride=D, res_scale=t["alpha"], ln1=ln_first, out_f32=x, out_bf16=xn)
+                          res_tstride=D, res_scale=t["alpha"], ln1=ln_first, out_f32=x, out_bf16=xn,
+                          tile_map=tile_map)
         attns = [] if return_attn else None
         xn32 = None
         for i, lc in enumerate(caches):
@@ -96,7 +97,7 @@ class Encoder(nn.Module):
                 attns.append(lib.attention_probs(qkv, mask_u8, self.heads))
             next_ln = t["norm"] if last else caches[i + 1]["ln1"]
             x, xn, xn32 = E.run_fft_block(lc, self.heads, x, xn, mask_u8, kv_len, next_ln,
-                                          want_norm_f32=(last and want_f32))
+                                          want_norm_f32=(last and want_f32), tile_map=tile_map)
         if self.N == 0 and want_f32:
             xn32 = xn.float()
         return xn, xn32, (torch.stack(attns, 1) if return_attn else None)

@@ -99,8 +99,15 @@ class FastSpeech2(nn.Module):
         va = self.variance_adaptor.run(e_bf, sm, mm, d_target, p_target, e_target, want_aux=True)  # :176-181
         mel_u8 = va["mel_mask"]
         kv_mel = lib.mask_lengths(mel_u8)
-        d_bf, _, attn_dec = self.decoder.run(va["x"], mel_u8, kv_mel, want_f32=False, return_attn=self.return_attn)  # :195
-        mel_pre, mel_post = self.postnet.run(d_bf)  # :197
+        tile_map = None
+        Tm = mel_u8.shape[1]
+        if E.RAGGED_TILES and not self.return_attn and self.decoder.N > 0 and \
+                B * ((Tm + 127) // 128) > E.SHORT_BATCH_TILES and \
+                all(l.ff.f_1.kernel_size[0] == 1 for l in self.decoder.layers):  # short batches keep their own path
+            tile_map = lib.build_tile_map(kv_mel, mel_u8.shape[1])  # padding-only row tiles are not computed
+        d_bf, _, attn_dec = self.decoder.run(va["x"], mel_u8, kv_mel, want_f32=False, return_attn=self.return_attn,
+                                             tile_map=tile_map)  # :195
+        mel_pre, mel_post = self.postnet.run(d_bf, tile_map=tile_map)  # :197
         self.last_aux = dict(dur=va["dur"], mel_len=va["mel_len"], frame_idx=va["frame_idx"], mel_pos=va["mel_pos"],
                              mel_mask=mel_u8, p_idx=va["p_idx"], e_idx=va["e_idx"], encoder_output=e_bf,
                              decoder_output=d_bf)

@@ -31,8 +31,8 @@ class PostConvNet(nn.Module):
         self.dropout_list = nn.ModuleList([nn.Dropout(p=dropout) for _ in range(3)])
         self._ttsb_cache = E.Cache()
 
-    def run(self, d_bf16):
-        return E.run_postnet(E.postnet_cache(self), d_bf16)
+    def run(self, d_bf16, tile_map=None):
+        return E.run_postnet(E.postnet_cache(self), d_bf16, tile_map=tile_map)
 
     def forward(self, input_, mask=None):
         E.require_inference(self, "PostConvNet")

@@ -132,7 +132,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
                      const __grid_constant__ CUtensorMap tmKV, const __grid_constant__ CUtensorMap tmKV32,
                      const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmO32,
                      const uint8_t* __restrict__ mask, const int32_t* __restrict__ kv_info,
-                     float* __restrict__ lse2, int T, int H, float scale_log2) {
+                     float* __restrict__ lse2, int T, int H, float scale_log2, int skip_padded_q) {
   extern __shared__ uint8_t smem_raw[];
 #if defined(TTSB_ATT_TRACE)
   const long long t_entry = clock64();
@@ -157,6 +157,9 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
   const int kprefix = kv_info[2 * b + 1];   // keys [0, kprefix) are all valid
   const int kv_eff = klen > 0 ? klen : T;   // no valid key: the reference degenerates to uniform over T
   const int nkv = (kv_eff + kBKV - 1) / kBKV;
+  // ragged batches: a query tile wholly beyond the utterance's last valid row is padding (CTA-uniform exit, before
+  // any barrier or TMEM allocation); its ctx rows stay unwritten
+  if (skip_padded_q && klen > 0 && q0 >= klen) return;
 
   auto load_k = [&](int j) {
     const int ks = j % kKStages;
@@ -598,9 +601,8 @@ __global__ void attention_probs_kernel(const __nv_bfloat16* __restrict__ qkv, co
 
 using namespace ttsb;
 
-extern "C" int ttsb200_attention_fwd_lse(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
-                                         float* lse2, int32_t B, int32_t T, int32_t H, int32_t Dh,
-                                         ttsb200_stream_t s) {
+static int attention_fwd_launch(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx, float* lse2,
+                                int32_t B, int32_t T, int32_t H, int32_t Dh, int skip_padded_q, ttsb200_stream_t s) {
   TTSB_CHECK_ARG(qkv && mask && kv_info && ctx, "attention_fwd: null pointer");
   TTSB_CHECK_ARG(B > 0 && T > 0 && H > 0, "attention_fwd: bad dims");
   TTSB_CHECK_ARG(Dh == kDh, "attention_fwd: head dim %d unsupported (this build: %d)", Dh, kDh);
@@ -631,7 +633,7 @@ extern "C" int ttsb200_attention_fwd_lse(const void* qkv, const uint8_t* mask, c
   dim3 grid((T + kBQ - 1) / kBQ, H, B);
   const float scale_log2 = kLog2e / sqrtf(static_cast<float>(Dh));
   attention_fwd_kernel<kAttHalves><<<grid, kAttThreads, kAttSmem, static_cast<cudaStream_t>(s)>>>(
-      tmQ, tmQ32, tmKV, tmKV32, tmO, tmO32, mask, kv_info, lse2, T, H, scale_log2);
+      tmQ, tmQ32, tmKV, tmKV32, tmO, tmO32, mask, kv_info, lse2, T, H, scale_log2, skip_padded_q);
   TTSB_CHECK_CUDA(cudaGetLastError());
   return TTSB_OK;
 }
@@ -641,6 +643,17 @@ extern "C" int ttsb200_debug_att_trace(long long* dst, int n) {
   return cudaMemcpyFromSymbol(dst, g_att_trace, n * sizeof(long long)) == cudaSuccess ? 0 : -1;
 }
 #endif
+
+extern "C" int ttsb200_attention_fwd_lse(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
+                                         float* lse2, int32_t B, int32_t T, int32_t H, int32_t Dh,
+                                         ttsb200_stream_t s) {
+  return attention_fwd_launch(qkv, mask, kv_info, ctx, lse2, B, T, H, Dh, 0, s);
+}
+
+extern "C" int ttsb200_attention_fwd_ragged(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
+                                            int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t s) {
+  return attention_fwd_launch(qkv, mask, kv_info, ctx, nullptr, B, T, H, Dh, 1, s);
+}
 
 extern "C" int ttsb200_attention_fwd(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
                                      int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t s) {

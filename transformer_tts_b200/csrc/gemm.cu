@@ -100,6 +100,8 @@ struct GemmDev {
   float* out_row;
   float* pre_f32;                 // LN epilogues: the pre-LayerNorm value (saved for the backward pass)
   const __nv_bfloat16* gate_bf16; // AFFINE + ACT_RELU_GRAD: v = gate > 0 ? v : 0
+  const int* mt_map;              // ragged batches: compacted list of row tiles (b * m_tiles + tile) ...
+  const int* mt_count;            // ... and its length, both on the device (NULL = all B * m_tiles tiles)
 };
 
 __device__ __forceinline__ float tanh_fast(float x) {

@@ -154,6 +154,8 @@ extern "C" int ttsb200_conv_gemm(const ttsb200_gemm_args* a, ttsb200_stream_t st
   d.out_f32 = a->out_f32; d.out_bf16 = static_cast<__nv_bfloat16*>(a->out_bf16);
   d.out2_f32 = a->out2_f32; d.out_row = a->out_row;
   d.pre_f32 = a->pre_f32; d.gate_bf16 = static_cast<const __nv_bfloat16*>(a->gate_bf16);
+  TTSB_CHECK_ARG((a->tile_map == nullptr) == (a->tile_count == nullptr), "conv_gemm: tile_map and tile_count go together");
+  d.mt_map = a->tile_map; d.mt_count = a->tile_count;
   if (a->pre_f32) TTSB_CHECK_ARG(aligned16(a->pre_f32) && a->epi != TTSB200_EPI_AFFINE_ACT,
                                  "conv_gemm: pre_f32 is an output of the LayerNorm epilogues, 16-byte aligned");
   if (a->act == TTSB200_ACT_RELU_GRAD)

@@ -51,7 +51,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   // CTA pair: the two CTAs of a cluster take the m-tiles 2u and 2u+1 of unit u and share every W tile
   const uint32_t cta_rank = PAIR ? cluster_ctarank() : 0u;
   const bool is_leader = cta_rank == 0;
-  const int total_mt = p.B * p.m_tiles;
+  const int total_mt = p.mt_count ? __ldg(p.mt_count) : p.B * p.m_tiles;
   const int mt_units = PAIR ? (total_mt + 1) / 2 : total_mt;
   const int num_units = A_STAT ? mt_units : mt_units * p.n_tiles;
   const int unit0 = PAIR ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
@@ -111,6 +111,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       t0 = p.m_tiles * kBlockM;
       return;
     }
+    if (p.mt_map) mt = __ldg(p.mt_map + mt);  // ragged batch: the mt-th listed row tile
     b = mt / p.m_tiles;
     t0 = (mt - b * p.m_tiles) * kBlockM;
   };

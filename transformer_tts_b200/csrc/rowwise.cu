@@ -383,6 +383,36 @@ extern "C" int ttsb200_ffn2_tail(const float* u, const void* yn_bf16, const floa
   return TTSB_OK;
 }
 
+// Row-tile list of a ragged batch (ttsb200_gemm_args.tile_map): one block, a shuffle-free serial scan is enough for the
+// few hundred utterances of a batch.
+__global__ void build_tile_map_kernel(const int32_t* __restrict__ len, int len_stride, int B, int m_tiles, int halo,
+                                      int32_t* __restrict__ map, int32_t* __restrict__ count) {
+  __shared__ int s_off[1025];
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    const int n = len[static_cast<int64_t>(b) * len_stride];
+    int nt = n > 0 ? (n + halo + 127) / 128 : 0;
+    s_off[b + 1] = nt < m_tiles ? nt : m_tiles;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    s_off[0] = 0;
+    for (int b = 0; b < B; ++b) s_off[b + 1] += s_off[b];
+    *count = s_off[B];
+  }
+  __syncthreads();
+  for (int b = threadIdx.x; b < B; b += blockDim.x)
+    for (int i = s_off[b]; i < s_off[b + 1]; ++i) map[i] = b * m_tiles + (i - s_off[b]);
+}
+
+extern "C" int ttsb200_build_tile_map(const int32_t* len, int32_t len_stride, int32_t B, int32_t m_tiles,
+                                      int32_t halo, int32_t* map, int32_t* count, ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(len && map && count && B > 0 && B <= 1024 && m_tiles > 0 && len_stride > 0 && halo >= 0,
+                 "build_tile_map: bad args (B <= 1024)");
+  build_tile_map_kernel<<<1, 256, 0, static_cast<cudaStream_t>(s)>>>(len, len_stride, B, m_tiles, halo, map, count);
+  TTSB_LAUNCH_CHECK();
+  return TTSB_OK;
+}
+
 extern "C" int ttsb200_round_durations(const float* log_d, int32_t* dur, int64_t n, ttsb200_stream_t s) {
   TTSB_CHECK_ARG(log_d && dur && n > 0, "round_durations: bad args");
   round_durations_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(s)>>>(

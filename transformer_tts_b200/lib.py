@@ -35,6 +35,7 @@ class GemmArgs(C.Structure):
         ("out_f32", C.c_void_p), ("out_bf16", C.c_void_p), ("out2_f32", C.c_void_p),
         ("out_row", C.c_void_p),
         ("pre_f32", C.c_void_p), ("gate_bf16", C.c_void_p),
+        ("tile_map", C.c_void_p), ("tile_count", C.c_void_p),
     ]
 
 
@@ -44,8 +45,12 @@ _SIGNATURES = {
     "ttsb200_version": ([], C.c_int),
     "ttsb200_last_error_string": ([], C.c_char_p),
     "ttsb200_conv_gemm": ([C.POINTER(GemmArgs), C.c_void_p], C.c_int),
+    "ttsb200_build_tile_map": ([C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
+                                C.c_void_p], C.c_int),
     "ttsb200_attention_fwd": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
                                C.c_int32, C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_attention_fwd_ragged": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
+                                      C.c_int32, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_attention_probs": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
                                  C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_mask_lengths": ([C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p], C.c_int),
@@ -149,7 +154,8 @@ def conv_gemm(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, *, taps: int
               row_mask: Optional[torch.Tensor] = None,
               out_f32: Optional[torch.Tensor] = None, out_bf16: Optional[torch.Tensor] = None,
               out2_f32: Optional[torch.Tensor] = None, out_row: Optional[torch.Tensor] = None,
-              pre_f32: Optional[torch.Tensor] = None, gate_bf16: Optional[torch.Tensor] = None) -> None:
+              pre_f32: Optional[torch.Tensor] = None, gate_bf16: Optional[torch.Tensor] = None,
+              tile_map: Optional[tuple] = None) -> None:
     """x: bf16 (B,T,C); w: bf16 (taps,N,C).  See include/ttsb200.h for the epilogue modes."""
     B, T, Cin = x.shape
     tw, N, Cw = w.shape
@@ -179,18 +185,46 @@ def conv_gemm(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, *, taps: int
     a.out_row = _ptr(out_row, torch.float32, "out_row")
     a.pre_f32 = _ptr(pre_f32, torch.float32, "pre_f32")
     a.gate_bf16 = _ptr(gate_bf16, torch.bfloat16, "gate_bf16")
+    if tile_map is not None:  # (map, count) from build_tile_map: only the listed 128-row tiles are computed
+        a.tile_map, a.tile_count = _ptr(tile_map[0], torch.int32, "tile_map"), _ptr(tile_map[1], torch.int32, "tile_count")
     _check(load().ttsb200_conv_gemm(C.byref(a), _stream()), "conv_gemm")
     _count()
+
+
+def build_tile_map(lengths: torch.Tensor, T: int, halo: int = 0) -> tuple:
+    """Row-tile list of a ragged batch for conv_gemm(tile_map=...).  lengths: int32 (B,) or the (B,2) kv_info of
+    mask_lengths (column 0 = 1 + last valid row).  Returns (map int32 (B*m_tiles,), count int32 (1,)); no host sync."""
+    if lengths.dtype != torch.int32 or not lengths.is_contiguous():
+        raise TypeError("build_tile_map: lengths must be a contiguous int32 tensor")
+    B = lengths.shape[0]
+    stride = 1 if lengths.dim() == 1 else lengths.shape[1]
+    m_tiles = (T + 127) // 128
+    tmap = torch.empty(B * m_tiles, dtype=torch.int32, device=lengths.device)
+    count = torch.empty(1, dtype=torch.int32, device=lengths.device)
+    _check(load().ttsb200_build_tile_map(_ptr(lengths, torch.int32, "lengths"), stride, B, m_tiles, halo,
+                                         tmap.data_ptr(), count.data_ptr(), _stream()), "build_tile_map")
+    _count()
+    return tmap, count
 
 
 # --------------------------------------------------------------------------------------------------
 # attention
 # --------------------------------------------------------------------------------------------------
 def attention_fwd(qkv: torch.Tensor, mask: torch.Tensor, kv_len: torch.Tensor, ctx: torch.Tensor, H: int,
-                  lse2: Optional[torch.Tensor] = None) -> None:
-    """lse2 (B,H,T) fp32, when given, receives the log2-domain log-sum-exp of every row (training)."""
+                  lse2: Optional[torch.Tensor] = None, skip_padded_queries: bool = False) -> None:
+    """lse2 (B,H,T) fp32, when given, receives the log2-domain log-sum-exp of every row (training).
+    skip_padded_queries: 128-row query tiles wholly beyond an utterance's last valid row are not computed."""
     B, T, W = qkv.shape
     Dh = W // (3 * H)
+    if skip_padded_queries:
+        if lse2 is not None:
+            raise ValueError("attention_fwd: skip_padded_queries is an inference option (no lse2)")
+        _check(load().ttsb200_attention_fwd_ragged(_ptr(qkv, torch.bfloat16, "qkv"), _ptr(mask, torch.uint8, "mask"),
+                                                   _ptr(kv_len, torch.int32, "kv_len"),
+                                                   _ptr(ctx, torch.bfloat16, "ctx"), B, T, H, Dh, _stream()),
+               "attention_fwd_ragged")
+        _count()
+        return
     _check(load().ttsb200_attention_fwd_lse(_ptr(qkv, torch.bfloat16, "qkv"), _ptr(mask, torch.uint8, "mask"),
                                             _ptr(kv_len, torch.int32, "kv_len"), _ptr(ctx, torch.bfloat16, "ctx"),
                                             _ptr(lse2, torch.float32, "lse2"), B, T, H, Dh, _stream()),
