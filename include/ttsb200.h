@@ -184,6 +184,43 @@ int ttsb200_bucket_embed_add(const void* x_bf16, const float* p, const float* e,
 int ttsb200_cast_bf16(const float* x, void* y_bf16, int64_t n, ttsb200_stream_t stream);
 
 /* ================================================================================================
+ * fp32-ACCURATE ENCODER -> DURATION CHAIN (free-running inference).
+ * The reference rounds an fp32 log_d to integer durations (Models/varianceadaptor.py:69,75), so the chain that
+ * produces it — Models/encoder.py:83-112, Models/layers.py:29-41, Models/modules.py:7-88 and the duration
+ * predictor Models/varianceadaptor.py:216-229 — has to reproduce fp32 arithmetic for the durations, frame indices
+ * and mel lengths to come out bit-exact.  These entry points evaluate it on the tensor cores with every operand
+ * split into two fp16 values ("split" tensors: fp16 (B,T,2C) = [hi | lo] along the last axis, v = hi + lo) and
+ * three products per term (hi*hi + lo*hi + hi*lo); partial sums leave the truncating tensor-core accumulator
+ * after every 64-wide k-block and are added in fp32 round-to-nearest registers.
+ * ============================================================================================== */
+
+/* acc[b,t,n] = sum_j sum_c x[b,t+j-pad_left,c] * w[j,n,c];  v = acc*inv_scale + bias[n] (then ReLU if relu).
+ * x_split fp16 (B,T,2C); w_split fp16 [taps][N][2C] = split of w*2^e (inv_scale = 2^-e keeps the lo parts of the
+ * weights normal); N % 128 == 0, C % 64 == 0.  Exactly one output: out_f32 (B,T,N) or out_split fp16 (B,T,2N). */
+int ttsb200_gemm_x3(const void* x_split, const void* w_split, const float* bias, float inv_scale, int32_t B,
+                    int32_t T, int32_t N, int32_t C, int32_t taps, int32_t pad_left, int32_t relu, float* out_f32,
+                    void* out_split, ttsb200_stream_t stream);
+
+/* Models/modules.py:7-21 on fp32 q|k|v (B,T,3*H*Dh): ctx_split fp16 (B,T,2*H*Dh).  mask / kv_info as in
+ * ttsb200_attention_fwd.  Dh must be 96. */
+int ttsb200_attention_x3(const float* qkv_f32, const uint8_t* mask, const int32_t* kv_info, void* ctx_split,
+                         int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t stream);
+
+/* fp32 row operations of the chain (one warp per row, D = 256 or 384):
+ *   s = a (+ b0 fp32 | + b0_split hi+lo);  s_out = s (optional);  t = LayerNorm(s; g1, b1)
+ *   mode 0 ADD_LN   (Models/layers.py:31,33-35):                 out = t
+ *   mode 1 FFN_TAIL (Models/modules.py:85-87, layers.py:40,31):  z = c + t; z_out = z; out = LayerNorm(z; g2, b2)
+ *   mode 2 LN_DOT   (Models/varianceadaptor.py:222-229):         out_row = row_mask ? dot(t, dot_w) + dot_b : 0
+ * out goes to any of out_split (fp16 (rows,2D)), out_bf16, out_f32. */
+int ttsb200_xrow(int32_t mode, const float* a, const float* b0, const void* b0_split, const float* c,
+                 const float* g1, const float* b1, const float* g2, const float* b2, const float* dot_w,
+                 const float* dot_b, const uint8_t* row_mask, float eps, float* s_out, float* z_out, void* out_split,
+                 void* out_bf16, float* out_f32, float* out_row, int64_t rows, int32_t D, ttsb200_stream_t stream);
+
+/* out_split fp16 (rows,2D) = split of x*scale, x fp32 (rows,D) (weight / activation staging). */
+int ttsb200_split_f16(const float* x, void* out_split, int64_t rows, int32_t D, float scale, ttsb200_stream_t stream);
+
+/* ================================================================================================
  * TRAINING STEP (forward extras above: pre_f32, gate_bf16, ttsb200_attention_fwd_lse).
  * The reference has no explicit backward code: it calls loss.backward() / optimizer.step()
  * (train_fastspeech2.py:304-315) and PyTorch autograd differentiates the modules cited below.

@@ -6,7 +6,8 @@ sm_100a kernels of ``csrc/`` for one FFT block, one variance predictor and the P
 caches are rebuilt whenever a source parameter's storage or version counter changes
 (``load_state_dict`` and optimizer steps both bump ``Tensor._version``).
 
-Inference (eval, no autograd) only; the training path is not built yet and raises.
+The inference sequences live here; the training step (saved activations, explicit backward) is
+``transformer_tts_b200/training.py`` and reuses these caches.
 """
 from __future__ import annotations
 
@@ -55,8 +56,8 @@ def positional_table(d_model: int, device: torch.device, max_seq_len: int = 5000
 def require_inference(module: torch.nn.Module, what: str) -> None:
     if module.training:
         raise NotImplementedError(
-            f"{what}: only the inference path (model.eval()) is built on the sm_100a kernels so far; "
-            "the training step (backward kernels, SyncBatchNorm statistics) is not implemented")
+            f"{what}: standalone sub-modules run the inference kernels only (call .eval()); the training step is "
+            "built for the whole model — FastSpeech2.forward in train() mode / transformer_tts_b200.training.Trainer")
 
 
 def require_cuda(t: torch.Tensor, what: str) -> None:
@@ -307,3 +308,109 @@ def run_postnet(t: dict, d_bf16: torch.Tensor, tile_map=None):
     lib.conv_gemm(h, t["w2"], t["b2"], taps=5, pad_left=4, block_n=md, res_f32=mel_pre, res_bstride=T * md,
                   res_tstride=md, out_f32=mel_post, tile_map=tile_map)  # postnets.py:74-75
     return mel_pre, mel_post
+
+
+# --------------------------------------------------------------------------------------------------
+# fp32-accurate encoder -> duration chain (csrc/precise.cu): Models/encoder.py:83-112 + the duration predictor
+# Models/varianceadaptor.py:216-229 evaluated to fp32 accuracy on the tensor cores (fp16 hi/lo operand splitting,
+# three products per term, fp32 round-to-nearest accumulation outside the tensor core).  The reference rounds an
+# fp32 log_d (varianceadaptor.py:75): with this chain free-running durations match it bit for bit wherever the
+# reference's own exp(log_d) - 1 is not within ~1e-4 of a rounding boundary.
+# --------------------------------------------------------------------------------------------------
+def split_weight(w: torch.Tensor):
+    """fp32 (taps, N, C) -> (fp16 (taps, N, 2C) = [hi | lo] of w * 2^e, 2^-e).  The power of two puts max|w| in
+    [4096, 8192) so the lo halves (2^-11 of the value) stay normal fp16 numbers."""
+    w = w.detach().to(torch.float32).contiguous()
+    mx = float(w.abs().max())
+    e = 0 if mx == 0.0 or not np.isfinite(mx) else int(np.floor(np.log2(8192.0 / mx)))
+    e = max(-24, min(24, e))
+    return lib.split_f16(w, float(2.0 ** e)), float(2.0 ** -e)
+
+
+def layer_cache_x3(layer) -> dict:
+    c = getattr(layer, "_ttsb_cache_x3", None)
+    if c is None:
+        c = Cache()
+        object.__setattr__(layer, "_ttsb_cache_x3", c)
+    a, ff = layer.attn, layer.ff
+    params = [a.q_linear.weight, a.k_linear.weight, a.v_linear.weight, a.out.weight, ff.f_1.weight, ff.f_2.weight]
+    if c.stale(params):
+        t = c.t
+        t["wqkv"], t["sqkv"] = split_weight(torch.cat([a.q_linear.weight, a.k_linear.weight, a.v_linear.weight], 0).unsqueeze(0))
+        t["wo"], t["so"] = split_weight(a.out.weight.unsqueeze(0))
+        t["w1"], t["s1"] = split_weight(ff.f_1.weight.detach().permute(2, 0, 1))
+        t["w2"], t["s2"] = split_weight(ff.f_2.weight.detach().permute(2, 0, 1))
+        c.commit(params)
+    return c.t
+
+
+def predictor_cache_x3(pred) -> dict:
+    c = getattr(pred, "_ttsb_cache_x3", None)
+    if c is None:
+        c = Cache()
+        object.__setattr__(pred, "_ttsb_cache_x3", c)
+    params = [pred.conv1.weight, pred.conv2.weight]
+    if c.stale(params):
+        c.t["w1"], c.t["s1"] = split_weight(pred.conv1.weight.detach().permute(2, 0, 1))
+        c.t["w2"], c.t["s2"] = split_weight(pred.conv2.weight.detach().permute(2, 0, 1))
+        c.commit(params)
+    return c.t
+
+
+def run_encoder_precise(enc, src: torch.Tensor, mask_u8: torch.Tensor, kv_len: torch.Tensor):
+    """The text encoder (embedding=True) to fp32 accuracy.  Returns (LN_final(x) bf16 (B,T,D) for the frame-level
+    stack, the same as an fp16 hi|lo split (B,T,2D) for the duration predictor, and fp32)."""
+    if not enc.embedding:
+        raise NotImplementedError("run_encoder_precise: the text encoder only (embedding=True)")
+    t = enc._cache()
+    B, T = src.shape
+    D = enc.norm.weight.numel()
+    dev = src.device
+    pe = enc.pe.table(dev)
+    if T > pe.shape[0]:
+        raise ValueError(f"sequence length {T} exceeds the positional table ({pe.shape[0]}, modules.py:92)")
+    caches = [layer_cache(l) for l in enc.layers]
+    xcs = [layer_cache_x3(l) for l in enc.layers]
+    ln_first = caches[0]["ln1"] if enc.N > 0 else t["norm"]
+    f32 = lambda *s: torch.empty(s, device=dev, dtype=torch.float32)  # noqa: E731
+    f16 = lambda *s: torch.empty(s, device=dev, dtype=torch.float16)  # noqa: E731
+    x = f32(B, T, D)
+    out_bf = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
+    lib.embed_pe_ln(src.contiguous(), t["table"], pe, t["alpha"], ln_first[0], ln_first[1], LN_EPS, x, out_bf)
+    xs = f16(B, T, 2 * D)
+    out32 = f32(B, T, D)
+    lib.xrow(lib.XROW_ADD_LN, x, ln_first, out_split=xs, out_f32=out32 if enc.N == 0 else None, eps=LN_EPS)
+    H = enc.heads
+    for i, (lc, xc) in enumerate(zip(caches, xcs)):
+        last = i == enc.N - 1
+        k = lc["k"]
+        next_ln = t["norm"] if last else caches[i + 1]["ln1"]
+        qkv = lib.gemm_x3(xs, xc["wqkv"], lc["bqkv"], xc["sqkv"])                       # modules.py:49-51
+        ctx = lib.attention_x3(qkv, mask_u8, kv_len, H)                                  # modules.py:7-21,58-65
+        o = lib.gemm_x3(ctx, xc["wo"], lc["bo"], xc["so"])                               # modules.py:68
+        y, yns = f32(B, T, D), f16(B, T, 2 * D)
+        lib.xrow(lib.XROW_ADD_LN, x, lc["ln2"], b0=o, s_out=y, out_split=yns, eps=LN_EPS)  # layers.py:33,35
+        hs = lib.gemm_x3(yns, xc["w1"], lc["b1"], xc["s1"], taps=k, pad_left=k // 2, relu=True, split_out=True)
+        u = lib.gemm_x3(hs, xc["w2"], lc["b2"], xc["s2"], taps=k, pad_left=k // 2)      # modules.py:83-84
+        z, zns = f32(B, T, D), f16(B, T, 2 * D)
+        lib.xrow(lib.XROW_FFN_TAIL, u, lc["ln_ff"], b0_split=yns, c=y, ln2=next_ln, z_out=z, out_split=zns,
+                 out_bf16=out_bf if last else None, out_f32=out32 if last else None, eps=LN_EPS)  # modules.py:85-87, layers.py:40
+        x, xs = z, zns
+    return out_bf, xs, out32
+
+
+def run_predictor_precise(pred, x_split: torch.Tensor, mask_u8: Optional[torch.Tensor]) -> torch.Tensor:
+    """VariancePredictor (varianceadaptor.py:216-229) to fp32 accuracy on a split input.  Returns fp32 (B,T)."""
+    t = predictor_cache(pred)
+    xc = predictor_cache_x3(pred)
+    B, T, _ = x_split.shape
+    fs = t["b1"].numel()
+    dev = x_split.device
+    c1 = lib.gemm_x3(x_split, xc["w1"], t["b1"], xc["s1"], taps=3, pad_left=1, relu=True)   # :217-218
+    h1 = torch.empty((B, T, 2 * fs), device=dev, dtype=torch.float16)
+    lib.xrow(lib.XROW_ADD_LN, c1, t["ln1"], out_split=h1, eps=LN_EPS)                        # :219
+    c2 = lib.gemm_x3(h1, xc["w2"], t["b2"], xc["s2"], taps=3, pad_left=1, relu=True)        # :220-221
+    out = torch.empty((B, T), device=dev, dtype=torch.float32)
+    lib.xrow(lib.XROW_LN_DOT, c2, t["ln2"], dot_w=t["dw"], dot_b=t["db"], row_mask=mask_u8, out_row=out,
+             eps=LN_EPS)                                                                      # :222-229
+    return out

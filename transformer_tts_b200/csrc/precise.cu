@@ -1,0 +1,720 @@
+// fp32-accurate encoder -> duration-predictor chain on the tensor cores (SURVEY §7 "Parity conditioning", row N1).
+//
+// The reference rounds an fp32 log_d (Models/varianceadaptor.py:69,75); a bf16 encoder chain flips ~5 % of the
+// durations.  This file holds the kernels of a chain that reproduces fp32 arithmetic to ~fp32 noise
+// while still running its contractions on tcgen05 / mma tensor cores:
+//
+//   * every operand is split into two fp16 values,  v = hi + lo  (hi = fp16(v), lo = fp16(v - hi): 22 mantissa
+//     bits; weights are pre-scaled by a power of two so their lo parts stay normal), and a product is evaluated as
+//     hi*hi + lo*hi + hi*lo (the lo*lo term is below 2^-22);
+//   * the tensor core's own accumulator TRUNCATES (measured: tools/exp/tc_accum_probe.py — one round-toward-zero
+//     per K=16 MMA step, a drift of 2^-24 per step, 2.8e-5 at K = 7680), so an accumulation chain never runs
+//     longer than one 64-wide k-block (8 tiny + 4 large MMA steps): each k-block's partial sum is read back from
+//     TMEM and added in fp32 round-to-nearest REGISTERS by the epilogue warps, overlapped with the next k-block's
+//     MMAs through four TMEM accumulator buffers.
+//
+// Kernels: gemm_x3 (implicit-GEMM conv1d / linear, TMA -> tcgen05 -> TMEM -> register accumulation),
+// attention_x3 (flash-style masked attention on mma.sync m16n8k16 with the same splitting and short chains; the
+// encoder's sequences are a few hundred phonemes, <2 % of the chain's FLOPs), xrow (fp32 residual / LayerNorm /
+// FFN tail / predictor head, one warp per row) and split_f16.
+//
+// Reference ops replaced: Models/encoder.py:83-112, Models/layers.py:29-41, Models/modules.py:7-88,
+// Models/varianceadaptor.py:216-229 (the duration predictor), evaluated to fp32 accuracy.
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+#include "../../include/ttsb200.h"
+
+namespace ttsb {
+
+// ------------------------------------------------------------------------------------------------
+// fp16 hi/lo split
+// ------------------------------------------------------------------------------------------------
+// {hi(a), hi(b)} and {lo(a), lo(b)} as packed half2 words (a in the low half).  satfinite: |v| > 65504 saturates
+// instead of producing inf/NaN (the chain is specified for |activations| < 6e4).
+__device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(hi) : "f"(b), "f"(a));
+  const float2 h = __half22float2(*reinterpret_cast<const __half2*>(&hi));
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"(b - h.y), "f"(a - h.x));
+}
+
+// ------------------------------------------------------------------------------------------------
+// gemm_x3
+// ------------------------------------------------------------------------------------------------
+constexpr int kXM = 128;            // rows per tile (time steps of one utterance)
+constexpr int kXN = 128;            // output channels per tile
+constexpr int kXK = 64;             // k-block: 64 fp16 = one 128-byte swizzle row
+constexpr int kXStages = 3;
+constexpr int kXBox = 16384;        // 128 rows x 128 bytes
+constexpr int kXStageBytes = 4 * kXBox;  // A hi | A lo | W hi | W lo
+constexpr int kXNumAcc = 4;         // TMEM accumulator buffers (128 columns each)
+constexpr int kXThreads = 64 + 256; // warp 0 TMA producer, warp 1 MMA issuer, warps 2..9 accumulate / epilogue
+constexpr int kXStoreBytes = 2 * kXBox;  // one staging box per epilogue warpgroup
+constexpr int kXSmem = kXStages * kXStageBytes + kXStoreBytes + 1024;
+
+struct X3Dev {
+  int B, T, N, C, taps, pad_left, relu, out_split;
+  int m_tiles, n_tiles;
+  float inv_scale;
+  const float* bias;
+};
+
+// kind::f16 instruction descriptor with fp16 (not bf16) operands: D fp32 (1<<4), A/B format 0
+__host__ __device__ constexpr uint32_t umma_idesc_f16(uint32_t M, uint32_t N) {
+  return (1u << 4) | ((N >> 3) << 17) | ((M >> 4) << 24);
+}
+
+__device__ __forceinline__ void x_tma_store_3d(const CUtensorMap* m, uint32_t src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(src), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+__device__ __forceinline__ void x_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void x_store_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void x_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void x_wg_bar(int wg) { asm volatile("bar.sync %0, 128;" ::"r"(2 + wg) : "memory"); }
+
+__global__ void __launch_bounds__(kXThreads, 1)
+gemm_x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+               const __grid_constant__ CUtensorMap tmOut, const X3Dev p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if ((smem_u32(smem) & 1023u) != 0) {
+    if (threadIdx.x == 0) printf("ttsb200: gemm_x3 dynamic shared memory base is not 1024-byte aligned\n");
+    __trap();
+  }
+  uint8_t* sStages = smem;
+  uint8_t* sStore = smem + kXStages * kXStageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sStore + kXStoreBytes);
+  uint64_t* bar_full = bars;                            // [S]
+  uint64_t* bar_empty = bars + kXStages;                // [S]
+  uint64_t* bar_accf = bars + 2 * kXStages;             // [4] k-block partial sum complete in TMEM
+  uint64_t* bar_acce = bars + 2 * kXStages + kXNumAcc;  // [4] ... and read back by all 256 epilogue threads
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kXStages + 2 * kXNumAcc);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int kblocks = p.C / kXK;
+  const int num_iters = p.taps * kblocks;
+  const int num_tiles = p.B * p.m_tiles * p.n_tiles;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmW);
+    tma_prefetch_desc(&tmOut);
+    for (int s = 0; s < kXStages; ++s) {
+      mbar_init(smem_u32(&bar_full[s]), 1);
+      mbar_init(smem_u32(&bar_empty[s]), 1);
+    }
+    for (int i = 0; i < kXNumAcc; ++i) {
+      mbar_init(smem_u32(&bar_accf[i]), 1);
+      mbar_init(smem_u32(&bar_acce[i]), 256);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(smem_u32(tmem_slot), 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  auto decode = [&](int tile, int& b, int& t0, int& nt) {
+    const int mt = tile / p.n_tiles;
+    nt = tile - mt * p.n_tiles;
+    b = mt / p.m_tiles;
+    t0 = (mt - b * p.m_tiles) * kXM;
+  };
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      uint32_t git = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        int b, t0, nt;
+        decode(tile, b, t0, nt);
+        for (int it = 0; it < num_iters; ++it, ++git) {
+          const int s = git % kXStages;
+          mbar_wait(smem_u32(&bar_empty[s]), ((git / kXStages) & 1) ^ 1);
+          const uint32_t full = smem_u32(&bar_full[s]);
+          mbar_arrive_expect_tx(full, kXStageBytes);
+          const int tap = it / kblocks;
+          const int c0 = (it - tap * kblocks) * kXK;
+          const uint32_t st = smem_u32(sStages + s * kXStageBytes);
+          const int t = t0 + tap - p.pad_left;  // conv tap = time-shifted box; out-of-range rows are zero-filled
+          tma_load_3d(st, &tmA, full, c0, t, b);
+          tma_load_3d(st + kXBox, &tmA, full, p.C + c0, t, b);
+          tma_load_2d(st + 2 * kXBox, &tmW, full, c0, tap * p.N + nt * kXN);
+          tma_load_2d(st + 3 * kXBox, &tmW, full, p.C + c0, tap * p.N + nt * kXN);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (converged warp, one elected lane issues) =====================
+    constexpr uint32_t idesc = umma_idesc_f16(kXM, kXN);
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t leader = elect_one();
+    uint32_t git = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int it = 0; it < num_iters; ++it, ++git) {
+        const int s = git % kXStages;
+        const uint32_t ab = git % kXNumAcc;
+        mbar_wait(smem_u32(&bar_acce[ab]), ((git / kXNumAcc) & 1) ^ 1);  // buffer read back by the epilogue warps
+        mbar_wait(smem_u32(&bar_full[s]), (git / kXStages) & 1);
+        tc_fence_after();
+        const uint32_t st = smem_u32(sStages + s * kXStageBytes);
+        const uint32_t d_tmem = tb + ab * kXN;
+        if (leader) {
+          // the two small cross terms first, the large hi*hi term last: the accumulator truncates once per MMA
+          // step relative to its current magnitude, so only the last four steps cost 2^-24 each
+#pragma unroll
+          for (int k = 0; k < kXK / 16; ++k) {
+            const uint64_t a_hi = umma_smem_desc(st + k * 32, 16, 1024, kLayoutSW128);
+            const uint64_t a_lo = umma_smem_desc(st + kXBox + k * 32, 16, 1024, kLayoutSW128);
+            const uint64_t w_hi = umma_smem_desc(st + 2 * kXBox + k * 32, 16, 1024, kLayoutSW128);
+            const uint64_t w_lo = umma_smem_desc(st + 3 * kXBox + k * 32, 16, 1024, kLayoutSW128);
+            umma_bf16(d_tmem, a_lo, w_hi, idesc, k != 0 ? 1u : 0u);
+            umma_bf16(d_tmem, a_hi, w_lo, idesc, 1u);
+          }
+#pragma unroll
+          for (int k = 0; k < kXK / 16; ++k) {
+            const uint64_t a_hi = umma_smem_desc(st + k * 32, 16, 1024, kLayoutSW128);
+            const uint64_t w_hi = umma_smem_desc(st + 2 * kXBox + k * 32, 16, 1024, kLayoutSW128);
+            umma_bf16(d_tmem, a_hi, w_hi, idesc, 1u);
+          }
+          umma_commit(smem_u32(&bar_empty[s]));
+          umma_commit(smem_u32(&bar_accf[ab]));
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    // ===================== accumulate + epilogue warps: thread == output row == TMEM lane =====================
+    const int e = warp - 2;
+    const int wg = e >> 2;          // column half of the tile
+    const int q = warp & 3;         // TMEM lane quarter this warp may touch
+    const int row = q * 32 + lane;
+    const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
+    uint8_t* my_box = sStore + wg * kXBox;
+    uint32_t git = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      int b, t0, nt;
+      decode(tile, b, t0, nt);
+      float acc[64];
+#pragma unroll
+      for (int i = 0; i < 64; ++i) acc[i] = 0.f;
+      for (int it = 0; it < num_iters; ++it, ++git) {
+        const uint32_t ab = git % kXNumAcc;
+        mbar_wait(smem_u32(&bar_accf[ab]), (git / kXNumAcc) & 1);
+        tc_fence_after();
+        float v[64];
+        const uint32_t ta = tmem_base + ab * kXN + wg * 64 + lane_off;
+        tmem_ld32(ta, v);
+        tmem_ld32(ta + 32, v + 32);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(smem_u32(&bar_acce[ab]));  // the values are in registers: the buffer is free again
+#pragma unroll
+        for (int i = 0; i < 64; i += 2) add2(acc[i], acc[i + 1], v[i], v[i + 1]);  // fp32 round-to-nearest
+      }
+      // ---- tile epilogue: v = acc * 2^-e + bias (+ ReLU) -> fp32 boxes or fp16 hi | lo boxes -> TMA store ----
+      const int n0 = nt * kXN + wg * 64;
+#pragma unroll
+      for (int i = 0; i < 64; ++i) {
+        acc[i] = fmaf(acc[i], p.inv_scale, __ldg(p.bias + n0 + i));
+        if (p.relu) acc[i] = fmaxf(acc[i], 0.f);
+      }
+      if (!p.out_split) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          if (row == 0) x_store_wait_read0();  // the previous store from this box has read it
+          x_wg_bar(wg);
+          uint8_t* rp = my_box + row * 128;
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(rp + ((j ^ (row & 7)) << 4)) =
+                make_float4(acc[h * 32 + 4 * j], acc[h * 32 + 4 * j + 1], acc[h * 32 + 4 * j + 2], acc[h * 32 + 4 * j + 3]);
+          fence_async_smem();
+          x_wg_bar(wg);
+          if (row == 0) {
+            x_tma_store_3d(&tmOut, smem_u32(my_box), n0 + h * 32, t0, b);
+            x_store_commit();
+          }
+        }
+      } else {
+        uint32_t hi[32], lo[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) split2(acc[2 * i], acc[2 * i + 1], hi[i], lo[i]);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const uint32_t* src = h == 0 ? hi : lo;
+          if (row == 0) x_store_wait_read0();
+          x_wg_bar(wg);
+          uint8_t* rp = my_box + row * 128;
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<uint4*>(rp + ((j ^ (row & 7)) << 4)) =
+                make_uint4(src[4 * j], src[4 * j + 1], src[4 * j + 2], src[4 * j + 3]);
+          fence_async_smem();
+          x_wg_bar(wg);
+          if (row == 0) {
+            x_tma_store_3d(&tmOut, smem_u32(my_box), h * p.N + n0, t0, b);
+            x_store_commit();
+          }
+        }
+      }
+    }
+    if (row == 0) x_store_wait_all();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+// ------------------------------------------------------------------------------------------------
+// attention_x3: softmax(mask(q k^T / sqrt(dk), -1e4)) v on mma.sync with split operands and short chains.
+//   qkv fp32 (B,T,3*H*96) -> ctx fp16 hi | lo (B,T,2*H*96)
+// One CTA = 64 queries of one (utterance, head), 4 warps x 16 rows; 64-key tiles of K and V are split into fp16
+// hi / lo planes in shared memory ([key][dim], 208-byte rows: conflict-free for the fragment loads and ldmatrix).
+// ------------------------------------------------------------------------------------------------
+constexpr int kADh = 96;
+constexpr int kABQ = 64;
+constexpr int kABK = 64;
+constexpr int kAPitch = 104;  // halfs per smem row (208 bytes)
+constexpr int kAPlane = kABK * kAPitch * 2;                   // bytes of one plane
+constexpr int kASmem = 4 * kAPlane + 64;                      // K hi, K lo, V hi, V lo, key flags
+constexpr float kAInScale = 16.f;     // q, k, v are scaled by 2^4 before the split (their lo parts stay normal)
+constexpr float kAPScale = 1024.f;    // p <= 1 is scaled by 2^10 before the split
+
+__device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void ldmatrix_x2_trans(uint32_t& r0, uint32_t& r1, uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0, %1}, [%2];" : "=r"(r0), "=r"(r1) : "r"(addr));
+}
+
+__global__ void __launch_bounds__(128)
+attention_x3_kernel(const float* __restrict__ qkv, const uint8_t* __restrict__ mask, const int32_t* __restrict__ kv_info,
+                    __half* __restrict__ ctx, int T, int H) {
+  extern __shared__ __align__(16) uint8_t asmem[];
+  __half* sKh = reinterpret_cast<__half*>(asmem);
+  __half* sKl = reinterpret_cast<__half*>(asmem + kAPlane);
+  __half* sVh = reinterpret_cast<__half*>(asmem + 2 * kAPlane);
+  __half* sVl = reinterpret_cast<__half*>(asmem + 3 * kAPlane);
+  uint8_t* sflag = asmem + 4 * kAPlane;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, t4 = lane & 3;
+  const int q0 = blockIdx.x * kABQ, h = blockIdx.y, b = blockIdx.z;
+  const int D = H * kADh;
+  const int64_t ld = 3LL * D;
+  const float* base = qkv + static_cast<int64_t>(b) * T * ld;
+  const int klen = kv_info[2 * b];
+  const int kv_eff = klen > 0 ? klen : T;  // no valid key: uniform over all T keys like the reference
+  const int nkv = (kv_eff + kABK - 1) / kABK;
+
+  // ---- Q fragments (rows g and g + 8 of this warp's 16), split ----
+  uint32_t qh[6][4], ql[6][4];
+  {
+    const int r0 = q0 + warp * 16 + g, r1 = r0 + 8;
+    const float* p0 = base + static_cast<int64_t>(r0 < T ? r0 : 0) * ld + h * kADh;
+    const float* p1 = base + static_cast<int64_t>(r1 < T ? r1 : 0) * ld + h * kADh;
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      const float2 a = *reinterpret_cast<const float2*>(p0 + 16 * j + 2 * t4);
+      const float2 c = *reinterpret_cast<const float2*>(p1 + 16 * j + 2 * t4);
+      const float2 d = *reinterpret_cast<const float2*>(p0 + 16 * j + 8 + 2 * t4);
+      const float2 f = *reinterpret_cast<const float2*>(p1 + 16 * j + 8 + 2 * t4);
+      split2(a.x * kAInScale, a.y * kAInScale, qh[j][0], ql[j][0]);
+      split2(c.x * kAInScale, c.y * kAInScale, qh[j][1], ql[j][1]);
+      split2(d.x * kAInScale, d.y * kAInScale, qh[j][2], ql[j][2]);
+      split2(f.x * kAInScale, f.y * kAInScale, qh[j][3], ql[j][3]);
+    }
+  }
+  const float s_scale = 1.f / (sqrtf(static_cast<float>(kADh)) * kAInScale * kAInScale);
+  float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+  float o[12][4];
+#pragma unroll
+  for (int i = 0; i < 12; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+
+  for (int jt = 0; jt < nkv; ++jt) {
+    __syncthreads();  // the previous tile's fragments have been read
+    // ---- K, V tile -> hi / lo planes ----
+    for (int i = threadIdx.x; i < kABK * 24; i += 128) {
+      const int key = i / 24, c4 = i - key * 24;
+      const int kg = jt * kABK + key;
+      float4 kk = make_float4(0.f, 0.f, 0.f, 0.f), vv = kk;
+      if (kg < T) {
+        const float* rp = base + static_cast<int64_t>(kg) * ld + h * kADh + 4 * c4;
+        kk = *reinterpret_cast<const float4*>(rp + D);
+        vv = *reinterpret_cast<const float4*>(rp + 2 * D);
+      }
+      uint32_t h0, h1, e0, e1;
+      split2(kk.x * kAInScale, kk.y * kAInScale, h0, e0);
+      split2(kk.z * kAInScale, kk.w * kAInScale, h1, e1);
+      *reinterpret_cast<uint2*>(sKh + key * kAPitch + 4 * c4) = make_uint2(h0, h1);
+      *reinterpret_cast<uint2*>(sKl + key * kAPitch + 4 * c4) = make_uint2(e0, e1);
+      split2(vv.x * kAInScale, vv.y * kAInScale, h0, e0);
+      split2(vv.z * kAInScale, vv.w * kAInScale, h1, e1);
+      *reinterpret_cast<uint2*>(sVh + key * kAPitch + 4 * c4) = make_uint2(h0, h1);
+      *reinterpret_cast<uint2*>(sVl + key * kAPitch + 4 * c4) = make_uint2(e0, e1);
+    }
+    if (threadIdx.x < kABK) {
+      const int kg = jt * kABK + threadIdx.x;
+      sflag[threadIdx.x] = kg < T ? (mask[static_cast<int64_t>(b) * T + kg] ? 1 : 0) : 2;
+    }
+    __syncthreads();
+
+    // ---- S = Q K^T (16 x 64 per warp) ----
+    float s[8][4];
+#pragma unroll
+    for (int nb = 0; nb < 8; ++nb) {
+      float c_lo[4] = {0.f, 0.f, 0.f, 0.f}, c_hi[4] = {0.f, 0.f, 0.f, 0.f};
+      const __half* kh = sKh + (nb * 8 + g) * kAPitch + 2 * t4;
+      const __half* kl = sKl + (nb * 8 + g) * kAPitch + 2 * t4;
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        const uint32_t bh0 = *reinterpret_cast<const uint32_t*>(kh + 16 * j);
+        const uint32_t bh1 = *reinterpret_cast<const uint32_t*>(kh + 16 * j + 8);
+        const uint32_t bl0 = *reinterpret_cast<const uint32_t*>(kl + 16 * j);
+        const uint32_t bl1 = *reinterpret_cast<const uint32_t*>(kl + 16 * j + 8);
+        mma16816(c_lo, ql[j], bh0, bh1);
+        mma16816(c_lo, qh[j], bl0, bl1);
+        mma16816(c_hi, qh[j], bh0, bh1);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) s[nb][i] = (c_hi[i] + c_lo[i]) * s_scale;
+      // mask like the reference: -1e4 on padded keys (modules.py:14); keys beyond T do not exist
+      const uint8_t f0 = sflag[nb * 8 + 2 * t4], f1 = sflag[nb * 8 + 2 * t4 + 1];
+      if (f0 != 1) { const float mv = f0 == 0 ? -1e4f : -INFINITY; s[nb][0] = mv; s[nb][2] = mv; }
+      if (f1 != 1) { const float mv = f1 == 0 ? -1e4f : -INFINITY; s[nb][1] = mv; s[nb][3] = mv; }
+    }
+    // ---- online softmax (rows g: elements 0,1; rows g + 8: elements 2,3) ----
+    float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+    for (int nb = 0; nb < 8; ++nb) {
+      mx0 = fmaxf(mx0, fmaxf(s[nb][0], s[nb][1]));
+      mx1 = fmaxf(mx1, fmaxf(s[nb][2], s[nb][3]));
+    }
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+    const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
+    const float al0 = expf(m0 - mn0), al1 = expf(m1 - mn1);  // m = -inf on the first tile -> 0
+    m0 = mn0; m1 = mn1;
+    l0 *= al0; l1 *= al1;
+#pragma unroll
+    for (int i = 0; i < 12; ++i) { o[i][0] *= al0; o[i][1] *= al0; o[i][2] *= al1; o[i][3] *= al1; }
+    uint32_t ph[4][4], pl[4][4];
+#pragma unroll
+    for (int nb = 0; nb < 8; ++nb) {
+      const float p0 = expf(s[nb][0] - m0), p1 = expf(s[nb][1] - m0);
+      const float p2 = expf(s[nb][2] - m1), p3 = expf(s[nb][3] - m1);
+      l0 += p0 + p1;
+      l1 += p2 + p3;
+      // C fragment of key blocks 2jj, 2jj+1 == A fragment of k-step jj
+      const int jj = nb >> 1, o2 = (nb & 1) * 2;
+      split2(p0 * kAPScale, p1 * kAPScale, ph[jj][o2], pl[jj][o2]);
+      split2(p2 * kAPScale, p3 * kAPScale, ph[jj][o2 + 1], pl[jj][o2 + 1]);
+    }
+    // ---- O += P V (16 x 96 per warp); V fragments through ldmatrix.trans from the [key][dim] planes ----
+#pragma unroll
+    for (int db = 0; db < 12; ++db) {
+      float c_lo[4] = {0.f, 0.f, 0.f, 0.f}, c_hi[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj) {
+        // lanes 0..15 supply the row addresses: keys 16jj + (lane & 15), dims [8db, 8db + 8)
+        const int krow = 16 * jj + (lane & 15);
+        uint32_t vh0, vh1, vl0, vl1;
+        ldmatrix_x2_trans(vh0, vh1, smem_u32(sVh + krow * kAPitch + 8 * db));
+        ldmatrix_x2_trans(vl0, vl1, smem_u32(sVl + krow * kAPitch + 8 * db));
+        mma16816(c_lo, pl[jj], vh0, vh1);
+        mma16816(c_lo, ph[jj], vl0, vl1);
+        mma16816(c_hi, ph[jj], vh0, vh1);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) o[db][i] += c_hi[i] + c_lo[i];
+    }
+  }
+  // ---- O / l -> fp16 hi | lo ----
+  l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+  l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+  l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+  l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+  const float inv0 = 1.f / (l0 * kAPScale * kAInScale), inv1 = 1.f / (l1 * kAPScale * kAInScale);
+  const int r0 = q0 + warp * 16 + g, r1 = r0 + 8;
+#pragma unroll
+  for (int db = 0; db < 12; ++db) {
+    const int col = h * kADh + 8 * db + 2 * t4;
+    uint32_t hi, lo;
+    if (r0 < T) {
+      split2(o[db][0] * inv0, o[db][1] * inv0, hi, lo);
+      __half* cp = ctx + (static_cast<int64_t>(b) * T + r0) * (2 * D);
+      *reinterpret_cast<uint32_t*>(cp + col) = hi;
+      *reinterpret_cast<uint32_t*>(cp + D + col) = lo;
+    }
+    if (r1 < T) {
+      split2(o[db][2] * inv1, o[db][3] * inv1, hi, lo);
+      __half* cp = ctx + (static_cast<int64_t>(b) * T + r1) * (2 * D);
+      *reinterpret_cast<uint32_t*>(cp + col) = hi;
+      *reinterpret_cast<uint32_t*>(cp + D + col) = lo;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// xrow: fp32 row operations of the chain, one warp per row, D = 128 * NV (256 or 384)
+//   s  = a (+ b0 | + hi/lo pair b0_split);  s_out = s
+//   t  = LN(s; g1, b1)
+//   mode ADD_LN:   out = t
+//   mode FFN_TAIL: z = c + t ; z_out = z ; out = LN(z; g2, b2)
+//   mode LN_DOT:   out_row = mask ? dot(t, w) + wb : 0
+//   out -> fp16 hi | lo (rows, 2D) and/or bf16 (rows, D) and/or fp32
+// ------------------------------------------------------------------------------------------------
+struct XRowArgs {
+  const float* a;
+  const float* b0;
+  const __half* b0_split;
+  const float* c;
+  const float *g1, *b1, *g2, *b2;
+  const float* dot_w;
+  const float* dot_b;
+  const uint8_t* row_mask;
+  float* s_out;
+  float* z_out;
+  __half* out_split;
+  __nv_bfloat16* out_bf16;
+  float* out_f32;
+  float* out_row;
+  float eps;
+  int64_t rows;
+  int mode;
+};
+enum { XROW_ADD_LN = 0, XROW_FFN_TAIL = 1, XROW_LN_DOT = 2 };
+
+template <int NV>
+__device__ __forceinline__ void xrow_ln(float4 (&v)[NV], const float* __restrict__ g, const float* __restrict__ b,
+                                        float eps, int lane) {
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+  const float mean = warp_sum(s) * (1.f / (128.f * NV));
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const float a = v[i].x - mean, c = v[i].y - mean, d = v[i].z - mean, e = v[i].w - mean;
+    q += (a * a + c * c) + (d * d + e * e);
+  }
+  // 1 / sqrt(var + eps) with an IEEE square root and division, as the reference's layer_norm does
+  const float rstd = 1.f / sqrtf(warp_sum(q) * (1.f / (128.f * NV)) + eps);
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const float4 gg = __ldg(reinterpret_cast<const float4*>(g) + i * 32 + lane);
+    const float4 bb = __ldg(reinterpret_cast<const float4*>(b) + i * 32 + lane);
+    v[i].x = fmaf((v[i].x - mean) * rstd, gg.x, bb.x);
+    v[i].y = fmaf((v[i].y - mean) * rstd, gg.y, bb.y);
+    v[i].z = fmaf((v[i].z - mean) * rstd, gg.z, bb.z);
+    v[i].w = fmaf((v[i].w - mean) * rstd, gg.w, bb.w);
+  }
+}
+
+template <int NV>
+__global__ void __launch_bounds__(256) xrow_kernel(const XRowArgs p) {
+  constexpr int D = 128 * NV;
+  const int lane = threadIdx.x & 31;
+  const int64_t row = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= p.rows) return;
+  float4 v[NV];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    v[i] = *(reinterpret_cast<const float4*>(p.a + row * D) + i * 32 + lane);
+    if (p.b0) {
+      const float4 r = *(reinterpret_cast<const float4*>(p.b0 + row * D) + i * 32 + lane);
+      v[i].x += r.x; v[i].y += r.y; v[i].z += r.z; v[i].w += r.w;
+    }
+    if (p.b0_split) {
+      const uint2 hh = *(reinterpret_cast<const uint2*>(p.b0_split + row * 2 * D) + i * 32 + lane);
+      const uint2 ll = *(reinterpret_cast<const uint2*>(p.b0_split + row * 2 * D + D) + i * 32 + lane);
+      const float2 h0 = __half22float2(*reinterpret_cast<const __half2*>(&hh.x));
+      const float2 h1 = __half22float2(*reinterpret_cast<const __half2*>(&hh.y));
+      const float2 e0 = __half22float2(*reinterpret_cast<const __half2*>(&ll.x));
+      const float2 e1 = __half22float2(*reinterpret_cast<const __half2*>(&ll.y));
+      v[i].x += h0.x + e0.x; v[i].y += h0.y + e0.y; v[i].z += h1.x + e1.x; v[i].w += h1.y + e1.y;
+    }
+    if (p.s_out) reinterpret_cast<float4*>(p.s_out + row * D)[i * 32 + lane] = v[i];
+  }
+  xrow_ln<NV>(v, p.g1, p.b1, p.eps, lane);
+  if (p.mode == XROW_LN_DOT) {
+    float dot = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const float4 w = __ldg(reinterpret_cast<const float4*>(p.dot_w) + i * 32 + lane);
+      dot = fmaf(v[i].x, w.x, dot); dot = fmaf(v[i].y, w.y, dot);
+      dot = fmaf(v[i].z, w.z, dot); dot = fmaf(v[i].w, w.w, dot);
+    }
+    dot = warp_sum(dot);
+    if (lane == 0) {
+      float o = dot + __ldg(p.dot_b);
+      if (p.row_mask && p.row_mask[row] == 0) o = 0.f;
+      p.out_row[row] = o;
+    }
+    return;
+  }
+  if (p.mode == XROW_FFN_TAIL) {
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const float4 r = *(reinterpret_cast<const float4*>(p.c + row * D) + i * 32 + lane);
+      v[i].x += r.x; v[i].y += r.y; v[i].z += r.z; v[i].w += r.w;
+      if (p.z_out) reinterpret_cast<float4*>(p.z_out + row * D)[i * 32 + lane] = v[i];
+    }
+    xrow_ln<NV>(v, p.g2, p.b2, p.eps, lane);
+  }
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    if (p.out_split) {
+      uint2 hh, ll;
+      split2(v[i].x, v[i].y, hh.x, ll.x);
+      split2(v[i].z, v[i].w, hh.y, ll.y);
+      reinterpret_cast<uint2*>(p.out_split + row * 2 * D)[i * 32 + lane] = hh;
+      reinterpret_cast<uint2*>(p.out_split + row * 2 * D + D)[i * 32 + lane] = ll;
+    }
+    if (p.out_bf16) {
+      uint2 u;
+      u.x = pack_bf16(v[i].x, v[i].y);
+      u.y = pack_bf16(v[i].z, v[i].w);
+      reinterpret_cast<uint2*>(p.out_bf16 + row * D)[i * 32 + lane] = u;
+    }
+    if (p.out_f32) reinterpret_cast<float4*>(p.out_f32 + row * D)[i * 32 + lane] = v[i];
+  }
+}
+
+// fp32 (rows, D) * scale -> fp16 hi | lo (rows, 2D); D % 4 == 0
+__global__ void split_f16_kernel(const float* __restrict__ x, __half* __restrict__ out, int64_t rows, int D, float scale) {
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int d4 = D / 4;
+  if (i >= rows * d4) return;
+  const int64_t r = i / d4;
+  const int c = static_cast<int>(i - r * d4);
+  const float4 v = *(reinterpret_cast<const float4*>(x + r * D) + c);
+  uint2 hh, ll;
+  split2(v.x * scale, v.y * scale, hh.x, ll.x);
+  split2(v.z * scale, v.w * scale, hh.y, ll.y);
+  *(reinterpret_cast<uint2*>(out + r * 2 * D) + c) = hh;
+  *(reinterpret_cast<uint2*>(out + r * 2 * D + D) + c) = ll;
+}
+
+}  // namespace ttsb
+
+using namespace ttsb;
+
+static inline bool x_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+extern "C" int ttsb200_gemm_x3(const void* x_split, const void* w_split, const float* bias, float inv_scale,
+                               int32_t B, int32_t T, int32_t N, int32_t C, int32_t taps, int32_t pad_left,
+                               int32_t relu, float* out_f32, void* out_split, ttsb200_stream_t stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  TTSB_CHECK_ARG(x_split && w_split && bias, "gemm_x3: null operand");
+  TTSB_CHECK_ARG(B > 0 && T > 0 && taps > 0, "gemm_x3: bad dims");
+  TTSB_CHECK_ARG(N % kXN == 0 && N > 0, "gemm_x3: N (%d) must be a multiple of %d", N, kXN);
+  TTSB_CHECK_ARG(C % kXK == 0 && C > 0, "gemm_x3: C (%d) must be a multiple of %d", C, kXK);
+  TTSB_CHECK_ARG((out_f32 != nullptr) != (out_split != nullptr), "gemm_x3: exactly one of out_f32 / out_split");
+  TTSB_CHECK_ARG(x_aligned16(x_split) && x_aligned16(w_split) && x_aligned16(out_f32) && x_aligned16(out_split),
+                 "gemm_x3: operands must be 16-byte aligned");
+  CUtensorMap tmA, tmW, tmOut;
+  const uint64_t uT = static_cast<uint64_t>(T), uB = static_cast<uint64_t>(B), uN = static_cast<uint64_t>(N);
+  {
+    const uint64_t dims[3] = {2ull * C, uT, uB};
+    const uint64_t strides[2] = {4ull * C, 4ull * C * uT};
+    const uint32_t box[3] = {kXK, kXM, 1};
+    int rc = make_tmap(&tmA, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, x_split, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+  }
+  {
+    const uint64_t dims[2] = {2ull * C, static_cast<uint64_t>(taps) * uN};
+    const uint64_t strides[1] = {4ull * C};
+    const uint32_t box[2] = {kXK, kXN};
+    int rc = make_tmap(&tmW, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, w_split, 2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+  }
+  if (out_f32) {
+    const uint64_t dims[3] = {uN, uT, uB};
+    const uint64_t strides[2] = {uN * 4, uN * 4 * uT};
+    const uint32_t box[3] = {32, kXM, 1};
+    int rc = make_tmap(&tmOut, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, out_f32, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+  } else {
+    const uint64_t dims[3] = {2 * uN, uT, uB};
+    const uint64_t strides[2] = {uN * 4, uN * 4 * uT};
+    const uint32_t box[3] = {64, kXM, 1};
+    int rc = make_tmap(&tmOut, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, out_split, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+  }
+  TTSB_SMEM_OPT_IN(gemm_x3_kernel, kXSmem);
+  X3Dev d;
+  d.B = B; d.T = T; d.N = N; d.C = C; d.taps = taps; d.pad_left = pad_left; d.relu = relu; d.out_split = out_split ? 1 : 0;
+  d.m_tiles = (T + kXM - 1) / kXM;
+  d.n_tiles = N / kXN;
+  d.inv_scale = inv_scale;
+  d.bias = bias;
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int tiles = B * d.m_tiles * d.n_tiles;
+  const int grid = tiles < sms ? tiles : sms;
+  gemm_x3_kernel<<<grid, kXThreads, kXSmem, stream>>>(tmA, tmW, tmOut, d);
+  TTSB_CHECK_CUDA(cudaGetLastError());
+  return TTSB_OK;
+}
+
+extern "C" int ttsb200_attention_x3(const float* qkv_f32, const uint8_t* mask, const int32_t* kv_info, void* ctx_split,
+                                    int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t stream) {
+  TTSB_CHECK_ARG(qkv_f32 && mask && kv_info && ctx_split, "attention_x3: null pointer");
+  TTSB_CHECK_ARG(B > 0 && T > 0 && H > 0, "attention_x3: bad dims");
+  TTSB_CHECK_ARG(Dh == kADh, "attention_x3: head dim %d unsupported (this build: %d)", Dh, kADh);
+  TTSB_CHECK_ARG(x_aligned16(qkv_f32) && x_aligned16(ctx_split), "attention_x3: qkv/ctx must be 16-byte aligned");
+  TTSB_SMEM_OPT_IN(attention_x3_kernel, kASmem);
+  dim3 grid((T + kABQ - 1) / kABQ, H, B);
+  attention_x3_kernel<<<grid, 128, kASmem, static_cast<cudaStream_t>(stream)>>>(
+      qkv_f32, mask, kv_info, static_cast<__half*>(ctx_split), T, H);
+  TTSB_CHECK_CUDA(cudaGetLastError());
+  return TTSB_OK;
+}
+
+extern "C" int ttsb200_xrow(int32_t mode, const float* a, const float* b0, const void* b0_split, const float* c,
+                            const float* g1, const float* b1, const float* g2, const float* b2, const float* dot_w,
+                            const float* dot_b, const uint8_t* row_mask, float eps, float* s_out, float* z_out,
+                            void* out_split, void* out_bf16, float* out_f32, float* out_row, int64_t rows, int32_t D,
+                            ttsb200_stream_t stream) {
+  TTSB_CHECK_ARG(a && g1 && b1 && rows > 0, "xrow: bad args");
+  TTSB_CHECK_ARG(mode >= XROW_ADD_LN && mode <= XROW_LN_DOT, "xrow: bad mode %d", mode);
+  TTSB_CHECK_ARG(!(b0 && b0_split), "xrow: b0 and b0_split are exclusive");
+  if (mode == XROW_FFN_TAIL) TTSB_CHECK_ARG(c && g2 && b2, "xrow: FFN_TAIL needs c, g2, b2");
+  if (mode == XROW_LN_DOT) TTSB_CHECK_ARG(dot_w && dot_b && out_row, "xrow: LN_DOT needs dot_w, dot_b, out_row");
+  else TTSB_CHECK_ARG(out_split || out_bf16 || out_f32, "xrow: no output");
+  XRowArgs p;
+  p.a = a; p.b0 = b0; p.b0_split = static_cast<const __half*>(b0_split); p.c = c;
+  p.g1 = g1; p.b1 = b1; p.g2 = g2; p.b2 = b2; p.dot_w = dot_w; p.dot_b = dot_b; p.row_mask = row_mask;
+  p.s_out = s_out; p.z_out = z_out; p.out_split = static_cast<__half*>(out_split);
+  p.out_bf16 = static_cast<__nv_bfloat16*>(out_bf16); p.out_f32 = out_f32; p.out_row = out_row;
+  p.eps = eps; p.rows = rows; p.mode = mode;
+  const unsigned grid = static_cast<unsigned>((rows + 7) / 8);
+  if (D == 384) xrow_kernel<3><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  else if (D == 256) xrow_kernel<2><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  else TTSB_CHECK_ARG(false, "xrow: D=%d unsupported (256 or 384)", D);
+  TTSB_CHECK_CUDA(cudaGetLastError());
+  return TTSB_OK;
+}
+
+extern "C" int ttsb200_split_f16(const float* x, void* out_split, int64_t rows, int32_t D, float scale,
+                                 ttsb200_stream_t stream) {
+  TTSB_CHECK_ARG(x && out_split && rows > 0 && D > 0 && D % 4 == 0, "split_f16: bad args");
+  const int64_t n = rows * (D / 4);
+  split_f16_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      x, static_cast<__half*>(out_split), rows, D, scale);
+  TTSB_CHECK_CUDA(cudaGetLastError());
+  return TTSB_OK;
+}

@@ -82,6 +82,12 @@ _SIGNATURES = {
     "ttsb200_sumsq": ([C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p], C.c_int),
     "ttsb200_adam_step": ([C.c_void_p] * 5 + [C.c_int64] + [C.c_float] * 6 + [C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_radam_step": ([C.c_void_p] * 5 + [C.c_int64] + [C.c_float] * 6 + [C.c_int32, C.c_void_p], C.c_int),
+    # ---- fp32-accurate encoder -> duration chain ----
+    "ttsb200_gemm_x3": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_float] + [C.c_int32] * 7 + [C.c_void_p] * 3, C.c_int),
+    "ttsb200_attention_x3": ([C.c_void_p] * 4 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
+    "ttsb200_xrow": ([C.c_int32] + [C.c_void_p] * 11 + [C.c_float] + [C.c_void_p] * 6 + [C.c_int64, C.c_int32,
+                                                                                        C.c_void_p], C.c_int),
+    "ttsb200_split_f16": ([C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_float, C.c_void_p], C.c_int),
     "ttsb200_ffn2_tail": ([C.c_void_p] * 7 + [C.c_float] + [C.c_void_p] * 4 + [C.c_int64, C.c_int32, C.c_void_p],
                           C.c_int),
 }
@@ -504,4 +510,66 @@ def radam_step(p, g, m, v, sumsq_t, *, gscale: float, clip: float, lr: float, be
                                      _ptr(m, torch.float32, "m"), _ptr(v, torch.float32, "v"),
                                      _ptr(sumsq_t, torch.float32, "sumsq"), p.numel(), gscale, clip, lr, beta1, beta2,
                                      eps, step, _stream()), "radam_step")
+    _count()
+
+
+# --------------------------------------------------------------------------------------------------
+# fp32-accurate encoder -> duration chain (include/ttsb200.h, "fp32-ACCURATE ENCODER -> DURATION CHAIN")
+# "split" tensors are fp16 (.., 2C) = [hi | lo] with value = hi + lo
+# --------------------------------------------------------------------------------------------------
+XROW_ADD_LN, XROW_FFN_TAIL, XROW_LN_DOT = range(3)
+
+
+def split_f16(x: torch.Tensor, scale: float = 1.0) -> torch.Tensor:
+    D = x.shape[-1]
+    out = torch.empty(x.shape[:-1] + (2 * D,), device=x.device, dtype=torch.float16)
+    _check(load().ttsb200_split_f16(_ptr(x, torch.float32, "x"), _ptr(out), x.numel() // D, D, scale, _stream()),
+           "split_f16")
+    _count()
+    return out
+
+
+def gemm_x3(x_split: torch.Tensor, w_split: torch.Tensor, bias: torch.Tensor, inv_scale: float, *, taps: int = 1,
+            pad_left: int = 0, relu: bool = False, split_out: bool = False) -> torch.Tensor:
+    """x_split fp16 (B,T,2C); w_split fp16 (taps,N,2C).  Returns fp32 (B,T,N) or the fp16 split (B,T,2N)."""
+    B, T, C2 = x_split.shape
+    tw, N, Cw2 = w_split.shape
+    if tw != taps or Cw2 != C2:
+        raise ValueError(f"gemm_x3: weight {tuple(w_split.shape)} does not match taps={taps}, 2C={C2}")
+    dev = x_split.device
+    out32 = None if split_out else torch.empty((B, T, N), device=dev, dtype=torch.float32)
+    outs = torch.empty((B, T, 2 * N), device=dev, dtype=torch.float16) if split_out else None
+    _check(load().ttsb200_gemm_x3(_ptr(x_split, torch.float16, "x_split"), _ptr(w_split, torch.float16, "w_split"),
+                                  _ptr(bias, torch.float32, "bias"), inv_scale, B, T, N, C2 // 2, taps, pad_left,
+                                  int(relu), _ptr(out32), _ptr(outs), _stream()), "gemm_x3")
+    _count()
+    return outs if split_out else out32
+
+
+def attention_x3(qkv32: torch.Tensor, mask: torch.Tensor, kv_len: torch.Tensor, H: int) -> torch.Tensor:
+    B, T, W = qkv32.shape
+    D = W // 3
+    ctx = torch.empty((B, T, 2 * D), device=qkv32.device, dtype=torch.float16)
+    _check(load().ttsb200_attention_x3(_ptr(qkv32, torch.float32, "qkv"), _ptr(mask, torch.uint8, "mask"),
+                                       _ptr(kv_len, torch.int32, "kv_len"), _ptr(ctx), B, T, H, D // H, _stream()),
+           "attention_x3")
+    _count()
+    return ctx
+
+
+def xrow(mode: int, a: torch.Tensor, ln1: tuple, *, b0=None, b0_split=None, c=None, ln2=None, dot_w=None, dot_b=None,
+         row_mask=None, eps: float = 1e-5, s_out=None, z_out=None, out_split=None, out_bf16=None, out_f32=None,
+         out_row=None) -> None:
+    D = a.shape[-1]
+    rows = a.numel() // D
+    g2, b2 = (ln2 if ln2 is not None else (None, None))
+    _check(load().ttsb200_xrow(mode, _ptr(a, torch.float32, "a"), _ptr(b0, torch.float32, "b0"),
+                               _ptr(b0_split, torch.float16, "b0_split"), _ptr(c, torch.float32, "c"),
+                               _ptr(ln1[0], torch.float32, "g1"), _ptr(ln1[1], torch.float32, "b1"),
+                               _ptr(g2, torch.float32, "g2"), _ptr(b2, torch.float32, "b2"),
+                               _ptr(dot_w, torch.float32, "dot_w"), _ptr(dot_b, torch.float32, "dot_b"),
+                               _ptr(row_mask, torch.uint8, "row_mask"), eps, _ptr(s_out, torch.float32, "s_out"),
+                               _ptr(z_out, torch.float32, "z_out"), _ptr(out_split, torch.float16, "out_split"),
+                               _ptr(out_bf16, torch.bfloat16, "out_bf16"), _ptr(out_f32, torch.float32, "out_f32"),
+                               _ptr(out_row, torch.float32, "out_row"), rows, D, _stream()), "xrow")
     _count()
