@@ -201,9 +201,9 @@ int ttsb200_gemm_x3(const void* x_split, const void* w_split, const float* bias,
                     int32_t T, int32_t N, int32_t C, int32_t taps, int32_t pad_left, int32_t relu, float* out_f32,
                     void* out_split, ttsb200_stream_t stream);
 
-/* Models/modules.py:7-21 on fp32 q|k|v (B,T,3*H*Dh): ctx_split fp16 (B,T,2*H*Dh).  mask / kv_info as in
- * ttsb200_attention_fwd.  Dh must be 96. */
-int ttsb200_attention_x3(const float* qkv_f32, const uint8_t* mask, const int32_t* kv_info, void* ctx_split,
+/* Models/modules.py:7-21 on the split q|k|v (fp16 (B,T,2*3*H*Dh) = [q k v hi | q k v lo], ttsb200_gemm_x3's split
+ * output): ctx_split fp16 (B,T,2*H*Dh).  mask / kv_info as in ttsb200_attention_fwd.  Dh must be 96. */
+int ttsb200_attention_x3(const void* qkv_split, const uint8_t* mask, const int32_t* kv_info, void* ctx_split,
                          int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t stream);
 
 /* fp32 row operations of the chain (one warp per row, D = 256 or 384):

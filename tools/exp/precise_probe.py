@@ -37,7 +37,7 @@ lens = torch.tensor([200, 131, 64])
 mask = (torch.arange(T)[None] < lens[:, None]).to(torch.uint8).to(dev)
 mask[1, 5] = 0
 kv = lib.mask_lengths(mask)
-ctx = lib.attention_x3(qkv, mask, kv, H)
+ctx = lib.attention_x3(lib.split_f16(qkv), mask, kv, H)
 D = H * Dh
 got = ctx[..., :D].double() + ctx[..., D:].double()
 q, k, v = (t.double().view(B, T, H, Dh).transpose(1, 2) for t in qkv.split(D, -1))

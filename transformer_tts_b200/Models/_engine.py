@@ -385,7 +385,7 @@ def run_encoder_precise(enc, src: torch.Tensor, mask_u8: torch.Tensor, kv_len: t
         last = i == enc.N - 1
         k = lc["k"]
         next_ln = t["norm"] if last else caches[i + 1]["ln1"]
-        qkv = lib.gemm_x3(xs, xc["wqkv"], lc["bqkv"], xc["sqkv"])                       # modules.py:49-51
+        qkv = lib.gemm_x3(xs, xc["wqkv"], lc["bqkv"], xc["sqkv"], split_out=True)       # modules.py:49-51
         ctx = lib.attention_x3(qkv, mask_u8, kv_len, H)                                  # modules.py:7-21,58-65
         o = lib.gemm_x3(ctx, xc["wo"], lc["bo"], xc["so"])                               # modules.py:68
         y, yns = f32(B, T, D), f16(B, T, 2 * D)

@@ -70,6 +70,12 @@ class FastSpeech2(nn.Module):
         self.postnet = PostConvNet(hp=hp, num_hidden=d_model_decoder, mel_dim=trg_vocab, reduction_rate=reduction_rate,
                                    dropout=dropout_postnet)
         self.debug = debug
+        # Free-running inference decides the durations by ROUNDING log_d (varianceadaptor.py:75).  "fp32": the encoder
+        # and the duration predictor run the fp32-accurate tensor-core chain (csrc/precise.cu) so the durations, frame
+        # indices and mel lengths equal the fp32 reference's; "bf16": the plain bf16 chain (faster, ~5 % of the
+        # durations land on the other side of a .5 boundary).  Teacher-forced calls always take the bf16
+        # chain: there log_d is only an output.
+        self.duration_precision = "fp32"
         self.return_attn = False   # materialise the (B,N,H,T,T) maps of slots 7/8 (parity tests only)
         self.last_aux = None       # integer by-products of the last forward (durations, frame indices, ...)
 
@@ -94,9 +100,17 @@ class FastSpeech2(nn.Module):
         dev = src.device
         sm = E.mask_to_u8(src_mask, B, L, dev)
         kv_src = lib.mask_lengths(sm)
-        e_bf, _, attn_enc = self.encoder.run(src, sm, kv_src, want_f32=False, return_attn=self.return_attn)  # :137
+        if self.duration_precision not in ("fp32", "bf16"):
+            raise ValueError(f"duration_precision must be 'fp32' or 'bf16', got {self.duration_precision!r}")
+        log_d = None
+        if d_target is None and self.duration_precision == "fp32" and not self.return_attn and self.encoder.N > 0:
+            e_bf, e_split, _ = E.run_encoder_precise(self.encoder, src, sm, kv_src)  # :137, to fp32 accuracy
+            log_d = E.run_predictor_precise(self.variance_adaptor.duration_predictor, e_split, sm)  # varianceadaptor.py:69
+            attn_enc = None
+        else:
+            e_bf, _, attn_enc = self.encoder.run(src, sm, kv_src, want_f32=False, return_attn=self.return_attn)  # :137
         mm = None if mel_mask is None else E.mask_to_u8(mel_mask, B, mel_mask.shape[-1], dev)
-        va = self.variance_adaptor.run(e_bf, sm, mm, d_target, p_target, e_target, want_aux=True)  # :176-181
+        va = self.variance_adaptor.run(e_bf, sm, mm, d_target, p_target, e_target, want_aux=True, log_d=log_d)  # :176-181
         mel_u8 = va["mel_mask"]
         kv_mel = lib.mask_lengths(mel_u8)
         tile_map = None

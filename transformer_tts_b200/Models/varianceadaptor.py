@@ -145,10 +145,12 @@ class VarianceAdaptor(nn.Module):
         return c.t
 
     def run(self, x_bf16, src_mask_u8, mel_mask_u8=None, duration_target=None, pitch_target=None,
-            energy_target=None, max_len=None, want_aux=True):
-        """Kernel sequence of varianceadaptor.py:66-129 on bf16 activations.  Returns a dict."""
+            energy_target=None, max_len=None, want_aux=True, log_d=None):
+        """Kernel sequence of varianceadaptor.py:66-129 on bf16 activations.  Returns a dict.
+        log_d: the duration predictor's output when the caller already evaluated it (fp32-accurate chain)."""
         dev = x_bf16.device
-        log_d = self.duration_predictor.run(x_bf16, src_mask_u8)  # :69
+        if log_d is None:
+            log_d = self.duration_predictor.run(x_bf16, src_mask_u8)  # :69
         if duration_target is not None:
             dur = torch.clamp(duration_target, min=0).to(torch.int32).contiguous()
             if mel_mask_u8 is not None:

@@ -39,31 +39,64 @@ __device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t&
 }
 
 // ------------------------------------------------------------------------------------------------
-// gemm_x3
+// gemm_x3: CTA pairs (cta_group::2).  One unit = 256 rows (two 128-row tiles, one per CTA of the cluster) x BN
+// output channels; each CTA stages its own rows of A (hi, lo) and HALF of the BN weight rows (hi, lo).
+//
+// The kernel is bound by L2 -> SM operand traffic, not by the tensor pipe: with every operand present twice (hi and
+// lo planes) a k-block moves 32 KB + BN*128 B into each SM for 12 MMAs, and with the MMAs AND the TMEM read-back
+// deleted the k=5 convolutions ran no faster (ttsb200_debug_x3, tools/exp/precise_times.py: 132 of 140 us).  So a
+// conv's taps share ONE activation box: A is loaded once per 64-channel block as 128 + 8 rows (time steps
+// t0 - pad_left ...), and tap j reads rows [j, j + 128) of it through a descriptor whose start address is offset by
+// j rows.  (The SWIZZLE_128B XOR is a function of the shared-memory ADDRESS bits, so a start address inside a
+// 1024-byte atom reads the rows TMA wrote there; the descriptor's "matrix base offset" field stays 0 — setting it
+// to j & 7 gave wrong products.)  Activations then cost 1/taps of the traffic; only the weights stream per tap,
+// through their own ring.  Cross-CTA "buffer drained" arrivals are RELAXED: see mbar_arrive_leader_relaxed.
 // ------------------------------------------------------------------------------------------------
-constexpr int kXM = 128;            // rows per tile (time steps of one utterance)
-constexpr int kXN = 128;            // output channels per tile
+constexpr int kXM = 128;            // rows per CTA (time steps of one utterance)
 constexpr int kXK = 64;             // k-block: 64 fp16 = one 128-byte swizzle row
-constexpr int kXStages = 3;
 constexpr int kXBox = 16384;        // 128 rows x 128 bytes
-constexpr int kXStageBytes = 4 * kXBox;  // A hi | A lo | W hi | W lo
-constexpr int kXNumAcc = 4;         // TMEM accumulator buffers (128 columns each)
 constexpr int kXThreads = 64 + 256; // warp 0 TMA producer, warp 1 MMA issuer, warps 2..9 accumulate / epilogue
 constexpr int kXStoreBytes = 2 * kXBox;  // one staging box per epilogue warpgroup
-constexpr int kXSmem = kXStages * kXStageBytes + kXStoreBytes + 1024;
+constexpr int kXAStages = 2;
+
+template <int BN, int HALO>
+struct X3Cfg {
+  static constexpr int kABox = (kXM + HALO) * 128;           // one plane of this CTA's activation rows (+ conv halo)
+  static constexpr int kAStage = 2 * kABox;                  // hi | lo
+  static constexpr int kWBox = (BN / 2) * 128;               // this CTA's half of the weight rows, one plane
+  static constexpr int kWStage = 2 * kWBox;                  // hi | lo
+  static constexpr int kWFit = (232448 - 1024 - kXStoreBytes - kXAStages * kAStage) / kWStage;
+  static constexpr int kWStages = kWFit > 6 ? 6 : kWFit;
+  static constexpr int kNumAcc = 512 / BN;                   // TMEM accumulator buffers (BN columns each)
+  static constexpr int kHalf = BN / 2;                       // columns per epilogue warpgroup
+  static constexpr int kSmem = kXAStages * kAStage + kWStages * kWStage + kXStoreBytes + 1024;
+  static_assert(BN == 128 || BN == 192, "tile widths built");
+  static_assert(kWBox % 1024 == 0 && kABox % 1024 == 0, "swizzle atoms");
+  static_assert(kWStages >= 3, "weight ring too shallow");
+  static_assert(kSmem <= 232448, "shared memory budget");
+};
 
 struct X3Dev {
   int B, T, N, C, taps, pad_left, relu, out_split;
   int m_tiles, n_tiles;
   float inv_scale;
   const float* bias;
+  int debug;  // timing experiments only (ttsb200_debug_x3): 1 = no TMEM read-back, 2 = no MMAs
 };
+
+__device__ long long g_x3_trace[148 * 16];
+
+// "this warp has read its part of the accumulator buffer" -> the leader CTA's barrier.  RELAXED: the values are in
+// registers (tcgen05.wait::ld), nothing this thread wrote has to become visible to the issuer, and the default
+// release.cluster form of a remote arrive cost ~1500 clk per k-block (tools/exp/precise_trace.py).
+__device__ __forceinline__ void mbar_arrive_leader_relaxed(uint32_t bar) {
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar & kPeerBitMask) : "memory");
+}
 
 // kind::f16 instruction descriptor with fp16 (not bf16) operands: D fp32 (1<<4), A/B format 0
 __host__ __device__ constexpr uint32_t umma_idesc_f16(uint32_t M, uint32_t N) {
   return (1u << 4) | ((N >> 3) << 17) | ((M >> 4) << 24);
 }
-
 __device__ __forceinline__ void x_tma_store_3d(const CUtensorMap* m, uint32_t src, int c0, int c1, int c2) {
   asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
                ::"l"(reinterpret_cast<uint64_t>(m)), "r"(src), "r"(c0), "r"(c1), "r"(c2)
@@ -74,122 +107,173 @@ __device__ __forceinline__ void x_store_wait_read0() { asm volatile("cp.async.bu
 __device__ __forceinline__ void x_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void x_wg_bar(int wg) { asm volatile("bar.sync %0, 128;" ::"r"(2 + wg) : "memory"); }
 
+template <int BN, int HALO>
 __global__ void __launch_bounds__(kXThreads, 1)
 gemm_x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                const __grid_constant__ CUtensorMap tmOut, const X3Dev p) {
+  using Cfg = X3Cfg<BN, HALO>;
+  constexpr int SA = kXAStages, SW = Cfg::kWStages, NA = Cfg::kNumAcc, HALF = Cfg::kHalf;
   extern __shared__ __align__(1024) uint8_t smem[];
   if ((smem_u32(smem) & 1023u) != 0) {
     if (threadIdx.x == 0) printf("ttsb200: gemm_x3 dynamic shared memory base is not 1024-byte aligned\n");
     __trap();
   }
-  uint8_t* sStages = smem;
-  uint8_t* sStore = smem + kXStages * kXStageBytes;
+  uint8_t* sA = smem;
+  uint8_t* sW = sA + SA * Cfg::kAStage;
+  uint8_t* sStore = sW + SW * Cfg::kWStage;
   uint64_t* bars = reinterpret_cast<uint64_t*>(sStore + kXStoreBytes);
-  uint64_t* bar_full = bars;                            // [S]
-  uint64_t* bar_empty = bars + kXStages;                // [S]
-  uint64_t* bar_accf = bars + 2 * kXStages;             // [4] k-block partial sum complete in TMEM
-  uint64_t* bar_acce = bars + 2 * kXStages + kXNumAcc;  // [4] ... and read back by all 256 epilogue threads
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kXStages + 2 * kXNumAcc);
+  uint64_t* bar_afull = bars;                      // [SA] (the leader's full barriers are used: both CTAs' loads signal them)
+  uint64_t* bar_aempty = bars + SA;                // [SA] multicast commit
+  uint64_t* bar_wfull = bars + 2 * SA;             // [SW]
+  uint64_t* bar_wempty = bars + 2 * SA + SW;       // [SW] multicast commit
+  uint64_t* bar_accf = bars + 2 * SA + 2 * SW;     // [NA] one (k-block, tap) partial sum complete in TMEM (multicast commit)
+  uint64_t* bar_acce = bar_accf + NA;              // [NA] ... and read back: one arrival per epilogue warp of both CTAs, on the leader's
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_acce + NA);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const uint32_t cta_rank = cluster_ctarank();
+  const bool is_leader = cta_rank == 0;
   const int kblocks = p.C / kXK;
-  const int num_iters = p.taps * kblocks;
-  const int num_tiles = p.B * p.m_tiles * p.n_tiles;
+  const int taps = p.taps;
+  const int total_mt = p.B * p.m_tiles;
+  const int num_units = ((total_mt + 1) / 2) * p.n_tiles;
+  const int unit0 = static_cast<int>(blockIdx.x >> 1);
+  const int ustride = static_cast<int>(gridDim.x >> 1);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmW);
     tma_prefetch_desc(&tmOut);
-    for (int s = 0; s < kXStages; ++s) {
-      mbar_init(smem_u32(&bar_full[s]), 1);
-      mbar_init(smem_u32(&bar_empty[s]), 1);
+    for (int s = 0; s < SA; ++s) {
+      mbar_init(smem_u32(&bar_afull[s]), 1);
+      mbar_init(smem_u32(&bar_aempty[s]), 1);
     }
-    for (int i = 0; i < kXNumAcc; ++i) {
+    for (int s = 0; s < SW; ++s) {
+      mbar_init(smem_u32(&bar_wfull[s]), 1);
+      mbar_init(smem_u32(&bar_wempty[s]), 1);
+    }
+    for (int i = 0; i < NA; ++i) {
       mbar_init(smem_u32(&bar_accf[i]), 1);
-      mbar_init(smem_u32(&bar_acce[i]), 256);
+      mbar_init(smem_u32(&bar_acce[i]), 16);
     }
     fence_mbar_init();
   }
   if (warp == 1) {
-    tmem_alloc(smem_u32(tmem_slot), 512);
-    tmem_relinquish();
+    tmem_alloc_2sm(smem_u32(tmem_slot), 512);
+    tmem_relinquish_2sm();
   }
   tc_fence_before();
-  __syncthreads();
+  cluster_sync_all();  // the peer's barriers are initialised before anything arrives on them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  auto decode = [&](int tile, int& b, int& t0, int& nt) {
-    const int mt = tile / p.n_tiles;
-    nt = tile - mt * p.n_tiles;
+  // unit -> this CTA's (utterance, first row, n-tile); n fastest so concurrently running pairs share activations in L2
+  auto decode = [&](int unit, int& b, int& t0, int& nt) {
+    const int mtp = unit / p.n_tiles;
+    nt = unit - mtp * p.n_tiles;
+    const int mt = 2 * mtp + static_cast<int>(cta_rank);
+    if (mt >= total_mt) {  // odd tile count: the last pair's second tile is empty (loads zero-fill, stores clip)
+      b = 0;
+      t0 = (p.m_tiles + 1) * kXM;
+      return;
+    }
     b = mt / p.m_tiles;
     t0 = (mt - b * p.m_tiles) * kXM;
   };
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
+    // ===================== TMA producer (both CTAs) =====================
     if (lane == 0) {
-      uint32_t git = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      uint32_t ga = 0, gw = 0;
+      for (int unit = unit0; unit < num_units; unit += ustride) {
         int b, t0, nt;
-        decode(tile, b, t0, nt);
-        for (int it = 0; it < num_iters; ++it, ++git) {
-          const int s = git % kXStages;
-          mbar_wait(smem_u32(&bar_empty[s]), ((git / kXStages) & 1) ^ 1);
-          const uint32_t full = smem_u32(&bar_full[s]);
-          mbar_arrive_expect_tx(full, kXStageBytes);
-          const int tap = it / kblocks;
-          const int c0 = (it - tap * kblocks) * kXK;
-          const uint32_t st = smem_u32(sStages + s * kXStageBytes);
-          const int t = t0 + tap - p.pad_left;  // conv tap = time-shifted box; out-of-range rows are zero-filled
-          tma_load_3d(st, &tmA, full, c0, t, b);
-          tma_load_3d(st + kXBox, &tmA, full, p.C + c0, t, b);
-          tma_load_2d(st + 2 * kXBox, &tmW, full, c0, tap * p.N + nt * kXN);
-          tma_load_2d(st + 3 * kXBox, &tmW, full, p.C + c0, tap * p.N + nt * kXN);
+        decode(unit, b, t0, nt);
+        for (int kb = 0; kb < kblocks; ++kb, ++ga) {
+          const int sa = ga % SA;
+          mbar_wait(smem_u32(&bar_aempty[sa]), ((ga / SA) & 1) ^ 1);
+          const uint32_t afull = smem_u32(&bar_afull[sa]);
+          if (is_leader) mbar_arrive_expect_tx(afull, 2 * Cfg::kAStage);
+          const uint32_t ast = smem_u32(sA + sa * Cfg::kAStage);
+          // rows t0 - pad_left .. + 128 + HALO: every tap's time-shifted window; out-of-range rows are zero-filled
+          tma_load_3d_2sm(ast, &tmA, afull, kb * kXK, t0 - p.pad_left, b);
+          tma_load_3d_2sm(ast + Cfg::kABox, &tmA, afull, p.C + kb * kXK, t0 - p.pad_left, b);
+          for (int tap = 0; tap < taps; ++tap, ++gw) {
+            const int sw = gw % SW;
+            mbar_wait(smem_u32(&bar_wempty[sw]), ((gw / SW) & 1) ^ 1);
+            const uint32_t wfull = smem_u32(&bar_wfull[sw]);
+            if (is_leader) mbar_arrive_expect_tx(wfull, 2 * Cfg::kWStage);
+            const uint32_t wst = smem_u32(sW + sw * Cfg::kWStage);
+            const int wrow = tap * p.N + nt * BN + static_cast<int>(cta_rank) * (BN / 2);
+            tma_load_2d_2sm(wst, &tmW, wfull, kb * kXK, wrow);
+            tma_load_2d_2sm(wst + Cfg::kWBox, &tmW, wfull, p.C + kb * kXK, wrow);
+          }
         }
       }
     }
-  } else if (warp == 1) {
-    // ===================== MMA issuer (converged warp, one elected lane issues) =====================
-    constexpr uint32_t idesc = umma_idesc_f16(kXM, kXN);
+  } else if (warp == 1 && is_leader) {
+    // ===================== MMA issuer (leader CTA; converged warp, one elected lane issues) =====================
+    constexpr uint32_t idesc = umma_idesc_f16(2 * kXM, BN);
     const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
     const uint32_t leader = elect_one();
-    uint32_t git = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      for (int it = 0; it < num_iters; ++it, ++git) {
-        const int s = git % kXStages;
-        const uint32_t ab = git % kXNumAcc;
-        mbar_wait(smem_u32(&bar_acce[ab]), ((git / kXNumAcc) & 1) ^ 1);  // buffer read back by the epilogue warps
-        mbar_wait(smem_u32(&bar_full[s]), (git / kXStages) & 1);
-        tc_fence_after();
-        const uint32_t st = smem_u32(sStages + s * kXStageBytes);
-        const uint32_t d_tmem = tb + ab * kXN;
-        if (leader) {
-          // the two small cross terms first, the large hi*hi term last: the accumulator truncates once per MMA
-          // step relative to its current magnitude, so only the last four steps cost 2^-24 each
+    uint32_t ga = 0, gw = 0;
+    const bool tr = (p.debug & 8) != 0;
+    long long t_a = 0, t_e = 0, t_w = 0, t_i = 0, t0c = 0, t_start = tr ? clock64() : 0;
+    for (int unit = unit0; unit < num_units; unit += ustride) {
+      for (int kb = 0; kb < kblocks; ++kb, ++ga) {
+        const int sa = ga % SA;
+        if (tr) t0c = clock64();
+        mbar_wait(smem_u32(&bar_afull[sa]), (ga / SA) & 1);
+        if (tr) t_a += clock64() - t0c;
+        const uint32_t ast = smem_u32(sA + sa * Cfg::kAStage);
+        for (int tap = 0; tap < taps; ++tap, ++gw) {
+          const int sw = gw % SW;
+          const uint32_t ab = gw % NA;
+          if (tr) t0c = clock64();
+          mbar_wait(smem_u32(&bar_acce[ab]), ((gw / NA) & 1) ^ 1);  // buffer read back by the epilogue warps of both CTAs
+          if (tr) { const long long t1 = clock64(); t_e += t1 - t0c; t0c = t1; }
+          mbar_wait(smem_u32(&bar_wfull[sw]), (gw / SW) & 1);
+          if (tr) { const long long t1 = clock64(); t_w += t1 - t0c; t0c = t1; }
+          tc_fence_after();
+          const uint32_t wst = smem_u32(sW + sw * Cfg::kWStage);
+          const uint32_t d_tmem = tb + ab * BN;
+          const uint32_t arow = ast + tap * 128;  // tap j = rows [j, j + 128) of the staged window
+          if (leader && (p.debug & 2)) {
+            umma_commit_2sm(smem_u32(&bar_wempty[sw]));
+            if (tap == taps - 1) umma_commit_2sm(smem_u32(&bar_aempty[sa]));
+            umma_commit_2sm(smem_u32(&bar_accf[ab]));
+          } else if (leader) {
+            // the two small cross terms first, the large hi*hi term last: the accumulator truncates once per MMA
+            // step relative to its current magnitude, so only the last four steps cost 2^-24 each
 #pragma unroll
-          for (int k = 0; k < kXK / 16; ++k) {
-            const uint64_t a_hi = umma_smem_desc(st + k * 32, 16, 1024, kLayoutSW128);
-            const uint64_t a_lo = umma_smem_desc(st + kXBox + k * 32, 16, 1024, kLayoutSW128);
-            const uint64_t w_hi = umma_smem_desc(st + 2 * kXBox + k * 32, 16, 1024, kLayoutSW128);
-            const uint64_t w_lo = umma_smem_desc(st + 3 * kXBox + k * 32, 16, 1024, kLayoutSW128);
-            umma_bf16(d_tmem, a_lo, w_hi, idesc, k != 0 ? 1u : 0u);
-            umma_bf16(d_tmem, a_hi, w_lo, idesc, 1u);
-          }
+            for (int k = 0; k < kXK / 16; ++k) {
+              const uint64_t a_hi = umma_smem_desc(arow + k * 32, 16, 1024, kLayoutSW128);
+              const uint64_t a_lo = umma_smem_desc(arow + Cfg::kABox + k * 32, 16, 1024, kLayoutSW128);
+              const uint64_t w_hi = umma_smem_desc(wst + k * 32, 16, 1024, kLayoutSW128);
+              const uint64_t w_lo = umma_smem_desc(wst + Cfg::kWBox + k * 32, 16, 1024, kLayoutSW128);
+              umma_bf16_2sm(d_tmem, a_lo, w_hi, idesc, k != 0 ? 1u : 0u);
+              umma_bf16_2sm(d_tmem, a_hi, w_lo, idesc, 1u);
+            }
 #pragma unroll
-          for (int k = 0; k < kXK / 16; ++k) {
-            const uint64_t a_hi = umma_smem_desc(st + k * 32, 16, 1024, kLayoutSW128);
-            const uint64_t w_hi = umma_smem_desc(st + 2 * kXBox + k * 32, 16, 1024, kLayoutSW128);
-            umma_bf16(d_tmem, a_hi, w_hi, idesc, 1u);
+            for (int k = 0; k < kXK / 16; ++k) {
+              const uint64_t a_hi = umma_smem_desc(arow + k * 32, 16, 1024, kLayoutSW128);
+              const uint64_t w_hi = umma_smem_desc(wst + k * 32, 16, 1024, kLayoutSW128);
+              umma_bf16_2sm(d_tmem, a_hi, w_hi, idesc, 1u);
+            }
+            umma_commit_2sm(smem_u32(&bar_wempty[sw]));
+            if (tap == taps - 1) umma_commit_2sm(smem_u32(&bar_aempty[sa]));
+            umma_commit_2sm(smem_u32(&bar_accf[ab]));
           }
-          umma_commit(smem_u32(&bar_empty[s]));
-          umma_commit(smem_u32(&bar_accf[ab]));
+          __syncwarp();
+          if (tr) t_i += clock64() - t0c;
         }
-        __syncwarp();
       }
     }
-  } else {
+    if (tr && lane == 0 && blockIdx.x < 296) {
+      long long* o = g_x3_trace + (blockIdx.x >> 1) * 16;
+      o[0] = clock64() - t_start; o[1] = t_a; o[2] = t_e; o[3] = t_w; o[4] = t_i; o[5] = gw;
+    }
+  } else if (warp >= 2) {
     // ===================== accumulate + epilogue warps: thread == output row == TMEM lane =====================
     const int e = warp - 2;
     const int wg = e >> 2;          // column half of the tile
@@ -197,37 +281,52 @@ gemm_x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int row = q * 32 + lane;
     const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
     uint8_t* my_box = sStore + wg * kXBox;
+    const int num_iters = kblocks * taps;
     uint32_t git = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int unit = unit0; unit < num_units; unit += ustride) {
       int b, t0, nt;
-      decode(tile, b, t0, nt);
-      float acc[64];
+      decode(unit, b, t0, nt);
+      float acc[HALF];
 #pragma unroll
-      for (int i = 0; i < 64; ++i) acc[i] = 0.f;
+      for (int i = 0; i < HALF; ++i) acc[i] = 0.f;
       for (int it = 0; it < num_iters; ++it, ++git) {
-        const uint32_t ab = git % kXNumAcc;
-        mbar_wait(smem_u32(&bar_accf[ab]), (git / kXNumAcc) & 1);
+        const uint32_t ab = git % NA;
+        const long long te0 = (p.debug & 8) ? clock64() : 0;
+        mbar_wait(smem_u32(&bar_accf[ab]), (git / NA) & 1);
+        if ((p.debug & 8) && e == 0 && lane == 0 && is_leader) g_x3_trace[(blockIdx.x >> 1) * 16 + 8] += clock64() - te0;
         tc_fence_after();
-        float v[64];
-        const uint32_t ta = tmem_base + ab * kXN + wg * 64 + lane_off;
-        tmem_ld32(ta, v);
-        tmem_ld32(ta + 32, v + 32);
-        tmem_ld_wait();
-        tc_fence_before();
-        mbar_arrive(smem_u32(&bar_acce[ab]));  // the values are in registers: the buffer is free again
+        const uint32_t ta = tmem_base + ab * BN + wg * HALF + lane_off;
+        constexpr int CW = 32;
 #pragma unroll
-        for (int i = 0; i < 64; i += 2) add2(acc[i], acc[i + 1], v[i], v[i + 1]);  // fp32 round-to-nearest
+        for (int c = 0; c < HALF; c += CW) {
+          float v[CW];
+          if (!(p.debug & 1)) {
+            if constexpr (CW == 32) tmem_ld32(ta + c, v);
+            else tmem_ld16(ta + c, v);
+            tmem_ld_wait();
+          } else {
+#pragma unroll
+            for (int i = 0; i < CW; ++i) v[i] = 1.f;
+          }
+          if (c + CW >= HALF) {  // the last chunk is in registers: the buffer is free again
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_leader_relaxed(smem_u32(&bar_acce[ab]));
+          }
+#pragma unroll
+          for (int i = 0; i < CW; i += 2) add2(acc[c + i], acc[c + i + 1], v[i], v[i + 1]);  // fp32 round-to-nearest
+        }
       }
       // ---- tile epilogue: v = acc * 2^-e + bias (+ ReLU) -> fp32 boxes or fp16 hi | lo boxes -> TMA store ----
-      const int n0 = nt * kXN + wg * 64;
+      const int n0 = nt * BN + wg * HALF;
 #pragma unroll
-      for (int i = 0; i < 64; ++i) {
+      for (int i = 0; i < HALF; ++i) {
         acc[i] = fmaf(acc[i], p.inv_scale, __ldg(p.bias + n0 + i));
         if (p.relu) acc[i] = fmaxf(acc[i], 0.f);
       }
       if (!p.out_split) {
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
+        for (int h = 0; h < HALF / 32; ++h) {
           if (row == 0) x_store_wait_read0();  // the previous store from this box has read it
           x_wg_bar(wg);
           uint8_t* rp = my_box + row * 128;
@@ -243,24 +342,30 @@ gemm_x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
         }
       } else {
-        uint32_t hi[32], lo[32];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) split2(acc[2 * i], acc[2 * i + 1], hi[i], lo[i]);
+        for (int h = 0; h < HALF / 32; ++h) {
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const uint32_t* src = h == 0 ? hi : lo;
-          if (row == 0) x_store_wait_read0();
-          x_wg_bar(wg);
-          uint8_t* rp = my_box + row * 128;
+          for (int pl = 0; pl < 2; ++pl) {  // hi plane, then lo plane (the split is recomputed: registers are scarce)
+            if (row == 0) x_store_wait_read0();
+            x_wg_bar(wg);
+            uint8_t* rp = my_box + row * 64;  // 128 rows x 32 fp16, SWIZZLE_64B: chunk j of row r at (j ^ ((r >> 1) & 3))
 #pragma unroll
-          for (int j = 0; j < 8; ++j)
-            *reinterpret_cast<uint4*>(rp + ((j ^ (row & 7)) << 4)) =
-                make_uint4(src[4 * j], src[4 * j + 1], src[4 * j + 2], src[4 * j + 3]);
-          fence_async_smem();
-          x_wg_bar(wg);
-          if (row == 0) {
-            x_tma_store_3d(&tmOut, smem_u32(my_box), h * p.N + n0, t0, b);
-            x_store_commit();
+            for (int j = 0; j < 4; ++j) {
+              uint32_t w[4], o[4];
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const int c = h * 32 + 8 * j + 2 * i;
+                if (pl == 0) split2(acc[c], acc[c + 1], w[i], o[i]);
+                else split2(acc[c], acc[c + 1], o[i], w[i]);
+              }
+              *reinterpret_cast<uint4*>(rp + ((j ^ ((row >> 1) & 3)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+            fence_async_smem();
+            x_wg_bar(wg);
+            if (row == 0) {
+              x_tma_store_3d(&tmOut, smem_u32(my_box), pl * p.N + n0 + h * 32, t0, b);
+              x_store_commit();
+            }
           }
         }
       }
@@ -269,15 +374,16 @@ gemm_x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 
   tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, 512);
+  cluster_sync_all();  // every multicast commit has been consumed by a wait in both CTAs before either one leaves
+  if (warp == 1) tmem_dealloc_2sm(tmem_base, 512);
 }
 
 // ------------------------------------------------------------------------------------------------
 // attention_x3: softmax(mask(q k^T / sqrt(dk), -1e4)) v on mma.sync with split operands and short chains.
-//   qkv fp32 (B,T,3*H*96) -> ctx fp16 hi | lo (B,T,2*H*96)
-// One CTA = 64 queries of one (utterance, head), 4 warps x 16 rows; 64-key tiles of K and V are split into fp16
-// hi / lo planes in shared memory ([key][dim], 208-byte rows: conflict-free for the fragment loads and ldmatrix).
+//   qkv fp16 hi | lo (B,T,2*3*H*96) (the q|k|v GEMM's split output) -> ctx fp16 hi | lo (B,T,2*H*96)
+// One CTA = 64 queries of one (utterance, head), 4 warps x 16 rows; the hi / lo planes of a 64-key tile of K and V
+// are copied to shared memory with cp.async ([key][dim], 208-byte rows: conflict-free for the fragment loads and
+// ldmatrix).
 // ------------------------------------------------------------------------------------------------
 constexpr int kADh = 96;
 constexpr int kABQ = 64;
@@ -285,7 +391,6 @@ constexpr int kABK = 64;
 constexpr int kAPitch = 104;  // halfs per smem row (208 bytes)
 constexpr int kAPlane = kABK * kAPitch * 2;                   // bytes of one plane
 constexpr int kASmem = 4 * kAPlane + 64;                      // K hi, K lo, V hi, V lo, key flags
-constexpr float kAInScale = 16.f;     // q, k, v are scaled by 2^4 before the split (their lo parts stay normal)
 constexpr float kAPScale = 1024.f;    // p <= 1 is scaled by 2^10 before the split
 
 __device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
@@ -297,8 +402,13 @@ __device__ __forceinline__ void ldmatrix_x2_trans(uint32_t& r0, uint32_t& r1, ui
   asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0, %1}, [%2];" : "=r"(r0), "=r"(r1) : "r"(addr));
 }
 
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, bool valid) {
+  const int n = valid ? 16 : 0;  // src-size 0: the 16 bytes are zero-filled
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(n) : "memory");
+}
+
 __global__ void __launch_bounds__(128)
-attention_x3_kernel(const float* __restrict__ qkv, const uint8_t* __restrict__ mask, const int32_t* __restrict__ kv_info,
+attention_x3_kernel(const __half* __restrict__ qkv, const uint8_t* __restrict__ mask, const int32_t* __restrict__ kv_info,
                     __half* __restrict__ ctx, int T, int H) {
   extern __shared__ __align__(16) uint8_t asmem[];
   __half* sKh = reinterpret_cast<__half*>(asmem);
@@ -311,31 +421,32 @@ attention_x3_kernel(const float* __restrict__ qkv, const uint8_t* __restrict__ m
   const int g = lane >> 2, t4 = lane & 3;
   const int q0 = blockIdx.x * kABQ, h = blockIdx.y, b = blockIdx.z;
   const int D = H * kADh;
-  const int64_t ld = 3LL * D;
-  const float* base = qkv + static_cast<int64_t>(b) * T * ld;
+  const int64_t ld = 6LL * D;                 // [q k v hi | q k v lo]
+  const int64_t lo_off = 3LL * D;
+  const __half* base = qkv + static_cast<int64_t>(b) * T * ld;
   const int klen = kv_info[2 * b];
   const int kv_eff = klen > 0 ? klen : T;  // no valid key: uniform over all T keys like the reference
   const int nkv = (kv_eff + kABK - 1) / kABK;
 
-  // ---- Q fragments (rows g and g + 8 of this warp's 16), split ----
+  // ---- Q fragments (rows g and g + 8 of this warp's 16): hi and lo planes as they are ----
   uint32_t qh[6][4], ql[6][4];
   {
     const int r0 = q0 + warp * 16 + g, r1 = r0 + 8;
-    const float* p0 = base + static_cast<int64_t>(r0 < T ? r0 : 0) * ld + h * kADh;
-    const float* p1 = base + static_cast<int64_t>(r1 < T ? r1 : 0) * ld + h * kADh;
+    const __half* p0 = base + static_cast<int64_t>(r0 < T ? r0 : 0) * ld + h * kADh + 2 * t4;
+    const __half* p1 = base + static_cast<int64_t>(r1 < T ? r1 : 0) * ld + h * kADh + 2 * t4;
 #pragma unroll
     for (int j = 0; j < 6; ++j) {
-      const float2 a = *reinterpret_cast<const float2*>(p0 + 16 * j + 2 * t4);
-      const float2 c = *reinterpret_cast<const float2*>(p1 + 16 * j + 2 * t4);
-      const float2 d = *reinterpret_cast<const float2*>(p0 + 16 * j + 8 + 2 * t4);
-      const float2 f = *reinterpret_cast<const float2*>(p1 + 16 * j + 8 + 2 * t4);
-      split2(a.x * kAInScale, a.y * kAInScale, qh[j][0], ql[j][0]);
-      split2(c.x * kAInScale, c.y * kAInScale, qh[j][1], ql[j][1]);
-      split2(d.x * kAInScale, d.y * kAInScale, qh[j][2], ql[j][2]);
-      split2(f.x * kAInScale, f.y * kAInScale, qh[j][3], ql[j][3]);
+      qh[j][0] = *reinterpret_cast<const uint32_t*>(p0 + 16 * j);
+      qh[j][1] = *reinterpret_cast<const uint32_t*>(p1 + 16 * j);
+      qh[j][2] = *reinterpret_cast<const uint32_t*>(p0 + 16 * j + 8);
+      qh[j][3] = *reinterpret_cast<const uint32_t*>(p1 + 16 * j + 8);
+      ql[j][0] = *reinterpret_cast<const uint32_t*>(p0 + lo_off + 16 * j);
+      ql[j][1] = *reinterpret_cast<const uint32_t*>(p1 + lo_off + 16 * j);
+      ql[j][2] = *reinterpret_cast<const uint32_t*>(p0 + lo_off + 16 * j + 8);
+      ql[j][3] = *reinterpret_cast<const uint32_t*>(p1 + lo_off + 16 * j + 8);
     }
   }
-  const float s_scale = 1.f / (sqrtf(static_cast<float>(kADh)) * kAInScale * kAInScale);
+  const float s_scale = 1.f / sqrtf(static_cast<float>(kADh));
   float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
   float o[12][4];
 #pragma unroll
@@ -343,30 +454,23 @@ attention_x3_kernel(const float* __restrict__ qkv, const uint8_t* __restrict__ m
 
   for (int jt = 0; jt < nkv; ++jt) {
     __syncthreads();  // the previous tile's fragments have been read
-    // ---- K, V tile -> hi / lo planes ----
-    for (int i = threadIdx.x; i < kABK * 24; i += 128) {
-      const int key = i / 24, c4 = i - key * 24;
+    // ---- K, V tile: four planes of 64 keys x 96 dims, 12 x 16 bytes per row ----
+    for (int i = threadIdx.x; i < kABK * 12; i += 128) {
+      const int key = i / 12, c8 = i - key * 12;
       const int kg = jt * kABK + key;
-      float4 kk = make_float4(0.f, 0.f, 0.f, 0.f), vv = kk;
-      if (kg < T) {
-        const float* rp = base + static_cast<int64_t>(kg) * ld + h * kADh + 4 * c4;
-        kk = *reinterpret_cast<const float4*>(rp + D);
-        vv = *reinterpret_cast<const float4*>(rp + 2 * D);
-      }
-      uint32_t h0, h1, e0, e1;
-      split2(kk.x * kAInScale, kk.y * kAInScale, h0, e0);
-      split2(kk.z * kAInScale, kk.w * kAInScale, h1, e1);
-      *reinterpret_cast<uint2*>(sKh + key * kAPitch + 4 * c4) = make_uint2(h0, h1);
-      *reinterpret_cast<uint2*>(sKl + key * kAPitch + 4 * c4) = make_uint2(e0, e1);
-      split2(vv.x * kAInScale, vv.y * kAInScale, h0, e0);
-      split2(vv.z * kAInScale, vv.w * kAInScale, h1, e1);
-      *reinterpret_cast<uint2*>(sVh + key * kAPitch + 4 * c4) = make_uint2(h0, h1);
-      *reinterpret_cast<uint2*>(sVl + key * kAPitch + 4 * c4) = make_uint2(e0, e1);
+      const bool ok = kg < T;
+      const __half* rp = base + static_cast<int64_t>(ok ? kg : 0) * ld + h * kADh + 8 * c8;
+      const uint32_t so = static_cast<uint32_t>((key * kAPitch + 8 * c8) * 2);
+      cp_async16(smem_u32(sKh) + so, rp + D, ok);
+      cp_async16(smem_u32(sKl) + so, rp + lo_off + D, ok);
+      cp_async16(smem_u32(sVh) + so, rp + 2 * D, ok);
+      cp_async16(smem_u32(sVl) + so, rp + lo_off + 2 * D, ok);
     }
     if (threadIdx.x < kABK) {
       const int kg = jt * kABK + threadIdx.x;
       sflag[threadIdx.x] = kg < T ? (mask[static_cast<int64_t>(b) * T + kg] ? 1 : 0) : 2;
     }
+    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
     __syncthreads();
 
     // ---- S = Q K^T (16 x 64 per warp) ----
@@ -446,7 +550,7 @@ attention_x3_kernel(const float* __restrict__ qkv, const uint8_t* __restrict__ m
   l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
   l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
   l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
-  const float inv0 = 1.f / (l0 * kAPScale * kAInScale), inv1 = 1.f / (l1 * kAPScale * kAInScale);
+  const float inv0 = 1.f / (l0 * kAPScale), inv1 = 1.f / (l1 * kAPScale);
   const int r0 = q0 + warp * 16 + g, r1 = r0 + 8;
 #pragma unroll
   for (int db = 0; db < 12; ++db) {
@@ -612,32 +716,36 @@ __global__ void split_f16_kernel(const float* __restrict__ x, __half* __restrict
 
 using namespace ttsb;
 
+static int g_x3_debug = 0;
+extern "C" void ttsb200_debug_x3(int flags) { g_x3_debug = flags; }
+extern "C" int ttsb200_debug_x3_trace(long long* dst, int n, int clear) {
+  if (clear) {
+    static long long zeros[148 * 16] = {0};
+    return cudaMemcpyToSymbol(g_x3_trace, zeros, sizeof(zeros)) == cudaSuccess ? 0 : -1;
+  }
+  return cudaMemcpyFromSymbol(dst, g_x3_trace, n * sizeof(long long)) == cudaSuccess ? 0 : -1;
+}
+
 static inline bool x_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
-extern "C" int ttsb200_gemm_x3(const void* x_split, const void* w_split, const float* bias, float inv_scale,
-                               int32_t B, int32_t T, int32_t N, int32_t C, int32_t taps, int32_t pad_left,
-                               int32_t relu, float* out_f32, void* out_split, ttsb200_stream_t stream_) {
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  TTSB_CHECK_ARG(x_split && w_split && bias, "gemm_x3: null operand");
-  TTSB_CHECK_ARG(B > 0 && T > 0 && taps > 0, "gemm_x3: bad dims");
-  TTSB_CHECK_ARG(N % kXN == 0 && N > 0, "gemm_x3: N (%d) must be a multiple of %d", N, kXN);
-  TTSB_CHECK_ARG(C % kXK == 0 && C > 0, "gemm_x3: C (%d) must be a multiple of %d", C, kXK);
-  TTSB_CHECK_ARG((out_f32 != nullptr) != (out_split != nullptr), "gemm_x3: exactly one of out_f32 / out_split");
-  TTSB_CHECK_ARG(x_aligned16(x_split) && x_aligned16(w_split) && x_aligned16(out_f32) && x_aligned16(out_split),
-                 "gemm_x3: operands must be 16-byte aligned");
+template <int BN, int HALO>
+static int launch_gemm_x3(const void* x_split, const void* w_split, float* out_f32, void* out_split, X3Dev d,
+                          cudaStream_t stream) {
+  using Cfg = X3Cfg<BN, HALO>;
   CUtensorMap tmA, tmW, tmOut;
-  const uint64_t uT = static_cast<uint64_t>(T), uB = static_cast<uint64_t>(B), uN = static_cast<uint64_t>(N);
+  const uint64_t uT = static_cast<uint64_t>(d.T), uB = static_cast<uint64_t>(d.B), uN = static_cast<uint64_t>(d.N);
+  const uint64_t uC = static_cast<uint64_t>(d.C);
   {
-    const uint64_t dims[3] = {2ull * C, uT, uB};
-    const uint64_t strides[2] = {4ull * C, 4ull * C * uT};
-    const uint32_t box[3] = {kXK, kXM, 1};
+    const uint64_t dims[3] = {2 * uC, uT, uB};
+    const uint64_t strides[2] = {4 * uC, 4 * uC * uT};
+    const uint32_t box[3] = {kXK, kXM + HALO, 1};
     int rc = make_tmap(&tmA, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, x_split, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
   }
   {
-    const uint64_t dims[2] = {2ull * C, static_cast<uint64_t>(taps) * uN};
-    const uint64_t strides[1] = {4ull * C};
-    const uint32_t box[2] = {kXK, kXN};
+    const uint64_t dims[2] = {2 * uC, static_cast<uint64_t>(d.taps) * uN};
+    const uint64_t strides[1] = {4 * uC};
+    const uint32_t box[2] = {kXK, BN / 2};
     int rc = make_tmap(&tmW, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, w_split, 2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
   }
@@ -650,36 +758,87 @@ extern "C" int ttsb200_gemm_x3(const void* x_split, const void* w_split, const f
   } else {
     const uint64_t dims[3] = {2 * uN, uT, uB};
     const uint64_t strides[2] = {uN * 4, uN * 4 * uT};
-    const uint32_t box[3] = {64, kXM, 1};
-    int rc = make_tmap(&tmOut, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, out_split, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+    const uint32_t box[3] = {32, kXM, 1};
+    int rc = make_tmap(&tmOut, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, out_split, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_64B);
     if (rc) return rc;
   }
-  TTSB_SMEM_OPT_IN(gemm_x3_kernel, kXSmem);
-  X3Dev d;
-  d.B = B; d.T = T; d.N = N; d.C = C; d.taps = taps; d.pad_left = pad_left; d.relu = relu; d.out_split = out_split ? 1 : 0;
-  d.m_tiles = (T + kXM - 1) / kXM;
-  d.n_tiles = N / kXN;
-  d.inv_scale = inv_scale;
-  d.bias = bias;
+  auto kern = gemm_x3_kernel<BN, HALO>;
+  TTSB_SMEM_OPT_IN(kern, Cfg::kSmem);
+  d.n_tiles = d.N / BN;
   int dev = 0, sms = 148;
   if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  const int tiles = B * d.m_tiles * d.n_tiles;
-  const int grid = tiles < sms ? tiles : sms;
-  gemm_x3_kernel<<<grid, kXThreads, kXSmem, stream>>>(tmA, tmW, tmOut, d);
-  TTSB_CHECK_CUDA(cudaGetLastError());
+  const int units = ((d.B * d.m_tiles + 1) / 2) * d.n_tiles;
+  const int pairs = units < sms / 2 ? units : sms / 2;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * pairs);
+  cfg.blockDim = dim3(kXThreads);
+  cfg.dynamicSmemBytes = Cfg::kSmem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  TTSB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmW, tmOut, d));
   return TTSB_OK;
 }
 
-extern "C" int ttsb200_attention_x3(const float* qkv_f32, const uint8_t* mask, const int32_t* kv_info, void* ctx_split,
+extern "C" int ttsb200_gemm_x3(const void* x_split, const void* w_split, const float* bias, float inv_scale,
+                               int32_t B, int32_t T, int32_t N, int32_t C, int32_t taps, int32_t pad_left,
+                               int32_t relu, float* out_f32, void* out_split, ttsb200_stream_t stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  TTSB_CHECK_ARG(x_split && w_split && bias, "gemm_x3: null operand");
+  TTSB_CHECK_ARG(B > 0 && T > 0 && taps > 0 && taps <= 8, "gemm_x3: bad dims (taps <= 8)");
+  TTSB_CHECK_ARG(N % 128 == 0 && N > 0, "gemm_x3: N (%d) must be a multiple of 128", N);
+  TTSB_CHECK_ARG(C % kXK == 0 && C > 0, "gemm_x3: C (%d) must be a multiple of %d", C, kXK);
+  TTSB_CHECK_ARG((out_f32 != nullptr) != (out_split != nullptr), "gemm_x3: exactly one of out_f32 / out_split");
+  TTSB_CHECK_ARG(x_aligned16(x_split) && x_aligned16(w_split) && x_aligned16(out_f32) && x_aligned16(out_split),
+                 "gemm_x3: operands must be 16-byte aligned");
+  X3Dev d;
+  d.B = B; d.T = T; d.N = N; d.C = C; d.taps = taps; d.pad_left = pad_left; d.relu = relu; d.out_split = out_split ? 1 : 0;
+  d.m_tiles = (T + kXM - 1) / kXM;
+  d.n_tiles = 0;
+  d.inv_scale = inv_scale;
+  d.bias = bias;
+  d.debug = g_x3_debug;
+  // tile width: the candidate that minimises waves x MMA clocks per unit over the 74 CTA pairs
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const long long mtp = (static_cast<long long>(B) * d.m_tiles + 1) / 2;
+  int best = 0;
+  long long best_cost = 0;
+  const int cands[2] = {192, 128};
+  for (int i = 0; i < 2; ++i) {
+    const int bn = cands[i];
+    if (N % bn) continue;
+    const long long units = mtp * (N / bn);
+    const long long waves = (units + sms / 2 - 1) / (sms / 2);
+    const long long cost = waves * (bn + 24);  // + a per-k-block overhead that does not scale with the width
+    if (!best || cost < best_cost) { best = bn; best_cost = cost; }
+  }
+  if (taps > 1) {  // conv: one activation window of 128 + 8 rows serves every tap
+    if (best == 192) return launch_gemm_x3<192, 8>(x_split, w_split, out_f32, out_split, d, stream);
+    if (best == 128) return launch_gemm_x3<128, 8>(x_split, w_split, out_f32, out_split, d, stream);
+  } else {
+    if (best == 192) return launch_gemm_x3<192, 0>(x_split, w_split, out_f32, out_split, d, stream);
+    if (best == 128) return launch_gemm_x3<128, 0>(x_split, w_split, out_f32, out_split, d, stream);
+  }
+  set_last_error("gemm_x3: no tile width for N=%d (split output: %d)", N, out_split ? 1 : 0);
+  return TTSB_ERR_ARG;
+}
+
+extern "C" int ttsb200_attention_x3(const void* qkv_split, const uint8_t* mask, const int32_t* kv_info, void* ctx_split,
                                     int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t stream) {
-  TTSB_CHECK_ARG(qkv_f32 && mask && kv_info && ctx_split, "attention_x3: null pointer");
+  TTSB_CHECK_ARG(qkv_split && mask && kv_info && ctx_split, "attention_x3: null pointer");
   TTSB_CHECK_ARG(B > 0 && T > 0 && H > 0, "attention_x3: bad dims");
   TTSB_CHECK_ARG(Dh == kADh, "attention_x3: head dim %d unsupported (this build: %d)", Dh, kADh);
-  TTSB_CHECK_ARG(x_aligned16(qkv_f32) && x_aligned16(ctx_split), "attention_x3: qkv/ctx must be 16-byte aligned");
+  TTSB_CHECK_ARG(x_aligned16(qkv_split) && x_aligned16(ctx_split), "attention_x3: qkv/ctx must be 16-byte aligned");
   TTSB_SMEM_OPT_IN(attention_x3_kernel, kASmem);
   dim3 grid((T + kABQ - 1) / kABQ, H, B);
   attention_x3_kernel<<<grid, 128, kASmem, static_cast<cudaStream_t>(stream)>>>(
-      qkv_f32, mask, kv_info, static_cast<__half*>(ctx_split), T, H);
+      static_cast<const __half*>(qkv_split), mask, kv_info, static_cast<__half*>(ctx_split), T, H);
   TTSB_CHECK_CUDA(cudaGetLastError());
   return TTSB_OK;
 }

@@ -546,11 +546,12 @@ def gemm_x3(x_split: torch.Tensor, w_split: torch.Tensor, bias: torch.Tensor, in
     return outs if split_out else out32
 
 
-def attention_x3(qkv32: torch.Tensor, mask: torch.Tensor, kv_len: torch.Tensor, H: int) -> torch.Tensor:
-    B, T, W = qkv32.shape
-    D = W // 3
-    ctx = torch.empty((B, T, 2 * D), device=qkv32.device, dtype=torch.float16)
-    _check(load().ttsb200_attention_x3(_ptr(qkv32, torch.float32, "qkv"), _ptr(mask, torch.uint8, "mask"),
+def attention_x3(qkv_split: torch.Tensor, mask: torch.Tensor, kv_len: torch.Tensor, H: int) -> torch.Tensor:
+    """qkv_split fp16 (B,T,2*3D) = [q k v hi | q k v lo]; returns the split context fp16 (B,T,2D)."""
+    B, T, W = qkv_split.shape
+    D = W // 6
+    ctx = torch.empty((B, T, 2 * D), device=qkv_split.device, dtype=torch.float16)
+    _check(load().ttsb200_attention_x3(_ptr(qkv_split, torch.float16, "qkv_split"), _ptr(mask, torch.uint8, "mask"),
                                        _ptr(kv_len, torch.int32, "kv_len"), _ptr(ctx), B, T, H, D // H, _stream()),
            "attention_x3")
     _count()
