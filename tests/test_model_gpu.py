@@ -7,9 +7,19 @@ Tolerances (BASELINE.json north_star / SURVEY §8c):
     bucket indices from given values: bit-exact;
   * mel_pre / mel_post in bf16 compute vs the fp32 oracle with the discrete decisions teacher-forced
     (oracle mode 3): rel-L2 < 1e-2 over valid frames;
-  * free-running durations: compared and reported; flips are tolerated only where the oracle's
-    exp(log_d)-1 sits within the bf16 noise of a .5 boundary.
+  * free-running durations, frame indices, mel lengths, positions (model.duration_precision == "fp32", the default:
+    the encoder -> duration chain runs to fp32 accuracy, csrc/precise.cu): bit-exact against the fp32 oracle on every
+    phoneme whose oracle exp(log_d)-1 is further than 1e-4 from a rounding boundary; the distance is
+    printed.  With duration_precision == "bf16" flips are only bounded.
 """
+
+BOUNDARY_TOL = 1e-4  # SURVEY §8c: free-running durations are exact where the oracle sits further than this from a .5
+
+
+def boundary_distance(log_d):
+    """|frac(exp(log_d) - 1) - 0.5| of the oracle: how far the reference's own value is from flipping."""
+    d = torch.exp(log_d.double()) - 1.0
+    return ((d % 1.0) - 0.5).abs()
 import pytest
 import torch
 
@@ -124,17 +134,36 @@ def test_free_running_batch1(setup):
     assert torch.equal(out[6].float(), exp_x)
     assert torch.equal(aux["mel_pos"], exp_pos) and torch.equal(aux["frame_idx"].long(), exp_idx)
     assert int(aux["mel_len"][0]) == out[0].shape[1] == int(aux["dur"].sum())
-    # against the fp32 oracle: bf16 noise may flip a duration that sits on a .5 boundary
+    # against the fp32 oracle: ZERO flips (the fp32-accurate chain is the default)
     d_ref = O.round_durations(ref["log_d_prediction"]).long()
     flips = (aux["dur"].long() != d_ref)
-    frac = (torch.exp(ref["log_d_prediction"]) - 1.0) % 1.0
-    dist = (frac - 0.5).abs()
+    dist = boundary_distance(ref["log_d_prediction"])
+    err = float((out[2] - ref["log_d_prediction"]).abs().max())
     print(f"\n[free-running B=1] frames ours={int(aux['dur'].sum())} oracle={int(d_ref.sum())} "
-          f"flips={int(flips.sum())}/64 min boundary distance={dist.min().item():.3e} "
-          f"log_d rel={rel_l2(out[2], ref['log_d_prediction']):.2e}")
-    assert (dist[flips] < 0.1).all(), "a duration flipped far from a rounding boundary"
-    assert int(flips.sum()) <= 8
-    assert rel_l2(out[2], ref["log_d_prediction"]) < TOL_BF16
+          f"flips={int(flips.sum())}/64 min boundary distance={dist.min().item():.3e} log_d max abs err={err:.2e}")
+    assert float(dist.min()) > BOUNDARY_TOL, "pick another seed: the oracle itself sits on a rounding boundary"
+    assert int(flips.sum()) == 0
+    assert err < 2e-5
+    # same discrete decisions -> same frames: the whole output tuple against the oracle
+    assert torch.equal(aux["mel_pos"], ref["mel_pos"]) and torch.equal(aux["frame_idx"].long(), ref["frame_idx"])
+    # the free-running mel also depends on the pitch / energy BUCKETS the bf16 predictors pick: one flipped bucket is
+    # worth ~2 %, so the end-to-end bar is 4e-2 here and the 1e-2 bar is checked with the oracle's own
+    # decisions forced (test_teacher_forced_parity, test_cfg2_full_size_vs_oracle)
+    bf = int((aux["p_idx"].long() != ref["p_idx"]).sum() + (aux["e_idx"].long() != ref["e_idx"]).sum())
+    e_mel = rel_l2(out[1], ref["outputs_postnet"])
+    print(f"[free-running B=1] mel_post rel-L2 {e_mel:.2e} with {bf} pitch/energy bucket flips of {2 * out[0].shape[1]}")
+    assert e_mel < 4e-2 and rel_l2(out[0], ref["outputs_prenet"]) < 4e-2
+    # the plain bf16 chain stays available; its flips are bounded, not forbidden
+    model.duration_precision = "bf16"
+    try:
+        with torch.no_grad():
+            out_b = model(text, src_mask)
+        fl_b = model.last_aux["dur"].long() != d_ref
+        print(f"[free-running B=1, duration_precision=bf16] flips={int(fl_b.sum())}/64")
+        assert (dist[fl_b] < 0.1).all() and int(fl_b.sum()) <= 8
+        assert rel_l2(out_b[2], ref["log_d_prediction"]) < TOL_BF16
+    finally:
+        model.duration_precision = "fp32"
 
 
 def test_free_running_batched(setup):
@@ -153,22 +182,84 @@ def test_free_running_batched(setup):
         out = model(text, src_mask)
     torch.cuda.synchronize()
     aux = model.last_aux
-    assert rel_l2(out[2], ref["log_d_prediction"]) < TOL_BF16
     assert torch.equal(aux["dur"].long(), O.round_durations(out[2]).long())
     d_ref = O.round_durations(ref["log_d_prediction"]).long()
     flips = aux["dur"].long() != d_ref
-    dist = (((torch.exp(ref["log_d_prediction"]) - 1.0) % 1.0) - 0.5).abs()
-    assert (dist[flips] < 0.1).all() and int(flips.sum()) <= 0.1 * flips.numel()
-    # the regulator and the mask rule on OUR durations: exact
+    dist = boundary_distance(ref["log_d_prediction"])[pos != 0]
+    print(f"\n[free-running B=4 ragged] flips={int(flips.sum())}/{flips.numel()} min boundary distance={float(dist.min()):.3e} "
+          f"frames ours={aux['mel_len'].tolist()} oracle={d_ref.sum(1).tolist()}")
+    assert float(dist.min()) > BOUNDARY_TOL, "pick another seed: the oracle itself sits on a rounding boundary"
+    assert int(flips.sum()) == 0
+    assert float((out[2] - ref["log_d_prediction"]).abs().max()) < 2e-5
+    # the regulator and the mask rule: exact against the oracle
     exp_x, exp_pos, exp_idx = O.length_regulator(aux["encoder_output"].float(), aux["dur"])
     assert torch.equal(out[6].float(), exp_x) and torch.equal(aux["mel_pos"], exp_pos)
+    assert torch.equal(aux["mel_pos"], ref["mel_pos"]) and torch.equal(aux["frame_idx"].long(), ref["frame_idx"])
     assert torch.equal(aux["mel_mask"].bool(), O.get_mask_from_lengths(exp_pos))
     assert out[0].shape[1] == int(aux["mel_len"].max())
-    print(f"\n[free-running B=4 ragged] flips={int(flips.sum())}/{flips.numel()} frames ours={aux['mel_len'].tolist()} "
-          f"oracle={d_ref.sum(1).tolist()}")
-    if not flips.any():  # same discrete decisions -> same frames: compare the mels
-        ml = aux["mel_len"]
-        assert rel_l2(valid_rows(out[1], ml), valid_rows(ref["outputs_postnet"], ml)) < 2e-2
+    ml = aux["mel_len"]
+    # the free-running mel moves with the pitch / energy buckets the bf16 predictors pick (one flipped
+    # bucket is worth 2 %), so the end-to-end bar is 3x the teacher-forced one
+    assert rel_l2(valid_rows(out[1], ml), valid_rows(ref["outputs_postnet"], ml)) < 4e-2
+
+
+def test_cfg2_full_size_vs_oracle(setup):
+    """BASELINE.json configs[1] at FULL size (B=64, 128 phonemes -> ~1000 frames, free-running) against the fp32 oracle
+    run on the GPU (fp32, TF32 off).  Durations, mel lengths, frame indices, positions and the mask must be bit-exact
+    wherever the oracle is not within BOUNDARY_TOL of a rounding boundary (on the committed seed: everywhere); the mel
+    is compared on the same frames with the oracle's own pitch / energy decisions teacher-forced (oracle mode 3), so
+    the 1e-2 bf16 bar applies."""
+    from oracle import fastspeech2_oracle as O
+    from transformer_tts_b200 import synth
+
+    hp, sd, sd_gpu, model = setup
+    B, L = 64, 128
+    text, pos, lens = synth.synth_text_batch(B, L, seed=1234)  # the batch bench.py times on rank 0
+    text, pos = text.cuda(), pos.cuda()
+    src_mask = (pos != 0).unsqueeze(-2)
+    with torch.no_grad():
+        e_out, _ = O.encoder(sd_gpu, "encoder.", text, src_mask, hp.n_layer_encoder, hp.n_head_encoder)
+        log_d_ref = O.variance_predictor(sd_gpu, "variance_adaptor.duration_predictor.", e_out, src_mask)
+        out = model(text, src_mask)
+    aux = dict(model.last_aux)
+    valid = pos != 0
+    d_ref = torch.where(valid, O.round_durations(log_d_ref).long(), torch.zeros_like(pos))
+    dist = boundary_distance(log_d_ref)
+    flips = (aux["dur"].long() != d_ref) & valid
+    near = (dist <= BOUNDARY_TOL) & valid
+    print(f"\n[cfg2 full size] phonemes {int(valid.sum())}, oracle min boundary distance {float(dist[valid].min()):.3e} "
+          f"({int(near.sum())} within {BOUNDARY_TOL:g}), flips {int(flips.sum())}, log_d max abs err "
+          f"{float((out[2] - log_d_ref)[valid].abs().max()):.2e}, frames {int(aux['mel_len'].sum())}")
+    assert not bool((flips & ~near).any()), "a duration flipped away from a rounding boundary"
+    assert int(flips.sum()) == 0, "committed seed: no phoneme sits within 1e-4 of a boundary, so no flip is excusable"
+    assert float((out[2] - log_d_ref)[valid].abs().max()) < 2e-5
+    # integer outputs against the oracle's regulator on ITS durations: bit-exact
+    mel_len = d_ref.sum(1)
+    T = int(mel_len.max())
+    assert torch.equal(aux["mel_len"].long(), mel_len) and out[0].shape[1] == T
+    ar = torch.arange(1, T + 1, device="cuda").unsqueeze(0)
+    pos_mel = torch.where(ar <= mel_len.unsqueeze(1), ar.expand(B, T), torch.zeros(B, T, dtype=torch.long, device="cuda"))
+    mel_mask = (pos_mel != 0).unsqueeze(-2)
+    with torch.no_grad():
+        ref = run_oracle(sd_gpu, hp, text, src_mask, mel_mask=mel_mask, d_target=d_ref)
+    assert torch.equal(aux["mel_pos"], ref["mel_pos"]) and torch.equal(aux["frame_idx"].long(), ref["frame_idx"])
+    assert torch.equal(aux["mel_mask"].bool(), O.get_mask_from_lengths(ref["mel_pos"]))
+    # free-running mel (our own bf16 pitch / energy decisions) against the oracle's: reported; bounded at 3x the bar
+    e_free = rel_l2(valid_rows(out[1], mel_len), valid_rows(ref["outputs_postnet"], mel_len))
+    # oracle mode 3 on the same frames: pitch / energy values forced to the oracle's -> the bf16 bar proper
+    with torch.no_grad():
+        out3 = model(text, src_mask, mel_mask=mel_mask, d_target=d_ref, p_target=ref["p_prediction"],
+                     e_target=ref["e_prediction"])
+        ref3 = run_oracle(sd_gpu, hp, text, src_mask, mel_mask=mel_mask, d_target=d_ref, p_target=ref["p_prediction"],
+                          e_target=ref["e_prediction"])
+    e_pre = rel_l2(valid_rows(out3[0], mel_len), valid_rows(ref3["outputs_prenet"], mel_len))
+    e_post = rel_l2(valid_rows(out3[1], mel_len), valid_rows(ref3["outputs_postnet"], mel_len))
+    bucket_flips = int((model.last_aux["p_idx"].long() != ref3["p_idx"]).sum() + (model.last_aux["e_idx"].long() != ref3["e_idx"]).sum())
+    print(f"[cfg2 full size] mel rel-L2 vs oracle: free-running {e_free:.2e}; decisions forced: pre {e_pre:.2e} post {e_post:.2e} "
+          f"(bucket flips {bucket_flips})")
+    assert bucket_flips == 0
+    assert e_pre < TOL_BF16 and e_post < TOL_BF16
+    assert e_free < 4e-2
 
 
 def test_full_size_properties_cfg2(setup):
