@@ -12,10 +12,16 @@ CUDA events; `e2e` = the same through the public module API with pinned HOST inp
 mel_post copied D2H inside the timed region.  Multi-GPU: utterances are sharded across ranks with no
 data-path collective (weak scaling); the only collective is the MAX over ranks of the elapsed time.
 
+The timed mode is `config.duration_precision` = "fp32": the encoder -> duration chain runs to fp32 accuracy so the
+durations, frame indices and mel lengths equal the fp32 reference's (tests/test_model_gpu.py::
+test_cfg2_full_size_vs_oracle checks exactly this batch).  `bf16_duration_chain` reports the faster mode whose
+durations may flip.  Sub-records: `torch_eager_b200` (the oracle port of the reference under stock
+PyTorch eager on the same GPU, bf16 autocast, decisions teacher-forced — BASELINE.md §3), `train` (the data-parallel
+training step of configs[2] with the NCCL all-reduce, at every N), `latency_b1` (the reference's own batch-1 call).
+
 `--impl reference` times the reference algorithm's CPU implementation (the oracle port, fp32, all host
-threads) on a bounded sample of the same workload — the unmodified reference is Python that cannot
-travel to the GPU box (it lives outside the repo), the oracle is its line-by-line restatement pinned
-by tests/golden.
+threads) on the same 64-utterance batch — the unmodified reference is Python that cannot travel to the GPU
+box (it lives outside the repo), the oracle is its line-by-line restatement pinned by tests/golden.
 """
 from __future__ import annotations
 
@@ -49,49 +55,85 @@ def read_peaks():
 
 
 class ClockSampler(threading.Thread):
-    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+    """Samples SM clocks / throttle reasons of this rank's GPU while the timed regions run.  NVML is queried in-process
+    (pynvml: microseconds per sample, no fork); `nvidia-smi` subprocesses are the fallback.  Round 1 forked a
+    10 Hz nvidia-smi on every rank inside the timed region, which the 8-GPU run may have paid for."""
 
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index: int):
+    def __init__(self, gpu_index: int, period_s: float = 0.05):
         super().__init__(daemon=True)
         self.gpu = gpu_index
+        self.period = period_s
         self.stop_flag = threading.Event()
-        self.samples = []
+        self.samples = []   # (sm_mhz, max_mhz, set of reason names)
+        self.nvml = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[gpu_index]) if vis and all(t.strip().isdigit() for t in vis.split(",")) else gpu_index
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.nvml = pynvml
+        except Exception:
+            self.nvml = None
+
+    def _sample_nvml(self):
+        n = self.nvml
+        sm = n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)
+        mx = n.nvmlDeviceGetMaxClockInfo(self.handle, n.NVML_CLOCK_SM)
+        get = getattr(n, "nvmlDeviceGetCurrentClocksEventReasons", None) or n.nvmlDeviceGetCurrentClocksThrottleReasons
+        r = get(self.handle)
+        names = set()
+        for nm, bit in (("hw_slowdown", 0x8), ("sw_power_cap", 0x4), ("sw_thermal_slowdown", 0x20),
+                        ("hw_thermal_slowdown", 0x40)):
+            if r & bit:
+                names.add(nm)
+        self.samples.append((float(sm), float(mx), names))
+
+    def _sample_smi(self):
+        out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                              str(self.gpu)], capture_output=True, text=True, timeout=5).stdout.strip()
+        if out:
+            f = [t.strip() for t in out.split(",")]
+            names = {n for n, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], f[2:6])
+                     if v.lower().startswith("active")}
+            self.samples.append((float(f[0]), float(f[1]), names))
 
     def run(self):
         while not self.stop_flag.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                      "-i", str(self.gpu)], capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.samples.append([s.strip() for s in out.split(",")])
+                if self.nvml is not None:
+                    self._sample_nvml()
+                else:
+                    self._sample_smi()
             except Exception:
                 pass
-            self.stop_flag.wait(0.1)
+            self.stop_flag.wait(self.period if self.nvml is not None else 0.5)
 
     def summary(self):
-        sm, mx, reasons = [], 0, set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for s in self.samples:
-            try:
-                sm.append(float(s[0]))
-                mx = max(mx, float(s[1]))
-                for n, v in zip(names, s[2:6]):
-                    if v.lower().startswith("active"):
-                        reasons.add(n)
-            except Exception:
-                continue
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx or None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        sm = [x[0] for x in self.samples]
+        reasons = set()
+        for x in self.samples:
+            reasons |= x[2]
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_min_mhz": min(sm) if sm else None,
+                "sm_max_mhz": max((x[1] for x in self.samples), default=None), "reasons": sorted(reasons),
+                "samples": len(sm), "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
-def make_batch(rank: int):
-    from transformer_tts_b200 import synth
+def make_batch(rank: int, world: int = 1):
+    """One pool of world x 64 utterances, dealt to ranks by transformer_tts_b200.sharding (longest first,
+    snake order); rank 0 of a 1-GPU run gets exactly the batch of tests/test_model_gpu.py::test_cfg2_full_size_vs_oracle."""
+    import torch
 
-    text, pos, lens = synth.synth_text_batch(B_PER_GPU, L_PHON, seed=1234 + rank)
-    return text, pos, lens
+    from transformer_tts_b200 import sharding, synth
+
+    text, pos, lens = synth.synth_text_batch(B_PER_GPU * world, L_PHON, seed=1234)
+    mine = sorted(sharding.shard_by_length([int(n) for n in lens], world)[rank])
+    idx = torch.tensor(mine)
+    return text[idx], pos[idx], lens[idx]
 
 
 def cpu_oracle_run(steps: int, warmup: int, sample_b: int):
@@ -105,7 +147,7 @@ def cpu_oracle_run(steps: int, warmup: int, sample_b: int):
     torch.set_num_threads(cores)
     hp = synth.make_hp()
     sd = synth.synth_state_dict(hp)
-    text, pos, _ = make_batch(0)
+    text, pos, _ = make_batch(0, 1)
     text, pos = text[:sample_b], pos[:sample_b]
     src_mask = (pos != 0).unsqueeze(-2)
     times, frames = [], 0
@@ -127,48 +169,65 @@ def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    r = cpu_oracle_run(max(1, min(args.steps, 20)), 1, sample_b=8)
+    r = cpu_oracle_run(max(1, min(args.steps, 10)), 1, sample_b=B_PER_GPU)  # the whole batch of the GPU arm
     line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "note": "CPU, bounded sample"},
+            "config": {"workload": WORKLOAD, "batch_per_gpu": B_PER_GPU, "phonemes": L_PHON,
+                       "note": "CPU fp32 oracle port, the same 64-utterance batch as the GPU arm's rank 0"},
             "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
 
-def kernel_rooflines(model, peaks, tmax):
-    """Per-kernel rooflines at the decoder shape of the workload (B x Tmax rows): every hot kernel is timed
-    alone with CUDA events around a captured graph of 12 launches, rotating over three buffer sets so that
-    consecutive launches never find their operands in the 126 MB L2.  Algorithmic work per launch as in DESIGN.md."""
+def load_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the hot kernels, from ONE `ncu --set full` capture of
+    tools/run_hot_kernels.py on this tree (profiles/r02_hot_kernels_traffic.json, written by tools/ncu_traffic.py with
+    the tree it was captured on).  Absent file -> traffic is reported as null, never as a stale literal."""
+    p = ROOT / "profiles" / "r02_hot_kernels_traffic.json"
+    if not p.exists():
+        return {}, None
+    d = json.loads(p.read_text())
+    return d.get("traffic_bytes", {}), d.get("tree")
+
+
+def kernel_rooflines(model, peaks, mel_len):
+    """Per-kernel rooflines at the decoder shape of the workload: the REAL ragged batch of the timed step (mel_len of
+    its 64 utterances, Tmax = their maximum, the same ragged tile list the step uses).  Every hot kernel is timed alone
+    with CUDA events around a captured graph of 12 launches, rotating over three buffer sets so that consecutive
+    launches never find their operands in the 126 MB L2.  Algorithmic work counts VALID rows only (SURVEY §8d:
+    padding work does not count) and is reported against both roofs."""
     import torch
 
     from transformer_tts_b200 import lib
     from transformer_tts_b200.Models import _engine as E
 
-    B, T, D, H = B_PER_GPU, int(tmax), 384, 4
+    lens = mel_len.to("cpu", torch.int64)
+    B, T, D, H = int(lens.numel()), int(lens.max()), 384, 4
     dev = "cuda"
     lc = E.layer_cache(model.decoder.layers[0])
     k = lc["k"]
     NS = 3
-    g = torch.Generator(device="cpu").manual_seed(7)
-    lens = torch.randint(int(0.8 * T), T + 1, (B,), generator=g)
-    lens[0] = T
     mask = (torch.arange(T)[None, :] < lens[:, None]).to(torch.uint8).to(dev)
     kv = lib.mask_lengths(mask)
-    rows_valid = float(lens.sum())
+    tmap = lib.build_tile_map(kv, T)
+    M = float(lens.sum())                      # valid rows
+    rows_padded = float(B * T)
     xs = [(torch.randn(B, T, D, device=dev) * 0.5).to(torch.bfloat16) for _ in range(NS)]
     x32 = [torch.randn(B, T, D, device=dev) for _ in range(NS)]
     qkvs = [(torch.randn(B, T, 3 * D, device=dev) * 0.5).to(torch.bfloat16) for _ in range(NS)]
     hs = [torch.relu(torch.randn(B, T, 4 * D, device=dev)).to(torch.bfloat16) for _ in range(NS)]
     ob = [torch.empty(B, T, D, device=dev, dtype=torch.bfloat16) for _ in range(NS)]
     o32 = [torch.empty(B, T, D, device=dev) for _ in range(NS)]
-    L = 128
+    L = L_PHON
     xe = [(torch.randn(B, L, D, device=dev)).to(torch.bfloat16) for _ in range(NS)]
-    dur = torch.full((B, L), T // L, dtype=torch.int32, device=dev)
-    cum, mel_len = lib.lr_scan(dur)
-    Tlr = int(mel_len.max().item())
+    # durations that expand L phonemes to exactly this batch's frame counts
+    dur = (lens[:, None] // L).expand(B, L).clone()
+    dur[:, 0] += lens - dur.sum(1)
+    dur = dur.to(torch.int32).to(dev)
+    cum, ml = lib.lr_scan(dur)
+    Tlr = T
     va = model.variance_adaptor
     pb, eb = va._bins(torch.device(dev))
     tabs = va._tables()
@@ -177,25 +236,30 @@ def kernel_rooflines(model, peaks, tmax):
     ln = lc["ln1"]
 
     def t_qkv(i):
-        lib.conv_gemm(xs[i], lc["wqkv"], lc["bqkv"], block_n=192, out_bf16=qkvs[i])
+        lib.conv_gemm(xs[i], lc["wqkv"], lc["bqkv"], block_n=192, out_bf16=qkvs[i], tile_map=tmap)
 
     def t_att(i):
-        lib.attention_fwd(qkvs[i], mask, kv, ob[i], H)
+        lib.attention_fwd(qkvs[i], mask, kv, ob[i], H, skip_padded_queries=True)
 
     def t_out(i):
         lib.conv_gemm(xs[i], lc["wo"], lc["bo"], block_n=D, epi=lib.EPI_RES_LN, res_f32=x32[i], res_bstride=T * D,
-                      res_tstride=D, ln1=lc["ln2"], out_f32=o32[i], out_bf16=ob[i])
+                      res_tstride=D, ln1=lc["ln2"], out_f32=o32[i], out_bf16=ob[i], tile_map=tmap)
 
     def t_ffn1(i):
-        lib.conv_gemm(xs[i], lc["w1"], lc["b1"], taps=k, pad_left=k // 2, block_n=256, act=lib.ACT_RELU, out_bf16=hs[i])
+        lib.conv_gemm(xs[i], lc["w1"], lc["b1"], taps=k, pad_left=k // 2, block_n=256, act=lib.ACT_RELU, out_bf16=hs[i],
+                      tile_map=tmap)
 
     def t_ffn2(i):
         lib.conv_gemm(hs[i], lc["w2"], lc["b2"], taps=k, pad_left=k // 2, block_n=D, epi=lib.EPI_FFN2, res_bf16=xs[i],
                       res_f32=x32[i], res_bstride=T * D, res_tstride=D, ln1=lc["ln_ff"], ln2=ln, out_f32=o32[i],
-                      out_bf16=ob[i])
+                      out_bf16=ob[i], tile_map=tmap)
+
+    def t_ffn(i):
+        t_ffn1(i)
+        t_ffn2(i)
 
     def t_lr(i):
-        lib.lr_expand(xe[i], cum, mel_len, Tlr, want_aux=True)
+        lib.lr_expand(xe[i], cum, ml, Tlr, want_aux=True)
 
     def t_bucket(i):
         lib.bucket_embed_add(xs[i], pv[i], ev_[i], pb, eb, tabs["ptab"], tabs["etab"])
@@ -203,36 +267,33 @@ def kernel_rooflines(model, peaks, tmax):
     def t_ln(i):
         lib.layernorm(x32[i], ln[0], ln[1], E.LN_EPS, y_bf16=ob[i])
 
-    M = float(B * T)
     att_flops = float((4.0 * lens.double() ** 2 * D).sum())
     s2 = 2  # bf16 bytes
-    # (name, launcher, algorithmic FLOPs, algorithmic HBM bytes): the kernel is reported against whichever roof
-    # gives the LARGER floor time (DESIGN.md section 4 lists both figures)
+    # (key, name, launcher, algorithmic FLOPs, algorithmic HBM bytes).  Bytes are what the op must move when NOTHING is
+    # re-read: operands once in, results once out.  The FFN pair's bytes are those of the fused op the reference writes
+    # as one function (Models/modules.py:81-88): x in (bf16), residual in + out (fp32), next-LN out (bf16) — the
+    # 1536-wide hidden activation is not algorithmic traffic.
     specs0 = [
-        ("conv_gemm<192,AFFINE,A-stationary> decoder q|k|v linears", t_qkv, 2 * M * D * 3 * D, M * D * s2 * 4),
-        ("attention_fwd decoder masked self-attention", t_att, att_flops, M * D * s2 * 4),
-        ("conv_gemm<384,RES_LN> decoder out-proj + residual + LayerNorm", t_out, 2 * M * D * D, M * D * (2 * s2 + 8)),
-        ("conv_gemm<256,AFFINE,A-stationary> decoder FFN conv1 + ReLU", t_ffn1, 2 * M * D * 4 * D * k, M * D * s2 * 5),
-        ("conv_gemm<384,FFN2> decoder FFN conv2 + LN + residual + LN", t_ffn2, 2 * M * D * 4 * D * k,
+        ("qkv", "conv_gemm<192,AFFINE,A-stationary> decoder q|k|v linears", t_qkv, 2 * M * D * 3 * D, M * D * s2 * 4),
+        ("attention", "attention_fwd decoder masked self-attention", t_att, att_flops, M * D * s2 * 4),
+        ("out_proj", "conv_gemm<384,RES_LN> decoder out-proj + residual + LayerNorm", t_out, 2 * M * D * D,
+         M * D * (2 * s2 + 8)),
+        ("ffn1", "conv_gemm<256,AFFINE,A-stationary> decoder FFN conv1 + ReLU", t_ffn1, 2 * M * D * 4 * D * k,
+         M * D * s2 * 5),
+        ("ffn2", "conv_gemm<384,FFN2> decoder FFN conv2 + LN + residual + LN", t_ffn2, 2 * M * D * 4 * D * k,
          M * D * (s2 * 6 + 8)),
-        ("lr_expand LengthRegulator frame gather", t_lr, 0,
-         B * L * D * s2 + B * L * 4 + B * Tlr * D * s2 + B * Tlr * (4 + 8 + 1) + B * 4),
-        ("bucket_embed_add pitch/energy bucketize + embedding add", t_bucket, 0, M * D * s2 * 2 + M * 8),
-        ("layernorm standalone fp32 -> bf16", t_ln, 0, M * D * (4 + s2)),
+        ("ffn_pair", "decoder FFN as the reference's ONE op (conv1 + ReLU + conv2 + res + LN + res + LN): both launches",
+         t_ffn, 4 * M * D * 4 * D * k, M * D * (s2 + 4 + 4 + s2)),
+        ("lr_expand", "lr_expand LengthRegulator frame gather", t_lr, 0,
+         B * L * D * s2 + B * L * 4 + M * D * s2 + rows_padded * (4 + 8 + 1) + B * 4),
+        ("bucket_embed_add", "bucket_embed_add pitch/energy bucketize + embedding add", t_bucket, 0,
+         rows_padded * D * s2 * 2 + rows_padded * 8),
+        ("layernorm", "layernorm standalone fp32 -> bf16", t_ln, 0, rows_padded * D * (4 + s2)),
     ]
-    specs = []
-    for name, fn, flops, nbytes in specs0:
-        t_tc = flops / (peaks["tc_burst"] * 1e12)
-        t_hbm = nbytes / (peaks["hbm"] * 1e9)
-        specs.append((name, fn, "tensor", flops) if t_tc >= t_hbm else (name, fn, "hbm", nbytes))
-    # dram__bytes_read.sum + dram__bytes_write.sum per launch from ONE `ncu --set full` capture of the same shapes
-    # (profiles/r01_hot_kernels_v5_full_summary.csv, tools/run_hot_kernels.py).  Writes that are still resident in
-    # the 126 MB write-back L2 when the kernel ends are not counted by the DRAM counters.
-    traffic_mb = [55.2 + 109.0, 154.9 + 36.8, 163.4 + 112.9, 56.3 + 162.8, 389.4 + 128.1, 6.3 + 2.4, 55.5 + 7.1,
-                  108.4 + 8.0]
+    traffic, traffic_tree = load_traffic()
     out = []
     reps = 4
-    for (name, fn, bound, work), tr_mb in zip(specs, traffic_mb):
+    for key, name, fn, flops, nbytes in specs0:
         for i in range(NS):
             fn(i)  # warm-up: first-call attribute setup, allocator pools
         torch.cuda.synchronize()
@@ -253,14 +314,139 @@ def kernel_rooflines(model, peaks, tmax):
             torch.cuda.synchronize()
             times.append(e0.elapsed_time(e1) / (reps * NS))
         ms = statistics.median(times)
-        if bound == "tensor":
-            ach, peak, unit = work / (ms * 1e-3) / 1e12, peaks["tc_burst"], "TFLOP/s"
+        tf = flops / (ms * 1e-3) / 1e12
+        gb = nbytes / (ms * 1e-3) / 1e9
+        t_tc = flops / (peaks["tc_burst"] * 1e12)
+        t_hbm = nbytes / (peaks["hbm"] * 1e9)
+        bound = "tensor" if t_tc >= t_hbm else "hbm"
+        ach, peak, unit = (tf, peaks["tc_burst"], "TFLOP/s") if bound == "tensor" else (gb, peaks["hbm"], "GB/s")
+        if key == "ffn_pair" and "ffn1" in traffic and "ffn2" in traffic:
+            tr = traffic["ffn1"] + traffic["ffn2"]
         else:
-            ach, peak, unit = work / (ms * 1e-3) / 1e9, peaks["hbm"], "GB/s"
-        out.append({"kernel": name, "bound": bound, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak,
-                    "traffic": tr_mb * 1e6, "ms_per_launch": ms, "algorithmic_work_per_launch": work,
+            tr = traffic.get(key)
+        out.append({"kernel": name, "key": key, "bound": bound, "achieved": ach, "peak": peak, "unit": unit,
+                    "frac": ach / peak, "traffic": tr, "ms_per_launch": ms,
+                    "algorithmic_flops_per_launch": flops, "algorithmic_bytes_per_launch": nbytes,
+                    "frac_of_tensor_roof": tf / peaks["tc_burst"], "frac_of_hbm_roof": gb / peaks["hbm"],
+                    "rows_valid": M, "rows_padded": rows_padded, "traffic_tree": traffic_tree,
                     "peak_source": peaks["src"] + (" burst bf16 (kernel timed alone)" if bound == "tensor" else " copy bandwidth")})
     return out
+
+
+def torch_eager_b200(hp, text_d, mask_d, aux, p_pred, e_pred, steps: int = 3):
+    """BASELINE.md §3 "reference on the same box": the oracle port of the reference's modules under STOCK PyTorch eager
+    on this GPU, bf16 autocast, durations / pitch / energy teacher-forced to the decisions of our own run (oracle mode
+    3, so both arms produce the same frames), CUDA events.  A reported baseline; never on the product path."""
+    import torch
+
+    from oracle import fastspeech2_oracle as O
+    from transformer_tts_b200 import synth
+
+    sd = {k: v.cuda() for k, v in synth.synth_state_dict(hp).items()}
+    dur = aux["dur"].long()
+    mel_len = dur.sum(1)
+    B, T = int(dur.shape[0]), int(mel_len.max())
+    ar = torch.arange(1, T + 1, device="cuda").unsqueeze(0)
+    mel_mask = (ar <= mel_len.unsqueeze(1)).unsqueeze(-2)
+    frames = int(mel_len.sum())
+
+    def step():
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+            return O.fastspeech2_forward(sd, vars(hp), text_d, mask_d, mel_mask=mel_mask, d_target=dur, p_target=p_pred,
+                                         e_target=e_pred)
+
+    step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    return {"value": frames / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "steps": steps, "frames_per_step": frames,
+            "what": "oracle port of Models/fastspeech2.py, stock PyTorch eager on cuda:0, torch.autocast(bfloat16), "
+                    "durations / pitch / energy teacher-forced (oracle mode 3), attention maps not kept"}
+
+
+def latency_b1(model, hp, iters: int = 20):
+    """BASELINE.json configs[0] shape on the GPU: the reference's own serving call (test_fastspeech2.py:165-171),
+    batch 1, 64 phonemes, free-running; wall-clock per call with a synchronize after each (a serving loop's latency)."""
+    import torch
+
+    from transformer_tts_b200 import lib, synth
+
+    text, pos, _ = synth.synth_text_batch(1, 64, seed=1234)
+    text, mask = text.cuda(), (pos != 0).unsqueeze(-2).cuda()
+    for _ in range(3):
+        model(text, mask)
+    torch.cuda.synchronize()
+    ts = []
+    l0 = lib.LAUNCH_COUNT
+    for _ in range(iters):
+        t0 = time.perf_counter()
+        o = model(text, mask)
+        torch.cuda.synchronize()
+        ts.append(1e3 * (time.perf_counter() - t0))
+    return {"ms_median": statistics.median(ts), "ms_min": min(ts), "frames": int(o[0].shape[1]),
+            "launches_per_call": (lib.LAUNCH_COUNT - l0) // iters, "workload": "B=1, 64 phonemes, free-running, eager"}
+
+
+def train_record(args, rank: int, world: int, steps: int = 5):
+    """BASELINE.json configs[2] inside the default line: the data-parallel training step (fwd + bwd + NCCL all-reduce
+    of the flat gradient buffer + SyncBatchNorm + fused RAdam), 32 utterances per GPU, so the driver's 1/2/4/8 scaling
+    run records the training curve next to the inference one."""
+    import torch
+    import torch.distributed as dist
+
+    from transformer_tts_b200 import build_fastspeech2, synth
+    from transformer_tts_b200.training import Trainer
+
+    hp = synth.make_hp()
+    model = build_fastspeech2(hp)
+    model.load_state_dict(synth.synth_state_dict(hp))
+    model = model.cuda().train()
+    tr = Trainer(model, optimizer="radam")
+    tr.broadcast_parameters()
+    host, frames = make_train_batch(rank, 32)
+    dev = {k: v.cuda() for k, v in host.items()}
+    for _ in range(3):
+        out = tr.train_step(**dev)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        out = tr.train_step(**dev)
+    e1.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    my_ms = e0.elapsed_time(e1) / steps
+    ar_ms = 0.0
+    if world > 1:
+        e0.record()
+        for _ in range(3):
+            dist.all_reduce(tr.flat_g)
+        e1.record()
+        torch.cuda.synchronize()
+        ar_ms = e0.elapsed_time(e1) / 3
+    t = torch.tensor([my_ms, ar_ms, float(frames)], device="cuda", dtype=torch.float64)
+    tot = t.clone()
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    ms, ar = float(t[0]), float(t[1])
+    total_frames = float(tot[2])
+    rec = {"metric": "fastspeech2_train_mel_frames_per_sec", "value": total_frames / (ms * 1e-3), "unit": UNIT,
+           "ms_per_step": ms, "allreduce_ms": ar, "steps": steps, "batch_per_gpu": 32, "frames_per_step": total_frames,
+           "optimizer": "radam", "loss": float(out["loss"]),
+           "parallelism": f"dp{world}: one NCCL all-reduce of the flat fp32 gradient buffer "
+                          f"({tr.flat_g.numel() * 4 / 1e6:.0f} MB) + SyncBatchNorm moments" if world > 1 else "dp1"}
+    del tr, model, dev, out
+    torch.cuda.empty_cache()
+    return rec
 
 
 def ours(args):
@@ -280,7 +466,8 @@ def ours(args):
     model = build_fastspeech2(hp).eval()
     model.load_state_dict(synth.synth_state_dict(hp))
     model = model.cuda()
-    text_h, pos_h, _ = make_batch(rank)
+    model.duration_precision = args.duration_precision
+    text_h, pos_h, _ = make_batch(rank, world)
     text_h, mask_h = text_h.pin_memory(), (pos_h != 0).unsqueeze(-2).pin_memory()
     text_d, mask_d = text_h.cuda(), mask_h.cuda()
     peaks = read_peaks()
@@ -290,45 +477,47 @@ def ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def max_over_ranks(x: float) -> float:
+    def reduce(x: float, op) -> float:
         if world == 1:
             return x
         t = torch.tensor([x], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=op)
         return float(t.item())
 
-    def sum_over_ranks(x: float) -> float:
+    def gather(x: float):
         if world == 1:
-            return x
-        t = torch.tensor([x], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+            return [round(x, 4)]
+        g = [torch.zeros(1, device="cuda", dtype=torch.float64) for _ in range(world)]
+        dist.all_gather(g, torch.tensor([x], device="cuda", dtype=torch.float64))
+        return [round(float(t.item()), 4) for t in g]
 
-    frames = 0
-    with torch.no_grad():
-        for _ in range(max(3, args.warmup)):
-            model(text_d, mask_d)
-        frames = int(model.last_aux["mel_len"].sum().item())
-        tmax = int(model.last_aux["mel_len"].max().item())
-        # ---- device-resident throughput ----
-        sampler = ClockSampler(local_rank)
-        sampler.start()
+    MAX, SUM = (dist.ReduceOp.MAX, dist.ReduceOp.SUM) if world > 1 else (None, None)
+
+    def timed_steps(n):
         barrier()
-        l0 = lib.LAUNCH_COUNT
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for _ in range(args.steps):
+        for _ in range(n):
             model(text_d, mask_d)
         e1.record()
         barrier()
+        return e0.elapsed_time(e1)
+
+    with torch.no_grad():
+        for _ in range(max(3, args.warmup)):
+            out = model(text_d, mask_d)
+        aux = dict(model.last_aux)
+        p_pred, e_pred = out[3].clone(), out[4].clone()
+        frames = int(aux["mel_len"].sum().item())
+        tmax = int(aux["mel_len"].max().item())
+        # ---- device-resident throughput (the parity mode) ----
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        l0 = lib.LAUNCH_COUNT
+        my_ms = timed_steps(args.steps)
         launches = lib.LAUNCH_COUNT - l0
-        my_ms = e0.elapsed_time(e1)
-        dev_ms = max_over_ranks(my_ms)
-        rank_ms = [my_ms / args.steps]
-        if world > 1:  # the step is the max over ranks: report every rank's own time next to it
-            g = [torch.zeros(1, device="cuda", dtype=torch.float64) for _ in range(world)]
-            dist.all_gather(g, torch.tensor([my_ms / args.steps], device="cuda", dtype=torch.float64))
-            rank_ms = [round(float(x.item()), 4) for x in g]
+        dev_ms = reduce(my_ms, MAX)
+        rank_ms = gather(my_ms / args.steps)
         # ---- end to end: pinned host inputs -> H2D -> forward -> mel_post D2H ----
         # Every step copies its inputs H2D and its mel D2H inside the timed region.  The D2H of step i runs on a
         # copy stream (two pinned buffers) while step i+1 computes, as a serving loop would; the timed region ends
@@ -350,37 +539,64 @@ def ours(args):
             e2e_step(i)
         copy_s.synchronize()
         barrier()
-        t0 = time.perf_counter()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for i in range(args.steps):
             e2e_step(i)
         main_s.wait_stream(copy_s)
         e1.record()
         barrier()
-        e2e_ms = max_over_ranks(e0.elapsed_time(e1))
+        e2e_ms = reduce(e0.elapsed_time(e1), MAX)
         sampler.stop_flag.set()
         sampler.join(timeout=2)
-        roofs = kernel_rooflines(model, peaks, tmax) if rank == 0 else None
-    total_frames = sum_over_ranks(float(frames))
+        clocks = sampler.summary()
+        clocks_by_rank = gather(float(clocks["sm_mhz"] or 0.0))
+        # ---- the other duration mode, for comparison ----
+        other = "bf16" if args.duration_precision == "fp32" else "fp32"
+        model.duration_precision = other
+        for _ in range(3):
+            model(text_d, mask_d)
+        frames_o = reduce(float(model.last_aux["mel_len"].sum().item()), SUM)
+        n_o = max(5, min(args.steps, 20))
+        other_ms = reduce(timed_steps(n_o), MAX)
+        model.duration_precision = args.duration_precision
+        lat = latency_b1(model, hp) if rank == 0 else None
+        roofs = kernel_rooflines(model, peaks, aux["mel_len"]) if rank == 0 else None
+        eager = torch_eager_b200(hp, text_d, mask_d, aux, p_pred, e_pred) if rank == 0 and not args.no_eager_baseline else None
+    total_frames = reduce(float(frames), SUM)
     value = total_frames * args.steps / (dev_ms * 1e-3)
     e2e_value = total_frames * args.steps / (e2e_ms * 1e-3)
+    del out_h
+    torch.cuda.empty_cache()
+    trn = None if args.no_train_record else train_record(args, rank, world)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        r = cpu_oracle_run(10, 1, sample_b=8)
+        r = cpu_oracle_run(3, 1, sample_b=B_PER_GPU)
         cpu = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]}
     if rank == 0:
+        by_key = {r["key"]: r for r in roofs}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(3, args.warmup), "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+                "ms_per_step_by_rank": rank_ms, "sm_mhz_by_rank": clocks_by_rank,
                 "config": {"workload": WORKLOAD, "batch_per_gpu": B_PER_GPU, "phonemes": L_PHON,
-                           "frames_per_step_per_gpu": frames, "t_max": tmax, "sharding": f"utterances x{world}, no collective",
-                           "ms_per_step_by_rank": rank_ms,
+                           "duration_precision": args.duration_precision,
+                           "duration_precision_note": "fp32 = encoder -> duration chain to fp32 accuracy (split-fp16 x3 "
+                                                      "tensor-core GEMMs): durations / frame indices / mel lengths equal "
+                                                      "the fp32 reference's; everything downstream bf16",
+                           "frames_per_step_rank0": frames, "t_max_rank0": tmax,
+                           "sharding": f"one pool of {B_PER_GPU * world} utterances dealt by sharding.shard_by_length "
+                                       f"over {world} rank(s), no data-path collective",
                            "l2": "working set per step (>1 GB of activations) exceeds the 126 MB L2; no explicit flush"},
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(text_h.numel() * 8 + mask_h.numel()),
-                        "d2h_bytes_per_step": int(out_h[0].numel() * 4), "ms_per_step": e2e_ms / args.steps},
-                "gpu_launches": launches, "clocks": sampler.summary(),
+                        "d2h_bytes_per_step": int(B_PER_GPU * tmax * hp.mel_dim * 4), "ms_per_step": e2e_ms / args.steps},
+                "gpu_launches": launches, "launches_per_step": launches / args.steps, "clocks": clocks,
                 # dominant kernel = largest share of the step (profiles/): the decoder attention
-                "roofline": roofs[1], "kernel_rooflines": roofs, "cpu_baseline": cpu}
+                "roofline": by_key["attention"], "kernel_rooflines": roofs,
+                ("bf16_duration_chain" if other == "bf16" else "fp32_duration_chain"):
+                    {"value": frames_o * n_o / (other_ms * 1e-3), "unit": UNIT, "ms_per_step": other_ms / n_o, "steps": n_o,
+                     "note": "same step with model.duration_precision = %r" % other},
+                "torch_eager_b200": eager, "latency_b1": lat, "train": trn, "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -502,6 +718,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-eager-baseline", action="store_true", help="skip the torch_eager_b200 sub-record")
+    ap.add_argument("--no-train-record", action="store_true", help="skip the training-step sub-record")
+    ap.add_argument("--duration-precision", default="fp32", choices=["fp32", "bf16"],
+                    help="fp32 (default): durations equal the fp32 reference's; bf16: the faster chain (SURVEY F9)")
     ap.add_argument("--workload", default="infer", choices=["infer", "train"])
     ap.add_argument("--train-batch", type=int, default=32)
     ap.add_argument("--overlap", action="store_true",

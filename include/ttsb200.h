@@ -28,6 +28,7 @@ typedef void* ttsb200_stream_t; /* cudaStream_t */
 #define TTSB200_ERR_CUDA (-2)
 #define TTSB200_ERR_TMAP (-3)
 
+#define TTSB200_ABI_VERSION 200 /* round 2: gemm_args.tile_map/tile_count, the fp32-accurate chain, dropout */
 int ttsb200_version(void);
 const char* ttsb200_last_error_string(void);
 

@@ -181,7 +181,9 @@ def test_c_abi_exports_every_declared_symbol():
     for name in declared:
         assert hasattr(dll, name), name
     dll.ttsb200_version.restype = ctypes.c_int
-    assert dll.ttsb200_version() >= 100
+    # the binding refuses a library built from other struct layouts / signatures (lib.load checks the same)
+    assert dll.ttsb200_version() == lib.ABI_VERSION
+    assert f"#define TTSB200_ABI_VERSION {lib.ABI_VERSION}" in header
 
 
 @pytest.mark.skipif(not ref_loader.reference_available(), reason="reference checkout not present (GPU box)")

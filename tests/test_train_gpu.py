@@ -245,3 +245,101 @@ def test_dropin_autograd_mode_matches_trainer():
     with torch.no_grad():
         ev = model(text[:1], src_mask[:1])
     assert ev[1].shape[-1] == hp.mel_dim
+
+
+def test_trainer_state_dict_roundtrip_resumes_bit_identically():
+    """train_fastspeech2.py:323,444 saves optimizer.state_dict() and resumes `step` from it: a Trainer restored from
+    model.state_dict() + Trainer.state_dict() must take the SAME next step as the one that kept running, and the
+    exported state must load into a real torch.optim.Adam over the same parameters."""
+    from transformer_tts_b200 import synth
+    from transformer_tts_b200.training import Trainer
+
+    hp, sd, model = build()
+    text, pos, _ = synth.synth_text_batch(3, 24, ragged=True, seed=5)
+    dur, pos_mel, f0, en = synth.synth_targets(pos, seed=5, max_dur=8)
+    mel = synth.synth_mel(pos_mel, hp.mel_dim, seed=5)
+    c = lambda t: t.cuda()  # noqa: E731
+    batch = dict(text=c(text), src_mask=c((pos != 0).unsqueeze(-2)), mel_mask=c((pos_mel != 0).unsqueeze(-2)),
+                 alignment=c(dur), f0=c(f0), energy=c(en), mel=c(mel))
+    tr = Trainer(model, optimizer="adam")
+    for _ in range(2):
+        tr.train_step(**batch)
+    msd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    osd = tr.state_dict()
+    assert set(osd["state"][0]) == {"step", "exp_avg", "exp_avg_sq"} and len(osd["state"]) == len(tr.params)
+    assert int(osd["state"][0]["step"]) == 2 and osd["param_groups"][0]["params"] == list(range(len(tr.params)))
+    tr.train_step(**batch)  # the run that kept going
+    want = {k: v.detach().clone() for k, v in model.state_dict().items()}
+
+    _, _, model2 = build(seed_sd=1)
+    model2.load_state_dict(msd)
+    tr2 = Trainer(model2, optimizer="adam")
+    tr2.load_state_dict(osd)
+    assert tr2.step_count == 2
+    tr2.train_step(**batch)
+    torch.cuda.synchronize()
+    for k, v in model2.state_dict().items():
+        if v.is_floating_point() and "running_" not in k:
+            # identical kernels and inputs; only the order of fp32 atomics in the weight gradients differs run to run
+            assert torch.allclose(v, want[k], rtol=0, atol=2e-6), k
+    # the exported layout is torch.optim.Adam's
+    _, _, model3 = build()
+    opt = torch.optim.Adam(model3.parameters(), lr=1e-3, betas=(0.9, 0.98), eps=1e-9)
+    opt.load_state_dict({"state": osd["state"], "param_groups": [dict(opt.state_dict()["param_groups"][0])]})
+    assert int(opt.state_dict()["state"][0]["step"]) == 2
+
+
+def test_reference_training_call_signature_runs_unchanged():
+    """The exact call of train_fastspeech2.py:167 on the exact batch tuple `collate_fn` returns
+    (datasets_fastspeech2.py:521-616): `accent`, `spkr_emb`, `fix_mask=hp.fix_mask` (None), `temperature` (None) and
+    `hop_size` — a Python list of None when hp.use_hop is off — are all passed on every step.  The model is built with
+    the kwargs of train_fastspeech2.py:381-389.  One optimizer step must run and the loss must be finite."""
+    import torch.nn as nn
+
+    from transformer_tts_b200 import data, synth
+    from transformer_tts_b200.Models.fastspeech2 import FastSpeech2
+
+    hp = synth.make_hp(dropout=0.0, dropout_variance_adaptor=0.0, fix_mask=None, use_hop=False)
+    model = FastSpeech2(hp=hp, src_vocab=hp.vocab_size, trg_vocab=hp.mel_dim, d_model_encoder=hp.d_model_encoder,
+                        N_e=hp.n_layer_encoder, n_head_encoder=hp.n_head_encoder,
+                        ff_conv_kernel_size_encoder=hp.ff_conv_kernel_size_encoder,
+                        concat_after_encoder=hp.concat_after_encoder, d_model_decoder=hp.d_model_decoder,
+                        N_d=hp.n_layer_decoder, n_head_decoder=hp.n_head_decoder,
+                        ff_conv_kernel_size_decoder=hp.ff_conv_kernel_size_decoder,
+                        concat_after_decoder=hp.concat_after_decoder, dropout_variance_adaptor=hp.dropout_variance_adaptor,
+                        reduction_rate=hp.reduction_rate, dropout=hp.dropout, dropout_postnet=0.0, n_bins=hp.nbins,
+                        f0_min=hp.f0_min, f0_max=hp.f0_max, energy_min=hp.energy_min, energy_max=hp.energy_max,
+                        pitch_pred=hp.pitch_pred, energy_pred=hp.energy_pred, accent_emb=hp.accent_emb,
+                        output_type=hp.output_type, num_group=hp.num_group, multi_speaker=hp.is_multi_speaker,
+                        spk_emb_dim=hp.spk_emb_dim, spk_emb_architecture=hp.spk_emb_architecture)
+    model.load_state_dict(synth.synth_state_dict(hp))
+    model = model.cuda().train()
+    # item dicts shaped like TrainDatasets.__getitem__'s through the package's collate_fn (bit-exact against the
+    # reference's own, tests/test_data.py)
+    from oracle import make_golden_data as MG
+
+    batch = data.collate_fn(MG.synth_items(n=3, seed=11))
+    (text, mel, pos_text, pos_mel, text_lengths, mel_lengths, stop_token, spk_emb, f0, energy, alignment, accent, gender,
+     spk_emb_postprocess, mel_name, hop_size) = batch
+    assert isinstance(hop_size, list) and all(h is None for h in hop_size)
+    text, mel, pos_text, pos_mel, f0, energy, alignment = (t.cuda() for t in (text, mel, pos_text, pos_mel, f0, energy,
+                                                                               alignment))
+    src_mask, trg_mask = data.create_masks(pos_text, pos_mel)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3, betas=(0.9, 0.98), eps=1e-9)
+    opt.zero_grad()
+    out = model(text, src_mask, trg_mask, alignment, f0, energy, accent, spkr_emb=spk_emb, fix_mask=hp.fix_mask,
+                temperature=None, hop_size=hop_size)  # train_fastspeech2.py:167, verbatim
+    (outputs_prenet, outputs_postnet, log_d_prediction, p_prediction, e_prediction, variance_adaptor_output,
+     text_dur_predicted, attn_enc, attn_dec_dec, _, _, _, sq_vae_loss, sq_vae_perplexity) = out
+    assert variance_adaptor_output.dtype == torch.float32 and text_dur_predicted.dtype == torch.float32
+    loss = nn.L1Loss()(outputs_prenet, mel) + nn.L1Loss()(outputs_postnet, mel)
+    loss = loss + nn.L1Loss()(p_prediction, f0) + nn.L1Loss()(e_prediction, energy)
+    loss = loss + nn.L1Loss()(log_d_prediction, torch.log(alignment.float() + 1))
+    loss.backward()
+    torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
+    opt.step()
+    assert torch.isfinite(loss).item()
+    model.eval()
+    with torch.no_grad():
+        ev = model(text[:1], src_mask[:1], hop_size=[None], accent=accent, spkr_emb=spk_emb)  # test_fastspeech2.py:169-171
+    assert ev[5].dtype == torch.float32 and torch.isfinite(ev[1]).all()

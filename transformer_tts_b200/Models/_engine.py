@@ -146,7 +146,7 @@ RAGGED_TILES = True
 
 
 def run_fft_block(t: dict, heads: int, x: torch.Tensor, xn: torch.Tensor, mask_u8: torch.Tensor,
-                  kv_len: torch.Tensor, next_ln, want_norm_f32: bool = False, tile_map=None):
+                  kv_len: torch.Tensor, next_ln, want_norm_f32: bool = False, tile_map=None, zero_dropped=False):
     """x: fp32 residual stream (B,T,D); xn = norm_1(x) in bf16.  Returns (x', LN_next(x') bf16[, fp32]).
     tile_map (k=1 blocks only): rows of unlisted 128-row tiles are neither read nor written."""
     B, T, D = x.shape
@@ -183,7 +183,8 @@ def run_fft_block(t: dict, heads: int, x: torch.Tensor, xn: torch.Tensor, mask_u
     h = torch.empty((B, T, 4 * D), device=dev, dtype=torch.bfloat16)
     lib.conv_gemm(yn, t["w1"], t["b1"], taps=k, pad_left=k // 2, block_n=256, act=lib.ACT_RELU, out_bf16=h,
                   tile_map=tile_map)  # modules.py:83
-    z, zn = run_ffn2(t, h, yn, y, next_ln, zn32=zn32, tile_map=tile_map)  # modules.py:84-87 + layers.py:40 + next norm
+    z, zn = run_ffn2(t, h, yn, y, next_ln, zn32=zn32, tile_map=tile_map,
+                     zero_dropped=zero_dropped)  # modules.py:84-87 + layers.py:40 + next norm
     return z, zn, zn32
 
 
@@ -208,7 +209,7 @@ SHORT_BATCH_TILES = 74
 
 
 def run_ffn2(t: dict, h: torch.Tensor, yn: torch.Tensor, y: torch.Tensor, next_ln, zn32=None, pre_f32=None,
-             out=None, tile_map=None):
+             out=None, tile_map=None, zero_dropped=False):
     """z = y + LN_ff(conv2(h) + b2 + yn); zn = LN_next(z).  Returns (z fp32, zn bf16) (written into `out` if given)."""
     B, T, D = y.shape
     dev = y.device
@@ -217,7 +218,9 @@ def run_ffn2(t: dict, h: torch.Tensor, yn: torch.Tensor, y: torch.Tensor, next_l
         z, zn = out
     else:
         z = torch.empty((B, T, D), device=dev, dtype=torch.float32)
-        zn = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
+        # rows of dropped (padding-only) tiles are never written: the stack's final output is defined (zero) there
+        zn = (torch.zeros if (tile_map is not None and zero_dropped) else torch.empty)((B, T, D), device=dev,
+                                                                                       dtype=torch.bfloat16)
     tiles = B * ((T + 127) // 128)
     if tiles <= SHORT_BATCH_TILES and D == 384 and tile_map is None:
         u = torch.empty((B, T, D), device=dev, dtype=torch.float32)

@@ -97,7 +97,7 @@ class Encoder(nn.Module):
                 attns.append(lib.attention_probs(qkv, mask_u8, self.heads))
             next_ln = t["norm"] if last else caches[i + 1]["ln1"]
             x, xn, xn32 = E.run_fft_block(lc, self.heads, x, xn, mask_u8, kv_len, next_ln,
-                                          want_norm_f32=(last and want_f32), tile_map=tile_map)
+                                          want_norm_f32=(last and want_f32), tile_map=tile_map, zero_dropped=last)
         if self.N == 0 and want_f32:
             xn32 = xn.float()
         return xn, xn32, (torch.stack(attns, 1) if return_attn else None)

@@ -76,6 +76,7 @@ class FastSpeech2(nn.Module):
         # durations land on the other side of a .5 boundary).  Teacher-forced calls always take the bf16
         # chain: there log_d is only an output.
         self.duration_precision = "fp32"
+        self.aux_outputs_fp32 = True   # tuple slots 5 / 6 in the reference's dtype (see _aux_f32)
         self.return_attn = False   # materialise the (B,N,H,T,T) maps of slots 7/8 (parity tests only)
         self.last_aux = None       # integer by-products of the last forward (durations, frame indices, ...)
 
@@ -83,19 +84,24 @@ class FastSpeech2(nn.Module):
                 spkr_emb=None, fix_mask=None, spkr_emb_post=None, temperature=None, pitch_perturbation=False,
                 duration_perturbation=False, hop_size=None):
         E.require_cuda(src, "FastSpeech2")
+        # Arguments the reference itself ignores in this configuration are ignored here too (they are passed by
+        # train_fastspeech2.py:167 on every call): `hop_size` is read only under hp.use_hop (fastspeech2.py:168-172;
+        # collate_fn hands over a list of None otherwise), `temperature` only under hp.use_sq_vae (:142-166), `accent`
+        # only by an Encoder built with accent_emb (encoder.py:106-108), `spkr_emb` only by multi-speaker layers
+        # (layers.py:36-39) and the 'middle' speaker projection (:138-140), `spkr_emb_post` only by the debug
+        # post-model (:201-236) — all of which the constructor rejects.
+        if fix_mask is not None:
+            raise NotImplementedError("fix_mask (band-limited attention, fastspeech2.py:124-135) is out of scope")
+        if pitch_perturbation or duration_perturbation:
+            assert not self.training, "fastspeech2.py:120"
+            raise NotImplementedError("pitch / duration perturbation (varianceadaptor.py:76-81,103-107) is out of scope")
         if self.training:
-            if fix_mask is not None or accent is not None or spkr_emb is not None or spkr_emb_post is not None \
-                    or temperature is not None or hop_size is not None or pitch_perturbation or duration_perturbation:
-                raise NotImplementedError("fix_mask / accent / speaker / temperature / hop / perturbation inputs are "
-                                          "out of scope")
             from ..training import autograd_forward
 
             mel_pre, mel_post, log_d, p, e, va_x, text_dur = autograd_forward(self, src, src_mask, mel_mask, d_target,
                                                                               p_target, e_target)
-            return (mel_pre, mel_post, log_d, p, e, va_x, text_dur, None, None, None, None, None, None, None)
-        if fix_mask is not None or accent is not None or spkr_emb is not None or spkr_emb_post is not None \
-                or temperature is not None or hop_size is not None or pitch_perturbation or duration_perturbation:
-            raise NotImplementedError("fix_mask / accent / speaker / temperature / hop / perturbation inputs are out of scope")
+            return (mel_pre, mel_post, log_d, p, e, self._aux_f32(va_x), self._aux_f32(text_dur), None, None, None,
+                    None, None, None, None)
         B, L = src.shape
         dev = src.device
         sm = E.mask_to_u8(src_mask, B, L, dev)
@@ -124,6 +130,22 @@ class FastSpeech2(nn.Module):
         mel_pre, mel_post = self.postnet.run(d_bf, tile_map=tile_map)  # :197
         self.last_aux = dict(dur=va["dur"], mel_len=va["mel_len"], frame_idx=va["frame_idx"], mel_pos=va["mel_pos"],
                              mel_mask=mel_u8, p_idx=va["p_idx"], e_idx=va["e_idx"], encoder_output=e_bf,
-                             decoder_output=d_bf)
-        return (mel_pre, mel_post, va["log_d"], va["p"], va["e"], va["x"], va["text_dur"], attn_enc, attn_dec,
-                None, None, None, None, None)  # fastspeech2.py:241
+                             decoder_output=d_bf, va_x=va["x"], text_dur=va["text_dur"])
+        return (mel_pre, mel_post, va["log_d"], va["p"], va["e"], self._aux_f32(va["x"]), self._aux_f32(va["text_dur"]),
+                attn_enc, attn_dec, None, None, None, None, None)  # fastspeech2.py:241
+
+    def _aux_f32(self, t):
+        """Slots 5 / 6 of the tuple (variance_adaptor_output, text_dur_predicted) are fp32 in the reference; the
+        kernels keep them in bf16.  No live caller reads them (train_fastspeech2.py:167, test_fastspeech2.py:169), so
+        `aux_outputs_fp32 = False` skips the two casts (216 MB of writes at cfg2)."""
+        return t.float() if self.aux_outputs_fp32 else t
+
+    def invalidate_caches(self) -> None:
+        """Drop every derived (bf16 / split / fused) weight copy.  The caches notice `load_state_dict`, optimizer steps
+        and any other in-place update that bumps `Tensor._version`; writes through `param.data` (EMA / averaging code)
+        do not bump it — call this after such an update."""
+        for m in self.modules():
+            for name in ("_ttsb_cache", "_ttsb_cache_x3"):
+                c = getattr(m, name, None)
+                if c is not None:
+                    c.sig = None

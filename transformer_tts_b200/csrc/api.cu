@@ -74,5 +74,7 @@ int make_tmap(CUtensorMap* out, CUtensorMapDataType dtype, const void* base, int
 
 }  // namespace ttsb
 
-extern "C" int ttsb200_version(void) { return 100; }
+// Bumped whenever a struct layout or an entry point's signature changes; lib.py refuses a library that reports
+// another value (a stale .so next to newer sources).
+extern "C" int ttsb200_version(void) { return TTSB200_ABI_VERSION; }
 extern "C" const char* ttsb200_last_error_string(void) { return ttsb::g_last_error; }

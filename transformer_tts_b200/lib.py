@@ -17,6 +17,8 @@ from . import _build
 EPI_AFFINE_ACT, EPI_RES_LN, EPI_FFN2, EPI_RELU_LN, EPI_RELU_LN_DOT = range(5)
 ACT_NONE, ACT_RELU, ACT_TANH, ACT_RELU_GRAD = range(4)
 
+ABI_VERSION = 200  # include/ttsb200.h TTSB200_ABI_VERSION: struct layouts / signatures this binding was written for
+
 LAUNCH_COUNT = 0  # kernels launched through this binding (bench.py reports it as gpu_launches)
 
 
@@ -108,10 +110,18 @@ def load() -> C.CDLL:
     if _build.is_stale():
         try:
             _build.build()
-        except Exception as e:  # no nvcc on the GPU box is fine as long as a built .so travelled
+        except Exception as e:
+            # A snapshot copied to the GPU box may carry a fresh .so with older-looking mtimes and no nvcc: that is
+            # fine as long as the library reports the ABI this binding expects (checked below); a MISSING library is
+            # always an error.
             if not path.exists():
                 raise RuntimeError(f"libttsb200.so is missing and cannot be built: {e}") from e
     lib = C.CDLL(str(path))
+    lib.ttsb200_version.restype = C.c_int
+    got = lib.ttsb200_version()
+    if got != ABI_VERSION:
+        raise RuntimeError(f"{path} reports ABI version {got}, this binding needs {ABI_VERSION}: the library is stale "
+                           "(rebuild with `python -m transformer_tts_b200._build --force`)")
     for name, (argtypes, restype) in _SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError if the symbol is missing: fail loudly
         fn.argtypes = argtypes

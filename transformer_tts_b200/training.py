@@ -550,6 +550,54 @@ class Trainer:
         out["lr"] = self.optimizer_step()
         return out
 
+    # ------------------------------------------------------------------------------------------
+    # checkpointing: the reference saves optimizer.state_dict() and resumes `step` from it
+    # (train_fastspeech2.py:323,444).  Same layout as torch.optim.Adam / radam.RAdam: per-parameter
+    # {'step', 'exp_avg', 'exp_avg_sq'} in model.parameters() order, views of the flat buffers cloned out.
+    # ------------------------------------------------------------------------------------------
+    def state_dict(self) -> dict:
+        if not self.flatten:
+            raise RuntimeError("state_dict() needs flatten=True; in autograd mode the caller's optimizer owns the state")
+        state = {}
+        for i, (p, (o, k)) in enumerate(zip(self.params, self.offsets)):
+            state[i] = {"step": torch.tensor(float(self.step_count)),
+                        "exp_avg": self.flat_m[o:o + k].view(p.shape).clone(),
+                        "exp_avg_sq": self.flat_v[o:o + k].view(p.shape).clone()}
+        group = {"lr": self.lr() if self.step_count else (self.fixed_lr or self.lr_max), "betas": tuple(self.betas),
+                 "eps": self.eps, "weight_decay": 0, "amsgrad": False, "params": list(range(len(self.params)))}
+        return {"state": state if self.step_count else {}, "param_groups": [group],
+                "ttsb200": {"optimizer": self.optimizer, "step_count": self.step_count}}
+
+    def load_state_dict(self, sd: dict) -> None:
+        """Accepts what `state_dict()` wrote, or a torch.optim.Adam / radam.RAdam state_dict of the same model."""
+        if not self.flatten:
+            raise RuntimeError("load_state_dict() needs flatten=True")
+        state = sd.get("state", {})
+        if state and len(state) != len(self.params):
+            raise ValueError(f"optimizer state holds {len(state)} tensors, the model has {len(self.params)} parameters")
+        steps = set()
+        self.flat_m.zero_()
+        self.flat_v.zero_()
+        for i, (p, (o, k)) in enumerate(zip(self.params, self.offsets)):
+            st = state.get(i, state.get(str(i)))
+            if st is None:
+                continue
+            for name, flat in (("exp_avg", self.flat_m), ("exp_avg_sq", self.flat_v)):
+                t = st[name]
+                if tuple(t.shape) != tuple(p.shape):
+                    raise ValueError(f"optimizer state {i}.{name} has shape {tuple(t.shape)}, parameter {tuple(p.shape)}")
+                flat[o:o + k].copy_(t.reshape(-1).to(device=self.dev, dtype=torch.float32))
+            steps.add(int(float(st["step"])))
+        extra = sd.get("ttsb200", {})
+        if len(steps) > 1:
+            raise ValueError(f"per-parameter step counts differ ({sorted(steps)}): not a state of this training loop")
+        self.step_count = steps.pop() if steps else int(extra.get("step_count", 0))
+        g = sd.get("param_groups", [{}])[0]
+        if "betas" in g:
+            self.betas = tuple(g["betas"])
+        if "eps" in g:
+            self.eps = g["eps"]
+
     def broadcast_parameters(self, src: int = 0) -> None:
         """DDP's initial parameter broadcast, one collective over the flat buffer."""
         if self.world > 1:
