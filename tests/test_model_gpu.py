@@ -470,3 +470,49 @@ def test_ragged_tile_list_is_bit_identical_on_valid_frames(setup):
     m_tiles = (T + 127) // 128
     want = [b * m_tiles + j for b in range(ml.numel()) for j in range(min(m_tiles, (int(ml[b]) + 127) // 128))]
     assert int(count) == len(want) and tmap[:len(want)].tolist() == want
+
+
+def test_pre_length_regulator_graph_is_bit_identical_to_eager(setup):
+    """Free-running inference replays the stage before the LengthRegulator's host sync as a CUDA graph keyed by
+    (B, L, duration_precision): outputs must equal the eager launch sequence bit for bit, for new inputs written into
+    the captured buffers, after a weight reload (the graph is re-captured), and for both duration modes."""
+    from transformer_tts_b200 import synth
+
+    hp, sd, sd_gpu, model = setup
+    outs = {}
+    try:
+        for prec in ("fp32", "bf16"):
+            model.duration_precision = prec
+            for seed in (11, 12):
+                text, pos, _ = synth.synth_text_batch(3, 40, ragged=True, seed=seed)
+                text, pos = text.cuda(), pos.cuda()
+                m = (pos != 0).unsqueeze(-2)
+                for graphs in (True, False, True):
+                    model.use_cuda_graphs = graphs
+                    with torch.no_grad():
+                        o = model(text, m)
+                    k = (prec, seed, graphs)
+                    cur = (o[0].clone(), o[1].clone(), o[2].clone(), model.last_aux["dur"].clone())
+                    if k in outs:  # the second graph run of the same input: a replay
+                        assert all(torch.equal(a, b) for a, b in zip(outs[k], cur))
+                    outs[k] = cur
+                for a, b in zip(outs[(prec, seed, True)], outs[(prec, seed, False)]):
+                    assert torch.equal(a, b), f"graph replay differs from eager ({prec}, seed {seed})"
+            assert not torch.equal(outs[(prec, 11, True)][2], outs[(prec, 12, True)][2])
+        # weights change -> the captured graph (which points at the old derived weights) must not be replayed
+        model.duration_precision = "fp32"
+        model.use_cuda_graphs = True
+        text, pos, _ = synth.synth_text_batch(3, 40, ragged=True, seed=11)
+        text, pos = text.cuda(), pos.cuda()
+        m = (pos != 0).unsqueeze(-2)
+        model.load_state_dict(synth.synth_state_dict(hp, seed=1))
+        with torch.no_grad():
+            o1 = model(text, m)[2].clone()
+        model.load_state_dict(sd)
+        with torch.no_grad():
+            o2 = model(text, m)[2].clone()
+        assert not torch.equal(o1, o2) and torch.equal(o2, outs[("fp32", 11, True)][2])
+    finally:
+        model.duration_precision = "fp32"
+        model.use_cuda_graphs = True
+        model.load_state_dict(sd)

@@ -77,6 +77,8 @@ class FastSpeech2(nn.Module):
         # chain: there log_d is only an output.
         self.duration_precision = "fp32"
         self.aux_outputs_fp32 = True   # tuple slots 5 / 6 in the reference's dtype (see _aux_f32)
+        self.use_cuda_graphs = True    # free-running inference: the pre-LengthRegulator stage replays a CUDA graph
+        self._graphs = {}
         self.return_attn = False   # materialise the (B,N,H,T,T) maps of slots 7/8 (parity tests only)
         self.last_aux = None       # integer by-products of the last forward (durations, frame indices, ...)
 
@@ -105,18 +107,18 @@ class FastSpeech2(nn.Module):
         B, L = src.shape
         dev = src.device
         sm = E.mask_to_u8(src_mask, B, L, dev)
-        kv_src = lib.mask_lengths(sm)
+        kv_src_fn = lambda: lib.mask_lengths(sm)  # noqa: E731
         if self.duration_precision not in ("fp32", "bf16"):
             raise ValueError(f"duration_precision must be 'fp32' or 'bf16', got {self.duration_precision!r}")
-        log_d = None
-        if d_target is None and self.duration_precision == "fp32" and not self.return_attn and self.encoder.N > 0:
-            e_bf, e_split, _ = E.run_encoder_precise(self.encoder, src, sm, kv_src)  # :137, to fp32 accuracy
-            log_d = E.run_predictor_precise(self.variance_adaptor.duration_predictor, e_split, sm)  # varianceadaptor.py:69
-            attn_enc = None
-        else:
-            e_bf, _, attn_enc = self.encoder.run(src, sm, kv_src, want_f32=False, return_attn=self.return_attn)  # :137
         mm = None if mel_mask is None else E.mask_to_u8(mel_mask, B, mel_mask.shape[-1], dev)
-        va = self.variance_adaptor.run(e_bf, sm, mm, d_target, p_target, e_target, want_aux=True, log_d=log_d)  # :176-181
+        attn_enc = None
+        if d_target is None and not self.return_attn and self.encoder.N > 0:
+            # free-running: encoder -> duration predictor -> rounding -> prefix sum, up to the one host sync (Tmax)
+            e_bf, pre = self._pre_lr(src.contiguous(), sm)
+            va = self.variance_adaptor.run(e_bf, sm, mm, None, p_target, e_target, want_aux=True, pre=pre)  # :176-181
+        else:
+            e_bf, _, attn_enc = self.encoder.run(src, sm, kv_src_fn(), want_f32=False, return_attn=self.return_attn)  # :137
+            va = self.variance_adaptor.run(e_bf, sm, mm, d_target, p_target, e_target, want_aux=True)  # :176-181
         mel_u8 = va["mel_mask"]
         kv_mel = lib.mask_lengths(mel_u8)
         tile_map = None
@@ -134,6 +136,54 @@ class FastSpeech2(nn.Module):
         return (mel_pre, mel_post, va["log_d"], va["p"], va["e"], self._aux_f32(va["x"]), self._aux_f32(va["text_dur"]),
                 attn_enc, attn_dec, None, None, None, None, None)  # fastspeech2.py:241
 
+    # ------------------------------------------------------------------------------------------
+    # Everything before the LengthRegulator's host sync has shapes that depend on (B, L) only, so it is captured ONCE
+    # per (B, L, duration_precision) as a CUDA graph and replayed: ~50 kernel launches (fp32-accurate chain) become
+    # one, without launch gaps on the device.  Replays are bit-identical to the eager sequence (same kernels, same
+    # operands; the TMA descriptors are kernel parameters and live in the graph).
+    # ------------------------------------------------------------------------------------------
+    def _pre_lr_eager(self, src, sm):
+        kv_src = lib.mask_lengths(sm)
+        log_d = None
+        if self.duration_precision == "fp32":
+            e_bf, e_split, _ = E.run_encoder_precise(self.encoder, src, sm, kv_src)  # :137, to fp32 accuracy
+            log_d = E.run_predictor_precise(self.variance_adaptor.duration_predictor, e_split, sm)  # varianceadaptor.py:69
+        else:
+            e_bf, _, _ = self.encoder.run(src, sm, kv_src, want_f32=False)  # :137
+        return e_bf, self.variance_adaptor.run_pre(e_bf, sm, log_d)
+
+    def _pre_lr_params(self):
+        ps = list(self.encoder.parameters()) + list(self.variance_adaptor.duration_predictor.parameters())
+        return ps
+
+    def _pre_lr(self, src, sm):
+        if not self.use_cuda_graphs or torch.cuda.is_current_stream_capturing():
+            return self._pre_lr_eager(src, sm)
+        B, L = src.shape
+        key = (B, L, self.duration_precision, src.device.index)
+        sig = E._sig(self._pre_lr_params())
+        ent = self._graphs.get(key)
+        if ent is None or ent["sig"] != sig:
+            static_src, static_sm = src.clone(), sm.clone()
+            self._pre_lr_eager(static_src, static_sm)  # builds the derived-weight caches, first-call kernel attributes
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            n0 = lib.LAUNCH_COUNT
+            with torch.cuda.graph(g):
+                outs = self._pre_lr_eager(static_src, static_sm)
+            n_kernels = lib.LAUNCH_COUNT - n0  # kernels of ours inside one replay (bench.py's gpu_launches)
+            if len(self._graphs) >= 8:
+                self._graphs.pop(next(iter(self._graphs)))
+            ent = dict(sig=sig, graph=g, src=static_src, sm=static_sm, outs=outs, n=n_kernels)
+            self._graphs[key] = ent
+        ent["src"].copy_(src)
+        ent["sm"].copy_(sm)
+        ent["graph"].replay()
+        lib._count(ent["n"])
+        e_bf, (log_d, dur, cum, mel_len, tmax) = ent["outs"]
+        # the graph's output buffers are overwritten by the next replay: what leaves this call is copied out
+        return e_bf.clone(), (log_d.clone(), dur.clone(), cum, mel_len.clone(), tmax)
+
     def _aux_f32(self, t):
         """Slots 5 / 6 of the tuple (variance_adaptor_output, text_dur_predicted) are fp32 in the reference; the
         kernels keep them in bf16.  No live caller reads them (train_fastspeech2.py:167, test_fastspeech2.py:169), so
@@ -149,3 +199,4 @@ class FastSpeech2(nn.Module):
                 c = getattr(m, name, None)
                 if c is not None:
                     c.sig = None
+        self._graphs.clear()

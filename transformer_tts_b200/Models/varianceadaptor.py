@@ -82,13 +82,16 @@ class LengthRegulator(nn.Module):
         self.use_lstm = use_lstm
 
     @staticmethod
-    def run(x_bf16, dur_i32, max_length=None, want_aux=True):
-        """Returns (expanded bf16 (B,Tmax,D), frame_idx, mel_pos, mel_mask u8, mel_len i32, cum)."""
-        cum, mel_len = lib.lr_scan(dur_i32)
+    def run(x_bf16, dur_i32, max_length=None, want_aux=True, scan=None):
+        """Returns (expanded bf16 (B,Tmax,D), frame_idx, mel_pos, mel_mask u8, mel_len i32, cum).
+        scan: (cum, mel_len, max(mel_len) as a device scalar) when the caller already ran the prefix sum."""
+        cum, mel_len, tmax_dev = scan if scan is not None else (*lib.lr_scan(dur_i32), None)
         if max_length:
             Tmax = int(max_length)
         else:
-            Tmax = int(mel_len.max().item())  # the one host sync of free-running inference (varianceadaptor.py:254)
+            if tmax_dev is None:
+                tmax_dev = mel_len.max()
+            Tmax = int(tmax_dev.item())  # the one host sync of free-running inference (varianceadaptor.py:254)
             Tmax = max(Tmax, 1)
         out, fidx, mel_pos, mel_mask = lib.lr_expand(x_bf16, cum, mel_len, Tmax, want_aux=want_aux)
         return out, fidx, mel_pos, mel_mask, mel_len, cum
@@ -145,20 +148,27 @@ class VarianceAdaptor(nn.Module):
         return c.t
 
     def run(self, x_bf16, src_mask_u8, mel_mask_u8=None, duration_target=None, pitch_target=None,
-            energy_target=None, max_len=None, want_aux=True, log_d=None):
+            energy_target=None, max_len=None, want_aux=True, log_d=None, pre=None):
         """Kernel sequence of varianceadaptor.py:66-129 on bf16 activations.  Returns a dict.
-        log_d: the duration predictor's output when the caller already evaluated it (fp32-accurate chain)."""
+        log_d: the duration predictor's output when the caller already evaluated it (fp32-accurate chain).
+        pre: (log_d, dur, cum, mel_len, max mel_len) from `run_pre` (free-running: everything before the one host sync)."""
         dev = x_bf16.device
-        if log_d is None:
-            log_d = self.duration_predictor.run(x_bf16, src_mask_u8)  # :69
-        if duration_target is not None:
-            dur = torch.clamp(duration_target, min=0).to(torch.int32).contiguous()
-            if mel_mask_u8 is not None:
-                max_len = mel_mask_u8.shape[1]  # :71-72
-        else:
-            dur = lib.round_durations(log_d)  # :75
+        scan = None
+        if pre is not None:
+            log_d, dur, cum, mel_len, tmax_dev = pre
+            scan = (cum, mel_len, tmax_dev)
             max_len = None
-        xe, fidx, mel_pos, lr_mask, mel_len, _ = self.length_regulator.run(x_bf16, dur, max_len, want_aux)  # :73/:82
+        else:
+            if log_d is None:
+                log_d = self.duration_predictor.run(x_bf16, src_mask_u8)  # :69
+            if duration_target is not None:
+                dur = torch.clamp(duration_target, min=0).to(torch.int32).contiguous()
+                if mel_mask_u8 is not None:
+                    max_len = mel_mask_u8.shape[1]  # :71-72
+            else:
+                dur = lib.round_durations(log_d)  # :75
+                max_len = None
+        xe, fidx, mel_pos, lr_mask, mel_len, _ = self.length_regulator.run(x_bf16, dur, max_len, want_aux, scan=scan)  # :73/:82
         if duration_target is None or mel_mask_u8 is None:
             mel_mask_u8 = lr_mask  # :84 (the kernel applies the `arange <= mel_pos` rule)
         p = self.pitch_predictor.run(xe, mel_mask_u8)  # :96
@@ -171,6 +181,15 @@ class VarianceAdaptor(nn.Module):
                                                  want_idx=want_aux)  # :100-126
         return dict(x=out, log_d=log_d, p=p, e=e, mel_pos=mel_pos, mel_mask=mel_mask_u8, text_dur=xe,
                     frame_idx=fidx, mel_len=mel_len, dur=dur, p_idx=p_idx, e_idx=e_idx)
+
+    def run_pre(self, x_bf16, src_mask_u8, log_d=None):
+        """Free-running: everything between the encoder and the host read of Tmax — duration predictor (:69) unless
+        `log_d` is given, rounding (:75), the LengthRegulator's prefix sum and the batch maximum.  No host sync."""
+        if log_d is None:
+            log_d = self.duration_predictor.run(x_bf16, src_mask_u8)
+        dur = lib.round_durations(log_d)
+        cum, mel_len = lib.lr_scan(dur)
+        return log_d, dur, cum, mel_len, mel_len.max()
 
     def forward(self, x, src_mask, mel_mask=None, duration_target=None, pitch_target=None, energy_target=None,
                 max_len=None, p_scheduled_sampling=0.0, pitch_perturbation=False, duration_perturbation=False):
