@@ -208,15 +208,18 @@ int ttsb200_attention_x3(const void* qkv_split, const uint8_t* mask, const int32
                          int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t stream);
 
 /* fp32 row operations of the chain (one warp per row, D = 256 or 384):
- *   s = a (+ b0 fp32 | + b0_split hi+lo);  s_out = s (optional);  t = LayerNorm(s; g1, b1)
+ *   s = a (+ b0 fp32 | + b0_bf16 | + b0_split hi+lo);  s_out = s (optional);  t = LayerNorm(s; g1, b1)
+ *   training with dropout (DROPOUT below): b0 := b0 * m(site_b) before the add, s := s * m(site_s) before s_out and
+ *   the LayerNorm, t := t * m(site_t) after it
  *   mode 0 ADD_LN   (Models/layers.py:31,33-35):                 out = t
  *   mode 1 FFN_TAIL (Models/modules.py:85-87, layers.py:40,31):  z = c + t; z_out = z; out = LayerNorm(z; g2, b2)
  *   mode 2 LN_DOT   (Models/varianceadaptor.py:222-229):         out_row = row_mask ? dot(t, dot_w) + dot_b : 0
  * out goes to any of out_split (fp16 (rows,2D)), out_bf16, out_f32. */
-int ttsb200_xrow(int32_t mode, const float* a, const float* b0, const void* b0_split, const float* c,
-                 const float* g1, const float* b1, const float* g2, const float* b2, const float* dot_w,
+int ttsb200_xrow(int32_t mode, const float* a, const float* b0, const void* b0_bf16, const void* b0_split,
+                 const float* c, const float* g1, const float* b1, const float* g2, const float* b2, const float* dot_w,
                  const float* dot_b, const uint8_t* row_mask, float eps, float* s_out, float* z_out, void* out_split,
-                 void* out_bf16, float* out_f32, float* out_row, int64_t rows, int32_t D, ttsb200_stream_t stream);
+                 void* out_bf16, float* out_f32, float* out_row, int64_t rows, int32_t D, float drop_p,
+                 uint64_t drop_seed, int64_t site_b, int64_t site_s, int64_t site_t, ttsb200_stream_t stream);
 
 /* out_split fp16 (rows,2D) = split of x*scale, x fp32 (rows,D) (weight / activation staging). */
 int ttsb200_split_f16(const float* x, void* out_split, int64_t rows, int32_t D, float scale, ttsb200_stream_t stream);
@@ -257,6 +260,16 @@ int ttsb200_layernorm_bwd(const float* x, const float* gamma, const float* beta,
                           const uint8_t* row_mask, const float* add_f32, int32_t relu_gate, float* dx_f32,
                           void* dx_bf16, float* dgamma, float* dbeta, float* dvec, float* dscal,
                           int64_t rows, int32_t D, float eps, ttsb200_stream_t stream);
+/* The same with the dropout masks of the forward pass regenerated (see DROPOUT below): site_g >= 0: the LayerNorm
+ * OUTPUT was dropped (g := g * m, the head's dvec uses y * m); site_dx >= 0 with dx_mode 1: the LayerNorm INPUT was a
+ * dropout's output (dx := dx * m on both outputs), dx_mode 2: only dx_bf16 is masked (the copy that feeds the GEMM
+ * gradients of a dropped branch, Models/layers.py:33; dx_f32 continues down the residual path). */
+int ttsb200_layernorm_bwd_drop(const float* x, const float* gamma, const float* beta, const float* g_f32,
+                               const void* g_bf16, const float* g_row, const float* g_vec, const uint8_t* row_mask,
+                               const float* add_f32, int32_t relu_gate, float* dx_f32, void* dx_bf16, float* dgamma,
+                               float* dbeta, float* dvec, float* dscal, int64_t rows, int32_t D, float eps,
+                               float drop_p, uint64_t drop_seed, int64_t site_g, int64_t site_dx, int32_t dx_mode,
+                               ttsb200_stream_t stream);
 
 /* out[c] += sum_rows x[row*ld + c]  (bias gradients); x bf16 or fp32. */
 int ttsb200_colsum(const void* x, int32_t is_bf16, int64_t ld, float* out, int64_t rows, int32_t cols,
@@ -267,12 +280,38 @@ int ttsb200_colsum(const void* x, int32_t is_bf16, int64_t ld, float* out, int64
  * the caller (after the cross-rank all-reduce of SyncBatchNorm). */
 int ttsb200_bn_stats(const float* x, float* stats, int64_t rows, int32_t C, ttsb200_stream_t stream);
 int ttsb200_bn_tanh_fwd(const float* x, const float* mean_rstd, const float* gamma, const float* beta,
-                        void* h_bf16, int64_t rows, int32_t C, ttsb200_stream_t stream);
+                        void* h_bf16, int64_t rows, int32_t C, float drop_p, uint64_t drop_seed, int64_t drop_site,
+                        ttsb200_stream_t stream);
 /* apply == 0: red (2,384) += [sum dt | sum dt*xhat] with dt = dh*(1-h^2)  (= dbeta | dgamma);
  * apply == 1: dx bf16 = gamma*rstd*(dt - red[0]*inv_count - xhat*red[1]*inv_count). */
 int ttsb200_bn_tanh_bwd(const void* dh_bf16, const void* h_bf16, const float* x, const float* mean_rstd,
                         const float* gamma, float* red, void* dx_bf16, int64_t rows, int32_t C,
-                        float inv_count, int32_t apply, ttsb200_stream_t stream);
+                        float inv_count, int32_t apply, float drop_p, uint64_t drop_seed, int64_t drop_site,
+                        ttsb200_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * DROPOUT (training; the reference constructs the model with dropout 0.1 / 0.5, train_fastspeech2.py:381-389).
+ * Masks are counter-based: keep(i) = hash32(i, key(seed, site)) >= p * 2^32, kept elements scaled by 1 / (1 - p) as
+ * F.dropout does; `site` names one dropout call site of one module instance, i is the element's offset in the dropped
+ * tensor.  Forward kernels apply the mask, backward kernels regenerate it from the same (p, seed, site): no mask
+ * tensor exists.  drop_p == 0 or site < 0 disables a dropout point.  Call sites in the reference:
+ * Models/modules.py:18-19 (attention probabilities), :86 (FeedForward), :111 (PositionalEncoder),
+ * Models/layers.py:33,40 (dropout_1 / dropout_2), Models/varianceadaptor.py:219,222, Models/postnets.py:71-73.
+ * ---------------------------------------------------------------------------------------------- */
+/* dst[i] = src[i] * m(i); is_bf16 selects the element type; dst may alias src. */
+int ttsb200_dropout(const void* src, void* dst, int32_t is_bf16, int64_t n, float p, uint64_t seed, int64_t site,
+                    ttsb200_stream_t stream);
+/* out[i] = m(i) (0 or 1/(1-p)): the mask itself, for parity tests. */
+int ttsb200_dropout_mask(float* out, int64_t n, float p, uint64_t seed, int64_t site, ttsb200_stream_t stream);
+/* ttsb200_attention_fwd_lse / ttsb200_attention_bwd with dropout on the softmax probabilities (Models/modules.py:
+ * 18-19): ctx = (P * m) V; element index of m = ((b*H + h)*T + query)*T + key. */
+int ttsb200_attention_fwd_drop(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx, float* lse2,
+                               int32_t B, int32_t T, int32_t H, int32_t Dh, float drop_p, uint64_t drop_seed,
+                               int64_t drop_site, ttsb200_stream_t stream);
+int ttsb200_attention_bwd_drop(const void* qkv, const void* dctx, const uint8_t* mask, const int32_t* kv_info,
+                               const float* lse2, const float* delta, void* dqkv, int32_t B, int32_t T, int32_t H,
+                               int32_t Dh, float drop_p, uint64_t drop_seed, int64_t drop_site,
+                               ttsb200_stream_t stream);
 
 /* LengthRegulator backward (Models/varianceadaptor.py:167-177): dx[b,l,:] = add[b,l,:] + sum of g[b,t,:]
  * over the frames of phoneme l (cum from ttsb200_lr_scan, frames beyond Tmax were cropped). fp32. */

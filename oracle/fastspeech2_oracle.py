@@ -13,8 +13,9 @@ the build container, runs it on seeded inputs and commits the outputs under ``te
 when /root/reference is present).
 
 Deliberate scope: default hparams branch only — transformer encoder/decoder, no
-speaker/accent embeddings, no SQ-VAE/hop/debug/fix_mask, dropout 0 (attention dropout fires even in
-eval() in the reference, so parity is only defined at 0).
+speaker/accent embeddings, no SQ-VAE/hop/debug/fix_mask.  Dropout: 0 unless the caller supplies the masks
+(`drop` argument: every dropout call site of the reference is named, see `_drop`); attention dropout fires
+even in eval() in the reference, so inference parity is only defined at 0.
 """
 from __future__ import annotations
 
@@ -26,6 +27,17 @@ import torch
 import torch.nn.functional as F
 
 Tensor = torch.Tensor
+
+
+def _drop(drop, name: str, x: Tensor, channels_first: bool = False) -> Tensor:
+    """Training-mode dropout call site `name` of the reference (nn.Dropout / F.dropout).  The reference draws its masks
+    from torch's generator, which no other implementation can reproduce; for parity tests the caller supplies them:
+    `drop(name, shape) -> mask` (0 or 1/(1-p)) in the time-major (B,T,C) / (B,H,T,T) layout.  None = dropout 0."""
+    if drop is None:
+        return x
+    if channels_first:  # (B,C,T) activations, mask given as (B,T,C)
+        return x * drop(name, tuple(x.transpose(1, 2).shape)).transpose(1, 2)
+    return x * drop(name, tuple(x.shape))
 
 
 # --------------------------------------------------------------------------------------------------
@@ -47,32 +59,34 @@ def positional_table(d_model: int, max_seq_len: int = 5000) -> Tensor:
     return pe  # (max_seq_len, d_model); the reference keeps it as (1, max_seq_len, d_model)
 
 
-def positional_encoder(x: Tensor, alpha: Tensor) -> Tensor:
-    """modules.py:107-111 (dropout 0)."""
+def positional_encoder(x: Tensor, alpha: Tensor, drop=None, tag: str = "enc") -> Tensor:
+    """modules.py:107-111."""
     pe = positional_table(x.shape[-1])[: x.shape[1]].to(x.device)
-    return x + alpha * pe.unsqueeze(0)
+    return _drop(drop, f"{tag}.pe", x + alpha * pe.unsqueeze(0))
 
 
 # --------------------------------------------------------------------------------------------------
 # Models/modules.py:7-21  attention ; :43-70 MultiHeadAttention.forward
 # --------------------------------------------------------------------------------------------------
-def attention(q: Tensor, k: Tensor, v: Tensor, d_k: int, mask: Optional[Tensor]):
+def attention(q: Tensor, k: Tensor, v: Tensor, d_k: int, mask: Optional[Tensor], drop=None, site: str = ""):
     scores = torch.matmul(q, k.transpose(-2, -1)) / math.sqrt(d_k)  # :8-9
     if mask is not None:
         mask = mask.unsqueeze(1)  # :12
         scores = scores.masked_fill(mask == 0, -1e4)  # :14
     scores = torch.softmax(scores, dim=-1)  # :15/:17
-    return torch.matmul(scores, v), scores  # :20-21 (dropout 0)
+    scores = _drop(drop, site, scores)  # :18-19
+    return torch.matmul(scores, v), scores  # :20-21
 
 
-def multi_head_attention(sd: Dict[str, Tensor], pfx: str, x: Tensor, mask: Optional[Tensor], heads: int):
+def multi_head_attention(sd: Dict[str, Tensor], pfx: str, x: Tensor, mask: Optional[Tensor], heads: int, drop=None,
+                         site: str = ""):
     bs, _, d_model = x.shape
     d_k = d_model // heads
     k = F.linear(x, sd[pfx + "k_linear.weight"], sd[pfx + "k_linear.bias"]).view(bs, -1, heads, d_k)  # :49
     q = F.linear(x, sd[pfx + "q_linear.weight"], sd[pfx + "q_linear.bias"]).view(bs, -1, heads, d_k)  # :50
     v = F.linear(x, sd[pfx + "v_linear.weight"], sd[pfx + "v_linear.bias"]).view(bs, -1, heads, d_k)  # :51
     k, q, v = k.transpose(1, 2), q.transpose(1, 2), v.transpose(1, 2)  # :58-60
-    ctx, attn = attention(q, k, v, d_k, mask)  # :63
+    ctx, attn = attention(q, k, v, d_k, mask, drop, site)  # :63
     concat = ctx.transpose(1, 2).contiguous().view(bs, -1, d_model)  # :65
     return F.linear(concat, sd[pfx + "out.weight"], sd[pfx + "out.bias"]), attn  # :68
 
@@ -80,43 +94,45 @@ def multi_head_attention(sd: Dict[str, Tensor], pfx: str, x: Tensor, mask: Optio
 # --------------------------------------------------------------------------------------------------
 # Models/modules.py:72-88  FeedForward
 # --------------------------------------------------------------------------------------------------
-def feed_forward(sd: Dict[str, Tensor], pfx: str, x: Tensor) -> Tensor:
+def feed_forward(sd: Dict[str, Tensor], pfx: str, x: Tensor, drop=None, site: str = "") -> Tensor:
     k = sd[pfx + "f_1.weight"].shape[-1]
     res = x
     h = F.relu(F.conv1d(x.transpose(1, 2), sd[pfx + "f_1.weight"], sd[pfx + "f_1.bias"], padding=int(k / 2)))  # :83
     h = F.conv1d(h, sd[pfx + "f_2.weight"], sd[pfx + "f_2.bias"], padding=int(k / 2)).transpose(1, 2)  # :84
-    h = h + res  # :85
+    h = _drop(drop, site, h + res)  # :85-86
     return F.layer_norm(h, (h.shape[-1],), sd[pfx + "layer_norm.weight"], sd[pfx + "layer_norm.bias"])  # :87
 
 
 # --------------------------------------------------------------------------------------------------
 # Models/layers.py:29-41  EncoderLayer.forward
 # --------------------------------------------------------------------------------------------------
-def encoder_layer(sd, pfx: str, x: Tensor, mask: Optional[Tensor], heads: int):
+def encoder_layer(sd, pfx: str, x: Tensor, mask: Optional[Tensor], heads: int, drop=None, site: str = ""):
+    """`site` = "<enc|dec>.<layer index>": prefix of this block's four dropout call sites."""
     d = x.shape[-1]
     res = x
     xn = F.layer_norm(x, (d,), sd[pfx + "norm_1.weight"], sd[pfx + "norm_1.bias"])  # :31
-    out, attn = multi_head_attention(sd, pfx + "attn.", xn, mask, heads)  # :32
-    x = res + out  # :33
+    out, attn = multi_head_attention(sd, pfx + "attn.", xn, mask, heads, drop, site + ".attn")  # :32
+    x = res + _drop(drop, site + ".drop1", out)  # :33
     res = x
     xn = F.layer_norm(x, (d,), sd[pfx + "norm_2.weight"], sd[pfx + "norm_2.bias"])  # :35
-    x = res + feed_forward(sd, pfx + "ff.", xn)  # :40
+    x = res + _drop(drop, site + ".drop2", feed_forward(sd, pfx + "ff.", xn, drop, site + ".ff"))  # :40
     return x, attn
 
 
 # --------------------------------------------------------------------------------------------------
 # Models/encoder.py:83-112  Encoder.forward (embedding=True for the text encoder, Linear for the decoder)
 # --------------------------------------------------------------------------------------------------
-def encoder(sd, pfx: str, src: Tensor, mask: Optional[Tensor], n_layers: int, heads: int, return_attn=False):
+def encoder(sd, pfx: str, src: Tensor, mask: Optional[Tensor], n_layers: int, heads: int, return_attn=False, drop=None):
     w = sd[pfx + "embed.weight"]
     if src.dtype in (torch.int64, torch.int32):
         x = F.embedding(src, w, padding_idx=0)  # :55,:84 (padding_idx only affects gradients)
     else:
         x = F.linear(src, w, sd[pfx + "embed.bias"])  # :57,:84
-    x = positional_encoder(x, sd[pfx + "pe.alpha"])  # :94
+    tag = "enc" if pfx.startswith("encoder") else "dec"
+    x = positional_encoder(x, sd[pfx + "pe.alpha"], drop, tag)  # :94
     attns = []
     for i in range(n_layers):
-        x, attn = encoder_layer(sd, f"{pfx}layers.{i}.", x, mask, heads)  # :99
+        x, attn = encoder_layer(sd, f"{pfx}layers.{i}.", x, mask, heads, drop, f"{tag}.{i}")  # :99
         if return_attn:
             attns.append(attn)
     x = F.layer_norm(x, (x.shape[-1],), sd[pfx + "norm.weight"], sd[pfx + "norm.bias"])  # :112
@@ -126,14 +142,17 @@ def encoder(sd, pfx: str, src: Tensor, mask: Optional[Tensor], n_layers: int, he
 # --------------------------------------------------------------------------------------------------
 # Models/varianceadaptor.py:186-231  VariancePredictor
 # --------------------------------------------------------------------------------------------------
-def variance_predictor(sd, pfx: str, x: Tensor, mask: Optional[Tensor]) -> Tensor:
+def variance_predictor(sd, pfx: str, x: Tensor, mask: Optional[Tensor], drop=None) -> Tensor:
     fs = sd[pfx + "conv1.weight"].shape[0]
+    name = pfx.rstrip(".").split(".")[-1].replace("_predictor", "")  # duration | pitch | energy
     h = F.conv1d(x.transpose(1, 2), sd[pfx + "conv1.weight"], sd[pfx + "conv1.bias"], padding=1)  # :217
     h = F.relu(h).transpose(1, 2)  # :218
-    h = F.layer_norm(h, (fs,), sd[pfx + "layer_norm1.weight"], sd[pfx + "layer_norm1.bias"]).transpose(1, 2)  # :219
+    h = F.layer_norm(h, (fs,), sd[pfx + "layer_norm1.weight"], sd[pfx + "layer_norm1.bias"])  # :219
+    h = _drop(drop, name + ".drop1", h).transpose(1, 2)
     h = F.conv1d(h, sd[pfx + "conv2.weight"], sd[pfx + "conv2.bias"], padding=1)  # :220
     h = F.relu(h).transpose(1, 2)  # :221
     h = F.layer_norm(h, (fs,), sd[pfx + "layer_norm2.weight"], sd[pfx + "layer_norm2.bias"])  # :222
+    h = _drop(drop, name + ".drop2", h)
     out = F.linear(h, sd[pfx + "linear_layer.weight"], sd[pfx + "linear_layer.bias"]).squeeze(-1)  # :223-224
     if mask is not None:
         m = mask.squeeze(1) if mask.dim() == 3 else mask
@@ -191,9 +210,9 @@ def variance_bins(n_bins: int, f0_min: float, f0_max: float, energy_min: float, 
 # --------------------------------------------------------------------------------------------------
 # Models/varianceadaptor.py:66-129  VarianceAdaptor.forward
 # --------------------------------------------------------------------------------------------------
-def variance_adaptor(sd, pfx: str, x: Tensor, src_mask, mel_mask, d_target, p_target, e_target, bins):
+def variance_adaptor(sd, pfx: str, x: Tensor, src_mask, mel_mask, d_target, p_target, e_target, bins, drop=None):
     pitch_bins, energy_bins = (b.to(x.device) for b in bins)
-    log_d = variance_predictor(sd, pfx + "duration_predictor.", x, src_mask)  # :69
+    log_d = variance_predictor(sd, pfx + "duration_predictor.", x, src_mask, drop)  # :69
     if d_target is not None:
         max_len = mel_mask.shape[2] if mel_mask is not None else None  # :71-72
         x, mel_pos, frame_idx = length_regulator(x, d_target, max_len)  # :73
@@ -201,10 +220,10 @@ def variance_adaptor(sd, pfx: str, x: Tensor, src_mask, mel_mask, d_target, p_ta
         dur = round_durations(log_d)  # :75
         x, mel_pos, frame_idx = length_regulator(x, dur, None)  # :82
         mel_mask = get_mask_from_lengths(mel_pos)  # :84 -> 2-D (B,T)
-    p = variance_predictor(sd, pfx + "pitch_predictor.", x, mel_mask)  # :96
+    p = variance_predictor(sd, pfx + "pitch_predictor.", x, mel_mask, drop)  # :96
     p_src = p_target if p_target is not None else p  # :97-109 (scheduled sampling p=0 returns the target)
     p_idx = torch.bucketize(p_src, pitch_bins)
-    e = variance_predictor(sd, pfx + "energy_predictor.", x, mel_mask)  # :115
+    e = variance_predictor(sd, pfx + "energy_predictor.", x, mel_mask, drop)  # :115
     e_src = e_target if e_target is not None else e  # :116-118
     e_idx = torch.bucketize(e_src, energy_bins)
     text_dur = x  # :122
@@ -224,13 +243,14 @@ def _bn_eval(sd, pfx: str, x: Tensor, training: bool = False) -> Tensor:
                         sd[pfx + "bias"], training=False, eps=1e-5)
 
 
-def postnet(sd, pfx: str, x: Tensor, training: bool = False):
+def postnet(sd, pfx: str, x: Tensor, training: bool = False, drop=None):
     mel_pred = F.linear(x, sd[pfx + "out.weight"], sd[pfx + "out.bias"]).transpose(1, 2)  # :67
     h = F.conv1d(mel_pred, sd[pfx + "conv1.weight"], sd[pfx + "conv1.bias"], padding=4)[:, :, :-4]  # :71
-    h = torch.tanh(_bn_eval(sd, pfx + "pre_batchnorm.", h, training))
+    h = _drop(drop, "postnet.0", torch.tanh(_bn_eval(sd, pfx + "pre_batchnorm.", h, training)), channels_first=True)
     for i in range(3):  # :72-73
         h = F.conv1d(h, sd[f"{pfx}conv_list.{i}.weight"], sd[f"{pfx}conv_list.{i}.bias"], padding=4)[:, :, :-4]
-        h = torch.tanh(_bn_eval(sd, f"{pfx}batch_norm_list.{i}.", h, training))
+        h = _drop(drop, f"postnet.{i + 1}", torch.tanh(_bn_eval(sd, f"{pfx}batch_norm_list.{i}.", h, training)),
+                  channels_first=True)
     h = F.conv1d(h, sd[pfx + "conv2.weight"], sd[pfx + "conv2.bias"], padding=4)[:, :, :-4]  # :74
     post = mel_pred + h  # :75
     return mel_pred.transpose(1, 2), post.transpose(1, 2)  # :77
@@ -242,21 +262,21 @@ def postnet(sd, pfx: str, x: Tensor, training: bool = False):
 def fastspeech2_forward(sd: Dict[str, Tensor], hp: dict, src: Tensor, src_mask: Tensor,
                         mel_mask: Optional[Tensor] = None, d_target: Optional[Tensor] = None,
                         p_target: Optional[Tensor] = None, e_target: Optional[Tensor] = None,
-                        return_attn: bool = False, training: bool = False) -> dict:
+                        return_attn: bool = False, training: bool = False, drop=None) -> dict:
     """hp keys: n_layer_encoder, n_head_encoder, n_layer_decoder, n_head_decoder, nbins, f0_min,
     f0_max, energy_min, energy_max.  Returns a dict with the reference's tuple slots by name."""
     bins = variance_bins(hp["nbins"], hp["f0_min"], hp["f0_max"], hp["energy_min"], hp["energy_max"])
     e_out, attn_enc = encoder(sd, "encoder.", src, src_mask, hp["n_layer_encoder"], hp["n_head_encoder"],
-                              return_attn)  # :137
+                              return_attn, drop)  # :137
     va = variance_adaptor(sd, "variance_adaptor.", e_out, src_mask, mel_mask, d_target, p_target, e_target,
-                          bins)  # :176-181
+                          bins, drop)  # :176-181
     # Free-running: the reference hands the 2-D (B,T) mask to attention(), whose unsqueeze(1) only
     # broadcasts as a key mask at B == 1 (SURVEY F3; B=2 raises, B=H mis-assigns).  The oracle uses the
     # intended per-utterance key mask (B,1,T), which is bit-identical to the reference at B == 1.
     dec_mask = mel_mask if d_target is not None else va["mel_mask"].unsqueeze(1)
     d_out, attn_dec = encoder(sd, "decoder.", va["x"], dec_mask, hp["n_layer_decoder"], hp["n_head_decoder"],
-                              return_attn)  # :195
-    mel_pre, mel_post = postnet(sd, "postnet.", d_out, training)  # :197
+                              return_attn, drop)  # :195
+    mel_pre, mel_post = postnet(sd, "postnet.", d_out, training, drop)  # :197
     return dict(outputs_prenet=mel_pre, outputs_postnet=mel_post, log_d_prediction=va["log_d"],
                 p_prediction=va["p"], e_prediction=va["e"], variance_adaptor_output=va["x"],
                 text_dur_predicted=va["text_dur"], attn_enc=attn_enc, attn_dec=attn_dec,
@@ -278,13 +298,13 @@ def training_losses(out: dict, mel: Tensor, alignment: Tensor, f0: Tensor, energ
                 f0_loss=f0_loss, energy_loss=energy_loss)
 
 
-def training_step_grads(sd: Dict[str, Tensor], hp: dict, text, src_mask, mel_mask, alignment, f0, energy, mel):
-    """Forward in train() semantics (BatchNorm batch statistics, dropout 0) + losses + autograd backward,
+def training_step_grads(sd: Dict[str, Tensor], hp: dict, text, src_mask, mel_mask, alignment, f0, energy, mel, drop=None):
+    """Forward in train() semantics (BatchNorm batch statistics; dropout masks supplied by `drop`) + losses + autograd backward,
     as train_fastspeech2.py:167,212-259,304 does.  Returns (losses, {name: grad}) for the float parameters."""
     names = [k for k, v in sd.items() if v.is_floating_point() and "running_" not in k]
     p = {k: (sd[k].detach().clone().requires_grad_(True) if k in names else sd[k]) for k in sd}
     out = fastspeech2_forward(p, hp, text, src_mask, mel_mask=mel_mask, d_target=alignment, p_target=f0,
-                              e_target=energy, training=True)
+                              e_target=energy, training=True, drop=drop)
     losses = training_losses(out, mel, alignment, f0, energy)
     grads = torch.autograd.grad(losses["loss"], [p[k] for k in names], allow_unused=True)
     return ({k: v.detach() for k, v in losses.items()},

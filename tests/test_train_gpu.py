@@ -299,7 +299,7 @@ def test_reference_training_call_signature_runs_unchanged():
     from transformer_tts_b200 import data, synth
     from transformer_tts_b200.Models.fastspeech2 import FastSpeech2
 
-    hp = synth.make_hp(dropout=0.0, dropout_variance_adaptor=0.0, fix_mask=None, use_hop=False)
+    hp = synth.make_hp(dropout=0.1, dropout_variance_adaptor=0.5, fix_mask=None, use_hop=False)  # utils/default.yaml:73, fill_variables
     model = FastSpeech2(hp=hp, src_vocab=hp.vocab_size, trg_vocab=hp.mel_dim, d_model_encoder=hp.d_model_encoder,
                         N_e=hp.n_layer_encoder, n_head_encoder=hp.n_head_encoder,
                         ff_conv_kernel_size_encoder=hp.ff_conv_kernel_size_encoder,
@@ -307,7 +307,7 @@ def test_reference_training_call_signature_runs_unchanged():
                         N_d=hp.n_layer_decoder, n_head_decoder=hp.n_head_decoder,
                         ff_conv_kernel_size_decoder=hp.ff_conv_kernel_size_decoder,
                         concat_after_decoder=hp.concat_after_decoder, dropout_variance_adaptor=hp.dropout_variance_adaptor,
-                        reduction_rate=hp.reduction_rate, dropout=hp.dropout, dropout_postnet=0.0, n_bins=hp.nbins,
+                        reduction_rate=hp.reduction_rate, dropout=hp.dropout, dropout_postnet=0.5, n_bins=hp.nbins,
                         f0_min=hp.f0_min, f0_max=hp.f0_max, energy_min=hp.energy_min, energy_max=hp.energy_max,
                         pitch_pred=hp.pitch_pred, energy_pred=hp.energy_pred, accent_emb=hp.accent_emb,
                         output_type=hp.output_type, num_group=hp.num_group, multi_speaker=hp.is_multi_speaker,

@@ -126,13 +126,16 @@ enum {
 // v3: 64-key tiles, K triple- and V double-buffered in smem, S double-buffered in TMEM, so that neither a TMA
 // round trip nor the S -> registers copy sits on the per-tile critical path (v2 had single K/V buffers: its
 // per-tile time was 181 us of 226 us with the softmax arithmetic removed).
-template <int NH>
-__global__ void __launch_bounds__(64 + 128 * NH, 2)
+// DROP: training with dropout on the probabilities (Models/modules.py:18-19): the row sum l is taken BEFORE the mask
+// (softmax, then dropout), P * m is what multiplies V.  Its own instantiation: the plain kernel keeps its registers.
+template <int NH, bool DROP = false>
+__global__ void __launch_bounds__(64 + 128 * NH, DROP ? 1 : 2)
 attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmQ32,
                      const __grid_constant__ CUtensorMap tmKV, const __grid_constant__ CUtensorMap tmKV32,
                      const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmO32,
                      const uint8_t* __restrict__ mask, const int32_t* __restrict__ kv_info,
-                     float* __restrict__ lse2, int T, int H, float scale_log2, int skip_padded_q) {
+                     float* __restrict__ lse2, int T, int H, float scale_log2, int skip_padded_q,
+                     const DropCfg drop = DropCfg()) {
   extern __shared__ uint8_t smem_raw[];
 #if defined(TTSB_ATT_TRACE)
   const long long t_entry = clock64();
@@ -484,6 +487,12 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         }
 #endif
       }
+      if constexpr (DROP) {
+        const uint64_t e0 = ((static_cast<uint64_t>(b) * H + h) * T + static_cast<uint64_t>(q0 + row < T ? q0 + row : 0)) * T +
+                            j * kBKV + half * CW;
+#pragma unroll
+        for (int i = 0; i < CW; ++i) s[i] *= drop_scale(drop, e0 + i);
+      }
       // P (bf16 pairs, key 2c in the low half of column c) -> this thread's TMEM lane: the A operand of P V
       {
         uint32_t pk[CW / 2];
@@ -602,7 +611,8 @@ __global__ void attention_probs_kernel(const __nv_bfloat16* __restrict__ qkv, co
 using namespace ttsb;
 
 static int attention_fwd_launch(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx, float* lse2,
-                                int32_t B, int32_t T, int32_t H, int32_t Dh, int skip_padded_q, ttsb200_stream_t s) {
+                                int32_t B, int32_t T, int32_t H, int32_t Dh, int skip_padded_q, ttsb200_stream_t s,
+                                const DropCfg drop = DropCfg()) {
   TTSB_CHECK_ARG(qkv && mask && kv_info && ctx, "attention_fwd: null pointer");
   TTSB_CHECK_ARG(B > 0 && T > 0 && H > 0, "attention_fwd: bad dims");
   TTSB_CHECK_ARG(Dh == kDh, "attention_fwd: head dim %d unsupported (this build: %d)", Dh, kDh);
@@ -629,11 +639,19 @@ static int attention_fwd_launch(const void* qkv, const uint8_t* mask, const int3
   if (rc) return rc;
   rc = make_tmap_bf16(&tmO32, ctx, 3, odims, ostrides, box_q32, CU_TENSOR_MAP_SWIZZLE_64B);
   if (rc) return rc;
-  TTSB_SMEM_OPT_IN(attention_fwd_kernel<kAttHalves>, kAttSmem);
   dim3 grid((T + kBQ - 1) / kBQ, H, B);
   const float scale_log2 = kLog2e / sqrtf(static_cast<float>(Dh));
-  attention_fwd_kernel<kAttHalves><<<grid, kAttThreads, kAttSmem, static_cast<cudaStream_t>(s)>>>(
-      tmQ, tmQ32, tmKV, tmKV32, tmO, tmO32, mask, kv_info, lse2, T, H, scale_log2, skip_padded_q);
+  if (drop.thresh) {
+    auto kern = attention_fwd_kernel<kAttHalves, true>;
+    TTSB_SMEM_OPT_IN(kern, kAttSmem);
+    kern<<<grid, kAttThreads, kAttSmem, static_cast<cudaStream_t>(s)>>>(tmQ, tmQ32, tmKV, tmKV32, tmO, tmO32, mask, kv_info,
+                                                                       lse2, T, H, scale_log2, skip_padded_q, drop);
+  } else {
+    auto kern = attention_fwd_kernel<kAttHalves, false>;
+    TTSB_SMEM_OPT_IN(kern, kAttSmem);
+    kern<<<grid, kAttThreads, kAttSmem, static_cast<cudaStream_t>(s)>>>(tmQ, tmQ32, tmKV, tmKV32, tmO, tmO32, mask, kv_info,
+                                                                       lse2, T, H, scale_log2, skip_padded_q, drop);
+  }
   TTSB_CHECK_CUDA(cudaGetLastError());
   return TTSB_OK;
 }
@@ -648,6 +666,13 @@ extern "C" int ttsb200_attention_fwd_lse(const void* qkv, const uint8_t* mask, c
                                          float* lse2, int32_t B, int32_t T, int32_t H, int32_t Dh,
                                          ttsb200_stream_t s) {
   return attention_fwd_launch(qkv, mask, kv_info, ctx, lse2, B, T, H, Dh, 0, s);
+}
+
+extern "C" int ttsb200_attention_fwd_drop(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
+                                          float* lse2, int32_t B, int32_t T, int32_t H, int32_t Dh, float drop_p,
+                                          uint64_t drop_seed, int64_t drop_site, ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f, "attention_fwd: dropout probability must be in [0, 1)");
+  return attention_fwd_launch(qkv, mask, kv_info, ctx, lse2, B, T, H, Dh, 0, s, make_drop(drop_p, drop_seed, drop_site));
 }
 
 extern "C" int ttsb200_attention_fwd_ragged(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,

@@ -92,7 +92,8 @@ __global__ void __launch_bounds__(kThreads, 1)
 attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
                     const uint8_t* __restrict__ mask, const int32_t* __restrict__ kv_info,
                     const float* __restrict__ lse2, const float* __restrict__ delta,
-                    __nv_bfloat16* __restrict__ dqkv, int T, int H, float scale_log2, float scale) {
+                    __nv_bfloat16* __restrict__ dqkv, int T, int H, float scale_log2, float scale,
+                    const DropCfg drop) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
@@ -248,8 +249,23 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
         tmem_ld32(tmem_S + lane_off + c, s);
         tmem_ld32(tmem_dP + lane_off + c, dp);
         tmem_ld_wait();
+        // dropout on the probabilities (Models/modules.py:18-19): ctx = (P * m) V, so dP := (dO V^T) * m before
+        // dS = P * (dP - delta), and dV += (P * m)^T dO
+        float mk[32];
+        if (drop.thresh) {
+          const uint64_t e0 = (static_cast<uint64_t>(stat_base) + static_cast<uint64_t>(row_ok ? t : 0)) * T + k0 + c;
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            mk[e] = drop_scale(drop, e0 + e);
+            dp[e] *= mk[e];
+          }
+        }
         if (clean) softmax_bwd32_clean(s, dp, neg_l2, neg_dsc, scale_log2, scale);
         else softmax_bwd32(s, dp, sflag + c, row_ok, l2, dl, scale_log2, scale);
+        if (drop.thresh) {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) s[e] *= mk[e];
+        }
         store_row32(sP, row, c, s);
         store_row32(sDS, row, c, dp);
       }
@@ -295,7 +311,8 @@ __global__ void __launch_bounds__(kThreads, 1)
 attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
                    const uint8_t* __restrict__ mask, const int32_t* __restrict__ kv_info,
                    const float* __restrict__ lse2, const float* __restrict__ delta,
-                   __nv_bfloat16* __restrict__ dqkv, int T, int H, float scale_log2, float scale) {
+                   __nv_bfloat16* __restrict__ dqkv, int T, int H, float scale_log2, float scale,
+                   const DropCfg drop) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
@@ -430,6 +447,11 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         tmem_ld32(tmem_S + lane_off + c, s);
         tmem_ld32(tmem_dP + lane_off + c, dp);
         tmem_ld_wait();
+        if (drop.thresh) {  // dP := (dO V^T) * m, as in the dKV kernel
+          const uint64_t e0 = (static_cast<uint64_t>(stat_base) + static_cast<uint64_t>(row_ok ? t : 0)) * T + j * kBKV + c;
+#pragma unroll
+          for (int e = 0; e < 32; ++e) dp[e] *= drop_scale(drop, e0 + e);
+        }
         if (clean) softmax_bwd32_clean(s, dp, neg_l2, neg_dsc, scale_log2, scale);
         else softmax_bwd32(s, dp, flg + c, row_ok, l2, dl, scale_log2, scale);
         store_row32(sDS, row, c, dp);
@@ -472,6 +494,15 @@ using namespace ttsb;
 extern "C" int ttsb200_attention_bwd(const void* qkv, const void* dctx, const uint8_t* mask, const int32_t* kv_info,
                                      const float* lse2, const float* delta, void* dqkv, int32_t B, int32_t T,
                                      int32_t H, int32_t Dh, ttsb200_stream_t s) {
+  return ttsb200_attention_bwd_drop(qkv, dctx, mask, kv_info, lse2, delta, dqkv, B, T, H, Dh, 0.f, 0, -1, s);
+}
+
+extern "C" int ttsb200_attention_bwd_drop(const void* qkv, const void* dctx, const uint8_t* mask,
+                                          const int32_t* kv_info, const float* lse2, const float* delta, void* dqkv,
+                                          int32_t B, int32_t T, int32_t H, int32_t Dh, float drop_p, uint64_t drop_seed,
+                                          int64_t drop_site, ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f, "attention_bwd: dropout probability must be in [0, 1)");
+  const DropCfg drop = make_drop(drop_p, drop_seed, drop_site);
   TTSB_CHECK_ARG(qkv && dctx && mask && kv_info && lse2 && delta && dqkv, "attention_bwd: null pointer");
   TTSB_CHECK_ARG(B > 0 && T > 0 && H > 0 && Dh == ab::kDh, "attention_bwd: bad dims (Dh must be 96)");
   TTSB_CHECK_ARG(((reinterpret_cast<uintptr_t>(qkv) | reinterpret_cast<uintptr_t>(dctx) |
@@ -499,10 +530,10 @@ extern "C" int ttsb200_attention_bwd(const void* qkv, const void* dctx, const ui
   dim3 grid((T + 127) / 128, H, B);
   cudaStream_t st = static_cast<cudaStream_t>(s);
   ab::attn_bwd_dkv_kernel<<<grid, ab::kThreads, ab::kSmemDkv, st>>>(
-      tmQKV, tmDO, mask, kv_info, lse2, delta, static_cast<__nv_bfloat16*>(dqkv), T, H, scale_log2, scale);
+      tmQKV, tmDO, mask, kv_info, lse2, delta, static_cast<__nv_bfloat16*>(dqkv), T, H, scale_log2, scale, drop);
   TTSB_CHECK_CUDA(cudaGetLastError());
   ab::attn_bwd_dq_kernel<<<grid, ab::kThreads, ab::kSmemDq, st>>>(
-      tmQKV, tmDO, mask, kv_info, lse2, delta, static_cast<__nv_bfloat16*>(dqkv), T, H, scale_log2, scale);
+      tmQKV, tmDO, mask, kv_info, lse2, delta, static_cast<__nv_bfloat16*>(dqkv), T, H, scale_log2, scale, drop);
   TTSB_CHECK_CUDA(cudaGetLastError());
   return TTSB_OK;
 }

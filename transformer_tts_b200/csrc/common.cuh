@@ -63,9 +63,54 @@ int make_tmap(CUtensorMap* out, CUtensorMapDataType dtype, const void* base, int
               const uint64_t* strides_bytes, const uint32_t* box, CUtensorMapSwizzle swz);
 
 // ----------------------------------------------------------------------------------------------
+// Dropout masks (training): counter-based, so the forward kernel, every backward kernel and the tests regenerate
+// the SAME mask from (seed, site, element index) and no mask tensor is ever stored.  site = one dropout call site of
+// the reference (Models/modules.py:18-19,86,111, Models/layers.py:33,40, Models/varianceadaptor.py:219,222,
+// Models/postnets.py:71-73) in one module instance; element index = the element's offset in the dropped tensor.
+// keep(i) = hash32(i, key(seed, site)) >= p * 2^32; kept elements are scaled by 1 / (1 - p) like F.dropout.
+// ----------------------------------------------------------------------------------------------
+struct DropCfg {
+  uint32_t k0, k1;   // key words derived from (seed, site)
+  uint32_t thresh;   // p * 2^32; 0 = dropout disabled
+  float inv_keep;    // 1 / (1 - p)
+};
+static inline uint64_t drop_splitmix64(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+static inline DropCfg make_drop(float p, uint64_t seed, int64_t site) {
+  DropCfg d;
+  d.k0 = d.k1 = d.thresh = 0;
+  d.inv_keep = 1.f;
+  if (p > 0.f && site >= 0) {
+    const uint64_t k = drop_splitmix64(seed ^ drop_splitmix64(static_cast<uint64_t>(site) + 0x5851F42D4C957F2Dull));
+    d.k0 = static_cast<uint32_t>(k);
+    d.k1 = static_cast<uint32_t>(k >> 32);
+    const double t = static_cast<double>(p) * 4294967296.0;
+    d.thresh = t >= 4294967295.0 ? 0xFFFFFFFFu : (t < 1.0 ? 1u : static_cast<uint32_t>(t));
+    d.inv_keep = 1.f / (1.f - p);
+  }
+  return d;
+}
+
+// ----------------------------------------------------------------------------------------------
 // device helpers
 // ----------------------------------------------------------------------------------------------
 #ifdef __CUDACC__
+
+// 1 / (1 - p) for a kept element, 0 for a dropped one ("lowbias32" integer hash of the index mixed with the key)
+__device__ __forceinline__ float drop_scale(const DropCfg& d, uint64_t idx) {
+  uint32_t x = static_cast<uint32_t>(idx) * 0x9E3779B1u + d.k0;
+  x ^= (static_cast<uint32_t>(idx >> 32) + d.k1) * 0x85EBCA77u;
+  x ^= x >> 16;
+  x *= 0x7FEB352Du;
+  x ^= x >> 15;
+  x *= 0x846CA68Bu;
+  x ^= x >> 16;
+  return x >= d.thresh ? d.inv_keep : 0.f;
+}
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));

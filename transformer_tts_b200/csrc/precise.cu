@@ -573,8 +573,10 @@ attention_x3_kernel(const __half* __restrict__ qkv, const uint8_t* __restrict__ 
 
 // ------------------------------------------------------------------------------------------------
 // xrow: fp32 row operations of the chain, one warp per row, D = 128 * NV (256 or 384)
-//   s  = a (+ b0 | + hi/lo pair b0_split);  s_out = s
+//   s  = a (+ b0 | + b0_bf16 | + hi/lo pair b0_split);  s_out = s
 //   t  = LN(s; g1, b1)
+//   training with dropout: b0 := drop_b(b0) before the add (Models/layers.py:33), s := drop_s(s) before s_out and the
+//   LayerNorm (Models/modules.py:86), t := drop_t(t) after it (layers.py:40, varianceadaptor.py:219,222)
 //   mode ADD_LN:   out = t
 //   mode FFN_TAIL: z = c + t ; z_out = z ; out = LN(z; g2, b2)
 //   mode LN_DOT:   out_row = mask ? dot(t, w) + wb : 0
@@ -583,7 +585,9 @@ attention_x3_kernel(const __half* __restrict__ qkv, const uint8_t* __restrict__ 
 struct XRowArgs {
   const float* a;
   const float* b0;
+  const __nv_bfloat16* b0_bf16;
   const __half* b0_split;
+  DropCfg drop_b, drop_s, drop_t;
   const float* c;
   const float *g1, *b1, *g2, *b2;
   const float* dot_w;
@@ -637,8 +641,21 @@ __global__ void __launch_bounds__(256) xrow_kernel(const XRowArgs p) {
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
     v[i] = *(reinterpret_cast<const float4*>(p.a + row * D) + i * 32 + lane);
-    if (p.b0) {
-      const float4 r = *(reinterpret_cast<const float4*>(p.b0 + row * D) + i * 32 + lane);
+    const uint64_t e0 = static_cast<uint64_t>(row) * D + (i * 32 + lane) * 4;
+    if (p.b0 || p.b0_bf16) {
+      float4 r;
+      if (p.b0) {
+        r = *(reinterpret_cast<const float4*>(p.b0 + row * D) + i * 32 + lane);
+      } else {
+        const uint2 u = *(reinterpret_cast<const uint2*>(p.b0_bf16 + row * D) + i * 32 + lane);
+        const float2 lo = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.x));
+        const float2 hi = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.y));
+        r = make_float4(lo.x, lo.y, hi.x, hi.y);
+      }
+      if (p.drop_b.thresh) {
+        r.x *= drop_scale(p.drop_b, e0); r.y *= drop_scale(p.drop_b, e0 + 1);
+        r.z *= drop_scale(p.drop_b, e0 + 2); r.w *= drop_scale(p.drop_b, e0 + 3);
+      }
       v[i].x += r.x; v[i].y += r.y; v[i].z += r.z; v[i].w += r.w;
     }
     if (p.b0_split) {
@@ -650,9 +667,21 @@ __global__ void __launch_bounds__(256) xrow_kernel(const XRowArgs p) {
       const float2 e1 = __half22float2(*reinterpret_cast<const __half2*>(&ll.y));
       v[i].x += h0.x + e0.x; v[i].y += h0.y + e0.y; v[i].z += h1.x + e1.x; v[i].w += h1.y + e1.y;
     }
+    if (p.drop_s.thresh) {
+      v[i].x *= drop_scale(p.drop_s, e0); v[i].y *= drop_scale(p.drop_s, e0 + 1);
+      v[i].z *= drop_scale(p.drop_s, e0 + 2); v[i].w *= drop_scale(p.drop_s, e0 + 3);
+    }
     if (p.s_out) reinterpret_cast<float4*>(p.s_out + row * D)[i * 32 + lane] = v[i];
   }
   xrow_ln<NV>(v, p.g1, p.b1, p.eps, lane);
+  if (p.drop_t.thresh) {
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const uint64_t e0 = static_cast<uint64_t>(row) * D + (i * 32 + lane) * 4;
+      v[i].x *= drop_scale(p.drop_t, e0); v[i].y *= drop_scale(p.drop_t, e0 + 1);
+      v[i].z *= drop_scale(p.drop_t, e0 + 2); v[i].w *= drop_scale(p.drop_t, e0 + 3);
+    }
+  }
   if (p.mode == XROW_LN_DOT) {
     float dot = 0.f;
 #pragma unroll
@@ -843,19 +872,25 @@ extern "C" int ttsb200_attention_x3(const void* qkv_split, const uint8_t* mask, 
   return TTSB_OK;
 }
 
-extern "C" int ttsb200_xrow(int32_t mode, const float* a, const float* b0, const void* b0_split, const float* c,
-                            const float* g1, const float* b1, const float* g2, const float* b2, const float* dot_w,
-                            const float* dot_b, const uint8_t* row_mask, float eps, float* s_out, float* z_out,
-                            void* out_split, void* out_bf16, float* out_f32, float* out_row, int64_t rows, int32_t D,
+extern "C" int ttsb200_xrow(int32_t mode, const float* a, const float* b0, const void* b0_bf16, const void* b0_split,
+                            const float* c, const float* g1, const float* b1, const float* g2, const float* b2,
+                            const float* dot_w, const float* dot_b, const uint8_t* row_mask, float eps, float* s_out,
+                            float* z_out, void* out_split, void* out_bf16, float* out_f32, float* out_row, int64_t rows,
+                            int32_t D, float drop_p, uint64_t drop_seed, int64_t site_b, int64_t site_s, int64_t site_t,
                             ttsb200_stream_t stream) {
   TTSB_CHECK_ARG(a && g1 && b1 && rows > 0, "xrow: bad args");
   TTSB_CHECK_ARG(mode >= XROW_ADD_LN && mode <= XROW_LN_DOT, "xrow: bad mode %d", mode);
-  TTSB_CHECK_ARG(!(b0 && b0_split), "xrow: b0 and b0_split are exclusive");
+  TTSB_CHECK_ARG((b0 != nullptr) + (b0_bf16 != nullptr) + (b0_split != nullptr) <= 1, "xrow: b0, b0_bf16 and b0_split are exclusive");
+  TTSB_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f, "xrow: dropout probability must be in [0, 1)");
   if (mode == XROW_FFN_TAIL) TTSB_CHECK_ARG(c && g2 && b2, "xrow: FFN_TAIL needs c, g2, b2");
   if (mode == XROW_LN_DOT) TTSB_CHECK_ARG(dot_w && dot_b && out_row, "xrow: LN_DOT needs dot_w, dot_b, out_row");
   else TTSB_CHECK_ARG(out_split || out_bf16 || out_f32, "xrow: no output");
   XRowArgs p;
-  p.a = a; p.b0 = b0; p.b0_split = static_cast<const __half*>(b0_split); p.c = c;
+  p.a = a; p.b0 = b0; p.b0_bf16 = static_cast<const __nv_bfloat16*>(b0_bf16);
+  p.b0_split = static_cast<const __half*>(b0_split); p.c = c;
+  p.drop_b = make_drop(drop_p, drop_seed, site_b);
+  p.drop_s = make_drop(drop_p, drop_seed, site_s);
+  p.drop_t = make_drop(drop_p, drop_seed, site_t);
   p.g1 = g1; p.b1 = b1; p.g2 = g2; p.b2 = b2; p.dot_w = dot_w; p.dot_b = dot_b; p.row_mask = row_mask;
   p.s_out = s_out; p.z_out = z_out; p.out_split = static_cast<__half*>(out_split);
   p.out_bf16 = static_cast<__nv_bfloat16*>(out_bf16); p.out_f32 = out_f32; p.out_row = out_row;

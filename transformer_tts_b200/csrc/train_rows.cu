@@ -64,15 +64,26 @@ __device__ __forceinline__ void block_col_atomic(float (&acc)[NV * 4], float* __
 // ------------------------------------------------------------------------------------------------
 // HEAD = the predictor-head variant (g = g_row * g_vec, dvec / dscal outputs): its 36 extra registers per thread
 // cost the plain variant (19 launches per training step) its second resident CTA, so it is a template switch.
-template <int NV, bool HEAD>
-__global__ void __launch_bounds__(kRowThreads, HEAD ? 1 : 2)
+// DROP (training with dropout > 0, its own instantiation so the plain variant keeps its register count):
+//   dg: the LayerNorm OUTPUT was dropped in the forward (y' = y * m): g := g * m before anything else, and the head's
+//       dvec uses y * m  (Models/modules.py:86-87 is followed by layers.py:40's dropout; varianceadaptor.py:219,222)
+//   dx: the LayerNorm INPUT was the output of a dropout (x = x0 * m): dx := dx * m   — mode 1: both outputs;
+//       mode 2: only dx_bf16, the copy that feeds the GEMM gradients of a dropped branch (layers.py:33), while
+//       dx_f32 continues down the residual path unmasked
+struct LnDrop {
+  DropCfg dg, dx;
+  int dx_mode;
+};
+
+template <int NV, bool HEAD, bool DROP = false>
+__global__ void __launch_bounds__(kRowThreads, (HEAD || DROP) ? 1 : 2)
 ln_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
               const float* __restrict__ g_f32, const __nv_bfloat16* __restrict__ g_bf16,
               const float* __restrict__ g_row, const float* __restrict__ g_vec,
               const uint8_t* __restrict__ row_mask, const float* __restrict__ add_f32, int relu_gate,
               float* __restrict__ dx_f32, __nv_bfloat16* __restrict__ dx_bf16, float* __restrict__ dgamma,
               float* __restrict__ dbeta, float* __restrict__ dvec, float* __restrict__ dscal, int64_t rows,
-              float eps) {
+              float eps, const LnDrop drop = LnDrop()) {
   constexpr int D = 128 * NV;
   __shared__ float sbuf[kRowWarps * D];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -108,6 +119,19 @@ ln_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, cons
       else if (g_bf16) g[i] = ld_bf16x4(g_bf16 + row * D + (i * 32 + lane) * 4);
       else g[i] = make_float4(gr * gv[i].x, gr * gv[i].y, gr * gv[i].z, gr * gv[i].w);
     }
+    [[maybe_unused]] float4 mk[NV];
+    if constexpr (DROP) {
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        mk[i] = make_float4(1.f, 1.f, 1.f, 1.f);
+        if (drop.dg.thresh) {
+          const uint64_t e0 = static_cast<uint64_t>(row) * D + (i * 32 + lane) * 4;
+          mk[i] = make_float4(drop_scale(drop.dg, e0), drop_scale(drop.dg, e0 + 1), drop_scale(drop.dg, e0 + 2),
+                              drop_scale(drop.dg, e0 + 3));
+          g[i].x *= mk[i].x; g[i].y *= mk[i].y; g[i].z *= mk[i].z; g[i].w *= mk[i].w;
+        }
+      }
+    }
     const float mean = warp_sum(s) * (1.f / D);
     float q = 0.f;
 #pragma unroll
@@ -128,8 +152,10 @@ ln_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, cons
       a_dg[4 * i + 2] += g[i].z * xh[i].z; a_dg[4 * i + 3] += g[i].w * xh[i].w;
       a_db[4 * i] += g[i].x; a_db[4 * i + 1] += g[i].y; a_db[4 * i + 2] += g[i].z; a_db[4 * i + 3] += g[i].w;
       if (HEAD && g_row) {
-        a_dv[4 * i] += gr * fmaf(gm[i].x, xh[i].x, bt[i].x); a_dv[4 * i + 1] += gr * fmaf(gm[i].y, xh[i].y, bt[i].y);
-        a_dv[4 * i + 2] += gr * fmaf(gm[i].z, xh[i].z, bt[i].z); a_dv[4 * i + 3] += gr * fmaf(gm[i].w, xh[i].w, bt[i].w);
+        float4 y = make_float4(fmaf(gm[i].x, xh[i].x, bt[i].x), fmaf(gm[i].y, xh[i].y, bt[i].y),
+                               fmaf(gm[i].z, xh[i].z, bt[i].z), fmaf(gm[i].w, xh[i].w, bt[i].w));
+        if constexpr (DROP) { y.x *= mk[i].x; y.y *= mk[i].y; y.z *= mk[i].z; y.w *= mk[i].w; }
+        a_dv[4 * i] += gr * y.x; a_dv[4 * i + 1] += gr * y.y; a_dv[4 * i + 2] += gr * y.z; a_dv[4 * i + 3] += gr * y.w;
       }
     }
     a_ds += gr;
@@ -152,8 +178,17 @@ ln_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, cons
         if (!(v[i].z > -mean)) d.z = 0.f;
         if (!(v[i].w > -mean)) d.w = 0.f;
       }
+      float4 dm = d;
+      if constexpr (DROP) {
+        if (drop.dx.thresh) {
+          const uint64_t e0 = static_cast<uint64_t>(row) * D + (i * 32 + lane) * 4;
+          dm.x *= drop_scale(drop.dx, e0); dm.y *= drop_scale(drop.dx, e0 + 1);
+          dm.z *= drop_scale(drop.dx, e0 + 2); dm.w *= drop_scale(drop.dx, e0 + 3);
+          if (drop.dx_mode == 1) d = dm;
+        }
+      }
       if (dx_f32) __stcs(reinterpret_cast<float4*>(dx_f32 + row * D) + i * 32 + lane, d);
-      if (dx_bf16) st_bf16x4(dx_bf16 + row * D + (i * 32 + lane) * 4, d);
+      if (dx_bf16) st_bf16x4(dx_bf16 + row * D + (i * 32 + lane) * 4, dm);
     }
   }
   if (dgamma) block_col_atomic<NV>(a_dg, dgamma, sbuf, lane, warp);
@@ -245,7 +280,7 @@ bn_stats_kernel(const float* __restrict__ x, float* __restrict__ stats, int64_t 
 template <int NV>
 __global__ void __launch_bounds__(kRowThreads)
 bn_tanh_fwd_kernel(const float* __restrict__ x, const float* __restrict__ ms, const float* __restrict__ gamma,
-                   const float* __restrict__ beta, __nv_bfloat16* __restrict__ h, int64_t rows) {
+                   const float* __restrict__ beta, __nv_bfloat16* __restrict__ h, int64_t rows, const DropCfg drop) {
   constexpr int D = 128 * NV;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float4 sc[NV], sh[NV];
@@ -263,8 +298,13 @@ bn_tanh_fwd_kernel(const float* __restrict__ x, const float* __restrict__ ms, co
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const float4 v = __ldcs(reinterpret_cast<const float4*>(x + row * D) + i * 32 + lane);
-      const float4 o = make_float4(tanhf(fmaf(v.x, sc[i].x, sh[i].x)), tanhf(fmaf(v.y, sc[i].y, sh[i].y)),
-                                   tanhf(fmaf(v.z, sc[i].z, sh[i].z)), tanhf(fmaf(v.w, sc[i].w, sh[i].w)));
+      float4 o = make_float4(tanhf(fmaf(v.x, sc[i].x, sh[i].x)), tanhf(fmaf(v.y, sc[i].y, sh[i].y)),
+                             tanhf(fmaf(v.z, sc[i].z, sh[i].z)), tanhf(fmaf(v.w, sc[i].w, sh[i].w)));
+      if (drop.thresh) {  // Models/postnets.py:71-73: dropout(tanh(batch_norm(conv(x))))
+        const uint64_t e0 = static_cast<uint64_t>(row) * D + (i * 32 + lane) * 4;
+        o.x *= drop_scale(drop, e0); o.y *= drop_scale(drop, e0 + 1);
+        o.z *= drop_scale(drop, e0 + 2); o.w *= drop_scale(drop, e0 + 3);
+      }
       st_bf16x4(h + row * D + (i * 32 + lane) * 4, o);
     }
   }
@@ -277,7 +317,8 @@ template <int NV, bool APPLY>
 __global__ void __launch_bounds__(kRowThreads)
 bn_tanh_bwd_kernel(const __nv_bfloat16* __restrict__ dh, const __nv_bfloat16* __restrict__ h,
                    const float* __restrict__ x, const float* __restrict__ ms, const float* __restrict__ gamma,
-                   float* __restrict__ red, __nv_bfloat16* __restrict__ dx, int64_t rows, float inv_count) {
+                   float* __restrict__ red, __nv_bfloat16* __restrict__ dx, int64_t rows, float inv_count,
+                   const DropCfg drop) {
   constexpr int D = 128 * NV;
   __shared__ float sbuf[APPLY ? 1 : kRowWarps * D];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -303,8 +344,17 @@ bn_tanh_bwd_kernel(const __nv_bfloat16* __restrict__ dh, const __nv_bfloat16* __
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int64_t off = row * D + (i * 32 + lane) * 4;
-      const float4 g = ld_bf16x4(dh + off);
-      const float4 t = ld_bf16x4(h + off);
+      float4 g = ld_bf16x4(dh + off);
+      float4 t = ld_bf16x4(h + off);
+      if (drop.thresh) {
+        // h = tanh(.) * m was saved: kept elements give tanh back as h * (1 - p), dropped ones carry no gradient
+        const uint64_t e0 = static_cast<uint64_t>(off);
+        const float4 m = make_float4(drop_scale(drop, e0), drop_scale(drop, e0 + 1), drop_scale(drop, e0 + 2),
+                                     drop_scale(drop, e0 + 3));
+        const float keep = 1.f / drop.inv_keep;
+        g.x *= m.x; g.y *= m.y; g.z *= m.z; g.w *= m.w;
+        t.x *= keep; t.y *= keep; t.z *= keep; t.w *= keep;
+      }
       const float4 v = __ldcs(reinterpret_cast<const float4*>(x + row * D) + i * 32 + lane);
       const float4 dt = make_float4(g.x * (1.f - t.x * t.x), g.y * (1.f - t.y * t.y), g.z * (1.f - t.z * t.z),
                                     g.w * (1.f - t.w * t.w));
@@ -569,7 +619,24 @@ extern "C" int ttsb200_layernorm_bwd(const float* x, const float* gamma, const f
                                      const uint8_t* row_mask, const float* add_f32, int32_t relu_gate,
                                      float* dx_f32, void* dx_bf16, float* dgamma, float* dbeta, float* dvec,
                                      float* dscal, int64_t rows, int32_t D, float eps, ttsb200_stream_t s) {
+  return ttsb200_layernorm_bwd_drop(x, gamma, beta, g_f32, g_bf16, g_row, g_vec, row_mask, add_f32, relu_gate, dx_f32,
+                                    dx_bf16, dgamma, dbeta, dvec, dscal, rows, D, eps, 0.f, 0, -1, -1, 0, s);
+}
+
+extern "C" int ttsb200_layernorm_bwd_drop(const float* x, const float* gamma, const float* beta, const float* g_f32,
+                                          const void* g_bf16, const float* g_row, const float* g_vec,
+                                          const uint8_t* row_mask, const float* add_f32, int32_t relu_gate,
+                                          float* dx_f32, void* dx_bf16, float* dgamma, float* dbeta, float* dvec,
+                                          float* dscal, int64_t rows, int32_t D, float eps, float drop_p,
+                                          uint64_t drop_seed, int64_t site_g, int64_t site_dx, int32_t dx_mode,
+                                          ttsb200_stream_t s) {
   TTSB_CHECK_ARG(x && gamma && rows > 0, "layernorm_bwd: bad args");
+  TTSB_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f && dx_mode >= 0 && dx_mode <= 2, "layernorm_bwd: bad dropout arguments");
+  LnDrop drop;
+  drop.dg = make_drop(drop_p, drop_seed, site_g);
+  drop.dx = make_drop(drop_p, drop_seed, dx_mode ? site_dx : -1);
+  drop.dx_mode = dx_mode;
+  const bool dropping = drop.dg.thresh != 0 || drop.dx.thresh != 0;
   TTSB_CHECK_ARG((g_f32 != nullptr) + (g_bf16 != nullptr) + (g_row != nullptr) == 1,
                  "layernorm_bwd: exactly one gradient source");
   TTSB_CHECK_ARG(!g_row || g_vec, "layernorm_bwd: g_row needs g_vec");
@@ -578,15 +645,18 @@ extern "C" int ttsb200_layernorm_bwd(const float* x, const float* gamma, const f
   auto gb = static_cast<const __nv_bfloat16*>(g_bf16);
   auto db = static_cast<__nv_bfloat16*>(dx_bf16);
   const bool head = g_row != nullptr || g_vec != nullptr || dvec != nullptr || dscal != nullptr;
-#define TTSB_LN_BWD(NV, HEAD)                                                                                      \
-  ln_bwd_kernel<NV, HEAD><<<grid, kRowThreads, 0, st>>>(x, gamma, beta, g_f32, gb, g_row, g_vec, row_mask, add_f32, \
-                                                        relu_gate, dx_f32, db, dgamma, dbeta, dvec, dscal, rows, eps)
+#define TTSB_LN_BWD(NV, HEAD, DROP)                                                                                 \
+  ln_bwd_kernel<NV, HEAD, DROP><<<grid, kRowThreads, 0, st>>>(x, gamma, beta, g_f32, gb, g_row, g_vec, row_mask,       \
+                                                              add_f32, relu_gate, dx_f32, db, dgamma, dbeta, dvec,      \
+                                                              dscal, rows, eps, drop)
   if (D == 384) {
-    if (head) TTSB_LN_BWD(3, true);
-    else TTSB_LN_BWD(3, false);
+    if (dropping) { if (head) TTSB_LN_BWD(3, true, true); else TTSB_LN_BWD(3, false, true); }
+    else if (head) TTSB_LN_BWD(3, true, false);
+    else TTSB_LN_BWD(3, false, false);
   } else if (D == 256) {
-    if (head) TTSB_LN_BWD(2, true);
-    else TTSB_LN_BWD(2, false);
+    if (dropping) { if (head) TTSB_LN_BWD(2, true, true); else TTSB_LN_BWD(2, false, true); }
+    else if (head) TTSB_LN_BWD(2, true, false);
+    else TTSB_LN_BWD(2, false, false);
   }
 #undef TTSB_LN_BWD
   else {
@@ -628,33 +698,82 @@ extern "C" int ttsb200_bn_stats(const float* x, float* stats, int64_t rows, int3
 }
 
 extern "C" int ttsb200_bn_tanh_fwd(const float* x, const float* mean_rstd, const float* gamma, const float* beta,
-                                   void* h_bf16, int64_t rows, int32_t C, ttsb200_stream_t s) {
+                                   void* h_bf16, int64_t rows, int32_t C, float drop_p, uint64_t drop_seed,
+                                   int64_t drop_site, ttsb200_stream_t s) {
   TTSB_CHECK_ARG(x && mean_rstd && gamma && beta && h_bf16 && rows > 0 && C == 384, "bn_tanh_fwd: bad args");
+  TTSB_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f, "bn_tanh_fwd: dropout probability must be in [0, 1)");
   bn_tanh_fwd_kernel<3><<<persistent_grid(rows), kRowThreads, 0, static_cast<cudaStream_t>(s)>>>(
-      x, mean_rstd, gamma, beta, static_cast<__nv_bfloat16*>(h_bf16), rows);
+      x, mean_rstd, gamma, beta, static_cast<__nv_bfloat16*>(h_bf16), rows, make_drop(drop_p, drop_seed, drop_site));
   TTSB_LAUNCH_CHECK();
   return TTSB_OK;
 }
 
 extern "C" int ttsb200_bn_tanh_bwd(const void* dh_bf16, const void* h_bf16, const float* x, const float* mean_rstd,
                                    const float* gamma, float* red, void* dx_bf16, int64_t rows, int32_t C,
-                                   float inv_count, int32_t apply, ttsb200_stream_t s) {
+                                   float inv_count, int32_t apply, float drop_p, uint64_t drop_seed,
+                                   int64_t drop_site, ttsb200_stream_t s) {
   TTSB_CHECK_ARG(dh_bf16 && h_bf16 && x && mean_rstd && red && rows > 0 && C == 384, "bn_tanh_bwd: bad args");
+  TTSB_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f, "bn_tanh_bwd: dropout probability must be in [0, 1)");
+  const DropCfg drop = make_drop(drop_p, drop_seed, drop_site);
   auto dh = static_cast<const __nv_bfloat16*>(dh_bf16);
   auto h = static_cast<const __nv_bfloat16*>(h_bf16);
   cudaStream_t st = static_cast<cudaStream_t>(s);
   if (apply) {
     TTSB_CHECK_ARG(gamma && dx_bf16, "bn_tanh_bwd: apply needs gamma and dx");
     bn_tanh_bwd_kernel<3, true><<<persistent_grid(rows), kRowThreads, 0, st>>>(
-        dh, h, x, mean_rstd, gamma, red, static_cast<__nv_bfloat16*>(dx_bf16), rows, inv_count);
+        dh, h, x, mean_rstd, gamma, red, static_cast<__nv_bfloat16*>(dx_bf16), rows, inv_count, drop);
   } else {
     bn_tanh_bwd_kernel<3, false><<<persistent_grid(rows), kRowThreads, 0, st>>>(dh, h, x, mean_rstd, gamma, red,
-                                                                                nullptr, rows, inv_count);
+                                                                                nullptr, rows, inv_count, drop);
   }
   TTSB_LAUNCH_CHECK();
   return TTSB_OK;
 }
 
+namespace ttsb {
+// ------------------------------------------------------------------------------------------------
+// Standalone dropout over a dense buffer (Models/modules.py:111 on embedding + positional encoding, and the same mask
+// on the gradient in the backward pass): dst[i] = src[i] * m(i).  dtype 0 = fp32, 1 = bf16; dst may alias src.
+// ttsb200_dropout_mask writes m itself (0 or 1 / (1 - p)) for tests.
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) dropout_kernel(const T* __restrict__ src, T* __restrict__ dst, int64_t n,
+                                                      const DropCfg drop) {
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float m = drop_scale(drop, static_cast<uint64_t>(i));
+  if constexpr (sizeof(T) == 4) dst[i] = src[i] * m;
+  else dst[i] = __float2bfloat16_rn(__bfloat162float(src[i]) * m);
+}
+__global__ void __launch_bounds__(256) dropout_mask_kernel(float* __restrict__ out, int64_t n, const DropCfg drop) {
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = drop.thresh ? drop_scale(drop, static_cast<uint64_t>(i)) : 1.f;
+}
+
+}  // namespace ttsb
+extern "C" int ttsb200_dropout(const void* src, void* dst, int32_t is_bf16, int64_t n, float p, uint64_t seed,
+                               int64_t site, ttsb200_stream_t s) {
+  using namespace ttsb;
+  TTSB_CHECK_ARG(src && dst && n > 0 && p > 0.f && p < 1.f && site >= 0, "dropout: bad args (0 < p < 1)");
+  const DropCfg d = make_drop(p, seed, site);
+  const unsigned grid = static_cast<unsigned>((n + 255) / 256);
+  if (is_bf16)
+    dropout_kernel<__nv_bfloat16><<<grid, 256, 0, static_cast<cudaStream_t>(s)>>>(
+        static_cast<const __nv_bfloat16*>(src), static_cast<__nv_bfloat16*>(dst), n, d);
+  else
+    dropout_kernel<float><<<grid, 256, 0, static_cast<cudaStream_t>(s)>>>(static_cast<const float*>(src),
+                                                                         static_cast<float*>(dst), n, d);
+  TTSB_CHECK_CUDA(cudaGetLastError());
+  return TTSB_OK;
+}
+extern "C" int ttsb200_dropout_mask(float* out, int64_t n, float p, uint64_t seed, int64_t site, ttsb200_stream_t s) {
+  using namespace ttsb;
+  TTSB_CHECK_ARG(out && n > 0 && p >= 0.f && p < 1.f, "dropout_mask: bad args");
+  dropout_mask_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(s)>>>(
+      out, n, make_drop(p, seed, site));
+  TTSB_CHECK_CUDA(cudaGetLastError());
+  return TTSB_OK;
+}
 extern "C" int ttsb200_lr_bwd(const float* g, const int32_t* cum, float* dx, const float* add_f32, int32_t B,
                               int32_t L, int32_t Tmax, int32_t D, ttsb200_stream_t s) {
   TTSB_CHECK_ARG(g && cum && dx && B > 0 && L > 0 && Tmax > 0 && D == 384, "lr_bwd: bad args (D must be 384)");

@@ -75,8 +75,16 @@ _SIGNATURES = {
                                                                                  C.c_void_p], C.c_int),
     "ttsb200_colsum": ([C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_bn_stats": ([C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p], C.c_int),
-    "ttsb200_bn_tanh_fwd": ([C.c_void_p] * 5 + [C.c_int64, C.c_int32, C.c_void_p], C.c_int),
-    "ttsb200_bn_tanh_bwd": ([C.c_void_p] * 7 + [C.c_int64, C.c_int32, C.c_float, C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_bn_tanh_fwd": ([C.c_void_p] * 5 + [C.c_int64, C.c_int32, C.c_float, C.c_uint64, C.c_int64, C.c_void_p], C.c_int),
+    "ttsb200_bn_tanh_bwd": ([C.c_void_p] * 7 + [C.c_int64, C.c_int32, C.c_float, C.c_int32, C.c_float, C.c_uint64,
+                                                C.c_int64, C.c_void_p], C.c_int),
+    # ---- dropout (training) ----
+    "ttsb200_layernorm_bwd_drop": ([C.c_void_p] * 9 + [C.c_int32] + [C.c_void_p] * 6 + [C.c_int64, C.c_int32, C.c_float,
+                                    C.c_float, C.c_uint64, C.c_int64, C.c_int64, C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_dropout": ([C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_uint64, C.c_int64, C.c_void_p], C.c_int),
+    "ttsb200_dropout_mask": ([C.c_void_p, C.c_int64, C.c_float, C.c_uint64, C.c_int64, C.c_void_p], C.c_int),
+    "ttsb200_attention_fwd_drop": ([C.c_void_p] * 5 + [C.c_int32] * 4 + [C.c_float, C.c_uint64, C.c_int64, C.c_void_p], C.c_int),
+    "ttsb200_attention_bwd_drop": ([C.c_void_p] * 7 + [C.c_int32] * 4 + [C.c_float, C.c_uint64, C.c_int64, C.c_void_p], C.c_int),
     "ttsb200_lr_bwd": ([C.c_void_p] * 4 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
     "ttsb200_embed_bwd": ([C.c_void_p] * 4 + [C.c_int32, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
                                               C.c_int32, C.c_void_p], C.c_int),
@@ -87,8 +95,8 @@ _SIGNATURES = {
     # ---- fp32-accurate encoder -> duration chain ----
     "ttsb200_gemm_x3": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_float] + [C.c_int32] * 7 + [C.c_void_p] * 3, C.c_int),
     "ttsb200_attention_x3": ([C.c_void_p] * 4 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
-    "ttsb200_xrow": ([C.c_int32] + [C.c_void_p] * 11 + [C.c_float] + [C.c_void_p] * 6 + [C.c_int64, C.c_int32,
-                                                                                        C.c_void_p], C.c_int),
+    "ttsb200_xrow": ([C.c_int32] + [C.c_void_p] * 12 + [C.c_float] + [C.c_void_p] * 6 + [C.c_int64, C.c_int32, C.c_float,
+                     C.c_uint64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p], C.c_int),
     "ttsb200_split_f16": ([C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_float, C.c_void_p], C.c_int),
     "ttsb200_ffn2_tail": ([C.c_void_p] * 7 + [C.c_float] + [C.c_void_p] * 4 + [C.c_int64, C.c_int32, C.c_void_p],
                           C.c_int),
@@ -227,11 +235,20 @@ def build_tile_map(lengths: torch.Tensor, T: int, halo: int = 0) -> tuple:
 # attention
 # --------------------------------------------------------------------------------------------------
 def attention_fwd(qkv: torch.Tensor, mask: torch.Tensor, kv_len: torch.Tensor, ctx: torch.Tensor, H: int,
-                  lse2: Optional[torch.Tensor] = None, skip_padded_queries: bool = False) -> None:
+                  lse2: Optional[torch.Tensor] = None, skip_padded_queries: bool = False,
+                  drop: Optional[tuple] = None) -> None:
     """lse2 (B,H,T) fp32, when given, receives the log2-domain log-sum-exp of every row (training).
-    skip_padded_queries: 128-row query tiles wholly beyond an utterance's last valid row are not computed."""
+    skip_padded_queries: 128-row query tiles wholly beyond an utterance's last valid row are not computed.
+    drop = (p, seed, site): dropout on the probabilities (training, Models/modules.py:18-19)."""
     B, T, W = qkv.shape
     Dh = W // (3 * H)
+    if drop is not None and drop[0] > 0:
+        _check(load().ttsb200_attention_fwd_drop(_ptr(qkv, torch.bfloat16, "qkv"), _ptr(mask, torch.uint8, "mask"),
+                                                 _ptr(kv_len, torch.int32, "kv_len"), _ptr(ctx, torch.bfloat16, "ctx"),
+                                                 _ptr(lse2, torch.float32, "lse2"), B, T, H, Dh, float(drop[0]),
+                                                 int(drop[1]), int(drop[2]), _stream()), "attention_fwd_drop")
+        _count()
+        return
     if skip_padded_queries:
         if lse2 is not None:
             raise ValueError("attention_fwd: skip_padded_queries is an inference option (no lse2)")
@@ -396,31 +413,35 @@ def attn_delta(dctx: torch.Tensor, ctx: torch.Tensor, H: int) -> torch.Tensor:
     return delta
 
 
-def attention_bwd(qkv, dctx, mask, kv_len, lse2, delta, H: int) -> torch.Tensor:
+def attention_bwd(qkv, dctx, mask, kv_len, lse2, delta, H: int, drop: Optional[tuple] = None) -> torch.Tensor:
     B, T, W = qkv.shape
     dqkv = torch.empty_like(qkv)
-    _check(load().ttsb200_attention_bwd(_ptr(qkv, torch.bfloat16, "qkv"), _ptr(dctx, torch.bfloat16, "dctx"),
-                                        _ptr(mask, torch.uint8, "mask"), _ptr(kv_len, torch.int32, "kv_len"),
-                                        _ptr(lse2, torch.float32, "lse2"), _ptr(delta, torch.float32, "delta"),
-                                        _ptr(dqkv), B, T, H, W // (3 * H), _stream()), "attention_bwd")
+    p, seed, site = drop if drop is not None else (0.0, 0, -1)
+    _check(load().ttsb200_attention_bwd_drop(_ptr(qkv, torch.bfloat16, "qkv"), _ptr(dctx, torch.bfloat16, "dctx"),
+                                             _ptr(mask, torch.uint8, "mask"), _ptr(kv_len, torch.int32, "kv_len"),
+                                             _ptr(lse2, torch.float32, "lse2"), _ptr(delta, torch.float32, "delta"),
+                                             _ptr(dqkv), B, T, H, W // (3 * H), float(p), int(seed), int(site),
+                                             _stream()), "attention_bwd")
     _count(2)
     return dqkv
 
 
 def layernorm_bwd(x, gamma, *, beta=None, g_f32=None, g_bf16=None, g_row=None, g_vec=None, row_mask=None,
                   add_f32=None, relu_gate=False, dx_f32=None, dx_bf16=None, dgamma=None, dbeta=None, dvec=None,
-                  dscal=None, eps: float = 1e-5) -> None:
+                  dscal=None, eps: float = 1e-5, drop_p: float = 0.0, drop_seed: int = 0, site_g: int = -1,
+                  site_dx: int = -1, dx_mode: int = 0) -> None:
+    """site_g / site_dx / dx_mode: the forward pass's dropout masks, see ttsb200_layernorm_bwd_drop."""
     D = x.shape[-1]
     rows = x.numel() // D
-    _check(load().ttsb200_layernorm_bwd(
+    _check(load().ttsb200_layernorm_bwd_drop(
         _ptr(x, torch.float32, "x"), _ptr(gamma, torch.float32, "gamma"), _ptr(beta, torch.float32, "beta"),
         _ptr(g_f32, torch.float32, "g_f32"), _ptr(g_bf16, torch.bfloat16, "g_bf16"),
         _ptr(g_row, torch.float32, "g_row"), _ptr(g_vec, torch.float32, "g_vec"),
         _ptr(row_mask, torch.uint8, "row_mask"), _ptr(add_f32, torch.float32, "add_f32"), int(relu_gate),
         _ptr(dx_f32, torch.float32, "dx_f32"), _ptr(dx_bf16, torch.bfloat16, "dx_bf16"),
         _ptr(dgamma, torch.float32, "dgamma"), _ptr(dbeta, torch.float32, "dbeta"),
-        _ptr(dvec, torch.float32, "dvec"), _ptr(dscal, torch.float32, "dscal"), rows, D, eps, _stream()),
-        "layernorm_bwd")
+        _ptr(dvec, torch.float32, "dvec"), _ptr(dscal, torch.float32, "dscal"), rows, D, eps, float(drop_p),
+        int(drop_seed), int(site_g), int(site_dx), int(dx_mode), _stream()), "layernorm_bwd")
     _count()
 
 
@@ -444,21 +465,22 @@ def bn_stats(x: torch.Tensor, stats: torch.Tensor) -> None:
     _count()
 
 
-def bn_tanh_fwd(x, mean_rstd, gamma, beta, h) -> None:
+def bn_tanh_fwd(x, mean_rstd, gamma, beta, h, drop: tuple = (0.0, 0, -1)) -> None:
     Cc = x.shape[-1]
     _check(load().ttsb200_bn_tanh_fwd(_ptr(x, torch.float32, "x"), _ptr(mean_rstd, torch.float32, "mean_rstd"),
                                       _ptr(gamma, torch.float32, "gamma"), _ptr(beta, torch.float32, "beta"),
-                                      _ptr(h, torch.bfloat16, "h"), x.numel() // Cc, Cc, _stream()), "bn_tanh_fwd")
+                                      _ptr(h, torch.bfloat16, "h"), x.numel() // Cc, Cc, float(drop[0]), int(drop[1]),
+                                      int(drop[2]), _stream()), "bn_tanh_fwd")
     _count()
 
 
-def bn_tanh_bwd(dh, h, x, mean_rstd, gamma, red, dx, inv_count: float, apply: bool) -> None:
+def bn_tanh_bwd(dh, h, x, mean_rstd, gamma, red, dx, inv_count: float, apply: bool, drop: tuple = (0.0, 0, -1)) -> None:
     Cc = x.shape[-1]
     _check(load().ttsb200_bn_tanh_bwd(_ptr(dh, torch.bfloat16, "dh"), _ptr(h, torch.bfloat16, "h"),
                                       _ptr(x, torch.float32, "x"), _ptr(mean_rstd, torch.float32, "mean_rstd"),
                                       _ptr(gamma, torch.float32, "gamma"), _ptr(red, torch.float32, "red"),
                                       _ptr(dx, torch.bfloat16, "dx"), x.numel() // Cc, Cc, inv_count, int(apply),
-                                      _stream()), "bn_tanh_bwd")
+                                      float(drop[0]), int(drop[1]), int(drop[2]), _stream()), "bn_tanh_bwd")
     _count()
 
 
@@ -568,13 +590,15 @@ def attention_x3(qkv_split: torch.Tensor, mask: torch.Tensor, kv_len: torch.Tens
     return ctx
 
 
-def xrow(mode: int, a: torch.Tensor, ln1: tuple, *, b0=None, b0_split=None, c=None, ln2=None, dot_w=None, dot_b=None,
-         row_mask=None, eps: float = 1e-5, s_out=None, z_out=None, out_split=None, out_bf16=None, out_f32=None,
-         out_row=None) -> None:
+def xrow(mode: int, a: torch.Tensor, ln1: tuple, *, b0=None, b0_bf16=None, b0_split=None, c=None, ln2=None, dot_w=None,
+         dot_b=None, row_mask=None, eps: float = 1e-5, s_out=None, z_out=None, out_split=None, out_bf16=None,
+         out_f32=None, out_row=None, drop_p: float = 0.0, drop_seed: int = 0, site_b: int = -1, site_s: int = -1,
+         site_t: int = -1) -> None:
     D = a.shape[-1]
     rows = a.numel() // D
     g2, b2 = (ln2 if ln2 is not None else (None, None))
     _check(load().ttsb200_xrow(mode, _ptr(a, torch.float32, "a"), _ptr(b0, torch.float32, "b0"),
+                               _ptr(b0_bf16, torch.bfloat16, "b0_bf16"),
                                _ptr(b0_split, torch.float16, "b0_split"), _ptr(c, torch.float32, "c"),
                                _ptr(ln1[0], torch.float32, "g1"), _ptr(ln1[1], torch.float32, "b1"),
                                _ptr(g2, torch.float32, "g2"), _ptr(b2, torch.float32, "b2"),
@@ -582,5 +606,29 @@ def xrow(mode: int, a: torch.Tensor, ln1: tuple, *, b0=None, b0_split=None, c=No
                                _ptr(row_mask, torch.uint8, "row_mask"), eps, _ptr(s_out, torch.float32, "s_out"),
                                _ptr(z_out, torch.float32, "z_out"), _ptr(out_split, torch.float16, "out_split"),
                                _ptr(out_bf16, torch.bfloat16, "out_bf16"), _ptr(out_f32, torch.float32, "out_f32"),
-                               _ptr(out_row, torch.float32, "out_row"), rows, D, _stream()), "xrow")
+                               _ptr(out_row, torch.float32, "out_row"), rows, D, float(drop_p), int(drop_seed),
+                               int(site_b), int(site_s), int(site_t), _stream()), "xrow")
     _count()
+
+
+# --------------------------------------------------------------------------------------------------
+# dropout (training): counter-based masks, regenerated from (p, seed, site) wherever they are needed
+# --------------------------------------------------------------------------------------------------
+def dropout_(x: torch.Tensor, p: float, seed: int, site: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """x * m (m = 0 or 1/(1-p)), in place unless `out` is given.  fp32 or bf16."""
+    if x.dtype not in (torch.float32, torch.bfloat16):
+        raise TypeError("dropout_: fp32 or bf16")
+    dst = x if out is None else out
+    if dst.dtype != x.dtype or dst.numel() != x.numel():
+        raise ValueError("dropout_: out must match x")
+    _check(load().ttsb200_dropout(_ptr(x, None, "x"), _ptr(dst, None, "out"), int(x.dtype == torch.bfloat16), x.numel(),
+                                  float(p), int(seed), int(site), _stream()), "dropout")
+    _count()
+    return dst
+
+
+def dropout_mask(n: int, p: float, seed: int, site: int, device="cuda") -> torch.Tensor:
+    out = torch.empty(n, device=device, dtype=torch.float32)
+    _check(load().ttsb200_dropout_mask(_ptr(out), n, float(p), int(seed), int(site), _stream()), "dropout_mask")
+    _count()
+    return out

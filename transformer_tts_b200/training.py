@@ -38,15 +38,70 @@ def _t(w_taps: torch.Tensor) -> torch.Tensor:
     return wt.contiguous()
 
 
-def require_zero_dropout(model) -> None:
-    """Parity with the reference is only defined at dropout 0 and no RNG-mask kernels exist yet."""
-    bad = [n for n, m in model.named_modules()
-           if (isinstance(m, torch.nn.Dropout) and m.p > 0) or (isinstance(getattr(m, "dropout", None), float)
-                                                                 and m.dropout > 0)]
-    if bad:
-        raise NotImplementedError("training with dropout > 0 is not built (no RNG-mask kernels yet); construct the "
-                                  "model with dropout = dropout_postnet = dropout_variance_adaptor = 0; offending: "
-                                  + ", ".join(bad[:4]))
+class DropoutPlan:
+    """Dropout call sites of the reference's training forward and their probabilities.
+
+    The reference constructs the model with dropout = hp.dropout (0.1), dropout_postnet = 0.5 and
+    dropout_variance_adaptor (train_fastspeech2.py:381-389).  Every call site of one module instance gets a `site`
+    number; a mask is a pure function of (seed, site, element index) (csrc/common.cuh), so the forward kernels apply
+    it and the backward kernels regenerate it.  The seed advances with every training forward.  Sites per FFT block:
+    attention probabilities (Models/modules.py:18-19), dropout_1 on the attention output (layers.py:33), the
+    FeedForward's own dropout before its LayerNorm (modules.py:86), dropout_2 on the FeedForward output (layers.py:40);
+    per stack the PositionalEncoder's (modules.py:111); per VariancePredictor dropout1 / dropout2
+    (varianceadaptor.py:219,222); per PostNet conv the dropout after tanh (postnets.py:71-73)."""
+
+    def __init__(self, model, base_seed: int = 0):
+        self.base_seed = int(base_seed)
+        self.calls = 0
+        self._sites: Dict[str, int] = {}
+        enc, dec, va, pn = model.encoder, model.decoder, model.variance_adaptor, model.postnet
+        self.p_stack = {"enc": float(enc.pe.dropout.p), "dec": float(dec.pe.dropout.p)}
+        for tag, st in (("enc", enc), ("dec", dec)):
+            for l in st.layers:
+                ps = {float(l.dropout_1.p), float(l.dropout_2.p), float(l.ff.dropout.p), float(l.attn.dropout or 0.0),
+                      self.p_stack[tag]}
+                if len(ps) != 1:
+                    raise NotImplementedError(f"{tag}: one dropout probability per FFT stack (the reference passes a "
+                                              f"single `dropout` to all of its call sites), got {sorted(ps)}")
+        self.p_pred = {n: float(getattr(va, n + "_predictor").dropout1.p) for n in ("duration", "pitch", "energy")}
+        for n in self.p_pred:
+            if float(getattr(va, n + "_predictor").dropout2.p) != self.p_pred[n]:
+                raise NotImplementedError("VariancePredictor: dropout1 and dropout2 share one probability in the reference")
+        self.p_post = float(pn.dropout1.p)
+        if any(float(d.p) != self.p_post for d in pn.dropout_list):
+            raise NotImplementedError("PostConvNet: one dropout probability")
+        for name, p in list(self.p_stack.items()) + list(self.p_pred.items()) + [("postnet", self.p_post)]:
+            if not 0.0 <= p < 1.0:
+                raise ValueError(f"dropout probability of {name} must be in [0, 1), got {p}")
+
+    @property
+    def active(self) -> bool:
+        return any(p > 0 for p in self.p_stack.values()) or any(p > 0 for p in self.p_pred.values()) or self.p_post > 0
+
+    def site(self, name: str) -> int:
+        return self._sites.setdefault(name, len(self._sites))
+
+    def prob(self, name: str) -> float:
+        """Probability of the call site `name` ("enc.3.attn", "dec.pe", "pitch.drop1", "postnet.2", ...)."""
+        head = name.split(".")[0]
+        if head in self.p_stack:
+            return self.p_stack[head]
+        if head in self.p_pred:
+            return self.p_pred[head]
+        if head == "postnet":
+            return self.p_post
+        raise KeyError(name)
+
+    def mask(self, name: str, shape, seed: int, device="cuda") -> torch.Tensor:
+        """The mask (0 or 1/(1-p)) the kernels apply at `name` for `seed`, materialised (tests / debugging only)."""
+        n = 1
+        for d in shape:
+            n *= int(d)
+        return lib.dropout_mask(n, self.prob(name), seed, self.site(name), device=device).view(*shape)
+
+    def next_seed(self) -> int:
+        self.calls += 1
+        return (self.base_seed * 0x9E3779B97F4A7C15 + self.calls * 0xD1B54A32D192ED03) & 0xFFFFFFFFFFFFFFFF
 
 
 def allreduce_mean_scale(flat_g: torch.Tensor, world: int, group=None) -> float:
@@ -89,13 +144,13 @@ class Trainer:
     def __init__(self, model, *, lr_max: float = 1e-3, betas=(0.9, 0.98), eps: float = 1e-9, clip: float = 1.0,
                  warmup_step: int = 4000, warmup_factor: float = 1.0, fixed_lr: Optional[float] = None,
                  process_group=None, sync_bn: bool = True, bn_momentum: float = 0.1, flatten: bool = True,
-                 optimizer: str = "adam", overlap_allreduce: bool = False):
+                 optimizer: str = "adam", overlap_allreduce: bool = False, dropout_seed: int = 0):
         """flatten=True (training loop owner): parameters are re-pointed into one flat fp32 buffer, `p.grad` are
         views of the flat gradient buffer and optimizer_step() runs the fused clip+Adam kernel.
         flatten=False (drop-in autograd mode, see `autograd_forward`): parameters are left alone, only the flat
         gradient buffer exists and the caller's torch optimizer owns the update."""
         lib.load()
-        require_zero_dropout(model)
+        self.drop = DropoutPlan(model, base_seed=dropout_seed)
         # hp.optimizer (train_fastspeech2.py:412-416): 'radam' -> radam.RAdam at the fixed rate lr_max (the Noam
         # schedule is skipped for it, :117-120); anything else -> torch.optim.Adam at the Noam rate
         self.optimizer = optimizer.lower()
@@ -194,7 +249,7 @@ class Trainer:
     # ------------------------------------------------------------------------------------------
     # FFT stack (Models/encoder.py:83-112, layers.py:29-41)
     # ------------------------------------------------------------------------------------------
-    def _stack_fwd(self, enc, src, mask_u8, kv):
+    def _stack_fwd(self, enc, src, mask_u8, kv, tag: str = "enc", seed: int = 0):
         t = enc._cache()
         B, T = src.shape[0], src.shape[1]
         D = enc.norm.weight.numel()
@@ -206,12 +261,17 @@ class Trainer:
         x = torch.empty((B, T, D), device=dev, dtype=torch.float32)
         xn = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
         ln_first = caches[0]["ln1"]
+        pd = self.drop.p_stack[tag]          # one probability for every dropout call site of this stack
+        S = lambda name: self.drop.site(f"{tag}.{name}")  # noqa: E731
         if enc.embedding:
             lib.embed_pe_ln(src.contiguous(), t["table"], pe, t["alpha"], ln_first[0], ln_first[1], E.LN_EPS, x, xn)
         else:
             lib.conv_gemm(src, t["wemb"], t["bemb"], block_n=D, epi=lib.EPI_RES_LN, res_f32=pe, res_bstride=0,
                           res_tstride=D, res_scale=t["alpha"], ln1=ln_first, out_f32=x, out_bf16=xn)
-        tape = dict(src=src, mask=mask_u8, kv=kv, pe=pe, T=T, blocks=[], caches=caches, top=t)
+        if pd > 0:  # PositionalEncoder's dropout (modules.py:111): x0 := drop(x0), then the first norm_1 again
+            lib.dropout_(x, pd, seed, S("pe"))
+            lib.layernorm(x, ln_first[0], ln_first[1], E.LN_EPS, y_bf16=xn)
+        tape = dict(src=src, mask=mask_u8, kv=kv, pe=pe, T=T, blocks=[], caches=caches, top=t, tag=tag, seed=seed, pd=pd)
         H = enc.heads
         for i, lc in enumerate(caches):
             k = lc["k"]
@@ -220,15 +280,31 @@ class Trainer:
             lib.conv_gemm(xn, lc["wqkv"], lc["bqkv"], block_n=192, out_bf16=qkv)
             ctx = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
             lse = torch.empty((B, H, T), device=dev, dtype=torch.float32)
-            lib.attention_fwd(qkv, mask_u8, kv, ctx, H, lse2=lse)
+            lib.attention_fwd(qkv, mask_u8, kv, ctx, H, lse2=lse, drop=(pd, seed, S(f"{i}.attn")))
             y = torch.empty((B, T, D), device=dev, dtype=torch.float32)
             yn = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
-            lib.conv_gemm(ctx, lc["wo"], lc["bo"], block_n=D, epi=lib.EPI_RES_LN, res_f32=x, res_bstride=T * D,
-                          res_tstride=D, ln1=lc["ln2"], out_f32=y, out_bf16=yn)
             h = torch.empty((B, T, 4 * D), device=dev, dtype=torch.bfloat16)
-            lib.conv_gemm(yn, lc["w1"], lc["b1"], taps=k, pad_left=k // 2, block_n=256, act=lib.ACT_RELU, out_bf16=h)
             upre = torch.empty((B, T, D), device=dev, dtype=torch.float32)
-            z, zn = E.run_ffn2(lc, h, yn, y, next_ln, pre_f32=upre)
+            if pd > 0:
+                # With dropout between the GEMM and its residual / LayerNorm the fused epilogues do not apply: the GEMMs
+                # leave acc + bias in fp32 and one fp32 row kernel per half block does dropout + residual + LayerNorm.
+                o = torch.empty((B, T, D), device=dev, dtype=torch.float32)
+                lib.conv_gemm(ctx, lc["wo"], lc["bo"], block_n=128, out_f32=o)
+                lib.xrow(lib.XROW_ADD_LN, x, lc["ln2"], b0=o, s_out=y, out_bf16=yn, eps=E.LN_EPS, drop_p=pd,
+                         drop_seed=seed, site_b=S(f"{i}.drop1"))                                     # layers.py:33,35
+                lib.conv_gemm(yn, lc["w1"], lc["b1"], taps=k, pad_left=k // 2, block_n=256, act=lib.ACT_RELU, out_bf16=h)
+                u = torch.empty((B, T, D), device=dev, dtype=torch.float32)
+                lib.conv_gemm(h, lc["w2"], lc["b2"], taps=k, pad_left=k // 2, block_n=128, out_f32=u)
+                z = torch.empty((B, T, D), device=dev, dtype=torch.float32)
+                zn = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
+                lib.xrow(lib.XROW_FFN_TAIL, u, lc["ln_ff"], b0_bf16=yn, c=y, ln2=next_ln, s_out=upre, z_out=z, out_bf16=zn,
+                         eps=E.LN_EPS, drop_p=pd, drop_seed=seed, site_s=S(f"{i}.ff"),
+                         site_t=S(f"{i}.drop2"))                                    # modules.py:85-87, layers.py:40
+            else:
+                lib.conv_gemm(ctx, lc["wo"], lc["bo"], block_n=D, epi=lib.EPI_RES_LN, res_f32=x, res_bstride=T * D,
+                              res_tstride=D, ln1=lc["ln2"], out_f32=y, out_bf16=yn)
+                lib.conv_gemm(yn, lc["w1"], lc["b1"], taps=k, pad_left=k // 2, block_n=256, act=lib.ACT_RELU, out_bf16=h)
+                z, zn = E.run_ffn2(lc, h, yn, y, next_ln, pre_f32=upre)
             tape["blocks"].append(dict(x=x, xn=xn, qkv=qkv, ctx=ctx, lse=lse, y=y, yn=yn, h=h, upre=upre))
             x, xn = z, zn
         tape["z_last"] = x
@@ -242,6 +318,9 @@ class Trainer:
         dev = g_out.device
         H = enc.heads
         mask, kv = tape["mask"], tape["kv"]
+        pd, seed, tag = tape["pd"], tape["seed"], tape["tag"]
+        S = lambda name: self.drop.site(f"{tag}.{name}") if pd > 0 else -1  # noqa: E731
+        dk = dict(drop_p=pd, drop_seed=seed)
         f32 = lambda *s: torch.empty(s, device=dev, dtype=torch.float32)  # noqa: E731
         bf = lambda *s: torch.empty(s, device=dev, dtype=torch.bfloat16)  # noqa: E731
         dz = f32(B, T, D)
@@ -254,8 +333,10 @@ class Trainer:
             k = lc["k"]
             # z = y + LN_ff(upre)
             dupre, dupre_bf = f32(B, T, D), bf(B, T, D)
+            # dropout: LN_ff's output was dropped (dropout_2), its input is the FeedForward dropout's output
             lib.layernorm_bwd(s["upre"], lc["ln_ff"][0], g_f32=dz, dx_f32=dupre, dx_bf16=dupre_bf,
-                              dgamma=G(ff.layer_norm.weight), dbeta=G(ff.layer_norm.bias))
+                              dgamma=G(ff.layer_norm.weight), dbeta=G(ff.layer_norm.bias), site_g=S(f"{i}.drop2"),
+                              site_dx=S(f"{i}.ff"), dx_mode=1 if pd > 0 else 0, **dk)
             # upre = conv2(h) + b2 + yn
             lib.colsum(dupre_bf, G(ff.f_2.bias))
             lib.conv_wgrad(dupre_bf, s["h"], G(ff.f_2.weight), taps=k, pad_left=k // 2, conv_layout=True)
@@ -270,15 +351,17 @@ class Trainer:
                           res_f32=dupre, res_bstride=T * D, res_tstride=D, out_f32=dyn)
             # yn = norm_2(y); z = y + ff(yn)
             dy, dy_bf = f32(B, T, D), bf(B, T, D)
+            # dropout: dy_bf feeds the gradients of the attention branch, whose output dropout_1 masked (dx_mode 2)
             lib.layernorm_bwd(s["y"], lc["ln2"][0], g_f32=dyn, add_f32=dz, dx_f32=dy, dx_bf16=dy_bf,
-                              dgamma=G(layer.norm_2.weight), dbeta=G(layer.norm_2.bias))
+                              dgamma=G(layer.norm_2.weight), dbeta=G(layer.norm_2.bias), site_dx=S(f"{i}.drop1"),
+                              dx_mode=2 if pd > 0 else 0, **dk)
             # y = x + ctx Wo^T + bo
             lib.colsum(dy_bf, G(a.out.bias))
             lib.conv_wgrad(dy_bf, s["ctx"], G(a.out.weight))
             dctx = bf(B, T, D)
             lib.conv_gemm(dy_bf, _t(lc["wo"]), self.zeros(D), block_n=192, out_bf16=dctx)
             delta = lib.attn_delta(dctx, s["ctx"], H)
-            dqkv = lib.attention_bwd(s["qkv"], dctx, mask, kv, s["lse"], delta, H)
+            dqkv = lib.attention_bwd(s["qkv"], dctx, mask, kv, s["lse"], delta, H, drop=(pd, seed, S(f"{i}.attn")))
             for j, lin in enumerate((a.q_linear, a.k_linear, a.v_linear)):
                 lib.colsum(dqkv, G(lin.bias), cols=D, col_off=j * D)
                 lib.conv_wgrad(dqkv, s["xn"], G(lin.weight), n_off=j * D, N=D)
@@ -287,8 +370,11 @@ class Trainer:
             # xn = norm_1(x); y = x + attn(xn)
             dx = f32(B, T, D)
             dz_bf = bf(B, T, D) if i == 0 else None
+            # dropout: the first block's input is the PositionalEncoder dropout's output
+            first = i == 0 and pd > 0
             lib.layernorm_bwd(s["x"], lc["ln1"][0], g_f32=dxn, add_f32=dy, dx_f32=dx, dx_bf16=dz_bf,
-                              dgamma=G(layer.norm_1.weight), dbeta=G(layer.norm_1.bias))
+                              dgamma=G(layer.norm_1.weight), dbeta=G(layer.norm_1.bias),
+                              site_dx=S("pe") if first else -1, dx_mode=1 if first else 0, **dk)
             dz = dx
         # x0 = embed(src) + alpha * pe
         t = tape["top"]
@@ -306,20 +392,30 @@ class Trainer:
     # ------------------------------------------------------------------------------------------
     # VariancePredictor (Models/varianceadaptor.py:216-231)
     # ------------------------------------------------------------------------------------------
-    def _pred_fwd(self, pred, x_bf16, mask_u8):
+    def _pred_fwd(self, pred, x_bf16, mask_u8, name: str = "duration", seed: int = 0):
         t = E.predictor_cache(pred)
         B, T, _ = x_bf16.shape
         fs = t["b1"].numel()
         dev = x_bf16.device
+        pd = self.drop.p_pred[name]
         h = torch.empty((B, T, fs), device=dev, dtype=torch.bfloat16)
         r1 = torch.empty((B, T, fs), device=dev, dtype=torch.float32)
-        lib.conv_gemm(x_bf16, t["w1"], t["b1"], taps=3, pad_left=1, block_n=fs, epi=lib.EPI_RELU_LN, ln1=t["ln1"],
-                      out_bf16=h, pre_f32=r1)
         out = torch.empty((B, T), device=dev, dtype=torch.float32)
         r2 = torch.empty((B, T, fs), device=dev, dtype=torch.float32)
-        lib.conv_gemm(h, t["w2"], t["b2"], taps=3, pad_left=1, block_n=fs, epi=lib.EPI_RELU_LN_DOT, ln1=t["ln2"],
-                      dot_w=t["dw"], dot_b=t["db"], row_mask=mask_u8, out_row=out, pre_f32=r2)
-        return out, dict(x=x_bf16, h=h, r1=r1, r2=r2, mask=mask_u8, t=t)
+        if pd > 0:  # dropout after each LayerNorm (varianceadaptor.py:219,222): GEMM + ReLU in fp32, then a row kernel
+            s1, s2 = self.drop.site(f"{name}.drop1"), self.drop.site(f"{name}.drop2")
+            lib.conv_gemm(x_bf16, t["w1"], t["b1"], taps=3, pad_left=1, block_n=128, act=lib.ACT_RELU, out_f32=r1)
+            lib.xrow(lib.XROW_ADD_LN, r1, t["ln1"], out_bf16=h, eps=E.LN_EPS, drop_p=pd, drop_seed=seed, site_t=s1)
+            lib.conv_gemm(h, t["w2"], t["b2"], taps=3, pad_left=1, block_n=128, act=lib.ACT_RELU, out_f32=r2)
+            lib.xrow(lib.XROW_LN_DOT, r2, t["ln2"], dot_w=t["dw"], dot_b=t["db"], row_mask=mask_u8, out_row=out,
+                     eps=E.LN_EPS, drop_p=pd, drop_seed=seed, site_t=s2)
+        else:
+            s1 = s2 = -1
+            lib.conv_gemm(x_bf16, t["w1"], t["b1"], taps=3, pad_left=1, block_n=fs, epi=lib.EPI_RELU_LN, ln1=t["ln1"],
+                          out_bf16=h, pre_f32=r1)
+            lib.conv_gemm(h, t["w2"], t["b2"], taps=3, pad_left=1, block_n=fs, epi=lib.EPI_RELU_LN_DOT, ln1=t["ln2"],
+                          dot_w=t["dw"], dot_b=t["db"], row_mask=mask_u8, out_row=out, pre_f32=r2)
+        return out, dict(x=x_bf16, h=h, r1=r1, r2=r2, mask=mask_u8, t=t, dk=dict(drop_p=pd, drop_seed=seed), s1=s1, s2=s2)
 
     def _pred_bwd(self, pred, tape, g_out: torch.Tensor, add_f32: Optional[torch.Tensor]) -> torch.Tensor:
         """g_out (B,T) fp32 -> fp32 gradient w.r.t. the predictor input (+ add_f32)."""
@@ -332,14 +428,15 @@ class Trainer:
         lib.layernorm_bwd(tape["r2"], t["ln2"][0], beta=t["ln2"][1], g_row=g_out.contiguous(), g_vec=t["dw"],
                           row_mask=tape["mask"], relu_gate=True, dx_bf16=dc2, dgamma=G(pred.layer_norm2.weight),
                           dbeta=G(pred.layer_norm2.bias), dvec=G(pred.linear_layer.weight),
-                          dscal=G(pred.linear_layer.bias))
+                          dscal=G(pred.linear_layer.bias), site_g=tape["s2"], **tape["dk"])
         lib.colsum(dc2, G(pred.conv2.bias))
         lib.conv_wgrad(dc2, tape["h"], G(pred.conv2.weight), taps=3, pad_left=1, conv_layout=True)
         dh = torch.empty((B, T, fs), device=dev, dtype=torch.float32)
         lib.conv_gemm(dc2, _t(t["w2"]), self.zeros(fs), taps=3, pad_left=1, block_n=128, out_f32=dh)
         dc1 = torch.empty((B, T, fs), device=dev, dtype=torch.bfloat16)
         lib.layernorm_bwd(tape["r1"], t["ln1"][0], g_f32=dh, relu_gate=True, dx_bf16=dc1,
-                          dgamma=G(pred.layer_norm1.weight), dbeta=G(pred.layer_norm1.bias))
+                          dgamma=G(pred.layer_norm1.weight), dbeta=G(pred.layer_norm1.bias), site_g=tape["s1"],
+                          **tape["dk"])
         lib.colsum(dc1, G(pred.conv1.bias))
         lib.conv_wgrad(dc1, tape["x"], G(pred.conv1.weight), taps=3, pad_left=1, conv_layout=True)
         dx = torch.empty((B, T, Din), device=dev, dtype=torch.float32)
@@ -361,7 +458,7 @@ class Trainer:
             bn.num_batches_tracked += 1
         return ms, count
 
-    def _postnet_fwd(self, pn, d_bf16):
+    def _postnet_fwd(self, pn, d_bf16, seed: int = 0):
         t = E.postnet_cache(pn)
         B, T, D = d_bf16.shape
         dev = d_bf16.device
@@ -373,15 +470,17 @@ class Trainer:
         bns = [pn.pre_batchnorm] + list(pn.batch_norm_list)
         h = mel_pre_bf
         layers = []
-        for (w, _, _), cv, bn in zip(t["convs"], convs, bns):
+        pp = self.drop.p_post
+        for li, ((w, _, _), cv, bn) in enumerate(zip(t["convs"], convs, bns)):
+            dr = (pp, seed, self.drop.site(f"postnet.{li}") if pp > 0 else -1)
             c = torch.empty((B, T, D), device=dev, dtype=torch.float32)
             lib.conv_gemm(h, w, cv.bias, taps=5, pad_left=4, block_n=192, out_f32=c)
             stats = torch.zeros((2, D), device=dev, dtype=torch.float32)
             lib.bn_stats(c, stats)
             ms, count = self._bn_finish_stats(stats, B * T, bn)
             o = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
-            lib.bn_tanh_fwd(c, ms, bn.weight, bn.bias, o)
-            layers.append(dict(x=h, c=c, ms=ms, h=o, count=count, w=w))
+            lib.bn_tanh_fwd(c, ms, bn.weight, bn.bias, o, drop=dr)  # postnets.py:71-73 incl. the dropout after tanh
+            layers.append(dict(x=h, c=c, ms=ms, h=o, count=count, w=w, drop=dr))
             h = o
         mel_post = torch.empty((B, T, md), device=dev, dtype=torch.float32)
         lib.conv_gemm(h, t["w2"], t["b2"], taps=5, pad_left=4, block_n=md, res_f32=mel_pre, res_bstride=T * md,
@@ -408,13 +507,13 @@ class Trainer:
         for i in range(len(convs) - 1, -1, -1):
             s, cv, bn = tape["layers"][i], convs[i], bns[i]
             red = torch.zeros((2, D), device=dev, dtype=torch.float32)
-            lib.bn_tanh_bwd(dh, s["h"], s["c"], s["ms"], bn.weight, red, None, 1.0 / s["count"], apply=False)
+            lib.bn_tanh_bwd(dh, s["h"], s["c"], s["ms"], bn.weight, red, None, 1.0 / s["count"], apply=False, drop=s["drop"])
             G(bn.bias).add_(red[0])
             G(bn.weight).add_(red[1])
             if self.sync_bn:  # SyncBatchNorm backward: the two reductions are summed over all ranks
                 dist.all_reduce(red, group=self.pg)
             dc = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
-            lib.bn_tanh_bwd(dh, s["h"], s["c"], s["ms"], bn.weight, red, dc, 1.0 / s["count"], apply=True)
+            lib.bn_tanh_bwd(dh, s["h"], s["c"], s["ms"], bn.weight, red, dc, 1.0 / s["count"], apply=True, drop=s["drop"])
             lib.colsum(dc, G(cv.bias))
             lib.conv_wgrad(dc, s["x"], G(cv.weight), taps=5, pad_left=4, conv_layout=True)
             if i > 0:
@@ -441,26 +540,28 @@ class Trainer:
         dev = text.device
         sm = E.mask_to_u8(src_mask, B, L, dev)
         kv_src = lib.mask_lengths(sm)
-        e_bf, tape_enc = self._stack_fwd(enc, text, sm, kv_src)
+        seed = self.drop.next_seed() if self.drop.active else 0   # a new set of dropout masks per training forward
+        self.last_dropout_seed = seed
+        e_bf, tape_enc = self._stack_fwd(enc, text, sm, kv_src, "enc", seed)
         mm = E.mask_to_u8(mel_mask, B, mel_mask.shape[-1], dev)
         Tm = mm.shape[1]
         # ---- variance adaptor (varianceadaptor.py:66-129, teacher-forced) ----
-        log_d, tape_d = self._pred_fwd(va.duration_predictor, e_bf, sm)
+        log_d, tape_d = self._pred_fwd(va.duration_predictor, e_bf, sm, "duration", seed)
         dur = torch.clamp(alignment, min=0).to(torch.int32).contiguous()
         cum, mel_len = lib.lr_scan(dur)
         xe, _, _, _ = lib.lr_expand(e_bf, cum, mel_len, Tm, want_aux=False)
-        p, tape_p = self._pred_fwd(va.pitch_predictor, xe, mm)
-        e, tape_e = self._pred_fwd(va.energy_predictor, xe, mm)
+        p, tape_p = self._pred_fwd(va.pitch_predictor, xe, mm, "pitch", seed)
+        e, tape_e = self._pred_fwd(va.energy_predictor, xe, mm, "energy", seed)
         pb, eb = va._bins(dev)
         tabs = va._tables()
         f0 = f0.to(torch.float32).contiguous()
         energy = energy.to(torch.float32).contiguous()
         va_x, p_idx, e_idx = lib.bucket_embed_add(xe, f0, energy, pb, eb, tabs["ptab"], tabs["etab"], want_idx=True)
         kv_mel = lib.mask_lengths(mm)
-        d_bf, tape_dec = self._stack_fwd(dec, va_x, mm, kv_mel)
-        mel_pre, mel_post, tape_pn = self._postnet_fwd(pn, d_bf)
+        d_bf, tape_dec = self._stack_fwd(dec, va_x, mm, kv_mel, "dec", seed)
+        mel_pre, mel_post, tape_pn = self._postnet_fwd(pn, d_bf, seed)
         tape = dict(enc=tape_enc, dec=tape_dec, pn=tape_pn, d=tape_d, p=tape_p, e=tape_e, cum=cum, p_idx=p_idx,
-                    e_idx=e_idx, Tm=Tm, shapes=[mel_pre.shape, mel_post.shape, log_d.shape, p.shape, e.shape])
+                    e_idx=e_idx, Tm=Tm, seed=seed, shapes=[mel_pre.shape, mel_post.shape, log_d.shape, p.shape, e.shape])
         return dict(mel_pre=mel_pre, mel_post=mel_post, log_d=log_d, p=p, e=e, va_x=va_x, text_dur=xe,
                     f0=f0, energy=energy), tape
 
