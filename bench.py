@@ -254,9 +254,10 @@ def kernel_rooflines(model, peaks, mel_len):
                       res_f32=x32[i], res_bstride=T * D, res_tstride=D, ln1=lc["ln_ff"], ln2=ln, out_f32=o32[i],
                       out_bf16=ob[i], tile_map=tmap)
 
-    def t_ffn(i):
-        t_ffn1(i)
-        t_ffn2(i)
+    z32 = [torch.empty(B, T, D, device=dev) for _ in range(NS)]
+
+    def t_ffn(i):  # the kernel the inference step runs for k=1 blocks (csrc/ffn_fused.cuh)
+        lib.ffn_fused(xs[i], lc["w1"], lc["b1"], lc["w2"], lc["b2"], x32[i], lc["ln_ff"], ln, z32[i], ob[i], tile_map=tmap)
 
     def t_lr(i):
         lib.lr_expand(xe[i], cum, ml, Tlr, want_aux=True)
@@ -278,12 +279,12 @@ def kernel_rooflines(model, peaks, mel_len):
         ("attention", "attention_fwd decoder masked self-attention", t_att, att_flops, M * D * s2 * 4),
         ("out_proj", "conv_gemm<384,RES_LN> decoder out-proj + residual + LayerNorm", t_out, 2 * M * D * D,
          M * D * (2 * s2 + 8)),
-        ("ffn1", "conv_gemm<256,AFFINE,A-stationary> decoder FFN conv1 + ReLU", t_ffn1, 2 * M * D * 4 * D * k,
-         M * D * s2 * 5),
-        ("ffn2", "conv_gemm<384,FFN2> decoder FFN conv2 + LN + residual + LN", t_ffn2, 2 * M * D * 4 * D * k,
+        ("ffn_fused", "ffn_fused decoder FeedForward, the reference's ONE op (conv1 + ReLU + conv2 + res + LN + res + LN), "
+                      "hidden activation kept in TMEM", t_ffn, 4 * M * D * 4 * D * k, M * D * (s2 + 4 + 4 + s2)),
+        ("ffn1", "conv_gemm<256,AFFINE,A-stationary> FFN conv1 + ReLU (two-kernel path: training, short batches)", t_ffn1,
+         2 * M * D * 4 * D * k, M * D * s2 * 5),
+        ("ffn2", "conv_gemm<384,FFN2> FFN conv2 + LN + residual + LN (two-kernel path)", t_ffn2, 2 * M * D * 4 * D * k,
          M * D * (s2 * 6 + 8)),
-        ("ffn_pair", "decoder FFN as the reference's ONE op (conv1 + ReLU + conv2 + res + LN + res + LN): both launches",
-         t_ffn, 4 * M * D * 4 * D * k, M * D * (s2 + 4 + 4 + s2)),
         ("lr_expand", "lr_expand LengthRegulator frame gather", t_lr, 0,
          B * L * D * s2 + B * L * 4 + M * D * s2 + rows_padded * (4 + 8 + 1) + B * 4),
         ("bucket_embed_add", "bucket_embed_add pitch/energy bucketize + embedding add", t_bucket, 0,
@@ -320,10 +321,7 @@ def kernel_rooflines(model, peaks, mel_len):
         t_hbm = nbytes / (peaks["hbm"] * 1e9)
         bound = "tensor" if t_tc >= t_hbm else "hbm"
         ach, peak, unit = (tf, peaks["tc_burst"], "TFLOP/s") if bound == "tensor" else (gb, peaks["hbm"], "GB/s")
-        if key == "ffn_pair" and "ffn1" in traffic and "ffn2" in traffic:
-            tr = traffic["ffn1"] + traffic["ffn2"]
-        else:
-            tr = traffic.get(key)
+        tr = traffic.get(key)
         out.append({"kernel": name, "key": key, "bound": bound, "achieved": ach, "peak": peak, "unit": unit,
                     "frac": ach / peak, "traffic": tr, "ms_per_launch": ms,
                     "algorithmic_flops_per_launch": flops, "algorithmic_bytes_per_launch": nbytes,

@@ -96,6 +96,16 @@ typedef struct ttsb200_gemm_args {
 
 int ttsb200_conv_gemm(const ttsb200_gemm_args* args, ttsb200_stream_t stream);
 
+/* The FeedForward of a k=1 FFT block as ONE kernel (Models/modules.py:81-88 + Models/layers.py:40,31):
+ *   z = y + LN(relu(x W1^T + b1) W2^T + b2 + x; ln1);  zn = LN(z; ln2)
+ * x bf16 (B,T,384) = norm_2(y); w1 bf16 [1536][384]; w2 bf16 [384][1536]; y / z fp32 (B,T,384); zn bf16.
+ * The 1536-wide hidden activation stays in tensor memory (TMEM): it is neither written to nor read from HBM.
+ * tile_map / tile_count as in ttsb200_gemm_args (NULL = all tiles). */
+int ttsb200_ffn_fused(const void* x_bf16, const void* w1_bf16, const float* b1, const void* w2_bf16, const float* b2,
+                      const float* y_f32, const float* ln1_g, const float* ln1_b, const float* ln2_g, const float* ln2_b,
+                      float eps, float* z_f32, void* zn_bf16, int32_t B, int32_t T, int32_t D, int32_t hidden,
+                      const int32_t* tile_map, const int32_t* tile_count, ttsb200_stream_t stream);
+
 /* Row-tile list of a ragged batch for ttsb200_gemm_args.tile_map: utterance b contributes its first
  * min(m_tiles, ceil((len[b*len_stride] + halo) / 128)) tiles; map has room for B*m_tiles entries, *count receives
  * the number written.  len may be kv_info of ttsb200_mask_lengths (len_stride 2).  No host synchronisation. */

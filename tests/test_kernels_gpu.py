@@ -411,3 +411,52 @@ def test_second_device_in_one_process(L):
             torch.cuda.synchronize()
             outs.append((ctx.cpu(), o.cpu()))
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+
+
+@pytest.mark.parametrize("B,T,ragged", [(2, 128, False), (3, 300, True), (5, 1000, True)])
+def test_ffn_fused_is_bit_identical_to_the_two_kernel_path(B, T, ragged):
+    """csrc/ffn_fused.cuh: conv1 + ReLU + conv2 + residual + LayerNorm + residual + LayerNorm of a k=1 FFT block in one
+    kernel, the hidden activation kept in tensor memory.  Same MMAs in the same order as conv_gemm x 2, so z (fp32) and
+    zn (bf16) must be BIT-IDENTICAL on every computed row; both are also checked against an fp64 reference (whose
+    hidden activation is rounded to bf16 like the kernels')."""
+    import torch.nn.functional as F
+
+    from transformer_tts_b200 import lib
+
+    torch.manual_seed(B * 100 + T)
+    dev, D, Hd = "cuda", 384, 1536
+    x = (torch.randn(B, T, D, device=dev) * 0.7).bfloat16()
+    y = torch.randn(B, T, D, device=dev)
+    w1 = (torch.randn(1, Hd, D, device=dev) * 0.05).bfloat16()
+    w2 = (torch.randn(1, D, Hd, device=dev) * 0.03).bfloat16()
+    b1, b2 = torch.randn(Hd, device=dev) * 0.1, torch.randn(D, device=dev) * 0.1
+    ln1 = (torch.randn(D, device=dev), torch.randn(D, device=dev))
+    ln2 = (torch.randn(D, device=dev), torch.randn(D, device=dev))
+    lens = torch.randint(T // 3, T + 1, (B,)) if ragged else torch.full((B,), T)
+    lens[0] = T
+    mask = (torch.arange(T)[None] < lens[:, None]).to(torch.uint8).to(dev)
+    kv = lib.mask_lengths(mask)
+    for tmap in (None, lib.build_tile_map(kv, T)):
+        z = torch.full((B, T, D), 7.0, device=dev)
+        zn = torch.full((B, T, D), 7.0, device=dev, dtype=torch.bfloat16)
+        lib.ffn_fused(x, w1, b1, w2, b2, y, ln1, ln2, z, zn, tile_map=tmap)
+        h = torch.empty(B, T, Hd, device=dev, dtype=torch.bfloat16)
+        lib.conv_gemm(x, w1, b1, block_n=256, act=lib.ACT_RELU, out_bf16=h)
+        z2, zn2 = torch.empty_like(z), torch.empty_like(zn)
+        lib.conv_gemm(h, w2, b2, block_n=D, epi=lib.EPI_FFN2, res_bf16=x, res_f32=y, res_bstride=T * D, res_tstride=D,
+                      ln1=ln1, ln2=ln2, out_f32=z2, out_bf16=zn2)
+        m_tiles = (T + 127) // 128
+        tiles = ((lens + 127) // 128).clamp(max=m_tiles) if tmap is not None else torch.full((B,), m_tiles)
+        rows = torch.arange(T)[None] < (tiles * 128)[:, None]
+        rows = rows.to(dev)
+        assert torch.equal(z[rows], z2[rows]) and torch.equal(zn[rows], zn2[rows])
+        if tmap is not None:  # rows of dropped tiles are neither read nor written
+            assert bool((z[~rows] == 7.0).all()) and bool((zn[~rows].float() == 7.0).all())
+        xd = x.double()
+        hd = torch.relu(xd @ w1[0].double().T + b1.double()).bfloat16().double()
+        u = hd @ w2[0].double().T + b2.double() + xd
+        zr = y.double() + F.layer_norm(u, (D,), ln1[0].double(), ln1[1].double(), 1e-5)
+        znr = F.layer_norm(zr, (D,), ln2[0].double(), ln2[1].double(), 1e-5)
+        e_z = float((z[rows].double() - zr[rows]).norm() / zr[rows].norm())
+        e_zn = float((zn[rows].double() - znr[rows]).norm() / znr[rows].norm())
+        assert e_z < 1e-4 and e_zn < 4e-3, (e_z, e_zn)

@@ -11,7 +11,7 @@ import sys
 
 # first inference repetition of tools/run_hot_kernels.py, in launch order
 ORDER = [("qkv", "conv_gemm_kernel<192"), ("attention", "attention_fwd_kernel"), ("out_proj", "conv_gemm_kernel<384, 1"),
-         ("ffn1", "conv_gemm_kernel<256"), ("ffn2", "conv_gemm_kernel<384, 2"), ("layernorm", "layernorm_kernel"),
+         ("ffn_fused", "ffn_fused_kernel"), ("ffn1", "conv_gemm_kernel<256"), ("ffn2", "conv_gemm_kernel<384, 2"), ("layernorm", "layernorm_kernel"),
          ("lr_expand", "lr_expand_kernel"), ("bucket_embed_add", "bucket_embed_add_kernel")]
 
 

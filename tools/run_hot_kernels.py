@@ -43,6 +43,7 @@ def main():
                 lib.attention_fwd(qkv, mask, kv, ob, H)
                 lib.conv_gemm(xs, lc["wo"], lc["bo"], block_n=D, epi=lib.EPI_RES_LN, res_f32=x32, res_bstride=T * D,
                               res_tstride=D, ln1=lc["ln2"], out_f32=o32, out_bf16=ob)
+                lib.ffn_fused(xs, lc["w1"], lc["b1"], lc["w2"], lc["b2"], x32, lc["ln_ff"], lc["ln1"], o32, ob)
                 lib.conv_gemm(xs, lc["w1"], lc["b1"], block_n=256, act=lib.ACT_RELU, out_bf16=hs)
                 lib.conv_gemm(hs, lc["w2"], lc["b2"], block_n=D, epi=lib.EPI_FFN2, res_bf16=xs, res_f32=x32,
                               res_bstride=T * D, res_tstride=D, ln1=lc["ln_ff"], ln2=lc["ln1"], out_f32=o32, out_bf16=ob)

@@ -163,6 +163,15 @@ def run_fft_block(t: dict, heads: int, x: torch.Tensor, xn: torch.Tensor, mask_u
     lib.conv_gemm(ctx, t["wo"], t["bo"], block_n=D, epi=lib.EPI_RES_LN, res_f32=x, res_bstride=T * D,
                   res_tstride=D, ln1=t["ln2"], out_f32=y, out_bf16=yn, tile_map=tile_map)  # modules.py:68 + layers.py:33,35
     zn32 = torch.empty((B, T, D), device=dev, dtype=torch.float32) if want_norm_f32 else None
+    if FUSED_FFN and k == 1 and D == 384 and t["w1"].shape[1] == 4 * D and not want_norm_f32 and \
+            B * ((T + 127) // 128) > SHORT_BATCH_TILES:
+        # modules.py:81-88 + layers.py:40 + the next norm_1 as ONE kernel: the 1536-wide hidden activation stays in
+        # tensor memory instead of making a 434 MB round trip through HBM (bit-identical to the two-kernel path)
+        z = torch.empty((B, T, D), device=dev, dtype=torch.float32)
+        zn = (torch.zeros if (tile_map is not None and zero_dropped) else torch.empty)((B, T, D), device=dev,
+                                                                                       dtype=torch.bfloat16)
+        lib.ffn_fused(yn, t["w1"], t["b1"], t["w2"], t["b2"], y, t["ln_ff"], next_ln, z, zn, eps=LN_EPS, tile_map=tile_map)
+        return z, zn, zn32
     cb = ffn_chunk_utterances(B, T, D)
     if cb < B:
         # The 1536-wide hidden activation of the whole batch (217 MB at cfg2) is the largest HBM item of the step and
@@ -187,6 +196,10 @@ def run_fft_block(t: dict, heads: int, x: torch.Tensor, xn: torch.Tensor, mask_u
                      zero_dropped=zero_dropped)  # modules.py:84-87 + layers.py:40 + next norm
     return z, zn, zn32
 
+
+# k=1 blocks (the frame-level stack): the FeedForward as one kernel (csrc/ffn_fused.cuh).  False = conv1 and conv2 as two
+# conv_gemm launches (the path the training step and the short batches take).
+FUSED_FFN = True
 
 # conv1 -> conv2 grouping (see run_fft_block): a group is FFN_GROUP_WAVES full waves of 128-row tiles over the 148 SMs
 # (a group of 17 utterances x 9 tiles = 153 tiles would run a second, almost empty wave); 0 disables the grouping.

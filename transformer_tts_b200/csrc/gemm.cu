@@ -224,3 +224,4 @@ __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bu
 
 #include "gemm_kernel.cuh"  // the kernel (producer / MMA / epilogue roles)
 #include "gemm_host.cuh"    // tensor maps, launch, extern "C" entry point
+#include "ffn_fused.cuh"    // fused FeedForward of the k=1 decoder blocks

@@ -47,6 +47,7 @@ _SIGNATURES = {
     "ttsb200_version": ([], C.c_int),
     "ttsb200_last_error_string": ([], C.c_char_p),
     "ttsb200_conv_gemm": ([C.POINTER(GemmArgs), C.c_void_p], C.c_int),
+    "ttsb200_ffn_fused": ([C.c_void_p] * 10 + [C.c_float, C.c_void_p, C.c_void_p] + [C.c_int32] * 4 + [C.c_void_p] * 3, C.c_int),
     "ttsb200_build_tile_map": ([C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
                                 C.c_void_p], C.c_int),
     "ttsb200_attention_fwd": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
@@ -212,6 +213,24 @@ def conv_gemm(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, *, taps: int
     if tile_map is not None:  # (map, count) from build_tile_map: only the listed 128-row tiles are computed
         a.tile_map, a.tile_count = _ptr(tile_map[0], torch.int32, "tile_map"), _ptr(tile_map[1], torch.int32, "tile_count")
     _check(load().ttsb200_conv_gemm(C.byref(a), _stream()), "conv_gemm")
+    _count()
+
+
+def ffn_fused(x: torch.Tensor, w1: torch.Tensor, b1: torch.Tensor, w2: torch.Tensor, b2: torch.Tensor, y: torch.Tensor,
+              ln1: tuple, ln2: tuple, z: torch.Tensor, zn: torch.Tensor, eps: float = 1e-5,
+              tile_map: Optional[tuple] = None) -> None:
+    """z = y + LN(relu(x W1^T + b1) W2^T + b2 + x; ln1); zn = LN(z; ln2) in one kernel (k=1 blocks, D=384)."""
+    B, T, D = x.shape
+    hidden = w1.shape[-2]
+    tm, tc = (None, None) if tile_map is None else tile_map
+    _check(load().ttsb200_ffn_fused(_ptr(x, torch.bfloat16, "x"), _ptr(w1, torch.bfloat16, "w1"),
+                                    _ptr(b1, torch.float32, "b1"), _ptr(w2, torch.bfloat16, "w2"),
+                                    _ptr(b2, torch.float32, "b2"), _ptr(y, torch.float32, "y"),
+                                    _ptr(ln1[0], torch.float32, "ln1_g"), _ptr(ln1[1], torch.float32, "ln1_b"),
+                                    _ptr(ln2[0], torch.float32, "ln2_g"), _ptr(ln2[1], torch.float32, "ln2_b"), eps,
+                                    _ptr(z, torch.float32, "z"), _ptr(zn, torch.bfloat16, "zn"), B, T, D, hidden,
+                                    _ptr(tm, torch.int32, "tile_map"), _ptr(tc, torch.int32, "tile_count"), _stream()),
+           "ffn_fused")
     _count()
 
 
