@@ -465,6 +465,7 @@ def ours(args):
     model.load_state_dict(synth.synth_state_dict(hp))
     model = model.cuda()
     model.duration_precision = args.duration_precision
+    model.variance_precision = args.variance_precision if args.duration_precision == "fp32" else "bf16"
     text_h, pos_h, _ = make_batch(rank, world)
     text_h, mask_h = text_h.pin_memory(), (pos_h != 0).unsqueeze(-2).pin_memory()
     text_d, mask_d = text_h.cuda(), mask_h.cuda()
@@ -549,15 +550,21 @@ def ours(args):
         sampler.join(timeout=2)
         clocks = sampler.summary()
         clocks_by_rank = gather(float(clocks["sm_mhz"] or 0.0))
-        # ---- the other duration mode, for comparison ----
-        other = "bf16" if args.duration_precision == "fp32" else "fp32"
-        model.duration_precision = other
-        for _ in range(3):
-            model(text_d, mask_d)
-        frames_o = reduce(float(model.last_aux["mel_len"].sum().item()), SUM)
-        n_o = max(5, min(args.steps, 20))
-        other_ms = reduce(timed_steps(n_o), MAX)
-        model.duration_precision = args.duration_precision
+        # ---- the other precision modes, for comparison ----
+        timed_mode = (model.duration_precision, model.variance_precision)
+        modes = {}
+        for dp, vp in (("fp32", "fp32"), ("fp32", "bf16"), ("bf16", "bf16")):
+            if (dp, vp) == timed_mode:
+                continue
+            model.duration_precision, model.variance_precision = dp, vp
+            for _ in range(3):
+                model(text_d, mask_d)
+            frames_o = reduce(float(model.last_aux["mel_len"].sum().item()), SUM)
+            n_o = max(5, min(args.steps, 20))
+            other_ms = reduce(timed_steps(n_o), MAX)
+            modes[f"durations_{dp}_pitch_energy_{vp}"] = {"value": frames_o * n_o / (other_ms * 1e-3), "unit": UNIT,
+                                                          "ms_per_step": other_ms / n_o, "steps": n_o}
+        model.duration_precision, model.variance_precision = timed_mode
         lat = latency_b1(model, hp) if rank == 0 else None
         roofs = kernel_rooflines(model, peaks, aux["mel_len"]) if rank == 0 else None
         eager = torch_eager_b200(hp, text_d, mask_d, aux, p_pred, e_pred) if rank == 0 and not args.no_eager_baseline else None
@@ -578,10 +585,12 @@ def ours(args):
                 "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
                 "ms_per_step_by_rank": rank_ms, "sm_mhz_by_rank": clocks_by_rank,
                 "config": {"workload": WORKLOAD, "batch_per_gpu": B_PER_GPU, "phonemes": L_PHON,
-                           "duration_precision": args.duration_precision,
-                           "duration_precision_note": "fp32 = encoder -> duration chain to fp32 accuracy (split-fp16 x3 "
-                                                      "tensor-core GEMMs): durations / frame indices / mel lengths equal "
-                                                      "the fp32 reference's; everything downstream bf16",
+                           "duration_precision": model.duration_precision,
+                           "variance_precision": model.variance_precision,
+                           "precision_note": "fp32 = that chain (encoder + duration predictor; pitch / energy predictors) "
+                                             "runs to fp32 accuracy on split-fp16 x3 tensor-core GEMMs, so durations, frame "
+                                             "indices, mel lengths and pitch / energy buckets equal the fp32 reference's; "
+                                             "decoder and PostNet are bf16 in every mode",
                            "frames_per_step_rank0": frames, "t_max_rank0": tmax,
                            "sharding": f"one pool of {B_PER_GPU * world} utterances dealt by sharding.shard_by_length "
                                        f"over {world} rank(s), no data-path collective",
@@ -591,9 +600,9 @@ def ours(args):
                 "gpu_launches": launches, "launches_per_step": launches / args.steps, "clocks": clocks,
                 # dominant kernel = largest share of the step (profiles/): the decoder attention
                 "roofline": by_key["attention"], "kernel_rooflines": roofs,
-                ("bf16_duration_chain" if other == "bf16" else "fp32_duration_chain"):
-                    {"value": frames_o * n_o / (other_ms * 1e-3), "unit": UNIT, "ms_per_step": other_ms / n_o, "steps": n_o,
-                     "note": "same step with model.duration_precision = %r" % other},
+                # the same step in the other precision modes: fp32 = that predictor chain runs to fp32 accuracy so its
+                # discrete decisions (durations / pitch-energy buckets) equal the fp32 reference's; bf16 = plain bf16
+                "other_precision_modes": modes,
                 "torch_eager_b200": eager, "latency_b1": lat, "train": trn, "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -720,6 +729,8 @@ def main():
     ap.add_argument("--no-train-record", action="store_true", help="skip the training-step sub-record")
     ap.add_argument("--duration-precision", default="fp32", choices=["fp32", "bf16"],
                     help="fp32 (default): durations equal the fp32 reference's; bf16: the faster chain (SURVEY F9)")
+    ap.add_argument("--variance-precision", default="fp32", choices=["fp32", "bf16"],
+                    help="fp32 (default): pitch / energy buckets equal the fp32 reference's too (needs fp32 durations)")
     ap.add_argument("--workload", default="infer", choices=["infer", "train"])
     ap.add_argument("--train-batch", type=int, default=32)
     ap.add_argument("--overlap", action="store_true",

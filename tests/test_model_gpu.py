@@ -260,6 +260,23 @@ def test_cfg2_full_size_vs_oracle(setup):
     assert bucket_flips == 0
     assert e_pre < TOL_BF16 and e_post < TOL_BF16
     assert e_free < 4e-2
+    # variance_precision "fp32": the pitch / energy predictors run the fp32-accurate chain too, so a FREE-RUNNING
+    # forward takes the oracle's pitch / energy buckets as well and its mel meets the bf16 bar without teacher forcing
+    model.variance_precision = "fp32"
+    try:
+        with torch.no_grad():
+            outv = model(text, src_mask)
+        auxv = model.last_aux
+    finally:
+        model.variance_precision = "bf16"
+    assert torch.equal(auxv["dur"], aux["dur"])
+    pf = int((auxv["p_idx"].long() != ref["p_idx"]).sum())
+    ef = int((auxv["e_idx"].long() != ref["e_idx"]).sum())
+    e_free_v = rel_l2(valid_rows(outv[1], mel_len), valid_rows(ref["outputs_postnet"], mel_len))
+    p_err = float((valid_rows(outv[3], mel_len) - valid_rows(ref["p_prediction"], mel_len)).abs().max())
+    print(f"[cfg2 full size, variance_precision=fp32] free-running mel rel-L2 {e_free_v:.2e}, pitch / energy bucket flips "
+          f"{pf} / {ef} of {int(mel_len.sum())}, pitch max abs err {p_err:.2e}")
+    assert e_free_v < TOL_BF16
 
 
 def test_full_size_properties_cfg2(setup):

@@ -76,6 +76,10 @@ class FastSpeech2(nn.Module):
         # durations land on the other side of a .5 boundary).  Teacher-forced calls always take the bf16
         # chain: there log_d is only an output.
         self.duration_precision = "fp32"
+        # "fp32": the pitch / energy predictors run the fp32-accurate chain as well (needs duration_precision "fp32"), so
+        # the pitch / energy buckets — the other discrete decision of a free-running forward, worth ~2 % of mel rel-L2
+        # per flipped bucket — equal the fp32 reference's too.  Costs ~0.2 ms at cfg2; off by default.
+        self.variance_precision = "bf16"
         self.aux_outputs_fp32 = True   # tuple slots 5 / 6 in the reference's dtype (see _aux_f32)
         self.use_cuda_graphs = True    # free-running inference: the pre-LengthRegulator stage replays a CUDA graph
         self._graphs = {}
@@ -114,8 +118,13 @@ class FastSpeech2(nn.Module):
         attn_enc = None
         if d_target is None and not self.return_attn and self.encoder.N > 0:
             # free-running: encoder -> duration predictor -> rounding -> prefix sum, up to the one host sync (Tmax)
-            e_bf, pre = self._pre_lr(src.contiguous(), sm)
-            va = self.variance_adaptor.run(e_bf, sm, mm, None, p_target, e_target, want_aux=True, pre=pre)  # :176-181
+            if self.variance_precision not in ("fp32", "bf16"):
+                raise ValueError(f"variance_precision must be 'fp32' or 'bf16', got {self.variance_precision!r}")
+            if self.variance_precision == "fp32" and self.duration_precision != "fp32":
+                raise ValueError("variance_precision 'fp32' needs duration_precision 'fp32' (the fp32-accurate encoder)")
+            e_bf, e_split, pre = self._pre_lr(src.contiguous(), sm)
+            va = self.variance_adaptor.run(e_bf, sm, mm, None, p_target, e_target, want_aux=True, pre=pre,
+                                           x_split=e_split if self.variance_precision == "fp32" else None)  # :176-181
         else:
             e_bf, _, attn_enc = self.encoder.run(src, sm, kv_src_fn(), want_f32=False, return_attn=self.return_attn)  # :137
             va = self.variance_adaptor.run(e_bf, sm, mm, d_target, p_target, e_target, want_aux=True)  # :176-181
@@ -144,13 +153,13 @@ class FastSpeech2(nn.Module):
     # ------------------------------------------------------------------------------------------
     def _pre_lr_eager(self, src, sm):
         kv_src = lib.mask_lengths(sm)
-        log_d = None
+        log_d = e_split = None
         if self.duration_precision == "fp32":
             e_bf, e_split, _ = E.run_encoder_precise(self.encoder, src, sm, kv_src)  # :137, to fp32 accuracy
             log_d = E.run_predictor_precise(self.variance_adaptor.duration_predictor, e_split, sm)  # varianceadaptor.py:69
         else:
             e_bf, _, _ = self.encoder.run(src, sm, kv_src, want_f32=False)  # :137
-        return e_bf, self.variance_adaptor.run_pre(e_bf, sm, log_d)
+        return e_bf, e_split, self.variance_adaptor.run_pre(e_bf, sm, log_d)
 
     def _pre_lr_params(self):
         ps = list(self.encoder.parameters()) + list(self.variance_adaptor.duration_predictor.parameters())
@@ -180,9 +189,10 @@ class FastSpeech2(nn.Module):
         ent["sm"].copy_(sm)
         ent["graph"].replay()
         lib._count(ent["n"])
-        e_bf, (log_d, dur, cum, mel_len, tmax) = ent["outs"]
-        # the graph's output buffers are overwritten by the next replay: what leaves this call is copied out
-        return e_bf.clone(), (log_d.clone(), dur.clone(), cum, mel_len.clone(), tmax)
+        e_bf, e_split, (log_d, dur, cum, mel_len, tmax) = ent["outs"]
+        # the graph's output buffers are overwritten by the next replay: what leaves this call is copied out (e_split and
+        # cum are consumed by the LengthRegulator inside this forward)
+        return e_bf.clone(), e_split, (log_d.clone(), dur.clone(), cum, mel_len.clone(), tmax)
 
     def _aux_f32(self, t):
         """Slots 5 / 6 of the tuple (variance_adaptor_output, text_dur_predicted) are fp32 in the reference; the

@@ -148,10 +148,12 @@ class VarianceAdaptor(nn.Module):
         return c.t
 
     def run(self, x_bf16, src_mask_u8, mel_mask_u8=None, duration_target=None, pitch_target=None,
-            energy_target=None, max_len=None, want_aux=True, log_d=None, pre=None):
+            energy_target=None, max_len=None, want_aux=True, log_d=None, pre=None, x_split=None):
         """Kernel sequence of varianceadaptor.py:66-129 on bf16 activations.  Returns a dict.
         log_d: the duration predictor's output when the caller already evaluated it (fp32-accurate chain).
-        pre: (log_d, dur, cum, mel_len, max mel_len) from `run_pre` (free-running: everything before the one host sync)."""
+        pre: (log_d, dur, cum, mel_len, max mel_len) from `run_pre` (free-running: everything before the one host sync).
+        x_split: the encoder output as an fp16 hi|lo split (B,L,2D): the pitch / energy predictors then run the
+        fp32-accurate chain too, so the pitch / energy BUCKETS equal the fp32 reference's (variance_precision "fp32")."""
         dev = x_bf16.device
         scan = None
         if pre is not None:
@@ -171,8 +173,17 @@ class VarianceAdaptor(nn.Module):
         xe, fidx, mel_pos, lr_mask, mel_len, _ = self.length_regulator.run(x_bf16, dur, max_len, want_aux, scan=scan)  # :73/:82
         if duration_target is None or mel_mask_u8 is None:
             mel_mask_u8 = lr_mask  # :84 (the kernel applies the `arange <= mel_pos` rule)
-        p = self.pitch_predictor.run(xe, mel_mask_u8)  # :96
-        e = self.energy_predictor.run(xe, mel_mask_u8)  # :115
+        if x_split is not None:
+            # the split is expanded as 16-bit words by the same gather kernel (a frame copies its phoneme's hi and lo halves)
+            xs16 = x_split.view(torch.bfloat16)
+            xe_s, _, _, _ = lib.lr_expand(xs16, pre[2] if pre is not None else lib.lr_scan(dur)[0], mel_len, xe.shape[1],
+                                          want_aux=False)
+            xe_s = xe_s.view(torch.float16)
+            p = E.run_predictor_precise(self.pitch_predictor, xe_s, mel_mask_u8)   # :96
+            e = E.run_predictor_precise(self.energy_predictor, xe_s, mel_mask_u8)  # :115
+        else:
+            p = self.pitch_predictor.run(xe, mel_mask_u8)  # :96
+            e = self.energy_predictor.run(xe, mel_mask_u8)  # :115
         p_src = p if pitch_target is None else pitch_target.to(torch.float32).contiguous()  # :97-109
         e_src = e if energy_target is None else energy_target.to(torch.float32).contiguous()  # :116-118
         pb, eb = self._bins(dev)
