@@ -29,7 +29,7 @@ SLOTS = ["outputs_prenet", "outputs_postnet", "log_d_prediction", "p_prediction"
          "variance_adaptor_output", "text_dur_predicted", "attn_enc", "attn_dec"]
 
 
-def f16(t):  # big activations are stored as fp16-exactly-representable? no: keep fp32, just subsample
+def to_np(t):  # fp32 as computed (large tensors are subsampled by the callers, never re-quantised)
     return t.detach().cpu().numpy()
 
 
@@ -48,9 +48,9 @@ def main():
     with torch.no_grad():
         out = model(text, src_mask)
     np.savez_compressed(GOLDEN / "fs2_cfg1_free_running.npz", digest=digest, text=text.numpy(), pos=pos.numpy(),
-                        mel_pre=f16(out[0]), mel_post=f16(out[1]), log_d=f16(out[2]), p=f16(out[3]), e=f16(out[4]),
-                        va_out_sub=f16(out[5][:, ::8, ::16]), attn_enc_l0h0=f16(out[7][0, 0, 0]),
-                        attn_dec_l5h3_sub=f16(out[8][0, 5, 3, ::16, ::16]))
+                        mel_pre=to_np(out[0]), mel_post=to_np(out[1]), log_d=to_np(out[2]), p=to_np(out[3]), e=to_np(out[4]),
+                        va_out_sub=to_np(out[5][:, ::8, ::16]), attn_enc_l0h0=to_np(out[7][0, 0, 0]),
+                        attn_dec_l5h3_sub=to_np(out[8][0, 5, 3, ::16, ::16]))
 
     # ---- case B: ragged batch, teacher-forced durations + f0/energy targets (training-style call) ----
     text, pos, lens = synth.synth_text_batch(3, 40, ragged=True, seed=99)
@@ -62,9 +62,9 @@ def main():
         out2 = model(text, src_mask, mel_mask=mel_mask, d_target=dur)  # predicted pitch/energy drive the buckets
     np.savez_compressed(GOLDEN / "fs2_ragged_teacher_forced.npz", digest=digest, text=text.numpy(), pos=pos.numpy(),
                         dur=dur.numpy(), pos_mel=pos_mel.numpy(), f0=f0.numpy(), energy=en.numpy(),
-                        mel_pre=f16(out[0]), mel_post=f16(out[1]), log_d=f16(out[2]), p=f16(out[3]), e=f16(out[4]),
-                        va_out_sub=f16(out[5][:, ::4, ::16]), text_dur_sub=f16(out[6][:, ::4, ::16]),
-                        mel_post_pred_buckets=f16(out2[1]))
+                        mel_pre=to_np(out[0]), mel_post=to_np(out[1]), log_d=to_np(out[2]), p=to_np(out[3]), e=to_np(out[4]),
+                        va_out_sub=to_np(out[5][:, ::4, ::16]), text_dur_sub=to_np(out[6][:, ::4, ::16]),
+                        mel_post_pred_buckets=to_np(out2[1]))
 
     # ---- case C: op-level goldens from the reference's own submodules ----
     g = torch.Generator().manual_seed(7)
@@ -83,9 +83,9 @@ def main():
         lr_mask = sys.modules["Models.varianceadaptor"].get_mask_from_lengths(lr_pos)
         lr_x_max, _ = model.variance_adaptor.length_regulator(x, d, 30)
     np.savez_compressed(GOLDEN / "fs2_ops.npz", digest=digest, x=x.numpy(), mask=m.numpy(),
-                        enc_layer2=f16(y_layer), enc_layer2_attn=f16(attn), dec_ff1=f16(y_ff), pitch_pred=f16(y_vp),
-                        post_pre=f16(y_pre), post_post=f16(y_post), pe=f16(y_pe), lr_dur=d.numpy(), lr_x=f16(lr_x),
-                        lr_pos=lr_pos.numpy(), lr_mask=lr_mask.numpy(), lr_x_max30=f16(lr_x_max),
+                        enc_layer2=to_np(y_layer), enc_layer2_attn=to_np(attn), dec_ff1=to_np(y_ff), pitch_pred=to_np(y_vp),
+                        post_pre=to_np(y_pre), post_post=to_np(y_post), pe=to_np(y_pe), lr_dur=d.numpy(), lr_x=to_np(lr_x),
+                        lr_pos=lr_pos.numpy(), lr_mask=lr_mask.numpy(), lr_x_max30=to_np(lr_x_max),
                         pitch_bins=model.variance_adaptor.pitch_bins.cpu().numpy(),
                         energy_bins=model.variance_adaptor.energy_bins.cpu().numpy(),
                         pe_table_sub=model.encoder.pe.pe[0, ::97].numpy())

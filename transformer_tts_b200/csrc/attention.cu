@@ -1,14 +1,14 @@
 // Fused masked multi-head self-attention for sm_100a (Models/modules.py:7-21 inside :43-70).
 //
 // One CTA = one (utterance, head, 128-query tile).  Per 64-key tile j:
-//   TMA (SWIZZLE_64B boxes of 32 head-dims x 64 rows) -> smem K (3 stages), V (2 stages)
+//   TMA (a SWIZZLE_128B box of 64 head-dims + a SWIZZLE_64B box of 32, x 64 rows) -> smem K (2 stages), V (2 stages)
 //   tcgen05.mma  S_j = Q K_j^T        (M128 N64 K96, both operands K-major)         -> TMEM S buffer j & 1
 //   softmax warps: S_j TMEM -> 64 registers per thread (thread == query row), buffer released at once; scale,
 //                  key-padding mask (-1e4 like the reference), p = exp2(s - m) with a lazily moved reference
 //                  point m (O and l are rescaled only when the row maximum grew by more than 2^8),
 //                  P (bf16) -> smem in the SWIZZLE_128B K-major layout
 //   tcgen05.mma  O += P_j V_j         (M128 N96 K64, V is the MN-major B operand)   -> TMEM cols [128,224)
-// S is issued up to two tiles ahead, K/V loads up to three/two tiles ahead: no TMA round trip and no
+// S is issued up to two tiles ahead, K/V loads two tiles ahead: no TMA round trip and no
 // TMEM -> register copy sits on the per-tile critical path.  O never leaves TMEM until the final O / l.
 // Two CTAs fit per SM (101 KB smem, 256 TMEM columns each) so one CTA's softmax overlaps the other's MMAs and
 // prologue/epilogue.  Fully padded key tiles are skipped: with the reference's -1e4 fill their probabilities
@@ -112,8 +112,8 @@ __device__ __forceinline__ void att_tma_store_3d(const CUtensorMap* m, uint32_t 
 
 enum {
   BAR_Q = 0,
-  BAR_KF,                       // [3] K stage filled
-  BAR_KE = BAR_KF + kKStages,   // [3] K stage consumed
+  BAR_KF,                       // [kKStages] K stage filled
+  BAR_KE = BAR_KF + kKStages,   // [kKStages] K stage consumed
   BAR_VF = BAR_KE + kKStages,   // [2]
   BAR_VE = BAR_VF + kVStages,   // [2]
   BAR_SF = BAR_VE + kVStages,   // [2] S buffer written by the tensor core
@@ -123,7 +123,7 @@ enum {
   BAR_COUNT
 };
 
-// v3: 64-key tiles, K triple- and V double-buffered in smem, S double-buffered in TMEM, so that neither a TMA
+// 64-key tiles, K and V double-buffered in smem, S double-buffered in TMEM, so that neither a TMA
 // round trip nor the S -> registers copy sits on the per-tile critical path (v2 had single K/V buffers: its
 // per-tile time was 181 us of 226 us with the softmax arithmetic removed).
 // DROP: training with dropout on the probabilities (Models/modules.py:18-19): the row sum l is taken BEFORE the mask
@@ -143,7 +143,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
   uint8_t* sQ = smem;
-  uint8_t* sK = sQ + kQBytes;                   // [3] x 12 KB (each 1024-aligned: 12 KB = 12 * 1024)
+  uint8_t* sK = sQ + kQBytes;                   // [kKStages] x 12 KB (each 1024-aligned: 12 KB = 12 * 1024)
   uint8_t* sV = sK + kKStages * kKVBytes;       // [2] x 12 KB
   uint64_t* bars = reinterpret_cast<uint64_t*>(sV + kVStages * kKVBytes);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + BAR_COUNT);
