@@ -181,6 +181,16 @@ def reference_arm(args):
     print(json.dumps(line), flush=True)
 
 
+def tmap_stats():
+    import ctypes
+
+    from transformer_tts_b200 import lib
+
+    h, m = ctypes.c_ulonglong(0), ctypes.c_ulonglong(0)
+    lib.load().ttsb200_debug_tmap_cache(ctypes.byref(h), ctypes.byref(m))
+    return {"hits": h.value, "misses": m.value}
+
+
 def load_traffic():
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of the hot kernels, from ONE `ncu --set full` capture of
     tools/run_hot_kernels.py on this tree (profiles/r02_hot_kernels_traffic.json, written by tools/ncu_traffic.py with
@@ -554,7 +564,7 @@ def ours(args):
         timed_mode = (model.duration_precision, model.variance_precision)
         modes = {}
         for dp, vp in (("fp32", "fp32"), ("fp32", "bf16"), ("bf16", "bf16")):
-            if (dp, vp) == timed_mode:
+            if (dp, vp) == timed_mode or args.step_only:
                 continue
             model.duration_precision, model.variance_precision = dp, vp
             for _ in range(3):
@@ -565,21 +575,25 @@ def ours(args):
             modes[f"durations_{dp}_pitch_energy_{vp}"] = {"value": frames_o * n_o / (other_ms * 1e-3), "unit": UNIT,
                                                           "ms_per_step": other_ms / n_o, "steps": n_o}
         model.duration_precision, model.variance_precision = timed_mode
-        lat = latency_b1(model, hp) if rank == 0 else None
-        roofs = kernel_rooflines(model, peaks, aux["mel_len"]) if rank == 0 else None
-        eager = torch_eager_b200(hp, text_d, mask_d, aux, p_pred, e_pred) if rank == 0 and not args.no_eager_baseline else None
+        lat = latency_b1(model, hp) if rank == 0 and not args.step_only else None
+        roofs = kernel_rooflines(model, peaks, aux["mel_len"]) if rank == 0 and not args.step_only else None
+        eager = torch_eager_b200(hp, text_d, mask_d, aux, p_pred, e_pred) \
+            if rank == 0 and not (args.no_eager_baseline or args.step_only) else None
     total_frames = reduce(float(frames), SUM)
     value = total_frames * args.steps / (dev_ms * 1e-3)
     e2e_value = total_frames * args.steps / (e2e_ms * 1e-3)
     del out_h
     torch.cuda.empty_cache()
-    trn = None if args.no_train_record else train_record(args, rank, world)
+    trn = None if (args.no_train_record or args.step_only) else train_record(args, rank, world)
     cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not (args.no_cpu_baseline or args.step_only):
         r = cpu_oracle_run(3, 1, sample_b=B_PER_GPU)
         cpu = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]}
     if rank == 0:
-        by_key = {r["key"]: r for r in roofs}
+        by_key = {r["key"]: r for r in (roofs or [])}
+        # dominant kernel = the largest share of the timed step: the fused decoder FeedForward (6 launches x ~165 us of a
+        # ~6 ms step; the launch list under profiles/ has the shares), then the decoder attention (6 x ~127 us)
+        dominant = by_key.get("ffn_fused")
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(3, args.warmup), "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
@@ -598,8 +612,8 @@ def ours(args):
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(text_h.numel() * 8 + mask_h.numel()),
                         "d2h_bytes_per_step": int(B_PER_GPU * tmax * hp.mel_dim * 4), "ms_per_step": e2e_ms / args.steps},
                 "gpu_launches": launches, "launches_per_step": launches / args.steps, "clocks": clocks,
-                # dominant kernel = largest share of the step (profiles/): the decoder attention
-                "roofline": by_key["attention"], "kernel_rooflines": roofs,
+                "tma_descriptor_cache": tmap_stats(),
+                "roofline": dominant, "kernel_rooflines": roofs,
                 # the same step in the other precision modes: fp32 = that predictor chain runs to fp32 accuracy so its
                 # discrete decisions (durations / pitch-energy buckets) equal the fp32 reference's; bf16 = plain bf16
                 "other_precision_modes": modes,
@@ -727,6 +741,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-eager-baseline", action="store_true", help="skip the torch_eager_b200 sub-record")
     ap.add_argument("--no-train-record", action="store_true", help="skip the training-step sub-record")
+    ap.add_argument("--step-only", action="store_true",
+                    help="only the timed steps (no per-kernel rooflines, latency, other modes, baselines): for ncu launch lists")
     ap.add_argument("--duration-precision", default="fp32", choices=["fp32", "bf16"],
                     help="fp32 (default): durations equal the fp32 reference's; bf16: the faster chain (SURVEY F9)")
     ap.add_argument("--variance-precision", default="fp32", choices=["fp32", "bf16"],

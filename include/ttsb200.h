@@ -31,6 +31,8 @@ typedef void* ttsb200_stream_t; /* cudaStream_t */
 #define TTSB200_ABI_VERSION 200 /* round 2: gemm_args.tile_map/tile_count, the fp32-accurate chain, dropout */
 int ttsb200_version(void);
 const char* ttsb200_last_error_string(void);
+/* hits / misses of the library's TMA-descriptor cache (keyed by pointer, shape, strides, box, swizzle) since load */
+void ttsb200_debug_tmap_cache(unsigned long long* hits, unsigned long long* misses);
 
 /* ------------------------------------------------------------------------------------------------
  * Implicit-GEMM conv1d / linear on tcgen05 tensor cores (TMA-fed, TMEM accumulators).
@@ -100,7 +102,7 @@ int ttsb200_conv_gemm(const ttsb200_gemm_args* args, ttsb200_stream_t stream);
  *   z = y + LN(relu(x W1^T + b1) W2^T + b2 + x; ln1);  zn = LN(z; ln2)
  * x bf16 (B,T,384) = norm_2(y); w1 bf16 [1536][384]; w2 bf16 [384][1536]; y / z fp32 (B,T,384); zn bf16.
  * The 1536-wide hidden activation stays in tensor memory (TMEM): it is neither written to nor read from HBM.
- * tile_map / tile_count as in ttsb200_gemm_args (NULL = all tiles). */
+ * tile_map / tile_count: the ragged row-tile list of the ttsb200_gemm_args struct; NULL = all tiles. */
 int ttsb200_ffn_fused(const void* x_bf16, const void* w1_bf16, const float* b1, const void* w2_bf16, const float* b2,
                       const float* y_f32, const float* ln1_g, const float* ln1_b, const float* ln2_g, const float* ln2_b,
                       float eps, float* z_f32, void* zn_bf16, int32_t B, int32_t T, int32_t D, int32_t hidden,

@@ -2,8 +2,9 @@
 """Launch every hot kernel of the inference step (decoder shape of cfg2: B=64, T=1103) and of the training step
 (B=32, T=1073) twice, for `ncu --set full` captures:
 
-  ncu --set full --clock-control none --import-source on -k regex:'conv_gemm|attention_fwd|wgrad|attn_bwd|ln_bwd|lr_expand|bucket_embed|layernorm_kernel' \
-      --launch-skip-before-match 0 -o gpurun_out/r01_hot_v5 python tools/run_hot_kernels.py
+  ncu --set full --clock-control none --import-source on \
+      -k regex:'conv_gemm|ffn_fused|attention_fwd|gemm_x3|attention_x3|xrow|wgrad|attn_bwd|ln_bwd|lr_expand|bucket_embed|layernorm_kernel' \
+      -o gpurun_out/r02_hot python tools/run_hot_kernels.py
 """
 import sys
 from pathlib import Path
@@ -71,6 +72,25 @@ def main():
                                   dbeta=db)
                 lib.colsum(hs, torch.zeros(4 * D, device=dev))
         torch.cuda.synchronize()
+    # the fp32-accurate encoder -> duration chain at the encoder shape of cfg2 (B=64, L=128): csrc/precise.cu
+    B, L = 64, 128
+    lc = E.layer_cache(model.encoder.layers[0])
+    xc = E.layer_cache_x3(model.encoder.layers[0])
+    m8 = torch.ones(B, L, dtype=torch.uint8, device=dev)
+    kvl = lib.mask_lengths(m8)
+    x = torch.randn(B, L, D, device=dev)
+    for rep in range(2):
+        xs = lib.split_f16(x)
+        qkv = lib.gemm_x3(xs, xc["wqkv"], lc["bqkv"], xc["sqkv"], split_out=True)
+        ctx = lib.attention_x3(qkv, m8, kvl, H)
+        o = lib.gemm_x3(ctx, xc["wo"], lc["bo"], xc["so"])
+        y, yns = torch.empty_like(x), torch.empty_like(xs)
+        lib.xrow(lib.XROW_ADD_LN, x, lc["ln2"], b0=o, s_out=y, out_split=yns)
+        hs_ = lib.gemm_x3(yns, xc["w1"], lc["b1"], xc["s1"], taps=5, pad_left=2, relu=True, split_out=True)
+        u = lib.gemm_x3(hs_, xc["w2"], lc["b2"], xc["s2"], taps=5, pad_left=2)
+        z, zns = torch.empty_like(x), torch.empty_like(xs)
+        lib.xrow(lib.XROW_FFN_TAIL, u, lc["ln_ff"], b0_split=yns, c=y, ln2=lc["ln1"], z_out=z, out_split=zns)
+    torch.cuda.synchronize()
     print("ok", lib.LAUNCH_COUNT)
 
 

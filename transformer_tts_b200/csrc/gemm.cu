@@ -60,7 +60,10 @@ struct GemmCfg {
   // (CTA pairs have the room for two per warpgroup: the TMA store of one chunk overlaps the next chunk's math)
   static constexpr int kStoreBoxes = (PAIR && !kIsLN) ? TTSB_STORE_BOXES : 1;
   static constexpr int kStoreBytes = 2 * kStoreBoxes * 8192;
-  static constexpr int kRingSlots = kRing ? 4 : 0;  // even: each half owns its own slots
+#ifndef TTSB_RING_SLOTS
+#define TTSB_RING_SLOTS 4
+#endif
+  static constexpr int kRingSlots = kRing ? (PAIR ? TTSB_RING_SLOTS : 4) : 0;  // even: each half owns its own slots
   static constexpr int kRingBytes = kRingSlots * kBoxBytes16K;
   // parameter vectors in smem: AFFINE: (bias, scale) per warpgroup; LN: bias, g1, b1, g2, b2, dot_w
   static constexpr int kParamFloats = kIsLN ? 6 * BLOCK_N : 4 * BLOCK_N;

@@ -37,11 +37,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint64_t* bar_empty = bars + S;        // [S]
   uint64_t* bar_accf = bars + 2 * S;     // [2]
   uint64_t* bar_acce = bars + 2 * S + 2; // [2]
-  uint64_t* bar_rf = bars + 2 * S + 4;   // [4] ring slot filled
-  uint64_t* bar_re = bars + 2 * S + 8;   // [4] ring slot drained
-  uint64_t* bar_af = bars + 2 * S + 12;  // [6] resident A k-block filled
-  uint64_t* bar_ae = bars + 2 * S + 18;  // [6] resident A k-block free
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 24);
+  uint64_t* bar_rf = bars + 2 * S + 4;   // [8] ring slot filled
+  uint64_t* bar_re = bars + 2 * S + 12;  // [8] ring slot drained
+  uint64_t* bar_af = bars + 2 * S + 20;  // [6] resident A k-block filled
+  uint64_t* bar_ae = bars + 2 * S + 26;  // [6] resident A k-block free
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 32);
+  static_assert(RS <= 8 && (2 * S + 32) * 8 + 16 <= 512, "barrier block");
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -74,7 +75,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       mbar_init(smem_u32(&bar_af[i]), 1);
       mbar_init(smem_u32(&bar_ae[i]), 1);
     }
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < 8; ++i) {
       mbar_init(smem_u32(&bar_rf[i]), 1);
       mbar_init(smem_u32(&bar_re[i]), kWgThreads);
     }

@@ -46,6 +46,7 @@ _LIB: Optional[C.CDLL] = None
 _SIGNATURES = {
     "ttsb200_version": ([], C.c_int),
     "ttsb200_last_error_string": ([], C.c_char_p),
+    "ttsb200_debug_tmap_cache": ([C.c_void_p, C.c_void_p], None),
     "ttsb200_conv_gemm": ([C.POINTER(GemmArgs), C.c_void_p], C.c_int),
     "ttsb200_ffn_fused": ([C.c_void_p] * 10 + [C.c_float, C.c_void_p, C.c_void_p] + [C.c_int32] * 4 + [C.c_void_p] * 3, C.c_int),
     "ttsb200_build_tile_map": ([C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
