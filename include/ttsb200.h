@@ -175,12 +175,13 @@ int ttsb200_round_durations(const float* log_d, int32_t* dur, int64_t n, ttsb200
  *   pass 2 (expand): out[b,t,:] = x[b, idx(b,t), :] for t < mel_len[b], else 0, where idx is the
  *   phoneme whose [cum-d, cum) interval holds t; frame_idx (B,Tmax) int32 (-1 on padding),
  *   mel_pos (B,Tmax) int64 = t+1 on valid frames else 0, mel_mask (B,Tmax) uint8 by the
- *   reference's `arange <= mel_pos` rule (varianceadaptor.py:251-259).
+ *   reference's `arange <= mel_pos` rule (varianceadaptor.py:251-259).  out_f32 (optional, both kernels below): the
+ *   same output widened to fp32 — slots 6 / 5 of the reference's return tuple (Models/fastspeech2.py:241) are fp32.
  * dur is int32 (B,L), negative values count as 0. */
 int ttsb200_lr_scan(const int32_t* dur, int32_t* cum, int32_t* mel_len, int32_t B, int32_t L,
                     ttsb200_stream_t stream);
 int ttsb200_lr_expand(const void* x_bf16, const int32_t* cum, const int32_t* mel_len, void* out_bf16,
-                      int32_t* frame_idx, int64_t* mel_pos, uint8_t* mel_mask, int32_t B, int32_t L,
+                      int32_t* frame_idx, int64_t* mel_pos, uint8_t* mel_mask, float* out_f32, int32_t B, int32_t L,
                       int32_t Tmax, int32_t D, ttsb200_stream_t stream);
 
 /* out = x + pitch_table[bucketize(p, pitch_bins)] + energy_table[bucketize(e, energy_bins)]
@@ -190,7 +191,7 @@ int ttsb200_lr_expand(const void* x_bf16, const int32_t* cum, const int32_t* mel
 int ttsb200_bucket_embed_add(const void* x_bf16, const float* p, const float* e,
                              const float* pitch_bins, const float* energy_bins,
                              const float* pitch_table, const float* energy_table, void* out_bf16,
-                             int32_t* p_idx, int32_t* e_idx, int64_t rows, int32_t D, int32_t nb,
+                             int32_t* p_idx, int32_t* e_idx, float* out_f32, int64_t rows, int32_t D, int32_t nb,
                              ttsb200_stream_t stream);
 
 /* fp32 -> bf16 cast of a dense buffer (weight/activation staging). */

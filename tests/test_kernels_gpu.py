@@ -460,3 +460,27 @@ def test_ffn_fused_is_bit_identical_to_the_two_kernel_path(B, T, ragged):
         e_z = float((z[rows].double() - zr[rows]).norm() / zr[rows].norm())
         e_zn = float((zn[rows].double() - znr[rows]).norm() / znr[rows].norm())
         assert e_z < 1e-4 and e_zn < 4e-3, (e_z, e_zn)
+
+
+def test_fp32_second_outputs_of_lr_expand_and_bucket_embed_add():
+    """Slots 5 / 6 of the reference's return tuple are fp32: the producing kernels write the fp32 copy themselves; it must
+    be exactly the bf16 output widened."""
+    from transformer_tts_b200 import lib as L
+
+    torch.manual_seed(4)
+    B, Lp, D = 3, 20, 384
+    x = torch.randn(B, Lp, D, device="cuda").bfloat16()
+    dur = torch.randint(0, 7, (B, Lp), device="cuda", dtype=torch.int32)
+    cum, mel_len = L.lr_scan(dur)
+    Tmax = int(mel_len.max())
+    o32 = torch.full((B, Tmax, D), 9.0, device="cuda")
+    out, _, _, _ = L.lr_expand(x, cum, mel_len, Tmax, out_f32=o32)
+    assert torch.equal(o32, out.float())
+    p = torch.rand(B, Tmax, device="cuda") * 700 + 80
+    e = torch.rand(B, Tmax, device="cuda") * 400
+    pb = torch.exp(torch.linspace(4.26, 6.68, 255)).cuda()
+    eb = torch.linspace(0.0, 403.8, 255).cuda()
+    pt, et = torch.randn(256, D, device="cuda"), torch.randn(256, D, device="cuda")
+    x32 = torch.full((B, Tmax, D), 9.0, device="cuda")
+    y, _, _ = L.bucket_embed_add(out, p, e, pb, eb, pt, et, out_f32=x32)
+    assert torch.equal(x32, y.float())

@@ -124,10 +124,12 @@ class FastSpeech2(nn.Module):
                 raise ValueError("variance_precision 'fp32' needs duration_precision 'fp32' (the fp32-accurate encoder)")
             e_bf, e_split, pre = self._pre_lr(src.contiguous(), sm)
             va = self.variance_adaptor.run(e_bf, sm, mm, None, p_target, e_target, want_aux=True, pre=pre,
-                                           x_split=e_split if self.variance_precision == "fp32" else None)  # :176-181
+                                           x_split=e_split if self.variance_precision == "fp32" else None,
+                                           aux_f32=self.aux_outputs_fp32)  # :176-181
         else:
             e_bf, _, attn_enc = self.encoder.run(src, sm, kv_src_fn(), want_f32=False, return_attn=self.return_attn)  # :137
-            va = self.variance_adaptor.run(e_bf, sm, mm, d_target, p_target, e_target, want_aux=True)  # :176-181
+            va = self.variance_adaptor.run(e_bf, sm, mm, d_target, p_target, e_target, want_aux=True,
+                                           aux_f32=self.aux_outputs_fp32)  # :176-181
         mel_u8 = va["mel_mask"]
         kv_mel = lib.mask_lengths(mel_u8)
         tile_map = None
@@ -142,8 +144,10 @@ class FastSpeech2(nn.Module):
         self.last_aux = dict(dur=va["dur"], mel_len=va["mel_len"], frame_idx=va["frame_idx"], mel_pos=va["mel_pos"],
                              mel_mask=mel_u8, p_idx=va["p_idx"], e_idx=va["e_idx"], encoder_output=e_bf,
                              decoder_output=d_bf, va_x=va["x"], text_dur=va["text_dur"])
-        return (mel_pre, mel_post, va["log_d"], va["p"], va["e"], self._aux_f32(va["x"]), self._aux_f32(va["text_dur"]),
-                attn_enc, attn_dec, None, None, None, None, None)  # fastspeech2.py:241
+        va_x = va["x_f32"] if va["x_f32"] is not None else va["x"]
+        text_dur = va["text_dur_f32"] if va["text_dur_f32"] is not None else va["text_dur"]
+        return (mel_pre, mel_post, va["log_d"], va["p"], va["e"], va_x, text_dur, attn_enc, attn_dec, None, None, None,
+                None, None)  # fastspeech2.py:241
 
     # ------------------------------------------------------------------------------------------
     # Everything before the LengthRegulator's host sync has shapes that depend on (B, L) only, so it is captured ONCE
@@ -196,8 +200,9 @@ class FastSpeech2(nn.Module):
 
     def _aux_f32(self, t):
         """Slots 5 / 6 of the tuple (variance_adaptor_output, text_dur_predicted) are fp32 in the reference; the
-        kernels keep them in bf16.  No live caller reads them (train_fastspeech2.py:167, test_fastspeech2.py:169), so
-        `aux_outputs_fp32 = False` skips the two casts (216 MB of writes at cfg2)."""
+        kernels compute on bf16.  Inference: the producing kernels (bucket_embed_add, lr_expand) write the fp32 copies
+        themselves; training: a cast.  No live caller reads them (train_fastspeech2.py:167, test_fastspeech2.py:169), so
+        `aux_outputs_fp32 = False` skips them (216 MB of writes at cfg2)."""
         return t.float() if self.aux_outputs_fp32 else t
 
     def invalidate_caches(self) -> None:

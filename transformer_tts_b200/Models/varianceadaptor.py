@@ -82,9 +82,10 @@ class LengthRegulator(nn.Module):
         self.use_lstm = use_lstm
 
     @staticmethod
-    def run(x_bf16, dur_i32, max_length=None, want_aux=True, scan=None):
+    def run(x_bf16, dur_i32, max_length=None, want_aux=True, scan=None, f32_out=None):
         """Returns (expanded bf16 (B,Tmax,D), frame_idx, mel_pos, mel_mask u8, mel_len i32, cum).
-        scan: (cum, mel_len, max(mel_len) as a device scalar) when the caller already ran the prefix sum."""
+        scan: (cum, mel_len, max(mel_len) as a device scalar) when the caller already ran the prefix sum.
+        f32_out: a list that receives the expanded rows as an fp32 tensor too (written by the same kernel)."""
         cum, mel_len, tmax_dev = scan if scan is not None else (*lib.lr_scan(dur_i32), None)
         if max_length:
             Tmax = int(max_length)
@@ -93,7 +94,11 @@ class LengthRegulator(nn.Module):
                 tmax_dev = mel_len.max()
             Tmax = int(tmax_dev.item())  # the one host sync of free-running inference (varianceadaptor.py:254)
             Tmax = max(Tmax, 1)
-        out, fidx, mel_pos, mel_mask = lib.lr_expand(x_bf16, cum, mel_len, Tmax, want_aux=want_aux)
+        o32 = None
+        if f32_out is not None:
+            o32 = torch.empty((x_bf16.shape[0], Tmax, x_bf16.shape[2]), device=x_bf16.device, dtype=torch.float32)
+            f32_out.append(o32)
+        out, fidx, mel_pos, mel_mask = lib.lr_expand(x_bf16, cum, mel_len, Tmax, want_aux=want_aux, out_f32=o32)
         return out, fidx, mel_pos, mel_mask, mel_len, cum
 
     def LR(self, x, duration, max_length=None):
@@ -148,7 +153,7 @@ class VarianceAdaptor(nn.Module):
         return c.t
 
     def run(self, x_bf16, src_mask_u8, mel_mask_u8=None, duration_target=None, pitch_target=None,
-            energy_target=None, max_len=None, want_aux=True, log_d=None, pre=None, x_split=None):
+            energy_target=None, max_len=None, want_aux=True, log_d=None, pre=None, x_split=None, aux_f32=False):
         """Kernel sequence of varianceadaptor.py:66-129 on bf16 activations.  Returns a dict.
         log_d: the duration predictor's output when the caller already evaluated it (fp32-accurate chain).
         pre: (log_d, dur, cum, mel_len, max mel_len) from `run_pre` (free-running: everything before the one host sync).
@@ -170,7 +175,9 @@ class VarianceAdaptor(nn.Module):
             else:
                 dur = lib.round_durations(log_d)  # :75
                 max_len = None
-        xe, fidx, mel_pos, lr_mask, mel_len, _ = self.length_regulator.run(x_bf16, dur, max_len, want_aux, scan=scan)  # :73/:82
+        td32 = [] if aux_f32 else None  # aux_f32: tuple slots 5 / 6 in fp32, written by the kernels that produce them
+        xe, fidx, mel_pos, lr_mask, mel_len, _ = self.length_regulator.run(x_bf16, dur, max_len, want_aux, scan=scan,
+                                                                           f32_out=td32)  # :73/:82
         if duration_target is None or mel_mask_u8 is None:
             mel_mask_u8 = lr_mask  # :84 (the kernel applies the `arange <= mel_pos` rule)
         if x_split is not None:
@@ -188,10 +195,12 @@ class VarianceAdaptor(nn.Module):
         e_src = e if energy_target is None else energy_target.to(torch.float32).contiguous()  # :116-118
         pb, eb = self._bins(dev)
         tabs = self._tables()
+        x32 = torch.empty(xe.shape, device=dev, dtype=torch.float32) if aux_f32 else None
         out, p_idx, e_idx = lib.bucket_embed_add(xe, p_src, e_src, pb, eb, tabs["ptab"], tabs["etab"],
-                                                 want_idx=want_aux)  # :100-126
+                                                 want_idx=want_aux, out_f32=x32)  # :100-126
         return dict(x=out, log_d=log_d, p=p, e=e, mel_pos=mel_pos, mel_mask=mel_mask_u8, text_dur=xe,
-                    frame_idx=fidx, mel_len=mel_len, dur=dur, p_idx=p_idx, e_idx=e_idx)
+                    frame_idx=fidx, mel_len=mel_len, dur=dur, p_idx=p_idx, e_idx=e_idx, x_f32=x32,
+                    text_dur_f32=td32[0] if td32 else None)
 
     def run_pre(self, x_bf16, src_mask_u8, log_d=None):
         """Free-running: everything between the encoder and the host read of Tmax — duration predictor (:69) unless

@@ -175,7 +175,7 @@ __global__ void __launch_bounds__(256)
 lr_expand_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict__ cum,
                  const int32_t* __restrict__ mel_len, __nv_bfloat16* __restrict__ out,
                  int32_t* __restrict__ frame_idx, int64_t* __restrict__ mel_pos,
-                 uint8_t* __restrict__ mel_mask, int L, int Tmax, int D) {
+                 uint8_t* __restrict__ mel_mask, float* __restrict__ out32, int L, int Tmax, int D) {
   __shared__ int s_src[kLrFrames];
   const int b = blockIdx.y;
   const int t0 = blockIdx.x * kLrFrames;
@@ -225,6 +225,18 @@ lr_expand_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict_
 #pragma unroll
     for (int u = 0; u < U; ++u)
       if (ok[u]) __stcs(ob + c0 + u * 256, v[u]);
+    if (out32) {  // the same rows in fp32 (slot 6 of the reference's return tuple, Models/fastspeech2.py:241)
+      float4* o32 = reinterpret_cast<float4*>(out32 + (static_cast<int64_t>(b) * Tmax + t0) * D);
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (!ok[u]) continue;
+        const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&v[u]);
+        const float2 a = __bfloat1622float2(h2[0]), c = __bfloat1622float2(h2[1]);
+        const float2 d = __bfloat1622float2(h2[2]), e = __bfloat1622float2(h2[3]);
+        __stcs(o32 + 2 * (c0 + u * 256), make_float4(a.x, a.y, c.x, c.y));
+        __stcs(o32 + 2 * (c0 + u * 256) + 1, make_float4(d.x, d.y, e.x, e.y));
+      }
+    }
   }
 }
 
@@ -240,7 +252,8 @@ bucket_embed_add_kernel(const __nv_bfloat16* __restrict__ x, const float* __rest
                         const float* __restrict__ e, const float* __restrict__ pbins,
                         const float* __restrict__ ebins, const float* __restrict__ ptab,
                         const float* __restrict__ etab, __nv_bfloat16* __restrict__ out,
-                        int32_t* __restrict__ p_idx, int32_t* __restrict__ e_idx, int64_t rows, int nb) {
+                        int32_t* __restrict__ p_idx, int32_t* __restrict__ e_idx, float* __restrict__ out32,
+                        int64_t rows, int nb) {
   constexpr int D = 128 * NV;
   const int lane = threadIdx.x & 31;
   const int64_t warp0 = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -283,6 +296,12 @@ bucket_embed_add_kernel(const __nv_bfloat16* __restrict__ x, const float* __rest
       const float4 r = make_float4((x01.x + a.x) + bq.x, (x01.y + a.y) + bq.y, (x23.x + a.z) + bq.z,
                                    (x23.y + a.w) + bq.w);
       store_bf16x4(out + row * D + c * 4, r);
+      if (out32) {  // slot 5 of the reference's return tuple in its dtype: the bf16-rounded value, widened
+        const uint2 u = *reinterpret_cast<const uint2*>(out + row * D + c * 4);
+        const float2 lo = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.x));
+        const float2 hi = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.y));
+        __stcs(reinterpret_cast<float4*>(out32 + row * D) + c, make_float4(lo.x, lo.y, hi.x, hi.y));
+      }
     }
   }
 }
@@ -430,14 +449,14 @@ extern "C" int ttsb200_lr_scan(const int32_t* dur, int32_t* cum, int32_t* mel_le
 }
 
 extern "C" int ttsb200_lr_expand(const void* x, const int32_t* cum, const int32_t* mel_len, void* out,
-                                 int32_t* frame_idx, int64_t* mel_pos, uint8_t* mel_mask, int32_t B,
+                                 int32_t* frame_idx, int64_t* mel_pos, uint8_t* mel_mask, float* out_f32, int32_t B,
                                  int32_t L, int32_t Tmax, int32_t D, ttsb200_stream_t s) {
   TTSB_CHECK_ARG(x && cum && mel_len && out && B > 0 && L > 0 && Tmax > 0, "lr_expand: bad args");
   TTSB_CHECK_ARG(D % 8 == 0, "lr_expand: D (%d) must be a multiple of 8", D);
   dim3 grid((Tmax + kLrFrames - 1) / kLrFrames, B);
   lr_expand_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(s)>>>(
       static_cast<const __nv_bfloat16*>(x), cum, mel_len, static_cast<__nv_bfloat16*>(out), frame_idx,
-      mel_pos, mel_mask, L, Tmax, D);
+      mel_pos, mel_mask, out_f32, L, Tmax, D);
   TTSB_LAUNCH_CHECK();
   return TTSB_OK;
 }
@@ -445,7 +464,7 @@ extern "C" int ttsb200_lr_expand(const void* x, const int32_t* cum, const int32_
 extern "C" int ttsb200_bucket_embed_add(const void* x, const float* p, const float* e,
                                         const float* pbins, const float* ebins, const float* ptab,
                                         const float* etab, void* out, int32_t* p_idx, int32_t* e_idx,
-                                        int64_t rows, int32_t D, int32_t nb, ttsb200_stream_t s) {
+                                        float* out_f32, int64_t rows, int32_t D, int32_t nb, ttsb200_stream_t s) {
   TTSB_CHECK_ARG(x && p && e && pbins && ebins && ptab && etab && out && rows > 0 && nb > 0,
                  "bucket_embed_add: bad args");
   TTSB_CHECK_ARG(nb <= 256, "bucket_embed_add: at most 256 bin edges (got %d)", nb);
@@ -455,11 +474,11 @@ extern "C" int ttsb200_bucket_embed_add(const void* x, const float* p, const flo
   if (D == 384)
     bucket_embed_add_kernel<3><<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), p, e, pbins,
                                                      ebins, ptab, etab, static_cast<__nv_bfloat16*>(out),
-                                                     p_idx, e_idx, rows, nb);
+                                                     p_idx, e_idx, out_f32, rows, nb);
   else if (D == 256)
     bucket_embed_add_kernel<2><<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), p, e, pbins,
                                                      ebins, ptab, etab, static_cast<__nv_bfloat16*>(out),
-                                                     p_idx, e_idx, rows, nb);
+                                                     p_idx, e_idx, out_f32, rows, nb);
   else
     TTSB_CHECK_ARG(false, "bucket_embed_add: D=%d unsupported (256 or 384)", D);
   TTSB_LAUNCH_CHECK();

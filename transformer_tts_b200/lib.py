@@ -64,8 +64,8 @@ _SIGNATURES = {
                            C.c_int64, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_round_durations": ([C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p], C.c_int),
     "ttsb200_lr_scan": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p], C.c_int),
-    "ttsb200_lr_expand": ([C.c_void_p] * 7 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
-    "ttsb200_bucket_embed_add": ([C.c_void_p] * 10 + [C.c_int64, C.c_int32, C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_lr_expand": ([C.c_void_p] * 8 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
+    "ttsb200_bucket_embed_add": ([C.c_void_p] * 11 + [C.c_int64, C.c_int32, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_cast_bf16": ([C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p], C.c_int),
     # ---- training step ----
     "ttsb200_attention_fwd_lse": ([C.c_void_p] * 5 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
@@ -361,7 +361,9 @@ def lr_scan(dur: torch.Tensor):
     return cum, mel_len
 
 
-def lr_expand(x: torch.Tensor, cum: torch.Tensor, mel_len: torch.Tensor, Tmax: int, want_aux: bool = True):
+def lr_expand(x: torch.Tensor, cum: torch.Tensor, mel_len: torch.Tensor, Tmax: int, want_aux: bool = True,
+              out_f32: Optional[torch.Tensor] = None):
+    """out_f32 (B,Tmax,D) fp32, when given, receives the expanded rows widened to fp32 as well."""
     B, L, D = x.shape
     dev = x.device
     out = torch.empty((B, Tmax, D), device=dev, dtype=torch.bfloat16)
@@ -370,12 +372,13 @@ def lr_expand(x: torch.Tensor, cum: torch.Tensor, mel_len: torch.Tensor, Tmax: i
     mel_mask = torch.empty((B, Tmax), device=dev, dtype=torch.uint8)
     _check(load().ttsb200_lr_expand(_ptr(x, torch.bfloat16, "x"), _ptr(cum, torch.int32, "cum"),
                                     _ptr(mel_len, torch.int32, "mel_len"), _ptr(out), _ptr(frame_idx),
-                                    _ptr(mel_pos), _ptr(mel_mask), B, L, Tmax, D, _stream()), "lr_expand")
+                                    _ptr(mel_pos), _ptr(mel_mask), _ptr(out_f32, torch.float32, "out_f32"), B, L, Tmax,
+                                    D, _stream()), "lr_expand")
     _count()
     return out, frame_idx, mel_pos, mel_mask
 
 
-def bucket_embed_add(x, p, e, pbins, ebins, ptab, etab, want_idx: bool = False):
+def bucket_embed_add(x, p, e, pbins, ebins, ptab, etab, want_idx: bool = False, out_f32=None):
     D = x.shape[-1]
     rows = x.numel() // D
     out = torch.empty_like(x)
@@ -386,7 +389,8 @@ def bucket_embed_add(x, p, e, pbins, ebins, ptab, etab, want_idx: bool = False):
                                            _ptr(ebins, torch.float32, "energy_bins"),
                                            _ptr(ptab, torch.float32, "pitch_table"),
                                            _ptr(etab, torch.float32, "energy_table"), _ptr(out), _ptr(p_idx),
-                                           _ptr(e_idx), rows, D, pbins.numel(), _stream()), "bucket_embed_add")
+                                           _ptr(e_idx), _ptr(out_f32, torch.float32, "out_f32"), rows, D, pbins.numel(),
+                                           _stream()), "bucket_embed_add")
     _count()
     return out, p_idx, e_idx
 
