@@ -533,3 +533,43 @@ def test_pre_length_regulator_graph_is_bit_identical_to_eager(setup):
         model.duration_precision = "fp32"
         model.use_cuda_graphs = True
         model.load_state_dict(sd)
+
+
+@pytest.mark.parametrize("B,L,ragged,seed", [(1, 1, False, 5), (2, 7, True, 6), (3, 300, True, 8), (1, 513, False, 9)])
+def test_free_running_edge_shapes_match_oracle(setup, B, L, ragged, seed):
+    """Free-running parity away from the benchmark shape: a single phoneme, a few phonemes (every tile mostly padding),
+    long texts (several key tiles in the fp32-accurate encoder attention, T up to ~4000 frames, close to the reference's
+    positional-table limit of 5000).  Durations must equal the fp32 oracle's wherever the oracle is not within 1e-4 of a
+    rounding boundary; integer outputs exact; mel within the free-running bar."""
+    from oracle import fastspeech2_oracle as O
+    from transformer_tts_b200 import synth
+
+    hp, sd, sd_gpu, model = setup
+    text, pos, lens = synth.synth_text_batch(B, L, ragged=ragged, seed=seed, min_len=max(1, L // 3))
+    text, pos = text.cuda(), pos.cuda()
+    src_mask = (pos != 0).unsqueeze(-2)
+    valid = pos != 0
+    with torch.no_grad():
+        e_out, _ = O.encoder(sd_gpu, "encoder.", text, src_mask, hp.n_layer_encoder, hp.n_head_encoder)
+        log_d_ref = O.variance_predictor(sd_gpu, "variance_adaptor.duration_predictor.", e_out, src_mask)
+        out = model(text, src_mask)
+    aux = dict(model.last_aux)
+    d_ref = torch.where(valid, O.round_durations(log_d_ref).long(), torch.zeros_like(pos))
+    dist = boundary_distance(log_d_ref)
+    flips = (aux["dur"].long() != d_ref) & valid
+    near = (dist <= BOUNDARY_TOL) & valid
+    print(f"\n[edge B={B} L={L}] frames {int(aux['mel_len'].sum())} Tmax {out[0].shape[1]} flips {int(flips.sum())} "
+          f"near-boundary {int(near.sum())} log_d max abs err {float((out[2] - log_d_ref)[valid].abs().max()):.2e}")
+    assert not bool((flips & ~near).any())
+    assert float((out[2] - log_d_ref)[valid].abs().max()) < 2e-5
+    if int(flips.sum()) == 0 and int(d_ref.sum()) > 0:
+        mel_len = d_ref.sum(1)
+        T = int(mel_len.max())
+        ar = torch.arange(1, T + 1, device="cuda").unsqueeze(0)
+        pos_mel = torch.where(ar <= mel_len.unsqueeze(1), ar.expand(B, T), torch.zeros(B, T, dtype=torch.long, device="cuda"))
+        with torch.no_grad():
+            ref = run_oracle(sd_gpu, hp, text, src_mask, mel_mask=(pos_mel != 0).unsqueeze(-2), d_target=d_ref)
+        assert torch.equal(aux["mel_len"].long(), mel_len) and out[0].shape[1] == T
+        assert torch.equal(aux["mel_pos"], ref["mel_pos"]) and torch.equal(aux["frame_idx"].long(), ref["frame_idx"])
+        assert rel_l2(valid_rows(out[1], mel_len), valid_rows(ref["outputs_postnet"], mel_len)) < 4e-2
+    assert torch.isfinite(out[1]).all()
