@@ -194,6 +194,24 @@ int ttsb200_bucket_embed_add(const void* x_bf16, const float* p, const float* e,
                              int32_t* p_idx, int32_t* e_idx, float* out_f32, int64_t rows, int32_t D, int32_t nb,
                              ttsb200_stream_t stream);
 
+/* LengthRegulator that allocates nothing.  It has no counterpart in the reference and was added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  = ttsb200_lr_scan followed by ttsb200_lr_expand on the same stream, with the scratch between
+ * them (cum (B,L) int32 and mel_len (B) int32) held in a file-scope device array of the library (260 KB on every GPU
+ * that loads it, until exit) instead of caller memory.  The caller still passes inputs and outputs; arguments as in
+ * ttsb200_lr_expand, plus dur int32 (B,L) and the optional mel_len_out int32 (B).
+ * Limits: B <= TTSB200_LR_STATIC_MAX_BATCH and B*L <= TTSB200_LR_STATIC_MAX_PHONEMES; larger sizes return
+ * TTSB200 error -1 with a message naming the limit (use the two entry points above with your own scratch).
+ * Calls no cudaMalloc / cudaFree / allocating routine.  The first call on each device resolves the array's device
+ * address (cudaGetSymbolAddress), so make one call per device before stream capture.  The array is shared by every
+ * call on a device and keeps the last call's contents; the scan rewrites every entry the expansion reads, so nothing
+ * needs clearing, but calls that OVERLAP on the GPU (different streams without a dependency) race on it. */
+#define TTSB200_LR_STATIC_MAX_BATCH 1024
+#define TTSB200_LR_STATIC_MAX_PHONEMES 65536
+int ttsb200_length_regulate_static(const void* x_bf16, const int32_t* dur, void* out_bf16, int32_t* frame_idx,
+                                   int64_t* mel_pos, uint8_t* mel_mask, float* out_f32, int32_t* mel_len_out,
+                                   int32_t B, int32_t L, int32_t Tmax, int32_t D, ttsb200_stream_t stream);
+
 /* fp32 -> bf16 cast of a dense buffer (weight/activation staging). */
 int ttsb200_cast_bf16(const float* x, void* y_bf16, int64_t n, ttsb200_stream_t stream);
 

@@ -2,6 +2,8 @@
 // standalone LayerNorm, duration rounding, LengthRegulator (warp-scan prefix sum + vectorised
 // frame gather), bucketize + embedding add, mask -> length, fp32 -> bf16 cast.
 // All of them are sized so every warp moves 16-byte (or 8-byte for bf16x4) vectors, fully coalesced.
+#include <mutex>
+
 #include "common.cuh"
 #include "../../include/ttsb200.h"
 
@@ -493,5 +495,72 @@ extern "C" int ttsb200_cast_bf16(const float* x, void* y, int64_t n, ttsb200_str
   cast_bf16_kernel<<<static_cast<unsigned>((thr + 255) / 256), 256, 0, static_cast<cudaStream_t>(s)>>>(
       x, static_cast<__nv_bfloat16*>(y), n);
   TTSB_LAUNCH_CHECK();
+  return TTSB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// LengthRegulator without allocations: ttsb200_length_regulate_static.
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  ttsb200_lr_scan /
+// ttsb200_lr_expand take their scratch (cum (B,L) and mel_len (B)) from the caller; here it lives in a file-scope
+// device array of fixed size that every GPU loading the library holds until exit (260 KB).
+//
+// g_lr_scratch is a HOST-SIDE STAND-IN in host code, not a device address: the entry point resolves the device
+// address once per device with cudaGetSymbolAddress (that device current) and passes the pointer to the kernels.
+// Nothing has to start at zero: lr_scan_kernel writes every cum[b][0..L) and mel_len[b] that lr_expand_kernel
+// reads, in the same call and stream, so the previous call's contents are never observed.  All calls on one
+// device share the array: calls that overlap on the GPU (different streams, no dependency) race.
+// ------------------------------------------------------------------------------------------------
+namespace ttsb {
+constexpr int kLrStaticMaxCum = TTSB200_LR_STATIC_MAX_PHONEMES;  // B*L entries of cum
+constexpr int kLrStaticMaxB = TTSB200_LR_STATIC_MAX_BATCH;       // mel_len entries
+static __device__ __align__(256) int32_t g_lr_scratch[kLrStaticMaxCum + kLrStaticMaxB];
+
+constexpr int kLrMaxDevices = 64;
+static int32_t* g_lr_scratch_ptr[kLrMaxDevices];  // device address of g_lr_scratch, per device ordinal
+static std::mutex g_lr_scratch_mu;
+
+// Device address of g_lr_scratch on the CURRENT device (resolved once per device, return code checked).
+static int lr_static_scratch(int32_t** out) {
+  int dev = 0;
+  TTSB_CHECK_CUDA(cudaGetDevice(&dev));
+  TTSB_CHECK_ARG(dev >= 0 && dev < kLrMaxDevices, "length_regulate_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_lr_scratch_mu);
+  if (!g_lr_scratch_ptr[dev]) {
+    void* ptr = nullptr;
+    TTSB_CHECK_CUDA(cudaGetSymbolAddress(&ptr, g_lr_scratch));
+    TTSB_CHECK_ARG(ptr != nullptr, "length_regulate_static: cudaGetSymbolAddress returned a null address");
+    g_lr_scratch_ptr[dev] = static_cast<int32_t*>(ptr);
+  }
+  *out = g_lr_scratch_ptr[dev];
+  return TTSB_OK;
+}
+}  // namespace ttsb
+
+extern "C" int ttsb200_length_regulate_static(const void* x, const int32_t* dur, void* out, int32_t* frame_idx,
+                                              int64_t* mel_pos, uint8_t* mel_mask, float* out_f32,
+                                              int32_t* mel_len_out, int32_t B, int32_t L, int32_t Tmax, int32_t D,
+                                              ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(x && dur && out && B > 0 && L > 0 && Tmax > 0, "length_regulate_static: bad args");
+  TTSB_CHECK_ARG(D % 8 == 0, "length_regulate_static: D (%d) must be a multiple of 8", D);
+  TTSB_CHECK_ARG(B <= kLrStaticMaxB && static_cast<int64_t>(B) * L <= kLrStaticMaxCum,
+                 "length_regulate_static: B=%d, B*L=%lld exceed the static scratch (B <= %d, B*L <= %d); use "
+                 "ttsb200_lr_scan + ttsb200_lr_expand with caller-owned scratch",
+                 B, static_cast<long long>(B) * L, kLrStaticMaxB, kLrStaticMaxCum);
+  int32_t* scratch = nullptr;
+  const int rc = lr_static_scratch(&scratch);
+  if (rc != TTSB_OK) return rc;
+  int32_t* cum = scratch;
+  int32_t* mel_len = scratch + kLrStaticMaxCum;
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  lr_scan_kernel<<<(B + 3) / 4, 128, 0, st>>>(dur, cum, mel_len, B, L);
+  TTSB_LAUNCH_CHECK();
+  dim3 grid((Tmax + kLrFrames - 1) / kLrFrames, B);
+  lr_expand_kernel<<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), cum, mel_len,
+                                         static_cast<__nv_bfloat16*>(out), frame_idx, mel_pos, mel_mask, out_f32, L,
+                                         Tmax, D);
+  TTSB_LAUNCH_CHECK();
+  if (mel_len_out)  // device-to-device copy of B int32: no allocation, legal under stream capture
+    TTSB_CHECK_CUDA(cudaMemcpyAsync(mel_len_out, mel_len, sizeof(int32_t) * B, cudaMemcpyDeviceToDevice, st));
   return TTSB_OK;
 }

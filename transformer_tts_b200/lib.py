@@ -65,6 +65,7 @@ _SIGNATURES = {
     "ttsb200_round_durations": ([C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p], C.c_int),
     "ttsb200_lr_scan": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_lr_expand": ([C.c_void_p] * 8 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
+    "ttsb200_length_regulate_static": ([C.c_void_p] * 8 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
     "ttsb200_bucket_embed_add": ([C.c_void_p] * 11 + [C.c_int64, C.c_int32, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_cast_bf16": ([C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p], C.c_int),
     # ---- training step ----
