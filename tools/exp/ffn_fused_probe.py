@@ -85,4 +85,4 @@ L_.ttsb200_debug_ffn_trace(buf, 0, 0)
 for pair in (0, 20, 73):
     o = buf[pair * 16: pair * 16 + 16]
     n = max(o[6], 1)
-    print(f"pair {pair}: issuer total {o[0]} clk over {o[6]} units ({o[0] / n:.0f}/unit): wait X {o[1] / n:.0f} W1 {o[2] / n:.0f} W2 {o[3] / n:.0f} H {o[4] / n:.0f} A2E {o[5] / n:.0f} | LN epilogue {o[8] / n:.0f} clk/unit")
+    print(f"pair {pair}: issuer total {o[0]} clk over {o[6]} units ({o[0] / n:.0f}/unit): wait X {o[1] / n:.0f} W1 {o[2] / n:.0f} W2 {o[3] / n:.0f} H {o[4] / n:.0f} A2E {o[5] / n:.0f} | LN epilogue {o[8] / n:.0f} clk/unit = pass1 {o[9] / n:.0f} + pass2 {o[10] / n:.0f} (ring wait {o[12] / n:.0f}) + pass3 {o[11] / n:.0f}")

@@ -38,7 +38,8 @@ constexpr int kW2Box = 96 * 128;                // this CTA's 96 of 192 output r
 constexpr int kW2Stage = 2 * kW2Box;            // 24 KB
 constexpr int kWStages = 2;
 constexpr int kWBytes = kWStages * (kW1Stage + kW2Stage);  // 96 KB; aliased by the epilogue's fp32 residual ring
-constexpr int kRing = 6;                        // ring slots of 16 KB (even: a slot always belongs to the same column half)
+constexpr int kRing = 6;                        // residual boxes (16 KB) that alias the weight stages; the other 6 alias the x tile
+constexpr int kResBoxes = kD / 32;              // 12 boxes of 128 rows x 32 fp32 columns: the whole residual tile, one slot each
 constexpr int kStoreBytes = 0;                  // (the bf16 outputs are staged in the drained ring slots)
 constexpr int kParamFloats = 5 * kD;            // b2, g1, b1, g2, b2
 constexpr int kStatBytes = 2 * 2 * kBlockM * 8;
@@ -69,8 +70,9 @@ enum {
   B_A2E,                      // u read back by both CTAs' epilogue warps (leader's)
   B_EPI,                      // this CTA's epilogue is done with the ring, which aliases the weight stages (local, 256 arrivals)
   B_XR,                       // this CTA's epilogue has read the inner residual out of the x tile (local, 256 arrivals)
-  B_RF, B_RE = B_RF + kRing,  // residual ring
-  B_COUNT = B_RE + kRing
+  B_XS,                       // the fp32 stores out of the residual boxes that alias the x tile have read them (local, 2 arrivals)
+  B_RF,                       // [12] residual box landed
+  B_COUNT = B_RF + kResBoxes
 };
 
 __device__ __forceinline__ void umma_bf16_ts_2sm(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc,
@@ -125,6 +127,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       uint32_t cnt = 1;
       if (i == B_HF || i == B_HF + 1 || i == B_A2E) cnt = 16;      // 8 epilogue warps x 2 CTAs
       if (i == B_EPI || i == B_XR) cnt = kEpiThreads;
+      if (i == B_XS) cnt = 2;
       mbar_init(bar(i), cnt);
     }
     fence_mbar_init();
@@ -183,7 +186,8 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         decode(unit, b, t0);
         if (ui > 0) {
           mbar_wait(bar(B_XE), (ui - 1) & 1);   // the previous unit's last GEMM1 has read the x tile ...
-          mbar_wait(bar(B_XR), (ui - 1) & 1);   // ... and its epilogue the inner residual (x itself)
+          mbar_wait(bar(B_XS), (ui - 1) & 1);   // ... its epilogue has read the inner residual (x itself) and the second
+                                                // half of the residual boxes, which borrow the tile's memory, has left
         }
         const uint32_t xf = bar(B_XF);
         if (is_leader) mbar_arrive_expect_tx(xf, 2 * kXBytes);
@@ -206,7 +210,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     const uint32_t leader = elect_one();
     const uint32_t x_base = smem_u32(sX);
     uint32_t g1 = 0, g2 = 0, ui = 0;
-    const bool tr = p.debug != 0;
+    const bool tr = (p.debug & 1) != 0;
     long long t_w1 = 0, t_w2 = 0, t_hf = 0, t_xf = 0, t_a2e = 0, tc0 = 0;
     const long long t_start = tr ? clock64() : 0;
     auto gemm1 = [&](int j, bool last) {   // hidden chunk j -> TMEM buffer j & 1
@@ -271,25 +275,27 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       o[0] = clock64() - t_start; o[1] = t_xf; o[2] = t_w1; o[3] = t_w2; o[4] = t_hf; o[5] = t_a2e; o[6] = ui;
     }
   } else if (warp == 2) {
-    // ===================== residual-ring producer: waits for the unit's last GEMM2 (the ring aliases the weight stages) ==
+    // ===================== residual producer: the fp32 residual tile y, 12 boxes, EVERY box in its own slot ============
+    // Boxes 0..5 (the first three 32-column chunks of each half) alias the weight stages, idle after the unit's last
+    // GEMM2; boxes 6..11 alias the x tile, idle once pass 1 of the epilogue has read the inner residual out of it (the
+    // next unit's x tile is loaded after pass 2 instead: it is still early, the first GEMM1 waits for the weight stages,
+    // which the epilogue holds until its end).  No slot is ever recycled inside a unit, so no load waits for a store.
     if (lane == 0) {
       tma_prefetch_desc(&tmRes32);
-      uint32_t i = 0, ui = 0;
-      auto push = [&](const CUtensorMap* tm, int c0, int t0, int b) {
-        const int slot = i % kRing;
-        mbar_wait(bar(B_RE + slot), ((i / kRing) & 1) ^ 1);
-        const uint32_t full = bar(B_RF + slot);
-        mbar_arrive_expect_tx(full, kBoxBytes16K);
-        tma_load_3d(smem_u32(sRing + slot * kBoxBytes16K), tm, full, c0, t0, b);
-        ++i;
-      };
       constexpr int HALF = kD / 2;
+      uint32_t ui = 0;
       for (int unit = unit0; unit < num_units; unit += ustride, ++ui) {
         int b, t0;
         decode(unit, b, t0);
+        auto push = [&](int idx, uint8_t* box) {   // idx = 2 * chunk + column half
+          const uint32_t full = bar(B_RF + idx);
+          mbar_arrive_expect_tx(full, kBoxBytes16K);
+          tma_load_3d(smem_u32(box), &tmRes32, full, (idx & 1) * HALF + (idx >> 1) * 32, t0, b);
+        };
         mbar_wait(bar(B_A2F), ui & 1);
-        for (int c = 0; c < HALF / 32; ++c)
-          for (int hh = 0; hh < 2; ++hh) push(&tmRes32, hh * HALF + c * 32, t0, b);   // fp32 residual stream y
+        for (int idx = 0; idx < kRing; ++idx) push(idx, sRing + idx * kBoxBytes16K);
+        mbar_wait(bar(B_XR), ui & 1);
+        for (int idx = kRing; idx < kResBoxes; ++idx) push(idx, sX + (idx - kRing) * kBoxBytes16K);
       }
     }
   } else if (warp >= kEpiWarp0) {
@@ -297,7 +303,6 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     constexpr int BLOCK_N = kD;
     constexpr int HALF = kD / 2;
     constexpr int NCH = HALF / 32;
-    constexpr int RS = kRing;
     const int q = warp & 3;
     const int wg = (warp - kEpiWarp0) >> 2;
     const int row = q * 32 + lane;
@@ -318,36 +323,10 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     epi_bar_all();
     const int c0h = wg * HALF;
     const float inv_n = 1.f / static_cast<float>(BLOCK_N);
-    uint32_t xc = 0, rk = 0, ui = 0;
-    auto ring_acquire = [&](int& slot) -> uint8_t* {
-      const uint32_t idx = 2 * rk + wg;
-      slot = idx % RS;
-      mbar_wait(bar(B_RF + slot), (idx / RS) & 1);
-      ++rk;
-      return sRing + slot * kBoxBytes16K;
-    };
-    // fp32 result formed in place in a ring box leaves by TMA store.  The slot is released (by the issuing thread
-    // alone: the barrier counts 1) once the store has READ it — one chunk later, so nobody waits for that read.
-    int pend_slot = -1;
-    auto ring_store_release = [&](uint8_t* box, int slot, int c, int t0, int b) {
-      fence_async_smem();
-      wg_bar(wg);
-      if (row == 0) {
-        tma_store_3d(&tmOut32, smem_u32(box), c, t0, b);
-        tma_store_commit();
-        if (pend_slot >= 0) {
-          tma_store_wait_read1();   // every store but the one just committed has read its box
-          mbar_arrive(bar(B_RE + pend_slot));
-        }
-        pend_slot = slot;
-      }
-    };
-    auto ring_flush = [&]() {
-      if (row == 0) {
-        tma_store_wait_read0();
-        if (pend_slot >= 0) mbar_arrive(bar(B_RE + pend_slot));
-        pend_slot = -1;
-      }
+    uint32_t xc = 0, ui = 0;
+    long long t_ring = 0;
+    auto res_box = [&](int idx) -> uint8_t* {
+      return idx < kRing ? sRing + idx * kBoxBytes16K : sX + (idx - kRing) * kBoxBytes16K;
     };
     auto exchange = [&](float& a, float& c) {
       float2* buf = sStat + (xc & 1) * 2 * kBlockM;
@@ -407,7 +386,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       const bool valid = t < p.T;
       mbar_wait(bar(B_A2F), ui & 1);
       tc_fence_after();
-      const long long te0 = p.debug ? clock64() : 0;
+      const long long te0 = (p.debug & 1) ? clock64() : 0;
       const uint32_t trow = tmem_u + lane_off + c0h;
       float sum = 0.f, sq = 0.f;
 #pragma unroll 1
@@ -431,6 +410,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       }
       mbar_arrive(bar(B_XR));   // the x tile may be overwritten by the next unit's
       tmem_st_wait();
+      const long long te1 = (p.debug & 1) ? clock64() : 0;
       exchange(sum, sq);
       float mean = sum * inv_n;
       float rstd = rsqrtf(fmaxf(sq * inv_n - mean * mean, 0.f) + p.eps);
@@ -442,8 +422,13 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         tmem_ld32(trow + cc, v);
         tmem_ld_wait();
         layernorm32(v, c0h + cc, mean, rstd, sG1, sB1);
-        int slot;
-        uint8_t* box = ring_acquire(slot);
+        const int idx = 2 * ch + wg;
+        uint8_t* box = res_box(idx);
+        {
+          const long long tr0 = (p.debug & 1) ? clock64() : 0;
+          mbar_wait(bar(B_RF + idx), ui & 1);
+          if (p.debug & 1) t_ring += clock64() - tr0;
+        }
         float y[32];
         box_row_ld_f32(box, row, y);
 #pragma unroll
@@ -453,11 +438,20 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
           sq2 = fmaf(v[i], v[i], sq2);
         }
         tmem_st32(trow + cc, v);
-        box_row_st_f32(box, row, v);
-        ring_store_release(box, slot, c0h + cc, t0, b);
+        box_row_st_f32(box, row, v);   // z formed in place in the residual box leaves by TMA store
+        fence_async_smem();
+        wg_bar(wg);
+        if (row == 0) {
+          tma_store_3d(&tmOut32, smem_u32(box), c0h + cc, t0, b);
+          tma_store_commit();
+        }
       }
-      ring_flush();             // the last fp32 store has read its slot
+      if (row == 0) {             // every fp32 store of this warpgroup has read its box: the x tile's memory is free
+        tma_store_wait_read0();   // again, and pass 3 may stage its output in this warpgroup's first three boxes
+        mbar_arrive(bar(B_XS));
+      }
       tmem_st_wait();
+      const long long te2 = (p.debug & 1) ? clock64() : 0;
       exchange(sum2, sq2);      // (a barrier over all epilogue threads: every slot of the ring is drained past this point)
       mean = sum2 * inv_n;
       rstd = rsqrtf(fmaxf(sq2 * inv_n - mean * mean, 0.f) + p.eps);
@@ -485,7 +479,12 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       }
       (void)valid;
       if (row == 0) tma_store_wait_read0();   // the boxes alias the weight stages: the stores have read them
-      if (p.debug && et == 0 && is_leader) g_ffn_trace[(blockIdx.x >> 1) * 16 + 8] += clock64() - te0;
+      if ((p.debug & 1) && et == 0 && is_leader) {
+        long long* o = g_ffn_trace + (blockIdx.x >> 1) * 16;
+        const long long te3 = clock64();
+        o[8] += te3 - te0; o[9] += te1 - te0; o[10] += te2 - te1; o[11] += te3 - te2; o[12] += t_ring;
+        t_ring = 0;
+      }
       mbar_arrive(bar(B_EPI));                // the next unit's weights may stream in
     }
     if (row == 0) tma_store_wait_all();
