@@ -69,8 +69,8 @@ enum {
   B_A2F = B_HF + 2,           // u complete (multicast commit)
   B_A2E,                      // u read back by both CTAs' epilogue warps (leader's)
   B_EPI,                      // this CTA's epilogue is done with the ring, which aliases the weight stages (local, 256 arrivals)
-  B_XR,                       // this CTA's epilogue has read the inner residual out of the x tile (local, 256 arrivals)
-  B_XS,                       // the fp32 stores out of the residual boxes that alias the x tile have read them (local, 2 arrivals)
+  B_XR,                       // [6] this CTA's epilogue has read the inner residual out of k-block i of the x tile (local, 128 arrivals)
+  B_XS = B_XR + kKB,                       // the fp32 stores out of the residual boxes that alias the x tile have read them (local, 2 arrivals)
   B_RF,                       // [12] residual box landed
   B_COUNT = B_RF + kResBoxes
 };
@@ -126,7 +126,8 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     for (int i = 0; i < B_COUNT; ++i) {
       uint32_t cnt = 1;
       if (i == B_HF || i == B_HF + 1 || i == B_A2E) cnt = 16;      // 8 epilogue warps x 2 CTAs
-      if (i == B_EPI || i == B_XR) cnt = kEpiThreads;
+      if (i == B_EPI) cnt = kEpiThreads;
+      if (i >= B_XR && i < B_XR + kKB) cnt = kEpiThreads / 2;
       if (i == B_XS) cnt = 2;
       mbar_init(bar(i), cnt);
     }
@@ -143,6 +144,12 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
   const uint32_t tmem_u = tmem_base;               // u: columns [0, 384)
   const uint32_t tmem_h = tmem_base + kD;          // hidden chunks: [384, 448) and [448, 512)
 
+  // residual box idx = 2 * chunk + column half: 0..5 in the weight stages; 6.. in the x tile: the k-block that the box's
+  // own warpgroup reads (and releases) during chunks 2 * (chunk - 3), 2 * (chunk - 3) + 1 of pass 1
+  auto res_box = [&](int idx) -> uint8_t* {
+    if (idx < kRing) return sRing + idx * kBoxBytes16K;
+    return sX + ((idx & 1) * 3 + ((idx - kRing) >> 1)) * kBoxBytes16K;
+  };
   auto decode = [&](int unit, int& b, int& t0) {
     int mt = 2 * unit + static_cast<int>(cta_rank);
     if (mt >= total_mt) {  // odd tile count: the last pair's second tile is empty (loads zero-fill, stores clip)
@@ -193,10 +200,12 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         if (is_leader) mbar_arrive_expect_tx(xf, 2 * kXBytes);
 #pragma unroll
         for (int kb = 0; kb < kKB; ++kb) tma_load_3d_2sm(smem_u32(sX + kb * kBoxBytes16K), &tmX, xf, kb * kBlockK, t0, b);
-        if (ui > 0) mbar_wait(bar(B_EPI), (ui - 1) & 1);  // the weight stages alias the epilogue's residual ring
+        // the W1 stages alias residual boxes 0..2, drained with pass 2 (B_XS above): the first two GEMM1s of this unit run
+        // while pass 3 of the previous one is still storing; the W2 stages hold pass 3's staging boxes until its end
         load_w1(0);
         load_w1(1);
         for (int j = 0; j < kChunks; ++j) {
+          if (j == 0 && ui > 0) mbar_wait(bar(B_EPI), (ui - 1) & 1);
           load_w2(j);
           if (j + 2 < kChunks) load_w1(j + 2);
         }
@@ -276,10 +285,11 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     }
   } else if (warp == 2) {
     // ===================== residual producer: the fp32 residual tile y, 12 boxes, EVERY box in its own slot ============
-    // Boxes 0..5 (the first three 32-column chunks of each half) alias the weight stages, idle after the unit's last
-    // GEMM2; boxes 6..11 alias the x tile, idle once pass 1 of the epilogue has read the inner residual out of it (the
-    // next unit's x tile is loaded after pass 2 instead: it is still early, the first GEMM1 waits for the weight stages,
-    // which the epilogue holds until its end).  No slot is ever recycled inside a unit, so no load waits for a store.
+    // Boxes 0..5 (chunks 0..2 of each column half) alias the weight stages: 0..2 the W1 stages, idle after the unit's last
+    // GEMM1, 3..5 the W2 stages, idle after its last GEMM2.  Boxes 6..11 alias the x tile, k-block by k-block as pass 1
+    // of the epilogue has read the inner residual out of it (the next unit's x tile is loaded after pass 2).  No slot is
+    // recycled inside a unit, so no load waits for a store, and the loads leave in four groups instead of one burst
+    // (every pair reaches its epilogue at the same time).
     if (lane == 0) {
       tma_prefetch_desc(&tmRes32);
       constexpr int HALF = kD / 2;
@@ -287,15 +297,21 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       for (int unit = unit0; unit < num_units; unit += ustride, ++ui) {
         int b, t0;
         decode(unit, b, t0);
-        auto push = [&](int idx, uint8_t* box) {   // idx = 2 * chunk + column half
+        auto push = [&](int idx) {   // idx = 2 * chunk + column half
           const uint32_t full = bar(B_RF + idx);
           mbar_arrive_expect_tx(full, kBoxBytes16K);
-          tma_load_3d(smem_u32(box), &tmRes32, full, (idx & 1) * HALF + (idx >> 1) * 32, t0, b);
+          tma_load_3d(smem_u32(res_box(idx)), &tmRes32, full, (idx & 1) * HALF + (idx >> 1) * 32, t0, b);
         };
+        mbar_wait(bar(B_XE), ui & 1);
+        for (int idx = 0; idx < 3; ++idx) push(idx);
         mbar_wait(bar(B_A2F), ui & 1);
-        for (int idx = 0; idx < kRing; ++idx) push(idx, sRing + idx * kBoxBytes16K);
-        mbar_wait(bar(B_XR), ui & 1);
-        for (int idx = kRing; idx < kResBoxes; ++idx) push(idx, sX + (idx - kRing) * kBoxBytes16K);
+        for (int idx = 3; idx < kRing; ++idx) push(idx);
+        for (int k = 0; k < 3; ++k) {
+          mbar_wait(bar(B_XR + k), ui & 1);
+          push(kRing + 2 * k);
+          mbar_wait(bar(B_XR + 3 + k), ui & 1);
+          push(kRing + 2 * k + 1);
+        }
       }
     }
   } else if (warp >= kEpiWarp0) {
@@ -325,9 +341,6 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     const float inv_n = 1.f / static_cast<float>(BLOCK_N);
     uint32_t xc = 0, ui = 0;
     long long t_ring = 0;
-    auto res_box = [&](int idx) -> uint8_t* {
-      return idx < kRing ? sRing + idx * kBoxBytes16K : sX + (idx - kRing) * kBoxBytes16K;
-    };
     auto exchange = [&](float& a, float& c) {
       float2* buf = sStat + (xc & 1) * 2 * kBlockM;
       buf[wg * kBlockM + row] = make_float2(a, c);
@@ -407,8 +420,8 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
           sq = fmaf(v[i], v[i], sq);
         }
         tmem_st32(trow + cc, v);
+        if (ch & 1) mbar_arrive(bar(B_XR + ((c0h + cc) >> 6)));   // this k-block of the x tile may receive a residual box
       }
-      mbar_arrive(bar(B_XR));   // the x tile may be overwritten by the next unit's
       tmem_st_wait();
       const long long te1 = (p.debug & 1) ? clock64() : 0;
       exchange(sum, sq);
@@ -467,10 +480,13 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
           if (lane == 0) mbar_arrive_leader_rlx(bar(B_A2E));
         }
         layernorm32(v, c0h + cc, mean, rstd, sG2, sB2);
-        // staging: the drained ring slots of this warpgroup hold six 8 KB boxes, one per chunk: no box is reused
-        uint8_t* sbox = sRing + (((ch >> 1) * 2 + wg) * kBoxBytes16K) + (ch & 1) * 8192;
+        // staging: three 8 KB boxes per warpgroup in the W2 stages' memory (the W1 stages already receive the next unit's
+        // weights), box ch % 3.  Its previous store (chunk ch - 3) has been read: the issuing thread waited for all but
+        // the latest store before the warpgroup barrier of chunk ch - 1.
+        uint8_t* sbox = sW2 + (wg * 3 + ch % 3) * 8192;
         box_row_st_bf16x32_sw64(sbox, row, v);
         fence_async_smem();
+        if (row == 0) tma_store_wait_read1();
         wg_bar(wg);
         if (row == 0) {
           tma_store_3d(&tmOut, smem_u32(sbox), c0h + cc, t0, b);
@@ -478,7 +494,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         }
       }
       (void)valid;
-      if (row == 0) tma_store_wait_read0();   // the boxes alias the weight stages: the stores have read them
+      if (row == 0) tma_store_wait_read0();   // the boxes alias the W2 stages: the stores have read them
       if ((p.debug & 1) && et == 0 && is_leader) {
         long long* o = g_ffn_trace + (blockIdx.x >> 1) * 16;
         const long long te3 = clock64();
