@@ -377,6 +377,67 @@ int ttsb200_radam_step(float* p, const float* g, float* m, float* v, const float
                        float gscale, float clip, float lr, float beta1, float beta2, float eps, int32_t step,
                        ttsb200_stream_t stream);
 
+/* ================================================================================================
+ * AUTOREGRESSIVE DECODE STEP of Transformer-TTS (BASELINE.json configs[4]).
+ * The reference decodes by re-running the whole prefix through the model at every step (test.py:128-191); these entry
+ * points process ONE new decoder position per utterance against cached keys / values (Models/decoder.py:43-56,
+ * Models/layers.py:109-124, Models/modules.py:7-21,43-68).  R = rows = utterances in the batch.  Position-dependent
+ * addresses read the device scalar *pos, so a captured CUDA graph of one step replays for every step.
+ * ============================================================================================== */
+
+/* y[r,n] = act( sum_k xin[r,k] * w[n,k] + bias[n] ) (+ res[r,n]) (+ add_scale[0] * add_row[pos*N + n])
+ *   xin = x_bf16 rows, or x_f32 rows, optionally LayerNorm(x_f32 row; ln_g, ln_b, eps) (nn.LayerNorm, Models/layers.py:110,
+ *   114,118; Models/decoder.py:56), rounded to bf16 (the operand precision of every GEMM of this library);
+ *   input row r starts at x + r*ldx + (pos + x_pos_bias)*x_pos_stride (x_pos_stride != 0; a negative step index reads
+ *   zeros: the all-zero first decoder input of test.py:139);
+ *   w: bf16 [N][ldw], rows zero-padded to a multiple of 32 columns (ldw >= roundup(K,32), 16-byte aligned rows);
+ *   act = ReLU if relu (Models/prenets.py:32-37, Models/modules.py:83); add_row = positional-encoding table (>= pos+1, N)
+ *   with add_scale = alpha (Models/modules.py:107-111);
+ *   out_f32[r*ldo + pos*out_pos_stride + n] and / or out_bf16[r*ldob + n];
+ *   xn_bf16 (optional, (R,K) dense) receives the bf16 input rows after the LayerNorm (the FeedForward's inner residual,
+ *   Models/modules.py:81,85). */
+typedef struct {
+  const float* x_f32;
+  const void* x_bf16;
+  int64_t ldx;
+  const float* ln_g;
+  const float* ln_b;
+  float eps;
+  const void* w_bf16;
+  int64_t ldw;
+  const float* bias;
+  int32_t relu;
+  const float* res_f32;
+  int64_t ldres;
+  const float* add_row;
+  const float* add_scale;
+  float* out_f32;
+  int64_t ldo;
+  void* out_bf16;
+  int64_t ldob;
+  void* xn_bf16;
+  const int32_t* pos;
+  int64_t x_pos_stride;
+  int32_t x_pos_bias;
+  int64_t out_pos_stride;
+  int32_t R, K, N;
+} ttsb200_small_linear_args;
+int ttsb200_small_linear(const ttsb200_small_linear_args* args, ttsb200_stream_t stream);
+
+/* One query row per (utterance, head) against cached keys / values (Models/modules.py:7-21 for the newest position):
+ *   ctx[r, h*Dh + d] = sum_j softmax_j(q[r,h,:] . K[r,h,j,:] / sqrt(Dh)) V[r,h,j,d]
+ * q bf16, head h at columns [h*Dh, (h+1)*Dh) of row r (row stride ldq); caches bf16 [R][H][cap][Dh].
+ * Self-attention (attn_1, Models/layers.py:111): pos given; knew / vnew (row stride ldkv, head h at column h*Dh) are
+ * written to cache slot *pos first, then keys 0..*pos attend (the causal mask of train.py:38-58 at the last row).
+ * Cross-attention (attn_2, Models/layers.py:115): kv_len given; keys 0..kv_len[r]-1 attend (the reference fills padded
+ * keys with -1e4, whose probabilities are exactly 0 in fp32 next to any valid key).  Dh must be 96. */
+int ttsb200_attn_decode(const void* q_bf16, int64_t ldq, const void* knew_bf16, const void* vnew_bf16, int64_t ldkv,
+                        void* k_cache, void* v_cache, const int32_t* pos, const int32_t* kv_len, void* ctx_bf16,
+                        int64_t ldc, int32_t R, int32_t H, int32_t Dh, int32_t cap, ttsb200_stream_t stream);
+
+/* *pos += delta (the last node of a captured decode step). */
+int ttsb200_advance_pos(int32_t* pos, int32_t delta, ttsb200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,309 @@
+// Autoregressive decode step of Transformer-TTS (BASELINE.json configs[4]): the per-position work of
+// Models/decoder.py:43-56 / Models/layers.py:109-124 for ONE new decoder position of every utterance, with the keys and
+// values of the earlier positions kept in a cache instead of being recomputed (the reference's test.py:128-191 re-runs
+// the whole prefix through the model at every step).
+//
+// A step has R = batch rows (16 at cfg5), so every contraction is [R x K] . [K x N] with R <= 16: one
+// mma.sync.m16n8k16 tile in M.  The work is streaming the layer weights (28 MB bf16 for six layers, L2-resident) and
+// the cached keys / values; there is no tile big enough for tcgen05 (M = 128 minimum), so these are warp-level kernels:
+//
+//   small_linear : y = act(LN?(x) W^T + b) (+ residual) (+ alpha * pe[pos]); each warp owns 8 output columns, the R
+//                  input rows (LayerNorm applied while staging) sit in shared memory as the A operand, W rows stream
+//                  from L2 with 16-byte loads straight into B fragments (the contraction index is permuted so that a
+//                  16-byte load of one W row is two k-steps' worth of fragments);
+//   attn_decode  : one query per (utterance, head) against the cached keys/values (appending this step's first):
+//                  thread-per-key dot products with 16-byte loads, block softmax, 12-thread-per-key P.V.
+//
+// Position-dependent addressing (which cache slot, which positional-encoding row, where the step's output goes) reads a
+// device scalar, so one captured CUDA graph replays for every step.
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "../../include/ttsb200.h"
+
+namespace ttsb {
+namespace dec {
+
+constexpr int kSlWarps = 2;          // warps per CTA: 16 output columns
+constexpr int kSlRows = 16;          // rows per CTA = M of the MMA tile
+constexpr int kSlPadBytes = 16;      // row padding in shared memory: rows g, g+1, .. land in different 16-byte bank groups
+
+__device__ __forceinline__ void mma_bf16_16816(float* c, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                               uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__global__ void __launch_bounds__(kSlWarps * 32)
+small_linear_kernel(const ttsb200_small_linear_args p) {
+  extern __shared__ __align__(16) uint8_t sl_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int Kp = (p.K + 31) & ~31;
+  const int row_bytes = Kp * 2 + kSlPadBytes;
+  const int pos = p.pos ? __ldg(p.pos) : 0;
+  const int r0 = blockIdx.y * kSlRows;
+  const int xpos = pos + p.x_pos_bias;   // index of the step the input rows were produced at (negative: zeros)
+
+  // ---- stage the input rows as bf16 (LayerNorm applied on the way) ----
+  for (int rr = warp; rr < kSlRows; rr += kSlWarps) {
+    const int row = r0 + rr;
+    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(sl_smem + rr * row_bytes);
+    const bool valid = row < p.R && (p.x_pos_stride == 0 || xpos >= 0);
+    if (!valid) {
+      for (int k = lane; k < Kp; k += 32) dst[k] = __float2bfloat16(0.f);
+      continue;
+    }
+    const int64_t off = static_cast<int64_t>(row) * p.ldx + (p.x_pos_stride ? static_cast<int64_t>(xpos) * p.x_pos_stride : 0);
+    if (p.x_bf16) {
+      const __nv_bfloat16* src = static_cast<const __nv_bfloat16*>(p.x_bf16) + off;
+      for (int k = lane; k < Kp; k += 32) dst[k] = k < p.K ? src[k] : __float2bfloat16(0.f);
+      continue;
+    }
+    const float* src = p.x_f32 + off;
+    float mean = 0.f, rstd = 1.f;
+    if (p.ln_g) {   // two-pass statistics, as torch.nn.functional.layer_norm
+      float s = 0.f;
+      for (int k = lane; k < p.K; k += 32) s += src[k];
+      mean = warp_sum(s) / static_cast<float>(p.K);
+      float q = 0.f;
+      for (int k = lane; k < p.K; k += 32) {
+        const float d = src[k] - mean;
+        q = fmaf(d, d, q);
+      }
+      rstd = rsqrtf(warp_sum(q) / static_cast<float>(p.K) + p.eps);
+    }
+    __nv_bfloat16* xn = (p.xn_bf16 && blockIdx.x == 0) ? static_cast<__nv_bfloat16*>(p.xn_bf16) + static_cast<int64_t>(row) * p.K
+                                                       : nullptr;
+    for (int k = lane; k < Kp; k += 32) {
+      float v = 0.f;
+      if (k < p.K) {
+        v = src[k];
+        if (p.ln_g) v = fmaf((v - mean) * rstd, __ldg(p.ln_g + k), __ldg(p.ln_b + k));
+      }
+      const __nv_bfloat16 h = __float2bfloat16(v);
+      dst[k] = h;
+      if (xn && k < p.K) xn[k] = h;
+    }
+  }
+  __syncthreads();
+
+  // ---- 16 x 8 outputs per warp; contraction index permuted: lane (g, tq) takes physical k = 32 kb + 8 tq + [0, 8) of W
+  // row n0 + g as the B fragments of two k-steps, and the same physical k of x rows g, g + 8 as the A fragments ----
+  const int n0 = (blockIdx.x * kSlWarps + warp) * 8;
+  if (n0 >= p.N) return;
+  const int g = lane >> 2, tq = lane & 3;
+  const int wrow = min(n0 + g, p.N - 1);
+  const uint4* wp = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.w_bf16) + static_cast<int64_t>(wrow) * p.ldw) + tq;
+  const uint8_t* xa = sl_smem + g * row_bytes + tq * 16;
+  const uint8_t* xb = xa + 8 * row_bytes;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  const int nkb = Kp >> 5;
+  constexpr int U = 12;   // W loads in flight per lane (K = 384: the whole row)
+  for (int kc = 0; kc < nkb; kc += U) {
+    uint4 w[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (kc + u < nkb) w[u] = __ldg(wp + (kc + u) * 4);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (kc + u >= nkb) break;
+      const uint4 a = *reinterpret_cast<const uint4*>(xa + (kc + u) * 64);
+      const uint4 b = *reinterpret_cast<const uint4*>(xb + (kc + u) * 64);
+      mma_bf16_16816(acc, a.x, b.x, a.y, b.y, w[u].x, w[u].y);
+      mma_bf16_16816(acc, a.z, b.z, a.w, b.w, w[u].z, w[u].w);
+    }
+  }
+
+  // ---- epilogue: c0,c1 = (row g, cols 2 tq, 2 tq + 1); c2,c3 = (row g + 8, same cols) ----
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    const int row = r0 + g + half * 8;
+    if (row >= p.R) continue;
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int n = n0 + tq * 2 + e;
+      if (n >= p.N) continue;
+      float v = acc[half * 2 + e];
+      if (p.bias) v += __ldg(p.bias + n);
+      if (p.relu) v = fmaxf(v, 0.f);
+      if (p.res_f32) v += p.res_f32[static_cast<int64_t>(row) * p.ldres + n];
+      if (p.add_row) v = fmaf(__ldg(p.add_scale), __ldg(p.add_row + static_cast<int64_t>(pos) * p.N + n), v);
+      const int64_t opos = p.out_pos_stride ? static_cast<int64_t>(pos) * p.out_pos_stride : 0;
+      if (p.out_f32) p.out_f32[static_cast<int64_t>(row) * p.ldo + opos + n] = v;
+      if (p.out_bf16) static_cast<__nv_bfloat16*>(p.out_bf16)[static_cast<int64_t>(row) * p.ldob + n] = __float2bfloat16(v);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// attn_decode: grid (H, R), 256 threads.  Models/modules.py:7-21 for one query row.
+// ------------------------------------------------------------------------------------------------
+constexpr int kAdThreads = 256;
+
+template <int DH>
+__global__ void __launch_bounds__(kAdThreads)
+attn_decode_kernel(const __nv_bfloat16* __restrict__ q, int64_t ldq, const __nv_bfloat16* __restrict__ knew,
+                   const __nv_bfloat16* __restrict__ vnew, int64_t ldkv, __nv_bfloat16* __restrict__ kc,
+                   __nv_bfloat16* __restrict__ vc, const int32_t* __restrict__ pos_ptr,
+                   const int32_t* __restrict__ kv_len, __nv_bfloat16* __restrict__ ctx, int64_t ldc, int H, int cap) {
+  static_assert(DH % 8 == 0 && DH <= 128, "head dimension");
+  constexpr int VEC = DH / 8;                  // 16-byte vectors per key row
+  constexpr int GROUPS = kAdThreads / VEC;     // key groups of the P.V phase
+  extern __shared__ __align__(16) uint8_t ad_smem[];
+  float* s_p = reinterpret_cast<float*>(ad_smem);       // [cap] scores, then probabilities
+  __shared__ float s_q[DH];
+  __shared__ float s_red[kAdThreads / 32];
+  __shared__ float s_part[GROUPS][DH];
+  const int h = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
+  const int pos = pos_ptr ? __ldg(pos_ptr) : 0;
+  const int n = kv_len ? min(__ldg(kv_len + b), cap) : min(pos + 1, cap);
+  __nv_bfloat16* kb = kc + (static_cast<int64_t>(b) * H + h) * cap * DH;
+  __nv_bfloat16* vb = vc + (static_cast<int64_t>(b) * H + h) * cap * DH;
+  if (knew && pos < cap && tid < DH) {          // this step's key / value join the cache first
+    kb[static_cast<int64_t>(pos) * DH + tid] = knew[static_cast<int64_t>(b) * ldkv + h * DH + tid];
+    vb[static_cast<int64_t>(pos) * DH + tid] = vnew[static_cast<int64_t>(b) * ldkv + h * DH + tid];
+  }
+  if (tid < DH) s_q[tid] = __bfloat162float(q[static_cast<int64_t>(b) * ldq + h * DH + tid]) * rsqrtf(static_cast<float>(DH));
+  __syncthreads();
+
+  // scores: one key per thread
+  float mx = -INFINITY;
+  for (int j = tid; j < n; j += kAdThreads) {
+    const uint4* kr = reinterpret_cast<const uint4*>(kb + static_cast<int64_t>(j) * DH);
+    uint4 kv[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) kv[i] = kr[i];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) {
+      const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&kv[i]);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 f = __bfloat1622float2(h2[e]);
+        s = fmaf(f.x, s_q[i * 8 + e * 2], s);
+        s = fmaf(f.y, s_q[i * 8 + e * 2 + 1], s);
+      }
+    }
+    s_p[j] = s;
+    mx = fmaxf(mx, s);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if ((tid & 31) == 0) s_red[tid >> 5] = mx;
+  __syncthreads();
+  mx = s_red[0];
+#pragma unroll
+  for (int i = 1; i < kAdThreads / 32; ++i) mx = fmaxf(mx, s_red[i]);
+  __syncthreads();
+  float sum = 0.f;
+  for (int j = tid; j < n; j += kAdThreads) {
+    const float e = expf(s_p[j] - mx);
+    s_p[j] = e;
+    sum += e;
+  }
+  sum = warp_sum(sum);
+  if ((tid & 31) == 0) s_red[tid >> 5] = sum;
+  __syncthreads();
+  sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < kAdThreads / 32; ++i) sum += s_red[i];
+
+  // P.V: VEC threads per key (16 bytes of the value row each), GROUPS keys in flight
+  const int grp = tid / VEC, vi = tid - grp * VEC;
+  float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (grp < GROUPS) {
+    for (int j = grp; j < n; j += GROUPS) {
+      const uint4 vv = *reinterpret_cast<const uint4*>(vb + static_cast<int64_t>(j) * DH + vi * 8);
+      const float pj = s_p[j];
+      const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&vv);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 f = __bfloat1622float2(h2[e]);
+        o[e * 2] = fmaf(pj, f.x, o[e * 2]);
+        o[e * 2 + 1] = fmaf(pj, f.y, o[e * 2 + 1]);
+      }
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) s_part[grp][vi * 8 + e] = o[e];
+  }
+  __syncthreads();
+  if (tid < DH) {
+    float a = 0.f;
+#pragma unroll 1
+    for (int gI = 0; gI < GROUPS; ++gI) a += s_part[gI][tid];
+    ctx[static_cast<int64_t>(b) * ldc + h * DH + tid] = __float2bfloat16(a / sum);
+  }
+}
+
+__global__ void advance_pos_kernel(int32_t* pos, int32_t delta) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) *pos += delta;
+}
+
+}  // namespace dec
+}  // namespace ttsb
+
+using namespace ttsb;
+
+extern "C" int ttsb200_small_linear(const ttsb200_small_linear_args* a, ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(a != nullptr, "small_linear: null args");
+  const ttsb200_small_linear_args p = *a;
+  TTSB_CHECK_ARG((p.x_f32 != nullptr) != (p.x_bf16 != nullptr), "small_linear: exactly one of x_f32 / x_bf16");
+  TTSB_CHECK_ARG(p.w_bf16 && p.R > 0 && p.K > 0 && p.N > 0, "small_linear: bad args");
+  TTSB_CHECK_ARG(p.out_f32 || p.out_bf16, "small_linear: no output");
+  const int Kp = (p.K + 31) & ~31;
+  TTSB_CHECK_ARG(p.ldw >= Kp && p.ldw % 8 == 0 && (reinterpret_cast<uintptr_t>(p.w_bf16) & 15) == 0,
+                 "small_linear: weight rows must be 16-byte aligned and zero-padded to a multiple of 32 columns (ldw %lld, K %d)",
+                 static_cast<long long>(p.ldw), p.K);
+  TTSB_CHECK_ARG((p.ln_g == nullptr) == (p.ln_b == nullptr) && (!p.ln_g || p.x_f32), "small_linear: LayerNorm needs ln_g, ln_b and x_f32");
+  TTSB_CHECK_ARG(!p.xn_bf16 || p.x_f32, "small_linear: xn_bf16 needs x_f32");
+  TTSB_CHECK_ARG((p.add_row == nullptr) == (p.add_scale == nullptr), "small_linear: add_row and add_scale go together");
+  TTSB_CHECK_ARG((!p.x_pos_stride && !p.out_pos_stride && !p.add_row) || p.pos, "small_linear: position-dependent addressing needs pos");
+  TTSB_CHECK_ARG(!p.out_f32 || p.ldo >= p.N, "small_linear: ldo < N");
+  TTSB_CHECK_ARG(!p.out_bf16 || p.ldob >= p.N, "small_linear: ldob < N");
+  const int smem = dec::kSlRows * (Kp * 2 + dec::kSlPadBytes);
+  TTSB_CHECK_ARG(smem <= 100 * 1024, "small_linear: K = %d is too large", p.K);
+  auto kern = dec::small_linear_kernel;
+  TTSB_SMEM_OPT_IN(kern, 100 * 1024);
+  dim3 grid((p.N + dec::kSlWarps * 8 - 1) / (dec::kSlWarps * 8), (p.R + dec::kSlRows - 1) / dec::kSlRows);
+  kern<<<grid, dec::kSlWarps * 32, smem, static_cast<cudaStream_t>(s)>>>(p);
+  TTSB_CHECK_CUDA(cudaGetLastError());
+  return TTSB_OK;
+}
+
+extern "C" int ttsb200_attn_decode(const void* q_bf16, int64_t ldq, const void* knew_bf16, const void* vnew_bf16,
+                                   int64_t ldkv, void* k_cache, void* v_cache, const int32_t* pos,
+                                   const int32_t* kv_len, void* ctx_bf16, int64_t ldc, int32_t R, int32_t H, int32_t Dh,
+                                   int32_t cap, ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(q_bf16 && k_cache && v_cache && ctx_bf16 && R > 0 && H > 0 && cap > 0, "attn_decode: bad args");
+  TTSB_CHECK_ARG(Dh == 96, "attn_decode: head dimension %d unsupported (96)", Dh);
+  TTSB_CHECK_ARG((knew_bf16 == nullptr) == (vnew_bf16 == nullptr), "attn_decode: knew and vnew go together");
+  TTSB_CHECK_ARG((pos != nullptr) != (kv_len != nullptr), "attn_decode: exactly one of pos (self-attention) / kv_len (cross-attention)");
+  TTSB_CHECK_ARG(!knew_bf16 || pos, "attn_decode: appending needs pos");
+  TTSB_CHECK_ARG(cap <= 16384, "attn_decode: cache capacity %d above 16384 keys", cap);
+  TTSB_CHECK_ARG((reinterpret_cast<uintptr_t>(k_cache) & 15) == 0 && (reinterpret_cast<uintptr_t>(v_cache) & 15) == 0,
+                 "attn_decode: caches must be 16-byte aligned");
+  auto kern = dec::attn_decode_kernel<96>;
+  const int smem = cap * 4;
+  TTSB_SMEM_OPT_IN(kern, 16384 * 4);
+  kern<<<dim3(H, R), dec::kAdThreads, smem, static_cast<cudaStream_t>(s)>>>(
+      static_cast<const __nv_bfloat16*>(q_bf16), ldq, static_cast<const __nv_bfloat16*>(knew_bf16),
+      static_cast<const __nv_bfloat16*>(vnew_bf16), ldkv, static_cast<__nv_bfloat16*>(k_cache),
+      static_cast<__nv_bfloat16*>(v_cache), pos, kv_len, static_cast<__nv_bfloat16*>(ctx_bf16), ldc, H, cap);
+  TTSB_CHECK_CUDA(cudaGetLastError());
+  return TTSB_OK;
+}
+
+extern "C" int ttsb200_advance_pos(int32_t* pos, int32_t delta, ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(pos != nullptr, "advance_pos: null pointer");
+  dec::advance_pos_kernel<<<1, 32, 0, static_cast<cudaStream_t>(s)>>>(pos, delta);
+  TTSB_CHECK_CUDA(cudaGetLastError());
+  return TTSB_OK;
+}

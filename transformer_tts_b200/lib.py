@@ -41,6 +41,21 @@ class GemmArgs(C.Structure):
     ]
 
 
+class SmallLinearArgs(C.Structure):
+    """ttsb200_small_linear_args of include/ttsb200.h (field order and types must match)."""
+    _fields_ = [
+        ("x_f32", C.c_void_p), ("x_bf16", C.c_void_p), ("ldx", C.c_int64),
+        ("ln_g", C.c_void_p), ("ln_b", C.c_void_p), ("eps", C.c_float),
+        ("w_bf16", C.c_void_p), ("ldw", C.c_int64), ("bias", C.c_void_p), ("relu", C.c_int32),
+        ("res_f32", C.c_void_p), ("ldres", C.c_int64),
+        ("add_row", C.c_void_p), ("add_scale", C.c_void_p),
+        ("out_f32", C.c_void_p), ("ldo", C.c_int64), ("out_bf16", C.c_void_p), ("ldob", C.c_int64),
+        ("xn_bf16", C.c_void_p), ("pos", C.c_void_p),
+        ("x_pos_stride", C.c_int64), ("x_pos_bias", C.c_int32), ("out_pos_stride", C.c_int64),
+        ("R", C.c_int32), ("K", C.c_int32), ("N", C.c_int32),
+    ]
+
+
 _LIB: Optional[C.CDLL] = None
 
 _SIGNATURES = {
@@ -48,6 +63,11 @@ _SIGNATURES = {
     "ttsb200_last_error_string": ([], C.c_char_p),
     "ttsb200_debug_tmap_cache": ([C.c_void_p, C.c_void_p], None),
     "ttsb200_conv_gemm": ([C.POINTER(GemmArgs), C.c_void_p], C.c_int),
+    "ttsb200_small_linear": ([C.POINTER(SmallLinearArgs), C.c_void_p], C.c_int),
+    "ttsb200_attn_decode": ([C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
+                             C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p],
+                            C.c_int),
+    "ttsb200_advance_pos": ([C.c_void_p, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_ffn_fused": ([C.c_void_p] * 10 + [C.c_float, C.c_void_p, C.c_void_p] + [C.c_int32] * 4 + [C.c_void_p] * 3, C.c_int),
     "ttsb200_build_tile_map": ([C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
                                 C.c_void_p], C.c_int),
@@ -657,3 +677,82 @@ def dropout_mask(n: int, p: float, seed: int, site: int, device="cuda") -> torch
     _check(load().ttsb200_dropout_mask(_ptr(out), n, float(p), int(seed), int(site), _stream()), "dropout_mask")
     _count()
     return out
+
+
+# ------------------------------------------------------------------------------------------------
+# autoregressive decode step (Transformer-TTS)
+# ------------------------------------------------------------------------------------------------
+def pad_weight_rows(w: torch.Tensor) -> torch.Tensor:
+    """bf16 [N][roundup(K,32)] copy of a Linear weight (N,K), rows zero-padded: the layout small_linear streams."""
+    N, K = w.shape
+    Kp = (K + 31) // 32 * 32
+    out = torch.zeros((N, Kp), device=w.device, dtype=torch.bfloat16)
+    out[:, :K] = w.to(torch.bfloat16)
+    return out
+
+
+def small_linear(w: torch.Tensor, bias: Optional[torch.Tensor], K: int, *, x_f32: Optional[torch.Tensor] = None,
+                 x_bf16: Optional[torch.Tensor] = None, ldx: Optional[int] = None, R: Optional[int] = None, ln=None,
+                 eps: float = 1e-5, relu: bool = False, res_f32: Optional[torch.Tensor] = None,
+                 add_row: Optional[torch.Tensor] = None, add_scale: Optional[torch.Tensor] = None,
+                 out_f32: Optional[torch.Tensor] = None, ldo: Optional[int] = None,
+                 out_bf16: Optional[torch.Tensor] = None, xn_bf16: Optional[torch.Tensor] = None,
+                 pos: Optional[torch.Tensor] = None, x_pos_stride: int = 0, x_pos_bias: int = 0,
+                 out_pos_stride: int = 0) -> None:
+    """y = act(LN?(x) W^T + b) (+ res) (+ add_scale * add_row[pos]) for a few rows; see ttsb200_small_linear."""
+    x = x_f32 if x_f32 is not None else x_bf16
+    N = w.shape[0]
+    a = SmallLinearArgs()
+    a.x_f32 = _ptr(x_f32, torch.float32, "x_f32")
+    a.x_bf16 = _ptr(x_bf16, torch.bfloat16, "x_bf16")
+    a.ldx = int(ldx if ldx is not None else x.shape[-1])
+    a.R = int(R if R is not None else x.shape[0])
+    a.ln_g = _ptr(ln[0], torch.float32, "ln_g") if ln is not None else None
+    a.ln_b = _ptr(ln[1], torch.float32, "ln_b") if ln is not None else None
+    a.eps = eps
+    a.w_bf16 = _ptr(w, torch.bfloat16, "w")
+    a.ldw = int(w.shape[1])
+    a.bias = _ptr(bias, torch.float32, "bias")
+    a.relu = int(relu)
+    a.res_f32 = _ptr(res_f32, torch.float32, "res_f32")
+    a.ldres = int(res_f32.shape[-1]) if res_f32 is not None else 0
+    a.add_row = _ptr(add_row, torch.float32, "add_row")
+    a.add_scale = _ptr(add_scale, torch.float32, "add_scale")
+    a.out_f32 = _ptr(out_f32, torch.float32, "out_f32")
+    a.ldo = int(ldo if ldo is not None else (out_f32.shape[-1] if out_f32 is not None else 0))
+    a.out_bf16 = _ptr(out_bf16, torch.bfloat16, "out_bf16")
+    a.ldob = int(out_bf16.shape[-1]) if out_bf16 is not None else 0
+    a.xn_bf16 = _ptr(xn_bf16, torch.bfloat16, "xn_bf16")
+    a.pos = _ptr(pos, torch.int32, "pos")
+    a.x_pos_stride = int(x_pos_stride)
+    a.x_pos_bias = int(x_pos_bias)
+    a.out_pos_stride = int(out_pos_stride)
+    a.K = int(K)
+    a.N = int(N)
+    _check(load().ttsb200_small_linear(C.byref(a), _stream()), "small_linear")
+    _count()
+
+
+def attn_decode(q: torch.Tensor, q_off: int, ldq: int, k_cache: torch.Tensor, v_cache: torch.Tensor, ctx: torch.Tensor, *,
+                kv_new: Optional[torch.Tensor] = None, k_off: int = 0, v_off: int = 0, pos: Optional[torch.Tensor] = None,
+                kv_len: Optional[torch.Tensor] = None) -> None:
+    """One query row per (utterance, head) against the caches [R][H][cap][Dh]; q / kv_new are column ranges (element
+    offsets q_off / k_off / v_off) of a (R, ldq) bf16 buffer such as the q|k|v projection of the step."""
+    R, H, cap, Dh = k_cache.shape
+    es = 2
+    qp = _ptr(q, torch.bfloat16, "q") + q_off * es
+    kp = vp = None
+    if kv_new is not None:
+        base = _ptr(kv_new, torch.bfloat16, "kv_new")
+        kp, vp = base + k_off * es, base + v_off * es
+    _check(load().ttsb200_attn_decode(qp, ldq, kp, vp, int(kv_new.shape[-1]) if kv_new is not None else 0,
+                                      _ptr(k_cache, torch.bfloat16, "k_cache"), _ptr(v_cache, torch.bfloat16, "v_cache"),
+                                      _ptr(pos, torch.int32, "pos"), _ptr(kv_len, torch.int32, "kv_len"),
+                                      _ptr(ctx, torch.bfloat16, "ctx"), int(ctx.shape[-1]), R, H, Dh, cap, _stream()),
+           "attn_decode")
+    _count()
+
+
+def advance_pos(pos: torch.Tensor, delta: int = 1) -> None:
+    _check(load().ttsb200_advance_pos(_ptr(pos, torch.int32, "pos"), delta, _stream()), "advance_pos")
+    _count()

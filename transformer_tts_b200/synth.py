@@ -41,6 +41,95 @@ def make_hp(**overrides) -> SimpleNamespace:
     return SimpleNamespace(**d)
 
 
+def _attn_spec(spec, pfx: str, d: int) -> None:
+    for nm in ("q_linear", "v_linear", "k_linear", "out"):
+        spec[pfx + nm + ".weight"] = ((d, d), "linear_w")
+        spec[pfx + nm + ".bias"] = ((d,), ("linear_b", d))
+
+
+def _ff_spec(spec, pfx: str, d: int, k: int) -> None:
+    spec[pfx + "f_1.weight"] = ((4 * d, d, k), "conv_w")
+    spec[pfx + "f_1.bias"] = ((4 * d,), "conv_b")
+    spec[pfx + "f_2.weight"] = ((d, 4 * d, k), "conv_w")
+    spec[pfx + "f_2.bias"] = ((d,), "conv_b")
+    spec[pfx + "layer_norm.weight"] = ((d,), "norm_w")
+    spec[pfx + "layer_norm.bias"] = ((d,), "norm_b")
+
+
+def _postnet_spec(spec, dd: int, md: int, with_out: bool) -> None:
+    spec["postnet.conv1.weight"] = ((dd, md, 5), "conv_w")
+    spec["postnet.conv1.bias"] = ((dd,), "conv_b")
+    for i in range(3):
+        spec[f"postnet.conv_list.{i}.weight"] = ((dd, dd, 5), "conv_w")
+        spec[f"postnet.conv_list.{i}.bias"] = ((dd,), "conv_b")
+    spec["postnet.conv2.weight"] = ((md, dd, 5), "conv_w")
+    spec["postnet.conv2.bias"] = ((md,), "conv_b")
+    if with_out:
+        spec["postnet.out.weight"] = ((md, dd), "linear_w")
+        spec["postnet.out.bias"] = ((md,), ("linear_b", dd))
+    for bn in ("batch_norm_list.0", "batch_norm_list.1", "batch_norm_list.2", "pre_batchnorm"):
+        spec[f"postnet.{bn}.weight"] = ((dd,), "norm_w")
+        spec[f"postnet.{bn}.bias"] = ((dd,), "norm_b")
+        spec[f"postnet.{bn}.running_mean"] = ((dd,), "bn_mean")
+        spec[f"postnet.{bn}.running_var"] = ((dd,), "bn_var")
+        spec[f"postnet.{bn}.num_batches_tracked"] = ((), "bn_count")
+
+
+TTS_HP: Dict[str, object] = dict(reduction_rate=2, gst=False, dropout_prenet=0.0)
+
+
+def make_tts_hp(**overrides) -> SimpleNamespace:
+    """hparams of the Transformer-TTS configs (BASELINE.json configs[3], [4]): the canonical dimensions with the yaml's
+    reduction_rate = 2 (config/hparams_template.py) and the fields Models/transformer.py reads."""
+    d = dict(CANONICAL_HP)
+    d.update(TTS_HP)
+    d.update(overrides)
+    return SimpleNamespace(**d)
+
+
+def tts_state_dict_spec(hp) -> "OrderedDict[str, tuple]":
+    """Key -> (shape, kind) of `Models/transformer.py` Transformer (decoder_type 'transformer', no GST / speakers) in the
+    reference's state_dict order; tests/test_oracle_tts.py checks it against the reference module itself."""
+    spec: "OrderedDict[str, tuple]" = OrderedDict()
+    fs2 = state_dict_spec(hp)
+    for k, v in fs2.items():  # the text encoder is the FastSpeech2 one (Models/encoder.py)
+        if k.startswith("encoder."):
+            spec[k] = v
+    de, dd = hp.d_model_encoder, hp.d_model_decoder
+    if de != dd:
+        spec["linear.weight"] = ((dd, de), "linear_w")
+        spec["linear.bias"] = ((dd,), ("linear_b", de))
+    ph = 256  # DecoderPreNet hidden_size (Models/prenets.py:12)
+    spec["decoder.decoder_prenet.layer.fc1.weight"] = ((ph, hp.mel_dim), "linear_w")
+    spec["decoder.decoder_prenet.layer.fc1.bias"] = ((ph,), ("linear_b", hp.mel_dim))
+    spec["decoder.decoder_prenet.layer.fc2.weight"] = ((dd, ph), "linear_w")
+    spec["decoder.decoder_prenet.layer.fc2.bias"] = ((dd,), ("linear_b", ph))
+    spec["decoder.pe.alpha"] = ((1,), "alpha")
+    for i in range(hp.n_layer_decoder):
+        lp = f"decoder.layers.{i}."
+        for nm in ("norm_1", "norm_2", "norm_3"):
+            spec[lp + nm + ".weight"] = ((dd,), "norm_w")
+            spec[lp + nm + ".bias"] = ((dd,), "norm_b")
+        _attn_spec(spec, lp + "attn_1.", dd)
+        _attn_spec(spec, lp + "attn_2.", dd)
+        _ff_spec(spec, lp + "ff.", dd, hp.ff_conv_kernel_size_decoder)
+    spec["decoder.norm.weight"] = ((dd,), "norm_w")
+    spec["decoder.norm.bias"] = ((dd,), "norm_b")
+    md = hp.mel_dim * hp.reduction_rate
+    spec["out.weight"] = ((md, dd), "linear_w")
+    spec["out.bias"] = ((md,), ("linear_b", dd))
+    spec["stop_token.weight"] = ((hp.reduction_rate, dd), "linear_w")
+    spec["stop_token.bias"] = ((hp.reduction_rate,), ("linear_b", dd))
+    _postnet_spec(spec, dd, md, with_out=False)  # PostConvNet(prev_version=False) has no `out` (Models/postnets.py:40-41)
+    return spec
+
+
+def synth_tts_state_dict(hp=None, seed: int = 0) -> "OrderedDict[str, torch.Tensor]":
+    """Deterministic fp32 Transformer-TTS state_dict in the reference layout (same generators as synth_state_dict)."""
+    hp = hp or make_tts_hp()
+    return _draw(tts_state_dict_spec(hp), seed)
+
+
 def state_dict_spec(hp) -> "OrderedDict[str, tuple]":
     """Key -> (shape, kind) in the reference's state_dict order (SURVEY §8b, 289 entries canonical)."""
     spec: "OrderedDict[str, tuple]" = OrderedDict()
@@ -119,8 +208,14 @@ def synth_state_dict(hp=None, seed: int = 0, frames_per_phoneme: float = 9.6) ->
     ``frames_per_phoneme`` sets the duration predictor's output bias (log(x+1)); with the default
     the canonical model expands 128 phonemes to ~1000 frames (measured: mean 7.8 frames per phoneme; SURVEY §8d used log(11) with its own init)."""
     hp = hp or make_hp()
+    sd = _draw(state_dict_spec(hp), seed)
+    sd["variance_adaptor.duration_predictor.linear_layer.bias"].fill_(math.log(frames_per_phoneme + 1.0))
+    return sd
+
+
+def _draw(spec, seed: int) -> "OrderedDict[str, torch.Tensor]":
     sd: "OrderedDict[str, torch.Tensor]" = OrderedDict()
-    for key, (shape, kind) in state_dict_spec(hp).items():
+    for key, (shape, kind) in spec.items():
         g = _gen(key, seed)
         if isinstance(kind, tuple):  # ("linear_b", fan_in)
             bound = 1.0 / math.sqrt(kind[1])
@@ -153,7 +248,6 @@ def synth_state_dict(hp=None, seed: int = 0, frames_per_phoneme: float = 9.6) ->
         else:
             raise KeyError(kind)
         sd[key] = t.contiguous()
-    sd["variance_adaptor.duration_predictor.linear_layer.bias"].fill_(math.log(frames_per_phoneme + 1.0))
     return sd
 
 
