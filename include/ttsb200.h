@@ -426,14 +426,18 @@ int ttsb200_small_linear(const ttsb200_small_linear_args* args, ttsb200_stream_t
 
 /* One query row per (utterance, head) against cached keys / values (Models/modules.py:7-21 for the newest position):
  *   ctx[r, h*Dh + d] = sum_j softmax_j(q[r,h,:] . K[r,h,j,:] / sqrt(Dh)) V[r,h,j,d]
- * q bf16, head h at columns [h*Dh, (h+1)*Dh) of row r (row stride ldq); caches bf16 [R][H][cap][Dh].
+ * q bf16, head h at columns [h*Dh, (h+1)*Dh) of row r (row stride ldq).  Key j of (r,h) is the Dh bf16 values at
+ * k_cache + r*kv_stride_b + h*kv_stride_h + j*kv_stride_j (v_cache likewise; strides in elements): [R][H][cap][Dh] caches
+ * and the (R, L, 2*H*Dh) output of a k|v projection are both expressible.  cap = number of key slots.
  * Self-attention (attn_1, Models/layers.py:111): pos given; knew / vnew (row stride ldkv, head h at column h*Dh) are
- * written to cache slot *pos first, then keys 0..*pos attend (the causal mask of train.py:38-58 at the last row).
- * Cross-attention (attn_2, Models/layers.py:115): kv_len given; keys 0..kv_len[r]-1 attend (the reference fills padded
+ * written to slot *pos first, then keys 0..*pos attend (the causal mask of train.py:26-58 at the last row), clamped to
+ * kv_len[r] keys when kv_len is given too (the padding half of that mask, for teacher-forced prefixes).
+ * Cross-attention (attn_2, Models/layers.py:115): kv_len only; keys 0..kv_len[r]-1 attend (the reference fills padded
  * keys with -1e4, whose probabilities are exactly 0 in fp32 next to any valid key).  Dh must be 96. */
 int ttsb200_attn_decode(const void* q_bf16, int64_t ldq, const void* knew_bf16, const void* vnew_bf16, int64_t ldkv,
-                        void* k_cache, void* v_cache, const int32_t* pos, const int32_t* kv_len, void* ctx_bf16,
-                        int64_t ldc, int32_t R, int32_t H, int32_t Dh, int32_t cap, ttsb200_stream_t stream);
+                        void* k_cache, void* v_cache, int64_t kv_stride_b, int64_t kv_stride_h, int64_t kv_stride_j,
+                        const int32_t* pos, const int32_t* kv_len, void* ctx_bf16, int64_t ldc, int32_t R, int32_t H,
+                        int32_t Dh, int32_t cap, ttsb200_stream_t stream);
 
 /* *pos += delta (the last node of a captured decode step). */
 int ttsb200_advance_pos(int32_t* pos, int32_t delta, ttsb200_stream_t stream);

@@ -1,0 +1,221 @@
+"""Drop-in for ``Decoder`` of the reference's ``Models/decoder.py:29-56`` (Transformer-TTS).
+
+The reference evaluates the decoder on a whole prefix at once and, at inference, re-runs it on the growing prefix at
+every step (test.py:128-191).  Here the decoder is a STEP machine: `DecodeState.step()` processes one new position of
+every utterance against cached keys / values (csrc/decode.cu: `small_linear`, `attn_decode`), one CUDA graph replay per
+position.  `Decoder.forward` (teacher-forced prefix) feeds the given frames through the same steps; the autoregressive
+loop is `Transformer.generate` (Models/transformer.py).
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.nn as nn
+
+from .. import lib
+from . import _engine as E
+from .layers import DecoderLayer
+from .modules import PositionalEncoder
+from .prenets import DecoderPreNet
+
+
+class MultiSequential(torch.nn.Sequential):
+    """Same container class as the reference (decoder.py:10-17): keys `layers.<i>.` in the state_dict."""
+
+    def forward(self, *args):
+        for m in self:
+            args = m(*args)
+        return args
+
+
+def repeat(N, fn):
+    return MultiSequential(*[fn() for _ in range(N)])
+
+
+class DecodeState:
+    """Buffers and the captured graph of one decode session: R utterances, up to `cap` positions.
+
+    Per position (launch list, 9 per layer): prenet fc1 / fc2 (+ positional encoding); per layer LN1 + q|k|v, self-attention
+    (appends this position's key / value), out-proj + residual, LN2 + q, encoder-decoder attention, out-proj + residual,
+    LN3 + FeedForward conv1 + ReLU, conv2, FeedForward LayerNorm + residual; final LN + mel / stop heads; position += 1.
+    """
+
+    def __init__(self, dec: "Decoder", head: dict, e_bf16: torch.Tensor, src_len: torch.Tensor, cap: int,
+                 forced_in: Optional[torch.Tensor] = None, trg_len: Optional[torch.Tensor] = None,
+                 use_cuda_graph: bool = True):
+        t = dec._cache()
+        self.dec, self.t, self.head = dec, t, head
+        R, L, D = e_bf16.shape
+        H = dec.heads
+        dev = e_bf16.device
+        self.R, self.L, self.D, self.H, self.Dh, self.cap = R, L, D, H, D // H, cap
+        self.n_out = head["w"].shape[0]  # mel_dim * r + r
+        self.mel_dim = dec.decoder_prenet.input_size
+        self.src_len = src_len
+        self.trg_len = trg_len
+        self.forced_in = forced_in
+        if cap > t["pe"].shape[0]:
+            raise ValueError(f"{cap} decoder positions exceed the positional table ({t['pe'].shape[0]}, modules.py:92)")
+        f32, bf16 = torch.float32, torch.bfloat16
+        self.pos = torch.zeros(1, device=dev, dtype=torch.int32)
+        self.out_all = torch.zeros((R, cap, self.n_out), device=dev, dtype=f32)   # [mel (r frames) | stop (r)] per position
+        self.x = torch.empty((R, D), device=dev, dtype=f32)        # residual stream of the current position
+        self.x2 = torch.empty((R, D), device=dev, dtype=f32)
+        self.h1 = torch.empty((R, t["fc1_w"].shape[0]), device=dev, dtype=bf16)
+        self.qkv = torch.empty((R, 3 * D), device=dev, dtype=bf16)
+        self.q2 = torch.empty((R, D), device=dev, dtype=bf16)
+        self.ctx = torch.empty((R, D), device=dev, dtype=bf16)
+        self.xn = torch.empty((R, D), device=dev, dtype=bf16)
+        self.hid = torch.empty((R, 4 * D), device=dev, dtype=bf16)
+        self.u = torch.empty((R, D), device=dev, dtype=f32)
+        self.zn = torch.empty((R, D), device=dev, dtype=bf16)
+        # self-attention cache: [layer][k|v][R][H][cap][Dh]
+        self.kv_self = torch.zeros((dec.N, 2, R, H, cap, self.Dh), device=dev, dtype=bf16)
+        # encoder-decoder keys / values: one k|v projection of the encoder output per layer, (R, L, 2D), computed once
+        self.kv_cross = []
+        for lc in t["layers"]:
+            kv = torch.empty((R, L, 2 * D), device=dev, dtype=bf16)
+            lib.conv_gemm(e_bf16, lc["wkv2"], lc["bkv2"], block_n=128, out_bf16=kv)
+            self.kv_cross.append(kv)
+        self.graph = None
+        self.use_cuda_graph = use_cuda_graph
+
+    # -- one position -------------------------------------------------------------------------------------------------
+    def _launch_step(self) -> None:
+        t, R, D, H, Dh, cap = self.t, self.R, self.D, self.H, self.Dh, self.cap
+        pos = self.pos
+        if self.forced_in is not None:   # teacher-forced: decoder input of position p = trg[:, p]
+            T = self.forced_in.shape[1]
+            src = dict(x_f32=self.forced_in, ldx=T * self.mel_dim, x_pos_stride=self.mel_dim, x_pos_bias=0)
+        else:                            # autoregressive: frame 0 of the previous position's r frames, zeros at position 0
+            src = dict(x_f32=self.out_all, ldx=cap * self.n_out, x_pos_stride=self.n_out, x_pos_bias=-1)
+        lib.small_linear(t["fc1_w"], t["fc1_b"], self.mel_dim, R=R, relu=True, out_bf16=self.h1, pos=pos, **src)
+        lib.small_linear(t["fc2_w"], t["fc2_b"], t["fc1_w"].shape[0], x_bf16=self.h1, relu=True, add_row=t["pe"],
+                         add_scale=t["alpha"], out_f32=self.x, pos=pos)
+        x, x2 = self.x, self.x2
+        sb, sh, sj = H * cap * Dh, cap * Dh, Dh
+        for i, lc in enumerate(t["layers"]):
+            lib.small_linear(lc["wqkv1"], lc["bqkv1"], D, x_f32=x, ln=lc["ln1"], out_bf16=self.qkv)
+            lib.attn_decode(self.qkv, 0, 3 * D, self.kv_self[i], R * sb, (sb, sh, sj), cap, H, Dh, self.ctx,
+                            kv_new=self.qkv, knew_off=D, vnew_off=2 * D, pos=pos, kv_len=self.trg_len)
+            lib.small_linear(lc["wo1"], lc["bo1"], D, x_bf16=self.ctx, res_f32=x, out_f32=x2)
+            lib.small_linear(lc["wq2"], lc["bq2"], D, x_f32=x2, ln=lc["ln2"], out_bf16=self.q2)
+            lib.attn_decode(self.q2, 0, D, self.kv_cross[i], D, (self.L * 2 * D, Dh, 2 * D), self.L, H, Dh, self.ctx,
+                            kv_len=self.src_len)
+            lib.small_linear(lc["wo2"], lc["bo2"], D, x_bf16=self.ctx, res_f32=x2, out_f32=x)
+            lib.small_linear(lc["w1"], lc["b1"], D, x_f32=x, ln=lc["ln3"], relu=True, out_bf16=self.hid, xn_bf16=self.xn)
+            lib.small_linear(lc["w2"], lc["b2"], 4 * D, x_bf16=self.hid, out_f32=self.u)
+            # x2 = x + LN_ff(u + LN3(x))  (modules.py:85-87, layers.py:122); zn (the next LayerNorm) is not used here
+            lib.ffn2_tail(self.u, self.xn, x, lc["ln_ff"], t["ident"], E.LN_EPS, x2, self.zn)
+            x, x2 = x2, x
+        lib.small_linear(self.head["w"], self.head["b"], D, x_f32=x, ln=t["norm"], out_f32=self.out_all,
+                         ldo=cap * self.n_out, pos=pos, out_pos_stride=self.n_out)
+        lib.advance_pos(pos, 1)
+
+    def run(self, n_steps: int) -> None:
+        """Process the next n_steps positions (all utterances)."""
+        done = int(self.pos.item())
+        if done + n_steps > self.cap:
+            raise ValueError(f"{done} + {n_steps} positions exceed the session's capacity {self.cap}")
+        if n_steps <= 0:
+            return
+        if not self.use_cuda_graph:
+            for _ in range(n_steps):
+                self._launch_step()
+            return
+        if self.graph is None:
+            # an odd number of residual swaps would make the captured step end in the other buffer: 9 launches per layer
+            # leave x in self.x after an even number of layers, in self.x2 after an odd one — the head reads whichever
+            # it is inside the capture, and the next replay starts from the prenet again, so no state crosses steps
+            self._launch_step()          # warm-up (TMA-free kernels: only the smem opt-ins and lazy module load)
+            n_steps -= 1
+            if n_steps == 0:
+                return
+            g = torch.cuda.CUDAGraph()
+            launches = lib.LAUNCH_COUNT
+            with torch.cuda.graph(g):
+                self._launch_step()
+            self.launches_per_step = lib.LAUNCH_COUNT - launches
+            lib.LAUNCH_COUNT = launches   # capture launched nothing
+            self.graph = g
+        for _ in range(n_steps):
+            self.graph.replay()
+        lib.LAUNCH_COUNT += n_steps * self.launches_per_step
+
+
+class Decoder(nn.Module):
+    def __init__(self, vocab_size, d_model, N, heads, ff_conv_kernel_size, concat_after_decoder, dropout,
+                 dropout_prenet=0.5, multi_speaker=False, spk_emb_dim=None, output_type=None):
+        super().__init__()
+        if multi_speaker or output_type:
+            raise NotImplementedError("speaker embeddings / discrete targets are out of scope (SURVEY §2a)")
+        if ff_conv_kernel_size != 1:
+            raise NotImplementedError("a decoder FeedForward kernel wider than 1 looks at FUTURE positions (the conv is "
+                                      "centred, modules.py:76-78): it has no incremental form; hparams default is 1")
+        self.N = N
+        self.heads = heads
+        self.output_type = output_type
+        self.decoder_prenet = DecoderPreNet(vocab_size, d_model, p=dropout_prenet, output_type=output_type)
+        self.pe = PositionalEncoder(d_model, dropout=dropout)
+        self.layers = repeat(N, lambda: DecoderLayer(d_model, heads, ff_conv_kernel_size, dropout, concat_after_decoder,
+                                                     multi_speaker, spk_emb_dim))
+        self.norm = nn.LayerNorm(d_model)
+        self._ttsb_cache = E.Cache()
+
+    def _cache(self) -> dict:
+        c = self._ttsb_cache
+        params = list(self.parameters())
+        if c.stale(params):
+            t = c.t
+            dev = self.norm.weight.device
+            D = self.norm.weight.numel()
+            pn = self.decoder_prenet.layer
+            t["fc1_w"], t["fc1_b"] = lib.pad_weight_rows(pn.fc1.weight.detach()), E._f32(pn.fc1.bias)
+            t["fc2_w"], t["fc2_b"] = lib.pad_weight_rows(pn.fc2.weight.detach()), E._f32(pn.fc2.bias)
+            t["alpha"] = E._f32(self.pe.alpha)
+            t["pe"] = self.pe.table(dev)
+            t["norm"] = (E._f32(self.norm.weight), E._f32(self.norm.bias))
+            t["ident"] = (torch.ones(D, device=dev), torch.zeros(D, device=dev))
+            t["layers"] = []
+            for l in self.layers:
+                a1, a2, ff = l.attn_1, l.attn_2, l.ff
+                cat = lambda *ws: torch.cat([w.detach() for w in ws], 0)  # noqa: E731
+                lc = dict(
+                    ln1=(E._f32(l.norm_1.weight), E._f32(l.norm_1.bias)),
+                    ln2=(E._f32(l.norm_2.weight), E._f32(l.norm_2.bias)),
+                    ln3=(E._f32(l.norm_3.weight), E._f32(l.norm_3.bias)),
+                    ln_ff=(E._f32(ff.layer_norm.weight), E._f32(ff.layer_norm.bias)),
+                    wqkv1=lib.pad_weight_rows(cat(a1.q_linear.weight, a1.k_linear.weight, a1.v_linear.weight)),
+                    bqkv1=E._f32(cat(a1.q_linear.bias, a1.k_linear.bias, a1.v_linear.bias)),
+                    wo1=lib.pad_weight_rows(a1.out.weight.detach()), bo1=E._f32(a1.out.bias),
+                    wq2=lib.pad_weight_rows(a2.q_linear.weight.detach()), bq2=E._f32(a2.q_linear.bias),
+                    # k|v projection of the encoder output: a (1, 2D, D) conv_gemm operand, run once per utterance batch
+                    wkv2=E._bf16(cat(a2.k_linear.weight, a2.v_linear.weight)).unsqueeze(0).contiguous(),
+                    bkv2=E._f32(cat(a2.k_linear.bias, a2.v_linear.bias)),
+                    wo2=lib.pad_weight_rows(a2.out.weight.detach()), bo2=E._f32(a2.out.bias),
+                    w1=lib.pad_weight_rows(ff.f_1.weight.detach()[:, :, 0]), b1=E._f32(ff.f_1.bias),
+                    w2=lib.pad_weight_rows(ff.f_2.weight.detach()[:, :, 0]), b2=E._f32(ff.f_2.bias),
+                )
+                t["layers"].append(lc)
+            c.commit(params)
+        return c.t
+
+    def begin(self, head: dict, e_outputs: torch.Tensor, src_mask, cap: int, forced_in=None, trg_len=None,
+              use_cuda_graph: bool = True) -> DecodeState:
+        """Open a decode session over encoder outputs (R, L, D); head = the mel / stop projection (Transformer._head)."""
+        E.require_inference(self, "Decoder")
+        E.require_cuda(e_outputs, "Decoder")
+        R, L, _ = e_outputs.shape
+        m = E.mask_to_u8(src_mask, R, L, e_outputs.device)
+        kv = lib.mask_lengths(m)
+        if not torch.equal(kv[:, 0], kv[:, 1]):
+            raise NotImplementedError("the source mask must be a padding mask (valid prefix) — train.py:50")
+        if int(kv[:, 0].min()) < 1:
+            raise ValueError("an utterance without a single valid phoneme")
+        return DecodeState(self, head, e_outputs.to(torch.bfloat16).contiguous(), kv[:, 0].contiguous(), cap,
+                           forced_in=forced_in, trg_len=trg_len, use_cuda_graph=use_cuda_graph)
+
+    def forward(self, trg, e_outputs, src_mask, trg_mask, spk_emb=None, attn_detach=True):
+        raise NotImplementedError("Decoder.forward needs the output heads to run its step machine: call Transformer.forward "
+                                  "(teacher-forced prefix) or Transformer.generate (autoregressive)")

@@ -48,3 +48,31 @@ class EncoderLayer(nn.Module):
             lib.conv_gemm(xn, t["wqkv"], t["bqkv"], block_n=128, out_bf16=qkv)
             attn = lib.attention_probs(qkv, m, self.attn.h)
         return z, attn
+
+
+class DecoderLayer(nn.Module):
+    """Parameter holder for ``DecoderLayer`` of the reference's ``Models/layers.py:84-124`` (causal self-attention,
+    encoder-decoder attention, FeedForward, pre-LayerNorm residual blocks).  The kernels run from ``Decoder``
+    (Models/decoder.py), one decoder position at a time against cached keys / values."""
+
+    def __init__(self, d_model, heads, ff_conv_kernel_size, dropout=0.1, concat_after=False, multi_speaker=False,
+                 spk_emb_dim=None):
+        super().__init__()
+        if multi_speaker:
+            raise NotImplementedError("multi_speaker decoder blocks are out of scope (SURVEY §2a: default hparams only)")
+        if concat_after:
+            raise NotImplementedError("concat_after=True is not supported (hparams default is False)")
+        self.norm_1 = nn.LayerNorm(d_model)
+        self.norm_2 = nn.LayerNorm(d_model)
+        self.norm_3 = nn.LayerNorm(d_model)
+        self.dropout_1 = nn.Dropout(dropout)
+        self.dropout_2 = nn.Dropout(dropout)
+        self.dropout_3 = nn.Dropout(dropout)
+        self.attn_1 = MultiHeadAttention(heads, d_model, d_model, d_model, d_model, dropout=dropout, concat_after=concat_after)
+        self.attn_2 = MultiHeadAttention(heads, d_model, d_model, d_model, d_model, dropout=dropout, concat_after=concat_after)
+        self.ff = FeedForward(d_model, ff_conv_kernel_size, dropout=dropout)
+        self.multi_speaker = multi_speaker
+
+    def forward(self, x, e_outputs, src_mask, trg_mask, spkr_emb=None):
+        raise NotImplementedError("DecoderLayer runs inside Decoder (Models/decoder.py): its self-attention needs the "
+                                  "key / value cache of the earlier positions")

@@ -18,13 +18,12 @@ class PostConvNet(nn.Module):
 
     def __init__(self, hp, num_hidden, mel_dim, reduction_rate, dropout=0.5, prev_version=True):
         super().__init__()
-        if not prev_version:
-            raise NotImplementedError("prev_version=False is only used by Transformer-TTS (SURVEY §8f f3)")
         self.prev_version = prev_version
         self.conv1 = nn.Conv1d(in_channels=mel_dim * reduction_rate, out_channels=num_hidden, kernel_size=5, padding=4)
         self.conv_list = clones(nn.Conv1d(in_channels=num_hidden, out_channels=num_hidden, kernel_size=5, padding=4), 3)
         self.conv2 = nn.Conv1d(in_channels=num_hidden, out_channels=mel_dim * reduction_rate, kernel_size=5, padding=4)
-        self.out = nn.Linear(num_hidden, mel_dim * reduction_rate)
+        if self.prev_version:  # Transformer-TTS builds it with prev_version=False: no `out` (postnets.py:40-41)
+            self.out = nn.Linear(num_hidden, mel_dim * reduction_rate)
         self.batch_norm_list = clones(nn.BatchNorm1d(num_hidden), 3)
         self.pre_batchnorm = nn.BatchNorm1d(num_hidden)
         self.dropout1 = nn.Dropout(p=dropout)
@@ -37,4 +36,8 @@ class PostConvNet(nn.Module):
     def forward(self, input_, mask=None):
         E.require_inference(self, "PostConvNet")
         E.require_cuda(input_, "PostConvNet")
+        if not self.prev_version:
+            # postnets.py:64-79 with prev_version=False computes the five convolutions and then returns
+            # `mel_pred.transpose(1, 2)`, i.e. its INPUT: the result does not depend on them, so none is launched
+            return input_
         return self.run(input_.to(torch.bfloat16).contiguous())

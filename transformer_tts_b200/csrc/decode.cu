@@ -153,7 +153,8 @@ __global__ void __launch_bounds__(kAdThreads)
 attn_decode_kernel(const __nv_bfloat16* __restrict__ q, int64_t ldq, const __nv_bfloat16* __restrict__ knew,
                    const __nv_bfloat16* __restrict__ vnew, int64_t ldkv, __nv_bfloat16* __restrict__ kc,
                    __nv_bfloat16* __restrict__ vc, const int32_t* __restrict__ pos_ptr,
-                   const int32_t* __restrict__ kv_len, __nv_bfloat16* __restrict__ ctx, int64_t ldc, int H, int cap) {
+                   const int32_t* __restrict__ kv_len, __nv_bfloat16* __restrict__ ctx, int64_t ldc, int cap, int64_t sb,
+                   int64_t sh, int64_t sj) {
   static_assert(DH % 8 == 0 && DH <= 128, "head dimension");
   constexpr int VEC = DH / 8;                  // 16-byte vectors per key row
   constexpr int GROUPS = kAdThreads / VEC;     // key groups of the P.V phase
@@ -164,12 +165,13 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, int64_t ldq, const __nv_
   __shared__ float s_part[GROUPS][DH];
   const int h = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
   const int pos = pos_ptr ? __ldg(pos_ptr) : 0;
-  const int n = kv_len ? min(__ldg(kv_len + b), cap) : min(pos + 1, cap);
-  __nv_bfloat16* kb = kc + (static_cast<int64_t>(b) * H + h) * cap * DH;
-  __nv_bfloat16* vb = vc + (static_cast<int64_t>(b) * H + h) * cap * DH;
+  int n = pos_ptr ? min(pos + 1, cap) : cap;
+  if (kv_len) n = min(n, __ldg(kv_len + b));
+  __nv_bfloat16* kb = kc + b * sb + h * sh;
+  __nv_bfloat16* vb = vc + b * sb + h * sh;
   if (knew && pos < cap && tid < DH) {          // this step's key / value join the cache first
-    kb[static_cast<int64_t>(pos) * DH + tid] = knew[static_cast<int64_t>(b) * ldkv + h * DH + tid];
-    vb[static_cast<int64_t>(pos) * DH + tid] = vnew[static_cast<int64_t>(b) * ldkv + h * DH + tid];
+    kb[pos * sj + tid] = knew[static_cast<int64_t>(b) * ldkv + h * DH + tid];
+    vb[pos * sj + tid] = vnew[static_cast<int64_t>(b) * ldkv + h * DH + tid];
   }
   if (tid < DH) s_q[tid] = __bfloat162float(q[static_cast<int64_t>(b) * ldq + h * DH + tid]) * rsqrtf(static_cast<float>(DH));
   __syncthreads();
@@ -177,7 +179,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, int64_t ldq, const __nv_
   // scores: one key per thread
   float mx = -INFINITY;
   for (int j = tid; j < n; j += kAdThreads) {
-    const uint4* kr = reinterpret_cast<const uint4*>(kb + static_cast<int64_t>(j) * DH);
+    const uint4* kr = reinterpret_cast<const uint4*>(kb + j * sj);
     uint4 kv[VEC];
 #pragma unroll
     for (int i = 0; i < VEC; ++i) kv[i] = kr[i];
@@ -221,7 +223,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, int64_t ldq, const __nv_
   float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   if (grp < GROUPS) {
     for (int j = grp; j < n; j += GROUPS) {
-      const uint4 vv = *reinterpret_cast<const uint4*>(vb + static_cast<int64_t>(j) * DH + vi * 8);
+      const uint4 vv = *reinterpret_cast<const uint4*>(vb + j * sj + vi * 8);
       const float pj = s_p[j];
       const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&vv);
 #pragma unroll
@@ -279,24 +281,26 @@ extern "C" int ttsb200_small_linear(const ttsb200_small_linear_args* a, ttsb200_
 }
 
 extern "C" int ttsb200_attn_decode(const void* q_bf16, int64_t ldq, const void* knew_bf16, const void* vnew_bf16,
-                                   int64_t ldkv, void* k_cache, void* v_cache, const int32_t* pos,
-                                   const int32_t* kv_len, void* ctx_bf16, int64_t ldc, int32_t R, int32_t H, int32_t Dh,
-                                   int32_t cap, ttsb200_stream_t s) {
+                                   int64_t ldkv, void* k_cache, void* v_cache, int64_t kv_stride_b, int64_t kv_stride_h,
+                                   int64_t kv_stride_j, const int32_t* pos, const int32_t* kv_len, void* ctx_bf16,
+                                   int64_t ldc, int32_t R, int32_t H, int32_t Dh, int32_t cap, ttsb200_stream_t s) {
   TTSB_CHECK_ARG(q_bf16 && k_cache && v_cache && ctx_bf16 && R > 0 && H > 0 && cap > 0, "attn_decode: bad args");
   TTSB_CHECK_ARG(Dh == 96, "attn_decode: head dimension %d unsupported (96)", Dh);
   TTSB_CHECK_ARG((knew_bf16 == nullptr) == (vnew_bf16 == nullptr), "attn_decode: knew and vnew go together");
-  TTSB_CHECK_ARG((pos != nullptr) != (kv_len != nullptr), "attn_decode: exactly one of pos (self-attention) / kv_len (cross-attention)");
+  TTSB_CHECK_ARG(pos || kv_len, "attn_decode: pos (self-attention) and / or kv_len (cross-attention) is required");
   TTSB_CHECK_ARG(!knew_bf16 || pos, "attn_decode: appending needs pos");
-  TTSB_CHECK_ARG(cap <= 16384, "attn_decode: cache capacity %d above 16384 keys", cap);
-  TTSB_CHECK_ARG((reinterpret_cast<uintptr_t>(k_cache) & 15) == 0 && (reinterpret_cast<uintptr_t>(v_cache) & 15) == 0,
-                 "attn_decode: caches must be 16-byte aligned");
+  TTSB_CHECK_ARG(cap <= 16384, "attn_decode: %d keys above the 16384 supported", cap);
+  TTSB_CHECK_ARG((reinterpret_cast<uintptr_t>(k_cache) & 15) == 0 && (reinterpret_cast<uintptr_t>(v_cache) & 15) == 0 &&
+                     kv_stride_b % 8 == 0 && kv_stride_h % 8 == 0 && kv_stride_j % 8 == 0 && kv_stride_j >= Dh,
+                 "attn_decode: key / value rows must be 16-byte aligned");
   auto kern = dec::attn_decode_kernel<96>;
   const int smem = cap * 4;
   TTSB_SMEM_OPT_IN(kern, 16384 * 4);
   kern<<<dim3(H, R), dec::kAdThreads, smem, static_cast<cudaStream_t>(s)>>>(
       static_cast<const __nv_bfloat16*>(q_bf16), ldq, static_cast<const __nv_bfloat16*>(knew_bf16),
       static_cast<const __nv_bfloat16*>(vnew_bf16), ldkv, static_cast<__nv_bfloat16*>(k_cache),
-      static_cast<__nv_bfloat16*>(v_cache), pos, kv_len, static_cast<__nv_bfloat16*>(ctx_bf16), ldc, H, cap);
+      static_cast<__nv_bfloat16*>(v_cache), pos, kv_len, static_cast<__nv_bfloat16*>(ctx_bf16), ldc, cap, kv_stride_b,
+      kv_stride_h, kv_stride_j);
   TTSB_CHECK_CUDA(cudaGetLastError());
   return TTSB_OK;
 }

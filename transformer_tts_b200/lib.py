@@ -64,9 +64,9 @@ _SIGNATURES = {
     "ttsb200_debug_tmap_cache": ([C.c_void_p, C.c_void_p], None),
     "ttsb200_conv_gemm": ([C.POINTER(GemmArgs), C.c_void_p], C.c_int),
     "ttsb200_small_linear": ([C.POINTER(SmallLinearArgs), C.c_void_p], C.c_int),
-    "ttsb200_attn_decode": ([C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
-                             C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p],
-                            C.c_int),
+    "ttsb200_attn_decode": ([C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64,
+                             C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
+                             C.c_int32, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_advance_pos": ([C.c_void_p, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_ffn_fused": ([C.c_void_p] * 10 + [C.c_float, C.c_void_p, C.c_void_p] + [C.c_int32] * 4 + [C.c_void_p] * 3, C.c_int),
     "ttsb200_build_tile_map": ([C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
@@ -733,20 +733,22 @@ def small_linear(w: torch.Tensor, bias: Optional[torch.Tensor], K: int, *, x_f32
     _count()
 
 
-def attn_decode(q: torch.Tensor, q_off: int, ldq: int, k_cache: torch.Tensor, v_cache: torch.Tensor, ctx: torch.Tensor, *,
-                kv_new: Optional[torch.Tensor] = None, k_off: int = 0, v_off: int = 0, pos: Optional[torch.Tensor] = None,
-                kv_len: Optional[torch.Tensor] = None) -> None:
-    """One query row per (utterance, head) against the caches [R][H][cap][Dh]; q / kv_new are column ranges (element
-    offsets q_off / k_off / v_off) of a (R, ldq) bf16 buffer such as the q|k|v projection of the step."""
-    R, H, cap, Dh = k_cache.shape
+def attn_decode(q: torch.Tensor, q_off: int, ldq: int, k: torch.Tensor, v_off: int, strides, cap: int, H: int, Dh: int,
+                ctx: torch.Tensor, *, kv_new: Optional[torch.Tensor] = None, knew_off: int = 0, vnew_off: int = 0,
+                pos: Optional[torch.Tensor] = None, kv_len: Optional[torch.Tensor] = None) -> None:
+    """One query row per (utterance, head).  q / kv_new: column ranges (element offsets) of a (R, ldq) bf16 buffer such as
+    the step's q|k|v projection.  k: the bf16 buffer holding keys AND values: values start v_off elements after the keys;
+    strides = (utterance, head, key) element strides; cap = key slots."""
+    R = ctx.shape[0]
     es = 2
     qp = _ptr(q, torch.bfloat16, "q") + q_off * es
     kp = vp = None
     if kv_new is not None:
         base = _ptr(kv_new, torch.bfloat16, "kv_new")
-        kp, vp = base + k_off * es, base + v_off * es
-    _check(load().ttsb200_attn_decode(qp, ldq, kp, vp, int(kv_new.shape[-1]) if kv_new is not None else 0,
-                                      _ptr(k_cache, torch.bfloat16, "k_cache"), _ptr(v_cache, torch.bfloat16, "v_cache"),
+        kp, vp = base + knew_off * es, base + vnew_off * es
+    kb = _ptr(k, torch.bfloat16, "k")
+    _check(load().ttsb200_attn_decode(qp, ldq, kp, vp, int(kv_new.shape[-1]) if kv_new is not None else 0, kb,
+                                      kb + v_off * es, int(strides[0]), int(strides[1]), int(strides[2]),
                                       _ptr(pos, torch.int32, "pos"), _ptr(kv_len, torch.int32, "kv_len"),
                                       _ptr(ctx, torch.bfloat16, "ctx"), int(ctx.shape[-1]), R, H, Dh, cap, _stream()),
            "attn_decode")
