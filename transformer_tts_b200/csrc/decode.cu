@@ -36,6 +36,36 @@ __device__ __forceinline__ void mma_bf16_16816(float* c, uint32_t a0, uint32_t a
       : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
+// Programmatic dependent launch: a decode step is ~58 dependent kernels of a few microseconds, so the gap between two
+// of them matters as much as the kernels.  Each kernel lets its successor start at once (launch_dependents) and does
+// whatever touches only immutable data (weight fragments) before it waits for its predecessor's results (wait returns
+// when the preceding kernel has completed and its writes are visible).  Pre-wait code must not read anything a kernel
+// of the step writes: two kernels back may still be running.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+// 16-byte asynchronous global -> shared copy (src_bytes = 0 writes zeros): every copy of a stage is issued before the first
+// one is waited for, so a stage costs ONE trip to L2 / HBM however many rows it has.
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc, int src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+template <typename... Params, typename... Args>
+static cudaError_t launch_pdl(void (*kern)(Params...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<Params>(args)...);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -48,78 +78,126 @@ small_linear_kernel(const ttsb200_small_linear_args p) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int Kp = (p.K + 31) & ~31;
   const int row_bytes = Kp * 2 + kSlPadBytes;
-  const int pos = p.pos ? __ldg(p.pos) : 0;
   const int r0 = blockIdx.y * kSlRows;
-  const int xpos = pos + p.x_pos_bias;   // index of the step the input rows were produced at (negative: zeros)
-
-  // ---- stage the input rows as bf16 (LayerNorm applied on the way) ----
-  for (int rr = warp; rr < kSlRows; rr += kSlWarps) {
-    const int row = r0 + rr;
-    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(sl_smem + rr * row_bytes);
-    const bool valid = row < p.R && (p.x_pos_stride == 0 || xpos >= 0);
-    if (!valid) {
-      for (int k = lane; k < Kp; k += 32) dst[k] = __float2bfloat16(0.f);
-      continue;
-    }
-    const int64_t off = static_cast<int64_t>(row) * p.ldx + (p.x_pos_stride ? static_cast<int64_t>(xpos) * p.x_pos_stride : 0);
-    if (p.x_bf16) {
-      const __nv_bfloat16* src = static_cast<const __nv_bfloat16*>(p.x_bf16) + off;
-      for (int k = lane; k < Kp; k += 32) dst[k] = k < p.K ? src[k] : __float2bfloat16(0.f);
-      continue;
-    }
-    const float* src = p.x_f32 + off;
-    float mean = 0.f, rstd = 1.f;
-    if (p.ln_g) {   // two-pass statistics, as torch.nn.functional.layer_norm
-      float s = 0.f;
-      for (int k = lane; k < p.K; k += 32) s += src[k];
-      mean = warp_sum(s) / static_cast<float>(p.K);
-      float q = 0.f;
-      for (int k = lane; k < p.K; k += 32) {
-        const float d = src[k] - mean;
-        q = fmaf(d, d, q);
-      }
-      rstd = rsqrtf(warp_sum(q) / static_cast<float>(p.K) + p.eps);
-    }
-    __nv_bfloat16* xn = (p.xn_bf16 && blockIdx.x == 0) ? static_cast<__nv_bfloat16*>(p.xn_bf16) + static_cast<int64_t>(row) * p.K
-                                                       : nullptr;
-    for (int k = lane; k < Kp; k += 32) {
-      float v = 0.f;
-      if (k < p.K) {
-        v = src[k];
-        if (p.ln_g) v = fmaf((v - mean) * rstd, __ldg(p.ln_g + k), __ldg(p.ln_b + k));
-      }
-      const __nv_bfloat16 h = __float2bfloat16(v);
-      dst[k] = h;
-      if (xn && k < p.K) xn[k] = h;
+  pdl_launch_dependents();
+  // weights are immutable: this CTA's 16 W rows leave for shared memory before the predecessor has finished
+  uint8_t* sW = sl_smem + kSlRows * row_bytes;
+  {
+    const int nvp = Kp >> 3;   // 16-byte vectors per (zero-padded) row
+    const int ncta0 = blockIdx.x * kSlWarps * 8;
+    for (int i = threadIdx.x; i < kSlWarps * 8 * nvp; i += kSlWarps * 32) {
+      const int r = i / nvp, c = i - r * nvp;
+      const int wr = min(ncta0 + r, p.N - 1);
+      cp_async16(sW + r * row_bytes + c * 16,
+                 static_cast<const __nv_bfloat16*>(p.w_bf16) + static_cast<int64_t>(wr) * p.ldw + c * 8, 16);
     }
   }
+  const int n0 = (blockIdx.x * kSlWarps + warp) * 8;
+  const int g = lane >> 2, tq = lane & 3;
+  const int nkb = Kp >> 5;
+  pdl_wait();
+  const int pos = p.pos ? *reinterpret_cast<const volatile int32_t*>(p.pos) : 0;
+  const int xpos = pos + p.x_pos_bias;   // index of the step the input rows were produced at (negative: zeros)
+
+  // ---- stage the input rows as bf16 (LayerNorm applied on the way).  Every CTA needs all rows and has two warps, so the
+  // loads of several rows are put in flight together: the latency of one trip to L2 is paid once per group, not per row ----
+  const bool pos_ok = p.x_pos_stride == 0 || xpos >= 0;
+  const int64_t pos_off = p.x_pos_stride ? static_cast<int64_t>(xpos) * p.x_pos_stride : 0;
+  if (p.x_f32 && p.ln_g) {
+    constexpr int G = 4;            // rows in flight per warp
+    constexpr int MAXV = 16;        // K <= 512 (checked on the host)
+    const float inv_k = 1.f / static_cast<float>(p.K);
+    for (int rb = warp * G; rb < kSlRows; rb += kSlWarps * G) {
+      float v[G][MAXV];
+#pragma unroll
+      for (int i = 0; i < G; ++i) {
+        const int row = r0 + rb + i;
+        const bool valid = row < p.R && pos_ok;
+        const float* src = p.x_f32 + static_cast<int64_t>(valid ? row : 0) * p.ldx + pos_off;
+#pragma unroll
+        for (int j = 0; j < MAXV; ++j) {
+          const int k = lane + 32 * j;
+          v[i][j] = (valid && k < p.K) ? src[k] : 0.f;
+        }
+      }
+      float mean[G], rstd[G];
+#pragma unroll
+      for (int i = 0; i < G; ++i) {   // two-pass statistics, as torch.nn.functional.layer_norm
+        float sum = 0.f;
+#pragma unroll
+        for (int j = 0; j < MAXV; ++j) sum += v[i][j];
+        mean[i] = warp_sum(sum) * inv_k;
+      }
+#pragma unroll
+      for (int i = 0; i < G; ++i) {
+        float q = 0.f;
+#pragma unroll
+        for (int j = 0; j < MAXV; ++j) {
+          const float d = (lane + 32 * j < p.K) ? v[i][j] - mean[i] : 0.f;
+          q = fmaf(d, d, q);
+        }
+        rstd[i] = rsqrtf(warp_sum(q) * inv_k + p.eps);
+      }
+#pragma unroll
+      for (int j = 0; j < MAXV; ++j) {
+        const int k = lane + 32 * j;
+        if (k >= Kp) break;
+        const float gk = k < p.K ? __ldg(p.ln_g + k) : 0.f, bk = k < p.K ? __ldg(p.ln_b + k) : 0.f;
+#pragma unroll
+        for (int i = 0; i < G; ++i) {
+          const int row = r0 + rb + i;
+          const bool valid = row < p.R && pos_ok;
+          const __nv_bfloat16 h = __float2bfloat16(valid && k < p.K ? fmaf((v[i][j] - mean[i]) * rstd[i], gk, bk) : 0.f);
+          reinterpret_cast<__nv_bfloat16*>(sl_smem + (rb + i) * row_bytes)[k] = h;
+          if (p.xn_bf16 && blockIdx.x == 0 && valid && k < p.K)
+            static_cast<__nv_bfloat16*>(p.xn_bf16)[static_cast<int64_t>(row) * p.K + k] = h;
+        }
+      }
+    }
+  } else if (p.x_bf16 && (p.K & 7) == 0 && (p.ldx & 7) == 0 && (p.x_pos_stride & 7) == 0 &&
+             (reinterpret_cast<uintptr_t>(p.x_bf16) & 15) == 0) {
+    // bf16 rows: asynchronous 16-byte copies, every row of the tile in flight at once
+    const int nv = p.K >> 3, nvp = Kp >> 3;
+    for (int i = threadIdx.x; i < kSlRows * nvp; i += kSlWarps * 32) {
+      const int rr = i / nvp, c = i - rr * nvp;
+      const int row = r0 + rr;
+      const bool valid = row < p.R && pos_ok && c < nv;
+      cp_async16(sl_smem + rr * row_bytes + c * 16,
+                 static_cast<const __nv_bfloat16*>(p.x_bf16) + static_cast<int64_t>(valid ? row : 0) * p.ldx + pos_off + (valid ? c * 8 : 0),
+                 valid ? 16 : 0);
+    }
+  } else {
+    // fp32 rows without LayerNorm (the prenet's mel input) or unaligned bf16 rows: element-wise, flattened over the tile
+    // so that consecutive iterations are independent loads
+#pragma unroll 8
+    for (int i = threadIdx.x; i < kSlRows * Kp; i += kSlWarps * 32) {
+      const int rr = i / Kp, k = i - rr * Kp;
+      const int row = r0 + rr;
+      const bool valid = row < p.R && pos_ok && k < p.K;
+      const int64_t off = static_cast<int64_t>(valid ? row : 0) * p.ldx + pos_off + (valid ? k : 0);
+      __nv_bfloat16 h = __float2bfloat16(0.f);
+      if (valid) h = p.x_bf16 ? static_cast<const __nv_bfloat16*>(p.x_bf16)[off] : __float2bfloat16(p.x_f32[off]);
+      reinterpret_cast<__nv_bfloat16*>(sl_smem + rr * row_bytes)[k] = h;
+      if (p.xn_bf16 && blockIdx.x == 0 && valid) static_cast<__nv_bfloat16*>(p.xn_bf16)[static_cast<int64_t>(row) * p.K + k] = h;
+    }
+  }
+  cp_async_wait_all();
   __syncthreads();
 
   // ---- 16 x 8 outputs per warp; contraction index permuted: lane (g, tq) takes physical k = 32 kb + 8 tq + [0, 8) of W
   // row n0 + g as the B fragments of two k-steps, and the same physical k of x rows g, g + 8 as the A fragments ----
-  const int n0 = (blockIdx.x * kSlWarps + warp) * 8;
   if (n0 >= p.N) return;
-  const int g = lane >> 2, tq = lane & 3;
-  const int wrow = min(n0 + g, p.N - 1);
-  const uint4* wp = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.w_bf16) + static_cast<int64_t>(wrow) * p.ldw) + tq;
   const uint8_t* xa = sl_smem + g * row_bytes + tq * 16;
   const uint8_t* xb = xa + 8 * row_bytes;
+  const uint8_t* wa = sW + (warp * 8 + g) * row_bytes + tq * 16;
   float acc[4] = {0.f, 0.f, 0.f, 0.f};
-  const int nkb = Kp >> 5;
-  constexpr int U = 12;   // W loads in flight per lane (K = 384: the whole row)
-  for (int kc = 0; kc < nkb; kc += U) {
-    uint4 w[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u)
-      if (kc + u < nkb) w[u] = __ldg(wp + (kc + u) * 4);
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      if (kc + u >= nkb) break;
-      const uint4 a = *reinterpret_cast<const uint4*>(xa + (kc + u) * 64);
-      const uint4 b = *reinterpret_cast<const uint4*>(xb + (kc + u) * 64);
-      mma_bf16_16816(acc, a.x, b.x, a.y, b.y, w[u].x, w[u].y);
-      mma_bf16_16816(acc, a.z, b.z, a.w, b.w, w[u].z, w[u].w);
-    }
+#pragma unroll 4
+  for (int kb = 0; kb < nkb; ++kb) {
+    const uint4 a = *reinterpret_cast<const uint4*>(xa + kb * 64);
+    const uint4 b = *reinterpret_cast<const uint4*>(xb + kb * 64);
+    const uint4 w = *reinterpret_cast<const uint4*>(wa + kb * 64);
+    mma_bf16_16816(acc, a.x, b.x, a.y, b.y, w.x, w.y);
+    mma_bf16_16816(acc, a.z, b.z, a.w, b.w, w.z, w.w);
   }
 
   // ---- epilogue: c0,c1 = (row g, cols 2 tq, 2 tq + 1); c2,c3 = (row g + 8, same cols) ----
@@ -164,7 +242,9 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, int64_t ldq, const __nv_
   __shared__ float s_red[kAdThreads / 32];
   __shared__ float s_part[GROUPS][DH];
   const int h = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
-  const int pos = pos_ptr ? __ldg(pos_ptr) : 0;
+  pdl_launch_dependents();
+  pdl_wait();
+  const int pos = pos_ptr ? *reinterpret_cast<const volatile int32_t*>(pos_ptr) : 0;
   int n = pos_ptr ? min(pos + 1, cap) : cap;
   if (kv_len) n = min(n, __ldg(kv_len + b));
   __nv_bfloat16* kb = kc + b * sb + h * sh;
@@ -222,15 +302,26 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, int64_t ldq, const __nv_
   const int grp = tid / VEC, vi = tid - grp * VEC;
   float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   if (grp < GROUPS) {
-    for (int j = grp; j < n; j += GROUPS) {
-      const uint4 vv = *reinterpret_cast<const uint4*>(vb + j * sj + vi * 8);
-      const float pj = s_p[j];
-      const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&vv);
+    constexpr int UV = 4;   // value rows in flight per thread
+    for (int j0 = grp; j0 < n; j0 += GROUPS * UV) {
+      uint4 vv[UV];
+      float pj[UV];
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const float2 f = __bfloat1622float2(h2[e]);
-        o[e * 2] = fmaf(pj, f.x, o[e * 2]);
-        o[e * 2 + 1] = fmaf(pj, f.y, o[e * 2 + 1]);
+      for (int u = 0; u < UV; ++u) {
+        const int j = j0 + u * GROUPS;
+        const bool ok = j < n;
+        vv[u] = ok ? *reinterpret_cast<const uint4*>(vb + j * sj + vi * 8) : make_uint4(0, 0, 0, 0);
+        pj[u] = ok ? s_p[j] : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < UV; ++u) {
+        const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&vv[u]);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 f = __bfloat1622float2(h2[e]);
+          o[e * 2] = fmaf(pj[u], f.x, o[e * 2]);
+          o[e * 2 + 1] = fmaf(pj[u], f.y, o[e * 2 + 1]);
+        }
       }
     }
 #pragma unroll
@@ -246,6 +337,8 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, int64_t ldq, const __nv_
 }
 
 __global__ void advance_pos_kernel(int32_t* pos, int32_t delta) {
+  pdl_launch_dependents();
+  pdl_wait();
   if (threadIdx.x == 0 && blockIdx.x == 0) *pos += delta;
 }
 
@@ -266,17 +359,17 @@ extern "C" int ttsb200_small_linear(const ttsb200_small_linear_args* a, ttsb200_
                  static_cast<long long>(p.ldw), p.K);
   TTSB_CHECK_ARG((p.ln_g == nullptr) == (p.ln_b == nullptr) && (!p.ln_g || p.x_f32), "small_linear: LayerNorm needs ln_g, ln_b and x_f32");
   TTSB_CHECK_ARG(!p.xn_bf16 || p.x_f32, "small_linear: xn_bf16 needs x_f32");
+  TTSB_CHECK_ARG(!p.ln_g || p.K <= 512, "small_linear: LayerNorm rows of at most 512 columns (K = %d)", p.K);
   TTSB_CHECK_ARG((p.add_row == nullptr) == (p.add_scale == nullptr), "small_linear: add_row and add_scale go together");
   TTSB_CHECK_ARG((!p.x_pos_stride && !p.out_pos_stride && !p.add_row) || p.pos, "small_linear: position-dependent addressing needs pos");
   TTSB_CHECK_ARG(!p.out_f32 || p.ldo >= p.N, "small_linear: ldo < N");
   TTSB_CHECK_ARG(!p.out_bf16 || p.ldob >= p.N, "small_linear: ldob < N");
-  const int smem = dec::kSlRows * (Kp * 2 + dec::kSlPadBytes);
-  TTSB_CHECK_ARG(smem <= 100 * 1024, "small_linear: K = %d is too large", p.K);
+  const int smem = (dec::kSlRows + dec::kSlWarps * 8) * (Kp * 2 + dec::kSlPadBytes);   // x rows + this CTA's W rows
+  TTSB_CHECK_ARG(smem <= 200 * 1024, "small_linear: K = %d is too large", p.K);
   auto kern = dec::small_linear_kernel;
-  TTSB_SMEM_OPT_IN(kern, 100 * 1024);
+  TTSB_SMEM_OPT_IN(kern, 200 * 1024);
   dim3 grid((p.N + dec::kSlWarps * 8 - 1) / (dec::kSlWarps * 8), (p.R + dec::kSlRows - 1) / dec::kSlRows);
-  kern<<<grid, dec::kSlWarps * 32, smem, static_cast<cudaStream_t>(s)>>>(p);
-  TTSB_CHECK_CUDA(cudaGetLastError());
+  TTSB_CHECK_CUDA(dec::launch_pdl(kern, grid, dim3(dec::kSlWarps * 32), smem, static_cast<cudaStream_t>(s), p));
   return TTSB_OK;
 }
 
@@ -296,18 +389,16 @@ extern "C" int ttsb200_attn_decode(const void* q_bf16, int64_t ldq, const void* 
   auto kern = dec::attn_decode_kernel<96>;
   const int smem = cap * 4;
   TTSB_SMEM_OPT_IN(kern, 16384 * 4);
-  kern<<<dim3(H, R), dec::kAdThreads, smem, static_cast<cudaStream_t>(s)>>>(
-      static_cast<const __nv_bfloat16*>(q_bf16), ldq, static_cast<const __nv_bfloat16*>(knew_bf16),
-      static_cast<const __nv_bfloat16*>(vnew_bf16), ldkv, static_cast<__nv_bfloat16*>(k_cache),
-      static_cast<__nv_bfloat16*>(v_cache), pos, kv_len, static_cast<__nv_bfloat16*>(ctx_bf16), ldc, cap, kv_stride_b,
-      kv_stride_h, kv_stride_j);
-  TTSB_CHECK_CUDA(cudaGetLastError());
+  TTSB_CHECK_CUDA(dec::launch_pdl(kern, dim3(H, R), dim3(dec::kAdThreads), smem, static_cast<cudaStream_t>(s),
+                                  static_cast<const __nv_bfloat16*>(q_bf16), ldq, static_cast<const __nv_bfloat16*>(knew_bf16),
+                                  static_cast<const __nv_bfloat16*>(vnew_bf16), ldkv, static_cast<__nv_bfloat16*>(k_cache),
+                                  static_cast<__nv_bfloat16*>(v_cache), pos, kv_len, static_cast<__nv_bfloat16*>(ctx_bf16),
+                                  ldc, static_cast<int>(cap), kv_stride_b, kv_stride_h, kv_stride_j));
   return TTSB_OK;
 }
 
 extern "C" int ttsb200_advance_pos(int32_t* pos, int32_t delta, ttsb200_stream_t s) {
   TTSB_CHECK_ARG(pos != nullptr, "advance_pos: null pointer");
-  dec::advance_pos_kernel<<<1, 32, 0, static_cast<cudaStream_t>(s)>>>(pos, delta);
-  TTSB_CHECK_CUDA(cudaGetLastError());
+  TTSB_CHECK_CUDA(dec::launch_pdl(dec::advance_pos_kernel, dim3(1), dim3(32), 0, static_cast<cudaStream_t>(s), pos, delta));
   return TTSB_OK;
 }
