@@ -30,16 +30,22 @@ st = model.last_state
 t = st.t; lc = t["layers"][0]; D, H, Dh, cap, R = st.D, st.H, st.Dh, st.cap, st.R
 sb, sh, sj = H * cap * Dh, cap * Dh, Dh
 def timeit(name, fn, n=200):
+    """GPU time per launch inside a CUDA graph of n back-to-back launches (warm caches, no host in the loop)."""
     fn(); torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(n): fn()
+    g.replay(); torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(n): fn()
-    e1.record(); torch.cuda.synchronize()
-    print(f"  {name}: {e0.elapsed_time(e1) / n * 1e3:.1f} us")
-for p in (100, 500, 999):
+    e0.record(); g.replay(); e1.record(); torch.cuda.synchronize()
+    print(f"  {name}: {e0.elapsed_time(e1) / n * 1e3:.2f} us")
+for p in (500,):
     st.pos.fill_(p)
     print(f"pos {p}")
     timeit("LN1 + qkv (384 -> 1152)", lambda: lib.small_linear(lc["wqkv1"], lc["bqkv1"], D, x_f32=st.x, ln=lc["ln1"], out_bf16=st.qkv))
+    timeit("qkv from fp32 rows, no LN", lambda: lib.small_linear(lc["wqkv1"], lc["bqkv1"], D, x_f32=st.x, out_bf16=st.qkv))
+    timeit("qkv from bf16 rows", lambda: lib.small_linear(lc["wqkv1"], lc["bqkv1"], D, x_bf16=st.xn, out_bf16=st.qkv))
+    timeit("LN + 384 -> 384", lambda: lib.small_linear(lc["wq2"], lc["bq2"], D, x_f32=st.x, ln=lc["ln2"], out_bf16=st.q2))
     timeit("self attention", lambda: lib.attn_decode(st.qkv, 0, 3 * D, st.kv_self[0], R * sb, (sb, sh, sj), cap, H, Dh, st.ctx, kv_new=st.qkv, knew_off=D, vnew_off=2 * D, pos=st.pos))
     timeit("out-proj + res (384 -> 384)", lambda: lib.small_linear(lc["wo1"], lc["bo1"], D, x_bf16=st.ctx, res_f32=st.x, out_f32=st.x2))
     timeit("cross attention (128 keys)", lambda: lib.attn_decode(st.q2, 0, D, st.kv_cross[0], D, (st.L * 2 * D, Dh, 2 * D), st.L, H, Dh, st.ctx, kv_len=st.src_len))

@@ -50,7 +50,8 @@ class DecodeState:
         H = dec.heads
         dev = e_bf16.device
         self.R, self.L, self.D, self.H, self.Dh, self.cap = R, L, D, H, D // H, cap
-        self.n_out = head["w"].shape[0]  # mel_dim * r + r
+        self.n_head = head["w"].shape[0]            # mel_dim * r + r
+        self.n_out = (self.n_head + 3) // 4 * 4     # row pitch of out_all: 16-byte aligned rows for the fed-back mel
         self.mel_dim = dec.decoder_prenet.input_size
         self.src_len = src_len
         self.trg_len = trg_len

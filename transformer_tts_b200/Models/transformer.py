@@ -88,7 +88,7 @@ class Transformer(nn.Module):
         """(R, cap, mel*r + r) -> outputs (R, n, mel*r), stop (R, n, r) -> the reference's shapes (transformer.py:109-111)."""
         md = self.mel_dim * self.reduction_rate
         pre = out_all[:, :n, :md]
-        stop = out_all[:, :n, md:]
+        stop = out_all[:, :n, md:md + self.reduction_rate]   # (the row pitch is padded to a multiple of 4 floats)
         if self.reduction_rate == 1:
             stop = stop.squeeze(2)
         return pre, stop
@@ -148,13 +148,13 @@ class Transformer(nn.Module):
                 break
         r, md = self.reduction_rate, self.mel_dim * self.reduction_rate
         mel = st.out_all[:, :done, :md].reshape(text.shape[0], done * r, self.mel_dim)
-        stop = st.out_all[:, :done, md:]
+        stop = st.out_all[:, :done, md:md + r].contiguous()
         self.last_state = st
         return dict(mel=mel, stop_logits=stop, stop_step=self._stop_steps(st.out_all, done, stop_threshold), steps=done)
 
     def _stop_steps(self, out_all: torch.Tensor, n: int, thr: float) -> torch.Tensor:
         md = self.mel_dim * self.reduction_rate
-        p = torch.sigmoid(out_all[:, :n, md:]).mean(dim=-1) > thr
+        p = torch.sigmoid(out_all[:, :n, md:md + self.reduction_rate]).mean(dim=-1) > thr
         p[:, 0] = False
         idx = torch.arange(n, device=out_all.device).expand_as(p)
         return torch.where(p, idx, torch.full_like(idx, n)).min(dim=1).values

@@ -17,6 +17,7 @@
 // Position-dependent addressing (which cache slot, which positional-encoding row, where the step's output goes) reads a
 // device scalar, so one captured CUDA graph replays for every step.
 #include <cuda_bf16.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "../../include/ttsb200.h"
@@ -24,7 +25,11 @@
 namespace ttsb {
 namespace dec {
 
-constexpr int kSlWarps = 2;          // warps per CTA: 16 output columns
+constexpr int kSlColGroups = 4;      // 8-column groups per CTA: 32 output columns
+constexpr int kSlKSlices = 2;        // warps that share one column group, each taking every 2nd 32-wide k-block
+constexpr int kSlWarps = kSlColGroups * kSlKSlices;
+constexpr int kSlThreads = kSlWarps * 32;
+constexpr int kSlCols = kSlColGroups * 8;
 constexpr int kSlRows = 16;          // rows per CTA = M of the MMA tile
 constexpr int kSlPadBytes = 16;      // row padding in shared memory: rows g, g+1, .. land in different 16-byte bank groups
 
@@ -62,7 +67,8 @@ static cudaError_t launch_pdl(void (*kern)(Params...), dim3 grid, dim3 block, si
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  static const bool no_pdl = getenv("TTSB_NO_PDL") != nullptr;
+  cfg.numAttrs = no_pdl ? 0 : 1;
   return cudaLaunchKernelEx(&cfg, kern, static_cast<Params>(args)...);
 }
 
@@ -72,10 +78,16 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
-__global__ void __launch_bounds__(kSlWarps * 32)
+// A decode step is a chain of ~58 dependent kernels with a few microseconds of work each: what matters inside a kernel is
+// the number of DEPENDENT memory round trips, not bytes.  Hence: every global -> shared transfer of a stage is a cp.async
+// issued before any is waited for (one round trip per stage); 8 warps per CTA, so the LayerNorm pass has 2 rows per warp
+// and the contraction is cut in 4 k-slices per column group (partial sums meet in shared memory).
+__global__ void __launch_bounds__(kSlThreads)
 small_linear_kernel(const ttsb200_small_linear_args p) {
   extern __shared__ __align__(16) uint8_t sl_smem[];
+  __shared__ float s_red[kSlKSlices - 1][kSlColGroups][32][4];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int cgp = warp % kSlColGroups, ks = warp / kSlColGroups;
   const int Kp = (p.K + 31) & ~31;
   const int row_bytes = Kp * 2 + kSlPadBytes;
   const int r0 = blockIdx.y * kSlRows;
@@ -84,81 +96,32 @@ small_linear_kernel(const ttsb200_small_linear_args p) {
   uint8_t* sW = sl_smem + kSlRows * row_bytes;
   {
     const int nvp = Kp >> 3;   // 16-byte vectors per (zero-padded) row
-    const int ncta0 = blockIdx.x * kSlWarps * 8;
-    for (int i = threadIdx.x; i < kSlWarps * 8 * nvp; i += kSlWarps * 32) {
+    const int ncta0 = blockIdx.x * kSlCols;
+    for (int i = threadIdx.x; i < kSlCols * nvp; i += kSlThreads) {
       const int r = i / nvp, c = i - r * nvp;
       const int wr = min(ncta0 + r, p.N - 1);
       cp_async16(sW + r * row_bytes + c * 16,
                  static_cast<const __nv_bfloat16*>(p.w_bf16) + static_cast<int64_t>(wr) * p.ldw + c * 8, 16);
     }
   }
-  const int n0 = (blockIdx.x * kSlWarps + warp) * 8;
+  const int n0 = blockIdx.x * kSlCols + cgp * 8;
   const int g = lane >> 2, tq = lane & 3;
   const int nkb = Kp >> 5;
   pdl_wait();
   const int pos = p.pos ? *reinterpret_cast<const volatile int32_t*>(p.pos) : 0;
   const int xpos = pos + p.x_pos_bias;   // index of the step the input rows were produced at (negative: zeros)
 
-  // ---- stage the input rows as bf16 (LayerNorm applied on the way).  Every CTA needs all rows and has two warps, so the
-  // loads of several rows are put in flight together: the latency of one trip to L2 is paid once per group, not per row ----
+  // ---- stage the input rows as bf16 (LayerNorm applied on the way) ----
   const bool pos_ok = p.x_pos_stride == 0 || xpos >= 0;
   const int64_t pos_off = p.x_pos_stride ? static_cast<int64_t>(xpos) * p.x_pos_stride : 0;
-  if (p.x_f32 && p.ln_g) {
-    constexpr int G = 4;            // rows in flight per warp
-    constexpr int MAXV = 16;        // K <= 512 (checked on the host)
-    const float inv_k = 1.f / static_cast<float>(p.K);
-    for (int rb = warp * G; rb < kSlRows; rb += kSlWarps * G) {
-      float v[G][MAXV];
-#pragma unroll
-      for (int i = 0; i < G; ++i) {
-        const int row = r0 + rb + i;
-        const bool valid = row < p.R && pos_ok;
-        const float* src = p.x_f32 + static_cast<int64_t>(valid ? row : 0) * p.ldx + pos_off;
-#pragma unroll
-        for (int j = 0; j < MAXV; ++j) {
-          const int k = lane + 32 * j;
-          v[i][j] = (valid && k < p.K) ? src[k] : 0.f;
-        }
-      }
-      float mean[G], rstd[G];
-#pragma unroll
-      for (int i = 0; i < G; ++i) {   // two-pass statistics, as torch.nn.functional.layer_norm
-        float sum = 0.f;
-#pragma unroll
-        for (int j = 0; j < MAXV; ++j) sum += v[i][j];
-        mean[i] = warp_sum(sum) * inv_k;
-      }
-#pragma unroll
-      for (int i = 0; i < G; ++i) {
-        float q = 0.f;
-#pragma unroll
-        for (int j = 0; j < MAXV; ++j) {
-          const float d = (lane + 32 * j < p.K) ? v[i][j] - mean[i] : 0.f;
-          q = fmaf(d, d, q);
-        }
-        rstd[i] = rsqrtf(warp_sum(q) * inv_k + p.eps);
-      }
-#pragma unroll
-      for (int j = 0; j < MAXV; ++j) {
-        const int k = lane + 32 * j;
-        if (k >= Kp) break;
-        const float gk = k < p.K ? __ldg(p.ln_g + k) : 0.f, bk = k < p.K ? __ldg(p.ln_b + k) : 0.f;
-#pragma unroll
-        for (int i = 0; i < G; ++i) {
-          const int row = r0 + rb + i;
-          const bool valid = row < p.R && pos_ok;
-          const __nv_bfloat16 h = __float2bfloat16(valid && k < p.K ? fmaf((v[i][j] - mean[i]) * rstd[i], gk, bk) : 0.f);
-          reinterpret_cast<__nv_bfloat16*>(sl_smem + (rb + i) * row_bytes)[k] = h;
-          if (p.xn_bf16 && blockIdx.x == 0 && valid && k < p.K)
-            static_cast<__nv_bfloat16*>(p.xn_bf16)[static_cast<int64_t>(row) * p.K + k] = h;
-        }
-      }
-    }
-  } else if (p.x_bf16 && (p.K & 7) == 0 && (p.ldx & 7) == 0 && (p.x_pos_stride & 7) == 0 &&
-             (reinterpret_cast<uintptr_t>(p.x_bf16) & 15) == 0) {
-    // bf16 rows: asynchronous 16-byte copies, every row of the tile in flight at once
+  float* sF = reinterpret_cast<float*>(sW + kSlCols * row_bytes);   // fp32 staging rows [16][Kp] (fp32 inputs only)
+  const bool vec_bf16 = p.x_bf16 && (p.K & 7) == 0 && (p.ldx & 7) == 0 && (p.x_pos_stride & 7) == 0 &&
+                        (reinterpret_cast<uintptr_t>(p.x_bf16) & 15) == 0;
+  const bool vec_f32 = p.x_f32 && (p.K & 3) == 0 && (p.ldx & 3) == 0 && (p.x_pos_stride & 3) == 0 &&
+                       (reinterpret_cast<uintptr_t>(p.x_f32) & 15) == 0;
+  if (vec_bf16) {
     const int nv = p.K >> 3, nvp = Kp >> 3;
-    for (int i = threadIdx.x; i < kSlRows * nvp; i += kSlWarps * 32) {
+    for (int i = threadIdx.x; i < kSlRows * nvp; i += kSlThreads) {
       const int rr = i / nvp, c = i - rr * nvp;
       const int row = r0 + rr;
       const bool valid = row < p.R && pos_ok && c < nv;
@@ -166,39 +129,102 @@ small_linear_kernel(const ttsb200_small_linear_args p) {
                  static_cast<const __nv_bfloat16*>(p.x_bf16) + static_cast<int64_t>(valid ? row : 0) * p.ldx + pos_off + (valid ? c * 8 : 0),
                  valid ? 16 : 0);
     }
-  } else {
-    // fp32 rows without LayerNorm (the prenet's mel input) or unaligned bf16 rows: element-wise, flattened over the tile
-    // so that consecutive iterations are independent loads
-#pragma unroll 8
-    for (int i = threadIdx.x; i < kSlRows * Kp; i += kSlWarps * 32) {
+  } else if (vec_f32) {
+    const int nv = p.K >> 2, nvp = Kp >> 2;
+    for (int i = threadIdx.x; i < kSlRows * nvp; i += kSlThreads) {
+      const int rr = i / nvp, c = i - rr * nvp;
+      const int row = r0 + rr;
+      const bool valid = row < p.R && pos_ok && c < nv;
+      cp_async16(sF + rr * Kp + c * 4, p.x_f32 + static_cast<int64_t>(valid ? row : 0) * p.ldx + pos_off + (valid ? c * 4 : 0),
+                 valid ? 16 : 0);
+    }
+  } else {   // unaligned rows: element-wise
+    for (int i = threadIdx.x; i < kSlRows * Kp; i += kSlThreads) {
       const int rr = i / Kp, k = i - rr * Kp;
       const int row = r0 + rr;
       const bool valid = row < p.R && pos_ok && k < p.K;
       const int64_t off = static_cast<int64_t>(valid ? row : 0) * p.ldx + pos_off + (valid ? k : 0);
-      __nv_bfloat16 h = __float2bfloat16(0.f);
-      if (valid) h = p.x_bf16 ? static_cast<const __nv_bfloat16*>(p.x_bf16)[off] : __float2bfloat16(p.x_f32[off]);
-      reinterpret_cast<__nv_bfloat16*>(sl_smem + rr * row_bytes)[k] = h;
-      if (p.xn_bf16 && blockIdx.x == 0 && valid) static_cast<__nv_bfloat16*>(p.xn_bf16)[static_cast<int64_t>(row) * p.K + k] = h;
+      if (p.x_bf16)
+        reinterpret_cast<__nv_bfloat16*>(sl_smem + rr * row_bytes)[k] =
+            valid ? static_cast<const __nv_bfloat16*>(p.x_bf16)[off] : __float2bfloat16(0.f);
+      else
+        sF[rr * Kp + k] = valid ? p.x_f32[off] : 0.f;
     }
   }
   cp_async_wait_all();
   __syncthreads();
+  if (p.x_f32) {   // fp32 rows in shared memory -> (LayerNorm) -> bf16 operand rows
+    __shared__ float2 s_stat[kSlRows];   // (mean, rstd) per row
+    if (p.ln_g) {   // two-pass statistics, as torch.nn.functional.layer_norm: one warp per row, 2 rows per warp
+      const float inv_k = 1.f / static_cast<float>(p.K);
+      for (int rr = warp; rr < kSlRows; rr += kSlWarps) {
+        const float* src = sF + rr * Kp;
+        float sum = 0.f;
+        for (int k = lane; k < p.K; k += 32) sum += src[k];
+        const float mean = warp_sum(sum) * inv_k;
+        float q = 0.f;
+        for (int k = lane; k < p.K; k += 32) {
+          const float d = src[k] - mean;
+          q = fmaf(d, d, q);
+        }
+        const float rstd = rsqrtf(warp_sum(q) * inv_k + p.eps);
+        if (lane == 0) s_stat[rr] = make_float2(mean, rstd);
+      }
+      __syncthreads();
+    }
+    // element pairs, flattened over the tile: thread t takes pair columns t % (Kp/2) of rows t / (Kp/2), ...
+    const int hp = Kp >> 1;
+    int rr = threadIdx.x / hp, c = threadIdx.x - rr * hp;
+    const int drow = kSlThreads / hp, dcol = kSlThreads - drow * hp;
+    while (rr < kSlRows) {
+      const int k = 2 * c;
+      float2 v = *reinterpret_cast<const float2*>(sF + rr * Kp + k);
+      if (p.ln_g && k < p.K) {   // (K is even: checked on the host for LayerNorm inputs)
+        const float2 st = s_stat[rr];
+        const float2 gg = __ldg(reinterpret_cast<const float2*>(p.ln_g + k)), bb = __ldg(reinterpret_cast<const float2*>(p.ln_b + k));
+        v.x = fmaf((v.x - st.x) * st.y, gg.x, bb.x);
+        v.y = fmaf((v.y - st.x) * st.y, gg.y, bb.y);
+      }
+      const __nv_bfloat162 h = __floats2bfloat162_rn(v.x, v.y);
+      *reinterpret_cast<__nv_bfloat162*>(sl_smem + rr * row_bytes + k * 2) = h;
+      const int row = r0 + rr;
+      if (p.xn_bf16 && blockIdx.x == 0 && row < p.R && k < p.K)
+        *reinterpret_cast<__nv_bfloat162*>(static_cast<__nv_bfloat16*>(p.xn_bf16) + static_cast<int64_t>(row) * p.K + k) = h;
+      rr += drow;
+      c += dcol;
+      if (c >= hp) {
+        c -= hp;
+        ++rr;
+      }
+    }
+    __syncthreads();
+  }
 
-  // ---- 16 x 8 outputs per warp; contraction index permuted: lane (g, tq) takes physical k = 32 kb + 8 tq + [0, 8) of W
-  // row n0 + g as the B fragments of two k-steps, and the same physical k of x rows g, g + 8 as the A fragments ----
-  if (n0 >= p.N) return;
+  // ---- 16 x 8 outputs per column group; contraction index permuted: lane (g, tq) takes physical k = 32 kb + 8 tq + [0, 8)
+  // of W row n0 + g as the B fragments of two k-steps, and the same physical k of x rows g, g + 8 as the A fragments;
+  // k-slice ks takes k-blocks ks, ks + 4, ... ----
   const uint8_t* xa = sl_smem + g * row_bytes + tq * 16;
   const uint8_t* xb = xa + 8 * row_bytes;
-  const uint8_t* wa = sW + (warp * 8 + g) * row_bytes + tq * 16;
+  const uint8_t* wa = sW + (cgp * 8 + g) * row_bytes + tq * 16;
   float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll 4
-  for (int kb = 0; kb < nkb; ++kb) {
+  for (int kb = ks; kb < nkb; kb += kSlKSlices) {
     const uint4 a = *reinterpret_cast<const uint4*>(xa + kb * 64);
     const uint4 b = *reinterpret_cast<const uint4*>(xb + kb * 64);
     const uint4 w = *reinterpret_cast<const uint4*>(wa + kb * 64);
     mma_bf16_16816(acc, a.x, b.x, a.y, b.y, w.x, w.y);
     mma_bf16_16816(acc, a.z, b.z, a.w, b.w, w.z, w.w);
   }
+  if (ks > 0) {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) s_red[ks - 1][cgp][lane][e] = acc[e];
+  }
+  __syncthreads();
+  if (ks > 0 || n0 >= p.N) return;
+#pragma unroll
+  for (int q = 0; q < kSlKSlices - 1; ++q)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) acc[e] += s_red[q][cgp][lane][e];
 
   // ---- epilogue: c0,c1 = (row g, cols 2 tq, 2 tq + 1); c2,c3 = (row g + 8, same cols) ----
 #pragma unroll
@@ -222,9 +248,9 @@ small_linear_kernel(const ttsb200_small_linear_args p) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// attn_decode: grid (H, R), 256 threads.  Models/modules.py:7-21 for one query row.
+// attn_decode: grid (H, R), 512 threads.  Models/modules.py:7-21 for one query row.
 // ------------------------------------------------------------------------------------------------
-constexpr int kAdThreads = 256;
+constexpr int kAdThreads = 512;
 
 template <int DH>
 __global__ void __launch_bounds__(kAdThreads)
@@ -302,7 +328,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, int64_t ldq, const __nv_
   const int grp = tid / VEC, vi = tid - grp * VEC;
   float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   if (grp < GROUPS) {
-    constexpr int UV = 4;   // value rows in flight per thread
+    constexpr int UV = 8;   // value rows in flight per thread
     for (int j0 = grp; j0 < n; j0 += GROUPS * UV) {
       uint4 vv[UV];
       float pj[UV];
@@ -359,17 +385,21 @@ extern "C" int ttsb200_small_linear(const ttsb200_small_linear_args* a, ttsb200_
                  static_cast<long long>(p.ldw), p.K);
   TTSB_CHECK_ARG((p.ln_g == nullptr) == (p.ln_b == nullptr) && (!p.ln_g || p.x_f32), "small_linear: LayerNorm needs ln_g, ln_b and x_f32");
   TTSB_CHECK_ARG(!p.xn_bf16 || p.x_f32, "small_linear: xn_bf16 needs x_f32");
-  TTSB_CHECK_ARG(!p.ln_g || p.K <= 512, "small_linear: LayerNorm rows of at most 512 columns (K = %d)", p.K);
+  TTSB_CHECK_ARG(!(p.ln_g || p.xn_bf16) || (p.K % 2 == 0 && (reinterpret_cast<uintptr_t>(p.ln_g) & 7) == 0 &&
+                                            (reinterpret_cast<uintptr_t>(p.ln_b) & 7) == 0 &&
+                                            (reinterpret_cast<uintptr_t>(p.xn_bf16) & 3) == 0),
+                 "small_linear: LayerNorm / xn rows need an even K and 8-byte aligned ln_g, ln_b");
   TTSB_CHECK_ARG((p.add_row == nullptr) == (p.add_scale == nullptr), "small_linear: add_row and add_scale go together");
   TTSB_CHECK_ARG((!p.x_pos_stride && !p.out_pos_stride && !p.add_row) || p.pos, "small_linear: position-dependent addressing needs pos");
   TTSB_CHECK_ARG(!p.out_f32 || p.ldo >= p.N, "small_linear: ldo < N");
   TTSB_CHECK_ARG(!p.out_bf16 || p.ldob >= p.N, "small_linear: ldob < N");
-  const int smem = (dec::kSlRows + dec::kSlWarps * 8) * (Kp * 2 + dec::kSlPadBytes);   // x rows + this CTA's W rows
+  // x rows + this CTA's W rows (bf16, padded) + fp32 staging rows for fp32 inputs
+  const int smem = (dec::kSlRows + dec::kSlCols) * (Kp * 2 + dec::kSlPadBytes) + (p.x_f32 ? dec::kSlRows * Kp * 4 : 0);
   TTSB_CHECK_ARG(smem <= 200 * 1024, "small_linear: K = %d is too large", p.K);
   auto kern = dec::small_linear_kernel;
   TTSB_SMEM_OPT_IN(kern, 200 * 1024);
-  dim3 grid((p.N + dec::kSlWarps * 8 - 1) / (dec::kSlWarps * 8), (p.R + dec::kSlRows - 1) / dec::kSlRows);
-  TTSB_CHECK_CUDA(dec::launch_pdl(kern, grid, dim3(dec::kSlWarps * 32), smem, static_cast<cudaStream_t>(s), p));
+  dim3 grid((p.N + dec::kSlCols - 1) / dec::kSlCols, (p.R + dec::kSlRows - 1) / dec::kSlRows);
+  TTSB_CHECK_CUDA(dec::launch_pdl(kern, grid, dim3(dec::kSlThreads), smem, static_cast<cudaStream_t>(s), p));
   return TTSB_OK;
 }
 
