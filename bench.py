@@ -400,6 +400,68 @@ def latency_b1(model, hp, iters: int = 20):
             "launches_per_call": (lib.LAUNCH_COUNT - l0) // iters, "workload": "B=1, 64 phonemes, free-running, eager"}
 
 
+def ar_decode_record(cpu: bool, positions: int = 1000, batch: int = 16, phonemes: int = 128):
+    """BASELINE.json configs[4]: Transformer-TTS autoregressive inference with the incremental KV cache and the stop
+    token, batch 16, 1000 decoder positions (2000 frames at reduction rate 2).  Device time of `Transformer.generate`
+    (encoder + cross k|v projections + 1000 graph replays), inputs resident; `e2e` adds the H2D of the ids and the D2H of
+    the mel.  cpu_reference: the oracle evaluating the loop the REFERENCE's way (test.py:128-191: the whole prefix re-run
+    per step) on a bounded sample, the first `cpu_positions` positions of the same batch."""
+    import torch
+
+    from transformer_tts_b200 import build_transformer_tts, lib, synth
+
+    hp = synth.make_tts_hp()
+    sd = synth.synth_tts_state_dict(hp)
+    model = build_transformer_tts(hp).eval()
+    model.load_state_dict(sd)
+    model = model.cuda()
+    text, pos, _ = synth.synth_text_batch(batch, phonemes, ragged=True, seed=77, min_len=phonemes // 2)
+    text_h, mask_h = text.pin_memory(), (pos != 0).unsqueeze(-2).pin_memory()
+    text_d, mask_d = text_h.cuda(), mask_h.cuda()
+    model.generate(text_d, mask_d, max_steps=32)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ts, te = [], []
+    for _ in range(3):
+        l0 = lib.LAUNCH_COUNT
+        e0.record()
+        out = model.generate(text_d, mask_d, max_steps=positions)
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+        launches = lib.LAUNCH_COUNT - l0
+        t0 = time.perf_counter()
+        o2 = model.generate(text_h.cuda(non_blocking=True), mask_h.cuda(non_blocking=True), max_steps=positions)
+        mel_host = o2["mel"].cpu()
+        te.append(1e3 * (time.perf_counter() - t0))
+    ms, ems = min(ts), min(te)
+    frames = batch * positions * hp.reduction_rate
+    rec = {"metric": "transformer_tts_ar_mel_frames_per_sec", "value": frames / ms * 1e3, "unit": "frames/s",
+           "ms_total": ms, "us_per_position": ms / positions * 1e3, "batch": batch, "phonemes": phonemes,
+           "positions": positions, "reduction_rate": hp.reduction_rate, "frames": frames,
+           "launches_per_position": model.last_state.launches_per_step, "gpu_launches": launches,
+           "e2e": {"value": frames / ems * 1e3, "unit": "frames/s", "ms_total": ems,
+                   "h2d_bytes": int(text_h.numel() * 8 + mask_h.numel()), "d2h_bytes": int(mel_host.numel() * 4)},
+           "stop_positions_rank0": [int(v) for v in out["stop_step"].cpu()],
+           "what": "Transformer.generate: KV-cache decode, one CUDA graph replay (small_linear / attn_decode kernels, programmatic "
+                   "dependent launch) per position; random-init weights, so the stop token fires at random: all positions are decoded"}
+    if cpu:
+        from oracle import transformer_tts_oracle as T
+
+        n_cpu = 32
+        torch.set_num_threads(os.cpu_count() or 1)
+        with torch.no_grad():
+            T.greedy_decode(sd, vars(hp), text[:, :], pos, 2)
+            t0 = time.perf_counter()
+            T.greedy_decode(sd, vars(hp), text, pos, n_cpu)
+            dt = time.perf_counter() - t0
+        rec["cpu_reference"] = {"value": batch * n_cpu * hp.reduction_rate / dt, "unit": "frames/s", "cores": os.cpu_count(),
+                                "kind": "port", "seconds": dt,
+                                "sample": f"the reference's loop (whole prefix re-run per step) for the FIRST {n_cpu} positions of the "
+                                          f"same batch; its cost per step grows with the prefix, so 1000 positions are slower than this rate"}
+    return rec
+
+
 def train_record(args, rank: int, world: int, steps: int = 5):
     """BASELINE.json configs[2] inside the default line: the data-parallel training step (fwd + bwd + NCCL all-reduce
     of the flat gradient buffer + SyncBatchNorm + fused RAdam), 32 utterances per GPU, so the driver's 1/2/4/8 scaling
@@ -585,6 +647,9 @@ def ours(args):
     del out_h
     torch.cuda.empty_cache()
     trn = None if (args.no_train_record or args.step_only) else train_record(args, rank, world)
+    ar = None
+    if rank == 0 and not (args.step_only or args.no_ar_record):   # configs[4]; one GPU's batch (utterances are independent)
+        ar = ar_decode_record(cpu=world == 1 and not args.no_cpu_baseline)
     cpu = None
     if rank == 0 and world == 1 and not (args.no_cpu_baseline or args.step_only):
         r = cpu_oracle_run(3, 1, sample_b=B_PER_GPU)
@@ -617,7 +682,7 @@ def ours(args):
                 # the same step in the other precision modes: fp32 = that predictor chain runs to fp32 accuracy so its
                 # discrete decisions (durations / pitch-energy buckets) equal the fp32 reference's; bf16 = plain bf16
                 "other_precision_modes": modes,
-                "torch_eager_b200": eager, "latency_b1": lat, "train": trn, "cpu_baseline": cpu}
+                "torch_eager_b200": eager, "latency_b1": lat, "train": trn, "tts_ar_decode": ar, "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -741,13 +806,14 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-eager-baseline", action="store_true", help="skip the torch_eager_b200 sub-record")
     ap.add_argument("--no-train-record", action="store_true", help="skip the training-step sub-record")
+    ap.add_argument("--no-ar-record", action="store_true", help="skip the Transformer-TTS autoregressive decode sub-record")
     ap.add_argument("--step-only", action="store_true",
                     help="only the timed steps (no per-kernel rooflines, latency, other modes, baselines): for ncu launch lists")
     ap.add_argument("--duration-precision", default="fp32", choices=["fp32", "bf16"],
                     help="fp32 (default): durations equal the fp32 reference's; bf16: the faster chain (SURVEY F9)")
     ap.add_argument("--variance-precision", default="fp32", choices=["fp32", "bf16"],
                     help="fp32 (default): pitch / energy buckets equal the fp32 reference's too (needs fp32 durations)")
-    ap.add_argument("--workload", default="infer", choices=["infer", "train"])
+    ap.add_argument("--workload", default="infer", choices=["infer", "train", "ar"])
     ap.add_argument("--train-batch", type=int, default=32)
     ap.add_argument("--overlap", action="store_true",
                     help="train: overlapped tail/head gradient exchange instead of one all-reduce after the backward")
@@ -759,6 +825,8 @@ def main():
         reference_arm(args)
     elif args.workload == "train":
         train(args)
+    elif args.workload == "ar":   # BASELINE.json configs[4] alone (one GPU)
+        print(json.dumps(ar_decode_record(cpu=not args.no_cpu_baseline)), flush=True)
     else:
         ours(args)
 

@@ -439,6 +439,15 @@ int ttsb200_attn_decode(const void* q_bf16, int64_t ldq, const void* knew_bf16, 
                         const int32_t* pos, const int32_t* kv_len, void* ctx_bf16, int64_t ldc, int32_t R, int32_t H,
                         int32_t Dh, int32_t cap, ttsb200_stream_t stream);
 
+/* FeedForward tail of a decoder block for a few rows (Models/modules.py:85-87, Models/layers.py:122) and the NEXT
+ * LayerNorm (norm_1 of the following block, Models/layers.py:110, or Models/decoder.py:56):
+ *   z = y + LayerNorm(u + yn; ln1);  zn = bf16(LayerNorm(z; ln2))
+ * u = conv2 output + bias (fp32), yn = the FeedForward's input rows (bf16), y = the residual stream (fp32); (R, D) dense,
+ * D = 384.  The arithmetic of ttsb200_ffn2_tail, as a member of the step's programmatic-dependent-launch chain. */
+int ttsb200_ffn_tail_rows(const float* u, const void* yn_bf16, const float* y, const float* ln1_g, const float* ln1_b,
+                          const float* ln2_g, const float* ln2_b, float eps, float* z, void* zn_bf16, int32_t R,
+                          int32_t D, ttsb200_stream_t stream);
+
 /* *pos += delta (the last node of a captured decode step). */
 int ttsb200_advance_pos(int32_t* pos, int32_t delta, ttsb200_stream_t stream);
 

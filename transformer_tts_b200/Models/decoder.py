@@ -96,8 +96,12 @@ class DecodeState:
                          add_scale=t["alpha"], out_f32=self.x, pos=pos)
         x, x2 = self.x, self.x2
         sb, sh, sj = H * cap * Dh, cap * Dh, Dh
+        n_layers = len(t["layers"])
         for i, lc in enumerate(t["layers"]):
-            lib.small_linear(lc["wqkv1"], lc["bqkv1"], D, x_f32=x, ln=lc["ln1"], out_bf16=self.qkv)
+            if i == 0:
+                lib.small_linear(lc["wqkv1"], lc["bqkv1"], D, x_f32=x, ln=lc["ln1"], out_bf16=self.qkv)
+            else:      # norm_1 of this block was applied by the previous block's FeedForward tail
+                lib.small_linear(lc["wqkv1"], lc["bqkv1"], D, x_bf16=self.zn, out_bf16=self.qkv)
             lib.attn_decode(self.qkv, 0, 3 * D, self.kv_self[i], R * sb, (sb, sh, sj), cap, H, Dh, self.ctx,
                             kv_new=self.qkv, knew_off=D, vnew_off=2 * D, pos=pos, kv_len=self.trg_len)
             lib.small_linear(lc["wo1"], lc["bo1"], D, x_bf16=self.ctx, res_f32=x, out_f32=x2)
@@ -107,10 +111,12 @@ class DecodeState:
             lib.small_linear(lc["wo2"], lc["bo2"], D, x_bf16=self.ctx, res_f32=x2, out_f32=x)
             lib.small_linear(lc["w1"], lc["b1"], D, x_f32=x, ln=lc["ln3"], relu=True, out_bf16=self.hid, xn_bf16=self.xn)
             lib.small_linear(lc["w2"], lc["b2"], 4 * D, x_bf16=self.hid, out_f32=self.u)
-            # x2 = x + LN_ff(u + LN3(x))  (modules.py:85-87, layers.py:122); zn (the next LayerNorm) is not used here
-            lib.ffn2_tail(self.u, self.xn, x, lc["ln_ff"], t["ident"], E.LN_EPS, x2, self.zn)
+            # x2 = x + LN_ff(u + LN3(x))  (modules.py:85-87, layers.py:122); zn = the NEXT LayerNorm of x2: norm_1 of the
+            # following block (layers.py:110) or the decoder's final norm (decoder.py:56)
+            next_ln = t["layers"][i + 1]["ln1"] if i + 1 < n_layers else t["norm"]
+            lib.ffn_tail_rows(self.u, self.xn, x, lc["ln_ff"], next_ln, E.LN_EPS, x2, self.zn)
             x, x2 = x2, x
-        lib.small_linear(self.head["w"], self.head["b"], D, x_f32=x, ln=t["norm"], out_f32=self.out_all,
+        lib.small_linear(self.head["w"], self.head["b"], D, x_bf16=self.zn, out_f32=self.out_all,
                          ldo=cap * self.n_out, pos=pos, out_pos_stride=self.n_out)
         lib.advance_pos(pos, 1)
 

@@ -107,6 +107,13 @@ small_linear_kernel(const ttsb200_small_linear_args p) {
   const int n0 = blockIdx.x * kSlCols + cgp * 8;
   const int g = lane >> 2, tq = lane & 3;
   const int nkb = Kp >> 5;
+  // epilogue operands of this lane's two columns: bias is immutable (loaded now), the residual after the wait
+  const int ncol = n0 + tq * 2;
+  float bias_v[2] = {0.f, 0.f};
+  if (ks == 0 && p.bias) {
+    if (ncol < p.N) bias_v[0] = __ldg(p.bias + ncol);
+    if (ncol + 1 < p.N) bias_v[1] = __ldg(p.bias + ncol + 1);
+  }
   pdl_wait();
   const int pos = p.pos ? *reinterpret_cast<const volatile int32_t*>(p.pos) : 0;
   const int xpos = pos + p.x_pos_bias;   // index of the step the input rows were produced at (negative: zeros)
@@ -149,6 +156,16 @@ small_linear_kernel(const ttsb200_small_linear_args p) {
             valid ? static_cast<const __nv_bfloat16*>(p.x_bf16)[off] : __float2bfloat16(0.f);
       else
         sF[rr * Kp + k] = valid ? p.x_f32[off] : 0.f;
+    }
+  }
+  float res_v[4] = {0.f, 0.f, 0.f, 0.f};   // in flight together with the input rows
+  if (ks == 0 && p.res_f32) {
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const int row = r0 + g + half * 8;
+#pragma unroll
+      for (int e = 0; e < 2; ++e)
+        if (row < p.R && ncol + e < p.N) res_v[half * 2 + e] = p.res_f32[static_cast<int64_t>(row) * p.ldres + ncol + e];
     }
   }
   cp_async_wait_all();
@@ -235,10 +252,9 @@ small_linear_kernel(const ttsb200_small_linear_args p) {
     for (int e = 0; e < 2; ++e) {
       const int n = n0 + tq * 2 + e;
       if (n >= p.N) continue;
-      float v = acc[half * 2 + e];
-      if (p.bias) v += __ldg(p.bias + n);
+      float v = acc[half * 2 + e] + bias_v[e];
       if (p.relu) v = fmaxf(v, 0.f);
-      if (p.res_f32) v += p.res_f32[static_cast<int64_t>(row) * p.ldres + n];
+      v += res_v[half * 2 + e];
       if (p.add_row) v = fmaf(__ldg(p.add_scale), __ldg(p.add_row + static_cast<int64_t>(pos) * p.N + n), v);
       const int64_t opos = p.out_pos_stride ? static_cast<int64_t>(pos) * p.out_pos_stride : 0;
       if (p.out_f32) p.out_f32[static_cast<int64_t>(row) * p.ldo + opos + n] = v;
@@ -362,6 +378,56 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, int64_t ldq, const __nv_
   }
 }
 
+// FeedForward tail of a decoder block for a few rows (Models/modules.py:85-87, Models/layers.py:122, then the NEXT
+// LayerNorm: norm_1 of the following block, Models/layers.py:110, or the decoder's final norm, Models/decoder.py:56):
+//   z = y + LN(u + yn; ln1);  zn = bf16(LN(z; ln2))      one warp per row, D = 384
+// Same arithmetic as ttsb200_ffn2_tail; this one takes part in the programmatic-dependent-launch chain of the step.
+__global__ void __launch_bounds__(512)
+ffn_tail_rows_kernel(const float* __restrict__ u, const __nv_bfloat16* __restrict__ yn, const float* __restrict__ y,
+                     const float* __restrict__ g1, const float* __restrict__ b1, const float* __restrict__ g2,
+                     const float* __restrict__ b2, float eps, float* __restrict__ z, __nv_bfloat16* __restrict__ zn, int R) {
+  constexpr int D = 384, NV = D / 32;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 16 + warp;
+  pdl_launch_dependents();
+  float ga[NV], ba[NV], gb[NV], bb[NV];
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {   // LayerNorm parameters are immutable: loaded before the wait
+    const int k = lane + 32 * j;
+    ga[j] = __ldg(g1 + k); ba[j] = __ldg(b1 + k); gb[j] = __ldg(g2 + k); bb[j] = __ldg(b2 + k);
+  }
+  pdl_wait();
+  if (row >= R) return;
+  float v[NV], yy[NV];
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    const int64_t o = static_cast<int64_t>(row) * D + lane + 32 * j;
+    v[j] = u[o] + __bfloat162float(yn[o]);
+    yy[j] = y[o];
+  }
+  auto stats = [&](const float* a, float& mean, float& rstd) {   // two-pass, as torch
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) s += a[j];
+    mean = warp_sum(s) * (1.f / D);
+    float q = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) q = fmaf(a[j] - mean, a[j] - mean, q);
+    rstd = rsqrtf(warp_sum(q) * (1.f / D) + eps);
+  };
+  float mean, rstd;
+  stats(v, mean, rstd);
+#pragma unroll
+  for (int j = 0; j < NV; ++j) v[j] = yy[j] + fmaf((v[j] - mean) * rstd, ga[j], ba[j]);
+  stats(v, mean, rstd);
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    const int64_t o = static_cast<int64_t>(row) * D + lane + 32 * j;
+    z[o] = v[j];
+    zn[o] = __float2bfloat16(fmaf((v[j] - mean) * rstd, gb[j], bb[j]));
+  }
+}
+
 __global__ void advance_pos_kernel(int32_t* pos, int32_t delta) {
   pdl_launch_dependents();
   pdl_wait();
@@ -424,6 +490,17 @@ extern "C" int ttsb200_attn_decode(const void* q_bf16, int64_t ldq, const void* 
                                   static_cast<const __nv_bfloat16*>(vnew_bf16), ldkv, static_cast<__nv_bfloat16*>(k_cache),
                                   static_cast<__nv_bfloat16*>(v_cache), pos, kv_len, static_cast<__nv_bfloat16*>(ctx_bf16),
                                   ldc, static_cast<int>(cap), kv_stride_b, kv_stride_h, kv_stride_j));
+  return TTSB_OK;
+}
+
+extern "C" int ttsb200_ffn_tail_rows(const float* u, const void* yn_bf16, const float* y, const float* ln1_g,
+                                     const float* ln1_b, const float* ln2_g, const float* ln2_b, float eps, float* z,
+                                     void* zn_bf16, int32_t R, int32_t D, ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(u && yn_bf16 && y && ln1_g && ln1_b && ln2_g && ln2_b && z && zn_bf16 && R > 0, "ffn_tail_rows: bad args");
+  TTSB_CHECK_ARG(D == 384, "ffn_tail_rows: D = %d unsupported (384)", D);
+  TTSB_CHECK_CUDA(dec::launch_pdl(dec::ffn_tail_rows_kernel, dim3((R + 15) / 16), dim3(512), 0, static_cast<cudaStream_t>(s),
+                                  u, static_cast<const __nv_bfloat16*>(yn_bf16), y, ln1_g, ln1_b, ln2_g, ln2_b, eps, z,
+                                  static_cast<__nv_bfloat16*>(zn_bf16), static_cast<int>(R)));
   return TTSB_OK;
 }
 

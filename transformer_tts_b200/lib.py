@@ -68,6 +68,7 @@ _SIGNATURES = {
                              C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
                              C.c_int32, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_advance_pos": ([C.c_void_p, C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_ffn_tail_rows": ([C.c_void_p] * 7 + [C.c_float, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_ffn_fused": ([C.c_void_p] * 10 + [C.c_float, C.c_void_p, C.c_void_p] + [C.c_int32] * 4 + [C.c_void_p] * 3, C.c_int),
     "ttsb200_build_tile_map": ([C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
                                 C.c_void_p], C.c_int),
@@ -757,4 +758,15 @@ def attn_decode(q: torch.Tensor, q_off: int, ldq: int, k: torch.Tensor, v_off: i
 
 def advance_pos(pos: torch.Tensor, delta: int = 1) -> None:
     _check(load().ttsb200_advance_pos(_ptr(pos, torch.int32, "pos"), delta, _stream()), "advance_pos")
+    _count()
+
+
+def ffn_tail_rows(u, yn, y, ln1, ln2, eps, z, zn) -> None:
+    """z = y + LN(u + yn; ln1); zn = bf16(LN(z; ln2)) for the rows of a decode step (see ttsb200_ffn_tail_rows)."""
+    R, D = u.shape
+    _check(load().ttsb200_ffn_tail_rows(_ptr(u, torch.float32, "u"), _ptr(yn, torch.bfloat16, "yn"), _ptr(y, torch.float32, "y"),
+                                        _ptr(ln1[0], torch.float32, "ln1_g"), _ptr(ln1[1], torch.float32, "ln1_b"),
+                                        _ptr(ln2[0], torch.float32, "ln2_g"), _ptr(ln2[1], torch.float32, "ln2_b"), eps,
+                                        _ptr(z, torch.float32, "z"), _ptr(zn, torch.bfloat16, "zn"), R, D, _stream()),
+           "ffn_tail_rows")
     _count()
