@@ -134,6 +134,52 @@ def test_attn_decode_self_and_cross_match_fp64():
         assert rel(ctx[r], (pr @ v).reshape(D)) < 4e-3, r
 
 
+@pytest.mark.parametrize("R", [16, 5, 20])
+def test_cluster_kernels_match_the_unfused_step_kernels(R):
+    """decode_attn_out_q / decode_ffn_block (one 16-CTA cluster per 16 rows, slices exchanged through distributed shared
+    memory) against the chain of small_linear / ffn_tail_rows launches they replace: same operands, same arithmetic up to
+    the order of the k-slice partial sums."""
+    from transformer_tts_b200 import lib
+
+    g = torch.Generator().manual_seed(100 + R)
+    D, Hd = 384, 1536
+    rnd = lambda *s, sc=1.0: (torch.randn(*s, generator=g) * sc).to(DEV)   # noqa: E731
+    ctx = rnd(R, D).to(torch.bfloat16)
+    x = rnd(R, D)
+    wo, wq, w1, w2 = (lib.pad_weight_rows(rnd(D, D, sc=D ** -0.5)), lib.pad_weight_rows(rnd(D, D, sc=D ** -0.5)),
+                      lib.pad_weight_rows(rnd(Hd, D, sc=D ** -0.5)), lib.pad_weight_rows(rnd(D, Hd, sc=Hd ** -0.5)))
+    bo, bq, b1, b2 = rnd(D, sc=0.1), rnd(D, sc=0.1), rnd(Hd, sc=0.1), rnd(D, sc=0.1)
+    ln = lambda: (1 + 0.1 * rnd(D), 0.1 * rnd(D))   # noqa: E731
+    ln2, ln3, lnff, lnn = ln(), ln(), ln(), ln()
+    f32 = lambda: torch.empty(R, D, device=DEV)   # noqa: E731
+    bf = lambda n=D: torch.empty(R, n, device=DEV, dtype=torch.bfloat16)   # noqa: E731
+    # attention output projection + residual, LayerNorm, query projection
+    x2_ref, q_ref = f32(), bf()
+    lib.small_linear(wo, bo, D, x_bf16=ctx, res_f32=x, out_f32=x2_ref)
+    lib.small_linear(wq, bq, D, x_f32=x2_ref, ln=ln2, out_bf16=q_ref)
+    x2, q = f32(), bf()
+    lib.decode_attn_out_q(ctx, x, wo, bo, ln2, wq, bq, 1e-5, x2, q)
+    torch.cuda.synchronize()
+    assert rel(x2, x2_ref) < 1e-6 and rel(q, q_ref) < 2e-3          # q: bf16 roundings of values that differ in the last fp32 bits
+    # second attention's output projection, FeedForward, next LayerNorm
+    x3_ref, hid, xn, u, z_ref, zn_ref = f32(), bf(Hd), bf(), f32(), f32(), bf()
+    lib.small_linear(wo, bo, D, x_bf16=ctx, res_f32=x, out_f32=x3_ref)
+    lib.small_linear(w1, b1, D, x_f32=x3_ref, ln=ln3, relu=True, out_bf16=hid, xn_bf16=xn)
+    lib.small_linear(w2, b2, Hd, x_bf16=hid, out_f32=u)
+    lib.ffn_tail_rows(u, xn, x3_ref, lnff, lnn, 1e-5, z_ref, zn_ref)
+    x3, z, zn = f32(), f32(), bf()
+    lib.decode_ffn_block(ctx, x, wo, bo, ln3, w1, b1, w2, b2, lnff, lnn, 1e-5, x3, z, zn)
+    torch.cuda.synchronize()
+    assert rel(x3, x3_ref) < 1e-6
+    assert rel(z, z_ref) < 2e-3 and rel(zn, zn_ref) < 4e-3          # a hidden value on a bf16 rounding boundary may flip
+    # and against fp64 on the same bf16 operands
+    xd = x.double() + ctx.double() @ wo.double().T + bo.double()
+    xnd = F.layer_norm(xd, (D,), ln3[0].double(), ln3[1].double(), 1e-5).to(torch.bfloat16).double()
+    hd = torch.relu(xnd @ w1.double().T + b1.double()).to(torch.bfloat16).double()
+    zd = xd + F.layer_norm(hd @ w2.double().T + b2.double() + xnd, (D,), lnff[0].double(), lnff[1].double(), 1e-5)
+    assert rel(z, zd) < 2e-3
+
+
 # ---------------------------------------------------------------------------------------------------------------------
 # model
 # ---------------------------------------------------------------------------------------------------------------------
@@ -218,6 +264,26 @@ def test_cfg5_1000_positions_batch16_vs_oracle(world):
     p_or = torch.sigmoid(f["stop_logits"]).mean(-1)
     safe = ((p_or - 0.5).abs() > 1e-3).all(dim=1)
     assert torch.equal(out["stop_step"].cpu()[safe], f["stop_step"][safe])
+
+
+def test_cluster_and_unfused_decode_steps_agree(world):
+    from transformer_tts_b200 import synth
+
+    hp, sd, model = world
+    text, pos, _ = synth.synth_text_batch(16, 40, ragged=True, seed=55)
+    src_mask = (pos != 0).unsqueeze(-2).cuda()
+    assert model.decoder.use_cluster_kernels
+    a = model.generate(text.cuda(), src_mask, max_steps=30)
+    launches_cluster = model.last_state.launches_per_step
+    model.decoder.use_cluster_kernels = False
+    try:
+        b = model.generate(text.cuda(), src_mask, max_steps=30)
+        launches_unfused = model.last_state.launches_per_step
+    finally:
+        model.decoder.use_cluster_kernels = True
+    e = rel(a["mel"], b["mel"])
+    print(f"cluster kernels ({launches_cluster} launches per position) vs unfused ({launches_unfused}): mel rel-L2 {e:.2e}")
+    assert launches_cluster < launches_unfused and e < 1e-2      # free-running: both are within 5e-3 of the oracle
 
 
 def test_generate_early_exit_on_stop(world):

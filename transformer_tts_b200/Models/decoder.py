@@ -104,6 +104,18 @@ class DecodeState:
                 lib.small_linear(lc["wqkv1"], lc["bqkv1"], D, x_bf16=self.zn, out_bf16=self.qkv)
             lib.attn_decode(self.qkv, 0, 3 * D, self.kv_self[i], R * sb, (sb, sh, sj), cap, H, Dh, self.ctx,
                             kv_new=self.qkv, knew_off=D, vnew_off=2 * D, pos=pos, kv_len=self.trg_len)
+            # zn = the NEXT LayerNorm of the block's output: norm_1 of the following block (layers.py:110) or the decoder's
+            # final norm (decoder.py:56)
+            next_ln = t["layers"][i + 1]["ln1"] if i + 1 < n_layers else t["norm"]
+            if self.dec.use_cluster_kernels:
+                # 5 launches per block: the stretches between the attentions run as ONE 16-CTA cluster kernel each
+                # (csrc/decode_cluster.cu): result slices are exchanged through distributed shared memory
+                lib.decode_attn_out_q(self.ctx, x, lc["wo1"], lc["bo1"], lc["ln2"], lc["wq2"], lc["bq2"], E.LN_EPS, x2, self.q2)
+                lib.attn_decode(self.q2, 0, D, self.kv_cross[i], D, (self.L * 2 * D, Dh, 2 * D), self.L, H, Dh, self.ctx,
+                                kv_len=self.src_len)
+                lib.decode_ffn_block(self.ctx, x2, lc["wo2"], lc["bo2"], lc["ln3"], lc["w1"], lc["b1"], lc["w2"], lc["b2"],
+                                     lc["ln_ff"], next_ln, E.LN_EPS, self.u, x, self.zn)
+                continue
             lib.small_linear(lc["wo1"], lc["bo1"], D, x_bf16=self.ctx, res_f32=x, out_f32=x2)
             lib.small_linear(lc["wq2"], lc["bq2"], D, x_f32=x2, ln=lc["ln2"], out_bf16=self.q2)
             lib.attn_decode(self.q2, 0, D, self.kv_cross[i], D, (self.L * 2 * D, Dh, 2 * D), self.L, H, Dh, self.ctx,
@@ -111,9 +123,7 @@ class DecodeState:
             lib.small_linear(lc["wo2"], lc["bo2"], D, x_bf16=self.ctx, res_f32=x2, out_f32=x)
             lib.small_linear(lc["w1"], lc["b1"], D, x_f32=x, ln=lc["ln3"], relu=True, out_bf16=self.hid, xn_bf16=self.xn)
             lib.small_linear(lc["w2"], lc["b2"], 4 * D, x_bf16=self.hid, out_f32=self.u)
-            # x2 = x + LN_ff(u + LN3(x))  (modules.py:85-87, layers.py:122); zn = the NEXT LayerNorm of x2: norm_1 of the
-            # following block (layers.py:110) or the decoder's final norm (decoder.py:56)
-            next_ln = t["layers"][i + 1]["ln1"] if i + 1 < n_layers else t["norm"]
+            # x2 = x + LN_ff(u + LN3(x))  (modules.py:85-87, layers.py:122)
             lib.ffn_tail_rows(self.u, self.xn, x, lc["ln_ff"], next_ln, E.LN_EPS, x2, self.zn)
             x, x2 = x2, x
         lib.small_linear(self.head["w"], self.head["b"], D, x_bf16=self.zn, out_f32=self.out_all,
@@ -169,6 +179,8 @@ class Decoder(nn.Module):
                                                      multi_speaker, spk_emb_dim))
         self.norm = nn.LayerNorm(d_model)
         self._ttsb_cache = E.Cache()
+        # the stretches between the attentions of a block as cluster kernels (5 launches per block instead of 9)
+        self.use_cluster_kernels = d_model == 384
 
     def _cache(self) -> dict:
         c = self._ttsb_cache

@@ -13,7 +13,7 @@ from pathlib import Path
 
 CSRC = Path(__file__).resolve().parent / "csrc"
 LIB_PATH = CSRC / "libttsb200.so"
-SOURCES = ["api.cu", "gemm.cu", "attention.cu", "rowwise.cu", "wgrad.cu", "train_rows.cu", "attention_bwd.cu", "precise.cu", "decode.cu"]
+SOURCES = ["api.cu", "gemm.cu", "attention.cu", "rowwise.cu", "wgrad.cu", "train_rows.cu", "attention_bwd.cu", "precise.cu", "decode.cu", "decode_cluster.cu"]
 HEADERS = [CSRC / "common.cuh", CSRC / "gemm_kernel.cuh", CSRC / "gemm_epilogue.inc", CSRC / "gemm_host.cuh", CSRC / "ffn_fused.cuh",
            CSRC.parent.parent / "include" / "ttsb200.h"]
 

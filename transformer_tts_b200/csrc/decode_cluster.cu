@@ -1,0 +1,451 @@
+// Transformer-TTS decode step, fused per sub-block with thread-block CLUSTERS.
+//
+// A decode step is a chain of dependent launches at a ~4.6 us floor each (csrc/decode.cu); the pieces between the two
+// attentions of a decoder block need full rows between them (LayerNorm, the 1536-wide hidden activation), which is what
+// forces a kernel boundary — unless the CTAs that hold the column slices can exchange them on chip.  Here ONE cluster of
+// 16 CTAs processes up to 16 rows (the batch): every CTA owns 1/16 of the output columns of each linear, keeps its slice
+// of every weight matrix in shared memory (cp.async, issued before the programmatic-dependent-launch wait: weights are
+// immutable), and PUSHES its slice of each result into the shared memory of all 16 CTAs (st.shared::cluster); a cluster
+// barrier replaces the kernel boundary.
+//
+//   attn_out_q : x' = x + ctx Wo^T + bo (Models/layers.py:112);  q = LN2(x') Wq^T + bq (layers.py:114-115, modules.py:50)
+//   ffn_block  : x' = x + ctx Wo^T + bo (layers.py:116);  h = relu(LN3(x') W1^T + b1);  u = h W2^T + b2;
+//                z = x' + LN_ff(u + LN3(x')) (layers.py:118-122, modules.py:81-87);  zn = bf16(LN_next(z))
+//
+// Arithmetic is that of the unfused kernels (bf16 operands, fp32 accumulation, fp32 residual stream, two-pass LayerNorm).
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "../../include/ttsb200.h"
+
+namespace ttsb {
+namespace dcl {
+
+constexpr int kCluster = 16;
+constexpr int kD = 384, kHid = 1536;
+constexpr int kRows = 16;
+constexpr int kThreads = 256, kWarps = 8;
+constexpr int kPad = 16;
+constexpr int kRbD = kD * 2 + kPad;        // padded bf16 row of 384: 784 bytes
+constexpr int kRbH = kHid * 2 + kPad;      // padded bf16 row of 1536: 3088 bytes
+constexpr int kColsD = kD / kCluster;      // 24 output columns per CTA of a 384-wide linear
+constexpr int kColsH = kHid / kCluster;    // 96 hidden columns per CTA
+
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc, int src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ void cluster_barrier() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t local_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void st_cluster_v4(uint32_t addr, uint4 v) {
+  asm volatile("st.shared::cluster.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void st_cluster_v2(uint32_t addr, uint2 v) {
+  asm volatile("st.shared::cluster.v2.u32 [%0], {%1, %2};" ::"r"(addr), "r"(v.x), "r"(v.y) : "memory");
+}
+__device__ __forceinline__ void mma_bf16_16816(float* c, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                               uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// this CTA's `rows` rows of a bf16 weight matrix [*][K] (K a multiple of 32) -> padded shared-memory rows
+__device__ __forceinline__ void load_w_slice(uint8_t* dst, int rb, const __nv_bfloat16* w, int64_t ldw, int row0, int rows, int K) {
+  const int nv = K >> 3;
+  for (int i = threadIdx.x; i < rows * nv; i += kThreads) {
+    const int r = i / nv, c = i - r * nv;
+    cp_async16(dst + r * rb + c * 16, w + static_cast<int64_t>(row0 + r) * ldw + c * 8, 16);
+  }
+}
+// R rows of a dense bf16 (R, 384) tensor -> the padded operand tile (rows >= R: zeros)
+__device__ __forceinline__ void load_rows_bf16(uint8_t* dst, const __nv_bfloat16* x, int r0, int R) {
+  constexpr int nv = kD >> 3;
+  for (int i = threadIdx.x; i < kRows * nv; i += kThreads) {
+    const int rr = i / nv, c = i - rr * nv;
+    const bool valid = r0 + rr < R;
+    cp_async16(dst + rr * kRbD + c * 16, x + static_cast<int64_t>(valid ? r0 + rr : 0) * kD + (valid ? c * 8 : 0), valid ? 16 : 0);
+  }
+}
+
+// Partial products of a [16 x K] . [K x 8 n_tiles] slice: task (n-tile, k-slice) -> red[ks][nt][lane][4].
+// Fragment convention and the permuted contraction index as in small_linear (csrc/decode.cu).
+template <int KS>
+__device__ __forceinline__ void slice_mma(const uint8_t* A, int a_rb, const uint8_t* W, int w_rb, int n_tiles, int nkb, float* red) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, tq = lane & 3;
+  for (int t = warp; t < n_tiles * KS; t += kWarps) {
+    const int nt = t % n_tiles, ks = t / n_tiles;
+    const uint8_t* xa = A + g * a_rb + tq * 16;
+    const uint8_t* xb = xa + 8 * a_rb;
+    const uint8_t* wa = W + (nt * 8 + g) * w_rb + tq * 16;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 4
+    for (int kb = ks; kb < nkb; kb += KS) {
+      const uint4 a = *reinterpret_cast<const uint4*>(xa + kb * 64);
+      const uint4 b = *reinterpret_cast<const uint4*>(xb + kb * 64);
+      const uint4 w = *reinterpret_cast<const uint4*>(wa + kb * 64);
+      mma_bf16_16816(acc, a.x, b.x, a.y, b.y, w.x, w.y);
+      mma_bf16_16816(acc, a.z, b.z, a.w, b.w, w.z, w.w);
+    }
+    *reinterpret_cast<float4*>(red + ((ks * n_tiles + nt) * 32 + lane) * 4) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+  }
+}
+// value of output element (row, col) of the slice from the KS partials
+template <int KS>
+__device__ __forceinline__ float slice_value(const float* red, int n_tiles, int row, int col) {
+  const int nt = col >> 3, c8 = col & 7;
+  const int lane = (row & 7) * 4 + (c8 >> 1), e = (row >> 3) * 2 + (c8 & 1);
+  float v = 0.f;
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks) v += red[((ks * n_tiles + nt) * 32 + lane) * 4 + e];
+  return v;
+}
+
+// LayerNorm of the 16 fp32 rows in sX (two-pass, as torch) -> bf16 operand tile; 2 rows per warp
+__device__ __forceinline__ void layernorm_rows(const float* sX, uint8_t* sA, const float* g, const float* b, float eps) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int NV = kD / 32;
+  float gg[NV], bb[NV];
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    gg[j] = __ldg(g + lane + 32 * j);
+    bb[j] = __ldg(b + lane + 32 * j);
+  }
+  for (int rr = warp; rr < kRows; rr += kWarps) {
+    float v[NV];
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      v[j] = sX[rr * kD + lane + 32 * j];
+      s += v[j];
+    }
+    const float mean = warp_sum(s) * (1.f / kD);
+    float q = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) q = fmaf(v[j] - mean, v[j] - mean, q);
+    const float rstd = rsqrtf(warp_sum(q) * (1.f / kD) + eps);
+    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(sA + rr * kRbD);
+#pragma unroll
+    for (int j = 0; j < NV; ++j) dst[lane + 32 * j] = __float2bfloat16(fmaf((v[j] - mean) * rstd, gg[j], bb[j]));
+  }
+}
+
+// out-projection slice: y[row][c0 + col] = ctx . Wo^T + bo + x  for this CTA's 24 columns; written to x_out (global) and
+// pushed into every CTA's sX.  `red` / `stage` are scratch (stage: 16 x 24 floats).
+__device__ __forceinline__ void out_proj_push(const uint8_t* sA0, const uint8_t* sWo, const float* bo, const float* x_in,
+                                              float* x_out, float* sX, float* red, float* stage, int r0, int R, uint32_t rank) {
+  slice_mma<2>(sA0, kRbD, sWo, kRbD, kColsD / 8, kD / 32, red);
+  __syncthreads();
+  const int c0 = rank * kColsD;
+  for (int i = threadIdx.x; i < kRows * kColsD; i += kThreads) {
+    const int row = i / kColsD, col = i - row * kColsD;
+    float v = 0.f;
+    if (r0 + row < R) {
+      v = slice_value<2>(red, kColsD / 8, row, col) + __ldg(bo + c0 + col) + x_in[static_cast<int64_t>(r0 + row) * kD + c0 + col];
+      x_out[static_cast<int64_t>(r0 + row) * kD + c0 + col] = v;
+    }
+    stage[i] = v;
+  }
+  __syncthreads();
+  // push: 16 rows x 24 floats = 16 x 6 float4 per target CTA
+  const uint32_t sx_addr = smem_u32(sX);
+  for (int i = threadIdx.x; i < kCluster * kRows * (kColsD / 4); i += kThreads) {
+    const int tgt = i / (kRows * (kColsD / 4)), j = i - tgt * (kRows * (kColsD / 4));
+    const int row = j / (kColsD / 4), q4 = j - row * (kColsD / 4);
+    const uint4 v = *reinterpret_cast<const uint4*>(stage + row * kColsD + q4 * 4);
+    st_cluster_v4(map_to_cta(sx_addr + (row * kD + c0 + q4 * 4) * 4, tgt), v);
+  }
+}
+
+struct AttnOutQ {
+  const __nv_bfloat16* ctx;
+  const float* x_in;
+  const __nv_bfloat16 *wo, *wq;
+  const float *bo, *bq, *ln_g, *ln_b;
+  float* x_out;
+  __nv_bfloat16* q_out;
+  float eps;
+  int R;
+};
+
+constexpr int kSmemA = 2 * kColsD * kRbD + 2 * kRows * kRbD + kRows * kD * 4 + 4096 + kRows * kColsD * 4;
+
+__global__ void __launch_bounds__(kThreads, 1) attn_out_q_kernel(const AttnOutQ p) {
+  extern __shared__ __align__(16) uint8_t sm[];
+  uint8_t* sWo = sm;
+  uint8_t* sWq = sWo + kColsD * kRbD;
+  uint8_t* sA0 = sWq + kColsD * kRbD;
+  uint8_t* sA1 = sA0 + kRows * kRbD;
+  float* sX = reinterpret_cast<float*>(sA1 + kRows * kRbD);
+  float* red = sX + kRows * kD;                 // 2 k-slices x 3 n-tiles x 128 floats = 3 KB (4 KB reserved)
+  float* stage = red + 1024;
+  const uint32_t rank = cluster_rank();
+  const int r0 = (blockIdx.x / kCluster) * kRows;
+  pdl_launch_dependents();
+  load_w_slice(sWo, kRbD, p.wo, kD, rank * kColsD, kColsD, kD);
+  load_w_slice(sWq, kRbD, p.wq, kD, rank * kColsD, kColsD, kD);
+  pdl_wait();
+  load_rows_bf16(sA0, p.ctx, r0, p.R);
+  cp_async_wait_all();
+  __syncthreads();
+  out_proj_push(sA0, sWo, p.bo, p.x_in, p.x_out, sX, red, stage, r0, p.R, rank);
+  cluster_barrier();                            // every CTA holds the 16 full rows of x'
+  layernorm_rows(sX, sA1, p.ln_g, p.ln_b, p.eps);
+  __syncthreads();
+  slice_mma<2>(sA1, kRbD, sWq, kRbD, kColsD / 8, kD / 32, red);
+  __syncthreads();
+  const int c0 = rank * kColsD;
+  for (int i = threadIdx.x; i < kRows * kColsD; i += kThreads) {
+    const int row = i / kColsD, col = i - row * kColsD;
+    if (r0 + row < p.R)
+      p.q_out[static_cast<int64_t>(r0 + row) * kD + c0 + col] =
+          __float2bfloat16(slice_value<2>(red, kColsD / 8, row, col) + __ldg(p.bq + c0 + col));
+  }
+  // (every push into this CTA's shared memory happened before the barrier above: it may exit on its own)
+}
+
+struct FfnBlock {
+  const __nv_bfloat16* ctx;
+  const float* x_in;
+  const __nv_bfloat16 *wo, *w1, *w2;
+  const float *bo, *b1, *b2, *ln3_g, *ln3_b, *lnff_g, *lnff_b, *lnn_g, *lnn_b;
+  float* x_out;      // x' = x + out-proj (scratch, (R,384)); then z in z_out
+  float* z_out;
+  __nv_bfloat16* zn_out;
+  float eps;
+  int R;
+};
+
+// shared memory: Wo slice | W1 slice (later the W2 slice) | H (bf16 [16][1536], ctx tile at its start) | X fp32 | A1 | red | stage | u row
+constexpr int kOffW1 = kColsD * kRbD;
+constexpr int kOffH = kOffW1 + kColsH * kRbD;
+constexpr int kOffX = kOffH + kRows * kRbH;
+constexpr int kOffA1 = kOffX + kRows * kD * 4;
+constexpr int kOffRed = kOffA1 + kRows * kRbD;
+constexpr int kRedBytes = 8 * 3 * 128 * 4;                      // FFN2: 8 k-slices x 3 n-tiles (= FFN1: 2 x 12)
+constexpr int kOffStage = kOffRed + kRedBytes;
+constexpr int kStageBytes = kRows * kColsH * 2;                 // H slice bf16 (>= 16 x 24 floats)
+constexpr int kOffU = kOffStage + kStageBytes;
+constexpr int kSmemB = kOffU + kD * 4;
+static_assert(kColsD * kRbH <= kColsH * kRbD, "the W2 slice must fit where the W1 slice was");
+static_assert(kSmemB <= 232448, "shared memory budget");
+
+__global__ void __launch_bounds__(kThreads, 1) ffn_block_kernel(const FfnBlock p) {
+  extern __shared__ __align__(16) uint8_t sm[];
+  uint8_t* sWo = sm;
+  uint8_t* sW1 = sm + kOffW1;
+  uint8_t* sH = sm + kOffH;
+  float* sX = reinterpret_cast<float*>(sm + kOffX);
+  uint8_t* sA1 = sm + kOffA1;
+  float* red = reinterpret_cast<float*>(sm + kOffRed);
+  float* stage = reinterpret_cast<float*>(sm + kOffStage);
+  float* sU = reinterpret_cast<float*>(sm + kOffU);
+  const uint32_t rank = cluster_rank();
+  const int r0 = (blockIdx.x / kCluster) * kRows;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_launch_dependents();
+  load_w_slice(sWo, kRbD, p.wo, kD, rank * kColsD, kColsD, kD);
+  load_w_slice(sW1, kRbD, p.w1, kD, rank * kColsH, kColsH, kD);
+  pdl_wait();
+  load_rows_bf16(sH, p.ctx, r0, p.R);           // the ctx tile borrows the start of H
+  cp_async_wait_all();
+  __syncthreads();
+  out_proj_push(sH, sWo, p.bo, p.x_in, p.x_out, sX, red, stage, r0, p.R, rank);
+  cluster_barrier();                            // #1: full rows of x' everywhere; nobody reads the ctx tile any more
+  layernorm_rows(sX, sA1, p.ln3_g, p.ln3_b, p.eps);
+  __syncthreads();
+  // ---- FFN1 slice: 96 hidden columns ----
+  slice_mma<2>(sA1, kRbD, sW1, kRbD, kColsH / 8, kD / 32, red);
+  __syncthreads();
+  load_w_slice(sW1, kRbH, p.w2, kHid, rank * kColsD, kColsD, kHid);   // the W2 slice replaces W1 (in flight during the push)
+  {
+    __nv_bfloat16* hs = reinterpret_cast<__nv_bfloat16*>(stage);
+    const int c0 = rank * kColsH;
+    for (int i = threadIdx.x; i < kRows * kColsH; i += kThreads) {
+      const int row = i / kColsH, col = i - row * kColsH;
+      hs[i] = __float2bfloat16(fmaxf(slice_value<2>(red, kColsH / 8, row, col) + __ldg(p.b1 + c0 + col), 0.f));
+    }
+    __syncthreads();
+    // push: 16 rows x 96 bf16 = 16 x 12 uint4 per target CTA
+    const uint32_t h_addr = smem_u32(sH);
+    constexpr int VPR = kColsH / 8;
+    for (int i = threadIdx.x; i < kCluster * kRows * VPR; i += kThreads) {
+      const int tgt = i / (kRows * VPR), j = i - tgt * (kRows * VPR);
+      const int row = j / VPR, v8 = j - row * VPR;
+      const uint4 v = *reinterpret_cast<const uint4*>(hs + row * kColsH + v8 * 8);
+      st_cluster_v4(map_to_cta(h_addr + row * kRbH + (c0 + v8 * 8) * 2, tgt), v);
+    }
+  }
+  cp_async_wait_all();
+  cluster_barrier();                            // #2: the full hidden rows everywhere (and this CTA's W2 slice has landed)
+  // ---- FFN2 slice: 24 output columns, K = 1536 in 8 k-slices ----
+  slice_mma<8>(sH, kRbH, sW1, kRbH, kColsD / 8, kHid / 32, red);
+  __syncthreads();
+  {
+    // u[row][c0 + col] goes to the CTA that owns the row's tail (row r -> CTA r): 24 floats = 6 float4 per row
+    const int c0 = rank * kColsD;
+    for (int i = threadIdx.x; i < kRows * kColsD; i += kThreads) {
+      const int row = i / kColsD, col = i - row * kColsD;
+      stage[i] = slice_value<8>(red, kColsD / 8, row, col) + __ldg(p.b2 + c0 + col);
+    }
+    __syncthreads();
+    const uint32_t u_addr = smem_u32(sU);
+    for (int i = threadIdx.x; i < kRows * (kColsD / 4); i += kThreads) {
+      const int row = i / (kColsD / 4), q4 = i - row * (kColsD / 4);
+      const uint4 v = *reinterpret_cast<const uint4*>(stage + row * kColsD + q4 * 4);
+      st_cluster_v4(map_to_cta(u_addr + (c0 + q4 * 4) * 4, row), v);
+    }
+  }
+  cluster_barrier();                            // #3: CTA r holds the full row r of u
+  // ---- tail of row `rank`: z = x' + LN_ff(u + LN3(x'));  zn = bf16(LN_next(z)) ----
+  const int row = r0 + static_cast<int>(rank);
+  if (warp == 0 && row < p.R) {
+    constexpr int NV = kD / 32;
+    float v[NV], xr[NV];
+    const __nv_bfloat16* xn = reinterpret_cast<const __nv_bfloat16*>(sA1 + rank * kRbD);
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int k = lane + 32 * j;
+      v[j] = sU[k] + __bfloat162float(xn[k]);
+      xr[j] = sX[rank * kD + k];
+    }
+    auto stats = [&](const float* a, float& mean, float& rstd) {
+      float s = 0.f;
+#pragma unroll
+      for (int j = 0; j < NV; ++j) s += a[j];
+      mean = warp_sum(s) * (1.f / kD);
+      float q = 0.f;
+#pragma unroll
+      for (int j = 0; j < NV; ++j) q = fmaf(a[j] - mean, a[j] - mean, q);
+      rstd = rsqrtf(warp_sum(q) * (1.f / kD) + p.eps);
+    };
+    float mean, rstd;
+    stats(v, mean, rstd);
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int k = lane + 32 * j;
+      v[j] = xr[j] + fmaf((v[j] - mean) * rstd, __ldg(p.lnff_g + k), __ldg(p.lnff_b + k));
+    }
+    stats(v, mean, rstd);
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int k = lane + 32 * j;
+      p.z_out[static_cast<int64_t>(row) * kD + k] = v[j];
+      p.zn_out[static_cast<int64_t>(row) * kD + k] = __float2bfloat16(fmaf((v[j] - mean) * rstd, __ldg(p.lnn_g + k), __ldg(p.lnn_b + k)));
+    }
+  }
+}
+
+template <typename P>
+static cudaError_t launch_cluster(void (*kern)(P), int row_tiles, size_t smem, cudaStream_t st, const P& p) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(kCluster * row_tiles);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kCluster;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 2;
+  return cudaLaunchKernelEx(&cfg, kern, p);
+}
+
+// a 16-CTA cluster is above the portable size of 8: opt in once per device, together with the shared-memory size
+template <typename K>
+static int opt_in(K kern, int smem) {
+  static unsigned long long done = 0;
+  int dev = 0;
+  TTSB_CHECK_CUDA(cudaGetDevice(&dev));
+  if (!((done >> (dev & 63)) & 1ull)) {
+    TTSB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    TTSB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    done |= 1ull << (dev & 63);
+  }
+  return TTSB_OK;
+}
+
+}  // namespace dcl
+}  // namespace ttsb
+
+using namespace ttsb;
+
+static bool dcl_aligned(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+extern "C" int ttsb200_decode_attn_out_q(const void* ctx_bf16, const float* x_in, const void* wo_bf16, const float* bo,
+                                         const float* ln_g, const float* ln_b, const void* wq_bf16, const float* bq, float eps,
+                                         float* x_out, void* q_bf16, int32_t R, int32_t D, ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(ctx_bf16 && x_in && wo_bf16 && bo && ln_g && ln_b && wq_bf16 && bq && x_out && q_bf16 && R > 0,
+                 "decode_attn_out_q: bad args");
+  TTSB_CHECK_ARG(D == dcl::kD, "decode_attn_out_q: D = %d unsupported (384)", D);
+  TTSB_CHECK_ARG(dcl_aligned(ctx_bf16) && dcl_aligned(wo_bf16) && dcl_aligned(wq_bf16), "decode_attn_out_q: 16-byte alignment");
+  dcl::AttnOutQ p;
+  p.ctx = static_cast<const __nv_bfloat16*>(ctx_bf16);
+  p.x_in = x_in;
+  p.wo = static_cast<const __nv_bfloat16*>(wo_bf16);
+  p.wq = static_cast<const __nv_bfloat16*>(wq_bf16);
+  p.bo = bo; p.bq = bq; p.ln_g = ln_g; p.ln_b = ln_b;
+  p.x_out = x_out;
+  p.q_out = static_cast<__nv_bfloat16*>(q_bf16);
+  p.eps = eps;
+  p.R = R;
+  int rc = dcl::opt_in(dcl::attn_out_q_kernel, dcl::kSmemA);
+  if (rc) return rc;
+  TTSB_CHECK_CUDA(dcl::launch_cluster(dcl::attn_out_q_kernel, (R + dcl::kRows - 1) / dcl::kRows, dcl::kSmemA,
+                                      static_cast<cudaStream_t>(s), p));
+  return TTSB_OK;
+}
+
+extern "C" int ttsb200_decode_ffn_block(const void* ctx_bf16, const float* x_in, const void* wo_bf16, const float* bo,
+                                        const float* ln3_g, const float* ln3_b, const void* w1_bf16, const float* b1,
+                                        const void* w2_bf16, const float* b2, const float* lnff_g, const float* lnff_b,
+                                        const float* lnn_g, const float* lnn_b, float eps, float* x_mid, float* z_out,
+                                        void* zn_bf16, int32_t R, int32_t D, int32_t hidden, ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(ctx_bf16 && x_in && wo_bf16 && bo && ln3_g && ln3_b && w1_bf16 && b1 && w2_bf16 && b2 && lnff_g && lnff_b &&
+                     lnn_g && lnn_b && x_mid && z_out && zn_bf16 && R > 0, "decode_ffn_block: bad args");
+  TTSB_CHECK_ARG(D == dcl::kD && hidden == dcl::kHid, "decode_ffn_block: this build is for D=384, hidden=1536");
+  TTSB_CHECK_ARG(dcl_aligned(ctx_bf16) && dcl_aligned(wo_bf16) && dcl_aligned(w1_bf16) && dcl_aligned(w2_bf16),
+                 "decode_ffn_block: 16-byte alignment");
+  dcl::FfnBlock p;
+  p.ctx = static_cast<const __nv_bfloat16*>(ctx_bf16);
+  p.x_in = x_in;
+  p.wo = static_cast<const __nv_bfloat16*>(wo_bf16);
+  p.w1 = static_cast<const __nv_bfloat16*>(w1_bf16);
+  p.w2 = static_cast<const __nv_bfloat16*>(w2_bf16);
+  p.bo = bo; p.b1 = b1; p.b2 = b2;
+  p.ln3_g = ln3_g; p.ln3_b = ln3_b; p.lnff_g = lnff_g; p.lnff_b = lnff_b; p.lnn_g = lnn_g; p.lnn_b = lnn_b;
+  p.x_out = x_mid;
+  p.z_out = z_out;
+  p.zn_out = static_cast<__nv_bfloat16*>(zn_bf16);
+  p.eps = eps;
+  p.R = R;
+  int rc = dcl::opt_in(dcl::ffn_block_kernel, dcl::kSmemB);
+  if (rc) return rc;
+  TTSB_CHECK_CUDA(dcl::launch_cluster(dcl::ffn_block_kernel, (R + dcl::kRows - 1) / dcl::kRows, dcl::kSmemB,
+                                      static_cast<cudaStream_t>(s), p));
+  return TTSB_OK;
+}
