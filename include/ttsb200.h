@@ -453,16 +453,15 @@ int ttsb200_ffn_tail_rows(const float* u, const void* yn_bf16, const float* y, c
  * slices into the shared memory of all CTAs of the cluster; cluster barriers stand where kernel boundaries were.
  * Weights bf16 row-major as for ttsb200_small_linear (wo, wq [384][384]; w1 [1536][384]; w2 [384][1536]); D = 384.
  *   attn_out_q: x_out = x_in + ctx Wo^T + bo  (Models/layers.py:112);  q = bf16(LN(x_out; ln) Wq^T + bq)  (layers.py:114-115)
- *   ffn_block:  x_mid = x_in + ctx Wo^T + bo (layers.py:116);  h = relu(LN3(x_mid) W1^T + b1);  u = h W2^T + b2;
- *               z = x_mid + LN_ff(u + LN3(x_mid))  (layers.py:118-122, Models/modules.py:81-87);  zn = bf16(LN_next(z)) */
+ *   ffn_block:  x' = x_in + ctx Wo^T + bo (layers.py:116; kept on chip);  h = relu(LN3(x') W1^T + b1);  u = h W2^T + b2;
+ *               z = x' + LN_ff(u + LN3(x'))  (layers.py:118-122, Models/modules.py:81-87);  zn = bf16(LN_next(z)) */
 int ttsb200_decode_attn_out_q(const void* ctx_bf16, const float* x_in, const void* wo_bf16, const float* bo, const float* ln_g,
                               const float* ln_b, const void* wq_bf16, const float* bq, float eps, float* x_out, void* q_bf16,
                               int32_t R, int32_t D, ttsb200_stream_t stream);
 int ttsb200_decode_ffn_block(const void* ctx_bf16, const float* x_in, const void* wo_bf16, const float* bo, const float* ln3_g,
                              const float* ln3_b, const void* w1_bf16, const float* b1, const void* w2_bf16, const float* b2,
                              const float* lnff_g, const float* lnff_b, const float* lnn_g, const float* lnn_b, float eps,
-                             float* x_mid, float* z_out, void* zn_bf16, int32_t R, int32_t D, int32_t hidden,
-                             ttsb200_stream_t stream);
+                             float* z_out, void* zn_bf16, int32_t R, int32_t D, int32_t hidden, ttsb200_stream_t stream);
 
 /* *pos += delta (the last node of a captured decode step). */
 int ttsb200_advance_pos(int32_t* pos, int32_t delta, ttsb200_stream_t stream);

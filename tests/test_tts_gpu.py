@@ -167,10 +167,9 @@ def test_cluster_kernels_match_the_unfused_step_kernels(R):
     lib.small_linear(w1, b1, D, x_f32=x3_ref, ln=ln3, relu=True, out_bf16=hid, xn_bf16=xn)
     lib.small_linear(w2, b2, Hd, x_bf16=hid, out_f32=u)
     lib.ffn_tail_rows(u, xn, x3_ref, lnff, lnn, 1e-5, z_ref, zn_ref)
-    x3, z, zn = f32(), f32(), bf()
-    lib.decode_ffn_block(ctx, x, wo, bo, ln3, w1, b1, w2, b2, lnff, lnn, 1e-5, x3, z, zn)
+    z, zn = f32(), bf()
+    lib.decode_ffn_block(ctx, x, wo, bo, ln3, w1, b1, w2, b2, lnff, lnn, 1e-5, z, zn)
     torch.cuda.synchronize()
-    assert rel(x3, x3_ref) < 1e-6
     assert rel(z, z_ref) < 2e-3 and rel(zn, zn_ref) < 4e-3          # a hidden value on a bf16 rounding boundary may flip
     # and against fp64 on the same bf16 operands
     xd = x.double() + ctx.double() @ wo.double().T + bo.double()

@@ -54,5 +54,5 @@ for p in (500,):
     timeit("ffn2_tail", lambda: lib.ffn2_tail(st.u, st.xn, st.x, lc["ln_ff"], t["ident"], 1e-5, st.x2, st.zn))
     nl = t["layers"][1]["ln1"]
     timeit("cluster: out-proj + LN2 + q2", lambda: lib.decode_attn_out_q(st.ctx, st.x, lc["wo1"], lc["bo1"], lc["ln2"], lc["wq2"], lc["bq2"], 1e-5, st.x2, st.q2))
-    timeit("cluster: out-proj + LN3 + FFN + tail", lambda: lib.decode_ffn_block(st.ctx, st.x2, lc["wo2"], lc["bo2"], lc["ln3"], lc["w1"], lc["b1"], lc["w2"], lc["b2"], lc["ln_ff"], nl, 1e-5, st.u, st.x, st.zn))
+    timeit("cluster: out-proj + LN3 + FFN + tail", lambda: lib.decode_ffn_block(st.ctx, st.x2, lc["wo2"], lc["bo2"], lc["ln3"], lc["w1"], lc["b1"], lc["w2"], lc["b2"], lc["ln_ff"], nl, 1e-5, st.x, st.zn))
     timeit("advance_pos(0)", lambda: lib.advance_pos(st.pos, 0))

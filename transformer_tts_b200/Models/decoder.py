@@ -114,7 +114,7 @@ class DecodeState:
                 lib.attn_decode(self.q2, 0, D, self.kv_cross[i], D, (self.L * 2 * D, Dh, 2 * D), self.L, H, Dh, self.ctx,
                                 kv_len=self.src_len)
                 lib.decode_ffn_block(self.ctx, x2, lc["wo2"], lc["bo2"], lc["ln3"], lc["w1"], lc["b1"], lc["w2"], lc["b2"],
-                                     lc["ln_ff"], next_ln, E.LN_EPS, self.u, x, self.zn)
+                                     lc["ln_ff"], next_ln, E.LN_EPS, x, self.zn)
                 continue
             lib.small_linear(lc["wo1"], lc["bo1"], D, x_bf16=self.ctx, res_f32=x, out_f32=x2)
             lib.small_linear(lc["wq2"], lc["bq2"], D, x_f32=x2, ln=lc["ln2"], out_bf16=self.q2)

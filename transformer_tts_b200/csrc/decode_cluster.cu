@@ -87,6 +87,19 @@ __device__ __forceinline__ void load_rows_bf16(uint8_t* dst, const __nv_bfloat16
   }
 }
 
+// n floats (n % 4 == 0, 16-byte aligned source) -> shared memory
+__device__ __forceinline__ void load_f32(float* dst, const float* src, int n) {
+  for (int i = threadIdx.x; i < (n >> 2); i += kThreads) cp_async16(dst + i * 4, src + i * 4, 16);
+}
+// this CTA's 16 x 24 slice of fp32 rows (R, 384): row r at dst + 24 r
+__device__ __forceinline__ void load_res_slice(float* dst, const float* x, int r0, int R, int c0) {
+  for (int i = threadIdx.x; i < kRows * (kColsD / 4); i += kThreads) {
+    const int rr = i / (kColsD / 4), q4 = i - rr * (kColsD / 4);
+    const bool valid = r0 + rr < R;
+    cp_async16(dst + rr * kColsD + q4 * 4, x + static_cast<int64_t>(valid ? r0 + rr : 0) * kD + c0 + q4 * 4, valid ? 16 : 0);
+  }
+}
+
 // Partial products of a [16 x K] . [K x 8 n_tiles] slice: task (n-tile, k-slice) -> red[ks][nt][lane][4].
 // Fragment convention and the permuted contraction index as in small_linear (csrc/decode.cu).
 template <int KS>
@@ -110,6 +123,39 @@ __device__ __forceinline__ void slice_mma(const uint8_t* A, int a_rb, const uint
     *reinterpret_cast<float4*>(red + ((ks * n_tiles + nt) * 32 + lane) * 4) = make_float4(acc[0], acc[1], acc[2], acc[3]);
   }
 }
+// The same with CONTIGUOUS k-slices of `per` k-blocks each, the weights' K range split over two buffers at k-block
+// `split` (FFN2: the first half of the W2 slice is prefetched, the second half arrives where the W1 slice was).
+template <int KS>
+__device__ __forceinline__ void slice_mma_split(const uint8_t* A, int a_rb, const uint8_t* Wa, const uint8_t* Wb, int w_rb,
+                                                int split, int n_tiles, int per, float* red) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, tq = lane & 3;
+  for (int t = warp; t < n_tiles * KS; t += kWarps) {
+    const int nt = t % n_tiles, ks = t / n_tiles;
+    const int kb0 = ks * per;
+    const uint8_t* xa = A + g * a_rb + tq * 16 + kb0 * 64;
+    const uint8_t* xb = xa + 8 * a_rb;
+    const uint8_t* wa = (kb0 < split ? Wa + kb0 * 64 : Wb + (kb0 - split) * 64) + (nt * 8 + g) * w_rb + tq * 16;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 6
+    for (int i = 0; i < per; ++i) {
+      const uint4 a = *reinterpret_cast<const uint4*>(xa + i * 64);
+      const uint4 b = *reinterpret_cast<const uint4*>(xb + i * 64);
+      const uint4 w = *reinterpret_cast<const uint4*>(wa + i * 64);
+      mma_bf16_16816(acc, a.x, b.x, a.y, b.y, w.x, w.y);
+      mma_bf16_16816(acc, a.z, b.z, a.w, b.w, w.z, w.w);
+    }
+    *reinterpret_cast<float4*>(red + ((ks * n_tiles + nt) * 32 + lane) * 4) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+  }
+}
+// `cols` columns [k0, k0 + cols) of this CTA's `rows` rows of a bf16 matrix [*][ldw] -> padded shared-memory rows
+__device__ __forceinline__ void load_w_cols(uint8_t* dst, int rb, const __nv_bfloat16* w, int64_t ldw, int row0, int rows, int k0, int cols) {
+  const int nv = cols >> 3;
+  for (int i = threadIdx.x; i < rows * nv; i += kThreads) {
+    const int r = i / nv, c = i - r * nv;
+    cp_async16(dst + r * rb + c * 16, w + static_cast<int64_t>(row0 + r) * ldw + k0 + c * 8, 16);
+  }
+}
 // value of output element (row, col) of the slice from the KS partials
 template <int KS>
 __device__ __forceinline__ float slice_value(const float* red, int n_tiles, int row, int col) {
@@ -122,15 +168,25 @@ __device__ __forceinline__ float slice_value(const float* red, int n_tiles, int 
 }
 
 // LayerNorm of the 16 fp32 rows in sX (two-pass, as torch) -> bf16 operand tile; 2 rows per warp
-__device__ __forceinline__ void layernorm_rows(const float* sX, uint8_t* sA, const float* g, const float* b, float eps) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  constexpr int NV = kD / 32;
-  float gg[NV], bb[NV];
+constexpr int kNV = kD / 32;   // columns per lane of a 384-wide row
+struct LnParams {
+  float g[kNV], b[kNV];
+};
+__device__ __forceinline__ LnParams load_ln(const float* g, const float* b) {   // immutable: may run before pdl_wait
+  LnParams r;
+  const int lane = threadIdx.x & 31;
 #pragma unroll
-  for (int j = 0; j < NV; ++j) {
-    gg[j] = __ldg(g + lane + 32 * j);
-    bb[j] = __ldg(b + lane + 32 * j);
+  for (int j = 0; j < kNV; ++j) {
+    r.g[j] = __ldg(g + lane + 32 * j);
+    r.b[j] = __ldg(b + lane + 32 * j);
   }
+  return r;
+}
+__device__ __forceinline__ void layernorm_rows(const float* sX, uint8_t* sA, const LnParams& ln, float eps) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int NV = kNV;
+  const float* gg = ln.g;
+  const float* bb = ln.b;
   for (int rr = warp; rr < kRows; rr += kWarps) {
     float v[NV];
     float s = 0.f;
@@ -152,7 +208,8 @@ __device__ __forceinline__ void layernorm_rows(const float* sX, uint8_t* sA, con
 
 // out-projection slice: y[row][c0 + col] = ctx . Wo^T + bo + x  for this CTA's 24 columns; written to x_out (global) and
 // pushed into every CTA's sX.  `red` / `stage` are scratch (stage: 16 x 24 floats).
-__device__ __forceinline__ void out_proj_push(const uint8_t* sA0, const uint8_t* sWo, const float* bo, const float* x_in,
+// sBo: this CTA's 24 bias values; sRes: its 16 x 24 slice of the residual rows (both prefetched into shared memory)
+__device__ __forceinline__ void out_proj_push(const uint8_t* sA0, const uint8_t* sWo, const float* sBo, const float* sRes,
                                               float* x_out, float* sX, float* red, float* stage, int r0, int R, uint32_t rank) {
   slice_mma<2>(sA0, kRbD, sWo, kRbD, kColsD / 8, kD / 32, red);
   __syncthreads();
@@ -161,8 +218,8 @@ __device__ __forceinline__ void out_proj_push(const uint8_t* sA0, const uint8_t*
     const int row = i / kColsD, col = i - row * kColsD;
     float v = 0.f;
     if (r0 + row < R) {
-      v = slice_value<2>(red, kColsD / 8, row, col) + __ldg(bo + c0 + col) + x_in[static_cast<int64_t>(r0 + row) * kD + c0 + col];
-      x_out[static_cast<int64_t>(r0 + row) * kD + c0 + col] = v;
+      v = slice_value<2>(red, kColsD / 8, row, col) + sBo[col] + sRes[i];
+      if (x_out) x_out[static_cast<int64_t>(r0 + row) * kD + c0 + col] = v;
     }
     stage[i] = v;
   }
@@ -188,7 +245,7 @@ struct AttnOutQ {
   int R;
 };
 
-constexpr int kSmemA = 2 * kColsD * kRbD + 2 * kRows * kRbD + kRows * kD * 4 + 4096 + kRows * kColsD * 4;
+constexpr int kSmemA = 2 * kColsD * kRbD + 2 * kRows * kRbD + kRows * kD * 4 + 4096 + kRows * kColsD * 4 * 2 + 256;
 
 __global__ void __launch_bounds__(kThreads, 1) attn_out_q_kernel(const AttnOutQ p) {
   extern __shared__ __align__(16) uint8_t sm[];
@@ -199,27 +256,33 @@ __global__ void __launch_bounds__(kThreads, 1) attn_out_q_kernel(const AttnOutQ 
   float* sX = reinterpret_cast<float*>(sA1 + kRows * kRbD);
   float* red = sX + kRows * kD;                 // 2 k-slices x 3 n-tiles x 128 floats = 3 KB (4 KB reserved)
   float* stage = red + 1024;
+  float* sRes = stage + kRows * kColsD;
+  float* sBo = sRes + kRows * kColsD;           // 24 + 24 floats: bo | bq slices
   const uint32_t rank = cluster_rank();
   const int r0 = (blockIdx.x / kCluster) * kRows;
+  const int c0 = rank * kColsD;
   pdl_launch_dependents();
-  load_w_slice(sWo, kRbD, p.wo, kD, rank * kColsD, kColsD, kD);
-  load_w_slice(sWq, kRbD, p.wq, kD, rank * kColsD, kColsD, kD);
+  load_w_slice(sWo, kRbD, p.wo, kD, c0, kColsD, kD);
+  load_w_slice(sWq, kRbD, p.wq, kD, c0, kColsD, kD);
+  load_f32(sBo, p.bo + c0, kColsD);
+  load_f32(sBo + kColsD, p.bq + c0, kColsD);
+  const LnParams ln = load_ln(p.ln_g, p.ln_b);
   pdl_wait();
   load_rows_bf16(sA0, p.ctx, r0, p.R);
+  load_res_slice(sRes, p.x_in, r0, p.R, c0);
   cp_async_wait_all();
   __syncthreads();
-  out_proj_push(sA0, sWo, p.bo, p.x_in, p.x_out, sX, red, stage, r0, p.R, rank);
+  out_proj_push(sA0, sWo, sBo, sRes, p.x_out, sX, red, stage, r0, p.R, rank);
   cluster_barrier();                            // every CTA holds the 16 full rows of x'
-  layernorm_rows(sX, sA1, p.ln_g, p.ln_b, p.eps);
+  layernorm_rows(sX, sA1, ln, p.eps);
   __syncthreads();
   slice_mma<2>(sA1, kRbD, sWq, kRbD, kColsD / 8, kD / 32, red);
   __syncthreads();
-  const int c0 = rank * kColsD;
   for (int i = threadIdx.x; i < kRows * kColsD; i += kThreads) {
     const int row = i / kColsD, col = i - row * kColsD;
     if (r0 + row < p.R)
       p.q_out[static_cast<int64_t>(r0 + row) * kD + c0 + col] =
-          __float2bfloat16(slice_value<2>(red, kColsD / 8, row, col) + __ldg(p.bq + c0 + col));
+          __float2bfloat16(slice_value<2>(red, kColsD / 8, row, col) + sBo[kColsD + col]);
   }
   // (every push into this CTA's shared memory happened before the barrier above: it may exit on its own)
 }
@@ -229,61 +292,88 @@ struct FfnBlock {
   const float* x_in;
   const __nv_bfloat16 *wo, *w1, *w2;
   const float *bo, *b1, *b2, *ln3_g, *ln3_b, *lnff_g, *lnff_b, *lnn_g, *lnn_b;
-  float* x_out;      // x' = x + out-proj (scratch, (R,384)); then z in z_out
   float* z_out;
   __nv_bfloat16* zn_out;
   float eps;
   int R;
 };
 
-// shared memory: Wo slice | W1 slice (later the W2 slice) | H (bf16 [16][1536], ctx tile at its start) | X fp32 | A1 | red | stage | u row
+// shared memory: Wo slice | W1 slice (later: second K half of the W2 slice) | first K half of the W2 slice |
+// H (bf16 [16][1536]; before barrier #1 the ctx tile at its start and the out-projection's scratch behind it) |
+// X fp32 [16][384] (after LayerNorm 3: scratch of FFN1 / FFN2) | A1 = LN3(x') bf16 | x' row of this CTA | u row | small vectors
+constexpr int kHalfK = kHid / 2;                                // 768
+constexpr int kRbW2 = kHalfK * 2 + kPad;                        // 1552 bytes per half row of the W2 slice
 constexpr int kOffW1 = kColsD * kRbD;
-constexpr int kOffH = kOffW1 + kColsH * kRbD;
+constexpr int kOffW2a = kOffW1 + kColsH * kRbD;
+constexpr int kOffH = kOffW2a + kColsD * kRbW2;
 constexpr int kOffX = kOffH + kRows * kRbH;
 constexpr int kOffA1 = kOffX + kRows * kD * 4;
-constexpr int kOffRed = kOffA1 + kRows * kRbD;
-constexpr int kRedBytes = 8 * 3 * 128 * 4;                      // FFN2: 8 k-slices x 3 n-tiles (= FFN1: 2 x 12)
-constexpr int kOffStage = kOffRed + kRedBytes;
-constexpr int kStageBytes = kRows * kColsH * 2;                 // H slice bf16 (>= 16 x 24 floats)
-constexpr int kOffU = kOffStage + kStageBytes;
-constexpr int kSmemB = kOffU + kD * 4;
-static_assert(kColsD * kRbH <= kColsH * kRbD, "the W2 slice must fit where the W1 slice was");
-static_assert(kSmemB <= 232448, "shared memory budget");
+constexpr int kOffXrow = kOffA1 + kRows * kRbD;
+constexpr int kOffU = kOffXrow + kD * 4;
+constexpr int kOffVec = kOffU + kD * 4;                         // bo[24] | b2[24] | b1[96] | residual slice [16][24]
+constexpr int kVecBytes = (kColsD + kColsD + kColsH + kRows * kColsD) * 4;
+constexpr int kSmemB = kOffVec + kVecBytes;
+constexpr int kRedFloats = 8 * 3 * 128;                         // FFN2: 8 k-slices x 3 n-tiles (= FFN1: 2 x 12)
+static_assert(kColsD * kRbW2 <= kColsH * kRbD, "the second half of the W2 slice must fit where the W1 slice was");
+static_assert((kRedFloats + kRows * kColsH) * 4 <= kRows * kD * 4, "FFN scratch must fit in the X tile");
+static_assert(kRows * kRbD + (1024 + kRows * kColsD) * 4 <= kRows * kRbH, "out-projection scratch must fit behind the ctx tile");
+static_assert(kSmemB <= 231424, "shared memory budget (1 KB is static)");
 
 __global__ void __launch_bounds__(kThreads, 1) ffn_block_kernel(const FfnBlock p) {
   extern __shared__ __align__(16) uint8_t sm[];
   uint8_t* sWo = sm;
   uint8_t* sW1 = sm + kOffW1;
+  uint8_t* sW2a = sm + kOffW2a;
   uint8_t* sH = sm + kOffH;
   float* sX = reinterpret_cast<float*>(sm + kOffX);
   uint8_t* sA1 = sm + kOffA1;
-  float* red = reinterpret_cast<float*>(sm + kOffRed);
-  float* stage = reinterpret_cast<float*>(sm + kOffStage);
+  float* sXrow = reinterpret_cast<float*>(sm + kOffXrow);
   float* sU = reinterpret_cast<float*>(sm + kOffU);
+  float* sBo = reinterpret_cast<float*>(sm + kOffVec);
+  float* sB2 = sBo + kColsD;
+  float* sB1 = sB2 + kColsD;
+  float* sRes = sB1 + kColsH;
+  float* red0 = reinterpret_cast<float*>(sH + kRows * kRbD);    // out-projection scratch, behind the ctx tile
+  float* stage0 = red0 + 1024;
+  float* red = sX;                                              // FFN scratch: the X tile after LayerNorm 3
+  float* stage = sX + kRedFloats;
   const uint32_t rank = cluster_rank();
   const int r0 = (blockIdx.x / kCluster) * kRows;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   pdl_launch_dependents();
+  // everything immutable leaves for shared memory / registers before the predecessor has finished
   load_w_slice(sWo, kRbD, p.wo, kD, rank * kColsD, kColsD, kD);
   load_w_slice(sW1, kRbD, p.w1, kD, rank * kColsH, kColsH, kD);
+  load_w_cols(sW2a, kRbW2, p.w2, kHid, rank * kColsD, kColsD, 0, kHalfK);
+  load_f32(sBo, p.bo + rank * kColsD, kColsD);
+  load_f32(sB2, p.b2 + rank * kColsD, kColsD);
+  load_f32(sB1, p.b1 + rank * kColsH, kColsH);
+  const LnParams ln3 = load_ln(p.ln3_g, p.ln3_b);
+  LnParams lnff, lnn;
+  if (warp == 0) {
+    lnff = load_ln(p.lnff_g, p.lnff_b);
+    lnn = load_ln(p.lnn_g, p.lnn_b);
+  }
   pdl_wait();
   load_rows_bf16(sH, p.ctx, r0, p.R);           // the ctx tile borrows the start of H
+  load_res_slice(sRes, p.x_in, r0, p.R, rank * kColsD);
   cp_async_wait_all();
   __syncthreads();
-  out_proj_push(sH, sWo, p.bo, p.x_in, p.x_out, sX, red, stage, r0, p.R, rank);
+  out_proj_push(sH, sWo, sBo, sRes, nullptr, sX, red0, stage0, r0, p.R, rank);
   cluster_barrier();                            // #1: full rows of x' everywhere; nobody reads the ctx tile any more
-  layernorm_rows(sX, sA1, p.ln3_g, p.ln3_b, p.eps);
-  __syncthreads();
+  layernorm_rows(sX, sA1, ln3, p.eps);
+  for (int i = threadIdx.x; i < kD; i += kThreads) sXrow[i] = sX[rank * kD + i];   // the tail's residual row
+  __syncthreads();                              // the X tile is scratch from here on
   // ---- FFN1 slice: 96 hidden columns ----
   slice_mma<2>(sA1, kRbD, sW1, kRbD, kColsH / 8, kD / 32, red);
   __syncthreads();
-  load_w_slice(sW1, kRbH, p.w2, kHid, rank * kColsD, kColsD, kHid);   // the W2 slice replaces W1 (in flight during the push)
+  load_w_cols(sW1, kRbW2, p.w2, kHid, rank * kColsD, kColsD, kHalfK, kHalfK);   // second K half of W2, in flight during the push
   {
     __nv_bfloat16* hs = reinterpret_cast<__nv_bfloat16*>(stage);
     const int c0 = rank * kColsH;
     for (int i = threadIdx.x; i < kRows * kColsH; i += kThreads) {
       const int row = i / kColsH, col = i - row * kColsH;
-      hs[i] = __float2bfloat16(fmaxf(slice_value<2>(red, kColsH / 8, row, col) + __ldg(p.b1 + c0 + col), 0.f));
+      hs[i] = __float2bfloat16(fmaxf(slice_value<2>(red, kColsH / 8, row, col) + sB1[col], 0.f));
     }
     __syncthreads();
     // push: 16 rows x 96 bf16 = 16 x 12 uint4 per target CTA
@@ -297,16 +387,16 @@ __global__ void __launch_bounds__(kThreads, 1) ffn_block_kernel(const FfnBlock p
     }
   }
   cp_async_wait_all();
-  cluster_barrier();                            // #2: the full hidden rows everywhere (and this CTA's W2 slice has landed)
-  // ---- FFN2 slice: 24 output columns, K = 1536 in 8 k-slices ----
-  slice_mma<8>(sH, kRbH, sW1, kRbH, kColsD / 8, kHid / 32, red);
+  cluster_barrier();                            // #2: the full hidden rows everywhere (and this CTA's W2 slice is complete)
+  // ---- FFN2 slice: 24 output columns, K = 1536 in 8 contiguous k-slices of 6 k-blocks ----
+  slice_mma_split<8>(sH, kRbH, sW2a, sW1, kRbW2, kHalfK / 32, kColsD / 8, kHid / 32 / 8, red);
   __syncthreads();
   {
     // u[row][c0 + col] goes to the CTA that owns the row's tail (row r -> CTA r): 24 floats = 6 float4 per row
     const int c0 = rank * kColsD;
     for (int i = threadIdx.x; i < kRows * kColsD; i += kThreads) {
       const int row = i / kColsD, col = i - row * kColsD;
-      stage[i] = slice_value<8>(red, kColsD / 8, row, col) + __ldg(p.b2 + c0 + col);
+      stage[i] = slice_value<8>(red, kColsD / 8, row, col) + sB2[col];
     }
     __syncthreads();
     const uint32_t u_addr = smem_u32(sU);
@@ -320,14 +410,13 @@ __global__ void __launch_bounds__(kThreads, 1) ffn_block_kernel(const FfnBlock p
   // ---- tail of row `rank`: z = x' + LN_ff(u + LN3(x'));  zn = bf16(LN_next(z)) ----
   const int row = r0 + static_cast<int>(rank);
   if (warp == 0 && row < p.R) {
-    constexpr int NV = kD / 32;
-    float v[NV], xr[NV];
+    constexpr int NV = kNV;
+    float v[NV];
     const __nv_bfloat16* xn = reinterpret_cast<const __nv_bfloat16*>(sA1 + rank * kRbD);
 #pragma unroll
     for (int j = 0; j < NV; ++j) {
       const int k = lane + 32 * j;
       v[j] = sU[k] + __bfloat162float(xn[k]);
-      xr[j] = sX[rank * kD + k];
     }
     auto stats = [&](const float* a, float& mean, float& rstd) {
       float s = 0.f;
@@ -342,16 +431,13 @@ __global__ void __launch_bounds__(kThreads, 1) ffn_block_kernel(const FfnBlock p
     float mean, rstd;
     stats(v, mean, rstd);
 #pragma unroll
-    for (int j = 0; j < NV; ++j) {
-      const int k = lane + 32 * j;
-      v[j] = xr[j] + fmaf((v[j] - mean) * rstd, __ldg(p.lnff_g + k), __ldg(p.lnff_b + k));
-    }
+    for (int j = 0; j < NV; ++j) v[j] = sXrow[lane + 32 * j] + fmaf((v[j] - mean) * rstd, lnff.g[j], lnff.b[j]);
     stats(v, mean, rstd);
 #pragma unroll
     for (int j = 0; j < NV; ++j) {
       const int k = lane + 32 * j;
       p.z_out[static_cast<int64_t>(row) * kD + k] = v[j];
-      p.zn_out[static_cast<int64_t>(row) * kD + k] = __float2bfloat16(fmaf((v[j] - mean) * rstd, __ldg(p.lnn_g + k), __ldg(p.lnn_b + k)));
+      p.zn_out[static_cast<int64_t>(row) * kD + k] = __float2bfloat16(fmaf((v[j] - mean) * rstd, lnn.g[j], lnn.b[j]));
     }
   }
 }
@@ -423,10 +509,10 @@ extern "C" int ttsb200_decode_attn_out_q(const void* ctx_bf16, const float* x_in
 extern "C" int ttsb200_decode_ffn_block(const void* ctx_bf16, const float* x_in, const void* wo_bf16, const float* bo,
                                         const float* ln3_g, const float* ln3_b, const void* w1_bf16, const float* b1,
                                         const void* w2_bf16, const float* b2, const float* lnff_g, const float* lnff_b,
-                                        const float* lnn_g, const float* lnn_b, float eps, float* x_mid, float* z_out,
-                                        void* zn_bf16, int32_t R, int32_t D, int32_t hidden, ttsb200_stream_t s) {
+                                        const float* lnn_g, const float* lnn_b, float eps, float* z_out, void* zn_bf16,
+                                        int32_t R, int32_t D, int32_t hidden, ttsb200_stream_t s) {
   TTSB_CHECK_ARG(ctx_bf16 && x_in && wo_bf16 && bo && ln3_g && ln3_b && w1_bf16 && b1 && w2_bf16 && b2 && lnff_g && lnff_b &&
-                     lnn_g && lnn_b && x_mid && z_out && zn_bf16 && R > 0, "decode_ffn_block: bad args");
+                     lnn_g && lnn_b && z_out && zn_bf16 && R > 0, "decode_ffn_block: bad args");
   TTSB_CHECK_ARG(D == dcl::kD && hidden == dcl::kHid, "decode_ffn_block: this build is for D=384, hidden=1536");
   TTSB_CHECK_ARG(dcl_aligned(ctx_bf16) && dcl_aligned(wo_bf16) && dcl_aligned(w1_bf16) && dcl_aligned(w2_bf16),
                  "decode_ffn_block: 16-byte alignment");
@@ -438,7 +524,6 @@ extern "C" int ttsb200_decode_ffn_block(const void* ctx_bf16, const float* x_in,
   p.w2 = static_cast<const __nv_bfloat16*>(w2_bf16);
   p.bo = bo; p.b1 = b1; p.b2 = b2;
   p.ln3_g = ln3_g; p.ln3_b = ln3_b; p.lnff_g = lnff_g; p.lnff_b = lnff_b; p.lnn_g = lnn_g; p.lnn_b = lnn_b;
-  p.x_out = x_mid;
   p.z_out = z_out;
   p.zn_out = static_cast<__nv_bfloat16*>(zn_bf16);
   p.eps = eps;

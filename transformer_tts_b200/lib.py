@@ -69,8 +69,8 @@ _SIGNATURES = {
                              C.c_int32, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_advance_pos": ([C.c_void_p, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_decode_attn_out_q": ([C.c_void_p] * 8 + [C.c_float, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p], C.c_int),
-    "ttsb200_decode_ffn_block": ([C.c_void_p] * 14 + [C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
-                                                    C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_decode_ffn_block": ([C.c_void_p] * 14 + [C.c_float, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
+                                                    C.c_void_p], C.c_int),
     "ttsb200_ffn_tail_rows": ([C.c_void_p] * 7 + [C.c_float, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_ffn_fused": ([C.c_void_p] * 10 + [C.c_float, C.c_void_p, C.c_void_p] + [C.c_int32] * 4 + [C.c_void_p] * 3, C.c_int),
     "ttsb200_build_tile_map": ([C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
@@ -786,7 +786,7 @@ def decode_attn_out_q(ctx, x_in, wo, bo, ln, wq, bq, eps, x_out, q_out) -> None:
     _count()
 
 
-def decode_ffn_block(ctx, x_in, wo, bo, ln3, w1, b1, w2, b2, ln_ff, ln_next, eps, x_mid, z_out, zn_out) -> None:
+def decode_ffn_block(ctx, x_in, wo, bo, ln3, w1, b1, w2, b2, ln_ff, ln_next, eps, z_out, zn_out) -> None:
     """Second attention's out-projection, FeedForward and the next LayerNorm of a decoder block in one cluster kernel."""
     R, D = x_in.shape
     f32, bf = torch.float32, torch.bfloat16
@@ -794,6 +794,6 @@ def decode_ffn_block(ctx, x_in, wo, bo, ln3, w1, b1, w2, b2, ln_ff, ln_next, eps
         _ptr(ctx, bf, "ctx"), _ptr(x_in, f32, "x_in"), _ptr(wo, bf, "wo"), _ptr(bo, f32, "bo"), _ptr(ln3[0], f32, "ln3_g"),
         _ptr(ln3[1], f32, "ln3_b"), _ptr(w1, bf, "w1"), _ptr(b1, f32, "b1"), _ptr(w2, bf, "w2"), _ptr(b2, f32, "b2"),
         _ptr(ln_ff[0], f32, "lnff_g"), _ptr(ln_ff[1], f32, "lnff_b"), _ptr(ln_next[0], f32, "lnn_g"),
-        _ptr(ln_next[1], f32, "lnn_b"), eps, _ptr(x_mid, f32, "x_mid"), _ptr(z_out, f32, "z_out"), _ptr(zn_out, bf, "zn_out"),
+        _ptr(ln_next[1], f32, "lnn_b"), eps, _ptr(z_out, f32, "z_out"), _ptr(zn_out, bf, "zn_out"),
         R, D, int(w1.shape[0]), _stream()), "decode_ffn_block")
     _count()
