@@ -463,6 +463,9 @@ int ttsb200_decode_ffn_block(const void* ctx_bf16, const float* x_in, const void
                              const float* lnff_g, const float* lnff_b, const float* lnn_g, const float* lnn_b, float eps,
                              float* z_out, void* zn_bf16, int32_t R, int32_t D, int32_t hidden, ttsb200_stream_t stream);
 
+/* Experiments only: phase timeline (clock64 of one thread) of the last ttsb200_decode_ffn_block; mode 1 on, 0 off, 2 read. */
+int ttsb200_debug_dcl_trace(long long* dst, int mode);
+
 /* *pos += delta (the last node of a captured decode step). */
 int ttsb200_advance_pos(int32_t* pos, int32_t delta, ttsb200_stream_t stream);
 

@@ -56,3 +56,14 @@ for p in (500,):
     timeit("cluster: out-proj + LN2 + q2", lambda: lib.decode_attn_out_q(st.ctx, st.x, lc["wo1"], lc["bo1"], lc["ln2"], lc["wq2"], lc["bq2"], 1e-5, st.x2, st.q2))
     timeit("cluster: out-proj + LN3 + FFN + tail", lambda: lib.decode_ffn_block(st.ctx, st.x2, lc["wo2"], lc["bo2"], lc["ln3"], lc["w1"], lc["b1"], lc["w2"], lc["b2"], lc["ln_ff"], nl, 1e-5, st.x, st.zn))
     timeit("advance_pos(0)", lambda: lib.advance_pos(st.pos, 0))
+
+import ctypes
+L_ = lib.load()
+L_.ttsb200_debug_dcl_trace(None, 1)
+for _ in range(3):
+    lib.decode_ffn_block(st.ctx, st.x2, lc["wo2"], lc["bo2"], lc["ln3"], lc["w1"], lc["b1"], lc["w2"], lc["b2"], lc["ln_ff"], nl, 1e-5, st.x, st.zn)
+    torch.cuda.synchronize()
+buf = (ctypes.c_longlong * 16)()
+L_.ttsb200_debug_dcl_trace(buf, 2); L_.ttsb200_debug_dcl_trace(None, 0)
+names = ["start", "prefetch issued", "dependency wait", "ctx landed", "out-proj + push", "barrier 1", "LayerNorm 3", "FFN1 mma", "H push", "W2 + barrier 2", "FFN2 mma", "u push", "barrier 3", "tail"]
+print("ffn_block timeline (clk, isolated launch): " + ", ".join(f"{n} {buf[i] - (buf[i-1] if i else 0)}" for i, n in enumerate(names)))

@@ -24,7 +24,7 @@ namespace dcl {
 constexpr int kCluster = 16;
 constexpr int kD = 384, kHid = 1536;
 constexpr int kRows = 16;
-constexpr int kThreads = 256, kWarps = 8;
+constexpr int kThreads = 512, kWarps = 16;
 constexpr int kPad = 16;
 constexpr int kRbD = kD * 2 + kPad;        // padded bf16 row of 384: 784 bytes
 constexpr int kRbH = kHid * 2 + kPad;      // padded bf16 row of 1536: 3088 bytes
@@ -111,16 +111,28 @@ __device__ __forceinline__ void slice_mma(const uint8_t* A, int a_rb, const uint
     const uint8_t* xa = A + g * a_rb + tq * 16;
     const uint8_t* xb = xa + 8 * a_rb;
     const uint8_t* wa = W + (nt * 8 + g) * w_rb + tq * 16;
-    float acc[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll 4
-    for (int kb = ks; kb < nkb; kb += KS) {
+    // mma.sync has a long latency on this part: four independent accumulator chains instead of one of 2 * nkb / KS links
+    float acc[4][4] = {};
+    int kb = ks;
+    for (; kb + KS < nkb; kb += 2 * KS) {
+      const uint4 a0 = *reinterpret_cast<const uint4*>(xa + kb * 64), a1 = *reinterpret_cast<const uint4*>(xa + (kb + KS) * 64);
+      const uint4 b0 = *reinterpret_cast<const uint4*>(xb + kb * 64), b1 = *reinterpret_cast<const uint4*>(xb + (kb + KS) * 64);
+      const uint4 w0 = *reinterpret_cast<const uint4*>(wa + kb * 64), w1 = *reinterpret_cast<const uint4*>(wa + (kb + KS) * 64);
+      mma_bf16_16816(acc[0], a0.x, b0.x, a0.y, b0.y, w0.x, w0.y);
+      mma_bf16_16816(acc[1], a0.z, b0.z, a0.w, b0.w, w0.z, w0.w);
+      mma_bf16_16816(acc[2], a1.x, b1.x, a1.y, b1.y, w1.x, w1.y);
+      mma_bf16_16816(acc[3], a1.z, b1.z, a1.w, b1.w, w1.z, w1.w);
+    }
+    if (kb < nkb) {
       const uint4 a = *reinterpret_cast<const uint4*>(xa + kb * 64);
       const uint4 b = *reinterpret_cast<const uint4*>(xb + kb * 64);
       const uint4 w = *reinterpret_cast<const uint4*>(wa + kb * 64);
-      mma_bf16_16816(acc, a.x, b.x, a.y, b.y, w.x, w.y);
-      mma_bf16_16816(acc, a.z, b.z, a.w, b.w, w.z, w.w);
+      mma_bf16_16816(acc[0], a.x, b.x, a.y, b.y, w.x, w.y);
+      mma_bf16_16816(acc[1], a.z, b.z, a.w, b.w, w.z, w.w);
     }
-    *reinterpret_cast<float4*>(red + ((ks * n_tiles + nt) * 32 + lane) * 4) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    *reinterpret_cast<float4*>(red + ((ks * n_tiles + nt) * 32 + lane) * 4) =
+        make_float4((acc[0][0] + acc[1][0]) + (acc[2][0] + acc[3][0]), (acc[0][1] + acc[1][1]) + (acc[2][1] + acc[3][1]),
+                    (acc[0][2] + acc[1][2]) + (acc[2][2] + acc[3][2]), (acc[0][3] + acc[1][3]) + (acc[2][3] + acc[3][3]));
   }
 }
 // The same with CONTIGUOUS k-slices of `per` k-blocks each, the weights' K range split over two buffers at k-block
@@ -136,16 +148,27 @@ __device__ __forceinline__ void slice_mma_split(const uint8_t* A, int a_rb, cons
     const uint8_t* xa = A + g * a_rb + tq * 16 + kb0 * 64;
     const uint8_t* xb = xa + 8 * a_rb;
     const uint8_t* wa = (kb0 < split ? Wa + kb0 * 64 : Wb + (kb0 - split) * 64) + (nt * 8 + g) * w_rb + tq * 16;
-    float acc[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll 6
-    for (int i = 0; i < per; ++i) {
+    float acc[4][4] = {};   // four independent accumulator chains (see slice_mma)
+    int i = 0;
+    for (; i + 1 < per; i += 2) {
+      const uint4 a0 = *reinterpret_cast<const uint4*>(xa + i * 64), a1 = *reinterpret_cast<const uint4*>(xa + (i + 1) * 64);
+      const uint4 b0 = *reinterpret_cast<const uint4*>(xb + i * 64), b1 = *reinterpret_cast<const uint4*>(xb + (i + 1) * 64);
+      const uint4 w0 = *reinterpret_cast<const uint4*>(wa + i * 64), w1 = *reinterpret_cast<const uint4*>(wa + (i + 1) * 64);
+      mma_bf16_16816(acc[0], a0.x, b0.x, a0.y, b0.y, w0.x, w0.y);
+      mma_bf16_16816(acc[1], a0.z, b0.z, a0.w, b0.w, w0.z, w0.w);
+      mma_bf16_16816(acc[2], a1.x, b1.x, a1.y, b1.y, w1.x, w1.y);
+      mma_bf16_16816(acc[3], a1.z, b1.z, a1.w, b1.w, w1.z, w1.w);
+    }
+    if (i < per) {
       const uint4 a = *reinterpret_cast<const uint4*>(xa + i * 64);
       const uint4 b = *reinterpret_cast<const uint4*>(xb + i * 64);
       const uint4 w = *reinterpret_cast<const uint4*>(wa + i * 64);
-      mma_bf16_16816(acc, a.x, b.x, a.y, b.y, w.x, w.y);
-      mma_bf16_16816(acc, a.z, b.z, a.w, b.w, w.z, w.w);
+      mma_bf16_16816(acc[0], a.x, b.x, a.y, b.y, w.x, w.y);
+      mma_bf16_16816(acc[1], a.z, b.z, a.w, b.w, w.z, w.w);
     }
-    *reinterpret_cast<float4*>(red + ((ks * n_tiles + nt) * 32 + lane) * 4) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    *reinterpret_cast<float4*>(red + ((ks * n_tiles + nt) * 32 + lane) * 4) =
+        make_float4((acc[0][0] + acc[1][0]) + (acc[2][0] + acc[3][0]), (acc[0][1] + acc[1][1]) + (acc[2][1] + acc[3][1]),
+                    (acc[0][2] + acc[1][2]) + (acc[2][2] + acc[3][2]), (acc[0][3] + acc[1][3]) + (acc[2][3] + acc[3][3]));
   }
 }
 // `cols` columns [k0, k0 + cols) of this CTA's `rows` rows of a bf16 matrix [*][ldw] -> padded shared-memory rows
@@ -287,6 +310,10 @@ __global__ void __launch_bounds__(kThreads, 1) attn_out_q_kernel(const AttnOutQ 
   // (every push into this CTA's shared memory happened before the barrier above: it may exit on its own)
 }
 
+__device__ long long g_dcl_trace[16];
+__device__ int g_dcl_trace_on = 0;
+#define DCL_T(i) do { if (tr) tt[i] = clock64(); } while (0)
+
 struct FfnBlock {
   const __nv_bfloat16* ctx;
   const float* x_in;
@@ -340,6 +367,9 @@ __global__ void __launch_bounds__(kThreads, 1) ffn_block_kernel(const FfnBlock p
   const uint32_t rank = cluster_rank();
   const int r0 = (blockIdx.x / kCluster) * kRows;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool tr = g_dcl_trace_on && blockIdx.x == 0 && threadIdx.x == 0;   // phase timeline of one thread (experiments)
+  long long tt[14];
+  DCL_T(0);
   pdl_launch_dependents();
   // everything immutable leaves for shared memory / registers before the predecessor has finished
   load_w_slice(sWo, kRbD, p.wo, kD, rank * kColsD, kColsD, kD);
@@ -354,19 +384,26 @@ __global__ void __launch_bounds__(kThreads, 1) ffn_block_kernel(const FfnBlock p
     lnff = load_ln(p.lnff_g, p.lnff_b);
     lnn = load_ln(p.lnn_g, p.lnn_b);
   }
+  DCL_T(1);
   pdl_wait();
+  DCL_T(2);
   load_rows_bf16(sH, p.ctx, r0, p.R);           // the ctx tile borrows the start of H
   load_res_slice(sRes, p.x_in, r0, p.R, rank * kColsD);
   cp_async_wait_all();
   __syncthreads();
+  DCL_T(3);
   out_proj_push(sH, sWo, sBo, sRes, nullptr, sX, red0, stage0, r0, p.R, rank);
+  DCL_T(4);
   cluster_barrier();                            // #1: full rows of x' everywhere; nobody reads the ctx tile any more
+  DCL_T(5);
   layernorm_rows(sX, sA1, ln3, p.eps);
   for (int i = threadIdx.x; i < kD; i += kThreads) sXrow[i] = sX[rank * kD + i];   // the tail's residual row
   __syncthreads();                              // the X tile is scratch from here on
+  DCL_T(6);
   // ---- FFN1 slice: 96 hidden columns ----
   slice_mma<2>(sA1, kRbD, sW1, kRbD, kColsH / 8, kD / 32, red);
   __syncthreads();
+  DCL_T(7);
   load_w_cols(sW1, kRbW2, p.w2, kHid, rank * kColsD, kColsD, kHalfK, kHalfK);   // second K half of W2, in flight during the push
   {
     __nv_bfloat16* hs = reinterpret_cast<__nv_bfloat16*>(stage);
@@ -386,11 +423,14 @@ __global__ void __launch_bounds__(kThreads, 1) ffn_block_kernel(const FfnBlock p
       st_cluster_v4(map_to_cta(h_addr + row * kRbH + (c0 + v8 * 8) * 2, tgt), v);
     }
   }
+  DCL_T(8);
   cp_async_wait_all();
   cluster_barrier();                            // #2: the full hidden rows everywhere (and this CTA's W2 slice is complete)
+  DCL_T(9);
   // ---- FFN2 slice: 24 output columns, K = 1536 in 8 contiguous k-slices of 6 k-blocks ----
   slice_mma_split<8>(sH, kRbH, sW2a, sW1, kRbW2, kHalfK / 32, kColsD / 8, kHid / 32 / 8, red);
   __syncthreads();
+  DCL_T(10);
   {
     // u[row][c0 + col] goes to the CTA that owns the row's tail (row r -> CTA r): 24 floats = 6 float4 per row
     const int c0 = rank * kColsD;
@@ -406,7 +446,9 @@ __global__ void __launch_bounds__(kThreads, 1) ffn_block_kernel(const FfnBlock p
       st_cluster_v4(map_to_cta(u_addr + (c0 + q4 * 4) * 4, row), v);
     }
   }
+  DCL_T(11);
   cluster_barrier();                            // #3: CTA r holds the full row r of u
+  DCL_T(12);
   // ---- tail of row `rank`: z = x' + LN_ff(u + LN3(x'));  zn = bf16(LN_next(z)) ----
   const int row = r0 + static_cast<int>(rank);
   if (warp == 0 && row < p.R) {
@@ -439,6 +481,10 @@ __global__ void __launch_bounds__(kThreads, 1) ffn_block_kernel(const FfnBlock p
       p.z_out[static_cast<int64_t>(row) * kD + k] = v[j];
       p.zn_out[static_cast<int64_t>(row) * kD + k] = __float2bfloat16(fmaf((v[j] - mean) * rstd, lnn.g[j], lnn.b[j]));
     }
+  }
+  if (tr) {
+    tt[13] = clock64();
+    for (int i = 0; i < 14; ++i) g_dcl_trace[i] = tt[i] - tt[0];
   }
 }
 
@@ -533,4 +579,10 @@ extern "C" int ttsb200_decode_ffn_block(const void* ctx_bf16, const float* x_in,
   TTSB_CHECK_CUDA(dcl::launch_cluster(dcl::ffn_block_kernel, (R + dcl::kRows - 1) / dcl::kRows, dcl::kSmemB,
                                       static_cast<cudaStream_t>(s), p));
   return TTSB_OK;
+}
+
+// experiments: mode 1 = record the phase timeline of ffn_block (CTA 0, thread 0), 0 = off, 2 = read 16 values
+extern "C" int ttsb200_debug_dcl_trace(long long* dst, int mode) {
+  if (mode == 0 || mode == 1) return cudaMemcpyToSymbol(ttsb::dcl::g_dcl_trace_on, &mode, sizeof(int)) == cudaSuccess ? 0 : -1;
+  return cudaMemcpyFromSymbol(dst, ttsb::dcl::g_dcl_trace, 16 * sizeof(long long)) == cudaSuccess ? 0 : -1;
 }

@@ -68,6 +68,7 @@ _SIGNATURES = {
                              C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
                              C.c_int32, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_advance_pos": ([C.c_void_p, C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_debug_dcl_trace": ([C.c_void_p, C.c_int], C.c_int),
     "ttsb200_decode_attn_out_q": ([C.c_void_p] * 8 + [C.c_float, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_decode_ffn_block": ([C.c_void_p] * 14 + [C.c_float, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
                                                     C.c_void_p], C.c_int),
