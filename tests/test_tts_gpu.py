@@ -304,3 +304,32 @@ def test_generate_early_exit_on_stop(world):
     assert out["steps"] == 8 and out["stop_step"].tolist() == [1, 1]
     assert torch.equal(out["mel"], full["mel"][:, :8 * hp.reduction_rate])      # the mel head is untouched by the stop bias
     assert full["steps"] == 64
+
+
+def test_other_shapes_batch_above_one_cluster_and_reduction_rate_1():
+    """Batch 19 (two row tiles / clusters) and a model with reduction_rate = 1 (stop logits (B, T) as the reference squeezes
+    them, transformer.py:111) and 2 decoder blocks: generate and the teacher-forced forward against the oracle."""
+    from oracle import transformer_tts_oracle as T
+    from transformer_tts_b200 import build_transformer_tts, synth
+
+    hp = synth.make_tts_hp(reduction_rate=1, n_layer_decoder=2, n_layer_encoder=2)
+    sd = synth.synth_tts_state_dict(hp, seed=3)
+    model = build_transformer_tts(hp).eval()
+    model.load_state_dict(sd)
+    model = model.cuda()
+    text, pos, _ = synth.synth_text_batch(19, 21, ragged=True, seed=9)
+    n = 7
+    out = model.generate(text.cuda(), (pos != 0).unsqueeze(-2).cuda(), max_steps=n)
+    with torch.no_grad():
+        o = T.greedy_decode_cached(sd, vars(hp), text, pos, n)
+    assert out["mel"].shape == (19, n, hp.mel_dim) and out["stop_logits"].shape == (19, n, 1)
+    assert rel(out["mel"], o["mel"]) < 1e-2 and rel(out["stop_logits"], o["stop_logits"]) < 1e-2
+    trg = torch.randn(19, 5, hp.mel_dim, generator=torch.Generator().manual_seed(1))
+    pos_mel = torch.arange(1, 6).unsqueeze(0).repeat(19, 1)
+    pos_mel[3, 2:] = 0
+    src_mask, trg_mask = T.create_masks(pos, pos_mel)
+    with torch.no_grad():
+        pre, post, stop, *_ = model(text.cuda(), trg.cuda(), src_mask.cuda(), trg_mask.cuda(), None, training=False)
+        ref = T.transformer_forward(sd, vars(hp), text, trg, src_mask, trg_mask)
+    assert tuple(stop.shape) == (19, 5) == tuple(ref["stop_token"].shape)       # squeezed, as the reference returns it
+    assert rel(pre, ref["outputs_prenet"]) < 1e-2 and rel(stop, ref["stop_token"]) < 1e-2

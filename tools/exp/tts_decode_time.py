@@ -65,5 +65,5 @@ for _ in range(3):
     torch.cuda.synchronize()
 buf = (ctypes.c_longlong * 16)()
 L_.ttsb200_debug_dcl_trace(buf, 2); L_.ttsb200_debug_dcl_trace(None, 0)
-names = ["start", "prefetch issued", "dependency wait", "ctx landed", "out-proj + push", "barrier 1", "LayerNorm 3", "FFN1 mma", "H push", "W2 + barrier 2", "FFN2 mma", "u push", "barrier 3", "tail"]
+names = ["start", "prefetch issued", "dependency wait", "ctx landed", "out-proj + push", "barrier 1", "LayerNorm 3", "FFN1 mma", "hidden slice", "FFN2 first half + scatter", "W2 second half landed", "FFN2 second half + scatter", "barrier 2", "tail"]
 print("ffn_block timeline (clk, isolated launch): " + ", ".join(f"{n} {buf[i] - (buf[i-1] if i else 0)}" for i, n in enumerate(names)))

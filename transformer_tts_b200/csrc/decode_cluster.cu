@@ -9,7 +9,7 @@
 // barrier replaces the kernel boundary.
 //
 //   attn_out_q : x' = x + ctx Wo^T + bo (Models/layers.py:112);  q = LN2(x') Wq^T + bq (layers.py:114-115, modules.py:50)
-//   ffn_block  : x' = x + ctx Wo^T + bo (layers.py:116);  h = relu(LN3(x') W1^T + b1);  u = h W2^T + b2;
+//   ffn_block  : x' = x + ctx Wo^T + bo (layers.py:116);  h = relu(LN3(x') W1^T + b1);  u = h W2^T + b2 (split over K);
 //                z = x' + LN_ff(u + LN3(x')) (layers.py:118-122, modules.py:81-87);  zn = bf16(LN_next(z))
 //
 // Arithmetic is that of the unfused kernels (bf16 operands, fp32 accumulation, fp32 residual stream, two-pass LayerNorm).
@@ -325,25 +325,28 @@ struct FfnBlock {
   int R;
 };
 
-// shared memory: Wo slice | W1 slice (later: second K half of the W2 slice) | first K half of the W2 slice |
-// H (bf16 [16][1536]; before barrier #1 the ctx tile at its start and the out-projection's scratch behind it) |
-// X fp32 [16][384] (after LayerNorm 3: scratch of FFN1 / FFN2) | A1 = LN3(x') bf16 | x' row of this CTA | u row | small vectors
-constexpr int kHalfK = kHid / 2;                                // 768
-constexpr int kRbW2 = kHalfK * 2 + kPad;                        // 1552 bytes per half row of the W2 slice
+// FFN2 is split over K, not N: every CTA contracts its OWN 96 hidden columns against the matching 96 K-columns of all 384
+// W2 rows, and the 16 partial sums of output row r meet on CTA r (24 KB out per CTA, no exchange of the hidden activation,
+// no barrier between FFN1 and FFN2).
+// shared memory: Wo slice | W1 slice (later: rows 192..383 of the W2 K-slice) | rows 0..191 of the W2 K-slice |
+// R0 (ctx tile + out-projection scratch; after barrier #1: the 16 partial u rows this CTA receives) |
+// X fp32 [16][384] (after LayerNorm 3: FFN1 scratch) | A1 = LN3(x') bf16 | hidden slice bf16 [16][96] | x' row | u row | vectors
+constexpr int kRbK = kColsH * 2 + kPad;                         // 208 bytes: one row of the W2 K-slice / of the hidden slice
+constexpr int kHalfN = kD / 2;                                  // 192 W2 rows per half
 constexpr int kOffW1 = kColsD * kRbD;
 constexpr int kOffW2a = kOffW1 + kColsH * kRbD;
-constexpr int kOffH = kOffW2a + kColsD * kRbW2;
-constexpr int kOffX = kOffH + kRows * kRbH;
+constexpr int kOffR0 = kOffW2a + kHalfN * kRbK;
+constexpr int kOffX = kOffR0 + kRows * kD * 4;
 constexpr int kOffA1 = kOffX + kRows * kD * 4;
-constexpr int kOffXrow = kOffA1 + kRows * kRbD;
+constexpr int kOffHs = kOffA1 + kRows * kRbD;
+constexpr int kOffXrow = kOffHs + kRows * kRbK;
 constexpr int kOffU = kOffXrow + kD * 4;
-constexpr int kOffVec = kOffU + kD * 4;                         // bo[24] | b2[24] | b1[96] | residual slice [16][24]
-constexpr int kVecBytes = (kColsD + kColsD + kColsH + kRows * kColsD) * 4;
+constexpr int kOffVec = kOffU + kD * 4;                         // bo[24] | b1[96] | b2[384] | residual slice [16][24]
+constexpr int kVecBytes = (kColsD + kColsH + kD + kRows * kColsD) * 4;
 constexpr int kSmemB = kOffVec + kVecBytes;
-constexpr int kRedFloats = 8 * 3 * 128;                         // FFN2: 8 k-slices x 3 n-tiles (= FFN1: 2 x 12)
-static_assert(kColsD * kRbW2 <= kColsH * kRbD, "the second half of the W2 slice must fit where the W1 slice was");
-static_assert((kRedFloats + kRows * kColsH) * 4 <= kRows * kD * 4, "FFN scratch must fit in the X tile");
-static_assert(kRows * kRbD + (1024 + kRows * kColsD) * 4 <= kRows * kRbH, "out-projection scratch must fit behind the ctx tile");
+static_assert(kHalfN * kRbK <= kColsH * kRbD, "the second half of the W2 K-slice must fit where the W1 slice was");
+static_assert(4 * (kColsH / 8) * 128 * 4 <= kRows * kD * 4, "FFN1 scratch (4 k-slices x 12 n-tiles) must fit in the X tile");
+static_assert(kRows * kRbD + (1024 + kRows * kColsD) * 4 <= kRows * kD * 4, "ctx tile + out-projection scratch must fit in R0");
 static_assert(kSmemB <= 231424, "shared memory budget (1 KB is static)");
 
 __global__ void __launch_bounds__(kThreads, 1) ffn_block_kernel(const FfnBlock p) {
@@ -351,19 +354,20 @@ __global__ void __launch_bounds__(kThreads, 1) ffn_block_kernel(const FfnBlock p
   uint8_t* sWo = sm;
   uint8_t* sW1 = sm + kOffW1;
   uint8_t* sW2a = sm + kOffW2a;
-  uint8_t* sH = sm + kOffH;
+  uint8_t* sR0 = sm + kOffR0;
+  float* sPart = reinterpret_cast<float*>(sR0);                 // [16 source CTAs][384]
   float* sX = reinterpret_cast<float*>(sm + kOffX);
   uint8_t* sA1 = sm + kOffA1;
+  uint8_t* sHs = sm + kOffHs;
   float* sXrow = reinterpret_cast<float*>(sm + kOffXrow);
   float* sU = reinterpret_cast<float*>(sm + kOffU);
   float* sBo = reinterpret_cast<float*>(sm + kOffVec);
-  float* sB2 = sBo + kColsD;
-  float* sB1 = sB2 + kColsD;
-  float* sRes = sB1 + kColsH;
-  float* red0 = reinterpret_cast<float*>(sH + kRows * kRbD);    // out-projection scratch, behind the ctx tile
+  float* sB1 = sBo + kColsD;
+  float* sB2 = sB1 + kColsH;
+  float* sRes = sB2 + kD;
+  float* red0 = reinterpret_cast<float*>(sR0 + kRows * kRbD);   // out-projection scratch, behind the ctx tile
   float* stage0 = red0 + 1024;
-  float* red = sX;                                              // FFN scratch: the X tile after LayerNorm 3
-  float* stage = sX + kRedFloats;
+  float* red = sX;                                              // FFN1 scratch: the X tile after LayerNorm 3
   const uint32_t rank = cluster_rank();
   const int r0 = (blockIdx.x / kCluster) * kRows;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -374,10 +378,10 @@ __global__ void __launch_bounds__(kThreads, 1) ffn_block_kernel(const FfnBlock p
   // everything immutable leaves for shared memory / registers before the predecessor has finished
   load_w_slice(sWo, kRbD, p.wo, kD, rank * kColsD, kColsD, kD);
   load_w_slice(sW1, kRbD, p.w1, kD, rank * kColsH, kColsH, kD);
-  load_w_cols(sW2a, kRbW2, p.w2, kHid, rank * kColsD, kColsD, 0, kHalfK);
+  load_w_cols(sW2a, kRbK, p.w2, kHid, 0, kHalfN, rank * kColsH, kColsH);
   load_f32(sBo, p.bo + rank * kColsD, kColsD);
-  load_f32(sB2, p.b2 + rank * kColsD, kColsD);
   load_f32(sB1, p.b1 + rank * kColsH, kColsH);
+  load_f32(sB2, p.b2, kD);
   const LnParams ln3 = load_ln(p.ln3_g, p.ln3_b);
   LnParams lnff, lnn;
   if (warp == 0) {
@@ -387,70 +391,101 @@ __global__ void __launch_bounds__(kThreads, 1) ffn_block_kernel(const FfnBlock p
   DCL_T(1);
   pdl_wait();
   DCL_T(2);
-  load_rows_bf16(sH, p.ctx, r0, p.R);           // the ctx tile borrows the start of H
+  load_rows_bf16(sR0, p.ctx, r0, p.R);
   load_res_slice(sRes, p.x_in, r0, p.R, rank * kColsD);
   cp_async_wait_all();
   __syncthreads();
   DCL_T(3);
-  out_proj_push(sH, sWo, sBo, sRes, nullptr, sX, red0, stage0, r0, p.R, rank);
+  out_proj_push(sR0, sWo, sBo, sRes, nullptr, sX, red0, stage0, r0, p.R, rank);
   DCL_T(4);
-  cluster_barrier();                            // #1: full rows of x' everywhere; nobody reads the ctx tile any more
+  cluster_barrier();                            // #1: full rows of x' everywhere; R0 is free to receive partial sums
   DCL_T(5);
   layernorm_rows(sX, sA1, ln3, p.eps);
   for (int i = threadIdx.x; i < kD; i += kThreads) sXrow[i] = sX[rank * kD + i];   // the tail's residual row
   __syncthreads();                              // the X tile is scratch from here on
   DCL_T(6);
-  // ---- FFN1 slice: 96 hidden columns ----
-  slice_mma<2>(sA1, kRbD, sW1, kRbD, kColsH / 8, kD / 32, red);
+  // ---- FFN1 slice: this CTA's 96 hidden columns = 12 n-tiles x 4 k-slices of 3 k-blocks; warp w takes k-slice w & 3 and
+  // n-tiles (w >> 2) + 4 i: the activation fragments of its k-slice are loaded once and used for its three n-tiles (a task
+  // per (n-tile, k-slice) re-read them every time: 4 k clk, shared-memory bandwidth) ----
+  {
+    constexpr int KS = 4, PER = kD / 32 / KS, NT = kColsH / 8;
+    const int g = lane >> 2, tq = lane & 3;
+    const int ks = warp & (KS - 1);
+    uint4 a[PER], b[PER];
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {
+      a[i] = *reinterpret_cast<const uint4*>(sA1 + g * kRbD + tq * 16 + (ks * PER + i) * 64);
+      b[i] = *reinterpret_cast<const uint4*>(sA1 + (g + 8) * kRbD + tq * 16 + (ks * PER + i) * 64);
+    }
+    for (int nt = warp >> 2; nt < NT; nt += kWarps / KS) {
+      const uint8_t* wa = sW1 + (nt * 8 + g) * kRbD + tq * 16 + ks * PER * 64;
+      float c0[4] = {0.f, 0.f, 0.f, 0.f}, c1[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int i = 0; i < PER; ++i) {
+        const uint4 w = *reinterpret_cast<const uint4*>(wa + i * 64);
+        mma_bf16_16816(c0, a[i].x, b[i].x, a[i].y, b[i].y, w.x, w.y);
+        mma_bf16_16816(c1, a[i].z, b[i].z, a[i].w, b[i].w, w.z, w.w);
+      }
+      *reinterpret_cast<float4*>(red + ((ks * NT + nt) * 32 + lane) * 4) =
+          make_float4(c0[0] + c1[0], c0[1] + c1[1], c0[2] + c1[2], c0[3] + c1[3]);
+    }
+  }
   __syncthreads();
   DCL_T(7);
-  load_w_cols(sW1, kRbW2, p.w2, kHid, rank * kColsD, kColsD, kHalfK, kHalfK);   // second K half of W2, in flight during the push
-  {
-    __nv_bfloat16* hs = reinterpret_cast<__nv_bfloat16*>(stage);
-    const int c0 = rank * kColsH;
-    for (int i = threadIdx.x; i < kRows * kColsH; i += kThreads) {
-      const int row = i / kColsH, col = i - row * kColsH;
-      hs[i] = __float2bfloat16(fmaxf(slice_value<2>(red, kColsH / 8, row, col) + sB1[col], 0.f));
-    }
-    __syncthreads();
-    // push: 16 rows x 96 bf16 = 16 x 12 uint4 per target CTA
-    const uint32_t h_addr = smem_u32(sH);
-    constexpr int VPR = kColsH / 8;
-    for (int i = threadIdx.x; i < kCluster * kRows * VPR; i += kThreads) {
-      const int tgt = i / (kRows * VPR), j = i - tgt * (kRows * VPR);
-      const int row = j / VPR, v8 = j - row * VPR;
-      const uint4 v = *reinterpret_cast<const uint4*>(hs + row * kColsH + v8 * 8);
-      st_cluster_v4(map_to_cta(h_addr + row * kRbH + (c0 + v8 * 8) * 2, tgt), v);
-    }
+  load_w_cols(sW1, kRbK, p.w2, kHid, kHalfN, kHalfN, rank * kColsH, kColsH);   // W2 rows 192..383 replace the W1 slice
+  for (int i = threadIdx.x; i < kRows * kColsH; i += kThreads) {
+    const int row = i / kColsH, col = i - row * kColsH;
+    reinterpret_cast<__nv_bfloat16*>(sHs + row * kRbK)[col] =
+        __float2bfloat16(fmaxf(slice_value<4>(red, kColsH / 8, row, col) + sB1[col], 0.f));
   }
-  DCL_T(8);
-  cp_async_wait_all();
-  cluster_barrier();                            // #2: the full hidden rows everywhere (and this CTA's W2 slice is complete)
-  DCL_T(9);
-  // ---- FFN2 slice: 24 output columns, K = 1536 in 8 contiguous k-slices of 6 k-blocks ----
-  slice_mma_split<8>(sH, kRbH, sW2a, sW1, kRbW2, kHalfK / 32, kColsD / 8, kHid / 32 / 8, red);
   __syncthreads();
-  DCL_T(10);
+  DCL_T(8);
+  // ---- FFN2 over this CTA's K-slice: partial u[16][384]; row r's partial goes to CTA r ----
   {
-    // u[row][c0 + col] goes to the CTA that owns the row's tail (row r -> CTA r): 24 floats = 6 float4 per row
-    const int c0 = rank * kColsD;
-    for (int i = threadIdx.x; i < kRows * kColsD; i += kThreads) {
-      const int row = i / kColsD, col = i - row * kColsD;
-      stage[i] = slice_value<8>(red, kColsD / 8, row, col) + sB2[col];
+    const int g = lane >> 2, tq = lane & 3;
+    uint4 a[kColsH / 32], b[kColsH / 32];       // the hidden slice's fragments: loaded once, used for every n-tile
+#pragma unroll
+    for (int kb = 0; kb < kColsH / 32; ++kb) {
+      a[kb] = *reinterpret_cast<const uint4*>(sHs + g * kRbK + tq * 16 + kb * 64);
+      b[kb] = *reinterpret_cast<const uint4*>(sHs + (g + 8) * kRbK + tq * 16 + kb * 64);
     }
+    const uint32_t part_addr = smem_u32(sPart);
+    auto tiles = [&](const uint8_t* W, int nt0) {
+      for (int t = warp; t < kHalfN / 8; t += kWarps) {
+        const uint8_t* wa = W + (t * 8 + g) * kRbK + tq * 16;
+        float c0[4] = {0.f, 0.f, 0.f, 0.f}, c1[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int kb = 0; kb < kColsH / 32; ++kb) {
+          const uint4 w = *reinterpret_cast<const uint4*>(wa + kb * 64);
+          mma_bf16_16816(c0, a[kb].x, b[kb].x, a[kb].y, b[kb].y, w.x, w.y);
+          mma_bf16_16816(c1, a[kb].z, b[kb].z, a[kb].w, b[kb].w, w.z, w.w);
+        }
+        const uint32_t off = part_addr + (rank * kD + (nt0 + t) * 8 + tq * 2) * 4;
+        st_cluster_v2(map_to_cta(off, g), make_uint2(__float_as_uint(c0[0] + c1[0]), __float_as_uint(c0[1] + c1[1])));
+        st_cluster_v2(map_to_cta(off, g + 8), make_uint2(__float_as_uint(c0[2] + c1[2]), __float_as_uint(c0[3] + c1[3])));
+      }
+    };
+    tiles(sW2a, 0);
+    DCL_T(9);
+    cp_async_wait_all();
     __syncthreads();
-    const uint32_t u_addr = smem_u32(sU);
-    for (int i = threadIdx.x; i < kRows * (kColsD / 4); i += kThreads) {
-      const int row = i / (kColsD / 4), q4 = i - row * (kColsD / 4);
-      const uint4 v = *reinterpret_cast<const uint4*>(stage + row * kColsD + q4 * 4);
-      st_cluster_v4(map_to_cta(u_addr + (c0 + q4 * 4) * 4, row), v);
-    }
+    DCL_T(10);
+    tiles(sW1, kHalfN / 8);
   }
   DCL_T(11);
-  cluster_barrier();                            // #3: CTA r holds the full row r of u
+  cluster_barrier();                            // #2: CTA r holds the 16 partial sums of row r
   DCL_T(12);
-  // ---- tail of row `rank`: z = x' + LN_ff(u + LN3(x'));  zn = bf16(LN_next(z)) ----
+  // ---- tail of row `rank`: u = sum of the partials + b2;  z = x' + LN_ff(u + LN3(x'));  zn = bf16(LN_next(z)) ----
   const int row = r0 + static_cast<int>(rank);
+  if (row < p.R) {
+    for (int k = threadIdx.x; k < kD; k += kThreads) {
+      float u = sB2[k];
+#pragma unroll
+      for (int src = 0; src < kCluster; ++src) u += sPart[src * kD + k];
+      sU[k] = u;
+    }
+  }
+  __syncthreads();
   if (warp == 0 && row < p.R) {
     constexpr int NV = kNV;
     float v[NV];
