@@ -7,15 +7,20 @@
 // mma.sync.m16n8k16 tile in M.  The work is streaming the layer weights (28 MB bf16 for six layers, L2-resident) and
 // the cached keys / values; there is no tile big enough for tcgen05 (M = 128 minimum), so these are warp-level kernels:
 //
-//   small_linear : y = act(LN?(x) W^T + b) (+ residual) (+ alpha * pe[pos]); each warp owns 8 output columns, the R
-//                  input rows (LayerNorm applied while staging) sit in shared memory as the A operand, W rows stream
-//                  from L2 with 16-byte loads straight into B fragments (the contraction index is permuted so that a
-//                  16-byte load of one W row is two k-steps' worth of fragments);
+//   small_linear : y = act(LN?(x) W^T + b) (+ residual) (+ alpha * pe[pos]); 32 output columns per CTA (8 warps = 4 column
+//                  groups x 2 k-slices); the CTA's W rows and the R input rows travel to shared memory by cp.async, all in
+//                  flight at once; fp32 rows are normalised from shared memory; the contraction index is permuted so that
+//                  a 16-byte vector of a W row is two k-steps' worth of B fragments;
 //   attn_decode  : one query per (utterance, head) against the cached keys/values (appending this step's first):
-//                  thread-per-key dot products with 16-byte loads, block softmax, 12-thread-per-key P.V.
+//                  thread-per-key dot products with 16-byte loads, block softmax, 12-thread-per-key P.V;
+//   ffn_tail_rows: FeedForward tail + the next LayerNorm for a few rows.
 //
+// What costs time here is the number of DEPENDENT memory round trips and launches, not bytes: kernels
+// launch with programmatic dependent launch and load what is immutable before waiting for their predecessor; the
+// stretches between a block's attentions run as thread-block-cluster kernels (decode_cluster.cu).
 // Position-dependent addressing (which cache slot, which positional-encoding row, where the step's output goes) reads a
-// device scalar, so one captured CUDA graph replays for every step.
+// device scalar, so one captured CUDA graph replays for every step.  TTSB_NO_PDL=1 in the environment launches without
+// the dependent-launch attribute (A/B: B = 1, 378 -> 327 us per position with it).
 #include <cuda_bf16.h>
 #include <stdlib.h>
 

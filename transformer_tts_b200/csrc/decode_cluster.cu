@@ -27,7 +27,6 @@ constexpr int kRows = 16;
 constexpr int kThreads = 512, kWarps = 16;
 constexpr int kPad = 16;
 constexpr int kRbD = kD * 2 + kPad;        // padded bf16 row of 384: 784 bytes
-constexpr int kRbH = kHid * 2 + kPad;      // padded bf16 row of 1536: 3088 bytes
 constexpr int kColsD = kD / kCluster;      // 24 output columns per CTA of a 384-wide linear
 constexpr int kColsH = kHid / kCluster;    // 96 hidden columns per CTA
 
@@ -127,42 +126,6 @@ __device__ __forceinline__ void slice_mma(const uint8_t* A, int a_rb, const uint
       const uint4 a = *reinterpret_cast<const uint4*>(xa + kb * 64);
       const uint4 b = *reinterpret_cast<const uint4*>(xb + kb * 64);
       const uint4 w = *reinterpret_cast<const uint4*>(wa + kb * 64);
-      mma_bf16_16816(acc[0], a.x, b.x, a.y, b.y, w.x, w.y);
-      mma_bf16_16816(acc[1], a.z, b.z, a.w, b.w, w.z, w.w);
-    }
-    *reinterpret_cast<float4*>(red + ((ks * n_tiles + nt) * 32 + lane) * 4) =
-        make_float4((acc[0][0] + acc[1][0]) + (acc[2][0] + acc[3][0]), (acc[0][1] + acc[1][1]) + (acc[2][1] + acc[3][1]),
-                    (acc[0][2] + acc[1][2]) + (acc[2][2] + acc[3][2]), (acc[0][3] + acc[1][3]) + (acc[2][3] + acc[3][3]));
-  }
-}
-// The same with CONTIGUOUS k-slices of `per` k-blocks each, the weights' K range split over two buffers at k-block
-// `split` (FFN2: the first half of the W2 slice is prefetched, the second half arrives where the W1 slice was).
-template <int KS>
-__device__ __forceinline__ void slice_mma_split(const uint8_t* A, int a_rb, const uint8_t* Wa, const uint8_t* Wb, int w_rb,
-                                                int split, int n_tiles, int per, float* red) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int g = lane >> 2, tq = lane & 3;
-  for (int t = warp; t < n_tiles * KS; t += kWarps) {
-    const int nt = t % n_tiles, ks = t / n_tiles;
-    const int kb0 = ks * per;
-    const uint8_t* xa = A + g * a_rb + tq * 16 + kb0 * 64;
-    const uint8_t* xb = xa + 8 * a_rb;
-    const uint8_t* wa = (kb0 < split ? Wa + kb0 * 64 : Wb + (kb0 - split) * 64) + (nt * 8 + g) * w_rb + tq * 16;
-    float acc[4][4] = {};   // four independent accumulator chains (see slice_mma)
-    int i = 0;
-    for (; i + 1 < per; i += 2) {
-      const uint4 a0 = *reinterpret_cast<const uint4*>(xa + i * 64), a1 = *reinterpret_cast<const uint4*>(xa + (i + 1) * 64);
-      const uint4 b0 = *reinterpret_cast<const uint4*>(xb + i * 64), b1 = *reinterpret_cast<const uint4*>(xb + (i + 1) * 64);
-      const uint4 w0 = *reinterpret_cast<const uint4*>(wa + i * 64), w1 = *reinterpret_cast<const uint4*>(wa + (i + 1) * 64);
-      mma_bf16_16816(acc[0], a0.x, b0.x, a0.y, b0.y, w0.x, w0.y);
-      mma_bf16_16816(acc[1], a0.z, b0.z, a0.w, b0.w, w0.z, w0.w);
-      mma_bf16_16816(acc[2], a1.x, b1.x, a1.y, b1.y, w1.x, w1.y);
-      mma_bf16_16816(acc[3], a1.z, b1.z, a1.w, b1.w, w1.z, w1.w);
-    }
-    if (i < per) {
-      const uint4 a = *reinterpret_cast<const uint4*>(xa + i * 64);
-      const uint4 b = *reinterpret_cast<const uint4*>(xb + i * 64);
-      const uint4 w = *reinterpret_cast<const uint4*>(wa + i * 64);
       mma_bf16_16816(acc[0], a.x, b.x, a.y, b.y, w.x, w.y);
       mma_bf16_16816(acc[1], a.z, b.z, a.w, b.w, w.z, w.w);
     }

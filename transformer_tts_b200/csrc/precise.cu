@@ -473,29 +473,40 @@ attention_x3_kernel(const __half* __restrict__ qkv, const uint8_t* __restrict__ 
     asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
     __syncthreads();
 
-    // ---- S = Q K^T (16 x 64 per warp) ----
+    // ---- S = Q K^T (16 x 64 per warp).  mma.sync has a long latency on this part and a warp issues in order: the eight key
+    // blocks' accumulator chains are interleaved (k-step outer, key block inner) instead of run one after the other; every
+    // chain still sees its k-steps in the same order, so the result is bit-identical ----
     float s[8][4];
+    {
+      float c_lo[8][4], c_hi[8][4];
 #pragma unroll
-    for (int nb = 0; nb < 8; ++nb) {
-      float c_lo[4] = {0.f, 0.f, 0.f, 0.f}, c_hi[4] = {0.f, 0.f, 0.f, 0.f};
-      const __half* kh = sKh + (nb * 8 + g) * kAPitch + 2 * t4;
-      const __half* kl = sKl + (nb * 8 + g) * kAPitch + 2 * t4;
+      for (int nb = 0; nb < 8; ++nb)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) c_lo[nb][i] = c_hi[nb][i] = 0.f;
 #pragma unroll
       for (int j = 0; j < 6; ++j) {
-        const uint32_t bh0 = *reinterpret_cast<const uint32_t*>(kh + 16 * j);
-        const uint32_t bh1 = *reinterpret_cast<const uint32_t*>(kh + 16 * j + 8);
-        const uint32_t bl0 = *reinterpret_cast<const uint32_t*>(kl + 16 * j);
-        const uint32_t bl1 = *reinterpret_cast<const uint32_t*>(kl + 16 * j + 8);
-        mma16816(c_lo, ql[j], bh0, bh1);
-        mma16816(c_lo, qh[j], bl0, bl1);
-        mma16816(c_hi, qh[j], bh0, bh1);
+#pragma unroll
+        for (int nb = 0; nb < 8; ++nb) {
+          const __half* kh = sKh + (nb * 8 + g) * kAPitch + 2 * t4;
+          const __half* kl = sKl + (nb * 8 + g) * kAPitch + 2 * t4;
+          const uint32_t bh0 = *reinterpret_cast<const uint32_t*>(kh + 16 * j);
+          const uint32_t bh1 = *reinterpret_cast<const uint32_t*>(kh + 16 * j + 8);
+          const uint32_t bl0 = *reinterpret_cast<const uint32_t*>(kl + 16 * j);
+          const uint32_t bl1 = *reinterpret_cast<const uint32_t*>(kl + 16 * j + 8);
+          mma16816(c_lo[nb], ql[j], bh0, bh1);
+          mma16816(c_lo[nb], qh[j], bl0, bl1);
+          mma16816(c_hi[nb], qh[j], bh0, bh1);
+        }
       }
 #pragma unroll
-      for (int i = 0; i < 4; ++i) s[nb][i] = (c_hi[i] + c_lo[i]) * s_scale;
-      // mask like the reference: -1e4 on padded keys (modules.py:14); keys beyond T do not exist
-      const uint8_t f0 = sflag[nb * 8 + 2 * t4], f1 = sflag[nb * 8 + 2 * t4 + 1];
-      if (f0 != 1) { const float mv = f0 == 0 ? -1e4f : -INFINITY; s[nb][0] = mv; s[nb][2] = mv; }
-      if (f1 != 1) { const float mv = f1 == 0 ? -1e4f : -INFINITY; s[nb][1] = mv; s[nb][3] = mv; }
+      for (int nb = 0; nb < 8; ++nb) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) s[nb][i] = (c_hi[nb][i] + c_lo[nb][i]) * s_scale;
+        // mask like the reference: -1e4 on padded keys (modules.py:14); keys beyond T do not exist
+        const uint8_t f0 = sflag[nb * 8 + 2 * t4], f1 = sflag[nb * 8 + 2 * t4 + 1];
+        if (f0 != 1) { const float mv = f0 == 0 ? -1e4f : -INFINITY; s[nb][0] = mv; s[nb][2] = mv; }
+        if (f1 != 1) { const float mv = f1 == 0 ? -1e4f : -INFINITY; s[nb][1] = mv; s[nb][3] = mv; }
+      }
     }
     // ---- online softmax (rows g: elements 0,1; rows g + 8: elements 2,3) ----
     float mx0 = -INFINITY, mx1 = -INFINITY;
@@ -526,23 +537,34 @@ attention_x3_kernel(const __half* __restrict__ qkv, const uint8_t* __restrict__ 
       split2(p0 * kAPScale, p1 * kAPScale, ph[jj][o2], pl[jj][o2]);
       split2(p2 * kAPScale, p3 * kAPScale, ph[jj][o2 + 1], pl[jj][o2 + 1]);
     }
-    // ---- O += P V (16 x 96 per warp); V fragments through ldmatrix.trans from the [key][dim] planes ----
+    // ---- O += P V (16 x 96 per warp); V fragments through ldmatrix.trans from the [key][dim] planes.  Chains interleaved
+    // as above: six dim blocks at a time, k-step outer ----
 #pragma unroll
-    for (int db = 0; db < 12; ++db) {
-      float c_lo[4] = {0.f, 0.f, 0.f, 0.f}, c_hi[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int half = 0; half < 2; ++half) {
+      float c_lo[6][4], c_hi[6][4];
+#pragma unroll
+      for (int d = 0; d < 6; ++d)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) c_lo[d][i] = c_hi[d][i] = 0.f;
 #pragma unroll
       for (int jj = 0; jj < 4; ++jj) {
         // lanes 0..15 supply the row addresses: keys 16jj + (lane & 15), dims [8db, 8db + 8)
         const int krow = 16 * jj + (lane & 15);
-        uint32_t vh0, vh1, vl0, vl1;
-        ldmatrix_x2_trans(vh0, vh1, smem_u32(sVh + krow * kAPitch + 8 * db));
-        ldmatrix_x2_trans(vl0, vl1, smem_u32(sVl + krow * kAPitch + 8 * db));
-        mma16816(c_lo, pl[jj], vh0, vh1);
-        mma16816(c_lo, ph[jj], vl0, vl1);
-        mma16816(c_hi, ph[jj], vh0, vh1);
+#pragma unroll
+        for (int d = 0; d < 6; ++d) {
+          const int db = half * 6 + d;
+          uint32_t vh0, vh1, vl0, vl1;
+          ldmatrix_x2_trans(vh0, vh1, smem_u32(sVh + krow * kAPitch + 8 * db));
+          ldmatrix_x2_trans(vl0, vl1, smem_u32(sVl + krow * kAPitch + 8 * db));
+          mma16816(c_lo[d], pl[jj], vh0, vh1);
+          mma16816(c_lo[d], ph[jj], vl0, vl1);
+          mma16816(c_hi[d], ph[jj], vh0, vh1);
+        }
       }
 #pragma unroll
-      for (int i = 0; i < 4; ++i) o[db][i] += c_hi[i] + c_lo[i];
+      for (int d = 0; d < 6; ++d)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) o[half * 6 + d][i] += c_hi[d][i] + c_lo[d][i];
     }
   }
   // ---- O / l -> fp16 hi | lo ----
