@@ -130,6 +130,11 @@ int ttsb200_attention_fwd_ragged(const void* qkv_bf16, const uint8_t* mask, cons
                                  int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t stream);
 int ttsb200_attention_fwd(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
                           int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t stream);
+/* The same under the CAUSAL and key-padding mask of Transformer-TTS (train.py:26-58; attn_1 of Models/layers.py:111):
+ * key j attends to query i only for j <= i; hidden keys get the reference's -1e4 fill.  Key tiles above the diagonal are
+ * never loaded. */
+int ttsb200_attention_fwd_causal(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
+                                 int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t stream);
 /* Training forward: same kernel, also writes lse2 (B,H,T) fp32 = log2-domain log-sum-exp of every
  * query row, so that p = exp2(s * log2(e)/sqrt(Dh) - lse2) in the backward kernels. */
 int ttsb200_attention_fwd_lse(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,

@@ -260,6 +260,30 @@ def test_attention(L, B, T, lens):
         assert max_err(probs, p_ref) < 1e-5
 
 
+@pytest.mark.parametrize("B,T,lens", [(2, 128, [128, 77]), (3, 333, [333, 129, 1]), (2, 1000, [1000, 640]), (1, 65, [65])])
+def test_attention_causal(L, B, T, lens):
+    """The causal AND key-padding mask of Transformer-TTS (train.py:26-58): hidden keys get the -1e4 fill; rows beyond an
+    utterance's length (padding queries) attend to its valid keys up to their own index, as in the reference."""
+    H, Dh = 4, 96
+    qkv = rnd(B, T, 3 * H * Dh, dtype=torch.bfloat16, seed=45)
+    mask = torch.zeros(B, T, dtype=torch.uint8, device=dev())
+    for i, n in enumerate(lens):
+        mask[i, :n] = 1
+    kv = L.mask_lengths(mask)
+    ctx = torch.empty(B, T, H * Dh, device=dev(), dtype=torch.bfloat16)
+    L.attention_fwd(qkv, mask, kv, ctx, H, causal=True)
+    torch.cuda.synchronize()
+    D = H * Dh
+    q, k, v = [t.double().view(B, T, H, Dh).transpose(1, 2) for t in qkv.split(D, dim=-1)]
+    s = q @ k.transpose(-1, -2) / math.sqrt(Dh)
+    full = (mask.view(B, 1, 1, T) != 0) & torch.tril(torch.ones(T, T, dtype=torch.bool, device=dev())).view(1, 1, T, T)
+    p = torch.softmax(s.masked_fill(~full, -1e4), dim=-1)
+    ref = (p @ v).transpose(1, 2).reshape(B, T, D)
+    assert rel_err(ctx, ref) < 1e-2, rel_err(ctx, ref)
+    # row 0 sees only key 0: its context is v[0] exactly (bf16)
+    assert torch.equal(ctx[:, 0], qkv[:, 0, 2 * D:])
+
+
 def test_attention_sparse_mask(L):
     """Non-prefix masks are honoured (the reference accepts any boolean key mask)."""
     B, T, H, Dh = 1, 260, 4, 96

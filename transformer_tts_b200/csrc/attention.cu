@@ -159,10 +159,15 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
   const int klen = kv_info[2 * b];          // 1 + index of the last valid key
   const int kprefix = kv_info[2 * b + 1];   // keys [0, kprefix) are all valid
   const int kv_eff = klen > 0 ? klen : T;   // no valid key: the reference degenerates to uniform over T
-  const int nkv = (kv_eff + kBKV - 1) / kBKV;
+  // skip_padded_q is a flag word: bit 0 = skip padded query tiles (ragged batches), bit 1 = CAUSAL: key j attends only
+  // for j <= query index, on top of the key-padding mask (the target mask of Transformer-TTS, train.py:26-58) — key tiles
+  // wholly above the tile's last query are never loaded, tiles that cross the diagonal take the flagged path below
+  const bool causal = (skip_padded_q & 2) != 0;
+  int nkv = (kv_eff + kBKV - 1) / kBKV;
+  if (causal) nkv = min(nkv, (q0 + kBQ - 1) / kBKV + 1);
   // ragged batches: a query tile wholly beyond the utterance's last valid row is padding (CTA-uniform exit, before
   // any barrier or TMEM allocation); its ctx rows stay unwritten
-  if (skip_padded_q && klen > 0 && q0 >= klen) return;
+  if ((skip_padded_q & 1) && klen > 0 && q0 >= klen) return;
 
   auto load_k = [&](int j) {
     const int ks = j % kKStages;
@@ -370,7 +375,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     for (int j = 0; j < nkv; ++j) {
       const uint32_t sb = j & 1;
       // a tile inside the all-valid prefix of the mask needs no flags (CTA-uniform decision)
-      const bool clean = (j + 1) * kBKV <= kprefix;
+      const bool clean = (j + 1) * kBKV <= kprefix && (!causal || (j + 1) * kBKV <= q0 + 1);
       uint8_t* flg = sflag + sb * kBKV;
       if (!clean) {
         if (st < kBKV) {
@@ -400,7 +405,9 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
 #pragma unroll
         for (int i = 0; i < CW; ++i) {
           const uint8_t f = flg[half * CW + i];
-          s[i] = f == 1 ? s[i] * scale_log2 : (f == 0 ? masked : -INFINITY);
+          // (causal: a key beyond this row's own index is filled like a padded one, as the reference's combined mask does)
+          const bool hidden = f == 0 || (causal && f == 1 && j * kBKV + half * CW + i > q0 + row);
+          s[i] = hidden ? masked : (f == 1 ? s[i] * scale_log2 : -INFINITY);
           mx4[i & 3] = fmaxf(mx4[i & 3], s[i]);
         }
       }
@@ -678,6 +685,11 @@ extern "C" int ttsb200_attention_fwd_drop(const void* qkv, const uint8_t* mask, 
 extern "C" int ttsb200_attention_fwd_ragged(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
                                             int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t s) {
   return attention_fwd_launch(qkv, mask, kv_info, ctx, nullptr, B, T, H, Dh, 1, s);
+}
+
+extern "C" int ttsb200_attention_fwd_causal(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
+                                            int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t s) {
+  return attention_fwd_launch(qkv, mask, kv_info, ctx, nullptr, B, T, H, Dh, 2, s);
 }
 
 extern "C" int ttsb200_attention_fwd(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,

@@ -78,6 +78,8 @@ _SIGNATURES = {
                                 C.c_void_p], C.c_int),
     "ttsb200_attention_fwd": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
                                C.c_int32, C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_attention_fwd_causal": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
+                                      C.c_int32, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_attention_fwd_ragged": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
                                       C.c_int32, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_attention_probs": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
@@ -282,12 +284,21 @@ def build_tile_map(lengths: torch.Tensor, T: int, halo: int = 0) -> tuple:
 # --------------------------------------------------------------------------------------------------
 def attention_fwd(qkv: torch.Tensor, mask: torch.Tensor, kv_len: torch.Tensor, ctx: torch.Tensor, H: int,
                   lse2: Optional[torch.Tensor] = None, skip_padded_queries: bool = False,
-                  drop: Optional[tuple] = None) -> None:
+                  drop: Optional[tuple] = None, causal: bool = False) -> None:
     """lse2 (B,H,T) fp32, when given, receives the log2-domain log-sum-exp of every row (training).
     skip_padded_queries: 128-row query tiles wholly beyond an utterance's last valid row are not computed.
-    drop = (p, seed, site): dropout on the probabilities (training, Models/modules.py:18-19)."""
+    drop = (p, seed, site): dropout on the probabilities (training, Models/modules.py:18-19).
+    causal: key j attends to query i only for j <= i (inference; the target mask of Transformer-TTS)."""
     B, T, W = qkv.shape
     Dh = W // (3 * H)
+    if causal:
+        if lse2 is not None or skip_padded_queries or (drop is not None and drop[0] > 0):
+            raise ValueError("attention_fwd: causal is an inference option (no lse2 / dropout / ragged query skipping)")
+        _check(load().ttsb200_attention_fwd_causal(_ptr(qkv, torch.bfloat16, "qkv"), _ptr(mask, torch.uint8, "mask"),
+                                                   _ptr(kv_len, torch.int32, "kv_len"), _ptr(ctx, torch.bfloat16, "ctx"),
+                                                   B, T, H, Dh, _stream()), "attention_fwd_causal")
+        _count()
+        return
     if drop is not None and drop[0] > 0:
         _check(load().ttsb200_attention_fwd_drop(_ptr(qkv, torch.bfloat16, "qkv"), _ptr(mask, torch.uint8, "mask"),
                                                  _ptr(kv_len, torch.int32, "kv_len"), _ptr(ctx, torch.bfloat16, "ctx"),
