@@ -445,6 +445,45 @@ def ar_decode_record(cpu: bool, positions: int = 1000, batch: int = 16, phonemes
            "stop_positions_rank0": [int(v) for v in out["stop_step"].cpu()],
            "what": "Transformer.generate: KV-cache decode, one CUDA graph replay (small_linear / attn_decode kernels, programmatic "
                    "dependent launch) per position; random-init weights, so the stop token fires at random: all positions are decoded"}
+    # teacher-forced prefix forward at BASELINE.json configs[3]'s shape (mel length 800 = 400 decoder positions at r = 2,
+    # 128 phonemes), batch 32: the tensor-core path of Transformer.forward (inference only: the training step, row f2, is
+    # not built) next to the same modules under stock PyTorch eager fp32 on this GPU (the oracle port)
+    try:
+        from oracle import transformer_tts_oracle as T
+
+        Bp, Tp = 32, 400
+        textp, posp, _ = synth.synth_text_batch(Bp, phonemes, ragged=True, seed=78, min_len=phonemes // 2)
+        trg = torch.randn(Bp, Tp, hp.mel_dim, generator=torch.Generator().manual_seed(79))
+        pos_mel = torch.arange(1, Tp + 1).unsqueeze(0).repeat(Bp, 1)
+        sm, tm = T.create_masks(posp, pos_mel)
+        a = (textp.cuda(), trg.cuda(), sm.cuda(), tm.cuda(), None)
+        for _ in range(2):
+            model(*a, training=False)
+        torch.cuda.synchronize()
+        tp = []
+        for _ in range(5):
+            e0.record()
+            model(*a, training=False)
+            e1.record()
+            torch.cuda.synchronize()
+            tp.append(e0.elapsed_time(e1))
+        sd_gpu = {k: v.cuda() for k, v in sd.items()}
+        with torch.no_grad():
+            T.transformer_forward(sd_gpu, vars(hp), *a[:4])
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(3):
+                T.transformer_forward(sd_gpu, vars(hp), *a[:4])
+            e1.record()
+            torch.cuda.synchronize()
+        eager_ms = e0.elapsed_time(e1) / 3
+        rec["teacher_forced_forward"] = {"ms": min(tp), "batch": Bp, "positions": Tp, "phonemes": phonemes,
+                                         "frames_per_s": Bp * Tp * hp.reduction_rate / min(tp) * 1e3,
+                                         "torch_eager_fp32_same_gpu_ms": eager_ms,
+                                         "what": "Transformer.forward(prefix_mode='batched'): tcgen05 GEMMs, causal tcgen05 attention, "
+                                                 "encoder-decoder attention on a packed sequence, fused FeedForward; inference only"}
+    except Exception as ex:  # noqa: BLE001 — a sub-record must not take the headline line down
+        rec["teacher_forced_forward"] = {"error": str(ex)[:200]}
     if cpu:
         from oracle import transformer_tts_oracle as T
 

@@ -333,3 +333,34 @@ def test_other_shapes_batch_above_one_cluster_and_reduction_rate_1():
         ref = T.transformer_forward(sd, vars(hp), text, trg, src_mask, trg_mask)
     assert tuple(stop.shape) == (19, 5) == tuple(ref["stop_token"].shape)       # squeezed, as the reference returns it
     assert rel(pre, ref["outputs_prenet"]) < 1e-2 and rel(stop, ref["stop_token"]) < 1e-2
+
+
+def test_batched_prefix_forward_matches_step_machine_and_oracle(world):
+    """Transformer.forward on a 300-position ragged prefix: the tensor-core path (causal tcgen05 attention, encoder-decoder
+    attention on the packed sequence, fused FeedForward) against the decode-step machine and against the oracle."""
+    from oracle import transformer_tts_oracle as T
+    from transformer_tts_b200 import synth
+
+    hp, sd, model = world
+    B, L, Tn = 3, 50, 300
+    text, pos, _ = synth.synth_text_batch(B, L, ragged=True, seed=61)
+    trg = torch.randn(B, Tn, hp.mel_dim, generator=torch.Generator().manual_seed(62))
+    pos_mel = torch.arange(1, Tn + 1).unsqueeze(0).repeat(B, 1)
+    pos_mel[1, 170:] = 0
+    pos_mel[2, 1:] = 0
+    src_mask, trg_mask = T.create_masks(pos, pos_mel)
+    args = (text.cuda(), trg.cuda(), src_mask.cuda(), trg_mask.cuda(), None)
+    assert model.prefix_mode == "batched"
+    with torch.no_grad():
+        pre_b, _, stop_b, *_ = model(*args, training=False)
+        model.prefix_mode = "steps"
+        try:
+            pre_s, _, stop_s, *_ = model(*args, training=False)
+        finally:
+            model.prefix_mode = "batched"
+        ref = T.transformer_forward(sd, vars(hp), text, trg, src_mask, trg_mask)
+    e_bs, e_bo, e_so = rel(pre_b, pre_s), rel(pre_b, ref["outputs_prenet"]), rel(pre_s, ref["outputs_prenet"])
+    print(f"prefix of {Tn} positions: batched vs steps {e_bs:.2e}; batched vs oracle {e_bo:.2e}; steps vs oracle {e_so:.2e}; "
+          f"stop logits batched vs oracle {rel(stop_b, ref['stop_token']):.2e}")
+    assert e_bo < 1e-2 and e_so < 1e-2 and e_bs < 1e-2
+    assert rel(stop_b, ref["stop_token"]) < 1e-2

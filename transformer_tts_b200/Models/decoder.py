@@ -216,9 +216,80 @@ class Decoder(nn.Module):
                     w1=lib.pad_weight_rows(ff.f_1.weight.detach()[:, :, 0]), b1=E._f32(ff.f_1.bias),
                     w2=lib.pad_weight_rows(ff.f_2.weight.detach()[:, :, 0]), b2=E._f32(ff.f_2.bias),
                 )
+                    # the same weights as (taps=1, N, C) conv_gemm operands, for the batched teacher-forced prefix (run_prefix)
+                for name in ("wqkv1", "wo1", "wq2", "wo2", "w1", "w2"):
+                    lc[name + "_g"] = lc[name].unsqueeze(0).contiguous()
                 t["layers"].append(lc)
+            fc1 = pn.fc1.weight.detach()
+            t["fc1_g"] = E._bf16(fc1).unsqueeze(0).contiguous()          # (1, 256, mel_dim): C = 80, partial K box
+            t["fc2_g"] = t["fc2_w"].unsqueeze(0).contiguous()
             c.commit(params)
         return c.t
+
+    def run_prefix(self, head: dict, trg: torch.Tensor, e_outputs: torch.Tensor, src_mask, trg_key_mask_u8: torch.Tensor):
+        """The decoder on a whole teacher-forced prefix at once (Models/decoder.py:43-56 as the reference evaluates it):
+        trg (B, T, mel_dim) decoder inputs -> (B, T, head rows) fp32 = [mel (r frames) | stop (r)] per position.
+
+        Tensor-core path: the tcgen05 GEMMs and the fused FeedForward of the FastSpeech2 blocks, the tcgen05 attention
+        with the CAUSAL flag for attn_1, and for attn_2 (queries = decoder rows, keys = encoder rows) the same attention
+        kernel on a packed sequence [encoder rows | decoder rows] whose key mask admits only the encoder rows — valid keys
+        form a prefix, so every query tile loads ceil(L / 64) key tiles; the encoder rows' own outputs are discarded."""
+        E.require_inference(self, "Decoder")
+        t = self._cache()
+        B, T, _ = trg.shape
+        L, D, H = e_outputs.shape[1], self.norm.weight.numel(), self.heads
+        dev = trg.device
+        bf16, f32 = torch.bfloat16, torch.float32
+        if T > t["pe"].shape[0]:
+            raise ValueError(f"{T} decoder positions exceed the positional table ({t['pe'].shape[0]}, modules.py:92)")
+        e_bf16 = e_outputs.to(bf16).contiguous()
+        m_src = E.mask_to_u8(src_mask, B, L, dev)
+        kv_trg = lib.mask_lengths(trg_key_mask_u8)
+        maskp = torch.zeros((B, L + T), device=dev, dtype=torch.uint8)
+        maskp[:, :L] = m_src
+        kvp = lib.mask_lengths(maskp)
+        # prenet (prenets.py:33-38) + positional encoding (modules.py:107-111)
+        h1 = torch.empty((B, T, t["fc1_g"].shape[1]), device=dev, dtype=bf16)
+        lib.conv_gemm(trg.to(bf16).contiguous(), t["fc1_g"], t["fc1_b"], block_n=128, act=lib.ACT_RELU, out_bf16=h1)
+        pe = (t["alpha"] * t["pe"][:T]).contiguous()
+        x = torch.empty((B, T, D), device=dev, dtype=f32)
+        lib.conv_gemm(h1, t["fc2_g"], t["fc2_b"], block_n=128, act=lib.ACT_RELU, res_f32=pe, res_bstride=0, res_tstride=D,
+                      out_f32=x)
+        xn = torch.empty((B, T, D), device=dev, dtype=bf16)
+        l0 = t["layers"][0]
+        lib.layernorm(x, l0["ln1"][0], l0["ln1"][1], E.LN_EPS, y_bf16=xn)
+        packed = torch.zeros((B, L + T, 3 * D), device=dev, dtype=bf16)
+        n_layers = len(t["layers"])
+        for i, lc in enumerate(t["layers"]):
+            qkv = torch.empty((B, T, 3 * D), device=dev, dtype=bf16)
+            lib.conv_gemm(xn, lc["wqkv1_g"], lc["bqkv1"], block_n=192, out_bf16=qkv)
+            ctx = torch.empty((B, T, D), device=dev, dtype=bf16)
+            lib.attention_fwd(qkv, trg_key_mask_u8, kv_trg, ctx, H, causal=True)                       # layers.py:111
+            x2 = torch.empty((B, T, D), device=dev, dtype=f32)
+            x2n = torch.empty((B, T, D), device=dev, dtype=bf16)
+            lib.conv_gemm(ctx, lc["wo1_g"], lc["bo1"], block_n=D, epi=lib.EPI_RES_LN, res_f32=x, res_bstride=T * D,
+                          res_tstride=D, ln1=lc["ln2"], out_f32=x2, out_bf16=x2n)                      # :112, :114
+            q2 = torch.empty((B, T, D), device=dev, dtype=bf16)
+            lib.conv_gemm(x2n, lc["wq2_g"], lc["bq2"], block_n=128, out_bf16=q2)
+            kv = torch.empty((B, L, 2 * D), device=dev, dtype=bf16)
+            lib.conv_gemm(e_bf16, lc["wkv2"], lc["bkv2"], block_n=128, out_bf16=kv)
+            packed[:, :L, D:] = kv
+            packed[:, L:, :D] = q2
+            ctxp = torch.empty((B, L + T, D), device=dev, dtype=bf16)
+            lib.attention_fwd(packed, maskp, kvp, ctxp, H)                                             # :115
+            ctx2 = ctxp[:, L:, :].contiguous()
+            x3 = torch.empty((B, T, D), device=dev, dtype=f32)
+            x3n = torch.empty((B, T, D), device=dev, dtype=bf16)
+            lib.conv_gemm(ctx2, lc["wo2_g"], lc["bo2"], block_n=D, epi=lib.EPI_RES_LN, res_f32=x2, res_bstride=T * D,
+                          res_tstride=D, ln1=lc["ln3"], out_f32=x3, out_bf16=x3n)                      # :116, :118
+            next_ln = t["layers"][i + 1]["ln1"] if i + 1 < n_layers else t["norm"]
+            z = torch.empty((B, T, D), device=dev, dtype=f32)
+            zn = torch.empty((B, T, D), device=dev, dtype=bf16)
+            lib.ffn_fused(x3n, lc["w1_g"], lc["b1"], lc["w2_g"], lc["b2"], x3, lc["ln_ff"], next_ln, z, zn)   # :122, next :110
+            x, xn = z, zn
+        out = torch.empty((B, T, head["w_g"].shape[1]), device=dev, dtype=f32)
+        lib.conv_gemm(xn, head["w_g"], head["b_g"], block_n=192, out_f32=out)                          # decoder.py:56 + heads
+        return out
 
     def begin(self, head: dict, e_outputs: torch.Tensor, src_mask, cap: int, forced_in=None, trg_len=None,
               use_cuda_graph: bool = True) -> DecodeState:

@@ -53,6 +53,7 @@ class Transformer(nn.Module):
         self.postnet = PostConvNet(hp, d_model_decoder, trg_vocab, reduction_rate, dropout_postnet, prev_version=False)
         self._ttsb_cache = E.Cache()
         self.use_cuda_graphs = True
+        self.prefix_mode = "batched"   # forward(): "batched" = whole prefix on the tcgen05 kernels; "steps" = decode-step machine
 
     # ------------------------------------------------------------------------------------------------------------------
     def _head(self) -> dict:
@@ -64,6 +65,14 @@ class Transformer(nn.Module):
         if c.stale(params):
             c.t["w"] = lib.pad_weight_rows(torch.cat([self.out.weight.detach(), self.stop_token.weight.detach()], 0))
             c.t["b"] = E._f32(torch.cat([self.out.bias.detach(), self.stop_token.bias.detach()], 0))
+            # the same rows zero-padded to a multiple of the 192-column GEMM tile, as a (1, N, C) conv_gemm operand
+            n = c.t["w"].shape[0]
+            npad = (n + 191) // 192 * 192
+            wg = torch.zeros((1, npad, c.t["w"].shape[1]), device=c.t["w"].device, dtype=torch.bfloat16)
+            wg[0, :n] = c.t["w"]
+            bg = torch.zeros(npad, device=c.t["b"].device, dtype=torch.float32)
+            bg[:n] = c.t["b"]
+            c.t["w_g"], c.t["b_g"] = wg, bg
             if self.linear is not None:
                 c.t["wlin"] = E._bf16(self.linear.weight).unsqueeze(0).contiguous()
                 c.t["blin"] = E._f32(self.linear.bias)
@@ -99,15 +108,16 @@ class Transformer(nn.Module):
         stop_token, None, None, None): `PostConvNet(prev_version=False)` returns its input (postnets.py:64-79), so the
         two mel outputs are the same tensor values; the attention maps are not materialised.
 
-        Runs T decode steps (each position sees the cached keys / values of the earlier ones), so it costs O(T) launches
-        of small kernels: correct for the reference's loop (test.py:141,156), not meant as a training forward."""
+        prefix_mode "batched" (default): the whole prefix at once on the tensor-core kernels (Decoder.run_prefix: tcgen05
+        GEMMs, causal tcgen05 attention, encoder-decoder attention on a packed sequence, fused FeedForward);
+        "steps": T decode steps of the generate() machine (each position sees the cached keys / values of the earlier ones)."""
         if self.training:
             raise NotImplementedError("Transformer-TTS training (SURVEY §8f row f2) is not built: call .eval()")
         E.require_cuda(src, "Transformer")
         if spkr_emb is not None or ref_mel is not None:
             raise NotImplementedError("speaker / reference-mel inputs are out of scope")
         B, T, _ = trg.shape
-        trg_len = None
+        trg_len = key_valid = None
         if trg_mask is not None:
             tm = trg_mask if trg_mask.dim() == 3 else trg_mask.unsqueeze(1)
             key_valid = tm[:, -1, :].to(torch.uint8).contiguous()          # last row of causal & padding = the padding mask
@@ -116,10 +126,16 @@ class Transformer(nn.Module):
                 raise NotImplementedError("the target mask must be causal AND a padding mask (train.py:26-58)")
             trg_len = kvt[:, 0].contiguous()
         e = self.encode(src, src_mask)
-        st = self.decoder.begin(self._head(), e, src_mask, cap=T, forced_in=trg.float().contiguous(), trg_len=trg_len,
-                                use_cuda_graph=self.use_cuda_graphs and T > 2)
-        st.run(T)
-        pre, stop = self._split(st.out_all, T)
+        if self.prefix_mode == "batched" and self.decoder.norm.weight.numel() == 384:
+            # the whole prefix at once on the tensor-core kernels (Decoder.run_prefix)
+            key_valid = (torch.ones((B, T), device=trg.device, dtype=torch.uint8) if trg_mask is None else key_valid)
+            out_all = self.decoder.run_prefix(self._head(), trg.float(), e, src_mask, key_valid)
+        else:  # position by position through the decode-step machine (what generate() uses)
+            st = self.decoder.begin(self._head(), e, src_mask, cap=T, forced_in=trg.float().contiguous(), trg_len=trg_len,
+                                    use_cuda_graph=self.use_cuda_graphs and T > 2)
+            st.run(T)
+            out_all = st.out_all
+        pre, stop = self._split(out_all, T)
         pre = pre.contiguous()
         return pre, self.postnet(pre), stop.contiguous(), None, None, None
 
