@@ -128,7 +128,7 @@ enum {
 // per-tile time was 181 us of 226 us with the softmax arithmetic removed).
 // DROP: training with dropout on the probabilities (Models/modules.py:18-19): the row sum l is taken BEFORE the mask
 // (softmax, then dropout), P * m is what multiplies V.  Its own instantiation: the plain kernel keeps its registers.
-template <int NH, bool DROP = false>
+template <int NH, bool DROP = false, bool CAUSAL = false>
 __global__ void __launch_bounds__(64 + 128 * NH, DROP ? 1 : 2)
 attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmQ32,
                      const __grid_constant__ CUtensorMap tmKV, const __grid_constant__ CUtensorMap tmKV32,
@@ -159,15 +159,13 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
   const int klen = kv_info[2 * b];          // 1 + index of the last valid key
   const int kprefix = kv_info[2 * b + 1];   // keys [0, kprefix) are all valid
   const int kv_eff = klen > 0 ? klen : T;   // no valid key: the reference degenerates to uniform over T
-  // skip_padded_q is a flag word: bit 0 = skip padded query tiles (ragged batches), bit 1 = CAUSAL: key j attends only
-  // for j <= query index, on top of the key-padding mask (the target mask of Transformer-TTS, train.py:26-58) — key tiles
+  // CAUSAL (its own instantiation: the plain kernel keeps its registers and its 127 us): key j attends only for
+  // j <= query index, on top of the key-padding mask (the target mask of Transformer-TTS, train.py:26-58) — key tiles
   // wholly above the tile's last query are never loaded, tiles that cross the diagonal take the flagged path below
-  const bool causal = (skip_padded_q & 2) != 0;
-  int nkv = (kv_eff + kBKV - 1) / kBKV;
-  if (causal) nkv = min(nkv, (q0 + kBQ - 1) / kBKV + 1);
+  const int nkv = CAUSAL ? min((kv_eff + kBKV - 1) / kBKV, (q0 + kBQ - 1) / kBKV + 1) : (kv_eff + kBKV - 1) / kBKV;
   // ragged batches: a query tile wholly beyond the utterance's last valid row is padding (CTA-uniform exit, before
   // any barrier or TMEM allocation); its ctx rows stay unwritten
-  if ((skip_padded_q & 1) && klen > 0 && q0 >= klen) return;
+  if (skip_padded_q && klen > 0 && q0 >= klen) return;
 
   auto load_k = [&](int j) {
     const int ks = j % kKStages;
@@ -375,7 +373,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     for (int j = 0; j < nkv; ++j) {
       const uint32_t sb = j & 1;
       // a tile inside the all-valid prefix of the mask needs no flags (CTA-uniform decision)
-      const bool clean = (j + 1) * kBKV <= kprefix && (!causal || (j + 1) * kBKV <= q0 + 1);
+      const bool clean = CAUSAL ? ((j + 1) * kBKV <= kprefix && (j + 1) * kBKV <= q0 + 1) : ((j + 1) * kBKV <= kprefix);
       uint8_t* flg = sflag + sb * kBKV;
       if (!clean) {
         if (st < kBKV) {
@@ -405,9 +403,13 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
 #pragma unroll
         for (int i = 0; i < CW; ++i) {
           const uint8_t f = flg[half * CW + i];
-          // (causal: a key beyond this row's own index is filled like a padded one, as the reference's combined mask does)
-          const bool hidden = f == 0 || (causal && f == 1 && j * kBKV + half * CW + i > q0 + row);
-          s[i] = hidden ? masked : (f == 1 ? s[i] * scale_log2 : -INFINITY);
+          if constexpr (CAUSAL) {
+            // a key beyond this row's own index is filled like a padded one, as the reference's combined mask does
+            const bool hidden = f == 0 || (f == 1 && j * kBKV + half * CW + i > q0 + row);
+            s[i] = hidden ? masked : (f == 1 ? s[i] * scale_log2 : -INFINITY);
+          } else {
+            s[i] = f == 1 ? s[i] * scale_log2 : (f == 0 ? masked : -INFINITY);
+          }
           mx4[i & 3] = fmaxf(mx4[i & 3], s[i]);
         }
       }
@@ -648,7 +650,12 @@ static int attention_fwd_launch(const void* qkv, const uint8_t* mask, const int3
   if (rc) return rc;
   dim3 grid((T + kBQ - 1) / kBQ, H, B);
   const float scale_log2 = kLog2e / sqrtf(static_cast<float>(Dh));
-  if (drop.thresh) {
+  if (skip_padded_q & 2) {   // flag word: bit 0 = skip padded query tiles, bit 1 = causal (inference instantiation)
+    auto kern = attention_fwd_kernel<kAttHalves, false, true>;
+    TTSB_SMEM_OPT_IN(kern, kAttSmem);
+    kern<<<grid, kAttThreads, kAttSmem, static_cast<cudaStream_t>(s)>>>(tmQ, tmQ32, tmKV, tmKV32, tmO, tmO32, mask, kv_info,
+                                                                       lse2, T, H, scale_log2, skip_padded_q & 1, drop);
+  } else if (drop.thresh) {
     auto kern = attention_fwd_kernel<kAttHalves, true>;
     TTSB_SMEM_OPT_IN(kern, kAttSmem);
     kern<<<grid, kAttThreads, kAttSmem, static_cast<cudaStream_t>(s)>>>(tmQ, tmQ32, tmKV, tmKV32, tmO, tmO32, mask, kv_info,
