@@ -132,8 +132,8 @@ int ttsb200_attention_fwd(const void* qkv, const uint8_t* mask, const int32_t* k
                           int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t stream);
 /* The same under the CAUSAL and key-padding mask of Transformer-TTS (train.py:26-58; attn_1 of Models/layers.py:111):
  * key j attends to query i only for j <= i; hidden keys get the reference's -1e4 fill.  Key tiles above the diagonal are
- * never loaded. */
-int ttsb200_attention_fwd_causal(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
+ * never loaded.  lse2 (optional, (B,H,T) fp32) as in ttsb200_attention_fwd_lse, for ttsb200_attention_bwd_causal. */
+int ttsb200_attention_fwd_causal(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx, float* lse2,
                                  int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t stream);
 /* Training forward: same kernel, also writes lse2 (B,H,T) fp32 = log2-domain log-sum-exp of every
  * query row, so that p = exp2(s * log2(e)/sqrt(Dh) - lse2) in the backward kernels. */
@@ -284,6 +284,11 @@ int ttsb200_attention_bwd(const void* qkv, const void* dctx, const uint8_t* mask
                           int32_t H, int32_t Dh, ttsb200_stream_t stream);
 int ttsb200_attn_delta(const void* dctx, const void* ctx, float* delta, int32_t B, int32_t T, int32_t H,
                        int32_t Dh, ttsb200_stream_t stream);
+/* Backward of ttsb200_attention_fwd_causal (causal AND key-padding mask): a key tile starts at the query tile that holds
+ * its diagonal, a query tile stops at it; only the diagonal tiles evaluate the per-row predicate. */
+int ttsb200_attention_bwd_causal(const void* qkv, const void* dctx, const uint8_t* mask, const int32_t* kv_info,
+                                 const float* lse2, const float* delta, void* dqkv, int32_t B, int32_t T, int32_t H,
+                                 int32_t Dh, ttsb200_stream_t stream);
 
 /* LayerNorm backward (Models/layers.py:31,35; modules.py:87; varianceadaptor.py:219,222; encoder.py:112).
  * x = saved pre-LN input (rows,D) fp32, statistics are recomputed.  Exactly one gradient source:

@@ -180,6 +180,41 @@ def test_attention_bwd(L, B, T, lens):
         assert e < 2e-2, f"d{name}: {e}"
 
 
+@pytest.mark.parametrize("B,T,lens", [
+    (2, 128, [128, 100]),
+    (3, 300, [300, 257, 64]),
+    (2, 400, [400, 129]),
+    (1, 65, [65]),
+])
+def test_attention_bwd_causal(L, B, T, lens):
+    """Causal AND key-padding mask (the target mask of Transformer-TTS, train.py:26-58): forward with lse, backward."""
+    H, D = 4, 384
+    dk = D // H
+    qkv = rnd(B, T, 3 * D, scale=1.0, dtype=torch.bfloat16, seed=11)
+    dctx = rnd(B, T, D, scale=1.0, dtype=torch.bfloat16, seed=12)
+    mask = (torch.arange(T)[None, :] < torch.tensor(lens)[:, None]).to(torch.uint8).to(dev())
+    kv = L.mask_lengths(mask)
+    ctx = torch.empty(B, T, D, device=dev(), dtype=torch.bfloat16)
+    lse2 = torch.empty(B, H, T, device=dev())
+    L.attention_fwd(qkv, mask, kv, ctx, H, lse2=lse2, causal=True)
+    x = qkv.double().requires_grad_(True)
+    q, k, v = (x[..., i * D:(i + 1) * D].reshape(B, T, H, dk).transpose(1, 2) for i in range(3))
+    s = q @ k.transpose(-1, -2) / math.sqrt(dk)
+    full = (mask[:, None, None, :] != 0) & torch.tril(torch.ones(T, T, dtype=torch.bool, device=dev()))[None, None]
+    s = s.masked_fill(~full, -1e4)
+    ref_ctx = (torch.softmax(s, -1) @ v).transpose(1, 2).reshape(B, T, D)
+    ref_lse = torch.logsumexp(s, -1)
+    assert rel_err(ctx, ref_ctx) < 1e-2
+    assert (lse2.double() * math.log(2.0) - ref_lse).abs().max().item() < 2e-3
+    (ref_ctx * dctx.double()).sum().backward()
+    delta = L.attn_delta(dctx, ctx, H)
+    dqkv = L.attention_bwd(qkv, dctx, mask, kv, lse2, delta, H, causal=True)
+    torch.cuda.synchronize()
+    for i, name in enumerate("qkv"):
+        e = rel_err(dqkv[..., i * D:(i + 1) * D], x.grad[..., i * D:(i + 1) * D])
+        assert e < 2e-2, f"d{name}: {e}"
+
+
 # ------------------------------------------------------------------------------------------------
 # LayerNorm backward
 # ------------------------------------------------------------------------------------------------

@@ -695,8 +695,8 @@ extern "C" int ttsb200_attention_fwd_ragged(const void* qkv, const uint8_t* mask
 }
 
 extern "C" int ttsb200_attention_fwd_causal(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
-                                            int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t s) {
-  return attention_fwd_launch(qkv, mask, kv_info, ctx, nullptr, B, T, H, Dh, 2, s);
+                                            float* lse2, int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t s) {
+  return attention_fwd_launch(qkv, mask, kv_info, ctx, lse2, B, T, H, Dh, 2, s);
 }
 
 extern "C" int ttsb200_attention_fwd(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,

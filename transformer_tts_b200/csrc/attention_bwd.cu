@@ -57,18 +57,21 @@ __device__ __forceinline__ void store_row32(uint8_t* tile, int row, int c, const
 }
 
 // p and ds of 32 keys for one query row.  flg: 1 valid key, 0 masked key (< T), 2 key beyond T.
+// vis: keys [0, vis] of these 32 are visible to the row (causal mask of Transformer-TTS: a key beyond the query's own index
+// is filled like a padded one); pass a large value when there is no causal mask.
 __device__ __forceinline__ void softmax_bwd32(float* s /* in: s, out: p */, float* dp /* in: dp, out: ds */,
                                               const uint8_t* flg, bool row_ok, float lse2, float delta,
-                                              float scale_log2, float scale) {
+                                              float scale_log2, float scale, int vis = 1 << 30) {
   const float masked = -1e4f * kLog2e;
 #pragma unroll
   for (int i = 0; i < 32; ++i) {
     const uint8_t f = flg[i];
-    const float sl = f == 1 ? s[i] * scale_log2 : masked;
+    const bool v = f == 1 && i <= vis;
+    const float sl = v ? s[i] * scale_log2 : masked;
     float p = ex2(sl - lse2);
     if (f == 2 || !row_ok) p = 0.f;
     s[i] = p;
-    dp[i] = f == 1 ? p * (dp[i] - delta) * scale : 0.f;
+    dp[i] = v ? p * (dp[i] - delta) * scale : 0.f;
   }
 }
 
@@ -88,6 +91,9 @@ __device__ __forceinline__ void softmax_bwd32_clean(float* s, float* dp, float n
 
 enum { D_KV = 0, D_QF0, D_QF1, D_QE0, D_QE1, D_SF, D_PF, D_DONE, D_COUNT };
 
+// CAUSAL (its own instantiation): key k reaches query t only for k <= t, so a key tile starts at the query tile that
+// holds its diagonal (i0) and only that tile needs the per-row predicate.
+template <bool CAUSAL>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
                     const uint8_t* __restrict__ mask, const int32_t* __restrict__ kv_info,
@@ -114,7 +120,9 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
   const int klen = kv_info[2 * b];
   const int kv_eff = klen > 0 ? klen : T;
   const bool clean = k0 + kBKV <= kv_info[2 * b + 1];  // every key of this tile is valid: no flags needed
-  const int nq = (T + kBQ - 1) / kBQ;
+  const int nq_all = (T + kBQ - 1) / kBQ;
+  const int i0 = CAUSAL ? k0 / kBQ : 0;     // first query tile that sees this key tile
+  const int nq = nq_all - i0;               // query tiles processed (local index n, tile index i0 + n)
   const int64_t ld = 3LL * D;
 
   if (k0 >= kv_eff) {
@@ -168,8 +176,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
         mbar_arrive_expect_tx(qf, 2 * kTileBytes);
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-          tma_load_3d(smem_u32(sQ + buf * kTileBytes + c * kBoxBytes), &tmQKV, qf, h * kDh + c * 32, i * kBQ, b);
-          tma_load_3d(smem_u32(sDO + buf * kTileBytes + c * kBoxBytes), &tmDO, qf, h * kDh + c * 32, i * kBQ, b);
+          tma_load_3d(smem_u32(sQ + buf * kTileBytes + c * kBoxBytes), &tmQKV, qf, h * kDh + c * 32, (i0 + i) * kBQ, b);
+          tma_load_3d(smem_u32(sDO + buf * kTileBytes + c * kBoxBytes), &tmDO, qf, h * kDh + c * 32, (i0 + i) * kBQ, b);
         }
       }
     }
@@ -235,8 +243,9 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
     const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
     const int64_t stat_base = (static_cast<int64_t>(b) * H + h) * T;
     for (int i = 0; i < nq; ++i) {
-      const int t = i * kBQ + row;
+      const int t = (i0 + i) * kBQ + row;
       const bool row_ok = t < T;
+      const bool diag = CAUSAL && i == 0;   // the tile that holds this key tile's diagonal: per-row visibility
       const float l2 = row_ok ? __ldg(lse2 + stat_base + t) : 0.f;
       const float dl = row_ok ? __ldg(delta + stat_base + t) : 0.f;
       const float neg_l2 = row_ok ? -l2 : -INFINITY, neg_dsc = -dl * scale;
@@ -260,8 +269,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
             dp[e] *= mk[e];
           }
         }
-        if (clean) softmax_bwd32_clean(s, dp, neg_l2, neg_dsc, scale_log2, scale);
-        else softmax_bwd32(s, dp, sflag + c, row_ok, l2, dl, scale_log2, scale);
+        if (clean && !diag) softmax_bwd32_clean(s, dp, neg_l2, neg_dsc, scale_log2, scale);
+        else softmax_bwd32(s, dp, sflag + c, row_ok, l2, dl, scale_log2, scale, diag ? t - k0 - c : (1 << 30));
         if (drop.thresh) {
 #pragma unroll
           for (int e = 0; e < 32; ++e) s[e] *= mk[e];
@@ -307,6 +316,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
 
 enum { Q_Q = 0, Q_KF0, Q_KF1, Q_KE0, Q_KE1, Q_SF, Q_PF, Q_DONE, Q_COUNT };
 
+template <bool CAUSAL>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
                    const uint8_t* __restrict__ mask, const int32_t* __restrict__ kv_info,
@@ -331,7 +341,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
   const int D = H * kDh;
   const int klen = kv_info[2 * b];
   const int kv_eff = klen > 0 ? klen : T;
-  const int nkv = (kv_eff + kBKV - 1) / kBKV;
+  // CAUSAL: key tiles above this query tile's diagonal contribute nothing and are never loaded
+  const int nkv = CAUSAL ? min((kv_eff + kBKV - 1) / kBKV, (q0 + kBQ - 1) / kBKV + 1) : (kv_eff + kBKV - 1) / kBKV;
   const int64_t ld = 3LL * D;
 
   if (warp == 0 && lane == 0) {
@@ -430,7 +441,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     const float neg_l2 = row_ok ? -l2 : -INFINITY, neg_dsc = -dl * scale;
     const int kprefix = kv_info[2 * b + 1];
     for (int j = 0; j < nkv; ++j) {
-      const bool clean = (j + 1) * kBKV <= kprefix;  // CTA-uniform
+      const bool diag = CAUSAL && (j + 1) * kBKV > q0 + 1;   // the tile crosses the diagonal: per-row visibility
+      const bool clean = (j + 1) * kBKV <= kprefix && !diag;    // CTA-uniform
       uint8_t* flg = sflag + (j & 1) * 128;
       if (!clean) {
         if (st < kBKV) {
@@ -453,7 +465,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
           for (int e = 0; e < 32; ++e) dp[e] *= drop_scale(drop, e0 + e);
         }
         if (clean) softmax_bwd32_clean(s, dp, neg_l2, neg_dsc, scale_log2, scale);
-        else softmax_bwd32(s, dp, flg + c, row_ok, l2, dl, scale_log2, scale);
+        else softmax_bwd32(s, dp, flg + c, row_ok, l2, dl, scale_log2, scale, diag ? t - j * kBKV - c : (1 << 30));
         store_row32(sDS, row, c, dp);
       }
       fence_async_smem();
@@ -497,12 +509,28 @@ extern "C" int ttsb200_attention_bwd(const void* qkv, const void* dctx, const ui
   return ttsb200_attention_bwd_drop(qkv, dctx, mask, kv_info, lse2, delta, dqkv, B, T, H, Dh, 0.f, 0, -1, s);
 }
 
+static int attention_bwd_launch(const void* qkv, const void* dctx, const uint8_t* mask, const int32_t* kv_info,
+                                const float* lse2, const float* delta, void* dqkv, int32_t B, int32_t T, int32_t H,
+                                int32_t Dh, const DropCfg drop, bool causal, ttsb200_stream_t s);
+
 extern "C" int ttsb200_attention_bwd_drop(const void* qkv, const void* dctx, const uint8_t* mask,
                                           const int32_t* kv_info, const float* lse2, const float* delta, void* dqkv,
                                           int32_t B, int32_t T, int32_t H, int32_t Dh, float drop_p, uint64_t drop_seed,
                                           int64_t drop_site, ttsb200_stream_t s) {
   TTSB_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f, "attention_bwd: dropout probability must be in [0, 1)");
-  const DropCfg drop = make_drop(drop_p, drop_seed, drop_site);
+  return attention_bwd_launch(qkv, dctx, mask, kv_info, lse2, delta, dqkv, B, T, H, Dh, make_drop(drop_p, drop_seed, drop_site),
+                              false, s);
+}
+
+extern "C" int ttsb200_attention_bwd_causal(const void* qkv, const void* dctx, const uint8_t* mask, const int32_t* kv_info,
+                                            const float* lse2, const float* delta, void* dqkv, int32_t B, int32_t T,
+                                            int32_t H, int32_t Dh, ttsb200_stream_t s) {
+  return attention_bwd_launch(qkv, dctx, mask, kv_info, lse2, delta, dqkv, B, T, H, Dh, make_drop(0.f, 0, -1), true, s);
+}
+
+static int attention_bwd_launch(const void* qkv, const void* dctx, const uint8_t* mask, const int32_t* kv_info,
+                                const float* lse2, const float* delta, void* dqkv, int32_t B, int32_t T, int32_t H,
+                                int32_t Dh, const DropCfg drop, bool causal, ttsb200_stream_t s) {
   TTSB_CHECK_ARG(qkv && dctx && mask && kv_info && lse2 && delta && dqkv, "attention_bwd: null pointer");
   TTSB_CHECK_ARG(B > 0 && T > 0 && H > 0 && Dh == ab::kDh, "attention_bwd: bad dims (Dh must be 96)");
   TTSB_CHECK_ARG(((reinterpret_cast<uintptr_t>(qkv) | reinterpret_cast<uintptr_t>(dctx) |
@@ -523,17 +551,31 @@ extern "C" int ttsb200_attention_bwd_drop(const void* qkv, const void* dctx, con
     int rc = make_tmap_bf16(&tmDO, dctx, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_64B);
     if (rc) return rc;
   }
-  TTSB_SMEM_OPT_IN(ab::attn_bwd_dkv_kernel, ab::kSmemDkv);
-  TTSB_SMEM_OPT_IN(ab::attn_bwd_dq_kernel, ab::kSmemDq);
   const float scale = 1.f / sqrtf(static_cast<float>(Dh));
   const float scale_log2 = ab::kLog2e * scale;
   dim3 grid((T + 127) / 128, H, B);
   cudaStream_t st = static_cast<cudaStream_t>(s);
-  ab::attn_bwd_dkv_kernel<<<grid, ab::kThreads, ab::kSmemDkv, st>>>(
-      tmQKV, tmDO, mask, kv_info, lse2, delta, static_cast<__nv_bfloat16*>(dqkv), T, H, scale_log2, scale, drop);
-  TTSB_CHECK_CUDA(cudaGetLastError());
-  ab::attn_bwd_dq_kernel<<<grid, ab::kThreads, ab::kSmemDq, st>>>(
-      tmQKV, tmDO, mask, kv_info, lse2, delta, static_cast<__nv_bfloat16*>(dqkv), T, H, scale_log2, scale, drop);
+  if (causal) {
+    auto kdkv = ab::attn_bwd_dkv_kernel<true>;
+    auto kdq = ab::attn_bwd_dq_kernel<true>;
+    TTSB_SMEM_OPT_IN(kdkv, ab::kSmemDkv);
+    TTSB_SMEM_OPT_IN(kdq, ab::kSmemDq);
+    kdkv<<<grid, ab::kThreads, ab::kSmemDkv, st>>>(tmQKV, tmDO, mask, kv_info, lse2, delta, static_cast<__nv_bfloat16*>(dqkv), T,
+                                                   H, scale_log2, scale, drop);
+    TTSB_CHECK_CUDA(cudaGetLastError());
+    kdq<<<grid, ab::kThreads, ab::kSmemDq, st>>>(tmQKV, tmDO, mask, kv_info, lse2, delta, static_cast<__nv_bfloat16*>(dqkv), T, H,
+                                                 scale_log2, scale, drop);
+  } else {
+    auto kdkv = ab::attn_bwd_dkv_kernel<false>;
+    auto kdq = ab::attn_bwd_dq_kernel<false>;
+    TTSB_SMEM_OPT_IN(kdkv, ab::kSmemDkv);
+    TTSB_SMEM_OPT_IN(kdq, ab::kSmemDq);
+    kdkv<<<grid, ab::kThreads, ab::kSmemDkv, st>>>(tmQKV, tmDO, mask, kv_info, lse2, delta, static_cast<__nv_bfloat16*>(dqkv), T,
+                                                   H, scale_log2, scale, drop);
+    TTSB_CHECK_CUDA(cudaGetLastError());
+    kdq<<<grid, ab::kThreads, ab::kSmemDq, st>>>(tmQKV, tmDO, mask, kv_info, lse2, delta, static_cast<__nv_bfloat16*>(dqkv), T, H,
+                                                 scale_log2, scale, drop);
+  }
   TTSB_CHECK_CUDA(cudaGetLastError());
   return TTSB_OK;
 }

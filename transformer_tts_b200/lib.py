@@ -78,8 +78,9 @@ _SIGNATURES = {
                                 C.c_void_p], C.c_int),
     "ttsb200_attention_fwd": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
                                C.c_int32, C.c_int32, C.c_void_p], C.c_int),
-    "ttsb200_attention_fwd_causal": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
+    "ttsb200_attention_fwd_causal": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
                                       C.c_int32, C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_attention_bwd_causal": ([C.c_void_p] * 7 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
     "ttsb200_attention_fwd_ragged": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
                                       C.c_int32, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_attention_probs": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
@@ -292,11 +293,12 @@ def attention_fwd(qkv: torch.Tensor, mask: torch.Tensor, kv_len: torch.Tensor, c
     B, T, W = qkv.shape
     Dh = W // (3 * H)
     if causal:
-        if lse2 is not None or skip_padded_queries or (drop is not None and drop[0] > 0):
-            raise ValueError("attention_fwd: causal is an inference option (no lse2 / dropout / ragged query skipping)")
+        if skip_padded_queries or (drop is not None and drop[0] > 0):
+            raise ValueError("attention_fwd: causal has no dropout / ragged query skipping variant")
         _check(load().ttsb200_attention_fwd_causal(_ptr(qkv, torch.bfloat16, "qkv"), _ptr(mask, torch.uint8, "mask"),
                                                    _ptr(kv_len, torch.int32, "kv_len"), _ptr(ctx, torch.bfloat16, "ctx"),
-                                                   B, T, H, Dh, _stream()), "attention_fwd_causal")
+                                                   _ptr(lse2, torch.float32, "lse2"), B, T, H, Dh, _stream()),
+               "attention_fwd_causal")
         _count()
         return
     if drop is not None and drop[0] > 0:
@@ -474,10 +476,20 @@ def attn_delta(dctx: torch.Tensor, ctx: torch.Tensor, H: int) -> torch.Tensor:
     return delta
 
 
-def attention_bwd(qkv, dctx, mask, kv_len, lse2, delta, H: int, drop: Optional[tuple] = None) -> torch.Tensor:
+def attention_bwd(qkv, dctx, mask, kv_len, lse2, delta, H: int, drop: Optional[tuple] = None,
+                  causal: bool = False) -> torch.Tensor:
     B, T, W = qkv.shape
     dqkv = torch.empty_like(qkv)
     p, seed, site = drop if drop is not None else (0.0, 0, -1)
+    if causal:
+        if p > 0:
+            raise ValueError("attention_bwd: the causal variant has no dropout")
+        _check(load().ttsb200_attention_bwd_causal(_ptr(qkv, torch.bfloat16, "qkv"), _ptr(dctx, torch.bfloat16, "dctx"),
+                                                   _ptr(mask, torch.uint8, "mask"), _ptr(kv_len, torch.int32, "kv_len"),
+                                                   _ptr(lse2, torch.float32, "lse2"), _ptr(delta, torch.float32, "delta"),
+                                                   _ptr(dqkv), B, T, H, W // (3 * H), _stream()), "attention_bwd_causal")
+        _count(2)
+        return dqkv
     _check(load().ttsb200_attention_bwd_drop(_ptr(qkv, torch.bfloat16, "qkv"), _ptr(dctx, torch.bfloat16, "dctx"),
                                              _ptr(mask, torch.uint8, "mask"), _ptr(kv_len, torch.int32, "kv_len"),
                                              _ptr(lse2, torch.float32, "lse2"), _ptr(delta, torch.float32, "delta"),
