@@ -370,6 +370,13 @@ int ttsb200_embed_bwd(const float* g, const int64_t* idx64, const int32_t* idx32
 int ttsb200_l1_loss(const float* pred, const float* target, float* grad, void* grad_bf16, float* loss,
                     int64_t n, float scale, int32_t log_target, ttsb200_stream_t stream);
 
+/* F.binary_cross_entropy_with_logits(x, y, reduction='mean', pos_weight) (train.py:217, the stop-token loss of
+ * Transformer-TTS): loss += scale * sum[(1-y) x + (1 + (pos_weight-1) y) softplus(-x)], grad (optional) = its derivative. */
+int ttsb200_bce_logits_loss(const float* x, const float* y, float* grad, float* loss, int64_t n, float scale,
+                            float pos_weight, ttsb200_stream_t stream);
+/* out_bf16[i] = gate_bf16[i] > 0 ? g[i] : 0: backward of a ReLU whose (bf16) output is `gate` (Models/prenets.py:36-37). */
+int ttsb200_relu_gate(const float* g, const void* gate_bf16, void* out_bf16, int64_t n, ttsb200_stream_t stream);
+
 /* Optimizer over one flat fp32 buffer (train_fastspeech2.py:117-120,304-315): out += sum g^2; then
  * g' = g*gscale*min(1, clip/(sqrt(sumsq)*gscale + 1e-6)) (clip_grad_norm_; clip <= 0 disables) and one
  * torch.optim.Adam step (step >= 1 for the bias corrections). */

@@ -117,6 +117,32 @@ def test_relu_gate(L):
             assert rel_err(of, ref) < 2e-3
 
 
+def test_bce_logits_loss_and_relu_gate_rows(L):
+    """train.py:217 binary_cross_entropy_with_logits(reduction='mean', pos_weight) and its gradient; the elementwise ReLU
+    backward used by the decoder prenet (prenets.py:33-38)."""
+    g = torch.Generator().manual_seed(9)
+    for n, pw in ((4 * 301 * 2, 5.0), (7, 1.0), (100003, 0.25)):
+        x = (4 * torch.randn(n, generator=g)).to(dev())
+        x[: min(n, 4)] = torch.tensor([60.0, -60.0, 0.0, 1e-4])[: min(n, 4)].to(dev())   # both tails of log1p(exp(.))
+        y = (torch.rand(n, generator=g) < 0.3).float().to(dev())
+        loss = torch.zeros(1, device=dev())
+        grad = torch.empty_like(x)
+        L.bce_logits_loss(x, y, loss, grad=grad, pos_weight=pw)
+        xr = x.double().requires_grad_(True)
+        ref = F.binary_cross_entropy_with_logits(xr, y.double(), reduction="mean", pos_weight=torch.tensor(pw, device=dev()))
+        ref.backward()
+        assert abs(loss.item() - ref.item()) < 2e-6 * max(1.0, abs(ref.item())), (n, loss.item(), ref.item())
+        assert rel_err(grad, xr.grad) < 1e-6
+        l2 = torch.zeros(1, device=dev())
+        L.bce_logits_loss(x, y, l2, pos_weight=pw)       # loss only
+        assert l2.item() == loss.item()
+    gr = rnd(3, 77, 384, seed=5)
+    gate = torch.relu(rnd(3, 77, 384, dtype=torch.bfloat16, seed=6))
+    out = L.relu_gate(gr, gate)
+    assert out.dtype == torch.bfloat16
+    assert torch.equal(out, (gr * (gate > 0)).to(torch.bfloat16))
+
+
 def test_pre_f32(L):
     B, T, D = 2, 200, 384
     x = rnd(B, T, 4 * D, dtype=torch.bfloat16, seed=1)

@@ -506,6 +506,41 @@ l1_loss_kernel(const float* __restrict__ pred, const float* __restrict__ target,
 }
 
 // ------------------------------------------------------------------------------------------------
+// F.binary_cross_entropy_with_logits(x, y, reduction='mean', pos_weight=pw) (train.py:217, the stop-token loss of
+// Transformer-TTS): l = (1 - y) x + (1 + (pw - 1) y) softplus(-x);  loss += scale * sum l;
+// grad = scale * ((1 - y) - (1 + (pw - 1) y) sigmoid(-x)).  softplus(-x) = max(-x, 0) + log1p(exp(-|x|)) as torch.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+bce_logits_loss_kernel(const float* __restrict__ x, const float* __restrict__ y, float* __restrict__ grad,
+                       float* __restrict__ loss, int64_t n, float scale, float pos_weight) {
+  float acc = 0.f;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * 256 + threadIdx.x; i < n;
+       i += static_cast<int64_t>(gridDim.x) * 256) {
+    const float xv = x[i], yv = y[i];
+    const float w = 1.f + (pos_weight - 1.f) * yv;
+    const float sp = fmaxf(-xv, 0.f) + log1pf(expf(-fabsf(xv)));   // softplus(-x)
+    acc += (1.f - yv) * xv + w * sp;
+    if (grad) grad[i] = scale * ((1.f - yv) - w / (1.f + expf(xv)));   // sigmoid(-x) = 1 / (1 + e^x)
+  }
+  acc = warp_sum(acc);
+  __shared__ float sw[8];
+  if ((threadIdx.x & 31) == 0) sw[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float s = 0.f;
+    for (int w = 0; w < 8; ++w) s += sw[w];
+    atomicAdd(loss, s * scale);
+  }
+}
+
+// out_bf16[i] = gate_bf16[i] > 0 ? g[i] : 0   (backward of a ReLU whose output is `gate`; Models/prenets.py:36-37)
+__global__ void __launch_bounds__(256)
+relu_gate_kernel(const float* __restrict__ g, const __nv_bfloat16* __restrict__ gate, __nv_bfloat16* __restrict__ out, int64_t n) {
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * 256 + threadIdx.x; i < n; i += static_cast<int64_t>(gridDim.x) * 256)
+    out[i] = __float2bfloat16(__bfloat162float(gate[i]) > 0.f ? g[i] : 0.f);
+}
+
+// ------------------------------------------------------------------------------------------------
 // delta[b,h,t] = sum_d dctx[b,t,h*Dh+d] * ctx[b,t,h*Dh+d]   (softmax backward row term of attention)
 // one warp per (b,t); lanes own 4-column chunks; Dh = 96 = 24 chunks, so chunk c belongs to head c/24.
 // ------------------------------------------------------------------------------------------------
@@ -817,6 +852,25 @@ extern "C" int ttsb200_l1_loss(const float* pred, const float* target, float* gr
   const int64_t want = (n + 255) / 256;
   l1_loss_kernel<<<static_cast<unsigned>(want < 1184 ? want : 1184), 256, 0, static_cast<cudaStream_t>(s)>>>(
       pred, target, grad, static_cast<__nv_bfloat16*>(grad_bf16), loss, n, scale, log_target);
+  TTSB_LAUNCH_CHECK();
+  return TTSB_OK;
+}
+
+extern "C" int ttsb200_bce_logits_loss(const float* x, const float* y, float* grad, float* loss, int64_t n, float scale,
+                                       float pos_weight, ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(x && y && loss && n > 0, "bce_logits_loss: bad args");
+  const int64_t want = (n + 255) / 256;
+  bce_logits_loss_kernel<<<static_cast<unsigned>(want < 1184 ? want : 1184), 256, 0, static_cast<cudaStream_t>(s)>>>(
+      x, y, grad, loss, n, scale, pos_weight);
+  TTSB_LAUNCH_CHECK();
+  return TTSB_OK;
+}
+
+extern "C" int ttsb200_relu_gate(const float* g, const void* gate_bf16, void* out_bf16, int64_t n, ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(g && gate_bf16 && out_bf16 && n > 0, "relu_gate: bad args");
+  const int64_t want = (n + 255) / 256;
+  relu_gate_kernel<<<static_cast<unsigned>(want < 1184 ? want : 1184), 256, 0, static_cast<cudaStream_t>(s)>>>(
+      g, static_cast<const __nv_bfloat16*>(gate_bf16), static_cast<__nv_bfloat16*>(out_bf16), n);
   TTSB_LAUNCH_CHECK();
   return TTSB_OK;
 }

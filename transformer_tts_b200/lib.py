@@ -68,6 +68,9 @@ _SIGNATURES = {
                              C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
                              C.c_int32, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_advance_pos": ([C.c_void_p, C.c_int32, C.c_void_p], C.c_int),
+    "ttsb200_bce_logits_loss": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float, C.c_void_p],
+                                C.c_int),
+    "ttsb200_relu_gate": ([C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p], C.c_int),
     "ttsb200_debug_dcl_trace": ([C.c_void_p, C.c_int], C.c_int),
     "ttsb200_decode_attn_out_q": ([C.c_void_p] * 8 + [C.c_float, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_decode_ffn_block": ([C.c_void_p] * 14 + [C.c_float, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
@@ -821,3 +824,23 @@ def decode_ffn_block(ctx, x_in, wo, bo, ln3, w1, b1, w2, b2, ln_ff, ln_next, eps
         _ptr(ln_next[1], f32, "lnn_b"), eps, _ptr(z_out, f32, "z_out"), _ptr(zn_out, bf, "zn_out"),
         R, D, int(w1.shape[0]), _stream()), "decode_ffn_block")
     _count()
+
+
+def bce_logits_loss(x, y, loss, *, grad=None, pos_weight: float = 1.0) -> None:
+    """loss += mean BCE-with-logits(x, y; pos_weight) (train.py:217); grad (optional) receives d loss / d x."""
+    n = x.numel()
+    if y.numel() != n:
+        raise ValueError("bce_logits_loss: shape mismatch")
+    _check(load().ttsb200_bce_logits_loss(_ptr(x, torch.float32, "x"), _ptr(y, torch.float32, "y"),
+                                          _ptr(grad, torch.float32, "grad"), _ptr(loss, torch.float32, "loss"), n, 1.0 / n,
+                                          float(pos_weight), _stream()), "bce_logits_loss")
+    _count()
+
+
+def relu_gate(g: torch.Tensor, gate: torch.Tensor) -> torch.Tensor:
+    """bf16(g where gate > 0 else 0): backward of a ReLU whose output is `gate`."""
+    out = torch.empty(g.shape, device=g.device, dtype=torch.bfloat16)
+    _check(load().ttsb200_relu_gate(_ptr(g, torch.float32, "g"), _ptr(gate, torch.bfloat16, "gate"), _ptr(out), g.numel(),
+                                    _stream()), "relu_gate")
+    _count()
+    return out

@@ -150,7 +150,7 @@ class Trainer:
         flatten=False (drop-in autograd mode, see `autograd_forward`): parameters are left alone, only the flat
         gradient buffer exists and the caller's torch optimizer owns the update."""
         lib.load()
-        self.drop = DropoutPlan(model, base_seed=dropout_seed)
+        self.drop = self._dropout_plan(model, dropout_seed)
         # hp.optimizer (train_fastspeech2.py:412-416): 'radam' -> radam.RAdam at the fixed rate lr_max (the Noam
         # schedule is skipped for it, :117-120); anything else -> torch.optim.Adam at the Noam rate
         self.optimizer = optimizer.lower()
@@ -210,6 +210,10 @@ class Trainer:
         self.loss_buf = torch.zeros(8, device=dev, dtype=torch.float32)
         self._zeros = {}
         self.invalidate_caches()
+
+    def _dropout_plan(self, model, seed: int):
+        """The dropout call sites of the model (FastSpeech2 here; tts_training.TTSTrainer overrides it)."""
+        return DropoutPlan(model, base_seed=seed)
 
     # ------------------------------------------------------------------------------------------
     def _bind_grads(self) -> None:
