@@ -446,8 +446,8 @@ def ar_decode_record(cpu: bool, positions: int = 1000, batch: int = 16, phonemes
            "what": "Transformer.generate: KV-cache decode, one CUDA graph replay (small_linear / attn_decode kernels, programmatic "
                    "dependent launch) per position; random-init weights, so the stop token fires at random: all positions are decoded"}
     # teacher-forced prefix forward at BASELINE.json configs[3]'s shape (mel length 800 = 400 decoder positions at r = 2,
-    # 128 phonemes), batch 32: the tensor-core path of Transformer.forward (inference only: the training step, row f2, is
-    # not built) next to the same modules under stock PyTorch eager fp32 on this GPU (the oracle port)
+    # 128 phonemes), batch 32: the tensor-core path of Transformer.forward in eval mode (the training step at this shape is
+    # the next sub-record) next to the same modules under stock PyTorch eager fp32 on this GPU (the oracle port)
     try:
         from oracle import transformer_tts_oracle as T
 
@@ -481,9 +481,13 @@ def ar_decode_record(cpu: bool, positions: int = 1000, batch: int = 16, phonemes
                                          "frames_per_s": Bp * Tp * hp.reduction_rate / min(tp) * 1e3,
                                          "torch_eager_fp32_same_gpu_ms": eager_ms,
                                          "what": "Transformer.forward(prefix_mode='batched'): tcgen05 GEMMs, causal tcgen05 attention, "
-                                                 "encoder-decoder attention on a packed sequence, fused FeedForward; inference only"}
+                                                 "encoder-decoder attention on a packed sequence, fused FeedForward (eval mode)"}
     except Exception as ex:  # noqa: BLE001 — a sub-record must not take the headline line down
         rec["teacher_forced_forward"] = {"error": str(ex)[:200]}
+    try:
+        rec["teacher_forced_train_step"] = tts_train_record(cpu)
+    except Exception as ex:  # noqa: BLE001
+        rec["teacher_forced_train_step"] = {"error": str(ex)[:300]}
     if cpu:
         from oracle import transformer_tts_oracle as T
 
@@ -498,6 +502,101 @@ def ar_decode_record(cpu: bool, positions: int = 1000, batch: int = 16, phonemes
                                 "kind": "port", "seconds": dt,
                                 "sample": f"the reference's loop (whole prefix re-run per step) for the FIRST {n_cpu} positions of the "
                                           f"same batch; its cost per step grows with the prefix, so 1000 positions are slower than this rate"}
+    return rec
+
+
+def tts_train_record(cpu: bool, batch: int = 32, phonemes: int = 128, mel_len: int = 800):
+    """BASELINE.json configs[3]: Transformer-TTS teacher-forced training step (train.py:160-263: encoder, decoder with the
+    encoder-decoder attention, mel / stop heads, 2 x L1 + BCE, backward, clip + Adam), mel length 800, batch 32, dropout 0
+    (the scope of tts_training.TTSTrainer).  Device time per step, inputs resident; next to it the same step under stock
+    PyTorch eager fp32 autograd on this GPU (the oracle port, forward + backward only) and, with `cpu`, on the host cores."""
+    import torch
+    import torch.nn.functional as F
+
+    from oracle import transformer_tts_oracle as T
+    from transformer_tts_b200 import build_transformer_tts, lib, synth
+    from transformer_tts_b200.tts_training import TTSTrainer
+
+    hp = synth.make_tts_hp()
+    r = hp.reduction_rate
+    sd = synth.synth_tts_state_dict(hp)
+    model = build_transformer_tts(hp)
+    model.load_state_dict(sd)
+    model = model.cuda().train()
+    text, pos, _ = synth.synth_text_batch(batch, phonemes, ragged=True, seed=81, min_len=phonemes // 2)
+    g = torch.Generator().manual_seed(82)
+    lens = torch.randint(mel_len // 2 // r, mel_len // r + 1, (batch,), generator=g) * r
+    lens[0] = mel_len
+    pos_mel = torch.arange(1, mel_len + 1).unsqueeze(0).repeat(batch, 1)
+    pos_mel[pos_mel > lens.unsqueeze(1)] = 0
+    mel = torch.randn(batch, mel_len, hp.mel_dim, generator=g) * (pos_mel != 0).unsqueeze(-1)
+    stop = (pos_mel == 0).float()
+    stop[torch.arange(batch), lens - 1] = 1.0
+    mel_in, pos_in = mel[:, :-r:r, :].contiguous(), pos_mel[:, :-r:r].contiguous()
+    src_mask, trg_mask = T.create_masks(pos, pos_in)
+    a = (text.cuda(), mel_in.cuda(), src_mask.cuda(), (pos_in != 0).to(torch.uint8).cuda(), mel[:, r:, :].contiguous().cuda(),
+         stop[:, r:].contiguous().cuda())
+    tr = TTSTrainer(model, positive_weight=5.0)
+    for _ in range(3):
+        out = tr.train_step(*a)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    steps = 5
+    l0 = lib.LAUNCH_COUNT
+    e0.record()
+    for _ in range(steps):
+        out = tr.train_step(*a)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    frames = float((pos_mel[:, r:] != 0).sum())
+    rec = {"metric": "transformer_tts_train_mel_frames_per_sec", "value": frames / ms * 1e3, "unit": "frames/s", "ms_per_step": ms,
+           "batch": batch, "phonemes": phonemes, "mel_len": mel_len, "decoder_positions": int(mel_in.shape[1]),
+           "valid_target_frames": frames, "gpu_launches_per_step": (lib.LAUNCH_COUNT - l0) // steps, "loss": float(out["loss"]),
+           "dropout": 0.0, "optimizer": "adam (Noam rate), clip 1.0",
+           "what": "tts_training.TTSTrainer.train_step: tcgen05 GEMMs / wgrad, causal tcgen05 attention forward + backward, "
+                   "encoder-decoder attention on a packed sequence, fused clip + Adam over the flat buffers"}
+
+    def eager_step(sdx, dev):
+        leaf = {k: (v.to(dev).clone().requires_grad_(True) if v.is_floating_point() and not k.startswith("postnet.") else v.to(dev))
+                for k, v in sdx.items()}
+        c = lambda t: t.to(dev)  # noqa: E731
+
+        def step():
+            o = T.transformer_forward(leaf, vars(hp), c(text), c(mel_in), c(src_mask), c(trg_mask))
+            pre, st = o["outputs_prenet"], o["stop_token"]
+            b, t, ch = pre.shape
+            loss = 2 * F.l1_loss(pre.reshape(b, t * r, ch // r), c(mel[:, r:, :])) + F.binary_cross_entropy_with_logits(
+                st.reshape(b, t * r), c(stop[:, r:]), reduction="mean", pos_weight=torch.tensor(5.0, device=dev))
+            loss.backward()
+            return loss
+        return step
+
+    try:
+        step = eager_step(sd, "cuda")
+        step()
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(2):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        rec["torch_eager_fp32_same_gpu_ms"] = e0.elapsed_time(e1) / 2
+    except Exception as ex:  # noqa: BLE001
+        rec["torch_eager_fp32_same_gpu_ms"] = None
+        rec["eager_error"] = str(ex)[:200]
+    if cpu:
+        torch.set_num_threads(os.cpu_count() or 1)
+        step = eager_step(sd, "cpu")
+        step()
+        n_cpu = 3   # bounded sample: 3 steps (forward + backward, no optimizer) of the same batch after one warm-up step
+        t0 = time.perf_counter()
+        for _ in range(n_cpu):
+            step()
+        dt = (time.perf_counter() - t0) / n_cpu
+        rec["cpu_reference"] = {"value": frames / dt, "unit": "frames/s", "cores": os.cpu_count(), "kind": "port",
+                                "seconds_per_step": dt,
+                                "sample": f"forward + backward (no optimizer) of the same batch, mean of {n_cpu} steps after one warm-up"}
     return rec
 
 

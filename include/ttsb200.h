@@ -135,6 +135,11 @@ int ttsb200_attention_fwd(const void* qkv, const uint8_t* mask, const int32_t* k
  * never loaded.  lse2 (optional, (B,H,T) fp32) as in ttsb200_attention_fwd_lse, for ttsb200_attention_bwd_causal. */
 int ttsb200_attention_fwd_causal(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx, float* lse2,
                                  int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t stream);
+/* ... with dropout on the probabilities (train.py builds the model with dropout 0.1; Models/modules.py:18-19): the mask of
+ * element (b, h, i, j) as in the dropout variant of the plain kernel. */
+int ttsb200_attention_fwd_causal_drop(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx, float* lse2,
+                                      int32_t B, int32_t T, int32_t H, int32_t Dh, float drop_p, uint64_t drop_seed,
+                                      int64_t drop_site, ttsb200_stream_t stream);
 /* Training forward: same kernel, also writes lse2 (B,H,T) fp32 = log2-domain log-sum-exp of every
  * query row, so that p = exp2(s * log2(e)/sqrt(Dh) - lse2) in the backward kernels. */
 int ttsb200_attention_fwd_lse(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
@@ -289,6 +294,10 @@ int ttsb200_attn_delta(const void* dctx, const void* ctx, float* delta, int32_t 
 int ttsb200_attention_bwd_causal(const void* qkv, const void* dctx, const uint8_t* mask, const int32_t* kv_info,
                                  const float* lse2, const float* delta, void* dqkv, int32_t B, int32_t T, int32_t H,
                                  int32_t Dh, ttsb200_stream_t stream);
+int ttsb200_attention_bwd_causal_drop(const void* qkv, const void* dctx, const uint8_t* mask, const int32_t* kv_info,
+                                      const float* lse2, const float* delta, void* dqkv, int32_t B, int32_t T, int32_t H,
+                                      int32_t Dh, float drop_p, uint64_t drop_seed, int64_t drop_site,
+                                      ttsb200_stream_t stream);
 
 /* LayerNorm backward (Models/layers.py:31,35; modules.py:87; varianceadaptor.py:219,222; encoder.py:112).
  * x = saved pre-LN input (rows,D) fp32, statistics are recomputed.  Exactly one gradient source:

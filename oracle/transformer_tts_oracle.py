@@ -44,14 +44,15 @@ def create_masks(src_pos: Tensor, trg_pos: Optional[Tensor], src_pad: int = 0, t
 # --------------------------------------------------------------------------------------------------
 # Models/modules.py:43-70  MultiHeadAttention.forward with separate query and key/value inputs
 # --------------------------------------------------------------------------------------------------
-def multi_head_attention(sd: Dict[str, Tensor], pfx: str, q_in: Tensor, kv_in: Tensor, mask: Optional[Tensor], heads: int):
+def multi_head_attention(sd: Dict[str, Tensor], pfx: str, q_in: Tensor, kv_in: Tensor, mask: Optional[Tensor], heads: int,
+                         drop=None, site: str = ""):
     bs, _, d_model = q_in.shape
     d_k = d_model // heads
     k = F.linear(kv_in, sd[pfx + "k_linear.weight"], sd[pfx + "k_linear.bias"]).view(bs, -1, heads, d_k)  # :49
     q = F.linear(q_in, sd[pfx + "q_linear.weight"], sd[pfx + "q_linear.bias"]).view(bs, -1, heads, d_k)  # :50
     v = F.linear(kv_in, sd[pfx + "v_linear.weight"], sd[pfx + "v_linear.bias"]).view(bs, -1, heads, d_k)  # :51
     k, q, v = k.transpose(1, 2), q.transpose(1, 2), v.transpose(1, 2)  # :58-60
-    ctx, attn = O.attention(q, k, v, d_k, mask)  # :63
+    ctx, attn = O.attention(q, k, v, d_k, mask, drop, site)  # :63 (dropout on the probabilities, :18-19)
     concat = ctx.transpose(1, 2).contiguous().view(bs, -1, d_model)  # :65
     return F.linear(concat, sd[pfx + "out.weight"], sd[pfx + "out.bias"]), attn  # :68
 
@@ -59,27 +60,28 @@ def multi_head_attention(sd: Dict[str, Tensor], pfx: str, q_in: Tensor, kv_in: T
 # --------------------------------------------------------------------------------------------------
 # Models/prenets.py:8-44  DecoderPreNet (output_type None; dropout 0)
 # --------------------------------------------------------------------------------------------------
-def decoder_prenet(sd, pfx: str, x: Tensor) -> Tensor:
-    h = F.relu(F.linear(x, sd[pfx + "layer.fc1.weight"], sd[pfx + "layer.fc1.bias"]))  # :33-35
-    return F.relu(F.linear(h, sd[pfx + "layer.fc2.weight"], sd[pfx + "layer.fc2.bias"]))  # :36-38
+def decoder_prenet(sd, pfx: str, x: Tensor, drop=None) -> Tensor:
+    h = O._drop(drop, "prenet.1", F.relu(F.linear(x, sd[pfx + "layer.fc1.weight"], sd[pfx + "layer.fc1.bias"])))  # :33-35
+    return O._drop(drop, "prenet.2", F.relu(F.linear(h, sd[pfx + "layer.fc2.weight"], sd[pfx + "layer.fc2.bias"])))  # :36-38
 
 
 # --------------------------------------------------------------------------------------------------
 # Models/layers.py:109-124  DecoderLayer.forward
 # --------------------------------------------------------------------------------------------------
-def decoder_layer(sd, pfx: str, x: Tensor, e_outputs: Tensor, src_mask, trg_mask, heads: int):
+def decoder_layer(sd, pfx: str, x: Tensor, e_outputs: Tensor, src_mask, trg_mask, heads: int, drop=None, site: str = ""):
+    """`drop` / `site` = "dec.<layer index>": the training-mode dropout call sites, named as in fastspeech2_oracle._drop."""
     d = x.shape[-1]
     res = x
     xn = F.layer_norm(x, (d,), sd[pfx + "norm_1.weight"], sd[pfx + "norm_1.bias"])  # :110
-    out, attn_1 = multi_head_attention(sd, pfx + "attn_1.", xn, xn, trg_mask, heads)  # :111
-    x = res + out  # :112
+    out, attn_1 = multi_head_attention(sd, pfx + "attn_1.", xn, xn, trg_mask, heads, drop, site + ".attn1")  # :111
+    x = res + O._drop(drop, site + ".drop1", out)  # :112
     res = x
     xn = F.layer_norm(x, (d,), sd[pfx + "norm_2.weight"], sd[pfx + "norm_2.bias"])  # :114
-    out, attn_2 = multi_head_attention(sd, pfx + "attn_2.", xn, e_outputs, src_mask, heads)  # :115
-    x = res + out  # :116
+    out, attn_2 = multi_head_attention(sd, pfx + "attn_2.", xn, e_outputs, src_mask, heads, drop, site + ".attn2")  # :115
+    x = res + O._drop(drop, site + ".drop2", out)  # :116
     res = x
     xn = F.layer_norm(x, (d,), sd[pfx + "norm_3.weight"], sd[pfx + "norm_3.bias"])  # :118
-    x = res + O.feed_forward(sd, pfx + "ff.", xn)  # :122
+    x = res + O._drop(drop, site + ".drop3", O.feed_forward(sd, pfx + "ff.", xn, drop, site + ".ff"))  # :122
     return x, attn_1, attn_2
 
 
@@ -87,12 +89,12 @@ def decoder_layer(sd, pfx: str, x: Tensor, e_outputs: Tensor, src_mask, trg_mask
 # Models/decoder.py:43-56  Decoder.forward
 # --------------------------------------------------------------------------------------------------
 def decoder(sd, pfx: str, trg: Tensor, e_outputs: Tensor, src_mask, trg_mask, n_layers: int, heads: int,
-            return_attn: bool = False):
-    x = decoder_prenet(sd, pfx + "decoder_prenet.", trg)  # :44
-    x = O.positional_encoder(x, sd[pfx + "pe.alpha"])  # :47
+            return_attn: bool = False, drop=None):
+    x = decoder_prenet(sd, pfx + "decoder_prenet.", trg, drop)  # :44
+    x = O.positional_encoder(x, sd[pfx + "pe.alpha"], drop, "dec")  # :47
     a1, a2 = [], []
     for i in range(n_layers):
-        x, attn_1, attn_2 = decoder_layer(sd, f"{pfx}layers.{i}.", x, e_outputs, src_mask, trg_mask, heads)  # :53
+        x, attn_1, attn_2 = decoder_layer(sd, f"{pfx}layers.{i}.", x, e_outputs, src_mask, trg_mask, heads, drop, f"dec.{i}")  # :53
         if return_attn:
             a1.append(attn_1)
             a2.append(attn_2)
@@ -105,19 +107,21 @@ def decoder(sd, pfx: str, trg: Tensor, e_outputs: Tensor, src_mask, trg_mask, n_
 # --------------------------------------------------------------------------------------------------
 # Models/transformer.py:90-118  Transformer.forward
 # --------------------------------------------------------------------------------------------------
-def encode(sd, hp: dict, src: Tensor, src_mask: Tensor) -> Tensor:
-    e_outputs, _ = O.encoder(sd, "encoder.", src, src_mask, hp["n_layer_encoder"], hp["n_head_encoder"])  # :92
+def encode(sd, hp: dict, src: Tensor, src_mask: Tensor, drop=None) -> Tensor:
+    e_outputs, _ = O.encoder(sd, "encoder.", src, src_mask, hp["n_layer_encoder"], hp["n_head_encoder"], drop=drop)  # :92
     if "linear.weight" in sd:  # :93-94 (d_model_encoder != d_model_decoder)
         e_outputs = F.linear(e_outputs, sd["linear.weight"], sd["linear.bias"])
     return e_outputs
 
 
 def transformer_forward(sd: Dict[str, Tensor], hp: dict, src: Tensor, trg: Tensor, src_mask: Tensor, trg_mask: Tensor,
-                        return_attn: bool = False, e_outputs: Optional[Tensor] = None) -> dict:
+                        return_attn: bool = False, e_outputs: Optional[Tensor] = None, drop=None) -> dict:
+    """drop: None (every dropout probability 0) or `drop(name, shape) -> mask` for the named training-mode dropout call
+    sites (fastspeech2_oracle._drop): "enc.*" of the text encoder, "prenet.1|2", "dec.pe", "dec.<i>.attn1|drop1|attn2|drop2|ff|drop3"."""
     if e_outputs is None:
-        e_outputs = encode(sd, hp, src, src_mask)
+        e_outputs = encode(sd, hp, src, src_mask, drop)
     d_output, a1, a2 = decoder(sd, "decoder.", trg, e_outputs, src_mask, trg_mask, hp["n_layer_decoder"],
-                               hp["n_head_decoder"], return_attn)  # :107
+                               hp["n_head_decoder"], return_attn, drop)  # :107
     outputs_prenet = F.linear(d_output, sd["out.weight"], sd["out.bias"])  # :109
     outputs_postnet = outputs_prenet  # :110 with postnets.py:64-79, prev_version=False: the input comes back
     stop_token = F.linear(d_output, sd["stop_token.weight"], sd["stop_token.bias"])  # :111 (.squeeze(2) is a no-op for r > 1)

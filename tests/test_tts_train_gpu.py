@@ -1,6 +1,7 @@
 """Transformer-TTS teacher-forced training step on the GPU: transformer_tts_b200.tts_training.TTSTrainer
 against torch autograd through the fp32 oracle (oracle/transformer_tts_oracle.py, pinned to the unmodified reference by
-tests/golden/tts_teacher_forced.npz) with the losses of train.py:214-219, dropout 0.
+tests/golden/tts_teacher_forced.npz) with the losses of train.py:214-219 — at dropout 0, and at the reference's training configuration (dropout 0.1, prenet 0.5) with OUR counter-based masks handed to the oracle's named dropout call sites (the reference's own masks come from torch's
+generator and cannot be reproduced; same method as tests/test_dropout_gpu.py).
 
 Tolerances: as for the FastSpeech2 training step (tests/test_train_gpu.py): bf16 operands with fp32 accumulation on both
 passes; losses 2e-3 relative, per-tensor gradient relative L2 <= 1.2e-1 against max(reference norm, 1e-3 of the global norm),
@@ -34,33 +35,43 @@ def make_batch(hp, B, L, frames, seed):
     return dict(text=text, pos=pos, mel=mel, stop=stop, mel_input=mel_input, pos_in=pos_in)
 
 
-def oracle_grads(sd, hp, b):
+def oracle_grads(sd, hp, b, drop=None, dev="cpu"):
     from oracle import transformer_tts_oracle as T
 
     r = hp.reduction_rate
     skip = ("postnet.", "num_batches_tracked")
-    leaf = {k: (v.clone().float().requires_grad_(True) if v.is_floating_point() and not k.startswith(skip) and "running_" not in k
-                else v) for k, v in sd.items()}
+    leaf = {k: (v.to(dev).clone().float().requires_grad_(True)
+                if v.is_floating_point() and not k.startswith(skip) and "running_" not in k else v.to(dev)) for k, v in sd.items()}
     src_mask, trg_mask = T.create_masks(b["pos"], b["pos_in"])
-    out = T.transformer_forward(leaf, vars(hp), b["text"], b["mel_input"], src_mask, trg_mask)
+    c = lambda t: t.to(dev)  # noqa: E731
+    out = T.transformer_forward(leaf, vars(hp), c(b["text"]), c(b["mel_input"]), c(src_mask), c(trg_mask), drop=drop)
     pre, stop = out["outputs_prenet"], out["stop_token"]
-    bb, t, c = pre.shape
-    pre = pre.reshape(bb, t * r, c // r)
+    bb, t, ch = pre.shape
+    pre = pre.reshape(bb, t * r, ch // r)
     stop = stop.reshape(bb, t * r)
-    mel_loss = F.l1_loss(pre, b["mel"][:, r:, :])
-    tok = F.binary_cross_entropy_with_logits(stop, b["stop"][:, r:], reduction="mean", pos_weight=torch.tensor(POS_WEIGHT))
+    mel_loss = F.l1_loss(pre, c(b["mel"][:, r:, :]))
+    tok = F.binary_cross_entropy_with_logits(stop, c(b["stop"][:, r:]), reduction="mean",
+                                             pos_weight=torch.tensor(POS_WEIGHT, device=dev))
     loss = 2 * mel_loss + tok                            # mel_loss + post_mel_loss (the same values) + loss_token
     loss.backward()
     grads = {k: v.grad for k, v in leaf.items() if isinstance(v, torch.Tensor) and v.requires_grad}
     return dict(loss=loss.item(), mel_loss=mel_loss.item(), loss_token=tok.item()), grads, src_mask
 
 
-def build():
-    from transformer_tts_b200 import build_transformer_tts, synth
+def build(dropout=0.0, dropout_prenet=0.0):
+    from transformer_tts_b200 import synth
+    from transformer_tts_b200.Models.transformer import Transformer
 
     hp = synth.make_tts_hp()
     sd = synth.synth_tts_state_dict(hp)
-    model = build_transformer_tts(hp)
+    # the constructor call of train.py:117-126
+    model = Transformer(hp=hp, src_vocab=hp.vocab_size, trg_vocab=hp.mel_dim, d_model_encoder=hp.d_model_encoder,
+                        N_e=hp.n_layer_encoder, n_head_encoder=hp.n_head_encoder,
+                        ff_conv_kernel_size_encoder=hp.ff_conv_kernel_size_encoder, concat_after_encoder=hp.concat_after_encoder,
+                        d_model_decoder=hp.d_model_decoder, N_d=hp.n_layer_decoder, n_head_decoder=hp.n_head_decoder,
+                        ff_conv_kernel_size_decoder=hp.ff_conv_kernel_size_decoder, concat_after_decoder=hp.concat_after_decoder,
+                        reduction_rate=hp.reduction_rate, dropout=dropout, dropout_prenet=dropout_prenet, dropout_postnet=0.5,
+                        multi_speaker=False, spk_emb_dim=None, spk_emb_architecture="")
     model.load_state_dict(sd)
     return hp, sd, model.cuda().train()
 
@@ -123,12 +134,79 @@ def test_tts_optimizer_steps_reduce_loss():
     assert torch.isfinite(pre).all()
 
 
-def test_tts_trainer_rejects_dropout():
-    from transformer_tts_b200 import synth
-    from transformer_tts_b200.Models.transformer import Transformer
+def check_grads(tr, model, grads, bar_worst, bar_global):
+    floor = 1e-3 * float(sum(float((v.double() ** 2).sum()) for v in grads.values()) ** 0.5)
+    errs, num, den = [], 0.0, 0.0
+    for n, p in model.named_parameters():
+        if n.startswith("postnet."):
+            continue
+        a, w = tr.G(p).double().cpu(), grads[n].double().cpu()
+        errs.append((float((a - w).norm() / max(float(w.norm()), floor)), n))
+        num += float(((a - w) ** 2).sum())
+        den += float((w ** 2).sum())
+    errs.sort(reverse=True)
+    print("worst per-tensor gradient rel-L2:", errs[:6], "global", (num / den) ** 0.5)
+    assert errs[0][0] < bar_worst, errs[:8]
+    assert (num / den) ** 0.5 < bar_global
+
+
+@pytest.mark.parametrize("dropout,dropout_prenet", [(0.1, 0.5), (0.0, 0.5), (0.1, 0.0)])
+def test_tts_train_step_with_reference_dropout_matches_oracle_with_the_same_masks(dropout, dropout_prenet):
+    """train.py:117-126 builds the model with dropout = hp.dropout (0.1) and the prenet's default 0.5.  Bars as in
+    tests/test_dropout_gpu.py: losses 4e-3, global gradient 4e-2, worst tensor 2e-1."""
     from transformer_tts_b200.tts_training import TTSTrainer
 
-    hp = synth.make_tts_hp()
-    m = Transformer(hp, hp.vocab_size, hp.mel_dim, 384, 1, 4, 5, False, 384, 1, 4, 1, False, 2, dropout=0.1).cuda()
-    with pytest.raises(NotImplementedError, match="dropout"):
-        TTSTrainer(m)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    hp, sd, model = build(dropout, dropout_prenet)
+    tr = TTSTrainer(model, positive_weight=POS_WEIGHT, dropout_seed=42)
+    assert tr.drop.active and tr.drop.p_stack == {"enc": dropout, "dec": dropout} and tr.drop.p_prenet == dropout_prenet
+    b = make_batch(hp, 3, 24, 96, 31)
+    from oracle import transformer_tts_oracle as T
+
+    src_mask, _ = T.create_masks(b["pos"], b["pos_in"])
+    args = gpu_args(b, src_mask, hp.reduction_rate)
+    tr.zero_grad()
+    o = tr.forward_backward(*args)
+    seed = tr.last_dropout_seed
+    torch.cuda.synchronize()
+
+    def drop(name, shape):
+        if name.split(".")[0] in ("enc", "dec") and dropout == 0.0:
+            return torch.ones(shape, device="cuda")
+        if name.startswith("prenet") and dropout_prenet == 0.0:
+            return torch.ones(shape, device="cuda")
+        if name.endswith(".attn2"):   # the packed-sequence launch: element (b, h, L + t, l) of a (B, H, L+T, L+T) mask
+            bq, hq, tq, lq = shape
+            return tr.drop.mask(name, (bq, hq, lq + tq, lq + tq), seed)[:, :, lq:, :lq].float()
+        return tr.drop.mask(name, shape, seed).float()
+
+    losses, grads, _ = oracle_grads(sd, hp, b, drop=drop, dev="cuda")
+    for k in ("mel_loss", "loss_token", "loss"):
+        assert abs(float(o[k]) - losses[k]) <= 4e-3 * max(1.0, abs(losses[k])), (k, float(o[k]), losses[k])
+    check_grads(tr, model, grads, 2e-1, 4e-2)
+    # a second forward draws new masks; the same seed reproduces the step exactly
+    tr.zero_grad()
+    o2 = tr.forward_backward(*args)
+    assert tr.last_dropout_seed != seed and float(o2["loss"]) != float(o["loss"])
+    _, _, model_b = build(dropout, dropout_prenet)
+    tr_b = TTSTrainer(model_b, positive_weight=POS_WEIGHT, dropout_seed=42)
+    tr_b.zero_grad()
+    # (the loss sums are atomic accumulations: equal up to the order of the additions)
+    assert abs(float(tr_b.forward_backward(*args)["loss"]) - float(o["loss"])) < 2e-6 * abs(float(o["loss"]))
+
+
+def test_tts_reference_training_configuration_runs():
+    """dropout 0.1 / prenet 0.5, Noam rate, clip 1.0: eight optimizer steps, finite losses, parameters move."""
+    from oracle import transformer_tts_oracle as T
+    from transformer_tts_b200.tts_training import TTSTrainer
+
+    hp, sd, model = build(0.1, 0.5)
+    b = make_batch(hp, 4, 32, 160, 22)
+    src_mask, _ = T.create_masks(b["pos"], b["pos_in"])
+    tr = TTSTrainer(model, positive_weight=POS_WEIGHT)
+    w0 = model.decoder.decoder_prenet.layer.fc1.weight.detach().clone()
+    losses = [float(tr.train_step(*gpu_args(b, src_mask, hp.reduction_rate))["loss"]) for _ in range(8)]
+    print("losses with dropout:", losses)
+    assert all(l == l and abs(l) < 1e3 for l in losses)
+    assert not torch.equal(w0, model.decoder.decoder_prenet.layer.fc1.weight)

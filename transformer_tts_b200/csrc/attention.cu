@@ -650,7 +650,12 @@ static int attention_fwd_launch(const void* qkv, const uint8_t* mask, const int3
   if (rc) return rc;
   dim3 grid((T + kBQ - 1) / kBQ, H, B);
   const float scale_log2 = kLog2e / sqrtf(static_cast<float>(Dh));
-  if (skip_padded_q & 2) {   // flag word: bit 0 = skip padded query tiles, bit 1 = causal (inference instantiation)
+  if ((skip_padded_q & 2) && drop.thresh) {   // causal training with dropout on the probabilities (train.py, dropout 0.1)
+    auto kern = attention_fwd_kernel<kAttHalves, true, true>;
+    TTSB_SMEM_OPT_IN(kern, kAttSmem);
+    kern<<<grid, kAttThreads, kAttSmem, static_cast<cudaStream_t>(s)>>>(tmQ, tmQ32, tmKV, tmKV32, tmO, tmO32, mask, kv_info,
+                                                                       lse2, T, H, scale_log2, skip_padded_q & 1, drop);
+  } else if (skip_padded_q & 2) {   // flag word: bit 0 = skip padded query tiles, bit 1 = causal
     auto kern = attention_fwd_kernel<kAttHalves, false, true>;
     TTSB_SMEM_OPT_IN(kern, kAttSmem);
     kern<<<grid, kAttThreads, kAttSmem, static_cast<cudaStream_t>(s)>>>(tmQ, tmQ32, tmKV, tmKV32, tmO, tmO32, mask, kv_info,
@@ -697,6 +702,13 @@ extern "C" int ttsb200_attention_fwd_ragged(const void* qkv, const uint8_t* mask
 extern "C" int ttsb200_attention_fwd_causal(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
                                             float* lse2, int32_t B, int32_t T, int32_t H, int32_t Dh, ttsb200_stream_t s) {
   return attention_fwd_launch(qkv, mask, kv_info, ctx, lse2, B, T, H, Dh, 2, s);
+}
+
+extern "C" int ttsb200_attention_fwd_causal_drop(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,
+                                                 float* lse2, int32_t B, int32_t T, int32_t H, int32_t Dh, float drop_p,
+                                                 uint64_t drop_seed, int64_t drop_site, ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f, "attention_fwd: dropout probability must be in [0, 1)");
+  return attention_fwd_launch(qkv, mask, kv_info, ctx, lse2, B, T, H, Dh, 2, s, make_drop(drop_p, drop_seed, drop_site));
 }
 
 extern "C" int ttsb200_attention_fwd(const void* qkv, const uint8_t* mask, const int32_t* kv_info, void* ctx,

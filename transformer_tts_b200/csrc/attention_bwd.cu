@@ -528,6 +528,16 @@ extern "C" int ttsb200_attention_bwd_causal(const void* qkv, const void* dctx, c
   return attention_bwd_launch(qkv, dctx, mask, kv_info, lse2, delta, dqkv, B, T, H, Dh, make_drop(0.f, 0, -1), true, s);
 }
 
+extern "C" int ttsb200_attention_bwd_causal_drop(const void* qkv, const void* dctx, const uint8_t* mask,
+                                                 const int32_t* kv_info, const float* lse2, const float* delta, void* dqkv,
+                                                 int32_t B, int32_t T, int32_t H, int32_t Dh, float drop_p, uint64_t drop_seed,
+                                                 int64_t drop_site, ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f, "attention_bwd: dropout probability must be in [0, 1)");
+  return attention_bwd_launch(qkv, dctx, mask, kv_info, lse2, delta, dqkv, B, T, H, Dh, make_drop(drop_p, drop_seed, drop_site),
+                              true, s);
+}
+
+
 static int attention_bwd_launch(const void* qkv, const void* dctx, const uint8_t* mask, const int32_t* kv_info,
                                 const float* lse2, const float* delta, void* dqkv, int32_t B, int32_t T, int32_t H,
                                 int32_t Dh, const DropCfg drop, bool causal, ttsb200_stream_t s) {

@@ -119,6 +119,10 @@ _SIGNATURES = {
     "ttsb200_dropout_mask": ([C.c_void_p, C.c_int64, C.c_float, C.c_uint64, C.c_int64, C.c_void_p], C.c_int),
     "ttsb200_attention_fwd_drop": ([C.c_void_p] * 5 + [C.c_int32] * 4 + [C.c_float, C.c_uint64, C.c_int64, C.c_void_p], C.c_int),
     "ttsb200_attention_bwd_drop": ([C.c_void_p] * 7 + [C.c_int32] * 4 + [C.c_float, C.c_uint64, C.c_int64, C.c_void_p], C.c_int),
+    "ttsb200_attention_fwd_causal_drop": ([C.c_void_p] * 5 + [C.c_int32] * 4 + [C.c_float, C.c_uint64, C.c_int64, C.c_void_p],
+                                          C.c_int),
+    "ttsb200_attention_bwd_causal_drop": ([C.c_void_p] * 7 + [C.c_int32] * 4 + [C.c_float, C.c_uint64, C.c_int64, C.c_void_p],
+                                          C.c_int),
     "ttsb200_lr_bwd": ([C.c_void_p] * 4 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
     "ttsb200_embed_bwd": ([C.c_void_p] * 4 + [C.c_int32, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
                                               C.c_int32, C.c_void_p], C.c_int),
@@ -296,8 +300,15 @@ def attention_fwd(qkv: torch.Tensor, mask: torch.Tensor, kv_len: torch.Tensor, c
     B, T, W = qkv.shape
     Dh = W // (3 * H)
     if causal:
-        if skip_padded_queries or (drop is not None and drop[0] > 0):
-            raise ValueError("attention_fwd: causal has no dropout / ragged query skipping variant")
+        if skip_padded_queries:
+            raise ValueError("attention_fwd: causal has no ragged query skipping variant")
+        if drop is not None and drop[0] > 0:
+            _check(load().ttsb200_attention_fwd_causal_drop(
+                _ptr(qkv, torch.bfloat16, "qkv"), _ptr(mask, torch.uint8, "mask"), _ptr(kv_len, torch.int32, "kv_len"),
+                _ptr(ctx, torch.bfloat16, "ctx"), _ptr(lse2, torch.float32, "lse2"), B, T, H, Dh, float(drop[0]), int(drop[1]),
+                int(drop[2]), _stream()), "attention_fwd_causal_drop")
+            _count()
+            return
         _check(load().ttsb200_attention_fwd_causal(_ptr(qkv, torch.bfloat16, "qkv"), _ptr(mask, torch.uint8, "mask"),
                                                    _ptr(kv_len, torch.int32, "kv_len"), _ptr(ctx, torch.bfloat16, "ctx"),
                                                    _ptr(lse2, torch.float32, "lse2"), B, T, H, Dh, _stream()),
@@ -484,9 +495,14 @@ def attention_bwd(qkv, dctx, mask, kv_len, lse2, delta, H: int, drop: Optional[t
     B, T, W = qkv.shape
     dqkv = torch.empty_like(qkv)
     p, seed, site = drop if drop is not None else (0.0, 0, -1)
+    if causal and p > 0:
+        _check(load().ttsb200_attention_bwd_causal_drop(
+            _ptr(qkv, torch.bfloat16, "qkv"), _ptr(dctx, torch.bfloat16, "dctx"), _ptr(mask, torch.uint8, "mask"),
+            _ptr(kv_len, torch.int32, "kv_len"), _ptr(lse2, torch.float32, "lse2"), _ptr(delta, torch.float32, "delta"),
+            _ptr(dqkv), B, T, H, W // (3 * H), float(p), int(seed), int(site), _stream()), "attention_bwd_causal_drop")
+        _count(2)
+        return dqkv
     if causal:
-        if p > 0:
-            raise ValueError("attention_bwd: the causal variant has no dropout")
         _check(load().ttsb200_attention_bwd_causal(_ptr(qkv, torch.bfloat16, "qkv"), _ptr(dctx, torch.bfloat16, "dctx"),
                                                    _ptr(mask, torch.uint8, "mask"), _ptr(kv_len, torch.int32, "kv_len"),
                                                    _ptr(lse2, torch.float32, "lse2"), _ptr(delta, torch.float32, "delta"),
