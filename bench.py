@@ -536,24 +536,40 @@ def tts_train_record(cpu: bool, batch: int = 32, phonemes: int = 128, mel_len: i
     src_mask, trg_mask = T.create_masks(pos, pos_in)
     a = (text.cuda(), mel_in.cuda(), src_mask.cuda(), (pos_in != 0).to(torch.uint8).cuda(), mel[:, r:, :].contiguous().cuda(),
          stop[:, r:].contiguous().cuda())
-    tr = TTSTrainer(model, positive_weight=5.0)
-    for _ in range(3):
-        out = tr.train_step(*a)
-    torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     steps = 5
-    l0 = lib.LAUNCH_COUNT
-    e0.record()
-    for _ in range(steps):
-        out = tr.train_step(*a)
-    e1.record()
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / steps
+
+    def timed(tr):
+        for _ in range(3):
+            out = tr.train_step(*a)
+        torch.cuda.synchronize()
+        l0 = lib.LAUNCH_COUNT
+        e0.record()
+        for _ in range(steps):
+            out = tr.train_step(*a)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / steps, (lib.LAUNCH_COUNT - l0) // steps, out
+
+    # the reference's training construction (train.py:117-126: dropout 0.1, prenet 0.5), counter-based masks
+    from transformer_tts_b200.Models.transformer import Transformer
+    md = Transformer(hp=hp, src_vocab=hp.vocab_size, trg_vocab=hp.mel_dim, d_model_encoder=hp.d_model_encoder,
+                     N_e=hp.n_layer_encoder, n_head_encoder=hp.n_head_encoder,
+                     ff_conv_kernel_size_encoder=hp.ff_conv_kernel_size_encoder, concat_after_encoder=hp.concat_after_encoder,
+                     d_model_decoder=hp.d_model_decoder, N_d=hp.n_layer_decoder, n_head_decoder=hp.n_head_decoder,
+                     ff_conv_kernel_size_decoder=hp.ff_conv_kernel_size_decoder, concat_after_decoder=hp.concat_after_decoder,
+                     reduction_rate=r, dropout=0.1, dropout_prenet=0.5, dropout_postnet=0.5)
+    md.load_state_dict(sd)
+    ms_drop, launches_drop, _ = timed(TTSTrainer(md.cuda().train(), positive_weight=5.0))
+    del md
+    ms, launches, out = timed(TTSTrainer(model, positive_weight=5.0))
     frames = float((pos_mel[:, r:] != 0).sum())
     rec = {"metric": "transformer_tts_train_mel_frames_per_sec", "value": frames / ms * 1e3, "unit": "frames/s", "ms_per_step": ms,
            "batch": batch, "phonemes": phonemes, "mel_len": mel_len, "decoder_positions": int(mel_in.shape[1]),
-           "valid_target_frames": frames, "gpu_launches_per_step": (lib.LAUNCH_COUNT - l0) // steps, "loss": float(out["loss"]),
+           "valid_target_frames": frames, "gpu_launches_per_step": launches, "loss": float(out["loss"]),
            "dropout": 0.0, "optimizer": "adam (Noam rate), clip 1.0",
+           "with_reference_dropout": {"ms_per_step": ms_drop, "frames_per_s": frames / ms_drop * 1e3, "dropout": 0.1,
+                                      "dropout_prenet": 0.5, "gpu_launches_per_step": launches_drop},
            "what": "tts_training.TTSTrainer.train_step: tcgen05 GEMMs / wgrad, causal tcgen05 attention forward + backward, "
                    "encoder-decoder attention on a packed sequence, fused clip + Adam over the flat buffers"}
 

@@ -210,3 +210,63 @@ def test_tts_reference_training_configuration_runs():
     print("losses with dropout:", losses)
     assert all(l == l and abs(l) < 1e3 for l in losses)
     assert not torch.equal(w0, model.decoder.decoder_prenet.layer.fc1.weight)
+
+
+def test_reference_training_call_is_a_drop_in():
+    """The statements of train.py:186-259 on the drop-in module: model(...) in train() mode, the reshapes, the three loss
+    terms with torch, loss.backward(), clip_grad_norm_, torch.optim.Adam.  Gradients against the oracle's autograd (dropout 0),
+    then two optimizer steps with the reference's construction (dropout 0.1 / 0.5)."""
+    import torch.nn as nn
+
+    from oracle import transformer_tts_oracle as T
+
+    hp, sd, model = build()
+    r = hp.reduction_rate
+    b = make_batch(hp, 3, 24, 96, 41)
+    c = lambda t: t.cuda()  # noqa: E731
+
+    def step(model):
+        text, mel, stop_token = c(b["text"]), c(b["mel"]), c(b["stop"])
+        mel_input = mel[:, :-r:r, :]                                             # train.py:186
+        src_mask, trg_mask = T.create_masks(c(b["pos"]), c(b["pos_in"]))        # :195
+        outputs_prenet, outputs_postnet, outputs_stop_token, attn_enc, attn_dec_dec, attn_dec_enc = model(
+            text, mel_input, src_mask, trg_mask, None)                          # :197
+        attn_dec_dec, attn_dec_enc, attn_enc = attn_dec_dec.cpu(), attn_dec_enc.cpu(), attn_enc.cpu()   # :198-200
+        bb, t, ch = outputs_prenet.shape                                        # :204-208
+        outputs_prenet = outputs_prenet.reshape(bb, t * r, ch // r)
+        outputs_postnet = outputs_postnet.reshape(bb, t * r, ch // r)
+        outputs_stop_token = outputs_stop_token.reshape(bb, t * r)
+        mel_loss = nn.L1Loss()(outputs_prenet, mel[:, r:, :])                   # :211-217
+        post_mel_loss = nn.L1Loss()(outputs_postnet, mel[:, r:, :])
+        loss_token = F.binary_cross_entropy_with_logits(outputs_stop_token, stop_token[:, r:], reduction="mean",
+                                                        pos_weight=torch.tensor(POS_WEIGHT, device="cuda"))
+        loss = mel_loss + post_mel_loss + loss_token
+        loss.backward()                                                         # :252
+        return loss
+
+    loss = step(model)
+    losses, grads, _ = oracle_grads(sd, hp, b)
+    assert abs(float(loss.detach()) - losses["loss"]) < 2e-3 * max(1.0, abs(losses["loss"]))
+
+    class _G:   # check_grads reads gradients through .G(p)
+        @staticmethod
+        def G(p):
+            return p.grad
+
+    check_grads(_G, model, grads, 1.2e-1, 3e-2)
+    hp, sd, model = build(0.1, 0.5)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3, betas=(0.9, 0.98), eps=1e-9)
+    w0 = model.out.weight.detach().clone()
+    for _ in range(2):
+        opt.zero_grad()
+        loss = step(model)
+        torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)                 # :255
+        opt.step()
+        assert torch.isfinite(loss).item()
+    assert not torch.equal(w0, model.out.weight)
+    # eval() after training steps: the decode path sees the updated parameters
+    model.eval()
+    with torch.no_grad():
+        src_mask, trg_mask = T.create_masks(c(b["pos"]), c(b["pos_in"]))
+        pre, *_ = model(c(b["text"]), c(b["mel_input"]), src_mask, trg_mask, None, training=False)
+    assert torch.isfinite(pre).all()

@@ -7,7 +7,9 @@ makes at every step — and returns the same 6-tuple (attention maps None, SURVE
 test.py:128-191 itself, which the reference has only as script code: one decoder position per step against cached keys
 and values instead of a forward over the whole prefix per step.
 
-Training (train.py) is not built: `forward` raises in train() mode.
+In train() mode `forward` is the teacher-forced training forward of train.py:197 with autograd
+connected to every parameter through one Function (tts_training.autograd_forward: dropout with counter-based masks, backward
+on the same kernels); the loop-owning form with flat buffers and the fused clip + Adam is tts_training.TTSTrainer.
 """
 from __future__ import annotations
 
@@ -93,6 +95,24 @@ class Transformer(nn.Module):
             e_bf16 = out
         return e_bf16
 
+    def _forward_train(self, src, trg, src_mask, trg_mask):
+        """train.py:197: the same 6-tuple with autograd attached.  The three attention maps, which train.py:198-200 moves to
+        the host and nothing reads (the image logging is commented out), are EMPTY tensors (not materialised)."""
+        from ..tts_training import autograd_forward
+
+        if trg_mask is None:
+            raise NotImplementedError("the training forward needs the target mask (train.py:195)")
+        tm = trg_mask if trg_mask.dim() == 3 else trg_mask.unsqueeze(1)
+        key_valid = tm[:, -1, :].to(torch.uint8).contiguous()           # last row of causal & padding = the padding mask
+        kvt = lib.mask_lengths(key_valid)
+        if not torch.equal(kvt[:, 0], kvt[:, 1]):
+            raise NotImplementedError("the target mask must be causal AND a padding mask (train.py:26-58)")
+        pre, stop = autograd_forward(self, src, trg, src_mask, key_valid)
+        if self.reduction_rate == 1:
+            stop = stop.squeeze(2)
+        none = pre.new_empty(0)
+        return pre, pre, stop, none, none, none
+
     def _split(self, out_all: torch.Tensor, n: int):
         """(R, cap, mel*r + r) -> outputs (R, n, mel*r), stop (R, n, r) -> the reference's shapes (transformer.py:109-111)."""
         md = self.mel_dim * self.reduction_rate
@@ -111,11 +131,11 @@ class Transformer(nn.Module):
         prefix_mode "batched" (default): the whole prefix at once on the tensor-core kernels (Decoder.run_prefix: tcgen05
         GEMMs, causal tcgen05 attention, encoder-decoder attention on a packed sequence, fused FeedForward);
         "steps": T decode steps of the generate() machine (each position sees the cached keys / values of the earlier ones)."""
-        if self.training:
-            raise NotImplementedError("Transformer-TTS training (SURVEY §8f row f2) is not built: call .eval()")
         E.require_cuda(src, "Transformer")
         if spkr_emb is not None or ref_mel is not None:
             raise NotImplementedError("speaker / reference-mel inputs are out of scope")
+        if self.training:
+            return self._forward_train(src, trg, src_mask, trg_mask)
         B, T, _ = trg.shape
         trg_len = key_valid = None
         if trg_mask is not None:
