@@ -280,6 +280,11 @@ int ttsb200_split_f16(const float* x, void* out_split, int64_t rows, int32_t D, 
 int ttsb200_conv_wgrad(const void* dy, int64_t ld_dy, const void* x, int64_t ld_x, float* dw,
                        int64_t stride_tap, int64_t stride_n, int64_t stride_c, int32_t B, int32_t T,
                        int32_t N, int32_t C, int32_t taps, int32_t pad_left, ttsb200_stream_t stream);
+/* The same plus the bias gradient in the same launch: db[n] += sum_{b,t} dy[b,t,n] (fp32 (N), accumulated; NULL = none).  The
+ * tiles of x-channel block 0 multiply dy by a constant operand of ones, so dy is not read a second time by a column-sum pass. */
+int ttsb200_conv_wgrad_bias(const void* dy, int64_t ld_dy, const void* x, int64_t ld_x, float* dw, float* db,
+                            int64_t stride_tap, int64_t stride_n, int64_t stride_c, int32_t B, int32_t T,
+                            int32_t N, int32_t C, int32_t taps, int32_t pad_left, ttsb200_stream_t stream);
 
 /* Backward of ttsb200_attention_fwd (autograd of Models/modules.py:7-21): dqkv bf16 (B,T,3*H*Dh) =
  * [dq | dk | dv] from qkv, dctx bf16 (B,T,H*Dh), the saved lse2 (B,H,T) and delta (B,H,T) =

@@ -66,6 +66,12 @@ def test_conv_wgrad(L, B, T, N, C, taps, pad):
     dw2 = torch.zeros(taps, N, C, device=dev())
     L.conv_wgrad(dy, x, dw2, taps=taps, pad_left=pad)
     assert rel_err(dw2, w.grad.permute(2, 0, 1)) < 1e-3
+    # the bias gradient in the same launch (the ones operand): accumulated onto what is there, dW unchanged by it
+    db = torch.full((N,), 0.5, device=dev())
+    dw3 = torch.zeros(taps, N, C, device=dev())
+    L.conv_wgrad(dy, x, dw3, taps=taps, pad_left=pad, dbias=db)
+    assert rel_err(db, 0.5 + dy.double().sum((0, 1))) < 1e-5
+    assert rel_err(dw3, w.grad.permute(2, 0, 1)) < 1e-3
 
 
 def test_conv_wgrad_column_slice(L):
@@ -77,6 +83,9 @@ def test_conv_wgrad_column_slice(L):
         L.conv_wgrad(dqkv, x, dw, n_off=i * D, N=D)
         ref = dqkv[..., i * D:(i + 1) * D].double().reshape(-1, D).T @ x.double().reshape(-1, D)
         assert rel_err(dw, ref) < 1e-3
+        db = torch.zeros(D, device=dev())
+        L.conv_wgrad(dqkv, x, torch.zeros(D, D, device=dev()), n_off=i * D, N=D, dbias=db)
+        assert rel_err(db, dqkv[..., i * D:(i + 1) * D].double().sum((0, 1))) < 1e-5
 
 
 # ------------------------------------------------------------------------------------------------

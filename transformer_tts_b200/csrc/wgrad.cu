@@ -18,6 +18,11 @@
 // (dW is the caller's zeroed / accumulating gradient buffer, arbitrary element strides so that the
 // reference's Conv1d (out, in, k) layout is written directly).
 //
+// Bias gradient (db[n] = sum_{b,t} dy[b,t,n], the autograd backward of the bias): the tiles of x-channel block 0 / tap 0
+// issue one more MMA per 16 time rows against a constant B operand of ones (N = 16, a 2 KB shared-memory region filled with
+// bf16 1.0 — every element equal, so the operand layout does not matter) into 16 more TMEM columns; column 0 of that
+// accumulator is the bias gradient of the tile's 128 channels.  It replaces a separate column-sum pass over dy.
+//
 // Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer, warps 2..5 = epilogue.
 #include "common.cuh"
 #include "../../include/ttsb200.h"
@@ -31,12 +36,14 @@ constexpr int kWgStages = 6;
 constexpr int kWgBox = 64 * 64 * 2;                  // 64 rows x 64 channels bf16 = 8 KB
 constexpr int kWgStageBytes = 4 * kWgBox;            // A: 2 boxes, B: 2 boxes
 constexpr int kWgThreads = 192;
-constexpr int kWgSmem = kWgStages * kWgStageBytes + 1024 + 256;
+constexpr int kWgOnes = 2048;                        // the ones operand: 16 time rows x 128 B
+constexpr int kWgSmem = kWgStages * kWgStageBytes + kWgOnes + 1024 + 256;
 
 struct WgradDev {
   int B, T, N, C, taps, pad_left;
   int n_tiles, c_tiles, chunks_per_utt, total_chunks, chunks_per_split;
   float* dw;
+  float* db;             // optional bias gradient (N), accumulated
   long long sj, sn, sc;  // element strides of dW[j][n][c]
   int vec_ok;            // dW base and row strides keep 16-byte alignment for v4 reductions
 };
@@ -46,7 +53,8 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant__ C
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kWgStages * kWgStageBytes);
+  uint8_t* ones = smem + kWgStages * kWgStageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ones + kWgOnes);
   uint64_t* bar_full = bars;
   uint64_t* bar_empty = bars + kWgStages;
   uint64_t* bar_acc = bars + 2 * kWgStages;
@@ -65,6 +73,11 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant__ C
   int ch_hi = ch_lo + p.chunks_per_split;
   if (ch_hi > p.total_chunks) ch_hi = p.total_chunks;
   const int nch = ch_hi - ch_lo;  // may be <= 0 for the last split
+  const bool do_bias = p.db != nullptr && ct == 0 && tap == 0;
+  if (do_bias) {
+    for (int i = threadIdx.x; i < kWgOnes / 4; i += kWgThreads) reinterpret_cast<uint32_t*>(ones)[i] = 0x3F803F80u;  // bf16 1.0 x 2
+    fence_async_smem();
+  }
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmDy);
@@ -77,7 +90,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant__ C
     fence_mbar_init();
   }
   if (warp == 1) {
-    tmem_alloc(smem_u32(tmem_slot), 128);
+    tmem_alloc(smem_u32(tmem_slot), 256);   // 128 columns of dW + 16 of the bias-gradient accumulator
     tmem_relinquish();
   }
   tc_fence_before();
@@ -107,6 +120,8 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant__ C
     } else if (warp == 1) {
       // whole warp converged, MMAs predicated on one elected lane (uniform-register operands, no waterfall loops)
       constexpr uint32_t idesc = umma_idesc_bf16(kWgM, kWgN, 1, 1);  // both operands MN-major
+      constexpr uint32_t idesc_b = umma_idesc_bf16(kWgM, 16, 1, 1);
+      const uint64_t odesc = umma_smem_desc(smem_u32(ones), kWgBox, 1024, kLayoutSW128);
       const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
       const uint32_t leader = elect_one();
       for (int i = 0; i < nch; ++i) {
@@ -123,6 +138,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant__ C
             const uint64_t adesc = umma_smem_desc(a_base + k * 2048, kWgBox, 1024, kLayoutSW128);
             const uint64_t bdesc = umma_smem_desc(b_base + k * 2048, kWgBox, 1024, kLayoutSW128);
             umma_bf16(tb, adesc, bdesc, idesc, (i | k) != 0 ? 1u : 0u);
+            if (do_bias) umma_bf16(tb + kWgN, adesc, odesc, idesc_b, (i | k) != 0 ? 1u : 0u);
           }
           umma_commit(smem_u32(&bar_empty[s]));
         }
@@ -138,6 +154,12 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant__ C
       mbar_wait(smem_u32(bar_acc), 0);
       tc_fence_after();
       float* base = p.dw + tap * p.sj + static_cast<long long>(n) * p.sn;
+      if (do_bias) {
+        float v[32];
+        tmem_ld32(tmem_base + lane_off + kWgN, v);
+        tmem_ld_wait();
+        if (n < p.N) atomicAdd(p.db + n, v[0]);
+      }
 #pragma unroll 1
       for (int c = 0; c < kWgN; c += 32) {
         float v[32];
@@ -166,16 +188,16 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant__ C
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, 128);
+  if (warp == 1) tmem_dealloc(tmem_base, 256);
 }
 
 }  // namespace ttsb
 
 using namespace ttsb;
 
-extern "C" int ttsb200_conv_wgrad(const void* dy, int64_t ld_dy, const void* x, int64_t ld_x, float* dw,
-                                  int64_t stride_tap, int64_t stride_n, int64_t stride_c, int32_t B, int32_t T,
-                                  int32_t N, int32_t C, int32_t taps, int32_t pad_left, ttsb200_stream_t s) {
+extern "C" int ttsb200_conv_wgrad_bias(const void* dy, int64_t ld_dy, const void* x, int64_t ld_x, float* dw, float* db,
+                                       int64_t stride_tap, int64_t stride_n, int64_t stride_c, int32_t B, int32_t T,
+                                       int32_t N, int32_t C, int32_t taps, int32_t pad_left, ttsb200_stream_t s) {
   TTSB_CHECK_ARG(dy && x && dw, "conv_wgrad: null pointer");
   TTSB_CHECK_ARG(B > 0 && T > 0 && N > 0 && C > 0 && taps > 0, "conv_wgrad: bad dims");
   TTSB_CHECK_ARG(ld_dy % 8 == 0 && ld_x % 8 == 0 && ld_dy >= N && ld_x >= C && N % 8 == 0 && C % 8 == 0,
@@ -209,10 +231,16 @@ extern "C" int ttsb200_conv_wgrad(const void* dy, int64_t ld_dy, const void* x, 
   if (splits < 1) splits = 1;
   d.chunks_per_split = (d.total_chunks + splits - 1) / splits;
   splits = (d.total_chunks + d.chunks_per_split - 1) / d.chunks_per_split;
-  d.dw = dw; d.sj = stride_tap; d.sn = stride_n; d.sc = stride_c;
+  d.dw = dw; d.db = db; d.sj = stride_tap; d.sn = stride_n; d.sc = stride_c;
   d.vec_ok = ((reinterpret_cast<uintptr_t>(dw) & 15) == 0 && stride_n % 4 == 0 && stride_tap % 4 == 0) ? 1 : 0;
   dim3 grid(tiles, splits);
   wgrad_kernel<<<grid, kWgThreads, kWgSmem, static_cast<cudaStream_t>(s)>>>(tmDy, tmX, d);
   TTSB_CHECK_CUDA(cudaGetLastError());
   return TTSB_OK;
+}
+
+extern "C" int ttsb200_conv_wgrad(const void* dy, int64_t ld_dy, const void* x, int64_t ld_x, float* dw,
+                                  int64_t stride_tap, int64_t stride_n, int64_t stride_c, int32_t B, int32_t T,
+                                  int32_t N, int32_t C, int32_t taps, int32_t pad_left, ttsb200_stream_t s) {
+  return ttsb200_conv_wgrad_bias(dy, ld_dy, x, ld_x, dw, nullptr, stride_tap, stride_n, stride_c, B, T, N, C, taps, pad_left, s);
 }

@@ -103,6 +103,8 @@ _SIGNATURES = {
     "ttsb200_attention_fwd_lse": ([C.c_void_p] * 5 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
     "ttsb200_conv_wgrad": ([C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64,
                             C.c_int64] + [C.c_int32] * 6 + [C.c_void_p], C.c_int),
+    "ttsb200_conv_wgrad_bias": ([C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64,
+                                 C.c_int64] + [C.c_int32] * 6 + [C.c_void_p], C.c_int),
     "ttsb200_attention_bwd": ([C.c_void_p] * 7 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
     "ttsb200_attn_delta": ([C.c_void_p] * 3 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
     "ttsb200_layernorm_bwd": ([C.c_void_p] * 9 + [C.c_int32] + [C.c_void_p] * 6 + [C.c_int64, C.c_int32, C.c_float,
@@ -459,9 +461,10 @@ def cast_bf16(x: torch.Tensor) -> torch.Tensor:
 # training step (include/ttsb200.h, "TRAINING STEP")
 # --------------------------------------------------------------------------------------------------
 def conv_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, *, taps: int = 1, pad_left: int = 0,
-               n_off: int = 0, N: Optional[int] = None, conv_layout: bool = False) -> None:
+               n_off: int = 0, N: Optional[int] = None, conv_layout: bool = False, dbias: Optional[torch.Tensor] = None) -> None:
     """dW += dy^T (*) x.  dy bf16 (B,T,ld) of which columns [n_off, n_off+N) are used; x bf16 (B,T,C).
-    dw fp32: (N,C) for a linear, (taps,N,C) or — conv_layout — the reference's Conv1d (N,C,taps)."""
+    dw fp32: (N,C) for a linear, (taps,N,C) or — conv_layout — the reference's Conv1d (N,C,taps).
+    dbias fp32 (N), optional: += the column sums of the same dy columns (the bias gradient), in the same launch."""
     B, T, ldy = dy.shape
     Cin = x.shape[2]
     N = ldy - n_off if N is None else N
@@ -474,8 +477,11 @@ def conv_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, *, taps: int
         # reference's Conv1d (out, in, k) layout
         target = torch.zeros((taps, N, Cin), device=dw.device, dtype=torch.float32)
     sj, sn, sc = N * Cin, Cin, 1
-    _check(load().ttsb200_conv_wgrad(dy.data_ptr() + 2 * n_off, ldy, x.data_ptr(), x.shape[2], target.data_ptr(), sj,
-                                     sn, sc, B, T, N, Cin, taps, pad_left, _stream()), "conv_wgrad")
+    if dbias is not None and dbias.numel() != N:
+        raise ValueError(f"conv_wgrad: dbias has {dbias.numel()} elements, expected {N}")
+    _check(load().ttsb200_conv_wgrad_bias(dy.data_ptr() + 2 * n_off, ldy, x.data_ptr(), x.shape[2], target.data_ptr(),
+                                          _ptr(dbias, torch.float32, "dbias"), sj, sn, sc, B, T, N, Cin, taps, pad_left,
+                                          _stream()), "conv_wgrad")
     _count()
     if target is not dw:
         dw.view(N, Cin, taps).add_(target.permute(1, 2, 0))

@@ -342,14 +342,14 @@ class Trainer:
                               dgamma=G(ff.layer_norm.weight), dbeta=G(ff.layer_norm.bias), site_g=S(f"{i}.drop2"),
                               site_dx=S(f"{i}.ff"), dx_mode=1 if pd > 0 else 0, **dk)
             # upre = conv2(h) + b2 + yn
-            lib.colsum(dupre_bf, G(ff.f_2.bias))
-            lib.conv_wgrad(dupre_bf, s["h"], G(ff.f_2.weight), taps=k, pad_left=k // 2, conv_layout=True)
+            lib.conv_wgrad(dupre_bf, s["h"], G(ff.f_2.weight), taps=k, pad_left=k // 2, conv_layout=True,
+                           dbias=G(ff.f_2.bias))
             dh = bf(B, T, 4 * D)
             lib.conv_gemm(dupre_bf, _t(lc["w2"]), self.zeros(4 * D), taps=k, pad_left=k - 1 - k // 2, block_n=256,
                           act=lib.ACT_RELU_GRAD, gate_bf16=s["h"], out_bf16=dh)
             # h = relu(conv1(yn) + b1)
-            lib.colsum(dh, G(ff.f_1.bias))
-            lib.conv_wgrad(dh, s["yn"], G(ff.f_1.weight), taps=k, pad_left=k // 2, conv_layout=True)
+            lib.conv_wgrad(dh, s["yn"], G(ff.f_1.weight), taps=k, pad_left=k // 2, conv_layout=True,
+                           dbias=G(ff.f_1.bias))
             dyn = f32(B, T, D)
             lib.conv_gemm(dh, _t(lc["w1"]), self.zeros(D), taps=k, pad_left=k - 1 - k // 2, block_n=192,
                           res_f32=dupre, res_bstride=T * D, res_tstride=D, out_f32=dyn)
@@ -360,15 +360,13 @@ class Trainer:
                               dgamma=G(layer.norm_2.weight), dbeta=G(layer.norm_2.bias), site_dx=S(f"{i}.drop1"),
                               dx_mode=2 if pd > 0 else 0, **dk)
             # y = x + ctx Wo^T + bo
-            lib.colsum(dy_bf, G(a.out.bias))
-            lib.conv_wgrad(dy_bf, s["ctx"], G(a.out.weight))
+            lib.conv_wgrad(dy_bf, s["ctx"], G(a.out.weight), dbias=G(a.out.bias))
             dctx = bf(B, T, D)
             lib.conv_gemm(dy_bf, _t(lc["wo"]), self.zeros(D), block_n=192, out_bf16=dctx)
             delta = lib.attn_delta(dctx, s["ctx"], H)
             dqkv = lib.attention_bwd(s["qkv"], dctx, mask, kv, s["lse"], delta, H, drop=(pd, seed, S(f"{i}.attn")))
             for j, lin in enumerate((a.q_linear, a.k_linear, a.v_linear)):
-                lib.colsum(dqkv, G(lin.bias), cols=D, col_off=j * D)
-                lib.conv_wgrad(dqkv, s["xn"], G(lin.weight), n_off=j * D, N=D)
+                lib.conv_wgrad(dqkv, s["xn"], G(lin.weight), n_off=j * D, N=D, dbias=G(lin.bias))
             dxn = f32(B, T, D)
             lib.conv_gemm(dqkv, _t(lc["wqkv"]), self.zeros(D), block_n=192, out_f32=dxn)
             # xn = norm_1(x); y = x + attn(xn)
@@ -433,16 +431,16 @@ class Trainer:
                           row_mask=tape["mask"], relu_gate=True, dx_bf16=dc2, dgamma=G(pred.layer_norm2.weight),
                           dbeta=G(pred.layer_norm2.bias), dvec=G(pred.linear_layer.weight),
                           dscal=G(pred.linear_layer.bias), site_g=tape["s2"], **tape["dk"])
-        lib.colsum(dc2, G(pred.conv2.bias))
-        lib.conv_wgrad(dc2, tape["h"], G(pred.conv2.weight), taps=3, pad_left=1, conv_layout=True)
+        lib.conv_wgrad(dc2, tape["h"], G(pred.conv2.weight), taps=3, pad_left=1, conv_layout=True,
+                       dbias=G(pred.conv2.bias))
         dh = torch.empty((B, T, fs), device=dev, dtype=torch.float32)
         lib.conv_gemm(dc2, _t(t["w2"]), self.zeros(fs), taps=3, pad_left=1, block_n=128, out_f32=dh)
         dc1 = torch.empty((B, T, fs), device=dev, dtype=torch.bfloat16)
         lib.layernorm_bwd(tape["r1"], t["ln1"][0], g_f32=dh, relu_gate=True, dx_bf16=dc1,
                           dgamma=G(pred.layer_norm1.weight), dbeta=G(pred.layer_norm1.bias), site_g=tape["s1"],
                           **tape["dk"])
-        lib.colsum(dc1, G(pred.conv1.bias))
-        lib.conv_wgrad(dc1, tape["x"], G(pred.conv1.weight), taps=3, pad_left=1, conv_layout=True)
+        lib.conv_wgrad(dc1, tape["x"], G(pred.conv1.weight), taps=3, pad_left=1, conv_layout=True,
+                       dbias=G(pred.conv1.bias))
         dx = torch.empty((B, T, Din), device=dev, dtype=torch.float32)
         kw = {} if add_f32 is None else dict(res_f32=add_f32, res_bstride=T * Din, res_tstride=Din)
         lib.conv_gemm(dc1, _t(t["w1"]), self.zeros(Din), taps=3, pad_left=1, block_n=192, out_f32=dx, **kw)
@@ -518,8 +516,7 @@ class Trainer:
                 dist.all_reduce(red, group=self.pg)
             dc = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
             lib.bn_tanh_bwd(dh, s["h"], s["c"], s["ms"], bn.weight, red, dc, 1.0 / s["count"], apply=True, drop=s["drop"])
-            lib.colsum(dc, G(cv.bias))
-            lib.conv_wgrad(dc, s["x"], G(cv.weight), taps=5, pad_left=4, conv_layout=True)
+            lib.conv_wgrad(dc, s["x"], G(cv.weight), taps=5, pad_left=4, conv_layout=True, dbias=G(cv.bias))
             if i > 0:
                 dh = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
                 lib.conv_gemm(dc, _t(s["w"]), self.zeros(D), taps=5, pad_left=0, block_n=192, out_bf16=dh)
