@@ -391,6 +391,19 @@ int ttsb200_bce_logits_loss(const float* x, const float* y, float* grad, float* 
 /* out_bf16[i] = gate_bf16[i] > 0 ? g[i] : 0: backward of a ReLU whose (bf16) output is `gate` (Models/prenets.py:36-37). */
 int ttsb200_relu_gate(const float* g, const void* gate_bf16, void* out_bf16, int64_t n, ttsb200_stream_t stream);
 
+/* Input-gradient operands of a whole backward pass in one launch.  The reference gets input gradients from autograd
+ * (loss.backward(), train_fastspeech2.py:304 / train.py:252); here they are ttsb200_conv_gemm calls on the transposed,
+ * tap-flipped weights, and this entry builds all of them: for every entry dst[taps-1-j][c][n] = src[j][n][c] (bf16, device
+ * pointers; src = the forward operand (taps, N, C)).  tile0 = index of the entry's first 64 x 64 tile: entries in ascending
+ * tile0, taps * ceil(N/64) * ceil(C/64) tiles each, total_tiles their sum.  The table itself is in device memory. */
+typedef struct {
+  const void* src;
+  void* dst;
+  int32_t taps, N, C, tile0;
+} ttsb200_wt_entry;
+int ttsb200_weight_transpose(const ttsb200_wt_entry* table_dev, int32_t n_entries, int32_t total_tiles,
+                             ttsb200_stream_t stream);
+
 /* Optimizer over one flat fp32 buffer (train_fastspeech2.py:117-120,304-315): out += sum g^2; then
  * g' = g*gscale*min(1, clip/(sqrt(sumsq)*gscale + 1e-6)) (clip_grad_norm_; clip <= 0 disables) and one
  * torch.optim.Adam step (step >= 1 for the bias corrections). */

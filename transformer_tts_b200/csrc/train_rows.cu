@@ -541,6 +541,51 @@ relu_gate_kernel(const float* __restrict__ g, const __nv_bfloat16* __restrict__ 
 }
 
 // ------------------------------------------------------------------------------------------------
+// dgrad operands of a whole backward pass in ONE launch: for every table entry, dst[taps-1-j][c][n] = src[j][n][c]
+// (bf16; the forward operand (taps, N, C) of a Linear / Conv1d -> the transposed, tap-flipped operand the input-gradient
+// GEMM reads).  One CTA per 64 x 64 tile through shared memory; entries carry the index of their first tile.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+weight_transpose_kernel(const ttsb200_wt_entry* __restrict__ tab, int n_entries) {
+  __shared__ __nv_bfloat16 tile[64][66];
+  __shared__ ttsb200_wt_entry ent;
+  if (threadIdx.x == 0) {
+    int lo = 0, hi = n_entries - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (tab[mid].tile0 <= static_cast<int>(blockIdx.x)) lo = mid; else hi = mid - 1;
+    }
+    ent = tab[lo];
+  }
+  __syncthreads();
+  const int N = ent.N, C = ent.C;
+  const int tn = (N + 63) / 64, tc = (C + 63) / 64;
+  const int local = blockIdx.x - ent.tile0;
+  const int j = local / (tn * tc);
+  const int r = local - j * (tn * tc);
+  const int n0 = (r / tc) * 64, c0 = (r % tc) * 64;
+  const __nv_bfloat16* src = static_cast<const __nv_bfloat16*>(ent.src) + static_cast<int64_t>(j) * N * C;
+  __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(ent.dst) + static_cast<int64_t>(ent.taps - 1 - j) * C * N;
+  const int ty = threadIdx.x >> 5, tx = threadIdx.x & 31;
+  const __nv_bfloat16 zero = __float2bfloat16(0.f);
+#pragma unroll
+  for (int rr = 0; rr < 8; ++rr) {
+    const int row = ty + rr * 8, n = n0 + row, c = c0 + 2 * tx;
+    tile[row][2 * tx] = (n < N && c < C) ? src[static_cast<int64_t>(n) * C + c] : zero;
+    tile[row][2 * tx + 1] = (n < N && c + 1 < C) ? src[static_cast<int64_t>(n) * C + c + 1] : zero;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int rr = 0; rr < 8; ++rr) {
+    const int crow = ty + rr * 8, c = c0 + crow, n = n0 + 2 * tx;
+    if (c < C) {
+      if (n < N) dst[static_cast<int64_t>(c) * N + n] = tile[2 * tx][crow];
+      if (n + 1 < N) dst[static_cast<int64_t>(c) * N + n + 1] = tile[2 * tx + 1][crow];
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // delta[b,h,t] = sum_d dctx[b,t,h*Dh+d] * ctx[b,t,h*Dh+d]   (softmax backward row term of attention)
 // one warp per (b,t); lanes own 4-column chunks; Dh = 96 = 24 chunks, so chunk c belongs to head c/24.
 // ------------------------------------------------------------------------------------------------
@@ -871,6 +916,14 @@ extern "C" int ttsb200_relu_gate(const float* g, const void* gate_bf16, void* ou
   const int64_t want = (n + 255) / 256;
   relu_gate_kernel<<<static_cast<unsigned>(want < 1184 ? want : 1184), 256, 0, static_cast<cudaStream_t>(s)>>>(
       g, static_cast<const __nv_bfloat16*>(gate_bf16), static_cast<__nv_bfloat16*>(out_bf16), n);
+  TTSB_LAUNCH_CHECK();
+  return TTSB_OK;
+}
+
+extern "C" int ttsb200_weight_transpose(const ttsb200_wt_entry* table_dev, int32_t n_entries, int32_t total_tiles,
+                                        ttsb200_stream_t s) {
+  TTSB_CHECK_ARG(table_dev && n_entries > 0 && total_tiles > 0, "weight_transpose: bad args");
+  weight_transpose_kernel<<<static_cast<unsigned>(total_tiles), 256, 0, static_cast<cudaStream_t>(s)>>>(table_dev, n_entries);
   TTSB_LAUNCH_CHECK();
   return TTSB_OK;
 }

@@ -105,6 +105,7 @@ _SIGNATURES = {
                             C.c_int64] + [C.c_int32] * 6 + [C.c_void_p], C.c_int),
     "ttsb200_conv_wgrad_bias": ([C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64,
                                  C.c_int64] + [C.c_int32] * 6 + [C.c_void_p], C.c_int),
+    "ttsb200_weight_transpose": ([C.c_void_p, C.c_int32, C.c_int32, C.c_void_p], C.c_int),
     "ttsb200_attention_bwd": ([C.c_void_p] * 7 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
     "ttsb200_attn_delta": ([C.c_void_p] * 3 + [C.c_int32] * 4 + [C.c_void_p], C.c_int),
     "ttsb200_layernorm_bwd": ([C.c_void_p] * 9 + [C.c_int32] + [C.c_void_p] * 6 + [C.c_int64, C.c_int32, C.c_float,
@@ -866,3 +867,29 @@ def relu_gate(g: torch.Tensor, gate: torch.Tensor) -> torch.Tensor:
                                     _stream()), "relu_gate")
     _count()
     return out
+
+
+_WT_DTYPE = None
+
+
+def weight_transpose(srcs, dsts) -> None:
+    """dsts[i][taps-1-j, c, n] = srcs[i][j, n, c] for every pair, ONE launch (the dgrad operands of a backward pass).
+    srcs: bf16 (taps, N, C) contiguous; dsts: bf16 (taps, C, N) contiguous."""
+    import numpy as np
+
+    global _WT_DTYPE
+    if _WT_DTYPE is None:
+        _WT_DTYPE = np.dtype([("src", "<u8"), ("dst", "<u8"), ("taps", "<i4"), ("N", "<i4"), ("C", "<i4"), ("tile0", "<i4")])
+    if not srcs or len(srcs) != len(dsts):
+        raise ValueError("weight_transpose: need as many destinations as sources")
+    tab = np.zeros(len(srcs), dtype=_WT_DTYPE)
+    tiles = 0
+    for i, (a, b) in enumerate(zip(srcs, dsts)):
+        taps, N, Cin = a.shape
+        if tuple(b.shape) != (taps, Cin, N):
+            raise ValueError(f"weight_transpose: destination {tuple(b.shape)} for source {tuple(a.shape)}")
+        tab[i] = (_ptr(a, torch.bfloat16, "src"), _ptr(b, torch.bfloat16, "dst"), taps, N, Cin, tiles)
+        tiles += taps * ((N + 63) // 64) * ((Cin + 63) // 64)
+    tab_dev = torch.from_numpy(tab.view(np.uint8)).to(srcs[0].device)
+    _check(load().ttsb200_weight_transpose(tab_dev.data_ptr(), len(srcs), tiles, _stream()), "weight_transpose")
+    _count()

@@ -38,6 +38,15 @@ def _t(w_taps: torch.Tensor) -> torch.Tensor:
     return wt.contiguous()
 
 
+def _src(d, k):
+    """d[k], or d[k0][k1]... for a tuple path."""
+    if isinstance(k, tuple):
+        for kk in k:
+            d = d[kk]
+        return d
+    return d[k]
+
+
 class DropoutPlan:
     """Dropout call sites of the reference's training forward and their probabilities.
 
@@ -209,6 +218,10 @@ class Trainer:
         self.sumsq = torch.zeros(1, device=dev, dtype=torch.float32)
         self.loss_buf = torch.zeros(8, device=dev, dtype=torch.float32)
         self._zeros = {}
+        # dgrad operands (transposed, tap-flipped weights): the (cache dict, key) pairs a backward pass asks for are
+        # recorded on the first pass; from then on ONE batched kernel builds them all at the start of the backward
+        self._wt_pairs: Dict[tuple, tuple] = {}
+        self._wt_cache: Dict[tuple, tuple] = {}
         self.invalidate_caches()
 
     def _dropout_plan(self, model, seed: int):
@@ -234,6 +247,41 @@ class Trainer:
             z = torch.zeros(n, device=self.dev, dtype=torch.float32)
             self._zeros[n] = z
         return z
+
+    def _wt(self, d, k) -> torch.Tensor:
+        """The dgrad operand of the forward operand d[k] (bf16 (taps, N, C)): (taps, C, N), taps flipped.  `d` must be a
+        persistent cache dict (Models/_engine caches): the pair is remembered for `_prepare_wt`."""
+        src = _src(d, k)
+        key = (id(d), k)
+        ent = self._wt_cache.get(key)
+        if ent is not None and ent[0] is src:
+            return ent[1]
+        if key not in self._wt_pairs and len(self._wt_pairs) < 512:
+            self._wt_pairs[key] = (d, k)
+        return _t(src)
+
+    def _prepare_wt(self) -> None:
+        """All dgrad operands of this backward pass in one launch (ttsb200_weight_transpose) instead of one or two torch
+        copy kernels per weight.  Call after the forward (the forward operands are fresh then)."""
+        if not self._wt_pairs:
+            return
+        keys, srcs, dsts = [], [], []
+        for key, (d, k) in self._wt_pairs.items():
+            try:
+                src = _src(d, k)
+            except (KeyError, IndexError):
+                continue
+            ent = self._wt_cache.get(key)
+            if ent is not None and ent[0] is src:
+                continue
+            taps, N, Cin = src.shape
+            dst = ent[1] if ent is not None and tuple(ent[1].shape) == (taps, Cin, N) else \
+                torch.empty((taps, Cin, N), device=src.device, dtype=torch.bfloat16)
+            keys.append(key); srcs.append(src); dsts.append(dst)
+        if srcs:
+            lib.weight_transpose(srcs, dsts)
+            for key, src, dst in zip(keys, srcs, dsts):
+                self._wt_cache[key] = (src, dst)
 
     def invalidate_caches(self) -> None:
         """The optimizer kernel updates parameters through raw pointers: derived bf16 operands are stale."""
@@ -345,13 +393,13 @@ class Trainer:
             lib.conv_wgrad(dupre_bf, s["h"], G(ff.f_2.weight), taps=k, pad_left=k // 2, conv_layout=True,
                            dbias=G(ff.f_2.bias))
             dh = bf(B, T, 4 * D)
-            lib.conv_gemm(dupre_bf, _t(lc["w2"]), self.zeros(4 * D), taps=k, pad_left=k - 1 - k // 2, block_n=256,
+            lib.conv_gemm(dupre_bf, self._wt(lc, "w2"), self.zeros(4 * D), taps=k, pad_left=k - 1 - k // 2, block_n=256,
                           act=lib.ACT_RELU_GRAD, gate_bf16=s["h"], out_bf16=dh)
             # h = relu(conv1(yn) + b1)
             lib.conv_wgrad(dh, s["yn"], G(ff.f_1.weight), taps=k, pad_left=k // 2, conv_layout=True,
                            dbias=G(ff.f_1.bias))
             dyn = f32(B, T, D)
-            lib.conv_gemm(dh, _t(lc["w1"]), self.zeros(D), taps=k, pad_left=k - 1 - k // 2, block_n=192,
+            lib.conv_gemm(dh, self._wt(lc, "w1"), self.zeros(D), taps=k, pad_left=k - 1 - k // 2, block_n=192,
                           res_f32=dupre, res_bstride=T * D, res_tstride=D, out_f32=dyn)
             # yn = norm_2(y); z = y + ff(yn)
             dy, dy_bf = f32(B, T, D), bf(B, T, D)
@@ -362,13 +410,13 @@ class Trainer:
             # y = x + ctx Wo^T + bo
             lib.conv_wgrad(dy_bf, s["ctx"], G(a.out.weight), dbias=G(a.out.bias))
             dctx = bf(B, T, D)
-            lib.conv_gemm(dy_bf, _t(lc["wo"]), self.zeros(D), block_n=192, out_bf16=dctx)
+            lib.conv_gemm(dy_bf, self._wt(lc, "wo"), self.zeros(D), block_n=192, out_bf16=dctx)
             delta = lib.attn_delta(dctx, s["ctx"], H)
             dqkv = lib.attention_bwd(s["qkv"], dctx, mask, kv, s["lse"], delta, H, drop=(pd, seed, S(f"{i}.attn")))
             for j, lin in enumerate((a.q_linear, a.k_linear, a.v_linear)):
                 lib.conv_wgrad(dqkv, s["xn"], G(lin.weight), n_off=j * D, N=D, dbias=G(lin.bias))
             dxn = f32(B, T, D)
-            lib.conv_gemm(dqkv, _t(lc["wqkv"]), self.zeros(D), block_n=192, out_f32=dxn)
+            lib.conv_gemm(dqkv, self._wt(lc, "wqkv"), self.zeros(D), block_n=192, out_f32=dxn)
             # xn = norm_1(x); y = x + attn(xn)
             dx = f32(B, T, D)
             dz_bf = bf(B, T, D) if i == 0 else None
@@ -388,7 +436,7 @@ class Trainer:
         lib.colsum(dz, G(enc.embed.bias))
         lib.conv_wgrad(dz_bf, tape["src"], G(enc.embed.weight))
         dsrc = f32(B, T, tape["src"].shape[2])
-        lib.conv_gemm(dz_bf, _t(t["wemb"]), self.zeros(tape["src"].shape[2]), block_n=192, out_f32=dsrc)
+        lib.conv_gemm(dz_bf, self._wt(t, "wemb"), self.zeros(tape["src"].shape[2]), block_n=192, out_f32=dsrc)
         return dsrc
 
     # ------------------------------------------------------------------------------------------
@@ -434,7 +482,7 @@ class Trainer:
         lib.conv_wgrad(dc2, tape["h"], G(pred.conv2.weight), taps=3, pad_left=1, conv_layout=True,
                        dbias=G(pred.conv2.bias))
         dh = torch.empty((B, T, fs), device=dev, dtype=torch.float32)
-        lib.conv_gemm(dc2, _t(t["w2"]), self.zeros(fs), taps=3, pad_left=1, block_n=128, out_f32=dh)
+        lib.conv_gemm(dc2, self._wt(t, "w2"), self.zeros(fs), taps=3, pad_left=1, block_n=128, out_f32=dh)
         dc1 = torch.empty((B, T, fs), device=dev, dtype=torch.bfloat16)
         lib.layernorm_bwd(tape["r1"], t["ln1"][0], g_f32=dh, relu_gate=True, dx_bf16=dc1,
                           dgamma=G(pred.layer_norm1.weight), dbeta=G(pred.layer_norm1.bias), site_g=tape["s1"],
@@ -443,7 +491,7 @@ class Trainer:
                        dbias=G(pred.conv1.bias))
         dx = torch.empty((B, T, Din), device=dev, dtype=torch.float32)
         kw = {} if add_f32 is None else dict(res_f32=add_f32, res_bstride=T * Din, res_tstride=Din)
-        lib.conv_gemm(dc1, _t(t["w1"]), self.zeros(Din), taps=3, pad_left=1, block_n=192, out_f32=dx, **kw)
+        lib.conv_gemm(dc1, self._wt(t, "w1"), self.zeros(Din), taps=3, pad_left=1, block_n=192, out_f32=dx, **kw)
         return dx
 
     # ------------------------------------------------------------------------------------------
@@ -502,7 +550,7 @@ class Trainer:
         lib.colsum(g_post, G(pn.conv2.bias))
         lib.conv_wgrad(g_post_bf, tape["h_last"], G(pn.conv2.weight), taps=5, pad_left=4, conv_layout=True)
         dh = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
-        lib.conv_gemm(g_post_bf, _t(t["w2"]), self.zeros(D), taps=5, pad_left=0, block_n=192, out_bf16=dh)
+        lib.conv_gemm(g_post_bf, self._wt(t, "w2"), self.zeros(D), taps=5, pad_left=0, block_n=192, out_bf16=dh)
         g_mel = g_pre + g_post  # both paths reach mel_pre (postnets.py:75)
         dmel = torch.empty((B, T, md), device=dev, dtype=torch.float32)
         dmel_bf = torch.empty((B, T, md), device=dev, dtype=torch.bfloat16)
@@ -519,15 +567,15 @@ class Trainer:
             lib.conv_wgrad(dc, s["x"], G(cv.weight), taps=5, pad_left=4, conv_layout=True, dbias=G(cv.bias))
             if i > 0:
                 dh = torch.empty((B, T, D), device=dev, dtype=torch.bfloat16)
-                lib.conv_gemm(dc, _t(s["w"]), self.zeros(D), taps=5, pad_left=0, block_n=192, out_bf16=dh)
+                lib.conv_gemm(dc, self._wt(t, ("convs", i, 0)), self.zeros(D), taps=5, pad_left=0, block_n=192, out_bf16=dh)
             else:
-                lib.conv_gemm(dc, _t(s["w"]), self.zeros(md), taps=5, pad_left=0, block_n=md, res_f32=g_mel,
+                lib.conv_gemm(dc, self._wt(t, ("convs", i, 0)), self.zeros(md), taps=5, pad_left=0, block_n=md, res_f32=g_mel,
                               res_bstride=T * md, res_tstride=md, out_f32=dmel, out_bf16=dmel_bf)
         # mel_pre = out(d)
         lib.colsum(dmel, G(pn.out.bias))
         lib.conv_wgrad(dmel_bf, tape["d"], G(pn.out.weight))
         dd = torch.empty((B, T, D), device=dev, dtype=torch.float32)
-        lib.conv_gemm(dmel_bf, _t(t["wout"]), self.zeros(D), block_n=192, out_f32=dd)
+        lib.conv_gemm(dmel_bf, self._wt(t, "wout"), self.zeros(D), block_n=192, out_f32=dd)
         return dd
 
     # ------------------------------------------------------------------------------------------
@@ -568,6 +616,7 @@ class Trainer:
 
     def backward_train(self, tape, g_pre, g_post, g_d, g_p, g_e, g_post_bf=None) -> None:
         """Gradients of every parameter from the gradients of the five outputs (accumulated into the flat buffer)."""
+        self._prepare_wt()
         model = self.model
         enc, va, dec, pn = model.encoder, model.variance_adaptor, model.decoder, model.postnet
         G = self.G
