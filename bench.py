@@ -562,12 +562,17 @@ def tts_train_record(cpu: bool, batch: int = 32, phonemes: int = 128, mel_len: i
     md.load_state_dict(sd)
     ms_drop, launches_drop, _ = timed(TTSTrainer(md.cuda().train(), positive_weight=5.0))
     del md
-    ms, launches, out = timed(TTSTrainer(model, positive_weight=5.0))
+    ms_eager, launches, out = timed(TTSTrainer(model, positive_weight=5.0))
+    model = build_transformer_tts(hp)
+    model.load_state_dict(sd)
+    trg = TTSTrainer(model.cuda().train(), positive_weight=5.0, cuda_graph=True)
+    ms, _, out = timed(trg)
+    launches = getattr(trg, "graph_launches", launches) + 3
     frames = float((pos_mel[:, r:] != 0).sum())
     rec = {"metric": "transformer_tts_train_mel_frames_per_sec", "value": frames / ms * 1e3, "unit": "frames/s", "ms_per_step": ms,
            "batch": batch, "phonemes": phonemes, "mel_len": mel_len, "decoder_positions": int(mel_in.shape[1]),
            "valid_target_frames": frames, "gpu_launches_per_step": launches, "loss": float(out["loss"]),
-           "dropout": 0.0, "optimizer": "adam (Noam rate), clip 1.0",
+           "dropout": 0.0, "optimizer": "adam (Noam rate), clip 1.0", "cuda_graph": True, "ms_per_step_eager": ms_eager,
            "with_reference_dropout": {"ms_per_step": ms_drop, "frames_per_s": frames / ms_drop * 1e3, "dropout": 0.1,
                                       "dropout_prenet": 0.5, "gpu_launches_per_step": launches_drop},
            "what": "tts_training.TTSTrainer.train_step: tcgen05 GEMMs / wgrad, causal tcgen05 attention forward + backward, "
@@ -665,9 +670,34 @@ def train_record(args, rank: int, world: int, steps: int = 5):
     total_frames = float(tot[2])
     rec = {"metric": "fastspeech2_train_mel_frames_per_sec", "value": total_frames / (ms * 1e-3), "unit": UNIT,
            "ms_per_step": ms, "allreduce_ms": ar, "steps": steps, "batch_per_gpu": 32, "frames_per_step": total_frames,
-           "optimizer": "radam", "loss": float(out["loss"]),
+           "optimizer": "radam", "loss": float(out["loss"]), "cuda_graph": False,
            "parallelism": f"dp{world}: one NCCL all-reduce of the flat fp32 gradient buffer "
                           f"({tr.flat_g.numel() * 4 / 1e6:.0f} MB) + SyncBatchNorm moments" if world > 1 else "dp1"}
+    if world == 1 and not getattr(args, "no_train_graph", False):
+        # single process: zero_grad + forward + losses + backward replayed from ONE captured CUDA graph, optimizer eager
+        # (Trainer(cuda_graph=True)).  Not the headline of this record: data-parallel steps cannot use it (SyncBatchNorm
+        # collectives inside the step), and `ms_per_step` above stays comparable across the 1/2/4/8 runs.
+        try:
+            del tr, model
+            model = build_fastspeech2(hp)
+            model.load_state_dict(synth.synth_state_dict(hp))
+            tg = Trainer(model.cuda().train(), optimizer="radam", cuda_graph=True)
+            for _ in range(3):
+                tg.train_step(**dev)
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(steps):
+                tg.train_step(**dev)
+            e1.record()
+            torch.cuda.synchronize()
+            gms = e0.elapsed_time(e1) / steps
+            rec["single_process_cuda_graph"] = {"ms_per_step": gms, "value": total_frames / (gms * 1e-3), "unit": UNIT,
+                                                "graph_kernel_nodes": getattr(tg, "graph_launches", None),
+                                                "captured": bool(tg._graphs)}
+            del tg
+        except Exception as ex:  # noqa: BLE001
+            rec["single_process_cuda_graph"] = {"error": str(ex)[:200]}
+        tr = None
     del tr, model, dev, out
     torch.cuda.empty_cache()
     return rec
@@ -961,6 +991,7 @@ def main():
     ap.add_argument("--no-eager-baseline", action="store_true", help="skip the torch_eager_b200 sub-record")
     ap.add_argument("--no-train-record", action="store_true", help="skip the training-step sub-record")
     ap.add_argument("--no-ar-record", action="store_true", help="skip the Transformer-TTS autoregressive decode sub-record")
+    ap.add_argument("--no-train-graph", action="store_true", help="training sub-record with eager steps (no CUDA graph)")
     ap.add_argument("--step-only", action="store_true",
                     help="only the timed steps (no per-kernel rooflines, latency, other modes, baselines): for ncu launch lists")
     ap.add_argument("--duration-precision", default="fp32", choices=["fp32", "bf16"],

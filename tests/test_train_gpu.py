@@ -343,3 +343,43 @@ def test_reference_training_call_signature_runs_unchanged():
     with torch.no_grad():
         ev = model(text[:1], src_mask[:1], hop_size=[None], accent=accent, spkr_emb=spk_emb)  # test_fastspeech2.py:169-171
     assert ev[5].dtype == torch.float32 and torch.isfinite(ev[1]).all()
+
+
+def test_cuda_graphed_train_step_matches_eager():
+    """Trainer(cuda_graph=True): zero_grad + forward + losses + backward replayed from one captured graph per input shape, the
+    optimizer step eager.  Same loss sequence and parameters as the eager trainer (atomic accumulation order is the only
+    difference), a second shape gets its own graph, and dropout switches the graph off (a replay would repeat the masks)."""
+    from transformer_tts_b200 import synth
+    from transformer_tts_b200.training import Trainer
+
+    def batch(seed, B, L):
+        text, pos, _ = synth.synth_text_batch(B, L, ragged=True, seed=seed)
+        dur, pos_mel, f0, en = synth.synth_targets(pos, seed=seed, max_dur=10)
+        mel = synth.synth_mel(pos_mel, 80, seed=seed)
+        c = lambda t: t.cuda()  # noqa: E731
+        return (c(text), c((pos != 0).unsqueeze(-2)), c((pos_mel != 0).unsqueeze(-2)), c(dur), c(f0), c(en), c(mel))
+
+    b1, b2 = batch(5, 4, 32), batch(6, 3, 24)
+    runs = {}
+    for graphed in (False, True):
+        hp, sd, model = build()
+        tr = Trainer(model, cuda_graph=graphed)
+        losses = []
+        for i in range(6):
+            o = tr.train_step(*(b1 if i != 3 else b2))
+            losses.append(float(o["loss"]))
+        assert (len(tr._graphs) == 2) == graphed
+        runs[graphed] = (losses, tr.flat_p.clone(), model.postnet.pre_batchnorm.running_mean.clone())
+    (le, pe, re_), (lg, pg, rg) = runs[False], runs[True]
+    print("eager  ", le)
+    print("graphed", lg)
+    for a, b in zip(le, lg):
+        assert abs(a - b) <= 1e-3 * max(1.0, abs(a))
+    assert rel(pg, pe) < 1e-3 and rel(rg, re_) < 1e-3   # (bf16 roundings of activations amplify the atomic-order noise)
+    hp = synth.make_hp(dropout=0.1)
+    from transformer_tts_b200 import build_fastspeech2
+
+    md = build_fastspeech2(hp)
+    if any(m.p > 0 for m in md.modules() if isinstance(m, torch.nn.Dropout)):
+        tr = Trainer(md.cuda().train(), cuda_graph=True)
+        assert not tr._graph_ok()

@@ -270,3 +270,26 @@ def test_reference_training_call_is_a_drop_in():
         src_mask, trg_mask = T.create_masks(c(b["pos"]), c(b["pos_in"]))
         pre, *_ = model(c(b["text"]), c(b["mel_input"]), src_mask, trg_mask, None, training=False)
     assert torch.isfinite(pre).all()
+
+
+def test_tts_cuda_graphed_train_step_matches_eager():
+    from oracle import transformer_tts_oracle as T
+    from transformer_tts_b200.tts_training import TTSTrainer
+
+    runs = {}
+    for graphed in (False, True):
+        hp, sd, model = build()
+        b = make_batch(hp, 4, 32, 160, 23)
+        src_mask, _ = T.create_masks(b["pos"], b["pos_in"])
+        args = gpu_args(b, src_mask, hp.reduction_rate)
+        tr = TTSTrainer(model, positive_weight=POS_WEIGHT, cuda_graph=graphed)
+        losses = [float(tr.train_step(*args)["loss"]) for _ in range(6)]
+        assert (len(tr._graphs) == 1) == graphed
+        runs[graphed] = (losses, tr.flat_p.clone())
+    print("eager  ", runs[False][0])
+    print("graphed", runs[True][0])
+    for a, b in zip(runs[False][0], runs[True][0]):
+        assert abs(a - b) <= 1e-3 * max(1.0, abs(a))
+    assert float((runs[True][1] - runs[False][1]).norm() / runs[False][1].norm()) < 1e-3
+    hp, sd, model = build(0.1, 0.5)
+    assert not TTSTrainer(model, cuda_graph=True)._graph_ok()      # dropout: a replay would repeat the masks

@@ -870,6 +870,7 @@ def relu_gate(g: torch.Tensor, gate: torch.Tensor) -> torch.Tensor:
 
 
 _WT_DTYPE = None
+_WT_KEEP: list = []
 
 
 def weight_transpose(srcs, dsts) -> None:
@@ -890,6 +891,14 @@ def weight_transpose(srcs, dsts) -> None:
             raise ValueError(f"weight_transpose: destination {tuple(b.shape)} for source {tuple(a.shape)}")
         tab[i] = (_ptr(a, torch.bfloat16, "src"), _ptr(b, torch.bfloat16, "dst"), taps, N, Cin, tiles)
         tiles += taps * ((N + 63) // 64) * ((Cin + 63) // 64)
-    tab_dev = torch.from_numpy(tab.view(np.uint8)).to(srcs[0].device)
+    host = torch.from_numpy(tab.view(np.uint8))
+    if torch.cuda.is_current_stream_capturing():
+        # a captured copy reads its source again at every replay: page-locked and kept alive with the process
+        host = host.pin_memory()
+        _WT_KEEP.append(host)
+        tab_dev = host.to(srcs[0].device, non_blocking=True)
+        _WT_KEEP.append(tab_dev)
+    else:
+        tab_dev = host.to(srcs[0].device)
     _check(load().ttsb200_weight_transpose(tab_dev.data_ptr(), len(srcs), tiles, _stream()), "weight_transpose")
     _count()

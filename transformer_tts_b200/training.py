@@ -153,12 +153,21 @@ class Trainer:
     def __init__(self, model, *, lr_max: float = 1e-3, betas=(0.9, 0.98), eps: float = 1e-9, clip: float = 1.0,
                  warmup_step: int = 4000, warmup_factor: float = 1.0, fixed_lr: Optional[float] = None,
                  process_group=None, sync_bn: bool = True, bn_momentum: float = 0.1, flatten: bool = True,
-                 optimizer: str = "adam", overlap_allreduce: bool = False, dropout_seed: int = 0):
+                 optimizer: str = "adam", overlap_allreduce: bool = False, dropout_seed: int = 0,
+                 cuda_graph: bool = False):
         """flatten=True (training loop owner): parameters are re-pointed into one flat fp32 buffer, `p.grad` are
         views of the flat gradient buffer and optimizer_step() runs the fused clip+Adam kernel.
         flatten=False (drop-in autograd mode, see `autograd_forward`): parameters are left alone, only the flat
-        gradient buffer exists and the caller's torch optimizer owns the update."""
+        gradient buffer exists and the caller's torch optimizer owns the update.
+        cuda_graph=True: train_step() captures zero_grad + forward + losses + backward (weight-operand refresh included) as ONE
+        CUDA graph per input shape and replays it; the optimizer step (learning rate and bias corrections change per step)
+        stays three eager launches.  Used only where a replay is the same computation as an eager step: dropout inactive (the
+        mask seed is a kernel argument, a replay would repeat the masks) and a single process — capturing the SyncBatchNorm
+        moment all-reduces that sit inside the forward and backward was tried on 2 GPUs and hung (NCCL 2.28 under
+        torch.cuda.graph), so data-parallel steps stay eager.  If a capture fails the trainer falls back to eager steps."""
         lib.load()
+        self.cuda_graph = bool(cuda_graph)
+        self._graphs: Dict[tuple, tuple] = {}
         self.drop = self._dropout_plan(model, dropout_seed)
         # hp.optimizer (train_fastspeech2.py:412-416): 'radam' -> radam.RAdam at the fixed rate lr_max (the Noam
         # schedule is skipped for it, :117-120); anything else -> torch.optim.Adam at the Noam rate
@@ -691,7 +700,60 @@ class Trainer:
     def grad_norm(self) -> torch.Tensor:
         return torch.sqrt(self.sumsq) / self.world
 
+    # ------------------------------------------------------------------------------------------
+    # CUDA-graphed forward + backward (see __init__)
+    # ------------------------------------------------------------------------------------------
+    def _graph_ok(self) -> bool:
+        return self.cuda_graph and self.flatten and self.world == 1 and not self.drop.active
+
+    def _graphed_forward_backward(self, args: tuple) -> Dict[str, torch.Tensor]:
+        """zero_grad() + forward_backward(*args) through a captured graph.  The returned tensors are the graph's own
+        buffers: the next replay overwrites them."""
+        key = tuple((tuple(a.shape), a.dtype) if torch.is_tensor(a) else a for a in args)
+        ent = self._graphs.get(key)
+        if ent is None:
+            static = [a.clone() if torch.is_tensor(a) else a for a in args]
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):          # one eager pass first: lazy initialisation, allocator warm-up
+                saved = [b.clone() for b in self.model.buffers()]     # (its BatchNorm running-stat updates are undone)
+                self.invalidate_caches()
+                self.zero_grad()
+                self.forward_backward(*static)
+                with torch.no_grad():
+                    for b, sv in zip(self.model.buffers(), saved):
+                        b.copy_(sv)
+            torch.cuda.current_stream().wait_stream(side)
+            self.invalidate_caches()               # so that the capture contains the refresh of the weight operands
+            graph = torch.cuda.CUDAGraph()
+            l0 = lib.LAUNCH_COUNT
+            try:
+                with torch.cuda.graph(graph):
+                    self.zero_grad()
+                    out = self.forward_backward(*static)
+            except Exception as ex:  # noqa: BLE001 — e.g. a collective that cannot be captured on this stack
+                import warnings
+
+                warnings.warn(f"Trainer: CUDA graph capture failed ({str(ex)[:200]}); continuing with eager steps")
+                self.cuda_graph = False
+                torch.cuda.synchronize()
+                self.invalidate_caches()
+                self.zero_grad()
+                return self.forward_backward(*args)
+            ent = self._graphs[key] = (graph, static, out, lib.LAUNCH_COUNT - l0)
+        else:
+            for st, a in zip(ent[1], args):
+                if torch.is_tensor(a):
+                    st.copy_(a)
+        ent[0].replay()
+        self.graph_launches = ent[3]
+        return dict(ent[2])
+
     def train_step(self, text, src_mask, mel_mask, alignment, f0, energy, mel) -> Dict[str, torch.Tensor]:
+        if self._graph_ok():
+            out = self._graphed_forward_backward((text, src_mask, mel_mask, alignment, f0, energy, mel))
+            out["lr"] = self.optimizer_step()
+            return out
         self.zero_grad()
         self._overlap = self.overlap_allreduce
         try:
