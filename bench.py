@@ -540,6 +540,7 @@ def tts_train_record(cpu: bool, batch: int = 32, phonemes: int = 128, mel_len: i
     steps = 5
 
     def timed(tr):
+        tr.world = 1          # rank 0 runs this record alone, also under torchrun: no gradient exchange with absent peers
         for _ in range(3):
             out = tr.train_step(*a)
         torch.cuda.synchronize()
