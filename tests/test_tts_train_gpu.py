@@ -82,7 +82,8 @@ def gpu_args(b, src_mask, r):
             c(b["stop"][:, r:].contiguous()))
 
 
-@pytest.mark.parametrize("B,L,frames,seed", [(3, 24, 96, 11), (4, 40, 300, 12)])
+# (1, 3, 4): ONE decoder position and three phonemes; (2, 130, 520): 259 positions / 130 phonemes, both past a 128-row tile
+@pytest.mark.parametrize("B,L,frames,seed", [(3, 24, 96, 11), (4, 40, 300, 12), (1, 3, 4, 13), (2, 130, 520, 14)])
 def test_tts_train_step_vs_oracle_autograd(B, L, frames, seed):
     from transformer_tts_b200.tts_training import TTSTrainer
 
@@ -108,8 +109,11 @@ def test_tts_train_step_vs_oracle_autograd(B, L, frames, seed):
         den += float((w ** 2).sum())
     errs.sort(reverse=True)
     print("worst per-tensor gradient rel-L2:", errs[:8], "global", (num / den) ** 0.5)
-    assert errs[0][0] < 1.2e-1, errs[:8]
-    assert (num / den) ** 0.5 < 3e-2
+    # a single decoder position has no averaging over rows: every gradient is ONE outer product of bf16-rounded vectors
+    # carried through 12 blocks (pe.alpha, a cancelling scalar sum, is the worst); the bars of the batch cases do not apply
+    bar_worst, bar_global = (2.5e-1, 8e-2) if B * ((frames - hp.reduction_rate) // hp.reduction_rate) < 16 else (1.2e-1, 3e-2)
+    assert errs[0][0] < bar_worst, errs[:8]
+    assert (num / den) ** 0.5 < bar_global
 
 
 def test_tts_optimizer_steps_reduce_loss():
