@@ -105,3 +105,45 @@ def test_state_dict_layout_and_forward_match_live_reference(world):
         out = T.transformer_forward(sd, vars(hp), text, trg, sm, tm)
     _close(out["outputs_prenet"], pre, 2e-5)
     _close(out["stop_token"], stop, 2e-5)
+
+
+def test_oracle_autograd_matches_reference_training_golden():
+    """tests/golden/tts_train_step.npz (the unmodified reference's loss.backward() on the statements of train.py:186-252,
+    made by oracle/make_golden_tts_train.py): torch autograd through the oracle reproduces the losses and the gradients —
+    this is what makes the oracle the yardstick of the GPU training-step tests (tests/test_tts_train_gpu.py)."""
+    import torch.nn.functional as F
+
+    from oracle import transformer_tts_oracle as T
+    from oracle.make_golden_tts_train import FULL, POS_WEIGHT, SUB, tts_train_batch
+    from transformer_tts_b200 import synth
+
+    g = np.load(GOLDEN / "tts_train_step.npz")
+    hp = synth.make_tts_hp()
+    r = hp.reduction_rate
+    sd = synth.synth_tts_state_dict(hp)
+    assert str(g["digest"]) == synth.state_dict_digest(sd)
+    b = tts_train_batch(hp)
+    leaf = {k: (v.clone().requires_grad_(True) if v.is_floating_point() and not k.startswith("postnet.") else v) for k, v in sd.items()}
+    src_mask, trg_mask = T.create_masks(b["pos"], b["pos_in"])
+    torch.set_num_threads(8)
+    o = T.transformer_forward(leaf, vars(hp), b["text"], b["mel_input"], src_mask, trg_mask)
+    bb, t, c = o["outputs_prenet"].shape
+    pre = o["outputs_prenet"].reshape(bb, t * r, c // r)
+    mel_loss = F.l1_loss(pre, b["mel"][:, r:, :])
+    tok = F.binary_cross_entropy_with_logits(o["stop_token"].reshape(bb, t * r), b["stop"][:, r:], reduction="mean",
+                                             pos_weight=torch.tensor(POS_WEIGHT))
+    loss = 2 * mel_loss + tok
+    loss.backward()
+    np.testing.assert_allclose([mel_loss.item(), mel_loss.item(), tok.item(), loss.item()], g["losses"], rtol=1e-5)
+    np.testing.assert_allclose(pre.detach().numpy(), g["outputs_prenet"], rtol=0, atol=2e-4)
+    norms = dict(zip([str(n) for n in g["names"]], g["grad_norms"]))
+    gl = float(g["global_grad_norm"])
+    for n, v in leaf.items():
+        if isinstance(v, torch.Tensor) and v.requires_grad and n in norms:
+            assert abs(float(v.grad.double().norm()) - norms[n]) <= 1e-4 * max(norms[n], 1e-3 * gl), n
+    for n in FULL:
+        np.testing.assert_allclose(leaf[n].grad.numpy(), g["full:" + n], rtol=0, atol=1e-4 * gl)
+    for n in SUB:
+        gr = leaf[n].grad
+        np.testing.assert_allclose(gr.reshape(gr.shape[0], -1)[::7, ::13].numpy(), g["sub:" + n], rtol=0, atol=1e-5 * gl)
+    assert all(float(g["grad_norms"][i]) == 0.0 for i, n in enumerate(g["names"]) if str(n).startswith("postnet."))

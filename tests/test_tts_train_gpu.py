@@ -17,22 +17,10 @@ POS_WEIGHT = 5.0  # utils/default.yaml:76
 
 
 def make_batch(hp, B, L, frames, seed):
-    """What train.py:168-195 hands the model: mel (B, frames, mel_dim) with `frames` a multiple of r, ragged lengths."""
-    from transformer_tts_b200 import synth
+    """What train.py:168-195 hands the model (the builder the golden script uses)."""
+    from oracle.make_golden_tts_train import tts_train_batch
 
-    r = hp.reduction_rate
-    g = torch.Generator().manual_seed(seed)
-    text, pos, _ = synth.synth_text_batch(B, L, ragged=True, seed=seed)
-    lens = torch.randint(frames // 2 // r, frames // r + 1, (B,), generator=g) * r
-    lens[0] = frames
-    pos_mel = torch.arange(1, frames + 1).unsqueeze(0).repeat(B, 1)
-    pos_mel[pos_mel > lens.unsqueeze(1)] = 0
-    mel = torch.randn(B, frames, hp.mel_dim, generator=g) * (pos_mel != 0).unsqueeze(-1)
-    stop = (pos_mel == 0).float()                       # 1 on the padding frames ...
-    stop[torch.arange(B), lens - 1] = 1.0               # ... and on the last frame (utils: the stop token target)
-    mel_input = mel[:, :-r:r, :].contiguous()           # train.py:186
-    pos_in = pos_mel[:, :-r:r].contiguous()             # train.py:187
-    return dict(text=text, pos=pos, mel=mel, stop=stop, mel_input=mel_input, pos_in=pos_in)
+    return tts_train_batch(hp, B, L, frames, seed)
 
 
 def oracle_grads(sd, hp, b, drop=None, dev="cpu"):
@@ -297,3 +285,60 @@ def test_tts_cuda_graphed_train_step_matches_eager():
     assert float((runs[True][1] - runs[False][1]).norm() / runs[False][1].norm()) < 1e-3
     hp, sd, model = build(0.1, 0.5)
     assert not TTSTrainer(model, cuda_graph=True)._graph_ok()      # dropout: a replay would repeat the masks
+
+
+def test_tts_train_step_vs_reference_golden():
+    """tests/golden/tts_train_step.npz: losses and gradients of the UNMODIFIED reference module's loss.backward() on the step
+    statements of train.py:186-252 (oracle/make_golden_tts_train.py).  Bars as for the FastSpeech2 golden (test_train_gpu.py)."""
+    from pathlib import Path
+
+    import numpy as np
+
+    from oracle import transformer_tts_oracle as T
+    from oracle.make_golden_tts_train import FULL, SUB, tts_train_batch
+    from transformer_tts_b200 import synth
+    from transformer_tts_b200.tts_training import TTSTrainer
+
+    g = np.load(Path(__file__).resolve().parent / "golden" / "tts_train_step.npz")
+    hp, sd, model = build()
+    assert str(g["digest"]) == synth.state_dict_digest(sd)
+    b = tts_train_batch(hp)
+    src_mask, _ = T.create_masks(b["pos"], b["pos_in"])
+    tr = TTSTrainer(model, positive_weight=POS_WEIGHT)
+    tr.zero_grad()
+    out = tr.forward_backward(*gpu_args(b, src_mask, hp.reduction_rate))
+    torch.cuda.synchronize()
+    ref = g["losses"]
+    for i, k in enumerate(["mel_loss", "post_mel_loss", "loss_token", "loss"]):
+        assert abs(float(out[k]) - ref[i]) <= 2e-3 * max(1.0, abs(ref[i])), (k, float(out[k]), ref[i])
+    bb, t, c = out["outputs_prenet"].shape
+    r = hp.reduction_rate
+    e_out = float((out["outputs_prenet"].reshape(bb, t * r, c // r).double().cpu() - torch.from_numpy(g["outputs_prenet"]).double()).norm()
+                  / torch.from_numpy(g["outputs_prenet"]).double().norm())
+    assert e_out < 1e-2, e_out
+    norms = dict(zip([str(n) for n in g["names"]], g["grad_norms"]))
+    floor = 1e-3 * float(g["global_grad_norm"])
+    worst = []
+    for n, p in model.named_parameters():
+        gn = float(tr.G(p).double().norm())
+        worst.append((abs(gn - norms[n]) / max(norms[n], floor), n, gn, norms[n]))
+    worst.sort(reverse=True)
+    print("output rel-L2", e_out, "worst gradient-norm deviations:", worst[:4])
+    assert worst[0][0] < 5e-2, worst[:5]
+    pd = dict(model.named_parameters())
+    bad = []
+    for n in FULL:
+        ref_t = torch.from_numpy(g["full:" + n]).double()
+        e = float((tr.G(pd[n]).double().cpu() - ref_t).norm() / max(float(ref_t.norm()), floor))
+        if e >= 8e-2:
+            bad.append((n, e))
+    for n in SUB:
+        gr = tr.G(pd[n])
+        ref_t = torch.from_numpy(g["sub:" + n]).double()
+        e = float((gr.reshape(gr.shape[0], -1)[::7, ::13].double().cpu() - ref_t).norm() / (float(ref_t.norm()) + 1e-30))
+        if e >= 8e-2:
+            bad.append((n, e))
+    assert not bad, bad
+    gg = float(torch.sqrt((tr.flat_g.double() ** 2).sum()))
+    assert abs(gg - float(g["global_grad_norm"])) / float(g["global_grad_norm"]) < 3e-2
+
