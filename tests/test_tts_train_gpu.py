@@ -342,3 +342,36 @@ def test_tts_train_step_vs_reference_golden():
     gg = float(torch.sqrt((tr.flat_g.double() ** 2).sum()))
     assert abs(gg - float(g["global_grad_norm"])) / float(g["global_grad_norm"]) < 3e-2
 
+
+def test_tts_trainer_state_dict_roundtrip():
+    """train.py saves model and optimizer state dicts and resumes `step` from the optimizer's: a TTSTrainer restored from
+    model.state_dict() + TTSTrainer.state_dict() takes the same next step as the one that kept running (torch.optim.Adam
+    layout, inherited from training.Trainer)."""
+    from oracle import transformer_tts_oracle as T
+    from transformer_tts_b200.tts_training import TTSTrainer
+
+    hp, sd, model = build()
+    b = make_batch(hp, 3, 24, 96, 51)
+    src_mask, _ = T.create_masks(b["pos"], b["pos_in"])
+    args = gpu_args(b, src_mask, hp.reduction_rate)
+    tr = TTSTrainer(model, positive_weight=POS_WEIGHT)
+    for _ in range(2):
+        tr.train_step(*args)
+    msd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    osd = tr.state_dict()
+    assert len(osd["state"]) == len(tr.params) and int(osd["state"][0]["step"]) == 2
+    tr.train_step(*args)
+    want = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    _, _, model2 = build()
+    model2.load_state_dict(msd)
+    tr2 = TTSTrainer(model2, positive_weight=POS_WEIGHT)
+    tr2.load_state_dict(osd)
+    assert tr2.step_count == 2
+    tr2.train_step(*args)
+    torch.cuda.synchronize()
+    for k, v in model2.state_dict().items():
+        if v.is_floating_point() and "running_" not in k:
+            assert torch.allclose(v, want[k], rtol=0, atol=2e-6), k
+    opt = torch.optim.Adam(build()[2].parameters(), lr=1e-3, betas=(0.9, 0.98), eps=1e-9)
+    opt.load_state_dict({"state": osd["state"], "param_groups": [dict(opt.state_dict()["param_groups"][0])]})
+    assert int(opt.state_dict()["state"][0]["step"]) == 2

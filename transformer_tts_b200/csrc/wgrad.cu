@@ -226,9 +226,19 @@ extern "C" int ttsb200_conv_wgrad_bias(const void* dy, int64_t ld_dy, const void
   d.chunks_per_utt = (T + kWgK - 1) / kWgK;
   d.total_chunks = B * d.chunks_per_utt;
   const int tiles = d.n_tiles * d.c_tiles * taps;
-  int splits = (148 + tiles / 2) / tiles;  // about one wave of CTAs: every split costs a full tile of reductions
-  if (splits > d.total_chunks) splits = d.total_chunks;
-  if (splits < 1) splits = 1;
+  // split-K over the time chunks: one CTA per SM is resident, so the launch runs in ceil(tiles * splits / 148) waves of
+  // (chunks / splits) main-loop steps plus a fixed prologue + 128 x 128 reduction epilogue worth ~8 steps.  Take the cheapest
+  // split count (e.g. 180 tiles of the encoder's k = 5 convs: 1 split = 2 waves x 72, 3 splits = 4 waves x 29).
+  int splits = 1;
+  {
+    double best = 1e30;
+    const int max_s = d.total_chunks < 32 ? d.total_chunks : 32;
+    for (int sp = 1; sp <= max_s; ++sp) {
+      const int waves = (tiles * sp + 147) / 148;
+      const double cost = waves * (static_cast<double>((d.total_chunks + sp - 1) / sp) + 8.0);
+      if (cost < best - 1e-9) { best = cost; splits = sp; }
+    }
+  }
   d.chunks_per_split = (d.total_chunks + splits - 1) / splits;
   splits = (d.total_chunks + d.chunks_per_split - 1) / d.chunks_per_split;
   d.dw = dw; d.db = db; d.sj = stride_tap; d.sn = stride_n; d.sc = stride_c;
