@@ -82,17 +82,64 @@ def _sig(params: Sequence[torch.Tensor]):
     return tuple((p.data_ptr(), p._version) for p in params)
 
 
+def _mirror(w: torch.Tensor) -> Optional[torch.Tensor]:
+    """The bf16 mirror of a parameter that lives in a training.Trainer's flat buffer (ONE cast kernel refreshes the mirror of
+    the whole model after an optimizer step), if it is still current (`_version` guards writes that bypass the trainer)."""
+    m = getattr(w, "_ttsb_bf16", None)
+    if m is not None and m[1] == w._version and m[0].shape == w.shape:
+        return m[0]
+    return None
+
+
 def _bf16(w: torch.Tensor) -> torch.Tensor:
-    return w.detach().to(torch.bfloat16).contiguous()
+    m = _mirror(w)
+    return m if m is not None else w.detach().to(torch.bfloat16).contiguous()
 
 
 def _f32(w: torch.Tensor) -> torch.Tensor:
     return w.detach().to(torch.float32).contiguous()
 
 
+def _adjacent(ts) -> bool:
+    return all(a.is_contiguous() and a.data_ptr() + a.numel() * a.element_size() == b.data_ptr() for a, b in zip(ts, ts[1:])) \
+        and ts[-1].is_contiguous()
+
+
+def _cat_rows(ts) -> torch.Tensor:
+    """torch.cat(ts, 0) — or, when the tensors already sit next to each other in memory (a trainer's flat layout places
+    q | k | v so), a view of that memory: no kernel."""
+    if len(ts) > 1 and _adjacent(ts) and all(t.shape[1:] == ts[0].shape[1:] and t.dtype == ts[0].dtype for t in ts):
+        rows = sum(t.shape[0] for t in ts)
+        shape = (rows,) + tuple(ts[0].shape[1:])
+        stride, n = [], 1
+        for d in reversed(shape):
+            stride.insert(0, n)
+            n *= d
+        return torch.as_strided(ts[0], shape, tuple(stride))
+    return torch.cat(list(ts), 0)
+
+
+def _bf16_cat(ws) -> torch.Tensor:
+    """bf16 of the row-wise concatenation of parameters (q | k | v operands)."""
+    ms = [_mirror(w) for w in ws]
+    if all(m is not None for m in ms):
+        return _cat_rows(ms)
+    return torch.cat([w.detach() for w in ws], 0).to(torch.bfloat16).contiguous()
+
+
+def _f32_cat(ws) -> torch.Tensor:
+    ds = [w.detach() for w in ws]
+    if all(d.dtype == torch.float32 for d in ds):
+        return _cat_rows(ds)
+    return torch.cat(ds, 0).to(torch.float32).contiguous()
+
+
 def conv_w_to_taps(w: torch.Tensor) -> torch.Tensor:
     """Conv1d weight (out, in, k) -> bf16 (k, out, in): one K-major GEMM operand per tap."""
-    return _bf16(w.detach().permute(2, 0, 1))
+    m = _mirror(w)
+    if m is not None:
+        return m.permute(2, 0, 1).contiguous()      # k = 1: the same memory, no kernel
+    return w.detach().permute(2, 0, 1).to(torch.bfloat16).contiguous()
 
 
 class Cache:
@@ -123,8 +170,8 @@ def layer_cache(layer) -> dict:
         if a.concat_after:
             raise NotImplementedError("concat_after=True is not supported (hparams default is False)")
         t = c.t
-        t["wqkv"] = _bf16(torch.cat([a.q_linear.weight, a.k_linear.weight, a.v_linear.weight], 0)).unsqueeze(0).contiguous()
-        t["bqkv"] = _f32(torch.cat([a.q_linear.bias, a.k_linear.bias, a.v_linear.bias], 0))
+        t["wqkv"] = _bf16_cat([a.q_linear.weight, a.k_linear.weight, a.v_linear.weight]).unsqueeze(0).contiguous()
+        t["bqkv"] = _f32_cat([a.q_linear.bias, a.k_linear.bias, a.v_linear.bias])
         t["wo"] = _bf16(a.out.weight).unsqueeze(0).contiguous()
         t["bo"] = _f32(a.out.bias)
         t["w1"] = conv_w_to_taps(ff.f_1.weight)

@@ -190,8 +190,16 @@ class Decoder(nn.Module):
             dev = self.norm.weight.device
             D = self.norm.weight.numel()
             pn = self.decoder_prenet.layer
-            t["fc1_w"], t["fc1_b"] = lib.pad_weight_rows(pn.fc1.weight.detach()), E._f32(pn.fc1.bias)
-            t["fc2_w"], t["fc2_b"] = lib.pad_weight_rows(pn.fc2.weight.detach()), E._f32(pn.fc2.bias)
+
+            def opnd(*ws):
+                """bf16 [N][K] operand of the rows of `ws` (K a multiple of 32: the layout small_linear streams is the plain
+                one — a view of a trainer's bf16 mirror when there is one); otherwise the zero-padded copy."""
+                if ws[0].shape[1] % 32 == 0:
+                    return E._bf16_cat(list(ws)) if len(ws) > 1 else E._bf16(ws[0])
+                return lib.pad_weight_rows(torch.cat([w.detach() for w in ws], 0))
+
+            t["fc1_w"], t["fc1_b"] = opnd(pn.fc1.weight), E._f32(pn.fc1.bias)
+            t["fc2_w"], t["fc2_b"] = opnd(pn.fc2.weight), E._f32(pn.fc2.bias)
             t["alpha"] = E._f32(self.pe.alpha)
             t["pe"] = self.pe.table(dev)
             t["norm"] = (E._f32(self.norm.weight), E._f32(self.norm.bias))
@@ -199,22 +207,22 @@ class Decoder(nn.Module):
             t["layers"] = []
             for l in self.layers:
                 a1, a2, ff = l.attn_1, l.attn_2, l.ff
-                cat = lambda *ws: torch.cat([w.detach() for w in ws], 0)  # noqa: E731
+                catb = lambda *ws: E._f32_cat(list(ws))  # noqa: E731
                 lc = dict(
                     ln1=(E._f32(l.norm_1.weight), E._f32(l.norm_1.bias)),
                     ln2=(E._f32(l.norm_2.weight), E._f32(l.norm_2.bias)),
                     ln3=(E._f32(l.norm_3.weight), E._f32(l.norm_3.bias)),
                     ln_ff=(E._f32(ff.layer_norm.weight), E._f32(ff.layer_norm.bias)),
-                    wqkv1=lib.pad_weight_rows(cat(a1.q_linear.weight, a1.k_linear.weight, a1.v_linear.weight)),
-                    bqkv1=E._f32(cat(a1.q_linear.bias, a1.k_linear.bias, a1.v_linear.bias)),
-                    wo1=lib.pad_weight_rows(a1.out.weight.detach()), bo1=E._f32(a1.out.bias),
-                    wq2=lib.pad_weight_rows(a2.q_linear.weight.detach()), bq2=E._f32(a2.q_linear.bias),
+                    wqkv1=opnd(a1.q_linear.weight, a1.k_linear.weight, a1.v_linear.weight),
+                    bqkv1=catb(a1.q_linear.bias, a1.k_linear.bias, a1.v_linear.bias),
+                    wo1=opnd(a1.out.weight), bo1=E._f32(a1.out.bias),
+                    wq2=opnd(a2.q_linear.weight), bq2=E._f32(a2.q_linear.bias),
                     # k|v projection of the encoder output: a (1, 2D, D) conv_gemm operand, run once per utterance batch
-                    wkv2=E._bf16(cat(a2.k_linear.weight, a2.v_linear.weight)).unsqueeze(0).contiguous(),
-                    bkv2=E._f32(cat(a2.k_linear.bias, a2.v_linear.bias)),
-                    wo2=lib.pad_weight_rows(a2.out.weight.detach()), bo2=E._f32(a2.out.bias),
-                    w1=lib.pad_weight_rows(ff.f_1.weight.detach()[:, :, 0]), b1=E._f32(ff.f_1.bias),
-                    w2=lib.pad_weight_rows(ff.f_2.weight.detach()[:, :, 0]), b2=E._f32(ff.f_2.bias),
+                    wkv2=E._bf16_cat([a2.k_linear.weight, a2.v_linear.weight]).unsqueeze(0).contiguous(),
+                    bkv2=catb(a2.k_linear.bias, a2.v_linear.bias),
+                    wo2=opnd(a2.out.weight), bo2=E._f32(a2.out.bias),
+                    w1=E.conv_w_to_taps(ff.f_1.weight)[0], b1=E._f32(ff.f_1.bias),
+                    w2=E.conv_w_to_taps(ff.f_2.weight)[0], b2=E._f32(ff.f_2.bias),
                 )
                     # the same weights as (taps=1, N, C) conv_gemm operands, for the batched teacher-forced prefix (run_prefix)
                 for name in ("wqkv1", "wo1", "wq2", "wo2", "w1", "w2"):

@@ -451,9 +451,11 @@ def bucket_embed_add(x, p, e, pbins, ebins, ptab, etab, want_idx: bool = False, 
     return out, p_idx, e_idx
 
 
-def cast_bf16(x: torch.Tensor) -> torch.Tensor:
-    y = torch.empty(x.shape, device=x.device, dtype=torch.bfloat16)
-    _check(load().ttsb200_cast_bf16(_ptr(x, torch.float32, "x"), _ptr(y), x.numel(), _stream()), "cast_bf16")
+def cast_bf16(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    y = torch.empty(x.shape, device=x.device, dtype=torch.bfloat16) if out is None else out
+    if y.numel() != x.numel():
+        raise ValueError("cast_bf16: out must have as many elements as x")
+    _check(load().ttsb200_cast_bf16(_ptr(x, torch.float32, "x"), _ptr(y, torch.bfloat16, "out"), x.numel(), _stream()), "cast_bf16")
     _count()
     return y
 

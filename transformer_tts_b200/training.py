@@ -189,11 +189,14 @@ class Trainer:
             raise RuntimeError("Trainer: move the model to a CUDA device first (there is no CPU path)")
         dev = params[0][1].device
         self.dev = dev
-        # every tensor starts on a 16-byte boundary inside the flat buffers (vector loads, TMA bases)
+        # every tensor starts on an 8-element boundary inside the flat buffers: 16 bytes in the bf16 mirror (TMA bases), 32 in
+        # the fp32 buffers (vector loads).  The q | k | v weights (and biases) of an attention module sit next to each other,
+        # so their concatenated GEMM operand is a VIEW of the mirror, not a torch.cat per step.
         offs, total = {}, 0
-        for n, p in params:
+        sizes = dict((n, p.numel()) for n, p in params)
+        for n in self._flat_order([n for n, _ in params]):
             offs[n] = total
-            total += (p.numel() + 3) // 4 * 4
+            total += (sizes[n] + 7) // 8 * 8
         self.params = [p for _, p in params]
         self.offsets = [(offs[n], p.numel()) for n, p in params]
         self.total = total
@@ -214,8 +217,13 @@ class Trainer:
         self._overlap = False      # armed by train_step() only: an accumulating caller must not reduce early
         self._pending = None
         self._bind_grads()
+        self.flat_p16 = None
+        self._mirrors = []
         if flatten:
             self.flat_p = torch.zeros(total, device=dev, dtype=torch.float32)
+            # bf16 mirror of the parameters: refreshed by ONE cast kernel whenever the flat buffer changes (optimizer step,
+            # broadcast); Models/_engine builds the GEMM operands as views of it instead of per-tensor casts / cats
+            self.flat_p16 = torch.zeros(total, device=dev, dtype=torch.bfloat16)
             self.flat_m = torch.zeros(total, device=dev, dtype=torch.float32)
             self.flat_v = torch.zeros(total, device=dev, dtype=torch.float32)
             with torch.no_grad():
@@ -224,6 +232,7 @@ class Trainer:
                     self.flat_p[o:o + k].copy_(p.detach().reshape(-1).float())
                     p.data = self.flat_p[o:o + k].view(p.shape)  # parameters become views of the flat buffer
                     p.grad = self.grads[id(p)]
+                    self._mirrors.append((p, self.flat_p16[o:o + k].view(p.shape)))
         self.sumsq = torch.zeros(1, device=dev, dtype=torch.float32)
         self.loss_buf = torch.zeros(8, device=dev, dtype=torch.float32)
         self._zeros = {}
@@ -232,6 +241,35 @@ class Trainer:
         self._wt_pairs: Dict[tuple, tuple] = {}
         self._wt_cache: Dict[tuple, tuple] = {}
         self.invalidate_caches()
+
+    @staticmethod
+    def _flat_order(names):
+        """named_parameters() order, except that the six tensors {q,k,v}_linear.{weight,bias} of one attention module are
+        emitted together as q.w k.w v.w q.b k.b v.b at the position of the first of them."""
+        have, done, out = set(names), set(), []
+        for n in names:
+            if n in done:
+                continue
+            for tail in ("q_linear.weight", "k_linear.weight", "v_linear.weight", "q_linear.bias", "k_linear.bias",
+                         "v_linear.bias"):
+                if n.endswith("." + tail) or n == tail:
+                    pre = n[: len(n) - len(tail)]
+                    grp = [pre + f"{x}_linear.{y}" for y in ("weight", "bias") for x in ("q", "k", "v")]
+                    if all(g in have and g not in done for g in grp):
+                        out += grp
+                        done.update(grp)
+                    break
+            if n not in done:
+                out.append(n)
+                done.add(n)
+        return out
+
+    def _refresh_mirror(self) -> None:
+        if self.flat_p16 is None:
+            return
+        lib.cast_bf16(self.flat_p, out=self.flat_p16)
+        for p, m in self._mirrors:
+            p._ttsb_bf16 = (m, p._version)
 
     def _dropout_plan(self, model, seed: int):
         """The dropout call sites of the model (FastSpeech2 here; tts_training.TTSTrainer overrides it)."""
@@ -298,6 +336,7 @@ class Trainer:
             c = getattr(m, "_ttsb_cache", None)
             if c is not None:
                 c.sig = None
+        self._refresh_mirror()
 
     def lr(self) -> float:
         if self.fixed_lr is not None:
