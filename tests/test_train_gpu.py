@@ -383,3 +383,44 @@ def test_cuda_graphed_train_step_matches_eager():
     if any(m.p > 0 for m in md.modules() if isinstance(m, torch.nn.Dropout)):
         tr = Trainer(md.cuda().train(), cuda_graph=True)
         assert not tr._graph_ok()
+
+
+def test_parameters_written_behind_the_trainers_back_are_seen():
+    """The GEMM operands are views of the trainer's bf16 mirror of the flat parameter buffer, refreshed after every optimizer
+    step.  A write that bypasses the trainer (model.load_state_dict after the Trainer was built) bumps the parameters'
+    versions: the stale mirror must not be used."""
+    from transformer_tts_b200 import synth
+    from transformer_tts_b200.training import Trainer
+
+    hp, sd, model = build()
+    tr = Trainer(model)
+    batch = train_batch_small()
+    tr.zero_grad()
+    l0 = float(tr.forward_backward(*batch)["loss"])
+    sd2 = synth.synth_state_dict(hp, seed=3)
+    model.load_state_dict(sd2)                       # in place, through the views of the flat buffer
+    tr.zero_grad()
+    l1 = float(tr.forward_backward(*batch)["loss"])
+    _, _, fresh = build(seed_sd=3)
+    tf = Trainer(fresh)
+    tf.zero_grad()
+    l2 = float(tf.forward_backward(*batch)["loss"])
+    assert abs(l1 - l2) <= 1e-5 * max(1.0, abs(l2)) and abs(l1 - l0) > 1e-3, (l0, l1, l2)
+    # ... and after an optimizer step the mirror is current again (operands are views of it: no per-tensor casts)
+    tr.optimizer_step()
+    from transformer_tts_b200.Models import _engine as E
+
+    w = model.decoder.layers[0].attn.out.weight
+    assert E._mirror(w) is not None and torch.equal(E._mirror(w), w.detach().to(torch.bfloat16))
+    lc = E.layer_cache(model.decoder.layers[0])
+    assert lc["wqkv"].data_ptr() == E._mirror(model.decoder.layers[0].attn.q_linear.weight).data_ptr()   # q|k|v: a view
+
+
+def train_batch_small():
+    from transformer_tts_b200 import synth
+
+    text, pos, _ = synth.synth_text_batch(3, 24, ragged=True, seed=5)
+    dur, pos_mel, f0, en = synth.synth_targets(pos, seed=5, max_dur=8)
+    mel = synth.synth_mel(pos_mel, 80, seed=5)
+    c = lambda t: t.cuda()  # noqa: E731
+    return (c(text), c((pos != 0).unsqueeze(-2)), c((pos_mel != 0).unsqueeze(-2)), c(dur), c(f0), c(en), c(mel))
