@@ -16,7 +16,19 @@ def main():
 
     hp = synth.make_tts_hp()
     r = hp.reduction_rate
-    model = build_transformer_tts(hp)
+    if "--dropout" in sys.argv:   # the reference's training construction (train.py:117-126)
+        from transformer_tts_b200.Models.transformer import Transformer
+
+        model = Transformer(hp=hp, src_vocab=hp.vocab_size, trg_vocab=hp.mel_dim, d_model_encoder=hp.d_model_encoder,
+                            N_e=hp.n_layer_encoder, n_head_encoder=hp.n_head_encoder,
+                            ff_conv_kernel_size_encoder=hp.ff_conv_kernel_size_encoder,
+                            concat_after_encoder=hp.concat_after_encoder, d_model_decoder=hp.d_model_decoder,
+                            N_d=hp.n_layer_decoder, n_head_decoder=hp.n_head_decoder,
+                            ff_conv_kernel_size_decoder=hp.ff_conv_kernel_size_decoder,
+                            concat_after_decoder=hp.concat_after_decoder, reduction_rate=r, dropout=0.1, dropout_prenet=0.5,
+                            dropout_postnet=0.5)
+    else:
+        model = build_transformer_tts(hp)
     model.load_state_dict(synth.synth_tts_state_dict(hp))
     model = model.cuda().train()
     batch, phonemes, mel_len = 32, 128, 800
