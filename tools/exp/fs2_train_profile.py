@@ -14,7 +14,10 @@ def main():
     from transformer_tts_b200.training import Trainer
 
     hp = synth.make_hp()
-    model = build_fastspeech2(hp)
+    if "--dropout" in sys.argv:   # the reference's training construction (train_fastspeech2.py:381-389)
+        model = build_fastspeech2(hp, dropout=0.1, dropout_postnet=0.5, dropout_variance_adaptor=0.5)
+    else:
+        model = build_fastspeech2(hp)
     model.load_state_dict(synth.synth_state_dict(hp))
     model = model.cuda().train()
     tr = Trainer(model, optimizer="radam")
