@@ -60,6 +60,7 @@ class DecodeState:
             raise ValueError(f"{cap} decoder positions exceed the positional table ({t['pe'].shape[0]}, modules.py:92)")
         f32, bf16 = torch.float32, torch.bfloat16
         self.pos = torch.zeros(1, device=dev, dtype=torch.int32)
+        self.done = 0                               # host copy of *pos (no device read in the loop)
         self.out_all = torch.zeros((R, cap, self.n_out), device=dev, dtype=f32)   # [mel (r frames) | stop (r)] per position
         self.x = torch.empty((R, D), device=dev, dtype=f32)        # residual stream of the current position
         self.x2 = torch.empty((R, D), device=dev, dtype=f32)
@@ -130,35 +131,47 @@ class DecodeState:
                          ldo=cap * self.n_out, pos=pos, out_pos_stride=self.n_out)
         lib.advance_pos(pos, 1)
 
+    def step_eager(self) -> None:
+        self._launch_step()
+        self.done += 1
+
+    def capture(self) -> None:
+        """Capture one decode step as a CUDA graph (on the current stream); processes no position."""
+        # an odd number of residual swaps would make the captured step end in the other buffer: 9 launches per layer
+        # leave x in self.x after an even number of layers, in self.x2 after an odd one — the head reads whichever
+        # it is inside the capture, and the next replay starts from the prenet again, so no state crosses steps
+        g = torch.cuda.CUDAGraph()
+        launches = lib.LAUNCH_COUNT
+        with torch.cuda.graph(g):
+            self._launch_step()
+        self.launches_per_step = lib.LAUNCH_COUNT - launches
+        lib.LAUNCH_COUNT = launches   # capture launched nothing
+        self.graph = g
+
+    def replay(self) -> None:
+        """One position from the captured graph, on the current stream."""
+        self.graph.replay()
+        self.done += 1
+        lib.LAUNCH_COUNT += self.launches_per_step
+
     def run(self, n_steps: int) -> None:
         """Process the next n_steps positions (all utterances)."""
-        done = int(self.pos.item())
-        if done + n_steps > self.cap:
-            raise ValueError(f"{done} + {n_steps} positions exceed the session's capacity {self.cap}")
+        if self.done + n_steps > self.cap:
+            raise ValueError(f"{self.done} + {n_steps} positions exceed the session's capacity {self.cap}")
         if n_steps <= 0:
             return
         if not self.use_cuda_graph:
             for _ in range(n_steps):
-                self._launch_step()
+                self.step_eager()
             return
         if self.graph is None:
-            # an odd number of residual swaps would make the captured step end in the other buffer: 9 launches per layer
-            # leave x in self.x after an even number of layers, in self.x2 after an odd one — the head reads whichever
-            # it is inside the capture, and the next replay starts from the prenet again, so no state crosses steps
-            self._launch_step()          # warm-up (TMA-free kernels: only the smem opt-ins and lazy module load)
+            self.step_eager()            # warm-up (TMA-free kernels: only the smem opt-ins and lazy module load)
             n_steps -= 1
             if n_steps == 0:
                 return
-            g = torch.cuda.CUDAGraph()
-            launches = lib.LAUNCH_COUNT
-            with torch.cuda.graph(g):
-                self._launch_step()
-            self.launches_per_step = lib.LAUNCH_COUNT - launches
-            lib.LAUNCH_COUNT = launches   # capture launched nothing
-            self.graph = g
+            self.capture()
         for _ in range(n_steps):
-            self.graph.replay()
-        lib.LAUNCH_COUNT += n_steps * self.launches_per_step
+            self.replay()
 
 
 class Decoder(nn.Module):
