@@ -307,6 +307,19 @@ class Trainer:
             self._wt_pairs[key] = (d, k)
         return _t(src)
 
+    def _wgrad_rows(self, dy: torch.Tensor, x: torch.Tensor, linears, n_off: int = 0) -> None:
+        """Weight and bias gradients of Linear layers whose outputs are consecutive column blocks of `dy` (q | k | v).  The
+        flat layout places their parameters — hence their gradient views — next to each other, so the blocks are the rows of
+        ONE (sum N, C) matrix: one wgrad launch that reads x once, instead of one per layer."""
+        gw = [self.G(l.weight) for l in linears]
+        gb = [self.G(l.bias) for l in linears]
+        if len(linears) > 1 and E._adjacent(gw) and E._adjacent(gb):
+            lib.conv_wgrad(dy, x, E._cat_rows(gw), n_off=n_off, N=sum(g.shape[0] for g in gw), dbias=E._cat_rows(gb))
+            return
+        for l, w, b in zip(linears, gw, gb):
+            lib.conv_wgrad(dy, x, w, n_off=n_off, N=w.shape[0], dbias=b)
+            n_off += w.shape[0]
+
     def _prepare_wt(self) -> None:
         """All dgrad operands of this backward pass in one launch (ttsb200_weight_transpose) instead of one or two torch
         copy kernels per weight.  Call after the forward (the forward operands are fresh then)."""
@@ -461,8 +474,7 @@ class Trainer:
             lib.conv_gemm(dy_bf, self._wt(lc, "wo"), self.zeros(D), block_n=192, out_bf16=dctx)
             delta = lib.attn_delta(dctx, s["ctx"], H)
             dqkv = lib.attention_bwd(s["qkv"], dctx, mask, kv, s["lse"], delta, H, drop=(pd, seed, S(f"{i}.attn")))
-            for j, lin in enumerate((a.q_linear, a.k_linear, a.v_linear)):
-                lib.conv_wgrad(dqkv, s["xn"], G(lin.weight), n_off=j * D, N=D, dbias=G(lin.bias))
+            self._wgrad_rows(dqkv, s["xn"], (a.q_linear, a.k_linear, a.v_linear))
             dxn = f32(B, T, D)
             lib.conv_gemm(dqkv, self._wt(lc, "wqkv"), self.zeros(D), block_n=192, out_f32=dxn)
             # xn = norm_1(x); y = x + attn(xn)
