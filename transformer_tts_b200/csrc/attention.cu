@@ -129,7 +129,7 @@ enum {
 // DROP: training with dropout on the probabilities (Models/modules.py:18-19): the row sum l is taken BEFORE the mask
 // (softmax, then dropout), P * m is what multiplies V.  Its own instantiation: the plain kernel keeps its registers.
 template <int NH, bool DROP = false, bool CAUSAL = false>
-__global__ void __launch_bounds__(64 + 128 * NH, DROP ? 1 : 2)
+__global__ void __launch_bounds__(64 + 128 * NH, 2)
 attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmQ32,
                      const __grid_constant__ CUtensorMap tmKV, const __grid_constant__ CUtensorMap tmKV32,
                      const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmO32,
