@@ -700,6 +700,9 @@ def train_record(args, rank: int, world: int, steps: int = 5):
                                                 "graph_kernel_nodes": getattr(tg, "graph_launches", None),
                                                 "captured": bool(tg._graphs)}
             del tg
+        except Exception as ex:  # noqa: BLE001
+            rec["single_process_cuda_graph"] = {"error": str(ex)[:200]}
+        try:
             # the reference's training construction (train_fastspeech2.py:381-389: dropout 0.1, PostNet 0.5, variance adaptor
             # 0.5): counter-based masks in the kernels, eager steps (a graph replay would repeat the masks)
             md = build_fastspeech2(hp, dropout=0.1, dropout_postnet=0.5, dropout_variance_adaptor=0.5)
@@ -721,9 +724,8 @@ def train_record(args, rank: int, world: int, steps: int = 5):
                                              "active": bool(td.drop.active)}
             del td, md
         except Exception as ex:  # noqa: BLE001
-            rec["single_process_cuda_graph"] = {"error": str(ex)[:200]}
-        tr = None
-    del tr, model, dev, out
+            rec["with_reference_dropout"] = {"error": str(ex)[:200]}
+    tr = model = dev = out = None     # drop the references (a failed sub-measurement above may have deleted some already)
     torch.cuda.empty_cache()
     return rec
 
